@@ -1,0 +1,99 @@
+"""Per-correlation configuration holder (init-time plumbing).
+
+Follows the attribute surface of the reference's vega/correlation_item.py:8-140
+that the data reader, the plan builder and the oracle consume: tracer names and
+types, the parsed ini sections, coordinate grids, the metal-correlation list.
+Small-scale marginalisation templates (vega/correlation_item.py:169-275) are not
+built yet; asking for them raises.
+"""
+
+
+class CorrelationItem:
+    cosmo = None
+    model_coordinates = None
+    dist_model_coordinates = None
+    data_coordinates = None
+    low_mem_mode = False
+
+    def __init__(self, config, model_pk=False):
+        self.config = config
+        self.model_pk = model_pk
+        data_cfg = config['data']
+        model_cfg = config['model']
+        self.name = data_cfg.get('name')
+        self.tracer1 = {'name': data_cfg.get('tracer1'), 'type': data_cfg.get('tracer1-type')}
+        self.tracer2 = {'name': data_cfg.get('tracer2', self.tracer1['name']),
+                        'type': data_cfg.get('tracer2-type', self.tracer1['type'])}
+
+        self.cov_rescale = data_cfg.getfloat('cov_rescale', None)
+        self.has_distortion = data_cfg.getboolean('distortion', True)
+        self.has_data = data_cfg.getboolean('has_datafile', True)
+        if 'filename' not in data_cfg:
+            self.has_data = False
+        self.test_flag = data_cfg.getboolean('test', False)
+
+        self.new_metals = model_cfg.getboolean('new_metals', False)
+        if self.new_metals:
+            raise NotImplementedError(
+                'new_metals (metal matrices histogrammed from forest weights, '
+                'vega/metals.py:502-752) is init-time work outside the B200 hot path; '
+                'supply the metal matrices in a metal file instead.')
+
+        self.marginalize_small_scales = {}
+        for key, name in (('marginalize-below-rtmax', 'rtmax'), ('marginalize-above-rtmin', 'rtmin'),
+                          ('marginalize-below-rpmax', 'rpmax'), ('marginalize-above-rpmin', 'rpmin')):
+            value = model_cfg.getfloat(key, 0)
+            if value > 0:
+                self.marginalize_small_scales[name] = value
+        if model_cfg.getboolean('marginalize-all-rmin-cuts', False):
+            self.marginalize_small_scales['all-rmin'] = True
+        if self.marginalize_small_scales:
+            raise NotImplementedError('Small-scale marginalisation templates are not built yet.')
+        self.marginalize_small_scales_prior_sigma = model_cfg.getfloat(
+            'marginalize-prior-sigma', 10.0)
+        self.marginalize_match_data_bins = model_cfg.getboolean(
+            'marginalize-match-data-bins', False)
+        self.fit_marg_scales = model_cfg.getboolean('fit-marginalized-scales', False)
+
+        self.has_metals = False
+        self.has_bb = False
+        self.tracer_catalog = {}
+        self.metal_correlations = []
+
+    def init_metals(self, tracer_catalog, metal_correlations):
+        """Canonical, de-duplicated metal-correlation list with the main tracers kept
+        in their slot (vega/correlation_item.py:76-105)."""
+        self.tracer_catalog = tracer_catalog
+        self.metal_correlations = []
+        for corr in metal_correlations:
+            pair = tuple(sorted([corr[0], corr[1]]))
+            if pair[0] == self.tracer2['name'] or pair[1] == self.tracer1['name']:
+                pair = (pair[1], pair[0])
+            if pair not in self.metal_correlations:
+                self.metal_correlations.append(pair)
+        self.has_metals = True
+
+    def init_broadband(self, coeff_binning_model):
+        self.coeff_binning_model = coeff_binning_model
+        self.has_bb = True
+
+    def init_coordinates(self, model_coordinates, dist_model_coordinates=None,
+                         data_coordinates=None):
+        self.model_coordinates = model_coordinates
+        self.data_coordinates = model_coordinates if data_coordinates is None \
+            else data_coordinates
+        self.dist_model_coordinates = model_coordinates if dist_model_coordinates is None \
+            else dist_model_coordinates
+
+    def init_cosmo(self, cosmo_params):
+        """The reference builds a picca Cosmo here (vega/correlation_item.py:139-151),
+        used only by new-bias-evolution and new_metals; both need picca, which is
+        outside this path, so only the parameters are kept."""
+        self.cosmo_params = cosmo_params
+        self.cosmo = None
+
+    def check_if_blind_corr(self, blind_tracers):
+        if 'all' in blind_tracers:
+            return True
+        return any(t in self.tracer1['name'] or t in self.tracer2['name']
+                   for t in blind_tracers)

@@ -1,0 +1,137 @@
+"""Host-side helpers shared by the init-time layer of the B200 path.
+
+Mirrors the parts of the reference's vega/utils.py the hot path depends on:
+exceptions (vega/utils.py:444-453), file lookup (:230-268), the growth factor
+(:128-227, init-time only) and the masked covariance inverse / log-determinant
+(:271-318, init-time only).  The per-evaluation helpers of that file
+(bias_beta, sinc, smoothing kernels) live on the device: see csrc/vg_pk.cuh.
+"""
+import os
+from functools import lru_cache
+from pathlib import Path
+
+import numpy as np
+from scipy.integrate import quad
+from scipy.interpolate import interp1d
+
+PACKAGE_DIR = Path(__file__).resolve().parent
+REPO_DIR = PACKAGE_DIR.parent
+
+# Extra directories searched by find_file (the directory of the main ini is
+# appended by VegaInterface so relative paths next to it resolve)
+_EXTRA_SEARCH_DIRS = []
+
+BLIND_FIXED_PARS = ['ap_full', 'at_full', 'aiso_full', 'epsilon_full', 'phi_full']
+DEFAULT_GROWTH_RATE = 0.970386
+
+
+class VegaModelError(Exception):
+    """Model-domain failure; chi2 turns it into the 1e100 sentinel
+    (vega/vega_interface.py:268-279)."""
+
+
+class VegaBoundsError(VegaModelError):
+    pass
+
+
+class VegaArinyoError(VegaModelError):
+    pass
+
+
+class VegaDeviceError(RuntimeError):
+    """The CUDA library is missing or a kernel launch failed.  There is no CPU
+    fallback: the product path fails loudly."""
+
+
+def add_search_dir(path):
+    path = Path(path)
+    if path not in _EXTRA_SEARCH_DIRS:
+        _EXTRA_SEARCH_DIRS.append(path)
+
+
+def find_file(path):
+    """Resolve an input path the way vega/utils.py:230-268 does: absolute (or
+    cwd-relative) first, then the packaged models, then the tests tree, then the
+    repository root; finally any directory registered with add_search_dir."""
+    input_path = Path(os.path.expandvars(str(path)))
+    if input_path.is_file():
+        return input_path
+    roots = [PACKAGE_DIR / 'models', REPO_DIR / 'tests', REPO_DIR / 'tests' / 'configs',
+             REPO_DIR] + _EXTRA_SEARCH_DIRS
+    for root in roots:
+        candidate = root / input_path
+        if candidate.is_file():
+            return candidate
+    raise RuntimeError('The path/file does not exists: ', input_path)
+
+
+def _hubble(z, Omega_m, Omega_de):
+    Omega_k = 1 - Omega_m - Omega_de
+    return np.sqrt(Omega_m * (1 + z)**3 + Omega_de + Omega_k * (1 + z)**2)
+
+
+def _growth_integrand(a, Omega_m, Omega_de):
+    z = 1 / a - 1
+    return 1. / (a * _hubble(z, Omega_m, Omega_de))**3
+
+
+@lru_cache(maxsize=32)
+def get_growth_interp(Omega_m, Omega_de):
+    """Cubic interpolation of D(z) on 1000 nodes in z in [0, 10]
+    (vega/utils.py:175-205; Dodelson eq. 7.77)."""
+    z_grid = np.linspace(0, 10, 1000)
+    growth = np.zeros(1000)
+    for i, z in enumerate(z_grid):
+        integral = quad(_growth_integrand, 0, 1 / (1 + z), args=(Omega_m, Omega_de))[0]
+        growth[i] = 5. / 2. * Omega_m * _hubble(z, Omega_m, Omega_de) * integral
+    return interp1d(z_grid, growth, kind='cubic')
+
+
+def growth_function(z, Omega_m, Omega_de):
+    return get_growth_interp(Omega_m, Omega_de)(z)
+
+
+def compute_masked_invcov(cov_mat, data_mask):
+    """inv(cov[mask][:, mask]) (vega/utils.py:271-299)."""
+    masked_cov = cov_mat[:, data_mask][data_mask, :]
+    try:
+        np.linalg.cholesky(masked_cov)
+    except np.linalg.LinAlgError:
+        print('WARNING: Reduced matrix is not positive definite')
+    return np.linalg.inv(masked_cov)
+
+
+def compute_log_cov_det(cov_mat, data_mask):
+    """log det of the masked covariance (vega/utils.py:302-318)."""
+    masked_cov = cov_mat[:, data_mask][data_mask, :]
+    return np.linalg.slogdet(masked_cov)[1]
+
+
+def tracer_bias_beta(params, name):
+    """(bias, beta) of one tracer from any two of (bias, bias_eta, beta)
+    (vega/utils.py:45-81).  Works on floats and on symbolic registers."""
+    growth_rate = params.get('growth_rate', DEFAULT_GROWTH_RATE)
+    bias = params.get('bias_' + name, None)
+    bias_eta = params.get('bias_eta_' + name, None)
+    beta = params.get('beta_' + name, None)
+    err_msg = ("For each tracer, you need to specify two of these three:"
+               " (bias, bias_eta, beta). If all three are given, we use bias and beta. "
+               f"Offending tracer: {name}")
+    if bias is None:
+        assert bias_eta is not None and beta is not None, err_msg
+        bias = bias_eta * growth_rate / beta
+    if bias_eta is None:
+        assert bias is not None and beta is not None, err_msg
+    if beta is None:
+        assert bias is not None and bias_eta is not None, err_msg
+        beta = bias_eta * growth_rate / bias
+    return bias, beta
+
+
+def bias_beta(params, tracer1_name, tracer2_name):
+    """vega/utils.py:84-108."""
+    bias1, beta1 = tracer_bias_beta(params, tracer1_name)
+    if tracer1_name == tracer2_name:
+        return bias1, beta1, bias1, beta1
+    bias2, beta2 = tracer_bias_beta(params, tracer2_name)
+    return bias1, beta1, bias2, beta2

@@ -1,0 +1,239 @@
+"""VegaInterface: the drop-in boundary of the B200 path.
+
+Keeps the reference's public surface (vega/vega_interface.py:22-446):
+``compute_model(params)``, ``chi2(params)``, ``log_lik(params)`` take a PARTIAL
+parameter dict merged over ``self.params`` and return dict-of-arrays / float, so
+iminuit, PolyChord adapters and the run_vega_mc scripts can drive it unchanged.
+What is new is underneath: every call is a batch of one through the batched
+engine (``chi2_batch(theta[B, P])``, ``log_lik_batch``, ``compute_model_batch``),
+which runs hand-written sm_100a kernels through the C ABI of include/vega_b200.h.
+There is no CPU fallback: without the CUDA library these methods raise.
+
+Init-time work (ini parsing, FITS reading, masks, C^-1) stays on the host and
+mirrors vega/vega_interface.py:36-206,665-954.
+"""
+import configparser
+import copy
+import os
+from pathlib import Path
+
+import numpy as np
+
+from . import fitsio, utils
+from .correlation_item import CorrelationItem
+from .data import Data
+from .parameters import get_default_values
+
+
+def _read_ini(path):
+    config = configparser.ConfigParser()
+    config.optionxform = lambda option: option
+    config.read(path)
+    return config
+
+
+class VegaInterface:
+    _blind = None
+    _use_global_cov = False
+    global_cov = None
+
+    def __init__(self, main_path, device=None, batch_chunk=None):
+        main_path = utils.find_file(main_path)
+        utils.add_search_dir(Path(main_path).resolve().parent)
+        self.main_config = _read_ini(main_path)
+
+        self.fiducial = self._read_fiducial(self.main_config['fiducial'])
+        self.fiducial['z_eff'] = self.main_config['data sets'].getfloat('zeff')
+        output_cfg = self.main_config['output'] if 'output' in self.main_config else {}
+        self.fiducial['save-components'] = False
+        if 'output' in self.main_config:
+            self.fiducial['save-components'] = (
+                output_cfg.getboolean('write_cf', False) or output_cfg.getboolean('write_pk', False))
+        ini_files = self.main_config['data sets'].get('ini files').split()
+        global_cov_file = self.main_config['data sets'].get('global-cov-file', None)
+
+        control = self.main_config['control'] if 'control' in self.main_config else None
+        self.model_pk = control.getboolean('model_pk', False) if control else False
+        self.low_mem_mode = False
+        self.marginalize_in_fit = control.getboolean('marginalize-in-fit', False) \
+            if control else False
+        if self.marginalize_in_fit:
+            raise NotImplementedError('marginalize-in-fit is not built yet.')
+
+        self.corr_items = {}
+        for path in ini_files:
+            config = _read_ini(utils.find_file(os.path.expandvars(path)))
+            name = config['data'].get('name')
+            self.corr_items[name] = CorrelationItem(config, self.model_pk)
+
+        self.params = self._read_parameters(self.corr_items, self.main_config['parameters'])
+        self.sample_params = self._read_sample(self.main_config['sample'])
+
+        use_template_growth_rate = control.getboolean('use_template_growth_rate', True) \
+            if control else True
+        if use_template_growth_rate and 'growth_rate' in self.fiducial:
+            assert 'growth_rate' not in self.sample_params['limits'], (
+                "use_template_growth_rate is True, but growth_rate is in the sample params.")
+            self.params['growth_rate'] = self.fiducial['growth_rate']
+        elif 'growth_rate' not in self.fiducial:
+            if 'growth_rate' in self.params:
+                self.fiducial['growth_rate'] = self.params['growth_rate']
+        for key in ('par_sigma_smooth', 'per_sigma_smooth'):
+            if key in self.params:
+                self.fiducial[key] = self.params[key]
+
+        self._has_data = all(item.has_data for item in self.corr_items.values())
+        self.data = {name: (Data(item) if self._has_data else None)
+                     for name, item in self.corr_items.items()}
+
+        self._blind = False
+        self._rnsps = None
+        if self._has_data and any(d.blind for d in self.data.values()):
+            raise NotImplementedError(
+                'Blinded data sets need the NERSC blinding files (vega/utils.py:337-349).')
+
+        self.mc_config = None
+        if 'monte carlo' in self.main_config:
+            self.mc_config = {'params': {p: float(v) for p, v in
+                                         self.main_config['mc parameters'].items()},
+                              'sample': self._read_sample(self.main_config['monte carlo'])}
+
+        self.priors = {}
+        if 'priors' in self.main_config:
+            self.priors = self._init_priors(self.main_config['priors'])
+            for param in self.priors:
+                not_sampled = param not in self.sample_params['limits']
+                if self.mc_config is not None:
+                    not_sampled &= param not in self.mc_config['sample']['limits']
+                if not_sampled:
+                    raise ValueError(
+                        f'Prior specified for a parameter that is not sampled: {param}')
+
+        cov_scale = control.getfloat('cov_scale', None) if control else None
+        if global_cov_file is not None:
+            self.read_global_cov(global_cov_file, cov_scale)
+
+        self.corr_num_marg_modes = {name: 0 for name in self.corr_items}
+        self.run_sampler = control.getboolean('run_sampler', False) if control else False
+        self.sampler = control.get('sampler', None) if control else None
+        self.monte_carlo = False
+        self.minimizer = None
+        self.analysis = None
+        self.output = None
+        self.plots = None
+        self.models = {}
+
+        self._device = device
+        self._batch_chunk = batch_chunk
+        self._engine = None
+        self._fast_metals = False
+
+    # -- init-time readers (vega/vega_interface.py:665-851) ---------------------------
+    @staticmethod
+    def _read_fiducial(fiducial_config):
+        path = utils.find_file(os.path.expandvars(fiducial_config.get('filename')))
+        hdul = fitsio.open(path)
+        header = hdul[1].header
+        fiducial = {
+            'z_fiducial': header['ZREF'], 'Omega_m': header['OM'], 'Omega_de': header['OL'],
+            'k': np.ascontiguousarray(hdul[1].data['K'], dtype=float),
+            'pk_full': np.ascontiguousarray(hdul[1].data['PK'], dtype=float),
+            'pk_smooth': np.ascontiguousarray(hdul[1].data['PKSB'], dtype=float),
+        }
+        if 'F_ZREF' in header:
+            fiducial['growth_rate'] = header['F_ZREF']
+        return fiducial
+
+    @staticmethod
+    def _read_parameters(corr_items, parameters_config):
+        params = {}
+        for item in corr_items.values():
+            if 'parameters' in item.config:
+                for param, value in item.config.items('parameters'):
+                    params[param] = float(value)
+        for param, value in parameters_config.items():
+            params[param] = float(value)
+        return params
+
+    def _read_sample(self, sample_config):
+        """``param = min max [start [sigma]]`` or ``param = True`` with defaults from
+        parameters/default_values.txt (vega/vega_interface.py:737-816)."""
+        sample = {'limits': {}, 'values': {}, 'errors': {}, 'fix': {}}
+        defaults = get_default_values()
+
+        def need_default(param):
+            if param not in defaults:
+                raise ValueError(f'Default values not found for: {param}. Please add them to '
+                                 'default_values.txt, or provide the full sampling specification.')
+
+        for param, values in sample_config.items():
+            if param not in self.params:
+                print(f'Warning: You tried sampling the parameter: {param}. As this parameter '
+                      'was not specified under [parameters], it will be skipped.')
+                continue
+            words = values.split()
+            if len(words) > 1:
+                lower = None if words[0] == 'None' else float(words[0])
+                upper = None if words[1] == 'None' else float(words[1])
+                sample['limits'][param] = (lower, upper)
+            else:
+                if words[0] not in ['True', 'true', 't', 'y', 'yes']:
+                    continue
+                need_default(param)
+                sample['limits'][param] = defaults[param]['limits']
+            if len(words) > 2:
+                sample['values'][param] = float(words[2])
+            else:
+                need_default(param)
+                sample['values'][param] = self.params[param]
+            if len(words) > 3:
+                assert len(words) == 4
+                sample['errors'][param] = float(words[3])
+            else:
+                need_default(param)
+                sample['errors'][param] = defaults[param]['error']
+            sample['fix'][param] = False
+        return sample
+
+    @staticmethod
+    def _init_priors(prior_config):
+        priors = {}
+        for param, prior in prior_config.items():
+            words = prior.split()
+            if len(words) != 3:
+                raise ValueError('Prior configuration must have the format:'
+                                 ' "<param> = gaussian <mean> <sigma>"')
+            if words[0] not in ['gaussian', 'Gaussian']:
+                raise ValueError('Only gaussian priors are supported.')
+            priors[param] = np.array(words[1:]).astype(float)
+        return priors
+
+    def read_global_cov(self, global_cov_file, scale=None):
+        """Joint covariance over all correlations (vega/vega_interface.py:888-954)."""
+        with fitsio.open(utils.find_file(global_cov_file)) as hdul:
+            self.global_cov = np.array(hdul[1].data['COV'], dtype=float)
+        if scale is not None:
+            self.global_cov *= scale
+        self._use_global_cov = True
+        self.full_data_mask = np.concatenate(
+            [self.data[name].data_mask for name in self.corr_items])
+        self.full_model_mask = np.concatenate(
+            [self.data[name].model_mask for name in self.corr_items])
+        self.masked_global_invcov = utils.compute_masked_invcov(
+            self.global_cov, self.full_data_mask)
+        self.masked_global_log_cov_det = utils.compute_log_cov_det(
+            self.global_cov, self.full_data_mask)
+
+    @staticmethod
+    def _gaussian_chi2_prior(value, mean, sigma):
+        return (value - mean)**2 / sigma**2
+
+    @staticmethod
+    def _gaussian_lik_prior(sigma):
+        return -0.5 * np.log(2 * np.pi) - np.log(sigma)
+
+    def _get_lcl_prms(self, params=None):
+        local_params = copy.deepcopy(self.params)
+        if params is not None:
+            local_params |= params
+        return local_params
