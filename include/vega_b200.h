@@ -1,11 +1,218 @@
-/* vega_b200 C ABI -- placeholder, filled as the library grows */
+/* vega_b200 -- C ABI of the B200 model-evaluation + likelihood path.
+ *
+ * The reference (andreicuceu/vega) is pure Python and has no FFI; this header is the
+ * boundary a maintainer would bind (ctypes stub in INTEGRATION.md) to replace
+ *   VegaInterface.compute_model / chi2 / log_lik   vega/vega_interface.py:208-387
+ *   Model.compute                                  vega/model.py:157-187
+ *   PowerSpectrum.compute                          vega/power_spectrum.py:87-196
+ *   PktoXi.compute / compute_pk_ells               vega/pktoxi.py:79-163
+ *   CorrelationFunction.compute                    vega/correlation_func.py:117-198
+ *   Metals.compute                                 vega/metals.py:258-336
+ *   BroadbandPolynomials.compute                   vega/broadband_poly.py:74-198
+ * for a BATCH of parameter vectors.  Plain pointers and sizes only, no torch types.
+ *
+ * Conventions: every function returns 0 on success (VG_ERR_* otherwise, text from
+ * vg_last_error()).  All arithmetic is FP64.  "dev" pointers are device pointers, "host"
+ * pointers are host pointers; the caller owns every buffer it passes.  Work is queued on
+ * the given CUDA stream (a cudaStream_t passed as void*) and is asynchronous with respect
+ * to the host unless stated.  status[b] != 0 means the reference would have raised a
+ * VegaModelError for that vector (vega/vega_interface.py:268-279): its chi2 is 1e100.
+ */
 #ifndef VEGA_B200_H
 #define VEGA_B200_H
+#include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
+
+#define VG_MAX_BB_TERMS 8
+
+/* P(k,mu) factor bits (vega/power_spectrum.py:118-194) */
+#define VG_F_ARINYO   (1u << 0)   /* compute_dnl_arinyo      :435-479 */
+#define VG_F_MCDONALD (1u << 1)   /* compute_dnl_mcdonald    :419-433 */
+#define VG_F_GK       (1u << 2)   /* compute_Gk              :481-502 */
+#define VG_F_PEAKNL   (1u << 3)   /* compute_peak_nl         :382-417 */
+#define VG_F_FSGAUSS  (1u << 4)   /* fullshape gauss         :504-553 */
+#define VG_F_FSEXP    (1u << 5)   /* fullshape exp           :560-586 */
+#define VG_F_VELO     (1u << 6)   /* velocity dispersion     :588-636 */
+#define VG_F_KDAMP    (1u << 7)   /* k^n damping  vega/utils.py:423-441 */
+
+/* One P(k,mu) -> xi evaluation: the (PowerSpectrum, CorrelationFunction) pair the
+ * reference builds per component (peak / smooth, vega/model.py:60-66) and per metal
+ * correlation (vega/metals.py:95-142).  Every idx_* is a column of the full parameter
+ * vector (or -1 when the parameter is absent from the configuration). */
+typedef struct vg_eval_desc {
+  /* ---- P(k,mu) ---- */
+  int32_t pk_lin_sel;       /* 0: pk_full - pk_smooth (peak), 1: pk_smooth, 2: pk_full */
+  int32_t is_peak;
+  int32_t fast_metals;      /* Kaiser term without b1*b2 (vega/power_spectrum.py:219-220) */
+  int32_t same_tracer;
+  int32_t idx_bias[2], idx_beta[2], idx_bias_eta[2];   /* vega/utils.py:45-108 */
+  int32_t idx_growth_rate;  /* -1: 0.970386 */
+  int32_t uv_on[2];         /* UV / HeII applies to tracer t (LYA only, :111-114) */
+  int32_t uvb, heii;
+  int32_t idx_lambda_uv, idx_bias_gamma, idx_bias_prim, idx_lambda_heii, idx_bias_gamma_e;
+  int32_t hcd_model;        /* 0 none, 1 Rogers2018, 2 fvoigt, 3 sinc  (:263-380) */
+  int32_t hcd_on[2];
+  int32_t idx_bias_hcd, idx_beta_hcd, idx_L0;   /* idx_L0 -1: L0 = 1 */
+  int32_t hcd_grid;         /* >=0: static F(k_par) grid; -1: F evaluated per vector */
+  int32_t static_grid;      /* >=0: grid holding the product of `static_mask` factors */
+  uint32_t dyn_mask;        /* factors evaluated per parameter vector */
+  uint32_t static_mask;     /* factors folded into `static_grid` (their parameters are fixed) */
+  int32_t arinyo_mode;      /* 2: LYxLY, 1: one LY tracer (sqrt), 0: none (ones) */
+  int32_t idx_arinyo[6];    /* q1 q2 kv av bv kp; q2 = -1 -> 0 */
+  int32_t idx_sigmaNL[2];   /* par, per; one may be -1 -> derived with 1+f (:391-405) */
+  int32_t idx_fs_gauss[4];  /* par1 per1 par2 per2: G(par1,per1)*G(par2,per2) */
+  int32_t idx_fs_exp[4];    /* par_sigma per_sigma par_exp per_exp */
+  int32_t velo_kind;        /* 1 gauss, 2 lorentz */
+  int32_t idx_velo[2];      /* per tracer, -1 when the tracer is not discrete */
+  int32_t kdamp_power;
+  double gk_drp, gk_drt;    /* binning sizes; 0 skips that sinc (:493-500) */
+  double kdamp_scale;
+  /* ---- xi(rp,rt) ---- */
+  int32_t coord_set;        /* coordinate table this evaluation is gathered on */
+  int32_t scale_form;       /* 0: ap=at=1, 1: ap_at, 2: aiso_epsilon, 3: phi_alpha
+                               (vega/scale_parameters.py:38-230, resolved per component) */
+  int32_t idx_scale[2];
+  int32_t scale_form_sys;   /* same, for the rel/asy terms (get_ap_at without corr name) */
+  int32_t idx_scale_sys[2];
+  int32_t idx_drp;          /* drp_{QSO} for cross-correlations, -1 otherwise */
+  int32_t single_ell;       /* -1: sum of all multipoles */
+  int32_t zevol_kind[2];    /* 0 standard power law, 1 Croom (:276-370) */
+  int32_t idx_alpha[2];
+  int32_t idx_croom[2];
+  int32_t radiation;        /* QSO radiation (smooth component only, :446-489) */
+  int32_t idx_qso_rad[4];   /* strength asymmetry lifetime decrease */
+  int32_t rescale_sys;      /* rescale-coords-systematics */
+  int32_t rel, asy;         /* relativistic / standard asymmetry (:491-551) */
+  int32_t idx_Arel[2], idx_Aasy[3];
+  int32_t uv_shot;          /* UVB shot noise (:628-686) */
+  int32_t idx_uvshot[3];    /* lambda_uv, bias_gamma(_e), uv_shotnoise_amp */
+  /* ---- output ---- */
+  int32_t out_slot;         /* 0: peak core, 1: smooth core, 2+c: metal correlation c */
+  int32_t weight_bias;      /* 1: multiply by b1*b2 of the pair (vega/metals.py:316-334) */
+  int32_t idx_weight_extra; /* bias_{M1}_{M2} (separate-metal-auto-biases), -1 none */
+  double weight_const;      /* 2 for M1 != M2 in an auto-correlation (vega/metals.py:238-239) */
+} vg_eval_desc;
+
+/* One broadband term (vega/broadband_poly.py:23-198) */
+typedef struct vg_bb_term {
+  int32_t kind;             /* 0: polynomial sum_ij a_ij x1^i x2^j, 1: Gaussian sky */
+  int32_t position;         /* 0 pre-mul, 1 pre-add, 2 post-mul, 3 post-add */
+  int32_t n_coef;           /* polynomial: number of (i,j) terms */
+  int32_t design_offset;    /* polynomial: first row of the design table for this term */
+  int32_t idx_coef_first;   /* unused (coefficients are listed in idx_coef) */
+  int32_t idx_sky[2];       /* scale-sky, sigma-sky */
+  int32_t idx_coef[32];
+} vg_bb_term;
+
+typedef struct vg_plan vg_plan;
+
 const char* vg_last_error(void);
 int vg_version(void);
+/* sizeof(vg_eval_desc) / sizeof(vg_bb_term) as compiled: bindings check their mirrors */
+int vg_sizeof_eval_desc(void);
+int vg_sizeof_bb_term(void);
+
+/* ---------------------------------------------------------------------------------
+ * Plan = the static state VegaInterface.__init__ builds once (vega/vega_interface.py:36-206):
+ * templates, grids, matrices, data, the parameter-name -> column map.  Host pointers
+ * are copied; the plan owns its device memory.
+ * ------------------------------------------------------------------------------- */
+
+/* n_params: length of the full parameter vector (every entry of VegaInterface.params plus
+ * derived columns); base: its fiducial values; theta_cols[n_theta]: the columns a batch row
+ * theta[b, 0..n_theta) overwrites (the [sample] set).  k, pk_*: the fiducial template
+ * (vega/vega_interface.py:665-703), pk_fid already rescaled to z_eff
+ * (vega/power_spectrum.py:72-73).  mu[nmu]: midpoint nodes (vega/power_spectrum.py:76-78);
+ * wleg[n_ell][nmu] = dmu*(2l+1)*L_l(mu) (vega/pktoxi.py:55,138). */
+int vg_plan_create(int32_t n_params, const double* base, int32_t n_theta, const int32_t* theta_cols,
+                   int32_t nk, const double* k, const double* pk_full, const double* pk_smooth,
+                   const double* pk_fid, int32_t nmu, const double* mu, int32_t n_ell,
+                   const double* wleg, int32_t idx_bao_amp, vg_plan** out);
+int vg_plan_destroy(vg_plan* plan);
+/* Fvoigt profile table for model-hcd = fvoigt (vega/power_spectrum.py:360-380) */
+int vg_plan_set_fvoigt(vg_plan* plan, int32_t n, const double* x, const double* f);
+/* UVB shot-noise A(tau) table (vega/correlation_func.py:597-626) */
+int vg_plan_set_uvshot_table(vg_plan* plan, int32_t n, const double* tau, const double* a);
+/* Gaussian priors (vega/vega_interface.py:423-446) */
+int vg_plan_set_priors(vg_plan* plan, int32_t n, const int32_t* cols, const double* mean,
+                       const double* sigma);
+/* A Hankel + spline operator set: for each of n_ell multipoles an operator
+ * op[l][2*n_out][nk_pad] (rows 0..n_out: xi at the knots; rows n_out..2n_out: spline second
+ * derivatives, both linear in P_l(k)) and the knots xk[l][n_out] = log r.  It restates
+ * mcfit.P2xi + interp1d(cubic) (vega/pktoxi.py:141-152) or Pk2Mp + splrep
+ * (vega/pktoxi.py:230-319).  bounds_error: 1 = out-of-range r flags VG_STATUS_BOUNDS
+ * (interp1d), 0 = end-polynomial extrapolation (splev).  ells[l]: multipole order. */
+int vg_plan_add_hankel(vg_plan* plan, int32_t n_ell, const int32_t* ells, int32_t n_out,
+                       const double* xk, const double* op, int32_t bounds_error, int32_t* id);
+
+int vg_plan_add_corr(vg_plan* plan, int32_t hankel_id, int32_t n_model, int32_t n_dist,
+                     int32_t* corr_id);
+/* Coordinate table of n_model bins: tab[5][n_model] = r, mu, log((1+z)/(1+z_eff)),
+ * (1+z)^2, growth factor ratio squared (vega/correlation_func.py:46-48,76-80,372-403). */
+int vg_corr_add_coords(vg_plan* plan, int32_t corr, const double* tab, double opz_eff2,
+                       int32_t* coord_set);
+int vg_corr_add_eval(vg_plan* plan, int32_t corr, const vg_eval_desc* desc, int32_t* eval_id);
+/* Static spline tables of the relativistic / asymmetry multipoles of the linear P(k)
+ * (vega/pktoxi.py:321-382): which = 0 rel l=1, 1 rel l=3, 2 asy l=0, 3 asy l=2;
+ * tab[3][n] = knots (log r), values, second derivatives. */
+int vg_corr_set_static_xi(vg_plan* plan, int32_t corr, int32_t which, int32_t n, const double* tab);
+/* Metal matrix of metal slot c, [n_model][n_model] row-major (vega/metals.py:338-367).
+ * Slots never set are identity (the reference's `test` flag, vega/data.py:683-684). */
+int vg_corr_set_metal_matrix(vg_plan* plan, int32_t corr, int32_t slot, const double* mat);
+/* Distortion matrix [n_dist][n_model] (vega/model.py:143-144); never set = identity. */
+int vg_corr_set_distortion(vg_plan* plan, int32_t corr, const double* dmat);
+/* DESI instrumental systematics: amp * table[n_model] added to the smooth component
+ * (vega/correlation_func.py:553-595, vega/model.py:133-135). */
+int vg_corr_set_inst_sys(vg_plan* plan, int32_t corr, const double* table, int32_t idx_amp,
+                         double amp_default);
+/* Broadband terms.  design_pre[rows][n_model], design_post[rows][n_dist]: monomials
+ * x1^i x2^j; sky_pre[2][n_model] / sky_post[2][n_dist]: rt and the 0<=rp<binsize window. */
+int vg_corr_set_broadband(vg_plan* plan, int32_t corr, int32_t n_terms, const vg_bb_term* terms,
+                          int32_t rows_pre, const double* design_pre, int32_t rows_post,
+                          const double* design_post, const double* sky_pre, const double* sky_post);
+/* Masked data of one correlation (vega/data.py:169-250,397-413): mask_idx[n_mask] are the
+ * distorted-model bins kept by the cuts, data[n_mask] the masked data vector, invcov
+ * [n_mask][n_mask] the inverse masked covariance (NULL = identity).  May be called again
+ * to swap in a Monte Carlo mock (vega/vega_interface.py:296-312). */
+int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t* mask_idx,
+                     const double* data, const double* invcov);
+/* Global covariance over all correlations (vega/vega_interface.py:888-954) */
+int vg_plan_set_global_invcov(vg_plan* plan, int32_t n_total, const double* invcov);
+/* Uploads everything, builds the static factor grids on the device. Synchronous. */
+int vg_plan_finalize(vg_plan* plan, void* stream);
+/* Largest number of vectors processed per pass (workspace is sized for it); default 1024 */
+int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
+/* Status bits raised while building the static grids (e.g. VG_STATUS_ARINYO): they apply
+ * to every vector */
+int vg_plan_static_status(const vg_plan* plan);
+/* Bytes of device memory held by the plan (static state + current workspace) */
+int64_t vg_plan_device_bytes(const vg_plan* plan);
+
+/* ---------------------------------------------------------------------------------
+ * Hot path.  theta_dev[B][n_theta] row-major device memory.
+ * ------------------------------------------------------------------------------- */
+/* compute_model for a batch: xi_out_dev[c] -> [B][n_dist_c] (vega/vega_interface.py:208-248) */
+int vg_model_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* const* xi_out_dev,
+                   int32_t* status_dev, void* stream);
+/* chi2 for a batch incl. priors (vega/vega_interface.py:250-325); status != 0 -> 1e100 */
+int vg_chi2_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* chi2_dev,
+                  int32_t* status_dev, void* stream);
+/* Same with HOST buffers: pinned staging + H2D of theta, D2H of chi2/status; synchronous. */
+int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, double* chi2_host,
+                       int32_t* status_host, void* stream);
+/* Per-stage taps for parity tests. stage: 0 P(k,mu) of one evaluation [B][nmu][nk];
+ * 1 multipoles [B][n_eval][n_ell][nk_pad]; 2 knot tables [B][n_eval][n_ell][2][n_out];
+ * 3 per-evaluation xi [B][n_eval][n_model]. */
+int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
+                   const double* theta_dev, int64_t B, double* out_dev, int32_t* status_dev,
+                   void* stream);
+int64_t vg_stage_size(const vg_plan* plan, int32_t corr, int32_t stage);
+/* Number of kernels launched by the library since the last call (bench bookkeeping) */
+int64_t vg_launch_count(int reset);
+
+/* Stand-alone FP64 tensor-core GEMM C[m,n] = alpha sum_k A[m,k] B[n,k] + beta C (tests) */
 int vg_dgemm_tn(const double* A, const double* B, double* C, int M, int N, int K,
                 long long lda, long long ldb, long long ldc, double alpha, double beta,
                 int splits, double* workspace, void* stream);

@@ -1,14 +1,22 @@
-// C-ABI of the vega_b200 CUDA library (see include/vega_b200.h).
+// C-ABI of the vega_b200 CUDA library (see include/vega_b200.h): plan construction and
+// the kernel sequence of the batched model / chi2 evaluation.
+#include <algorithm>
+#include <cmath>
 #include <cstdarg>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
 #include "../../include/vega_b200.h"
 #include "vg_common.cuh"
 #include "vg_gemm.cuh"
+#include "vg_pk.cuh"
+#include "vg_post.cuh"
+#include "vg_xi.cuh"
 
 static thread_local char g_error[1024] = "";
+static long long g_launches = 0;
 
 void vg_set_error(const char* fmt, ...) {
   va_list ap;
@@ -17,11 +25,885 @@ void vg_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+#define VG_REQUIRE(cond, ...)            \
+  do {                                   \
+    if (!(cond)) {                       \
+      vg_set_error(__VA_ARGS__);         \
+      return VG_ERR_ARG;                 \
+    }                                    \
+  } while (0)
+#define VG_TRY(expr)                     \
+  do {                                   \
+    int rc__ = (expr);                   \
+    if (rc__) return rc__;               \
+  } while (0)
+#define VG_LAUNCHED()                    \
+  do {                                   \
+    ++g_launches;                        \
+    VG_CUDA_CHECK(cudaGetLastError());   \
+  } while (0)
+
+namespace {
+
+inline int pad16(long long n) { return (int)((n + 15) / 16 * 16); }
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+  ~DevBuf() { release(); }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+  int alloc(size_t n, bool zero = true) {
+    release();
+    if (n == 0) n = 16;
+    VG_CUDA_CHECK(cudaMalloc(&p, n));
+    bytes = n;
+    if (zero) VG_CUDA_CHECK(cudaMemset(p, 0, n));
+    return VG_OK;
+  }
+  int ensure(size_t n) { return n <= bytes ? VG_OK : alloc(n); }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+template <class T> int upload(DevBuf& buf, const T* host, size_t n) {
+  VG_TRY(buf.alloc(n * sizeof(T)));
+  VG_CUDA_CHECK(cudaMemcpy(buf.p, host, n * sizeof(T), cudaMemcpyHostToDevice));
+  return VG_OK;
+}
+
+// host [rows][cols] -> device [rows_pad][ld] zero padded
+int upload_padded(DevBuf& buf, const double* host, long long rows, long long cols, long long ld,
+                  long long rows_alloc = -1) {
+  if (rows_alloc < rows) rows_alloc = rows;
+  VG_TRY(buf.alloc((size_t)rows_alloc * ld * sizeof(double)));
+  VG_CUDA_CHECK(cudaMemcpy2D(buf.p, ld * sizeof(double), host, cols * sizeof(double),
+                             cols * sizeof(double), rows, cudaMemcpyHostToDevice));
+  return VG_OK;
+}
+
+struct Hankel {
+  int n_ell = 0, n_out = 0, n_out_pad = 0, bounds_error = 1;
+  int ells[vg::PK_MAX_ELL] = {0, 0, 0, 0};
+  DevBuf xk;    // [n_ell][n_out_pad]
+  DevBuf op;    // [n_ell][2*n_out_pad][nk_pad]
+};
+
+struct Corr {
+  int hankel_id = 0, n_model = 0, n_dist = 0, ld_model = 0, ld_dist = 0;
+  std::vector<vg_eval_desc> evals;
+  DevBuf d_evals;
+  std::vector<DevBuf> coords;
+  std::vector<double> opz_eff2;
+  DevBuf d_coord_ptrs, d_opz_eff2;
+  int n_metal = 0;
+  bool metal_dense = false;
+  std::vector<std::vector<double>> metal_host;
+  DevBuf d_mcat;                 // [n_model][n_metal*ld_model]
+  bool has_dmat = false;
+  DevBuf d_dmat;                 // [n_dist][ld_model]
+  DevBuf d_dmat_masked;          // [n_mask][ld_model]
+  bool has_inst = false;
+  DevBuf d_inst; int idx_inst_amp = -1; double inst_amp_default = 0.0;
+  std::vector<vg_bb_term> bb_terms;
+  DevBuf d_bb_terms, d_design_pre, d_design_post, d_sky_pre, d_sky_post;
+  int rows_pre = 0, rows_post = 0;
+  int n_mask = 0, ld_mask = 0;
+  bool has_invcov = false;
+  std::vector<int32_t> mask_host;
+  DevBuf d_mask_idx, d_data, d_invcov;   // invcov [n_mask][ld_mask]
+  int sx_n[4] = {0, 0, 0, 0};
+  DevBuf d_sx[4];
+};
+
+}  // namespace
+
+struct vg_plan {
+  int npf = 0, n_theta = 0, nk = 0, nk_pad = 0, nmu = 0, n_ell = 0, idx_bao_amp = -1;
+  std::vector<double> base;
+  DevBuf d_base, d_theta_cols, d_k, d_pk[3], d_pk_fid, d_mu, d_wleg;
+  DevBuf d_fv_x, d_fv_f; int fv_n = 0;
+  DevBuf d_uv_tau, d_uv_a; int uv_n = 0;
+  int n_prior = 0;
+  DevBuf d_prior_cols, d_prior_mean, d_prior_sigma;
+  std::vector<std::unique_ptr<Hankel>> hankels;
+  std::vector<std::unique_ptr<Corr>> corrs;
+  std::vector<DevBuf> grids;
+  DevBuf d_grid_ptrs;
+  bool finalized = false;
+  int static_bad = 0;
+  // global covariance
+  bool has_global = false; int n_total = 0, ld_total = 0;
+  DevBuf d_global_invcov;
+  // workspace (sized for `chunk` vectors)
+  long long chunk = 0, chunk_max = 1024;
+  DevBuf w_pfull, w_pkell, w_tables, w_core, w_xmet, w_met, w_x, w_y, w_diff, w_partial, w_split,
+      w_chi2, w_status, w_theta;
+  void* pinned = nullptr; size_t pinned_bytes = 0;
+
+  vg::PkGridDev grid_dev() const {
+    vg::PkGridDev g{};
+    g.nk = nk; g.nk_pad = nk_pad; g.nmu = nmu; g.n_ell = n_ell;
+    g.k = d_k.as<double>();
+    for (int i = 0; i < 3; ++i) g.pk_lin[i] = d_pk[i].as<double>();
+    g.pk_fid = d_pk_fid.as<double>();
+    g.mu = d_mu.as<double>();
+    g.wleg = d_wleg.as<double>();
+    g.fv_x = d_fv_x.as<double>(); g.fv_f = d_fv_f.as<double>(); g.fv_n = fv_n;
+    g.grids = d_grid_ptrs.as<const double*>();
+    return g;
+  }
+};
+
 extern "C" {
 
 const char* vg_last_error(void) { return g_error; }
-
 int vg_version(void) { return 100; }
+int vg_sizeof_eval_desc(void) { return (int)sizeof(vg_eval_desc); }
+int vg_sizeof_bb_term(void) { return (int)sizeof(vg_bb_term); }
+int64_t vg_launch_count(int reset) {
+  long long v = g_launches;
+  if (reset) g_launches = 0;
+  return v;
+}
+
+int vg_plan_create(int32_t n_params, const double* base, int32_t n_theta, const int32_t* theta_cols,
+                   int32_t nk, const double* k, const double* pk_full, const double* pk_smooth,
+                   const double* pk_fid, int32_t nmu, const double* mu, int32_t n_ell,
+                   const double* wleg, int32_t idx_bao_amp, vg_plan** out) {
+  VG_REQUIRE(n_params > 0 && nk > 0 && nmu > 0 && n_ell > 0 && n_ell <= vg::PK_MAX_ELL && out,
+             "vg_plan_create: bad sizes");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    vg_set_error("vg_plan_create: no CUDA device (there is no CPU fallback)");
+    return VG_ERR_CUDA;
+  }
+  std::unique_ptr<vg_plan> p(new vg_plan);
+  p->npf = n_params; p->n_theta = n_theta; p->nk = nk; p->nk_pad = pad16(nk);
+  p->nmu = nmu; p->n_ell = n_ell; p->idx_bao_amp = idx_bao_amp;
+  p->base.assign(base, base + n_params);
+  for (int j = 0; j < n_theta; ++j)
+    VG_REQUIRE(theta_cols[j] >= 0 && theta_cols[j] < n_params, "theta column out of range");
+  VG_TRY(upload(p->d_base, base, n_params));
+  VG_TRY(upload(p->d_theta_cols, theta_cols, std::max(n_theta, 1)));
+  VG_TRY(upload(p->d_k, k, nk));
+  std::vector<double> peak(nk);
+  for (int i = 0; i < nk; ++i) peak[i] = pk_full[i] - pk_smooth[i];   // vega/model.py:177
+  VG_TRY(upload(p->d_pk[0], peak.data(), nk));
+  VG_TRY(upload(p->d_pk[1], pk_smooth, nk));
+  VG_TRY(upload(p->d_pk[2], pk_full, nk));
+  VG_TRY(upload(p->d_pk_fid, pk_fid, nk));
+  VG_TRY(upload(p->d_mu, mu, nmu));
+  VG_TRY(upload(p->d_wleg, wleg, (size_t)n_ell * nmu));
+  *out = p.release();
+  return VG_OK;
+}
+
+int vg_plan_destroy(vg_plan* plan) {
+  if (!plan) return VG_OK;
+  if (plan->pinned) cudaFreeHost(plan->pinned);
+  delete plan;
+  return VG_OK;
+}
+
+int vg_plan_set_chunk(vg_plan* plan, int64_t chunk) {
+  VG_REQUIRE(plan && chunk > 0, "bad chunk");
+  plan->chunk_max = chunk;
+  return VG_OK;
+}
+
+int vg_plan_set_fvoigt(vg_plan* plan, int32_t n, const double* x, const double* f) {
+  VG_REQUIRE(plan && n > 1, "bad fvoigt table");
+  VG_TRY(upload(plan->d_fv_x, x, n));
+  VG_TRY(upload(plan->d_fv_f, f, n));
+  plan->fv_n = n;
+  return VG_OK;
+}
+
+int vg_plan_set_uvshot_table(vg_plan* plan, int32_t n, const double* tau, const double* a) {
+  VG_REQUIRE(plan && n > 1, "bad uv table");
+  VG_TRY(upload(plan->d_uv_tau, tau, n));
+  VG_TRY(upload(plan->d_uv_a, a, n));
+  plan->uv_n = n;
+  return VG_OK;
+}
+
+int vg_plan_set_priors(vg_plan* plan, int32_t n, const int32_t* cols, const double* mean,
+                       const double* sigma) {
+  VG_REQUIRE(plan && n >= 0, "bad priors");
+  plan->n_prior = n;
+  if (n == 0) return VG_OK;
+  VG_TRY(upload(plan->d_prior_cols, cols, n));
+  VG_TRY(upload(plan->d_prior_mean, mean, n));
+  VG_TRY(upload(plan->d_prior_sigma, sigma, n));
+  return VG_OK;
+}
+
+int vg_plan_add_hankel(vg_plan* plan, int32_t n_ell, const int32_t* ells, int32_t n_out,
+                       const double* xk, const double* op, int32_t bounds_error, int32_t* id) {
+  VG_REQUIRE(plan && n_ell == plan->n_ell && n_out > 3, "bad hankel operator");
+  std::unique_ptr<Hankel> h(new Hankel);
+  h->n_ell = n_ell; h->n_out = n_out; h->n_out_pad = pad16(n_out) ; h->bounds_error = bounds_error;
+  for (int l = 0; l < n_ell; ++l) h->ells[l] = ells[l];
+  VG_TRY(h->xk.alloc((size_t)n_ell * h->n_out_pad * 8));
+  VG_CUDA_CHECK(cudaMemcpy2D(h->xk.p, (size_t)h->n_out_pad * 8, xk, (size_t)n_out * 8,
+                             (size_t)n_out * 8, n_ell, cudaMemcpyHostToDevice));
+  // op[l][2][n_out][nk] -> device [l][2*n_out_pad][nk_pad], second derivatives at row n_out_pad
+  const size_t rows = 2 * (size_t)h->n_out_pad;
+  VG_TRY(h->op.alloc((size_t)n_ell * rows * plan->nk_pad * 8));
+  for (int l = 0; l < n_ell; ++l)
+    for (int half = 0; half < 2; ++half) {
+      const double* src = op + ((size_t)l * 2 + half) * n_out * plan->nk;
+      double* dst = h->op.as<double>() + ((size_t)l * rows + (size_t)half * h->n_out_pad) * plan->nk_pad;
+      VG_CUDA_CHECK(cudaMemcpy2D(dst, (size_t)plan->nk_pad * 8, src, (size_t)plan->nk * 8,
+                                 (size_t)plan->nk * 8, n_out, cudaMemcpyHostToDevice));
+    }
+  *id = (int)plan->hankels.size();
+  plan->hankels.push_back(std::move(h));
+  return VG_OK;
+}
+
+int vg_plan_add_corr(vg_plan* plan, int32_t hankel_id, int32_t n_model, int32_t n_dist,
+                     int32_t* corr_id) {
+  VG_REQUIRE(plan && hankel_id >= 0 && hankel_id < (int)plan->hankels.size() && n_model > 0 &&
+                 n_dist > 0, "bad correlation");
+  std::unique_ptr<Corr> c(new Corr);
+  c->hankel_id = hankel_id; c->n_model = n_model; c->n_dist = n_dist;
+  c->ld_model = pad16(n_model); c->ld_dist = pad16(n_dist);
+  *corr_id = (int)plan->corrs.size();
+  plan->corrs.push_back(std::move(c));
+  return VG_OK;
+}
+
+#define VG_CORR(plan, corr)                                                        \
+  VG_REQUIRE(plan && corr >= 0 && corr < (int)plan->corrs.size(), "bad correlation id"); \
+  Corr& c = *plan->corrs[corr]
+
+int vg_corr_add_coords(vg_plan* plan, int32_t corr, const double* tab, double opz_eff2,
+                       int32_t* coord_set) {
+  VG_CORR(plan, corr);
+  DevBuf buf;
+  VG_TRY(upload(buf, tab, (size_t)5 * c.n_model));
+  *coord_set = (int)c.coords.size();
+  c.coords.push_back(std::move(buf));
+  c.opz_eff2.push_back(opz_eff2);
+  return VG_OK;
+}
+
+int vg_corr_add_eval(vg_plan* plan, int32_t corr, const vg_eval_desc* desc, int32_t* eval_id) {
+  VG_CORR(plan, corr);
+  VG_REQUIRE(desc->coord_set >= 0 && desc->coord_set < (int)c.coords.size(), "eval: bad coord_set");
+  VG_REQUIRE(desc->out_slot >= 0, "eval: bad out_slot");
+  *eval_id = (int)c.evals.size();
+  c.evals.push_back(*desc);
+  c.n_metal = std::max(c.n_metal, desc->out_slot - 1);
+  return VG_OK;
+}
+
+int vg_corr_set_static_xi(vg_plan* plan, int32_t corr, int32_t which, int32_t n, const double* tab) {
+  VG_CORR(plan, corr);
+  VG_REQUIRE(which >= 0 && which < 4 && n > 3, "bad static xi table");
+  VG_TRY(upload(c.d_sx[which], tab, (size_t)3 * n));
+  c.sx_n[which] = n;
+  return VG_OK;
+}
+
+int vg_corr_set_metal_matrix(vg_plan* plan, int32_t corr, int32_t slot, const double* mat) {
+  VG_CORR(plan, corr);
+  VG_REQUIRE(slot >= 0 && slot < 4096, "bad metal slot");
+  if ((int)c.metal_host.size() <= slot) c.metal_host.resize(slot + 1);
+  c.metal_host[slot].assign(mat, mat + (size_t)c.n_model * c.n_model);
+  c.metal_dense = true;
+  return VG_OK;
+}
+
+int vg_corr_set_distortion(vg_plan* plan, int32_t corr, const double* dmat) {
+  VG_CORR(plan, corr);
+  VG_TRY(upload_padded(c.d_dmat, dmat, c.n_dist, c.n_model, c.ld_model));
+  c.has_dmat = true;
+  return VG_OK;
+}
+
+int vg_corr_set_inst_sys(vg_plan* plan, int32_t corr, const double* table, int32_t idx_amp,
+                         double amp_default) {
+  VG_CORR(plan, corr);
+  VG_TRY(upload(c.d_inst, table, c.n_model));
+  c.has_inst = true; c.idx_inst_amp = idx_amp; c.inst_amp_default = amp_default;
+  return VG_OK;
+}
+
+int vg_corr_set_broadband(vg_plan* plan, int32_t corr, int32_t n_terms, const vg_bb_term* terms,
+                          int32_t rows_pre, const double* design_pre, int32_t rows_post,
+                          const double* design_post, const double* sky_pre, const double* sky_post) {
+  VG_CORR(plan, corr);
+  VG_REQUIRE(n_terms >= 0 && n_terms <= VG_MAX_BB_TERMS, "too many broadband terms");
+  c.bb_terms.assign(terms, terms + n_terms);
+  if (n_terms) VG_TRY(upload(c.d_bb_terms, terms, n_terms));
+  c.rows_pre = rows_pre; c.rows_post = rows_post;
+  if (rows_pre) VG_TRY(upload(c.d_design_pre, design_pre, (size_t)rows_pre * c.n_model));
+  if (rows_post) VG_TRY(upload(c.d_design_post, design_post, (size_t)rows_post * c.n_dist));
+  VG_TRY(upload(c.d_sky_pre, sky_pre, (size_t)2 * c.n_model));
+  VG_TRY(upload(c.d_sky_post, sky_post, (size_t)2 * c.n_dist));
+  return VG_OK;
+}
+
+int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t* mask_idx,
+                     const double* data, const double* invcov) {
+  VG_CORR(plan, corr);
+  VG_REQUIRE(n_mask > 0, "empty data mask");
+  for (int j = 0; j < n_mask; ++j)
+    VG_REQUIRE(mask_idx[j] >= 0 && mask_idx[j] < c.n_dist, "mask index out of range");
+  const bool new_mask = c.mask_host.size() != (size_t)n_mask ||
+                        !std::equal(mask_idx, mask_idx + n_mask, c.mask_host.begin());
+  c.n_mask = n_mask; c.ld_mask = pad16(n_mask);
+  if (new_mask) {
+    c.mask_host.assign(mask_idx, mask_idx + n_mask);
+    VG_TRY(upload(c.d_mask_idx, mask_idx, n_mask));
+    if (plan->finalized && c.has_dmat) {
+      vg_set_error("the data mask cannot change after vg_plan_finalize");
+      return VG_ERR_STATE;
+    }
+  }
+  VG_TRY(upload(c.d_data, data, n_mask));
+  if (invcov) {
+    VG_TRY(upload_padded(c.d_invcov, invcov, n_mask, n_mask, c.ld_mask));
+    c.has_invcov = true;
+  } else {
+    c.has_invcov = false;
+  }
+  return VG_OK;
+}
+
+int vg_plan_set_global_invcov(vg_plan* plan, int32_t n_total, const double* invcov) {
+  VG_REQUIRE(plan && n_total > 0, "bad global covariance");
+  plan->n_total = n_total; plan->ld_total = pad16(n_total);
+  VG_TRY(upload_padded(plan->d_global_invcov, invcov, n_total, n_total, plan->ld_total));
+  plan->has_global = true;
+  return VG_OK;
+}
+
+int vg_plan_finalize(vg_plan* plan, void* stream) {
+  VG_REQUIRE(plan && !plan->corrs.empty(), "plan has no correlation");
+  cudaStream_t st = (cudaStream_t)stream;
+  // number of static grids referenced
+  int n_grids = 0;
+  for (auto& cp : plan->corrs)
+    for (auto& d : cp->evals) n_grids = std::max({n_grids, d.static_grid + 1, d.hcd_grid + 1});
+  plan->grids.clear();
+  plan->grids.resize(n_grids);
+  std::vector<const double*> ptrs(std::max(n_grids, 1), nullptr);
+  for (int g = 0; g < n_grids; ++g) {
+    VG_TRY(plan->grids[g].alloc((size_t)plan->nmu * plan->nk * 8));
+    ptrs[g] = plan->grids[g].as<double>();
+  }
+  VG_TRY(upload(plan->d_grid_ptrs, ptrs.data(), ptrs.size()));
+
+  DevBuf bad;
+  VG_TRY(bad.alloc(sizeof(int)));
+  std::vector<char> built(n_grids, 0);
+  for (auto& cp : plan->corrs) {
+    Corr& c = *cp;
+    VG_REQUIRE(!c.evals.empty(), "correlation without evaluations");
+    VG_TRY(upload(c.d_evals, c.evals.data(), c.evals.size()));
+    std::vector<const double*> cptrs;
+    for (auto& b : c.coords) cptrs.push_back(b.as<double>());
+    VG_TRY(upload(c.d_coord_ptrs, cptrs.data(), cptrs.size()));
+    VG_TRY(upload(c.d_opz_eff2, c.opz_eff2.data(), c.opz_eff2.size()));
+    vg::PkGridDev g = plan->grid_dev();
+    dim3 grid(vg_cdiv(plan->nk, 128), plan->nmu);
+    for (size_t e = 0; e < c.evals.size(); ++e) {
+      const vg_eval_desc& d = c.evals[e];
+      if (d.static_grid >= 0 && !built[d.static_grid]) {
+        vg::static_grid_kernel<<<grid, 128, 0, st>>>(g, c.d_evals.as<vg_eval_desc>(), (int)e, 0,
+                                                   plan->d_base.as<double>(),
+                                                   plan->grids[d.static_grid].as<double>(), bad.as<int>());
+        VG_LAUNCHED();
+        built[d.static_grid] = 1;
+      }
+      if (d.hcd_grid >= 0 && !built[d.hcd_grid]) {
+        vg::static_grid_kernel<<<grid, 128, 0, st>>>(g, c.d_evals.as<vg_eval_desc>(), (int)e, 1,
+                                                   plan->d_base.as<double>(),
+                                                   plan->grids[d.hcd_grid].as<double>(), bad.as<int>());
+        VG_LAUNCHED();
+        built[d.hcd_grid] = 1;
+      }
+    }
+    // metal matrices, concatenated along K: mcat[i][c*ld_model + j] = M_c[i][j]
+    if (c.metal_dense && c.n_metal > 0) {
+      const size_t ldk = (size_t)c.n_metal * c.ld_model;
+      VG_TRY(c.d_mcat.alloc((size_t)c.n_model * ldk * 8));
+      std::vector<double> eye;
+      for (int s = 0; s < c.n_metal; ++s) {
+        const double* src;
+        if (s < (int)c.metal_host.size() && !c.metal_host[s].empty()) {
+          src = c.metal_host[s].data();
+        } else {
+          if (eye.empty()) {
+            eye.assign((size_t)c.n_model * c.n_model, 0.0);
+            for (int i = 0; i < c.n_model; ++i) eye[(size_t)i * c.n_model + i] = 1.0;
+          }
+          src = eye.data();
+        }
+        VG_CUDA_CHECK(cudaMemcpy2D(c.d_mcat.as<double>() + (size_t)s * c.ld_model, ldk * 8, src,
+                                   (size_t)c.n_model * 8, (size_t)c.n_model * 8, c.n_model,
+                                   cudaMemcpyHostToDevice));
+      }
+      c.metal_host.clear();
+      c.metal_host.shrink_to_fit();
+    }
+    // masked rows of the distortion matrix (chi2 needs only the bins kept by the cuts)
+    if (c.has_dmat && c.n_mask > 0) {
+      VG_TRY(c.d_dmat_masked.alloc((size_t)c.n_mask * c.ld_model * 8));
+      for (int j = 0; j < c.n_mask; ++j)
+        VG_CUDA_CHECK(cudaMemcpyAsync(c.d_dmat_masked.as<double>() + (size_t)j * c.ld_model,
+                                      c.d_dmat.as<double>() + (size_t)c.mask_host[j] * c.ld_model,
+                                      (size_t)c.ld_model * 8, cudaMemcpyDeviceToDevice, st));
+    }
+  }
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  VG_CUDA_CHECK(cudaMemcpy(&plan->static_bad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
+  if (plan->has_global) {
+    int tot = 0;
+    for (auto& cp : plan->corrs) tot += cp->n_mask;
+    VG_REQUIRE(tot == plan->n_total, "global covariance size %d != sum of masks %d", plan->n_total, tot);
+  }
+  plan->finalized = true;
+  return VG_OK;
+}
+
+int64_t vg_plan_device_bytes(const vg_plan* plan) {
+  if (!plan) return 0;
+  size_t n = 0;
+  for (auto& g : plan->grids) n += g.bytes;
+  for (auto& h : plan->hankels) n += h->xk.bytes + h->op.bytes;
+  for (auto& cp : plan->corrs) {
+    const Corr& c = *cp;
+    n += c.d_mcat.bytes + c.d_dmat.bytes + c.d_dmat_masked.bytes + c.d_invcov.bytes;
+    for (auto& b : c.coords) n += b.bytes;
+  }
+  n += plan->d_global_invcov.bytes;
+  n += plan->w_pfull.bytes + plan->w_pkell.bytes + plan->w_tables.bytes + plan->w_core.bytes +
+       plan->w_xmet.bytes + plan->w_met.bytes + plan->w_x.bytes + plan->w_y.bytes + plan->w_diff.bytes +
+       plan->w_partial.bytes + plan->w_split.bytes;
+  return (int64_t)n;
+}
+
+}  // extern "C"
+
+namespace {
+
+constexpr int NUM_SMS = 148;
+
+// C[M][ldc] = A[M][K] * B[N][K]^T with an automatic deterministic split-K when the tile
+// count is too small to fill the 148 SMs.
+int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, long long ldb,
+              double* C, long long ldc, int M, int N, int K, int batch, long long strideA,
+              long long strideB, long long strideC, cudaStream_t st) {
+  vg::GemmArgs g{};
+  g.A = A; g.B = B; g.M = M; g.N = N; g.K = K; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
+  g.batch = batch; g.strideA = strideA; g.strideB = strideB; g.strideC = strideC;
+  g.alpha = 1.0; g.beta = 0.0;
+  const long long tiles = (long long)vg_cdiv(M, vg::GEMM_BM) * vg_cdiv(N, vg::GEMM_BN) * batch;
+  const int ktiles = K / vg::GEMM_BK;
+  int splits = 1;
+  if (tiles < 3 * NUM_SMS) splits = (int)std::min<long long>(std::max(1, ktiles / 8), (4 * NUM_SMS + tiles - 1) / tiles);
+  g.splits = std::max(1, splits);
+  if (g.splits == 1) {
+    g.C = C;
+    VG_TRY(vg::launch_dgemm(g, vg::GEMM_STORE, st));
+    ++g_launches;
+    return VG_OK;
+  }
+  const long long n = (long long)M * ldc;
+  VG_TRY(plan->w_split.ensure((size_t)g.splits * n * 8));
+  g.C = plan->w_split.as<double>();
+  g.split_stride = n;
+  VG_TRY(vg::launch_dgemm(g, vg::GEMM_STORE, st));
+  ++g_launches;
+  vg::reduce_splits_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->w_split.as<double>(), C, n, g.splits, n);
+  VG_LAUNCHED();
+  return VG_OK;
+}
+
+int ensure_workspace(vg_plan* plan, long long Bc_) {
+  if (Bc_ <= plan->chunk) return VG_OK;
+  const size_t Bc = (size_t)Bc_;
+  size_t pkell = 0, tables = 0, core = 0, xmet = 0, met = 0, y = 0, diff = 0;
+  for (auto& cp : plan->corrs) {
+    const Corr& c = *cp;
+    const Hankel& h = *plan->hankels[c.hankel_id];
+    const size_t E = c.evals.size();
+    pkell = std::max(pkell, (size_t)Bc * E * plan->n_ell * plan->nk_pad);
+    tables = std::max(tables, (size_t)Bc * E * plan->n_ell * 2 * h.n_out_pad);
+    core = std::max(core, (size_t)2 * Bc * c.ld_model);
+    xmet = std::max(xmet, (size_t)Bc * std::max(c.n_metal, 1) * c.ld_model);
+    met = std::max(met, (size_t)Bc * c.ld_model);
+    y = std::max(y, (size_t)Bc * std::max(c.ld_dist, c.ld_mask));
+    diff = std::max(diff, (size_t)Bc * std::max(c.ld_mask, c.ld_dist));
+  }
+  if (plan->has_global) diff = std::max(diff, (size_t)Bc * plan->ld_total);
+  VG_TRY(plan->w_pfull.alloc((size_t)Bc * plan->npf * 8));
+  VG_TRY(plan->w_pkell.alloc(pkell * 8));
+  VG_TRY(plan->w_tables.alloc(tables * 8));
+  VG_TRY(plan->w_core.alloc(core * 8));
+  VG_TRY(plan->w_xmet.alloc(xmet * 8));
+  VG_TRY(plan->w_met.alloc(met * 8));
+  VG_TRY(plan->w_x.alloc(met * 8));
+  VG_TRY(plan->w_y.alloc(y * 8));
+  VG_TRY(plan->w_diff.alloc(diff * 8));
+  VG_TRY(plan->w_partial.alloc((size_t)Bc * 256 * 8));
+  VG_TRY(plan->w_chi2.alloc((size_t)Bc * 8));
+  VG_TRY(plan->w_status.alloc((size_t)Bc * 4));
+  VG_TRY(plan->w_theta.alloc((size_t)Bc * std::max(plan->n_theta, 1) * 8));
+  plan->chunk = Bc_;
+  return VG_OK;
+}
+
+int expand_params(vg_plan* plan, const double* theta_dev, long long Bc, int* status_dev, cudaStream_t st) {
+  const long long n = Bc * plan->npf;
+  vg::expand_theta_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->d_base.as<double>(), plan->npf, theta_dev,
+                                                        plan->n_theta, plan->d_theta_cols.as<int>(), Bc,
+                                                        plan->w_pfull.as<double>());
+  VG_LAUNCHED();
+  if (plan->n_theta > 0) {
+    const long long m = Bc * plan->n_theta;
+    vg::scatter_theta_kernel<<<vg_cdiv(m, 256), 256, 0, st>>>(theta_dev, plan->n_theta,
+                                                           plan->d_theta_cols.as<int>(), Bc, plan->npf,
+                                                           plan->w_pfull.as<double>());
+    VG_LAUNCHED();
+  }
+  VG_CUDA_CHECK(cudaMemsetAsync(status_dev, 0, (size_t)Bc * 4, st));
+  return VG_OK;
+}
+
+vg::BroadbandDev bb_dev(const Corr& c) {
+  vg::BroadbandDev bb{};
+  bb.n_terms = (int)c.bb_terms.size();
+  bb.terms = c.d_bb_terms.as<vg_bb_term>();
+  bb.design_pre = c.d_design_pre.as<double>(); bb.rows_pre = c.rows_pre;
+  bb.design_post = c.d_design_post.as<double>(); bb.rows_post = c.rows_post;
+  bb.sky_pre = c.d_sky_pre.as<double>(); bb.sky_post = c.d_sky_post.as<double>();
+  return bb;
+}
+
+// Stages K1..K3 + metals + pre-distortion assembly of one correlation: leaves
+// x[Bc][ld_model] in plan->w_x.  `upto` stops early for the per-stage taps.
+int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaStream_t st, int upto = 99) {
+  const Hankel& h = *plan->hankels[c.hankel_id];
+  const int E = (int)c.evals.size();
+  vg::PkGridDev g = plan->grid_dev();
+  bool any_dyn = false;
+  for (auto& d : c.evals) any_dyn |= d.dyn_mask != 0;
+  {  // K1 + K2a
+    dim3 block(vg::PK_KLANES, vg::PK_MUGROUPS);
+    const vg_eval_desc* ev = c.d_evals.as<vg_eval_desc>();
+    double* out = plan->w_pkell.as<double>();
+    const double* pf = plan->w_pfull.as<double>();
+    if (Bc >= 4) {
+      dim3 grid(vg_cdiv(plan->nk, vg::PK_KLANES), E, vg_cdiv(Bc, 4));
+      if (any_dyn) vg::pk_ell_kernel<4, true><<<grid, block, 0, st>>>(g, ev, E, pf, plan->npf, (int)Bc, out, status_dev);
+      else vg::pk_ell_kernel<4, false><<<grid, block, 0, st>>>(g, ev, E, pf, plan->npf, (int)Bc, out, status_dev);
+    } else {
+      dim3 grid(vg_cdiv(plan->nk, vg::PK_KLANES), E, (unsigned)Bc);
+      if (any_dyn) vg::pk_ell_kernel<1, true><<<grid, block, 0, st>>>(g, ev, E, pf, plan->npf, (int)Bc, out, status_dev);
+      else vg::pk_ell_kernel<1, false><<<grid, block, 0, st>>>(g, ev, E, pf, plan->npf, (int)Bc, out, status_dev);
+    }
+    VG_LAUNCHED();
+  }
+  if (upto <= 1) return VG_OK;
+  // K2b: Hankel + spline operator, one GEMM batched over the multipoles
+  const int rowT = 2 * h.n_out_pad;
+  VG_TRY(gemm_auto(plan, plan->w_pkell.as<double>(), (long long)plan->n_ell * plan->nk_pad,
+                   h.op.as<double>(), plan->nk_pad, plan->w_tables.as<double>(),
+                   (long long)plan->n_ell * rowT, (int)(Bc * E), rowT, plan->nk_pad, plan->n_ell,
+                   plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
+  if (upto <= 2) return VG_OK;
+  {  // K3
+    vg::XiArgs a{};
+    a.h.n_ell = h.n_ell; a.h.n_out = h.n_out; a.h.n_out_pad = h.n_out_pad; a.h.bounds_error = h.bounds_error;
+    for (int l = 0; l < vg::PK_MAX_ELL; ++l) a.h.ells[l] = h.ells[l];
+    a.h.xk = h.xk.as<double>();
+    a.evals = c.d_evals.as<vg_eval_desc>(); a.n_eval = E;
+    a.pfull = plan->w_pfull.as<double>(); a.npf = plan->npf; a.B = (int)Bc;
+    a.tables = plan->w_tables.as<double>();
+    a.coords = c.d_coord_ptrs.as<const double*>();
+    a.opz_eff2 = c.d_opz_eff2.as<double>();
+    a.n_model = c.n_model;
+    for (int i = 0; i < 4; ++i) { a.sx.n[i] = c.sx_n[i]; a.sx.tab[i] = c.d_sx[i].as<double>(); }
+    a.uv_tau = plan->d_uv_tau.as<double>(); a.uv_a = plan->d_uv_a.as<double>(); a.uv_n = plan->uv_n;
+    a.core = plan->w_core.as<double>(); a.xmet = plan->w_xmet.as<double>();
+    a.ld_model = c.ld_model; a.n_metal = std::max(c.n_metal, 1);
+    a.status = status_dev;
+    long long ctas_wanted = 4LL * NUM_SMS;
+    int chunks = (int)std::max<long long>(1, std::min<long long>(vg_cdiv(c.ld_model, 256),
+                                                             (ctas_wanted + Bc * E - 1) / (Bc * E)));
+    a.bins_per_cta = vg_cdiv(c.ld_model, chunks);
+    const size_t smem = (size_t)h.n_ell * rowT * 8;
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+      VG_CUDA_CHECK(cudaFuncSetAttribute(vg::xi_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      smem_set = smem;
+    }
+    dim3 grid(vg_cdiv(c.ld_model, a.bins_per_cta), E, (unsigned)Bc);
+    vg::xi_gather_kernel<<<grid, 256, smem, st>>>(a);
+    VG_LAUNCHED();
+  }
+  if (upto <= 3) return VG_OK;
+  // metals: sum_c w_c M_c xi_c  (vega/metals.py:258-367)
+  const double* met = nullptr;
+  if (c.n_metal > 0) {
+    if (c.metal_dense) {
+      const long long ldk = (long long)c.n_metal * c.ld_model;
+      VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, c.d_mcat.as<double>(), ldk,
+                       plan->w_met.as<double>(), c.ld_model, (int)Bc, c.n_model, (int)ldk, 1, 0, 0, 0, st));
+    } else {
+      const long long n = Bc * c.ld_model;
+      vg::metal_sum_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->w_xmet.as<double>(), c.n_metal, c.ld_model,
+                                                         c.n_model, Bc, plan->w_met.as<double>());
+      VG_LAUNCHED();
+    }
+    met = plan->w_met.as<double>();
+  }
+  vg::CombineArgs ca{};
+  ca.core = plan->w_core.as<double>(); ca.met = met;
+  ca.inst = c.has_inst ? c.d_inst.as<double>() : nullptr;
+  ca.idx_inst_amp = c.idx_inst_amp; ca.inst_amp_default = c.inst_amp_default;
+  ca.idx_bao_amp = plan->idx_bao_amp;
+  ca.bb = bb_dev(c);
+  ca.pfull = plan->w_pfull.as<double>(); ca.npf = plan->npf;
+  ca.n = c.n_model; ca.ld = c.ld_model; ca.B = Bc;
+  ca.x = plan->w_x.as<double>();
+  const long long n = Bc * c.ld_model;
+  vg::combine_pre_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(ca);
+  VG_LAUNCHED();
+  return VG_OK;
+}
+
+}  // namespace
+
+namespace {
+
+// Distortion matrix + post-distortion broadband of one correlation.
+//   data == false: model rows for ALL distorted bins -> out[Bc][ldo = ld_dist]
+//   data == true : residual d - m on the masked bins  -> out[Bc][ldo] at column col0
+int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* out, int ldo,
+                  int ncols, cudaStream_t st) {
+  const double* y = plan->w_x.as<double>();
+  int ldy = c.ld_model;
+  int y_is_masked = 0;
+  if (c.has_dmat) {
+    if (residual) {
+      VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_dmat_masked.as<double>(), c.ld_model,
+                       plan->w_y.as<double>(), c.ld_mask, (int)Bc, c.n_mask, c.ld_model, 1, 0, 0, 0, st));
+      ldy = c.ld_mask; y_is_masked = 1;
+    } else {
+      VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_dmat.as<double>(), c.ld_model,
+                       plan->w_y.as<double>(), c.ld_dist, (int)Bc, c.n_dist, c.ld_model, 1, 0, 0, 0, st));
+      ldy = c.ld_dist;
+    }
+    y = plan->w_y.as<double>();
+  }
+  vg::PostArgs pa{};
+  pa.y = y; pa.ldy = ldy; pa.y_is_masked = y_is_masked;
+  pa.mask_idx = residual ? c.d_mask_idx.as<int>() : nullptr;
+  pa.bb = bb_dev(c); pa.n_dist = c.n_dist;
+  pa.pfull = plan->w_pfull.as<double>(); pa.npf = plan->npf; pa.idx_bao_amp = plan->idx_bao_amp;
+  pa.data = residual ? c.d_data.as<double>() : nullptr;
+  pa.n_out = residual ? c.n_mask : c.n_dist;
+  pa.ldo = ldo; pa.ncols = ncols; pa.B = Bc; pa.out = out;
+  const long long n = Bc * ncols;
+  vg::post_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(pa);
+  VG_LAUNCHED();
+  return VG_OK;
+}
+
+// chi2[b] (+)= diff[b]^T invcov diff[b]
+int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* invcov, long long Bc,
+              double* chi2, int accumulate, cudaStream_t st) {
+  if (!invcov) {
+    vg::chi2_identity_kernel<<<(unsigned)Bc, 256, 0, st>>>(diff, n, ld, chi2, accumulate);
+    VG_LAUNCHED();
+    return VG_OK;
+  }
+  vg::GemmArgs g{};
+  g.A = diff; g.B = invcov; g.M = (int)Bc; g.N = n; g.K = ld; g.lda = ld; g.ldb = ld;
+  g.batch = 1; g.splits = 1; g.alpha = 1.0; g.beta = 0.0;
+  const int n_tiles = vg_cdiv(n, vg::GEMM_BN);
+  VG_TRY(plan->w_partial.ensure((size_t)Bc * n_tiles * 8));
+  g.C = plan->w_partial.as<double>(); g.ldc = n_tiles;
+  g.D = diff; g.ldd = ld;
+  VG_TRY(vg::launch_dgemm(g, vg::GEMM_ROWDOT, st));
+  ++g_launches;
+  vg::chi2_partials_kernel<<<vg_cdiv(Bc, 256), 256, 0, st>>>(plan->w_partial.as<double>(), n_tiles, Bc, chi2, accumulate);
+  VG_LAUNCHED();
+  return VG_OK;
+}
+
+int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi2_dev, int* status_dev,
+               cudaStream_t st) {
+  VG_TRY(expand_params(plan, theta_dev, Bc, status_dev, st));
+  int first = 1;
+  int col0 = 0;
+  for (auto& cp : plan->corrs) {
+    Corr& c = *cp;
+    VG_REQUIRE(c.n_mask > 0, "vg_chi2_batch: correlation without data (vg_corr_set_data)");
+    VG_TRY(run_corr_front(plan, c, Bc, status_dev, st));
+    if (plan->has_global) {
+      // residuals of all correlations side by side: [Bc][ld_total]
+      VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>() + col0, plan->ld_total,
+                           c.n_mask, st));
+      col0 += c.n_mask;
+    } else {
+      VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, st));
+      VG_TRY(quad_form(plan, plan->w_diff.as<double>(), c.n_mask, c.ld_mask,
+                       c.has_invcov ? c.d_invcov.as<double>() : nullptr, Bc, chi2_dev, !first, st));
+      first = 0;
+    }
+  }
+  if (plan->has_global)
+    VG_TRY(quad_form(plan, plan->w_diff.as<double>(), plan->n_total, plan->ld_total,
+                     plan->d_global_invcov.as<double>(), Bc, chi2_dev, 0, st));
+  if (plan->n_prior > 0) {
+    vg::prior_kernel<<<vg_cdiv(Bc, 256), 256, 0, st>>>(plan->w_pfull.as<double>(), plan->npf,
+                                                    plan->d_prior_cols.as<int>(), plan->d_prior_mean.as<double>(),
+                                                    plan->d_prior_sigma.as<double>(), plan->n_prior, Bc, chi2_dev);
+    VG_LAUNCHED();
+  }
+  return VG_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int vg_model_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* const* xi_out_dev,
+                   int32_t* status_dev, void* stream) {
+  VG_REQUIRE(plan && plan->finalized && B > 0 && xi_out_dev && status_dev, "vg_model_batch: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long chunk = std::min<long long>(B, plan->chunk_max);
+  VG_TRY(ensure_workspace(plan, chunk));
+  for (long long b0 = 0; b0 < B; b0 += chunk) {
+    const long long Bc = std::min<long long>(chunk, B - b0);
+    VG_TRY(expand_params(plan, theta_dev + b0 * plan->n_theta, Bc, status_dev + b0, st));
+    for (size_t ci = 0; ci < plan->corrs.size(); ++ci) {
+      Corr& c = *plan->corrs[ci];
+      VG_TRY(run_corr_front(plan, c, Bc, status_dev + b0, st));
+      // model rows straight into the caller's [B][n_dist] array
+      VG_TRY(run_corr_back(plan, c, Bc, false, xi_out_dev[ci] + b0 * c.n_dist, c.n_dist, c.n_dist, st));
+    }
+  }
+  return VG_OK;
+}
+
+int vg_chi2_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* chi2_dev,
+                  int32_t* status_dev, void* stream) {
+  VG_REQUIRE(plan && plan->finalized && B > 0 && chi2_dev && status_dev, "vg_chi2_batch: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long chunk = std::min<long long>(B, plan->chunk_max);
+  VG_TRY(ensure_workspace(plan, chunk));
+  for (long long b0 = 0; b0 < B; b0 += chunk) {
+    const long long Bc = std::min<long long>(chunk, B - b0);
+    VG_TRY(chi2_chunk(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st));
+  }
+  return VG_OK;
+}
+
+int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, double* chi2_host,
+                       int32_t* status_host, void* stream) {
+  VG_REQUIRE(plan && plan->finalized && B > 0 && theta_host && chi2_host && status_host,
+             "vg_chi2_batch_host: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long chunk = std::min<long long>(B, plan->chunk_max);
+  VG_TRY(ensure_workspace(plan, chunk));
+  const int nt = std::max(plan->n_theta, 1);
+  const size_t need = (size_t)chunk * (nt * 8 + 8 + 4);
+  if (need > plan->pinned_bytes) {
+    if (plan->pinned) cudaFreeHost(plan->pinned);
+    plan->pinned = nullptr; plan->pinned_bytes = 0;
+    VG_CUDA_CHECK(cudaMallocHost(&plan->pinned, need));
+    plan->pinned_bytes = need;
+  }
+  double* pin_theta = reinterpret_cast<double*>(plan->pinned);
+  double* pin_chi2 = pin_theta + (size_t)chunk * nt;
+  int32_t* pin_status = reinterpret_cast<int32_t*>(pin_chi2 + chunk);
+  for (long long b0 = 0; b0 < B; b0 += chunk) {
+    const long long Bc = std::min<long long>(chunk, B - b0);
+    if (plan->n_theta > 0) {
+      memcpy(pin_theta, theta_host + b0 * plan->n_theta, (size_t)Bc * plan->n_theta * 8);
+      VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_theta.p, pin_theta, (size_t)Bc * plan->n_theta * 8,
+                                    cudaMemcpyHostToDevice, st));
+    }
+    VG_TRY(chi2_chunk(plan, plan->w_theta.as<double>(), Bc, plan->w_chi2.as<double>(),
+                      plan->w_status.as<int>(), st));
+    VG_CUDA_CHECK(cudaMemcpyAsync(pin_chi2, plan->w_chi2.p, (size_t)Bc * 8, cudaMemcpyDeviceToHost, st));
+    VG_CUDA_CHECK(cudaMemcpyAsync(pin_status, plan->w_status.p, (size_t)Bc * 4, cudaMemcpyDeviceToHost, st));
+    VG_CUDA_CHECK(cudaStreamSynchronize(st));
+    memcpy(chi2_host + b0, pin_chi2, (size_t)Bc * 8);
+    memcpy(status_host + b0, pin_status, (size_t)Bc * 4);
+    for (long long b = 0; b < Bc; ++b) status_host[b0 + b] |= plan->static_bad;
+  }
+  return VG_OK;
+}
+
+int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }
+
+int64_t vg_stage_size(const vg_plan* plan, int32_t corr, int32_t stage) {
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size()) return -1;
+  const Corr& c = *plan->corrs[corr];
+  const Hankel& h = *plan->hankels[c.hankel_id];
+  const int64_t E = (int64_t)c.evals.size();
+  switch (stage) {
+    case 0: return (int64_t)plan->nmu * plan->nk;
+    case 1: return E * plan->n_ell * plan->nk_pad;
+    case 2: return E * plan->n_ell * 2 * h.n_out_pad;
+    case 3: return (int64_t)(2 + std::max(c.n_metal, 1)) * c.ld_model;
+    case 4: return c.ld_model;
+    default: return -1;
+  }
+}
+
+int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
+                   const double* theta_dev, int64_t B, double* out_dev, int32_t* status_dev,
+                   void* stream) {
+  VG_REQUIRE(plan && plan->finalized && B > 0 && out_dev && status_dev, "vg_stage_batch: bad arguments");
+  VG_CORR(plan, corr);
+  cudaStream_t st = (cudaStream_t)stream;
+  VG_REQUIRE(B <= plan->chunk_max, "vg_stage_batch: B exceeds the chunk size");
+  VG_TRY(ensure_workspace(plan, B));
+  VG_TRY(expand_params(plan, theta_dev, B, status_dev, st));
+  const int64_t per = vg_stage_size(plan, corr, stage);
+  VG_REQUIRE(per > 0, "vg_stage_batch: bad stage");
+  if (stage == 0) {
+    VG_REQUIRE(eval >= 0 && eval < (int)c.evals.size(), "bad evaluation index");
+    dim3 grid(vg_cdiv(plan->nk, 128), plan->nmu, (unsigned)B);
+    vg::pk_grid_kernel<<<grid, 128, 0, st>>>(plan->grid_dev(), c.d_evals.as<vg_eval_desc>(), eval,
+                                           plan->w_pfull.as<double>(), plan->npf, out_dev, status_dev);
+    VG_LAUNCHED();
+    return VG_OK;
+  }
+  VG_TRY(run_corr_front(plan, c, B, status_dev, st, stage == 4 ? 99 : stage));
+  const int nm = std::max(c.n_metal, 1);
+  if (stage == 1) {
+    VG_CUDA_CHECK(cudaMemcpyAsync(out_dev, plan->w_pkell.p, (size_t)B * per * 8, cudaMemcpyDeviceToDevice, st));
+  } else if (stage == 2) {
+    VG_CUDA_CHECK(cudaMemcpyAsync(out_dev, plan->w_tables.p, (size_t)B * per * 8, cudaMemcpyDeviceToDevice, st));
+  } else if (stage == 3) {
+    // [B][2 + n_metal][ld_model]: peak core, smooth core, weighted metal xi's
+    for (int s = 0; s < 2; ++s)
+      VG_CUDA_CHECK(cudaMemcpy2DAsync(out_dev + (size_t)s * c.ld_model, (size_t)per * 8,
+                                      plan->w_core.as<double>() + (size_t)s * B * c.ld_model,
+                                      (size_t)c.ld_model * 8, (size_t)c.ld_model * 8, B,
+                                      cudaMemcpyDeviceToDevice, st));
+    VG_CUDA_CHECK(cudaMemcpy2DAsync(out_dev + (size_t)2 * c.ld_model, (size_t)per * 8, plan->w_xmet.p,
+                                    (size_t)nm * c.ld_model * 8, (size_t)nm * c.ld_model * 8, B,
+                                    cudaMemcpyDeviceToDevice, st));
+  } else {
+    VG_CUDA_CHECK(cudaMemcpyAsync(out_dev, plan->w_x.p, (size_t)B * per * 8, cudaMemcpyDeviceToDevice, st));
+  }
+  return VG_OK;
+}
 
 int vg_dgemm_tn(const double* A, const double* B, double* C, int M, int N, int K,
                 long long lda, long long ldb, long long ldc, double alpha, double beta,

@@ -1,0 +1,338 @@
+// K1 + K2a: anisotropic power spectrum P(k,mu) on the (mu,k) grid and its projection onto
+// Legendre multipoles, for a batch of parameter vectors.
+//
+// Restates vega/power_spectrum.py:87-636 (PowerSpectrum.compute and its factors), the
+// helpers vega/utils.py:28-108,396-441 and the projection of vega/pktoxi.py:79-97,138
+// (midpoint rule on nmu uniform mu bins, weights dmu*(2l+1)*L_l(mu)).
+//
+// Layout: every grid is [nmu][nk] with k fastest, so a warp reads 32 consecutive k of one
+// mu row (256 B coalesced).  Factors whose parameters are fixed for the whole batch are
+// folded once into a static grid S(mu,k) (the reference caches the same factors between
+// calls: power_spectrum.py:139-141,311-324,407-417,459-479); factors with sampled
+// parameters are evaluated per vector.  The fused kernel never materialises P(k,mu): a
+// thread owns one k and a strided slice of mu for NB parameter vectors at a time, so each
+// static-grid value is read once per NB vectors and P_l(k) leaves the SM as 4 numbers.
+#pragma once
+#include "../../include/vega_b200.h"
+#include "vg_common.cuh"
+
+namespace vg {
+
+constexpr double DEFAULT_GROWTH_RATE = 0.970386;   // vega/utils.py:63
+constexpr int PK_MAX_ELL = 4;
+
+struct PkGridDev {
+  int nk, nk_pad, nmu, n_ell;
+  const double* k;
+  const double* pk_lin[3];     // 0 full-smooth, 1 smooth, 2 full
+  const double* pk_fid;
+  const double* mu;
+  const double* wleg;          // [n_ell][nmu]
+  const double* fv_x; const double* fv_f; int fv_n;
+  const double* const* grids;  // static grids, each [nmu][nk]
+};
+
+__device__ __forceinline__ double par(const double* p, int idx, double dflt) {
+  return idx >= 0 ? p[idx] : dflt;
+}
+
+// (bias, beta) of tracer t from any two of (bias, bias_eta, beta): vega/utils.py:45-81
+__device__ __forceinline__ void tracer_bias_beta(const vg_eval_desc& d, const double* p, int t,
+                                                 double& bias, double& beta) {
+  const double f = par(p, d.idx_growth_rate, DEFAULT_GROWTH_RATE);
+  const double eta = par(p, d.idx_bias_eta[t], 0.0);
+  bias = par(p, d.idx_bias[t], 0.0);
+  beta = par(p, d.idx_beta[t], 0.0);
+  if (d.idx_bias[t] < 0) bias = eta * f / beta;
+  if (d.idx_beta[t] < 0) beta = eta * f / bias;
+}
+
+// vega/power_spectrum.py:224-261: scale-dependent bias from UV / HeII fluctuations
+__device__ __forceinline__ void uv_bias_beta(const vg_eval_desc& d, const double* p, double k,
+                                             double& bias, double& beta) {
+  double eff = bias;
+  if (d.uvb) {
+    double x = k * p[d.idx_lambda_uv];
+    double w = atan(x) / x;
+    eff += p[d.idx_bias_gamma] * w / (1.0 + p[d.idx_bias_prim] * w);
+  }
+  if (d.heii) {
+    double x = k * p[d.idx_lambda_heii];
+    double w = atan(x) / x;
+    eff += p[d.idx_bias_gamma_e] * w / (1.0 + p[d.idx_bias_prim] * w);
+  }
+  beta = beta * bias / eff;
+  bias = eff;
+}
+
+// np.interp(x, xp, fp, left=1, right=0) on the Fvoigt table (power_spectrum.py:376-378)
+__device__ __forceinline__ double fvoigt_interp(const PkGridDev& g, double x) {
+  if (x < g.fv_x[0]) return 1.0;
+  if (x > g.fv_x[g.fv_n - 1]) return 0.0;
+  int lo = 0, hi = g.fv_n - 1;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (g.fv_x[mid] <= x) lo = mid; else hi = mid;
+  }
+  double x0 = g.fv_x[lo], x1 = g.fv_x[hi];
+  double slope = (g.fv_f[hi] - g.fv_f[lo]) / (x1 - x0);
+  return slope * (x - x0) + g.fv_f[lo];
+}
+
+// F_hcd(k_par): Rogers2018 exp(-L0 k_par), Fvoigt table, sinc (power_spectrum.py:326-380)
+__device__ __forceinline__ double hcd_profile(const vg_eval_desc& d, const PkGridDev& g,
+                                              double L0, double kpar) {
+  if (d.hcd_model == 1) return exp(-L0 * kpar);
+  if (d.hcd_model == 2) return fvoigt_interp(g, L0 * kpar);
+  double x = kpar * L0;
+  return sin(x) / x;
+}
+
+// Product of the factors selected by `mask` at one grid point.
+__device__ double pk_factors(uint32_t mask, const vg_eval_desc& d, const double* p,
+                             double k, double mu, double pk_fid_k, int* bad) {
+  const double kpar = k * mu;
+  const double kperp = k * sqrt(1.0 - mu * mu);
+  double f = 1.0;
+  if (mask & VG_F_ARINYO) {          // power_spectrum.py:435-479
+    const double q1 = p[d.idx_arinyo[0]], q2 = par(p, d.idx_arinyo[1], 0.0);
+    const double kv = p[d.idx_arinyo[2]], av = p[d.idx_arinyo[3]];
+    const double bv = p[d.idx_arinyo[4]], kp = p[d.idx_arinyo[5]];
+    const double d2 = k * k * k * pk_fid_k / (2.0 * M_PI * M_PI);
+    const double growth = q1 * d2 + q2 * d2 * d2;
+    const double vel = pow(k / kv, av) * pow(fabs(mu), bv);
+    double dnl = exp(growth * (1.0 - vel) - (k / kp) * (k / kp));
+    if (!isfinite(dnl)) *bad |= VG_STATUS_ARINYO;
+    if (d.arinyo_mode == 1) dnl = sqrt(dnl);
+    else if (d.arinyo_mode == 0) dnl = 1.0;
+    f *= dnl;
+  }
+  if (mask & VG_F_MCDONALD) {        // power_spectrum.py:419-433
+    const double kvel = 1.22 * pow(1.0 + k / 0.923, 0.451);
+    f *= exp(pow(k / 6.4, 0.569) - pow(k / 15.3, 2.01) - pow(k * mu / kvel, 1.5));
+  }
+  if (mask & VG_F_GK) {              // power_spectrum.py:481-502
+    if (d.gk_drp != 0.0) { double x = kpar * d.gk_drp / 2.0; f *= sin(x) / x; }
+    if (d.gk_drt != 0.0) { double x = kperp * d.gk_drt / 2.0; f *= sin(x) / x; }
+  }
+  if (mask & VG_F_PEAKNL) {          // power_spectrum.py:382-417
+    const double gr = par(p, d.idx_growth_rate, 0.0);
+    double sp = par(p, d.idx_sigmaNL[0], 0.0), st = par(p, d.idx_sigmaNL[1], 0.0);
+    if (d.idx_sigmaNL[0] < 0) sp = st * (1.0 + gr);
+    if (d.idx_sigmaNL[1] < 0) st = sp / (1.0 + gr);
+    f *= exp(-(kpar * kpar * sp * sp + kperp * kperp * st * st) / 2.0);
+  }
+  if (mask & VG_F_FSGAUSS) {         // power_spectrum.py:504-553, vega/utils.py:396-420
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const double sp = p[d.idx_fs_gauss[2 * i]], st = p[d.idx_fs_gauss[2 * i + 1]];
+      f *= exp(-(kpar * kpar * sp * sp + kperp * kperp * st * st) / 2.0);
+    }
+  }
+  if (mask & VG_F_FSEXP) {           // power_spectrum.py:560-586
+    const double sp = p[d.idx_fs_exp[0]], st = p[d.idx_fs_exp[1]];
+    const double ep = p[d.idx_fs_exp[2]], et = p[d.idx_fs_exp[3]];
+    const double gs = kpar * kpar * sp * sp + kperp * kperp * st * st;
+    const double es = fabs(kpar) * ep * ep + fabs(kperp) * et * et;
+    f *= exp(-gs / 2.0) * exp(-es);
+  }
+  if (mask & VG_F_VELO) {            // power_spectrum.py:588-636
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+      if (d.idx_velo[t] < 0) continue;
+      const double x = kpar * p[d.idx_velo[t]];
+      if (d.velo_kind == 1) f *= exp(-0.25 * x * x);
+      else f *= 1.0 / sqrt(1.0 + x * x);
+    }
+  }
+  if (mask & VG_F_KDAMP) {           // vega/utils.py:423-441
+    f *= exp(-d.kdamp_scale * d.kdamp_scale * pow(k, (double)d.kdamp_power) / 2.0);
+  }
+  return f;
+}
+
+// Kaiser term of tracer t as (a0 + h0 F) + (a1 + h1 F) mu^2, F = F_hcd(k_par)
+// (power_spectrum.py:198-222 with the effective bias/beta of :263-309 substituted).
+struct KaiserCoef {
+  double a0[2], a1[2], h0[2], h1[2];
+  double L0;
+};
+
+__device__ __forceinline__ KaiserCoef kaiser_setup(const vg_eval_desc& d, const double* p, double k) {
+  KaiserCoef c;
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    double b, beta;
+    tracer_bias_beta(d, p, t, b, beta);
+    if (d.uv_on[t] && (d.uvb || d.heii)) uv_bias_beta(d, p, k, b, beta);
+    c.a0[t] = b;
+    c.a1[t] = b * beta;
+    c.h0[t] = 0.0;
+    c.h1[t] = 0.0;
+    if (d.hcd_model && d.hcd_on[t]) {
+      const double bh = p[d.idx_bias_hcd], betah = p[d.idx_beta_hcd];
+      c.h0[t] = bh;
+      c.h1[t] = bh * betah;
+    } else if (d.fast_metals) {   // (1 + beta mu^2) without the bias
+      c.a0[t] = 1.0;
+      c.a1[t] = beta;
+    }
+  }
+  c.L0 = par(p, d.idx_L0, 1.0);
+  return c;
+}
+
+__device__ __forceinline__ double kaiser_eval(const vg_eval_desc& d, const KaiserCoef& c,
+                                              double F, double mu2) {
+  double t0b = fma(c.h0[0], F, c.a0[0]);
+  double t0 = fma(fma(c.h1[0], F, c.a1[0]), mu2, t0b);
+  double t1b = fma(c.h0[1], F, c.a0[1]);
+  double t1 = fma(fma(c.h1[1], F, c.a1[1]), mu2, t1b);
+  if (d.fast_metals && d.hcd_model) {
+    if (d.hcd_on[0]) t0 /= t0b;
+    if (d.hcd_on[1]) t1 /= t1b;
+  }
+  return t0 * t1;
+}
+
+constexpr int PK_KLANES = 32, PK_MUGROUPS = 8;
+
+// Fused K1+K2a.  grid = (ceil(nk/32), n_eval, ceil(B/NB)), block = (32, 8).
+// out[b][eval][l][nk_pad]  (pad columns are never written and stay zero)
+template <int NB, bool DYN>
+__global__ void __launch_bounds__(PK_KLANES * PK_MUGROUPS)
+pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
+              const double* __restrict__ pfull, int npf, int B, double* __restrict__ out,
+              int* __restrict__ status) {
+  __shared__ vg_eval_desc d;
+  __shared__ double red[PK_MUGROUPS][NB * PK_MAX_ELL][PK_KLANES + 1];
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * PK_KLANES + tx;
+  {
+    const int* src = reinterpret_cast<const int*>(evals + blockIdx.y);
+    int* dst = reinterpret_cast<int*>(&d);
+    for (int i = tid; i < (int)(sizeof(vg_eval_desc) / 4); i += PK_KLANES * PK_MUGROUPS) dst[i] = src[i];
+  }
+  __syncthreads();
+  const bool dyn = DYN && d.dyn_mask != 0;
+  const int ik_raw = blockIdx.x * PK_KLANES + tx;
+  const int ik = min(ik_raw, g.nk - 1);
+  const double k = g.k[ik];
+  const double pk_fid_k = g.pk_fid[ik];
+  const int b0 = blockIdx.z * NB;
+
+  KaiserCoef kc[NB];
+  const double* pp[NB];
+#pragma unroll
+  for (int e = 0; e < NB; ++e) {
+    pp[e] = pfull + (long long)min(b0 + e, B - 1) * npf;
+    kc[e] = kaiser_setup(d, pp[e], k);
+  }
+  const double* S = d.static_grid >= 0 ? g.grids[d.static_grid] : nullptr;
+  const double* Fg = (d.hcd_model && d.hcd_grid >= 0) ? g.grids[d.hcd_grid] : nullptr;
+  const bool hcd_dyn = d.hcd_model && d.hcd_grid < 0;
+
+  double acc[NB][PK_MAX_ELL];
+#pragma unroll
+  for (int e = 0; e < NB; ++e)
+#pragma unroll
+    for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = 0.0;
+  int bad[NB];
+#pragma unroll
+  for (int e = 0; e < NB; ++e) bad[e] = 0;
+
+  for (int i = ty; i < g.nmu; i += PK_MUGROUPS) {
+    const double mu = g.mu[i];
+    const double mu2 = mu * mu;
+    double w[PK_MAX_ELL];
+#pragma unroll
+    for (int l = 0; l < PK_MAX_ELL; ++l) w[l] = l < g.n_ell ? g.wleg[l * g.nmu + i] : 0.0;
+    const double s = S ? __ldg(S + (long long)i * g.nk + ik) : 1.0;
+    const double fs = Fg ? __ldg(Fg + (long long)i * g.nk + ik) : 0.0;
+#pragma unroll
+    for (int e = 0; e < NB; ++e) {
+      const double F = hcd_dyn ? hcd_profile(d, g, kc[e].L0, k * mu) : fs;
+      double P = kaiser_eval(d, kc[e], F, mu2) * s;
+      if (dyn) P *= pk_factors(d.dyn_mask, d, pp[e], k, mu, pk_fid_k, &bad[e]);
+#pragma unroll
+      for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = fma(w[l], P, acc[e][l]);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < NB; ++e) {
+#pragma unroll
+    for (int l = 0; l < PK_MAX_ELL; ++l) red[ty][e * PK_MAX_ELL + l][tx] = acc[e][l];
+    if (bad[e] && b0 + e < B) atomicOr(status + b0 + e, bad[e]);
+  }
+  __syncthreads();
+  const double pk_lin = g.pk_lin[d.pk_lin_sel][ik];
+  for (int o = ty; o < NB * PK_MAX_ELL; o += PK_MUGROUPS) {
+    const int e = o / PK_MAX_ELL, l = o % PK_MAX_ELL;
+    if (b0 + e >= B || l >= g.n_ell || ik_raw >= g.nk) continue;
+    double s = 0.0;
+#pragma unroll
+    for (int m = 0; m < PK_MUGROUPS; ++m) s += red[m][o][tx];
+    out[(((long long)(b0 + e) * n_eval + blockIdx.y) * g.n_ell + l) * g.nk_pad + ik] = s * pk_lin;
+  }
+}
+
+// Materialising K1 (HBM-write bound): P(k,mu) of ONE evaluation for every vector of the
+// batch, out[b][nmu][nk].  grid = (ceil(nk/128), nmu, B), block = 128.
+__global__ void __launch_bounds__(128)
+pk_grid_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int eval,
+               const double* __restrict__ pfull, int npf, double* __restrict__ out,
+               int* __restrict__ status) {
+  const vg_eval_desc& d = evals[eval];
+  const int ik = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y, b = blockIdx.z;
+  if (ik >= g.nk) return;
+  const double* p = pfull + (long long)b * npf;
+  const double k = g.k[ik], mu = g.mu[i];
+  KaiserCoef kc = kaiser_setup(d, p, k);
+  double F = 0.0;
+  if (d.hcd_model)
+    F = d.hcd_grid >= 0 ? g.grids[d.hcd_grid][(long long)i * g.nk + ik] : hcd_profile(d, g, kc.L0, k * mu);
+  double P = g.pk_lin[d.pk_lin_sel][ik] * kaiser_eval(d, kc, F, mu * mu);
+  if (d.static_grid >= 0) P *= g.grids[d.static_grid][(long long)i * g.nk + ik];
+  int bad = 0;
+  if (d.dyn_mask) P *= pk_factors(d.dyn_mask, d, p, k, mu, g.pk_fid[ik], &bad);
+  if (bad) atomicOr(status + b, bad);
+  out[((long long)b * g.nmu + i) * g.nk + ik] = P;
+}
+
+// Plan-time: static factor grid of one evaluation from the fiducial parameters
+// (mode 0: product of d.static_mask factors; mode 1: F_hcd(k_par) at the fiducial L0).
+__global__ void __launch_bounds__(128)
+static_grid_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int eval, int mode,
+                   const double* __restrict__ base, double* __restrict__ out, int* __restrict__ bad_out) {
+  const vg_eval_desc& d = evals[eval];
+  const int ik = blockIdx.x * 128 + threadIdx.x, i = blockIdx.y;
+  if (ik >= g.nk) return;
+  const double k = g.k[ik], mu = g.mu[i];
+  int bad = 0;
+  double v;
+  if (mode == 0) v = pk_factors(d.static_mask, d, base, k, mu, g.pk_fid[ik], &bad);
+  else v = hcd_profile(d, g, par(base, d.idx_L0, 1.0), k * mu);
+  if (bad) atomicOr(bad_out, bad);
+  out[(long long)i * g.nk + ik] = v;
+}
+
+// pfull[b][:] = base[:] with the sampled columns overwritten by theta[b][:]
+// (the merge of vega/vega_interface.py:389-404)
+__global__ void expand_theta_kernel(const double* __restrict__ base, int npf,
+                                    const double* __restrict__ theta, int n_theta,
+                                    const int* __restrict__ cols, long long B,
+                                    double* __restrict__ pfull) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * npf) return;
+  pfull[idx] = base[idx % npf];
+}
+__global__ void scatter_theta_kernel(const double* __restrict__ theta, int n_theta,
+                                     const int* __restrict__ cols, long long B, int npf,
+                                     double* __restrict__ pfull) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * n_theta) return;
+  long long b = idx / n_theta;
+  int j = (int)(idx % n_theta);
+  pfull[b * npf + cols[j]] = theta[idx];
+}
+
+}  // namespace vg

@@ -1,0 +1,175 @@
+// Elementwise stages around the K4 GEMMs: peak/smooth/metal combination, broadband
+// polynomials, residual against the data and the chi2 reduction.
+//
+// Restates vega/model.py:119-149,176-186 (component assembly; because the distortion
+// matrix is linear the peak and smooth components are combined BEFORE it:
+//   xi = mul_post * DM[ mul_pre*(bao_amp*peak + smooth + metals + inst) + (1+bao_amp)*add_pre ]
+//        + (1+bao_amp)*add_post,
+// which is algebraically the reference's bao_amp*xi_peak + xi_smooth with every broadband
+// term applied to both components), vega/broadband_poly.py:74-198 and the quadratic form
+// of vega/vega_interface.py:294-319.
+#pragma once
+#include "../../include/vega_b200.h"
+#include "vg_common.cuh"
+#include "vg_pk.cuh"
+
+namespace vg {
+
+struct BroadbandDev {
+  int n_terms;
+  const vg_bb_term* terms;
+  const double* design_pre;  int rows_pre;    // [rows][n_model]
+  const double* design_post; int rows_post;   // [rows][n_dist]
+  const double* sky_pre;                      // [2][n_model]: rt, window
+  const double* sky_post;                     // [2][n_dist]
+};
+
+// value of the broadband at bin i for position pos (0 pre-mul 1 pre-add 2 post-mul 3 post-add)
+__device__ __forceinline__ double bb_eval(const BroadbandDev& bb, int pos, const double* p,
+                                          int i, int n_bins) {
+  const bool mul = (pos & 1) == 0;
+  const double* design = pos < 2 ? bb.design_pre : bb.design_post;
+  const double* sky = pos < 2 ? bb.sky_pre : bb.sky_post;
+  double total = mul ? 1.0 : 0.0;
+  for (int t = 0; t < bb.n_terms; ++t) {
+    const vg_bb_term& term = bb.terms[t];
+    if (term.position != pos) continue;
+    double poly = 0.0;
+    if (term.kind == 0) {
+      for (int c = 0; c < term.n_coef; ++c)
+        poly += p[term.idx_coef[c]] * design[(long long)(term.design_offset + c) * n_bins + i];
+    } else {
+      const double scale = p[term.idx_sky[0]], sigma = p[term.idx_sky[1]];
+      const double rt = sky[i];
+      poly = sky[n_bins + i] != 0.0
+                 ? scale / (sigma * sqrt(2.0 * M_PI)) * exp(-0.5 * (rt / sigma) * (rt / sigma))
+                 : 0.0;
+    }
+    if (mul) total *= (1.0 + poly); else total += poly;
+  }
+  return total;
+}
+
+// xmet_sum[b][i] = sum_c xmet[b][c*ld + i]  (identity metal matrices, vega/data.py:683-684)
+__global__ void metal_sum_kernel(const double* __restrict__ xmet, int n_metal, int ld, int n,
+                                 long long B, double* __restrict__ out) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * ld) return;
+  long long b = idx / ld;
+  int i = (int)(idx % ld);
+  double s = 0.0;
+  if (i < n)
+    for (int c = 0; c < n_metal; ++c) s += xmet[(b * n_metal + c) * ld + i];
+  out[idx] = s;
+}
+
+struct CombineArgs {
+  const double* core;      // [2][B][ld]
+  const double* met;       // [B][ld] or null
+  const double* inst;      // [n] or null
+  int idx_inst_amp; double inst_amp_default;
+  int idx_bao_amp;
+  BroadbandDev bb;
+  const double* pfull; int npf;
+  int n, ld; long long B;
+  double* x;               // [B][ld]
+};
+
+__global__ void combine_pre_kernel(CombineArgs a) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= a.B * a.ld) return;
+  long long b = idx / a.ld;
+  int i = (int)(idx % a.ld);
+  if (i >= a.n) { a.x[idx] = 0.0; return; }
+  const double* p = a.pfull + b * a.npf;
+  const double amp = par(p, a.idx_bao_amp, 1.0);
+  double v = amp * a.core[idx] + a.core[a.B * a.ld + idx];
+  if (a.met) v += a.met[idx];
+  if (a.inst) v += par(p, a.idx_inst_amp, a.inst_amp_default) * a.inst[i];
+  if (a.bb.n_terms) {
+    v *= bb_eval(a.bb, 0, p, i, a.n);
+    v += (1.0 + amp) * bb_eval(a.bb, 1, p, i, a.n);
+  }
+  a.x[idx] = v;
+}
+
+struct PostArgs {
+  const double* y; int ldy;   // distorted model rows; y[b][row]
+  const int* mask_idx;        // [n_out] distorted-grid bin of output j (null: j)
+  int y_is_masked;            // 1: y row j already is bin mask_idx[j]
+  BroadbandDev bb; int n_dist;
+  const double* pfull; int npf; int idx_bao_amp;
+  const double* data;         // [n_out] or null (model output)
+  int n_out, ncols, ldo; long long B;   // columns j < ncols are written (zero for j >= n_out)
+  double* out;                // [B][ldo]: model (data == null) or residual data - model
+};
+
+__global__ void post_kernel(PostArgs a) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= a.B * a.ncols) return;
+  long long b = idx / a.ncols;
+  int j = (int)(idx % a.ncols);
+  double* o = a.out + b * a.ldo + j;
+  if (j >= a.n_out) { *o = 0.0; return; }
+  const double* p = a.pfull + b * a.npf;
+  const int bin = a.mask_idx ? a.mask_idx[j] : j;
+  double v = a.y[b * a.ldy + (a.y_is_masked ? j : bin)];
+  if (a.bb.n_terms) {
+    const double amp = par(p, a.idx_bao_amp, 1.0);
+    v *= bb_eval(a.bb, 2, p, bin, a.n_dist);
+    v += (1.0 + amp) * bb_eval(a.bb, 3, p, bin, a.n_dist);
+  }
+  *o = a.data ? a.data[j] - v : v;
+}
+
+// chi2[b] (+)= sum_j diff[b][j]^2   (identity covariance)
+__global__ void __launch_bounds__(256) chi2_identity_kernel(const double* __restrict__ diff, int n, int ld,
+                                                           double* __restrict__ chi2, int accumulate) {
+  __shared__ double red[256];
+  const long long b = blockIdx.x;
+  double s = 0.0;
+  for (int j = threadIdx.x; j < n; j += 256) { double v = diff[b * ld + j]; s = fma(v, v, s); }
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) chi2[b] = (accumulate ? chi2[b] : 0.0) + red[0];
+}
+
+// chi2[b] (+)= sum_t partial[b][t]  (row-dot partials of the C^-1 GEMM)
+__global__ void chi2_partials_kernel(const double* __restrict__ partial, int n_tiles, long long B,
+                                     double* __restrict__ chi2, int accumulate) {
+  long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  double s = 0.0;
+  for (int t = 0; t < n_tiles; ++t) s += partial[b * n_tiles + t];
+  chi2[b] = (accumulate ? chi2[b] : 0.0) + s;
+}
+
+// chi2[b] += sum_priors (theta - mean)^2 / sigma^2   (vega/vega_interface.py:423-446)
+__global__ void prior_kernel(const double* __restrict__ pfull, int npf, const int* __restrict__ cols,
+                             const double* __restrict__ mean, const double* __restrict__ sigma,
+                             int n_prior, long long B, double* __restrict__ chi2) {
+  long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  double s = 0.0;
+  for (int i = 0; i < n_prior; ++i) {
+    const double dv = pfull[b * npf + cols[i]] - mean[i];
+    s += dv * dv / (sigma[i] * sigma[i]);
+  }
+  chi2[b] += s;
+}
+
+// copy a [B][ld_src] block into a column window of a wider [B][ld_dst] buffer
+__global__ void copy_cols_kernel(const double* __restrict__ src, int ld_src, int n, long long B,
+                                 double* __restrict__ dst, int ld_dst, int col0) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * n) return;
+  long long b = idx / n;
+  int j = (int)(idx % n);
+  dst[b * ld_dst + col0 + j] = src[b * ld_src + j];
+}
+
+}  // namespace vg

@@ -1,0 +1,255 @@
+// K3: Alcock-Paczynski rescaling of the (r,mu) bins, cubic-spline read-out of xi_l(r),
+// Legendre sum, redshift evolution and the additive systematics, for a batch of vectors.
+//
+// Restates vega/correlation_func.py:117-236 (compute / compute_core / _rescale_coords),
+// :276-370 (bias evolution), :446-551 (QSO radiation, relativistic, asymmetry),
+// :628-686 (UV shot noise) and the read-out of vega/pktoxi.py:144-163
+// (interp1d(kind='cubic') in log r == the not-a-knot interpolating cubic spline; its
+// second derivatives arrive from the Hankel GEMM as a linear function of P_l(k)).
+//
+// One CTA handles one (vector, evaluation) pair and a chunk of bins; the knot table of
+// that pair ([n_ell][2][n_out_pad] doubles, ~52 KB) is staged in shared memory with one
+// bulk async copy (TMA, cp.async.bulk + mbarrier) per multipole, then each thread gathers
+// its bins from shared memory.
+#pragma once
+#include "../../include/vega_b200.h"
+#include "vg_common.cuh"
+#include "vg_pk.cuh"
+
+namespace vg {
+
+struct HankelDev {
+  int n_ell, n_out, n_out_pad, bounds_error;
+  int ells[PK_MAX_ELL];
+  const double* xk;        // [n_ell][n_out_pad] knots (log r)
+};
+
+struct StaticXiDev {       // rel l=1, rel l=3, asy l=0, asy l=2
+  int n[4];
+  const double* tab[4];    // [3][n]: knots, values, second derivatives
+};
+
+struct XiArgs {
+  HankelDev h;
+  const vg_eval_desc* evals; int n_eval;
+  const double* pfull; int npf; int B;
+  const double* tables;    // [B][n_eval][n_ell][2*n_out_pad]
+  const double* const* coords;   // coordinate tables, each [5][n_model]
+  const double* opz_eff2;  // per coordinate table: (1+z_eff)^2
+  int n_model;
+  StaticXiDev sx;
+  const double* uv_tau; const double* uv_a; int uv_n;
+  // outputs
+  double* core;            // [2][B][ld_model]   slot 0 peak, 1 smooth
+  double* xmet;            // [B][n_metal*ld_model]
+  int ld_model, n_metal;
+  int* status;
+  int bins_per_cta;
+};
+
+__device__ __forceinline__ double legendre_eval(int l, double x) {
+  const double x2 = x * x;
+  switch (l) {
+    case 0: return 1.0;
+    case 1: return x;
+    case 2: return 1.5 * x2 - 0.5;
+    case 3: return (2.5 * x2 - 1.5) * x;
+    case 4: return (35.0 * x2 * x2 - 30.0 * x2 + 3.0) * 0.125;
+    case 6: return (((231.0 * x2 - 315.0) * x2 + 105.0) * x2 - 5.0) * 0.0625;
+    case 5: return ((63.0 * x2 - 70.0) * x2 + 15.0) * x * 0.125;
+    default: {   // recurrence for anything higher
+      double p0 = 1.0, p1 = x;
+      for (int n = 2; n <= l; ++n) { double pn = ((2 * n - 1) * x * p1 - (n - 1) * p0) / n; p0 = p1; p1 = pn; }
+      return p1;
+    }
+  }
+}
+
+// interval of x in the (almost uniform) knot vector; returns -1/-2 when x is outside
+__device__ __forceinline__ int knot_interval(const double* xk, int n, double x, bool* outside) {
+  const double x0 = xk[0], x1 = xk[n - 1];
+  *outside = !(x >= x0 && x <= x1);
+  int j = (int)floor((x - x0) * (double)(n - 1) / (x1 - x0));
+  j = max(0, min(n - 2, j));
+  while (j > 0 && x < xk[j]) --j;
+  while (j < n - 2 && x >= xk[j + 1]) ++j;
+  return j;
+}
+
+__device__ __forceinline__ double spline_eval(const double* xk, const double* y, const double* m,
+                                              int j, double x) {
+  const double h = xk[j + 1] - xk[j];
+  const double t = (x - xk[j]) / h, a = 1.0 - t;
+  return a * y[j] + t * y[j + 1] + ((a * a * a - a) * m[j] + (t * t * t - t) * m[j + 1]) * (h * h / 6.0);
+}
+
+// (ap, at) from the fit parametrisation: vega/scale_parameters.py:79-125
+__device__ __forceinline__ void scale_ap_at(int form, const int* idx, const double* p,
+                                            double& ap, double& at) {
+  ap = 1.0; at = 1.0;
+  if (form == 1) { ap = p[idx[0]]; at = p[idx[1]]; }
+  else if (form == 2) { double a = p[idx[0]], e = p[idx[1]]; ap = a * (1 + e) * (1 + e); at = a / (1 + e); }
+  else if (form == 3) { double phi = p[idx[0]], al = p[idx[1]]; ap = al / sqrt(phi); at = al * sqrt(phi); }
+}
+
+// vega/correlation_func.py:200-236
+__device__ __forceinline__ void rescale_coords(double r, double mu, double ap, double at, double drp,
+                                               double& r2, double& mu2) {
+  if (r == 0.0) { r2 = 0.0; mu2 = 0.0; return; }
+  const double rp = ap * (r * mu + drp);
+  const double rt = at * (r * sqrt(1.0 - mu * mu));
+  r2 = sqrt(rp * rp + rt * rt);
+  mu2 = rp / r2;
+}
+
+__device__ __forceinline__ double static_xi_eval(const StaticXiDev& sx, int which, double logr) {
+  const int n = sx.n[which];
+  const double* t = sx.tab[which];
+  bool outside;
+  int j = knot_interval(t, n, logr, &outside);
+  return spline_eval(t, t + n, t + 2 * n, j, logr);
+}
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+
+__global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
+  extern __shared__ __align__(128) double sm_tab[];   // [n_ell][2*n_out_pad]
+  __shared__ __align__(8) unsigned long long bar;
+  __shared__ vg_eval_desc d;
+  const int tid = threadIdx.x;
+  const int e = blockIdx.y, b = blockIdx.z;
+  {
+    const int* src = reinterpret_cast<const int*>(a.evals + e);
+    int* dst = reinterpret_cast<int*>(&d);
+    for (int i = tid; i < (int)(sizeof(vg_eval_desc) / 4); i += 256) dst[i] = src[i];
+  }
+  const int row = 2 * a.h.n_out_pad;
+  const unsigned row_bytes = (unsigned)row * 8u;
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(smem_u32(&bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n"
+                 ::"r"(smem_u32(&bar)), "r"(row_bytes * (unsigned)a.h.n_ell) : "memory");
+    const double* src = a.tables + ((long long)b * a.n_eval + e) * a.h.n_ell * row;
+    for (int l = 0; l < a.h.n_ell; ++l) {
+      asm volatile(
+          "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+          ::"r"(smem_u32(sm_tab + l * row)), "l"(src + (long long)l * row), "r"(row_bytes),
+          "r"(smem_u32(&bar)) : "memory");
+    }
+  }
+  // per-vector scalars while the copy is in flight
+  const double* p = a.pfull + (long long)b * a.npf;
+  double ap, at;
+  scale_ap_at(d.scale_form, d.idx_scale, p, ap, at);
+  const double drp = par(p, d.idx_drp, 0.0);
+  const double* ct = a.coords[d.coord_set];
+  const double opz_eff2 = a.opz_eff2[d.coord_set];
+  const int n = a.n_model;
+  double zexp = 0.0;
+  if (d.zevol_kind[0] == 0) zexp += p[d.idx_alpha[0]];
+  if (d.zevol_kind[1] == 0) zexp += p[d.idx_alpha[1]];
+  const bool croom = d.zevol_kind[0] == 1 || d.zevol_kind[1] == 1;
+  const int n_croom = (d.zevol_kind[0] == 1) + (d.zevol_kind[1] == 1);
+  double weight = d.weight_const;
+  if (d.weight_bias) {
+    double b1, be1, b2, be2;
+    tracer_bias_beta(d, p, 0, b1, be1);
+    tracer_bias_beta(d, p, 1, b2, be2);
+    weight *= b1 * b2;
+  }
+  if (d.idx_weight_extra >= 0) weight *= p[d.idx_weight_extra];
+  double* out;
+  if (d.out_slot < 2) out = a.core + ((long long)d.out_slot * a.B + b) * a.ld_model;
+  else out = a.xmet + (long long)b * a.n_metal * a.ld_model + (long long)(d.out_slot - 2) * a.ld_model;
+
+  {  // wait for the table (phase 0)
+    unsigned done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+          : "=r"(done) : "r"(smem_u32(&bar)), "r"(0u) : "memory");
+    }
+  }
+
+  int bad = 0;
+  const int i0 = blockIdx.x * a.bins_per_cta;
+  const int i1 = min(a.ld_model, i0 + a.bins_per_cta);
+  for (int i = i0 + tid; i < i1; i += 256) {
+    if (i >= n) { out[i] = 0.0; continue; }   // keep the GEMM pad columns finite
+    const double r = ct[i], mu = ct[n + i];
+    double r2, mu2;
+    rescale_coords(r, mu, ap, at, drp, r2, mu2);
+    double xi = 0.0;
+    if (r2 != 0.0) {
+      const double x = log(r2);
+      for (int l = 0; l < a.h.n_ell; ++l) {
+        if (d.single_ell >= 0 && a.h.ells[l] != d.single_ell) continue;
+        const double* xk = a.h.xk + l * a.h.n_out_pad;
+        bool outside;
+        const int j = knot_interval(xk, a.h.n_out, x, &outside);
+        if (outside && a.h.bounds_error) bad |= VG_STATUS_BOUNDS;
+        const double v = spline_eval(xk, sm_tab + l * row, sm_tab + l * row + a.h.n_out_pad, j, x);
+        xi += d.single_ell >= 0 ? v : v * legendre_eval(a.h.ells[l], mu2);
+      }
+    }
+    // redshift evolution of the biases (:276-370) and growth (:372-403)
+    double evol = exp(zexp * ct[2 * n + i]);
+    if (croom) {
+      const double p0 = p[d.idx_croom[0]], p1 = p[d.idx_croom[1]];
+      const double c = (p0 + p1 * ct[3 * n + i]) / (p0 + p1 * opz_eff2);
+      evol *= n_croom == 2 ? c * c : c;
+    }
+    xi *= evol;
+    xi *= ct[4 * n + i];
+
+    if (d.radiation && !d.is_peak) {        // :446-489
+      double rp, rt;
+      if (d.rescale_sys) { rp = r2 * mu2 + drp; rt = r2 * sqrt(1.0 - mu2 * mu2); }
+      else { rp = r * mu + drp; rt = r * sqrt(1.0 - mu * mu); }
+      const double rs = sqrt(rp * rp + rt * rt), ms = rp / rs;
+      double v = p[d.idx_qso_rad[0]] / (rs * rs) * (1.0 - p[d.idx_qso_rad[1]] * (1.0 - ms * ms));
+      v *= exp(-rs * ((1.0 + ms) / p[d.idx_qso_rad[2]] + 1.0 / p[d.idx_qso_rad[3]]));
+      xi += v;
+    }
+    if (d.rel || d.asy) {                   // :491-551
+      double ap3, at3, r3, mu3;
+      scale_ap_at(d.scale_form_sys, d.idx_scale_sys, p, ap3, at3);
+      rescale_coords(r, mu, ap3, at3, drp, r3, mu3);
+      const double lx = log(r3);
+      if (d.rel) {
+        xi += p[d.idx_Arel[0]] * static_xi_eval(a.sx, 0, lx) * legendre_eval(1, mu3)
+            + p[d.idx_Arel[1]] * static_xi_eval(a.sx, 1, lx) * legendre_eval(3, mu3);
+      }
+      if (d.asy) {
+        const double t0 = static_xi_eval(a.sx, 2, lx), t2 = static_xi_eval(a.sx, 3, lx);
+        xi += (p[d.idx_Aasy[0]] * t0 - p[d.idx_Aasy[1]] * t2) * r3 * legendre_eval(1, mu3)
+            + p[d.idx_Aasy[2]] * t2 * r3 * legendre_eval(3, mu3);
+      }
+    }
+    if (d.uv_shot) {                        // :628-686
+      const double lam = p[d.idx_uvshot[0]], bg = p[d.idx_uvshot[1]];
+      const double rr = d.rescale_sys ? sqrt(r2 * r2 + mu2 * mu2) : r;
+      const double tau = rr / lam;
+      double av;
+      if (tau < a.uv_tau[0]) av = a.uv_a[0];
+      else if (tau > a.uv_tau[a.uv_n - 1]) av = 0.0;
+      else {
+        int lo = 0, hi = a.uv_n - 1;
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (a.uv_tau[mid] <= tau) lo = mid; else hi = mid; }
+        av = (a.uv_a[hi] - a.uv_a[lo]) / (a.uv_tau[hi] - a.uv_tau[lo]) * (tau - a.uv_tau[lo]) + a.uv_a[lo];
+      }
+      xi += bg * bg * p[d.idx_uvshot[2]] * lam / rr * av;
+    }
+    if (!isfinite(xi)) bad |= VG_STATUS_NONFINITE;
+    out[i] = weight * xi;
+  }
+  if (bad) atomicOr(a.status + b, bad);
+}
+
+}  // namespace vg
