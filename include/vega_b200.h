@@ -155,9 +155,11 @@ int vg_corr_add_coords(vg_plan* plan, int32_t corr, const double* tab, double op
                        int32_t* coord_set);
 int vg_corr_add_eval(vg_plan* plan, int32_t corr, const vg_eval_desc* desc, int32_t* eval_id);
 /* Static spline tables of the relativistic / asymmetry multipoles of the linear P(k)
- * (vega/pktoxi.py:321-382): which = 0 rel l=1, 1 rel l=3, 2 asy l=0, 3 asy l=2;
+ * (vega/pktoxi.py:321-382): which = 0 rel l=1, 1 rel l=3, 2 asy l=0, 3 asy l=2; pk_lin_sel:
+ * the isotropic P(k) of the component it is added to (0 peak, 1 smooth, 2 full);
  * tab[3][n] = knots (log r), values, second derivatives. */
-int vg_corr_set_static_xi(vg_plan* plan, int32_t corr, int32_t which, int32_t n, const double* tab);
+int vg_corr_set_static_xi(vg_plan* plan, int32_t corr, int32_t which, int32_t pk_lin_sel, int32_t n,
+                          const double* tab);
 /* Metal matrix of metal slot c, [n_model][n_model] row-major (vega/metals.py:338-367).
  * Slots never set are identity (the reference's `test` flag, vega/data.py:683-684). */
 int vg_corr_set_metal_matrix(vg_plan* plan, int32_t corr, int32_t slot, const double* mat);

@@ -84,7 +84,7 @@ _SIGNATURES = {
     'vg_plan_add_corr': (C.c_int, [_PTR, i32, i32, i32, C.POINTER(i32)]),
     'vg_corr_add_coords': (C.c_int, [_PTR, i32, _PTR, f64, C.POINTER(i32)]),
     'vg_corr_add_eval': (C.c_int, [_PTR, i32, C.POINTER(EvalDesc), C.POINTER(i32)]),
-    'vg_corr_set_static_xi': (C.c_int, [_PTR, i32, i32, i32, _PTR]),
+    'vg_corr_set_static_xi': (C.c_int, [_PTR, i32, i32, i32, i32, _PTR]),
     'vg_corr_set_metal_matrix': (C.c_int, [_PTR, i32, i32, _PTR]),
     'vg_corr_set_distortion': (C.c_int, [_PTR, i32, _PTR]),
     'vg_corr_set_inst_sys': (C.c_int, [_PTR, i32, _PTR, i32, f64]),

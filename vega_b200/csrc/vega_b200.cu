@@ -114,8 +114,8 @@ struct Corr {
   bool has_invcov = false;
   std::vector<int32_t> mask_host;
   DevBuf d_mask_idx, d_data, d_invcov;   // invcov [n_mask][ld_mask]
-  int sx_n[4] = {0, 0, 0, 0};
-  DevBuf d_sx[4];
+  int sx_n[12] = {0};
+  DevBuf d_sx[12];
 };
 
 }  // namespace
@@ -302,11 +302,12 @@ int vg_corr_add_eval(vg_plan* plan, int32_t corr, const vg_eval_desc* desc, int3
   return VG_OK;
 }
 
-int vg_corr_set_static_xi(vg_plan* plan, int32_t corr, int32_t which, int32_t n, const double* tab) {
+int vg_corr_set_static_xi(vg_plan* plan, int32_t corr, int32_t which, int32_t pk_lin_sel, int32_t n,
+                          const double* tab) {
   VG_CORR(plan, corr);
-  VG_REQUIRE(which >= 0 && which < 4 && n > 3, "bad static xi table");
-  VG_TRY(upload(c.d_sx[which], tab, (size_t)3 * n));
-  c.sx_n[which] = n;
+  VG_REQUIRE(which >= 0 && which < 4 && pk_lin_sel >= 0 && pk_lin_sel < 3 && n > 3, "bad static xi table");
+  VG_TRY(upload(c.d_sx[which * 3 + pk_lin_sel], tab, (size_t)3 * n));
+  c.sx_n[which * 3 + pk_lin_sel] = n;
   return VG_OK;
 }
 
@@ -631,7 +632,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     a.coords = c.d_coord_ptrs.as<const double*>();
     a.opz_eff2 = c.d_opz_eff2.as<double>();
     a.n_model = c.n_model;
-    for (int i = 0; i < 4; ++i) { a.sx.n[i] = c.sx_n[i]; a.sx.tab[i] = c.d_sx[i].as<double>(); }
+    for (int i = 0; i < 12; ++i) { a.sx.n[i] = c.sx_n[i]; a.sx.tab[i] = c.d_sx[i].as<double>(); }
     a.uv_tau = plan->d_uv_tau.as<double>(); a.uv_a = plan->d_uv_a.as<double>(); a.uv_n = plan->uv_n;
     a.core = plan->w_core.as<double>(); a.xmet = plan->w_xmet.as<double>();
     a.ld_model = c.ld_model; a.n_metal = std::max(c.n_metal, 1);

@@ -24,9 +24,9 @@ struct HankelDev {
   const double* xk;        // [n_ell][n_out_pad] knots (log r)
 };
 
-struct StaticXiDev {       // rel l=1, rel l=3, asy l=0, asy l=2
-  int n[4];
-  const double* tab[4];    // [3][n]: knots, values, second derivatives
+struct StaticXiDev {       // [which = rel l=1, rel l=3, asy l=0, asy l=2][pk_lin_sel]
+  int n[12];
+  const double* tab[12];   // [3][n]: knots, values, second derivatives
 };
 
 struct XiArgs {
@@ -223,11 +223,11 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
       rescale_coords(r, mu, ap3, at3, drp, r3, mu3);
       const double lx = log(r3);
       if (d.rel) {
-        xi += p[d.idx_Arel[0]] * static_xi_eval(a.sx, 0, lx) * legendre_eval(1, mu3)
-            + p[d.idx_Arel[1]] * static_xi_eval(a.sx, 1, lx) * legendre_eval(3, mu3);
+        xi += p[d.idx_Arel[0]] * static_xi_eval(a.sx, 0 * 3 + d.pk_lin_sel, lx) * legendre_eval(1, mu3)
+            + p[d.idx_Arel[1]] * static_xi_eval(a.sx, 1 * 3 + d.pk_lin_sel, lx) * legendre_eval(3, mu3);
       }
       if (d.asy) {
-        const double t0 = static_xi_eval(a.sx, 2, lx), t2 = static_xi_eval(a.sx, 3, lx);
+        const double t0 = static_xi_eval(a.sx, 2 * 3 + d.pk_lin_sel, lx), t2 = static_xi_eval(a.sx, 3 * 3 + d.pk_lin_sel, lx);
         xi += (p[d.idx_Aasy[0]] * t0 - p[d.idx_Aasy[1]] * t2) * r3 * legendre_eval(1, mu3)
             + p[d.idx_Aasy[2]] * t2 * r3 * legendre_eval(3, mu3);
       }

@@ -91,6 +91,22 @@ def growth_function(z, Omega_m, Omega_de):
     return get_growth_interp(Omega_m, Omega_de)(z)
 
 
+@lru_cache(maxsize=32)
+def _growth_interp_old(Omega_m, Omega_de):
+    """Deprecated growth table: 100 nodes in z in [0, 5], linear interpolation
+    (vega/correlation_func.py:405-444, old_growth_func = True)."""
+    z_grid = 5. * np.arange(100, dtype=float) / 99
+    growth = np.zeros(100)
+    for i, z in enumerate(z_grid):
+        integral = quad(_growth_integrand, 0, 1 / (1 + z), args=(Omega_m, Omega_de))[0]
+        growth[i] = 5 / 2. * Omega_m * _hubble(z, Omega_m, Omega_de) * integral
+    return interp1d(z_grid, growth)
+
+
+def growth_function_old(z, Omega_m, Omega_de):
+    return _growth_interp_old(Omega_m, Omega_de)(z)
+
+
 def compute_masked_invcov(cov_mat, data_mask):
     """inv(cov[mask][:, mask]) (vega/utils.py:271-299)."""
     masked_cov = cov_mat[:, data_mask][data_mask, :]
@@ -135,3 +151,18 @@ def bias_beta(params, tracer1_name, tracer2_name):
         return bias1, beta1, bias1, beta1
     bias2, beta2 = tracer_bias_beta(params, tracer2_name)
     return bias1, beta1, bias2, beta2
+
+
+def uv_shotnoise_table(ntau=100, nrho=10000):
+    """A(tau) of the UVB shot-noise term, tabulated once at init
+    (vega/correlation_func.py:597-626; Gontcho A Gontcho et al. 2014 eq. 19)."""
+    from scipy.special import expn
+    tau = np.linspace(0.01, 5, ntau)
+    rho = np.linspace(0.0001, 10, nrho)
+    drho = rho[1] - rho[0]
+    amp = np.zeros(ntau)
+    for i, t in enumerate(tau):
+        x = rho * np.sqrt(1 + (t / rho)**2)
+        y = rho * np.abs(1 - t / rho)
+        amp[i] = -np.sum(drho * np.exp(-rho) / rho * (expn(1, x) - expn(1, y)))
+    return tau, amp

@@ -19,7 +19,7 @@ from pathlib import Path
 
 import numpy as np
 
-from . import fitsio, utils
+from . import _lib, fitsio, utils
 from .correlation_item import CorrelationItem
 from .data import Data
 from .parameters import get_default_values
@@ -126,6 +126,8 @@ class VegaInterface:
         self._device = device
         self._batch_chunk = batch_chunk
         self._engine = None
+        self._engine_params = None
+        self._engine_mc = False
         self._fast_metals = False
 
     # -- init-time readers (vega/vega_interface.py:665-851) ---------------------------
@@ -237,3 +239,116 @@ class VegaInterface:
         if params is not None:
             local_params |= params
         return local_params
+
+    # -- device engine -----------------------------------------------------------------------
+    def _engine_for(self, names=()):
+        """The device plan whose batch columns cover the [sample] set plus every name in
+        `names`.  Parameters outside those columns are constants folded into the plan's
+        static grids, so asking for a new one rebuilds the plan."""
+        from .plan import PlanBuilder
+        wanted = list(self.sample_params['limits'].keys())
+        if self._engine is not None:
+            wanted = list(self._engine.sampled)
+        extra = [n for n in names if n not in wanted]
+        if self._engine is None or extra or self._engine_params != self.params:
+            for n in extra:
+                if n not in self.params:
+                    raise KeyError(f'Unknown parameter {n}: it is not listed under [parameters].')
+            self._engine = PlanBuilder(self, sampled=wanted + extra).build(chunk=self._batch_chunk)
+            self._engine_params = dict(self.params)
+            self._engine_mc = False
+        if self._has_data and self._engine_mc != bool(self.monte_carlo):
+            for ci, name in enumerate(self.corr_items):
+                self._engine.set_data(ci, self.data[name], monte_carlo=bool(self.monte_carlo))
+            self._engine_mc = bool(self.monte_carlo)
+        return self._engine
+
+    def _theta_row(self, engine, params=None):
+        local = self._get_lcl_prms(params)
+        return np.array([[local[n] for n in engine.sampled]], dtype=np.float64)
+
+    @property
+    def theta_names(self):
+        """Column names of the batched entry points."""
+        return list(self._engine_for().sampled)
+
+    # -- the reference's scalar API (batch of one) ----------------------------------------------
+    def compute_model(self, params=None, run_init=True, direct_pk=None, marg_coeff=None):
+        """Model xi of every correlation for one parameter dict
+        (vega/vega_interface.py:208-248).  Returns {name: ndarray(n_dist)}."""
+        if direct_pk is not None or marg_coeff is not None:
+            raise NotImplementedError('direct_pk / marg_coeff are not part of the B200 path yet.')
+        engine = self._engine_for(tuple(params) if params else ())
+        models, status = engine.model_device(engine.theta_tensor(self._theta_row(engine, params)))
+        status = int(status.cpu()[0])
+        if status & _lib.STATUS_ARINYO:
+            raise utils.VegaArinyoError
+        if status & _lib.STATUS_BOUNDS:
+            raise utils.VegaBoundsError
+        return {name: xi[0].cpu().numpy() for name, xi in models.items()}
+
+    def chi2(self, params=None, direct_pk=None, return_marg_coeff=False):
+        """chi2 incl. priors for one parameter dict (vega/vega_interface.py:250-325);
+        model-domain failures give 1e100."""
+        assert self._has_data
+        if direct_pk is not None or return_marg_coeff:
+            raise NotImplementedError('direct_pk / marginalisation are not part of the B200 path yet.')
+        engine = self._engine_for(tuple(params) if params else ())
+        chi2, status = engine.chi2_host(self._theta_row(engine, params))
+        if status[0] & (_lib.STATUS_ARINYO | _lib.STATUS_BOUNDS):
+            return 1e100
+        chi2 = float(chi2[0])
+        assert isinstance(chi2, float)
+        return chi2
+
+    def log_lik(self, params=None, direct_pk=None, return_marg_coeff=False):
+        """Log-likelihood for one parameter dict (vega/vega_interface.py:327-387)."""
+        assert self._has_data
+        chi2 = self.chi2(params, direct_pk, return_marg_coeff)
+        return float(self._log_norm() - 0.5 * chi2)
+
+    def _log_norm(self):
+        """Parameter-independent part of log_lik (vega/vega_interface.py:351-369)."""
+        log_norm = 0.
+        for name in self.corr_items:
+            log_norm -= 0.5 * self.data[name].data_size * np.log(2 * np.pi)
+            if not self._use_global_cov:
+                log_norm -= 0.5 * (self.data[name].scaled_log_cov_det if self.monte_carlo
+                                   else self.data[name].log_cov_det)
+        if self._use_global_cov:
+            log_norm -= 0.5 * self.masked_global_log_cov_det
+        for prior in self.priors.values():
+            log_norm += self._gaussian_lik_prior(prior[1])
+        return log_norm
+
+    # -- batched API (new) -----------------------------------------------------------------------
+    def chi2_batch(self, theta, names=None):
+        """chi2 of B parameter vectors.  theta: ndarray [B, P] with columns `names`
+        (default: the [sample] set, see theta_names).  Host in, host out."""
+        engine = self._engine_for(tuple(names) if names else ())
+        theta = self._reorder(engine, theta, names)
+        chi2, status = engine.chi2_host(theta)
+        chi2[(status & (_lib.STATUS_ARINYO | _lib.STATUS_BOUNDS)) != 0] = 1e100
+        return chi2
+
+    def log_lik_batch(self, theta, names=None):
+        return self._log_norm() - 0.5 * self.chi2_batch(theta, names)
+
+    def compute_model_batch(self, theta, names=None):
+        """{name: ndarray [B, n_dist]} for B parameter vectors."""
+        engine = self._engine_for(tuple(names) if names else ())
+        theta = self._reorder(engine, theta, names)
+        models, status = engine.model_device(engine.theta_tensor(theta))
+        return {name: xi.cpu().numpy() for name, xi in models.items()}, status.cpu().numpy()
+
+    def _reorder(self, engine, theta, names):
+        theta = np.atleast_2d(np.asarray(theta, dtype=np.float64))
+        if names is None or list(names) == engine.sampled:
+            if theta.shape[1] != len(engine.sampled):
+                raise ValueError(f'theta has {theta.shape[1]} columns, expected {len(engine.sampled)}: '
+                                 f'{engine.sampled}')
+            return theta
+        full = np.tile([self.params[n] for n in engine.sampled], (theta.shape[0], 1))
+        for j, n in enumerate(names):
+            full[:, engine.sampled.index(n)] = theta[:, j]
+        return full
