@@ -211,6 +211,12 @@ int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
                    const double* theta_dev, int64_t B, double* out_dev, int32_t* status_dev,
                    void* stream);
 int64_t vg_stage_size(const vg_plan* plan, int32_t corr, int32_t stage);
+/* Per-stage device timing with CUDA events on the launch stream (bench.py roofline figures).
+ * Tags: 0 P(k,mu)->multipoles, 1 Hankel GEMM, 2 xi gather, 3 metal GEMM, 4 distortion GEMM,
+ * 5 C^-1 GEMM, 6 elementwise stages.  vg_profile_read synchronises the device, fills
+ * ms_per_tag[8] / count_per_tag[8] with the totals since the last read and resets them. */
+int vg_profile_enable(vg_plan* plan, int enable);
+int vg_profile_read(vg_plan* plan, double* ms_per_tag, int64_t* count_per_tag);
 /* Number of kernels launched by the library since the last call (bench bookkeeping) */
 int64_t vg_launch_count(int reset);
 

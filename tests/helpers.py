@@ -29,3 +29,15 @@ def make_oracle(main_ini, omega_de_none=False, **kw):
     if omega_de_none:
         vega.fiducial['Omega_de'] = None
     return vega, Oracle(vega, tables=static_tables(), **kw)
+
+
+def make_c2(n_theta, width=3.0, main_ini='configs/c2/main.ini'):
+    """C2 workload: dense synthetic operands injected BEFORE the oracle is built (the oracle
+    captures the metal matrices at construction), mock data drawn around the oracle model."""
+    from oracle.vega_oracle import Oracle
+    from vega_b200 import synthetic
+    vega = VegaInterface(main_ini)
+    synthetic.inject_dense_operands(vega)
+    oracle = Oracle(vega, tables=static_tables())
+    synthetic.draw_mock_data(vega, oracle.compute_model())
+    return vega, oracle, synthetic.draw_theta(vega, n_theta, width=width)

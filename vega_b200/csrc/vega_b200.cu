@@ -95,6 +95,8 @@ struct Corr {
   int hankel_id = 0, n_model = 0, n_dist = 0, ld_model = 0, ld_dist = 0;
   std::vector<vg_eval_desc> evals;
   DevBuf d_evals;
+  std::vector<int> mode_ids[3];   // evaluations grouped by pk_ell kernel mode
+  DevBuf d_mode_ids[3];
   std::vector<DevBuf> coords;
   std::vector<double> opz_eff2;
   DevBuf d_coord_ptrs, d_opz_eff2;
@@ -134,6 +136,7 @@ struct vg_plan {
   DevBuf d_grid_ptrs;
   bool finalized = false;
   int static_bad = 0;
+  int std_ells = 0;
   // global covariance
   bool has_global = false; int n_total = 0, ld_total = 0;
   DevBuf d_global_invcov;
@@ -142,10 +145,16 @@ struct vg_plan {
   DevBuf w_pfull, w_pkell, w_tables, w_core, w_xmet, w_met, w_x, w_y, w_diff, w_partial, w_split,
       w_chi2, w_status, w_theta;
   void* pinned = nullptr; size_t pinned_bytes = 0;
+  // optional per-stage timing with CUDA events (bench.py roofline figures)
+  bool profile = false;
+  struct ProfRec { int tag; cudaEvent_t e0, e1; };
+  std::vector<ProfRec> prof_recs;
+  std::vector<cudaEvent_t> prof_pool;
 
   vg::PkGridDev grid_dev() const {
     vg::PkGridDev g{};
     g.nk = nk; g.nk_pad = nk_pad; g.nmu = nmu; g.n_ell = n_ell;
+    g.std_ells = std_ells;
     g.k = d_k.as<double>();
     for (int i = 0; i < 3; ++i) g.pk_lin[i] = d_pk[i].as<double>();
     g.pk_fid = d_pk_fid.as<double>();
@@ -156,6 +165,26 @@ struct vg_plan {
     return g;
   }
 };
+
+namespace {
+// Brackets a stage with two events on the launch stream when profiling is on.
+struct ProfScope {
+  vg_plan* plan; cudaStream_t st; cudaEvent_t e1 = nullptr;
+  ProfScope(vg_plan* p, int tag, cudaStream_t s) : plan(p), st(s) {
+    if (!plan->profile) return;
+    cudaEvent_t ev[2];
+    for (auto& e : ev) {
+      if (!plan->prof_pool.empty()) { e = plan->prof_pool.back(); plan->prof_pool.pop_back(); }
+      else cudaEventCreate(&e);
+    }
+    cudaEventRecord(ev[0], st);
+    e1 = ev[1];
+    plan->prof_recs.push_back({tag, ev[0], ev[1]});
+  }
+  ~ProfScope() { if (e1) cudaEventRecord(e1, st); }
+};
+enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_NTAGS = 8 };
+}  // namespace
 
 extern "C" {
 
@@ -401,6 +430,10 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
   }
   VG_TRY(upload(plan->d_grid_ptrs, ptrs.data(), ptrs.size()));
 
+  plan->std_ells = 1;
+  for (auto& h : plan->hankels)
+    for (int l = 0; l < vg::PK_MAX_ELL; ++l)
+      if (h->n_ell != 4 || h->ells[l] != 2 * l) plan->std_ells = 0;
   DevBuf bad;
   VG_TRY(bad.alloc(sizeof(int)));
   std::vector<char> built(n_grids, 0);
@@ -408,6 +441,13 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
     Corr& c = *cp;
     VG_REQUIRE(!c.evals.empty(), "correlation without evaluations");
     VG_TRY(upload(c.d_evals, c.evals.data(), c.evals.size()));
+    for (auto& ids : c.mode_ids) ids.clear();
+    for (size_t e = 0; e < c.evals.size(); ++e) {
+      const uint32_t m = c.evals[e].dyn_mask;
+      c.mode_ids[m == 0 ? vg::PK_MODE_STATIC : (m == VG_F_VELO ? vg::PK_MODE_VELO : vg::PK_MODE_GENERIC)].push_back((int)e);
+    }
+    for (int m = 0; m < 3; ++m)
+      if (!c.mode_ids[m].empty()) VG_TRY(upload(c.d_mode_ids[m], c.mode_ids[m].data(), c.mode_ids[m].size()));
     std::vector<const double*> cptrs;
     for (auto& b : c.coords) cptrs.push_back(b.as<double>());
     VG_TRY(upload(c.d_coord_ptrs, cptrs.data(), cptrs.size()));
@@ -563,6 +603,7 @@ int ensure_workspace(vg_plan* plan, long long Bc_) {
 }
 
 int expand_params(vg_plan* plan, const double* theta_dev, long long Bc, int* status_dev, cudaStream_t st) {
+  ProfScope prof(plan, PROF_ELEM, st);
   const long long n = Bc * plan->npf;
   vg::expand_theta_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->d_base.as<double>(), plan->npf, theta_dev,
                                                         plan->n_theta, plan->d_theta_cols.as<int>(), Bc,
@@ -595,33 +636,47 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   const Hankel& h = *plan->hankels[c.hankel_id];
   const int E = (int)c.evals.size();
   vg::PkGridDev g = plan->grid_dev();
-  bool any_dyn = false;
-  for (auto& d : c.evals) any_dyn |= d.dyn_mask != 0;
   {  // K1 + K2a
-    dim3 block(vg::PK_KLANES, vg::PK_MUGROUPS);
+    ProfScope prof(plan, PROF_PK, st);
     const vg_eval_desc* ev = c.d_evals.as<vg_eval_desc>();
     double* out = plan->w_pkell.as<double>();
     const double* pf = plan->w_pfull.as<double>();
-    if (Bc >= 4) {
-      dim3 grid(vg_cdiv(plan->nk, vg::PK_KLANES), E, vg_cdiv(Bc, 4));
-      if (any_dyn) vg::pk_ell_kernel<4, true><<<grid, block, 0, st>>>(g, ev, E, pf, plan->npf, (int)Bc, out, status_dev);
-      else vg::pk_ell_kernel<4, false><<<grid, block, 0, st>>>(g, ev, E, pf, plan->npf, (int)Bc, out, status_dev);
-    } else {
-      dim3 grid(vg_cdiv(plan->nk, vg::PK_KLANES), E, (unsigned)Bc);
-      if (any_dyn) vg::pk_ell_kernel<1, true><<<grid, block, 0, st>>>(g, ev, E, pf, plan->npf, (int)Bc, out, status_dev);
-      else vg::pk_ell_kernel<1, false><<<grid, block, 0, st>>>(g, ev, E, pf, plan->npf, (int)Bc, out, status_dev);
+    const int NB = Bc >= 2 ? 2 : 1;
+    const int groups = vg_cdiv(Bc, NB);
+    const int EG = groups >= 4 ? 4 : (groups >= 2 ? 2 : 1);
+    dim3 block(vg::PK_KLANES, vg::PK_GROUPS / EG, EG);
+    for (int m = 0; m < 3; ++m) {
+      if (c.mode_ids[m].empty()) continue;
+      dim3 grid(vg_cdiv(Bc, NB * EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)c.mode_ids[m].size());
+      const int* ids = c.d_mode_ids[m].as<int>();
+#define VG_PK_LAUNCH(NBV, MODEV) \
+      vg::pk_ell_kernel<NBV, MODEV><<<grid, block, 0, st>>>(g, ev, E, ids, pf, plan->npf, (int)Bc, out, status_dev)
+      if (NB == 2) {
+        if (m == 0) VG_PK_LAUNCH(2, vg::PK_MODE_STATIC);
+        else if (m == 1) VG_PK_LAUNCH(2, vg::PK_MODE_VELO);
+        else VG_PK_LAUNCH(2, vg::PK_MODE_GENERIC);
+      } else {
+        if (m == 0) VG_PK_LAUNCH(1, vg::PK_MODE_STATIC);
+        else if (m == 1) VG_PK_LAUNCH(1, vg::PK_MODE_VELO);
+        else VG_PK_LAUNCH(1, vg::PK_MODE_GENERIC);
+      }
+#undef VG_PK_LAUNCH
+      VG_LAUNCHED();
     }
-    VG_LAUNCHED();
   }
   if (upto <= 1) return VG_OK;
   // K2b: Hankel + spline operator, one GEMM batched over the multipoles
   const int rowT = 2 * h.n_out_pad;
+  {
+  ProfScope prof(plan, PROF_HANKEL, st);
   VG_TRY(gemm_auto(plan, plan->w_pkell.as<double>(), (long long)plan->n_ell * plan->nk_pad,
                    h.op.as<double>(), plan->nk_pad, plan->w_tables.as<double>(),
                    (long long)plan->n_ell * rowT, (int)(Bc * E), rowT, plan->nk_pad, plan->n_ell,
                    plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
+  }
   if (upto <= 2) return VG_OK;
   {  // K3
+    ProfScope prof(plan, PROF_XI, st);
     vg::XiArgs a{};
     a.h.n_ell = h.n_ell; a.h.n_out = h.n_out; a.h.n_out_pad = h.n_out_pad; a.h.bounds_error = h.bounds_error;
     for (int l = 0; l < vg::PK_MAX_ELL; ++l) a.h.ells[l] = h.ells[l];
@@ -655,6 +710,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   // metals: sum_c w_c M_c xi_c  (vega/metals.py:258-367)
   const double* met = nullptr;
   if (c.n_metal > 0) {
+    ProfScope prof(plan, c.metal_dense ? PROF_METAL : PROF_ELEM, st);
     if (c.metal_dense) {
       const long long ldk = (long long)c.n_metal * c.ld_model;
       VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, c.d_mcat.as<double>(), ldk,
@@ -677,6 +733,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   ca.n = c.n_model; ca.ld = c.ld_model; ca.B = Bc;
   ca.x = plan->w_x.as<double>();
   const long long n = Bc * c.ld_model;
+  ProfScope prof(plan, PROF_ELEM, st);
   vg::combine_pre_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(ca);
   VG_LAUNCHED();
   return VG_OK;
@@ -695,6 +752,7 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
   int ldy = c.ld_model;
   int y_is_masked = 0;
   if (c.has_dmat) {
+    ProfScope prof(plan, PROF_DM, st);
     if (residual) {
       VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_dmat_masked.as<double>(), c.ld_model,
                        plan->w_y.as<double>(), c.ld_mask, (int)Bc, c.n_mask, c.ld_model, 1, 0, 0, 0, st));
@@ -715,6 +773,7 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
   pa.n_out = residual ? c.n_mask : c.n_dist;
   pa.ldo = ldo; pa.ncols = ncols; pa.B = Bc; pa.out = out;
   const long long n = Bc * ncols;
+  ProfScope prof(plan, PROF_ELEM, st);
   vg::post_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(pa);
   VG_LAUNCHED();
   return VG_OK;
@@ -723,6 +782,7 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
 // chi2[b] (+)= diff[b]^T invcov diff[b]
 int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* invcov, long long Bc,
               double* chi2, int accumulate, cudaStream_t st) {
+  ProfScope prof(plan, invcov ? PROF_CHI2 : PROF_ELEM, st);
   if (!invcov) {
     vg::chi2_identity_kernel<<<(unsigned)Bc, 256, 0, st>>>(diff, n, ld, chi2, accumulate);
     VG_LAUNCHED();
@@ -849,6 +909,28 @@ int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, doubl
 }
 
 int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }
+
+int vg_profile_enable(vg_plan* plan, int enable) {
+  VG_REQUIRE(plan, "null plan");
+  plan->profile = enable != 0;
+  return VG_OK;
+}
+
+int vg_profile_read(vg_plan* plan, double* ms_per_tag, int64_t* count_per_tag) {
+  VG_REQUIRE(plan && ms_per_tag && count_per_tag, "vg_profile_read: bad arguments");
+  VG_CUDA_CHECK(cudaDeviceSynchronize());
+  for (int t = 0; t < PROF_NTAGS; ++t) { ms_per_tag[t] = 0.0; count_per_tag[t] = 0; }
+  for (auto& r : plan->prof_recs) {
+    float ms = 0.f;
+    VG_CUDA_CHECK(cudaEventElapsedTime(&ms, r.e0, r.e1));
+    ms_per_tag[r.tag] += ms;
+    count_per_tag[r.tag] += 1;
+    plan->prof_pool.push_back(r.e0);
+    plan->prof_pool.push_back(r.e1);
+  }
+  plan->prof_recs.clear();
+  return VG_OK;
+}
 
 int64_t vg_stage_size(const vg_plan* plan, int32_t corr, int32_t stage) {
   if (!plan || corr < 0 || corr >= (int)plan->corrs.size()) return -1;

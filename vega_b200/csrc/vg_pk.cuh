@@ -23,6 +23,7 @@ constexpr int PK_MAX_ELL = 4;
 
 struct PkGridDev {
   int nk, nk_pad, nmu, n_ell;
+  int std_ells;                // multipoles are exactly (0, 2, 4, 6): Legendre weights in registers
   const double* k;
   const double* pk_lin[3];     // 0 full-smooth, 1 smooth, 2 full
   const double* pk_fid;
@@ -195,41 +196,75 @@ __device__ __forceinline__ double kaiser_eval(const vg_eval_desc& d, const Kaise
   return t0 * t1;
 }
 
-constexpr int PK_KLANES = 32, PK_MUGROUPS = 8;
+constexpr int PK_KLANES = 32, PK_GROUPS = 8;   // CTA = 32 k lanes x (MG mu groups x EG vector groups)
+constexpr int PK_UNROLL = 4;                   // mu rows whose grid loads are issued together
 
-// Fused K1+K2a.  grid = (ceil(nk/32), n_eval, ceil(B/NB)), block = (32, 8).
+// Legendre weights are applied as L_l(mu) inside the loop and dmu*(2l+1) once at the end
+__device__ __forceinline__ void legendre_0246(double mu2, double* L) {
+  L[0] = 1.0;
+  L[1] = fma(1.5, mu2, -0.5);
+  L[2] = fma(fma(4.375, mu2, -3.75), mu2, 0.375);
+  L[3] = fma(fma(fma(14.4375, mu2, -19.6875), mu2, 6.5625), mu2, -0.3125);
+}
+
+enum { PK_MODE_STATIC = 0, PK_MODE_VELO = 1, PK_MODE_GENERIC = 2 };
+
+// Fused K1+K2a.  grid = (ceil(B / (NB*EG)), ceil(nk/32), n_ids), block = (32, MG, EG),
+// MG*EG = 8.  A thread owns one k, the mu rows i = mg, mg+MG, ... and NB parameter vectors;
+// the EG vector groups of a CTA walk the same (mu, k) addresses, so the static grids are
+// fetched from L2 once per NB*EG vectors.  MODE selects how the per-vector factors are
+// evaluated: none, velocity dispersion only (parameters hoisted into registers), or the
+// generic path that reads parameters per point.
 // out[b][eval][l][nk_pad]  (pad columns are never written and stay zero)
-template <int NB, bool DYN>
-__global__ void __launch_bounds__(PK_KLANES * PK_MUGROUPS)
+template <int NB, int MODE>
+__global__ void __launch_bounds__(PK_KLANES * PK_GROUPS, 2)
 pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
-              const double* __restrict__ pfull, int npf, int B, double* __restrict__ out,
-              int* __restrict__ status) {
+              const int* __restrict__ eval_ids, const double* __restrict__ pfull, int npf, int B,
+              double* __restrict__ out, int* __restrict__ status) {
   __shared__ vg_eval_desc d;
-  __shared__ double red[PK_MUGROUPS][NB * PK_MAX_ELL][PK_KLANES + 1];
-  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * PK_KLANES + tx;
+  __shared__ double red[PK_GROUPS][NB * PK_MAX_ELL][PK_KLANES + 1];
+  const int tx = threadIdx.x, mg = threadIdx.y, eg = threadIdx.z;
+  const int MG = blockDim.y, EG = blockDim.z;
+  const int tid = (eg * MG + mg) * PK_KLANES + tx;
+  const int eval = eval_ids[blockIdx.z];
   {
-    const int* src = reinterpret_cast<const int*>(evals + blockIdx.y);
+    const int* src = reinterpret_cast<const int*>(evals + eval);
     int* dst = reinterpret_cast<int*>(&d);
-    for (int i = tid; i < (int)(sizeof(vg_eval_desc) / 4); i += PK_KLANES * PK_MUGROUPS) dst[i] = src[i];
+    for (int i = tid; i < (int)(sizeof(vg_eval_desc) / 4); i += PK_KLANES * PK_GROUPS) dst[i] = src[i];
   }
   __syncthreads();
-  const bool dyn = DYN && d.dyn_mask != 0;
-  const int ik_raw = blockIdx.x * PK_KLANES + tx;
+  const int ik_raw = blockIdx.y * PK_KLANES + tx;
   const int ik = min(ik_raw, g.nk - 1);
   const double k = g.k[ik];
   const double pk_fid_k = g.pk_fid[ik];
-  const int b0 = blockIdx.z * NB;
+  const int b0 = (blockIdx.x * EG + eg) * NB;
 
-  KaiserCoef kc[NB];
+  // per-vector Kaiser coefficients: term_t = (a0 + h0 F) + (a1 + h1 F) mu^2
+  double a0[NB][2], a1[NB][2], h0[NB][2], h1[NB][2], L0[NB], sv[NB][2];
   const double* pp[NB];
 #pragma unroll
   for (int e = 0; e < NB; ++e) {
     pp[e] = pfull + (long long)min(b0 + e, B - 1) * npf;
-    kc[e] = kaiser_setup(d, pp[e], k);
+    const KaiserCoef kc = kaiser_setup(d, pp[e], k);
+#pragma unroll
+    for (int t = 0; t < 2; ++t) { a0[e][t] = kc.a0[t]; a1[e][t] = kc.a1[t]; h0[e][t] = kc.h0[t]; h1[e][t] = kc.h1[t]; }
+    L0[e] = kc.L0;
+    if (MODE == PK_MODE_VELO) {
+#pragma unroll
+      for (int t = 0; t < 2; ++t) sv[e][t] = d.idx_velo[t] >= 0 ? pp[e][d.idx_velo[t]] : 0.0;
+    }
   }
-  const double* S = d.static_grid >= 0 ? g.grids[d.static_grid] : nullptr;
-  const double* Fg = (d.hcd_model && d.hcd_grid >= 0) ? g.grids[d.hcd_grid] : nullptr;
+  const double* S = d.static_grid >= 0 ? g.grids[d.static_grid] + ik : nullptr;
+  const double* Fg = (d.hcd_model && d.hcd_grid >= 0) ? g.grids[d.hcd_grid] + ik : nullptr;
+  const bool hcd_any = d.hcd_model != 0;
   const bool hcd_dyn = d.hcd_model && d.hcd_grid < 0;
+  const bool same = d.same_tracer != 0;
+  const bool divide0 = d.fast_metals && d.hcd_model && d.hcd_on[0];
+  const bool divide1 = d.fast_metals && d.hcd_model && d.hcd_on[1];
+  const bool std_ells = g.std_ells != 0;
+  const int velo_kind = d.velo_kind;
+  const uint32_t dyn_mask = d.dyn_mask;
+  const double inv_nmu = 1.0 / (double)g.nmu;
 
   double acc[NB][PK_MAX_ELL];
 #pragma unroll
@@ -240,39 +275,93 @@ pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
 #pragma unroll
   for (int e = 0; e < NB; ++e) bad[e] = 0;
 
-  for (int i = ty; i < g.nmu; i += PK_MUGROUPS) {
-    const double mu = g.mu[i];
-    const double mu2 = mu * mu;
-    double w[PK_MAX_ELL];
+  const int step = MG * PK_UNROLL;
+  for (int i0 = mg; i0 < g.nmu; i0 += step) {
+    double s[PK_UNROLL], fs[PK_UNROLL];
 #pragma unroll
-    for (int l = 0; l < PK_MAX_ELL; ++l) w[l] = l < g.n_ell ? g.wleg[l * g.nmu + i] : 0.0;
-    const double s = S ? __ldg(S + (long long)i * g.nk + ik) : 1.0;
-    const double fs = Fg ? __ldg(Fg + (long long)i * g.nk + ik) : 0.0;
+    for (int u = 0; u < PK_UNROLL; ++u) {
+      const int i = i0 + u * MG;
+      const bool in = i < g.nmu;
+      s[u] = (S && in) ? __ldg(S + (long long)i * g.nk) : 1.0;
+      fs[u] = (Fg && in) ? __ldg(Fg + (long long)i * g.nk) : 0.0;
+    }
 #pragma unroll
-    for (int e = 0; e < NB; ++e) {
-      const double F = hcd_dyn ? hcd_profile(d, g, kc[e].L0, k * mu) : fs;
-      double P = kaiser_eval(d, kc[e], F, mu2) * s;
-      if (dyn) P *= pk_factors(d.dyn_mask, d, pp[e], k, mu, pk_fid_k, &bad[e]);
+    for (int u = 0; u < PK_UNROLL; ++u) {
+      const int i = i0 + u * MG;
+      if (i >= g.nmu) break;
+      const double mu = ((double)i + 0.5) / (double)g.nmu;   // == g.mu[i] (power_spectrum.py:77)
+      const double mu2 = mu * mu;
+      double w[PK_MAX_ELL];
+      if (std_ells) {
+        legendre_0246(mu2, w);
+      } else {
 #pragma unroll
-      for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = fma(w[l], P, acc[e][l]);
+        for (int l = 0; l < PK_MAX_ELL; ++l) w[l] = l < g.n_ell ? g.wleg[l * g.nmu + i] : 0.0;
+      }
+      const double kpar = k * mu;
+#pragma unroll
+      for (int e = 0; e < NB; ++e) {
+        double F = fs[u];
+        if (hcd_dyn) F = hcd_profile(d, g, L0[e], kpar);
+        double t0, t1;
+        if (hcd_any) {
+          const double t0b = fma(h0[e][0], F, a0[e][0]);
+          t0 = fma(fma(h1[e][0], F, a1[e][0]), mu2, t0b);
+          if (divide0) t0 /= t0b;
+          if (same) {
+            t1 = t0;
+          } else {
+            const double t1b = fma(h0[e][1], F, a0[e][1]);
+            t1 = fma(fma(h1[e][1], F, a1[e][1]), mu2, t1b);
+            if (divide1) t1 /= t1b;
+          }
+        } else {
+          t0 = fma(a1[e][0], mu2, a0[e][0]);
+          t1 = same ? t0 : fma(a1[e][1], mu2, a0[e][1]);
+        }
+        double P = t0 * t1 * s[u];
+        if (MODE == PK_MODE_VELO) {
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            if (d.idx_velo[t] < 0) continue;
+            const double x = kpar * sv[e][t];
+            if (velo_kind == 1) P *= exp(-0.25 * x * x);
+            else P *= rsqrt(fma(x, x, 1.0));
+          }
+        } else if (MODE == PK_MODE_GENERIC) {
+          P *= pk_factors(dyn_mask, d, pp[e], k, mu, pk_fid_k, &bad[e]);
+        }
+#pragma unroll
+        for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = fma(w[l], P, acc[e][l]);
+      }
+    }
+  }
+  (void)inv_nmu;
+  // deterministic reduction over the mu groups, one vector group at a time
+  for (int turn = 0; turn < EG; ++turn) {
+    __syncthreads();
+    if (eg == turn) {
+#pragma unroll
+      for (int e = 0; e < NB; ++e)
+#pragma unroll
+        for (int l = 0; l < PK_MAX_ELL; ++l) red[mg][e * PK_MAX_ELL + l][tx] = acc[e][l];
+    }
+    __syncthreads();
+    if (eg == turn) {
+      const double pk_lin = g.pk_lin[d.pk_lin_sel][ik];
+      for (int o = mg; o < NB * PK_MAX_ELL; o += MG) {
+        const int e = o / PK_MAX_ELL, l = o % PK_MAX_ELL;
+        if (b0 + e >= B || l >= g.n_ell || ik_raw >= g.nk) continue;
+        double sum = 0.0;
+        for (int m = 0; m < MG; ++m) sum += red[m][o][tx];
+        if (std_ells) sum *= (double)(4 * l + 1) / (double)g.nmu;   // dmu * (2 ell + 1), ell = 2l
+        out[(((long long)(b0 + e) * n_eval + eval) * g.n_ell + l) * g.nk_pad + ik] = sum * pk_lin;
+      }
     }
   }
 #pragma unroll
-  for (int e = 0; e < NB; ++e) {
-#pragma unroll
-    for (int l = 0; l < PK_MAX_ELL; ++l) red[ty][e * PK_MAX_ELL + l][tx] = acc[e][l];
+  for (int e = 0; e < NB; ++e)
     if (bad[e] && b0 + e < B) atomicOr(status + b0 + e, bad[e]);
-  }
-  __syncthreads();
-  const double pk_lin = g.pk_lin[d.pk_lin_sel][ik];
-  for (int o = ty; o < NB * PK_MAX_ELL; o += PK_MUGROUPS) {
-    const int e = o / PK_MAX_ELL, l = o % PK_MAX_ELL;
-    if (b0 + e >= B || l >= g.n_ell || ik_raw >= g.nk) continue;
-    double s = 0.0;
-#pragma unroll
-    for (int m = 0; m < PK_MUGROUPS; ++m) s += red[m][o][tx];
-    out[(((long long)(b0 + e) * n_eval + blockIdx.y) * g.n_ell + l) * g.nk_pad + ik] = s * pk_lin;
-  }
 }
 
 // Materialising K1 (HBM-write bound): P(k,mu) of ONE evaluation for every vector of the
