@@ -135,3 +135,207 @@ class ClockSampler:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['no samples']}
         return {'sm_mhz': float(np.median(sm)), 'sm_max_mhz': float(max(mx)), 'reasons': sorted(reasons),
                 'samples': len(sm)}
+
+
+def gemm_flops(engine, B):
+    """Algorithmic FP64 flops of the contraction stages for B vectors:
+    Hankel operator 2*n_ell*nk^2 per evaluation, metal matrices 2*Nm^2 each, distortion
+    matrix 2*Nmask*Nm (masked rows), chi2 2*Nmask^2."""
+    out = {'hankel_gemm': 0.0, 'metal_gemm': 0.0, 'dm_gemm': 0.0, 'chi2_gemm': 0.0}
+    nk, n_ell = 814, 4
+    for info in engine.infos:
+        item, data = info['item'], info['data']
+        nm = item.model_coordinates.r_grid.size
+        nmask = int(data.model_mask.sum())
+        n_eval = len(info['evals'])
+        n_metal = sum(m is not None for m in info['metal_mats'])
+        out['hankel_gemm'] += 2.0 * n_ell * nk * nk * n_eval * B
+        out['metal_gemm'] += 2.0 * nm * nm * n_metal * B
+        if not data.distortion_is_identity:
+            out['dm_gemm'] += 2.0 * nmask * nm * B
+        if not data.cov_is_identity:
+            out['chi2_gemm'] += 2.0 * nmask * nmask * B
+    return out
+
+
+def fp64_peaks(lib, torch):
+    """Measured FP64 denominators (MEASURED_PEAKS.json carries only HBM and bf16):
+    cuBLAS DGEMM 8192^3 (tensor/DMMA) and an FMA-chain probe (vector pipe)."""
+    a = torch.randn(8192, 8192, dtype=torch.float64, device='cuda')
+    b = torch.randn(8192, 8192, dtype=torch.float64, device='cuda')
+    best = 1e9
+    for it in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        if it:
+            best = min(best, e0.elapsed_time(e1))
+    dgemm = 2 * 8192.0**3 / (best * 1e-3) / 1e12
+    del a, b
+    tf = C.c_double()
+    scratch = torch.zeros(148 * 8 * 256, dtype=torch.float64, device='cuda')
+    lib.vg_probe_dfma(148 * 8, 20000, C.c_void_p(scratch.data_ptr()), C.byref(tf), None)
+    return dgemm, tf.value
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    vega = build_state()
+    from vega_b200 import synthetic
+    theta = synthetic.draw_theta(vega, args.batch)
+    base, dt = cpu_baseline(vega, theta, per_core=1, steps=args.steps, warmup=max(args.warmup, 1))
+    line = {'impl': 'reference', 'metric': 'chi2 evals/sec', 'value': base['value'], 'unit': 'evals/s',
+            'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt * 1e3,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
+            'data': 'synthetic', 'config': {'workload': WORKLOAD, 'batch_per_gpu': args.batch},
+            'cpu_baseline': base,
+            'e2e': {'value': base['value'], 'unit': 'evals/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'note': 'the reference is pure Python with no compiled sources; its path is timed through the '
+                    'numpy oracle (oracle/vega_oracle.py), one forked replica per host core'}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=10)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--batch', type=int, default=1024, help='parameter vectors per GPU per step')
+    ap.add_argument('--impl', default='b200')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local_rank = int(os.environ.get('LOCAL_RANK', 0))
+
+    if args.impl == 'reference':
+        run_reference_arm(args, rank, world)
+        return
+
+    from vega_b200 import synthetic, _lib
+    vega = build_state()
+    B = args.batch
+    theta = synthetic.draw_theta(vega, B, seed=20261104 + rank)
+
+    base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # before CUDA is initialised in this process: the replicas are forked
+        base, _ = cpu_baseline(vega, theta, per_core=2)
+
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+    lib = _lib.load()
+
+    synthetic.draw_mock_data(vega, vega.compute_model())
+    engine = vega._engine_for()
+    tt = engine.theta_tensor(theta)
+    chi2_t = torch.empty(B, dtype=torch.float64, device='cuda')
+    status_t = torch.empty(B, dtype=torch.int32, device='cuda')
+    gathered = torch.empty(world * B, dtype=torch.float64, device='cuda') if world > 1 else None
+
+    def step_device():
+        engine.chi2_device(tt, chi2_t, status_t)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, chi2_t)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    dgemm_peak, dfma_peak = fp64_peaks(lib, torch) if rank == 0 else (None, None)
+    barrier()
+
+    # ---- timed region 1: device-resident, per-stage events on ----
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    lib.vg_profile_enable(engine.handle, 1)
+    lib.vg_launch_count(1)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step_device()
+    e1.record()
+    barrier()
+    launches = lib.vg_launch_count(0)
+    elapsed = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
+    ms_stage = (C.c_double * 8)()
+    cnt_stage = (C.c_int64 * 8)()
+    lib.vg_profile_read(engine.handle, ms_stage, cnt_stage)
+    lib.vg_profile_enable(engine.handle, 0)
+    clock_info = clocks.stop() if rank == 0 else None
+    ms_per_step = float(elapsed.item()) / args.steps
+
+    # ---- timed region 2: end to end through the public API with host buffers ----
+    for _ in range(2):
+        vega.chi2_batch(theta)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        c_host = vega.chi2_batch(theta)
+    torch.cuda.synchronize()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device='cuda')
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_s.item()) * 1e3 / args.steps
+
+    if rank == 0:
+        flops = gemm_flops(engine, B)
+        stage_ms = {s: ms_stage[i] / args.steps for i, s in enumerate(STAGES)}
+        gemm_ms = sum(stage_ms[s] for s in flops)
+        achieved = sum(flops.values()) / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+        n_eval = sum(engine.n_eval)
+        grid_bytes = 6512000.0 * n_eval * B
+        kernels = {s: {'ms_per_step': stage_ms[s], 'launch_groups_per_step': cnt_stage[i] / args.steps}
+                   for i, s in enumerate(STAGES)}
+        for s in flops:
+            if stage_ms[s] > 0:
+                kernels[s]['tflops'] = flops[s] / (stage_ms[s] * 1e-3) / 1e12
+        if stage_ms['pk_ell'] > 0:
+            kernels['pk_ell']['grid_points_per_s'] = 814000.0 * n_eval * B / (stage_ms['pk_ell'] * 1e-3)
+            kernels['pk_ell']['equivalent_grid_GBps'] = grid_bytes / (stage_ms['pk_ell'] * 1e-3) / 1e9
+        line = {
+            'metric': 'chi2 evals/sec', 'value': world * B / (ms_per_step * 1e-3), 'unit': 'evals/s',
+            'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms_per_step,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
+            'data': 'synthetic',
+            'config': {'workload': WORKLOAD, 'batch_per_gpu': B, 'n_theta': len(engine.sampled),
+                       'evaluations_per_chi2': n_eval,
+                       'l2': 'inputs larger than L2: ~1.6 GB of static operands + ~2 GB of workspace '
+                             'streamed per step'},
+            'clocks': clock_info,
+            'e2e': {'value': world * B / (e2e_ms * 1e-3), 'unit': 'evals/s', 'ms_per_step': e2e_ms,
+                    'h2d_bytes_per_step': int(theta.nbytes), 'd2h_bytes_per_step': int(B * 12),
+                    'chi2_checksum': float(np.sum(c_host[c_host < 1e99]))},
+            'gpu_launches': int(launches),
+            'roofline': {'bound': 'tensor', 'kernel': 'dgemm_tn_kernel (DMMA FP64: Hankel, metal, distortion, C^-1)',
+                         'achieved': achieved, 'peak': dgemm_peak, 'unit': 'TFLOP/s',
+                         'frac': achieved / dgemm_peak if dgemm_peak else None, 'traffic': None,
+                         'peak_source': 'cuBLAS FP64 8192^3 measured live in this run (MEASURED_PEAKS.json has no '
+                                        'FP64 figure); algorithmic flops per SURVEY.md 8d',
+                         'share_of_step': gemm_ms / ms_per_step},
+            'roofline_pk_ell': {'bound': 'fp64 alu', 'dfma_probe_tflops': dfma_peak,
+                                'share_of_step': stage_ms['pk_ell'] / ms_per_step},
+            'kernels': kernels,
+            'cpu_baseline': base,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

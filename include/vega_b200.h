@@ -220,6 +220,10 @@ int vg_profile_read(vg_plan* plan, double* ms_per_tag, int64_t* count_per_tag);
 /* Number of kernels launched by the library since the last call (bench bookkeeping) */
 int64_t vg_launch_count(int reset);
 
+/* FP64 FMA throughput probe (8 independent chains per thread): the measured ALU roofline
+ * the fused P(k,mu) kernel is graded against.  out_dev: blocks*256 doubles of scratch. */
+int vg_probe_dfma(int blocks, int iters, double* out_dev, double* tflops, void* stream);
+
 /* Stand-alone FP64 tensor-core GEMM C[m,n] = alpha sum_k A[m,k] B[n,k] + beta C (tests) */
 int vg_dgemm_tn(const double* A, const double* B, double* C, int M, int N, int K,
                 long long lda, long long ldb, long long ldc, double alpha, double beta,

@@ -101,6 +101,7 @@ _SIGNATURES = {
     'vg_chi2_batch_host': (C.c_int, [_PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_stage_batch': (C.c_int, [_PTR, i32, i32, i32, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_stage_size': (C.c_int64, [_PTR, i32, i32]),
+    'vg_probe_dfma': (C.c_int, [C.c_int, C.c_int, _PTR, C.POINTER(f64), _PTR]),
     'vg_dgemm_tn': (C.c_int, [_PTR, _PTR, _PTR, C.c_int, C.c_int, C.c_int, C.c_longlong,
                               C.c_longlong, C.c_longlong, f64, f64, C.c_int, _PTR, _PTR]),
 }

@@ -95,8 +95,9 @@ struct Corr {
   int hankel_id = 0, n_model = 0, n_dist = 0, ld_model = 0, ld_dist = 0;
   std::vector<vg_eval_desc> evals;
   DevBuf d_evals;
-  std::vector<int> mode_ids[3];   // evaluations grouped by pk_ell kernel mode
-  DevBuf d_mode_ids[3];
+  // evaluations grouped by pk_ell kernel class: 0..9 fast (MODE*5 + KIND), 10..12 generic (10 + MODE)
+  std::vector<int> mode_ids[13];
+  DevBuf d_mode_ids[13];
   std::vector<DevBuf> coords;
   std::vector<double> opz_eff2;
   DevBuf d_coord_ptrs, d_opz_eff2;
@@ -443,10 +444,20 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
     VG_TRY(upload(c.d_evals, c.evals.data(), c.evals.size()));
     for (auto& ids : c.mode_ids) ids.clear();
     for (size_t e = 0; e < c.evals.size(); ++e) {
-      const uint32_t m = c.evals[e].dyn_mask;
-      c.mode_ids[m == 0 ? vg::PK_MODE_STATIC : (m == VG_F_VELO ? vg::PK_MODE_VELO : vg::PK_MODE_GENERIC)].push_back((int)e);
+      const vg_eval_desc& d = c.evals[e];
+      const uint32_t m = d.dyn_mask;
+      const int mode = m == 0 ? vg::PK_MODE_STATIC : (m == VG_F_VELO ? vg::PK_MODE_VELO : vg::PK_MODE_GENERIC);
+      const bool hcd = d.hcd_model && (d.hcd_on[0] || d.hcd_on[1]);
+      int kind = -1;
+      if (!hcd) kind = d.same_tracer ? 0 : 1;
+      else if (d.hcd_grid >= 0) {
+        if (d.same_tracer) kind = d.fast_metals ? -1 : 2;
+        else if (d.hcd_on[0] != d.hcd_on[1]) kind = d.fast_metals ? 4 : 3;
+      }
+      const bool fast = mode != vg::PK_MODE_GENERIC && kind >= 0 && plan->n_ell == vg::PK_MAX_ELL;
+      c.mode_ids[fast ? mode * 5 + kind : 10 + mode].push_back((int)e);
     }
-    for (int m = 0; m < 3; ++m)
+    for (int m = 0; m < 13; ++m)
       if (!c.mode_ids[m].empty()) VG_TRY(upload(c.d_mode_ids[m], c.mode_ids[m].data(), c.mode_ids[m].size()));
     std::vector<const double*> cptrs;
     for (auto& b : c.coords) cptrs.push_back(b.as<double>());
@@ -644,23 +655,38 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     const int NB = Bc >= 2 ? 2 : 1;
     const int groups = vg_cdiv(Bc, NB);
     const int EG = groups >= 4 ? 4 : (groups >= 2 ? 2 : 1);
-    dim3 block(vg::PK_KLANES, vg::PK_GROUPS / EG, EG);
-    for (int m = 0; m < 3; ++m) {
+    const int MG = vg::PK_GROUPS / EG;
+    dim3 block(vg::PK_KLANES, MG, EG);
+    const bool fast_ok = NB == 2 && plan->nmu % (MG * vg::PK_FAST_U) == 0;
+    for (int m = 0; m < 13; ++m) {
       if (c.mode_ids[m].empty()) continue;
       dim3 grid(vg_cdiv(Bc, NB * EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)c.mode_ids[m].size());
       const int* ids = c.d_mode_ids[m].as<int>();
-#define VG_PK_LAUNCH(NBV, MODEV) \
+#define VG_PK_FAST(MODEV, KINDV) \
+      vg::pk_ell_fast_kernel<2, MODEV, KINDV><<<grid, block, 0, st>>>(g, ev, E, ids, pf, plan->npf, (int)Bc, out)
+#define VG_PK_GEN(NBV, MODEV) \
       vg::pk_ell_kernel<NBV, MODEV><<<grid, block, 0, st>>>(g, ev, E, ids, pf, plan->npf, (int)Bc, out, status_dev)
-      if (NB == 2) {
-        if (m == 0) VG_PK_LAUNCH(2, vg::PK_MODE_STATIC);
-        else if (m == 1) VG_PK_LAUNCH(2, vg::PK_MODE_VELO);
-        else VG_PK_LAUNCH(2, vg::PK_MODE_GENERIC);
+      if (m < 10 && fast_ok) {
+        switch (m) {
+          case 0: VG_PK_FAST(0, 0); break; case 1: VG_PK_FAST(0, 1); break; case 2: VG_PK_FAST(0, 2); break;
+          case 3: VG_PK_FAST(0, 3); break; case 4: VG_PK_FAST(0, 4); break; case 5: VG_PK_FAST(1, 0); break;
+          case 6: VG_PK_FAST(1, 1); break; case 7: VG_PK_FAST(1, 2); break; case 8: VG_PK_FAST(1, 3); break;
+          default: VG_PK_FAST(1, 4); break;
+        }
       } else {
-        if (m == 0) VG_PK_LAUNCH(1, vg::PK_MODE_STATIC);
-        else if (m == 1) VG_PK_LAUNCH(1, vg::PK_MODE_VELO);
-        else VG_PK_LAUNCH(1, vg::PK_MODE_GENERIC);
+        const int mode = m < 10 ? m / 5 : m - 10;
+        if (NB == 2) {
+          if (mode == 0) VG_PK_GEN(2, vg::PK_MODE_STATIC);
+          else if (mode == 1) VG_PK_GEN(2, vg::PK_MODE_VELO);
+          else VG_PK_GEN(2, vg::PK_MODE_GENERIC);
+        } else {
+          if (mode == 0) VG_PK_GEN(1, vg::PK_MODE_STATIC);
+          else if (mode == 1) VG_PK_GEN(1, vg::PK_MODE_VELO);
+          else VG_PK_GEN(1, vg::PK_MODE_GENERIC);
+        }
       }
-#undef VG_PK_LAUNCH
+#undef VG_PK_FAST
+#undef VG_PK_GEN
       VG_LAUNCHED();
     }
   }
@@ -1012,3 +1038,43 @@ int vg_dgemm_tn(const double* A, const double* B, double* C, int M, int N, int K
 }
 
 }  // extern "C"
+
+// ---- FP64 FMA peak probe (roofline denominator of the ALU-bound fused P(k,mu) kernel) ----
+namespace {
+__global__ void __launch_bounds__(256) dfma_probe_kernel(double* out, int iters, double seed) {
+  double a[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a[j] = seed + j + threadIdx.x * 1e-3;
+  const double x = 1.0000001, y = 1e-9;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = fma(a[j], x, y);
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s += a[j];
+  if (s == 12345.678) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+}  // namespace
+
+extern "C" int vg_probe_dfma(int blocks, int iters, double* out_dev, double* tflops, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaEvent_t e0, e1;
+  VG_CUDA_CHECK(cudaEventCreate(&e0));
+  VG_CUDA_CHECK(cudaEventCreate(&e1));
+  dfma_probe_kernel<<<blocks, 256, 0, st>>>(out_dev, iters, 1.0);   // warm-up
+  float best = 1e30f;
+  for (int rep = 0; rep < 5; ++rep) {
+    VG_CUDA_CHECK(cudaEventRecord(e0, st));
+    dfma_probe_kernel<<<blocks, 256, 0, st>>>(out_dev, iters, 1.0 + rep);
+    VG_CUDA_CHECK(cudaEventRecord(e1, st));
+    VG_CUDA_CHECK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    VG_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    best = std::min(best, ms);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *tflops = 2.0 * 8.0 * (double)iters * 256.0 * blocks / (best * 1e-3) / 1e12;
+  return VG_OK;
+}

@@ -364,6 +364,130 @@ pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
     if (bad[e] && b0 + e < B) atomicOr(status + b0 + e, bad[e]);
 }
 
+// ---- fast path of the fused kernel ------------------------------------------------------
+// Same mapping as pk_ell_kernel, but every option that the generic kernel tests per grid
+// point is a template parameter, the mu loop has an exact trip count (nmu % (MG*5) == 0) and
+// all table reads of a 5-row batch are issued before the arithmetic.  KIND:
+//   0 no HCD, same tracer      t^2            1 no HCD, two tracers      tA * tB
+//   2 HCD grid, same tracer    tH^2           3 HCD grid on one tracer   tH * tP
+//   4 as 3 with the Kaiser term of the HCD tracer divided by its effective bias
+//     (fast_metals, power_spectrum.py:219-220 with the effective bias of :305-307)
+constexpr int PK_FAST_U = 5;
+
+template <int NB, int MODE, int KIND>
+__global__ void __launch_bounds__(PK_KLANES * PK_GROUPS, 2)
+pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
+                   const int* __restrict__ eval_ids, const double* __restrict__ pfull, int npf, int B,
+                   double* __restrict__ out) {
+  __shared__ vg_eval_desc d;
+  __shared__ double red[PK_GROUPS][NB * PK_MAX_ELL][PK_KLANES + 1];
+  const int tx = threadIdx.x, mg = threadIdx.y, eg = threadIdx.z;
+  const int MG = blockDim.y, EG = blockDim.z;
+  const int tid = (eg * MG + mg) * PK_KLANES + tx;
+  const int eval = eval_ids[blockIdx.z];
+  {
+    const int* src = reinterpret_cast<const int*>(evals + eval);
+    int* dst = reinterpret_cast<int*>(&d);
+    for (int i = tid; i < (int)(sizeof(vg_eval_desc) / 4); i += PK_KLANES * PK_GROUPS) dst[i] = src[i];
+  }
+  __syncthreads();
+  const int ik_raw = blockIdx.y * PK_KLANES + tx;
+  const int ik = min(ik_raw, g.nk - 1);
+  const double k = g.k[ik];
+  const int b0 = (blockIdx.x * EG + eg) * NB;
+  constexpr bool HCD = KIND >= 2;
+  constexpr bool TWO = KIND == 1 || KIND >= 3;
+  const int tH = (KIND >= 3 && !d.hcd_on[0]) ? 1 : 0;   // tracer carrying the HCD term
+  const int tP = 1 - tH;
+
+  double aH0[NB], aH1[NB], hH0[NB], hH1[NB], aP0[NB], aP1[NB], sv0[NB], sv1[NB];
+#pragma unroll
+  for (int e = 0; e < NB; ++e) {
+    const double* p = pfull + (long long)min(b0 + e, B - 1) * npf;
+    const KaiserCoef kc = kaiser_setup(d, p, k);
+    aH0[e] = kc.a0[tH]; aH1[e] = kc.a1[tH]; hH0[e] = kc.h0[tH]; hH1[e] = kc.h1[tH];
+    aP0[e] = kc.a0[tP]; aP1[e] = kc.a1[tP];
+    sv0[e] = (MODE == PK_MODE_VELO && d.idx_velo[0] >= 0) ? k * p[d.idx_velo[0]] : 0.0;
+    sv1[e] = (MODE == PK_MODE_VELO && d.idx_velo[1] >= 0) ? k * p[d.idx_velo[1]] : 0.0;
+  }
+  const bool velo0 = MODE == PK_MODE_VELO && d.idx_velo[0] >= 0;
+  const bool velo1 = MODE == PK_MODE_VELO && d.idx_velo[1] >= 0;
+  const bool velo_gauss = d.velo_kind == 1;
+  const long long row = (long long)MG * g.nk;
+  const double* S = d.static_grid >= 0 ? g.grids[d.static_grid] + (long long)mg * g.nk + ik : nullptr;
+  const double* Fg = HCD ? g.grids[d.hcd_grid] + (long long)mg * g.nk + ik : nullptr;
+  const double* mup = g.mu + mg;
+  const double* wp = g.wleg + mg;
+  const int nmu = g.nmu;
+
+  double acc[NB][PK_MAX_ELL];
+#pragma unroll
+  for (int e = 0; e < NB; ++e)
+#pragma unroll
+    for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = 0.0;
+
+  const int n_batches = nmu / (MG * PK_FAST_U);
+  for (int jb = 0; jb < n_batches; ++jb) {
+    double s[PK_FAST_U], f[PK_FAST_U], mu[PK_FAST_U];
+#pragma unroll
+    for (int u = 0; u < PK_FAST_U; ++u) {   // the L2-latency loads of the whole batch first
+      s[u] = S ? __ldg(S + u * row) : 1.0;
+      f[u] = HCD ? __ldg(Fg + u * row) : 0.0;
+      mu[u] = __ldg(mup + u * MG);
+    }
+    if (S) S += PK_FAST_U * row;
+    if (HCD) Fg += PK_FAST_U * row;
+    mup += PK_FAST_U * MG;
+#pragma unroll
+    for (int u = 0; u < PK_FAST_U; ++u) {
+      const double mu2 = mu[u] * mu[u];
+      double w[PK_MAX_ELL];                   // warp-uniform, L1-resident
+#pragma unroll
+      for (int l = 0; l < PK_MAX_ELL; ++l) w[l] = __ldg(wp + l * nmu + u * MG);
+#pragma unroll
+      for (int e = 0; e < NB; ++e) {
+        double t;
+        if (HCD) {
+          const double tb = fma(hH0[e], f[u], aH0[e]);
+          t = fma(fma(hH1[e], f[u], aH1[e]), mu2, tb);
+          if (KIND == 4) t /= tb;
+        } else {
+          t = fma(aH1[e], mu2, aH0[e]);
+        }
+        double P = TWO ? t * fma(aP1[e], mu2, aP0[e]) : t * t;
+        P *= s[u];
+        if (MODE == PK_MODE_VELO) {
+          if (velo0) { const double x = sv0[e] * mu[u]; P *= velo_gauss ? exp(-0.25 * x * x) : rsqrt(fma(x, x, 1.0)); }
+          if (velo1) { const double x = sv1[e] * mu[u]; P *= velo_gauss ? exp(-0.25 * x * x) : rsqrt(fma(x, x, 1.0)); }
+        }
+#pragma unroll
+        for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = fma(w[l], P, acc[e][l]);
+      }
+    }
+    wp += PK_FAST_U * MG;
+  }
+  for (int turn = 0; turn < EG; ++turn) {
+    __syncthreads();
+    if (eg == turn) {
+#pragma unroll
+      for (int e = 0; e < NB; ++e)
+#pragma unroll
+        for (int l = 0; l < PK_MAX_ELL; ++l) red[mg][e * PK_MAX_ELL + l][tx] = acc[e][l];
+    }
+    __syncthreads();
+    if (eg == turn) {
+      const double pk_lin = g.pk_lin[d.pk_lin_sel][ik];
+      for (int o = mg; o < NB * PK_MAX_ELL; o += MG) {
+        const int e = o / PK_MAX_ELL, l = o % PK_MAX_ELL;
+        if (b0 + e >= B || l >= g.n_ell || ik_raw >= g.nk) continue;
+        double sum = 0.0;
+        for (int m = 0; m < MG; ++m) sum += red[m][o][tx];
+        out[(((long long)(b0 + e) * n_eval + eval) * g.n_ell + l) * g.nk_pad + ik] = sum * pk_lin;
+      }
+    }
+  }
+}
+
 // Materialising K1 (HBM-write bound): P(k,mu) of ONE evaluation for every vector of the
 // batch, out[b][nmu][nk].  grid = (ceil(nk/128), nmu, B), block = 128.
 __global__ void __launch_bounds__(128)
