@@ -1,0 +1,91 @@
+"""Host-side plan logic (no GPU): descriptor flags / parameter columns produced from the
+reference's ini options, the (ap, at) rule selection, static-vs-sampled factor split."""
+import configparser
+
+import pytest
+
+from vega_b200 import VegaInterface, _lib
+from vega_b200.plan import PlanBuilder, resolve_scale
+
+
+def builder(main, sampled=None):
+    vega = VegaInterface(main)
+    return vega, PlanBuilder(vega, sampled=sampled)
+
+
+def test_full_config_descriptors():
+    vega, pb = builder('configs/full_configs/main.ini')
+    info = pb.describe_corr('lyalya_lyalya')
+    assert len(info['evals']) == 2 + 15
+    peak, smooth = info['evals'][:2]
+    assert peak.is_peak == 1 and peak.pk_lin_sel == 0 and peak.out_slot == 0
+    assert smooth.is_peak == 0 and smooth.pk_lin_sel == 1 and smooth.out_slot == 1
+    # bias_eta_LYA and beta_LYA are sampled: Kaiser is per vector, every other factor static
+    assert peak.dyn_mask == 0
+    assert peak.static_mask == _lib.F_ARINYO | _lib.F_GK | _lib.F_PEAKNL | _lib.F_FSGAUSS
+    assert smooth.static_mask == _lib.F_ARINYO | _lib.F_GK | _lib.F_FSGAUSS
+    assert peak.hcd_model == 1 and peak.hcd_grid >= 0 and peak.uvb == 1
+    assert peak.scale_form == 1 and smooth.scale_form == 0      # BAO fit: only the peak is rescaled
+    assert peak.idx_scale[0] == pb.col('ap') and peak.idx_scale[1] == pb.col('at')
+    # metals: no HCD (their PowerSpectrum is built from the [metals] section), bias weights
+    metal = info['evals'][2]
+    assert metal.hcd_model == 0 and metal.fast_metals == 1 and metal.weight_bias == 1
+    assert metal.scale_form == 0 and metal.pk_lin_sel == 2
+    mixed = [d for d, pair in zip(info['evals'][2:], info['item'].metal_correlations) if pair[0] != pair[1]]
+    assert all(d.weight_const == 2.0 for d in mixed)            # vega/metals.py:238-239
+
+
+def test_sampled_parameter_makes_factor_dynamic():
+    vega, pb = builder('configs/full_configs/main.ini',
+                       sampled=['sigma_velo_disp_lorentz_QSO', 'L0_hcd', 'par_sigma_smooth'])
+    info = pb.describe_corr('lyalya_qso')
+    peak = info['evals'][0]
+    assert peak.dyn_mask & _lib.F_VELO and peak.dyn_mask & _lib.F_FSGAUSS
+    assert peak.hcd_grid == -1                                   # L0 sampled: F evaluated per vector
+    assert peak.idx_drp == pb.col('drp_QSO')
+    assert peak.radiation == 1
+
+
+def test_cross_config_options():
+    vega, pb = builder('configs/picca_bench/main_cross.ini')
+    d7 = pb.describe_corr('test_7')['evals'][0]
+    assert d7.rel == 1 and d7.asy == 1 and d7.radiation == 1 and d7.velo_kind == 2
+    d = {n: pb.describe_corr(n)['evals'][0] for n in vega.corr_items}
+    assert any(x.zevol_kind[0] == 1 for x in d.values())        # a Croom QSO evolution config exists
+    assert pb.describe_corr('test_7')['legacy'] is True
+
+
+def scale_cfg(**kw):
+    cfg = configparser.ConfigParser()
+    cfg.optionxform = lambda o: o
+    cfg['cosmo-fit type'] = {k.replace('_', '-') if k != 'cosmo_fit_func' else 'cosmo fit func': str(v)
+                             for k, v in kw.items()}
+    return cfg['cosmo-fit type']
+
+
+def test_resolve_scale_rules():
+    """vega/scale_parameters.py:38-230"""
+    cfg = scale_cfg(cosmo_fit_func='ap_at')
+    assert resolve_scale(cfg, {}, True, 'LYAxLYA', False) == (1, 'ap', 'at')
+    assert resolve_scale(cfg, {}, False, 'LYAxLYA', False) == (0, None, None)
+    assert resolve_scale(cfg, {}, True, 'LYAxSiII', True) == (0, None, None)
+    cfg = scale_cfg(cosmo_fit_func='phi_alpha', smooth_scaling=True)
+    assert resolve_scale(cfg, {}, True, 'x', False) == (3, 'phi', 'alpha')
+    assert resolve_scale(cfg, {}, False, 'x', False) == (3, 'phi_smooth', 'alpha_smooth')
+    cfg = scale_cfg(cosmo_fit_func='phi_alpha', full_shape=True)
+    assert resolve_scale(cfg, {}, False, 'x', False) == (3, 'phi_full', 'alpha_smooth')
+    assert resolve_scale(cfg, {}, True, 'x', False) == (3, 'phi_full', 'alpha')
+    cfg = scale_cfg(cosmo_fit_func='phi_alpha', smooth_scaling=True, two_alpha_smooth=True)
+    assert resolve_scale(cfg, {}, False, 'LYAxQSO', False) == (3, 'phi_smooth', 'alpha_smooth_LYAxQSO')
+    cfg = scale_cfg(cosmo_fit_func='ap_at', full_shape=True)
+    with pytest.raises(ValueError):
+        resolve_scale(cfg, {}, False, 'x', False)
+    cfg = scale_cfg(cosmo_fit_func='aiso_epsilon', full_shape=True, full_shape_alpha=True)
+    assert resolve_scale(cfg, {}, False, 'x', False) == (2, 'aiso_full', 'epsilon_full')
+
+
+def test_unsupported_options_fail_loudly():
+    vega, pb = builder('configs/full_configs/main.ini')
+    vega.corr_items['lyalya_lyalya'].config['model']['fast_metals'] = 'True'
+    with pytest.raises(NotImplementedError):
+        pb.describe_corr('lyalya_lyalya')
