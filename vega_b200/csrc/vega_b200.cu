@@ -548,6 +548,24 @@ namespace {
 
 constexpr int NUM_SMS = 148;
 
+// split-K so that the CTA count fills whole waves of the 148 SMs (1 CTA/SM): the split count
+// with the best wave efficiency, keeping >= 16 K-tiles per split
+int pick_splits(long long tiles, int ktiles) {
+  int splits = 1;
+  if (tiles < 8 * NUM_SMS) {
+    double best = 0.0;
+    const int max_splits = (int)std::min<long long>(32, std::max(1, ktiles / 16));
+    for (int sp = 1; sp <= max_splits; ++sp) {
+      const long long ctas = tiles * sp;
+      const long long waves = (ctas + NUM_SMS - 1) / NUM_SMS;
+      double eff = (double)ctas / (double)(waves * NUM_SMS);
+      eff -= 0.004 * (sp - 1);            // the partial-sum write/read of each extra split
+      if (eff > best + 1e-9) { best = eff; splits = sp; }
+    }
+  }
+  return splits;
+}
+
 // C[M][ldc] = A[M][K] * B[N][K]^T with an automatic deterministic split-K when the tile
 // count is too small to fill the 148 SMs.
 int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, long long ldb,
@@ -559,8 +577,7 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
   g.alpha = 1.0; g.beta = 0.0;
   const long long tiles = (long long)vg_cdiv(M, vg::GEMM_BM) * vg_cdiv(N, vg::GEMM_BN) * batch;
   const int ktiles = K / vg::GEMM_BK;
-  int splits = 1;
-  if (tiles < 3 * NUM_SMS) splits = (int)std::min<long long>(std::max(1, ktiles / 8), (4 * NUM_SMS + tiles - 1) / tiles);
+  const int splits = pick_splits(tiles, ktiles);
   g.splits = std::max(1, splits);
   if (g.splits == 1) {
     g.C = C;
@@ -816,8 +833,10 @@ int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* in
   }
   vg::GemmArgs g{};
   g.A = diff; g.B = invcov; g.M = (int)Bc; g.N = n; g.K = ld; g.lda = ld; g.ldb = ld;
-  g.batch = 1; g.splits = 1; g.alpha = 1.0; g.beta = 0.0;
-  const int n_tiles = vg_cdiv(n, vg::GEMM_BN);
+  g.batch = 1; g.alpha = 1.0; g.beta = 0.0;
+  const int n_tiles0 = vg_cdiv(n, vg::GEMM_BN);
+  g.splits = pick_splits((long long)vg_cdiv(Bc, vg::GEMM_BM) * n_tiles0, ld / vg::GEMM_BK);
+  const int n_tiles = n_tiles0 * g.splits;
   VG_TRY(plan->w_partial.ensure((size_t)Bc * n_tiles * 8));
   g.C = plan->w_partial.as<double>(); g.ldc = n_tiles;
   g.D = diff; g.ldd = ld;

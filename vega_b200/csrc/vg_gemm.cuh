@@ -34,7 +34,7 @@ struct GemmArgs {
   int batch, splits;           // grid.z = batch*splits; split s covers K range s*Kper..
   long long split_stride;      // C offset per split (doubles)
   double alpha, beta;
-  // ROWDOT: out[m, blockIdx.y] = sum_n acc[m,n] * D[m,n]   (C = out, ldc = n_tiles)
+  // ROWDOT: out[m, blockIdx.y*splits + split] = sum_n acc[m,n] * D[m,n]   (C = out, ldc = n_tiles*splits)
   const double* D; long long ldd;
 };
 
@@ -175,7 +175,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_tn_kernel(GemmArgs g) {
       int m = m0 + tid;
       if (m < g.M) {
         double s = (red[tid * 4 + 0] + red[tid * 4 + 1]) + (red[tid * 4 + 2] + red[tid * 4 + 3]);
-        g.C[(long long)bz * g.strideC + (long long)m * g.ldc + blockIdx.y] = g.alpha * s;
+        // linear in the K range: each split contributes its own partial column
+        g.C[(long long)bz * g.strideC + (long long)m * g.ldc + blockIdx.y * g.splits + sp] = g.alpha * s;
       }
     }
   }
