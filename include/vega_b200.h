@@ -186,6 +186,16 @@ int vg_plan_set_global_invcov(vg_plan* plan, int32_t n_total, const double* invc
 int vg_plan_finalize(vg_plan* plan, void* stream);
 /* Largest number of vectors processed per pass (workspace is sized for it); default 1024 */
 int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
+/* Run-time options.  VG_OPT_MOMENTS (default 1): evaluations whose sampled P(k,mu)
+ * parameters are only Kaiser / HCD amplitudes are computed in moment form -- their knot
+ * tables are a 3/9-term combination of static tables built at finalize (exact algebra: the
+ * mu projection of vega/pktoxi.py:79-97, the FFTLog and the spline are linear); 0 sends every
+ * evaluation through the per-point P(k,mu) pass. */
+#define VG_OPT_MOMENTS 0
+int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
+/* Number of evaluations of a correlation served by the moment form (after finalize; 0 when
+ * the option is off) -- the remaining ones go through pk_ell + the Hankel GEMM */
+int vg_corr_n_moment(const vg_plan* plan, int32_t corr);
 /* Status bits raised while building the static grids (e.g. VG_STATUS_ARINYO): they apply
  * to every vector */
 int vg_plan_static_status(const vg_plan* plan);
@@ -213,7 +223,7 @@ int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
 int64_t vg_stage_size(const vg_plan* plan, int32_t corr, int32_t stage);
 /* Per-stage device timing with CUDA events on the launch stream (bench.py roofline figures).
  * Tags: 0 P(k,mu)->multipoles, 1 Hankel GEMM, 2 xi gather, 3 metal GEMM, 4 distortion GEMM,
- * 5 C^-1 GEMM, 6 elementwise stages.  vg_profile_read synchronises the device, fills
+ * 5 C^-1 GEMM, 6 elementwise stages, 7 moment-form knot tables.  vg_profile_read synchronises the device, fills
  * ms_per_tag[8] / count_per_tag[8] with the totals since the last read and resets them. */
 int vg_profile_enable(vg_plan* plan, int enable);
 int vg_profile_read(vg_plan* plan, double* ms_per_tag, int64_t* count_per_tag);

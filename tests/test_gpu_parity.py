@@ -111,3 +111,27 @@ def test_dgemm_against_torch():
         torch.cuda.synchronize()
         ref = A @ B.T
         assert (Cm[:, :N] - ref).abs().max() <= 1e-12 * ref.abs().max()
+
+
+def test_moment_form_matches_per_point_pass():
+    """csrc/vg_moments.cuh: knot tables as a 3/9-term combination of static tables must equal
+    the per-point P(k,mu) pass + Hankel GEMM (exact algebra, only the summation order
+    differs) -- and both must match the oracle."""
+    from vega_b200 import _lib
+    vega, oracle, theta = make_c2(4, width=1.0)
+    names = list(vega.sample_params['limits'])
+    engine = vega._engine_for()
+    assert sum(engine.n_moment(ci) for ci in range(len(engine.infos))) > 0
+    chi2_mom = vega.chi2_batch(theta)
+    models_mom, _ = vega.compute_model_batch(theta)
+    engine.set_option(_lib.OPT_MOMENTS, 0)
+    assert sum(engine.n_moment(ci) for ci in range(len(engine.infos))) == 0
+    chi2_full = vega.chi2_batch(theta)
+    models_full, _ = vega.compute_model_batch(theta)
+    engine.set_option(_lib.OPT_MOMENTS, 1)
+    for name in models_full:
+        scale = np.max(np.abs(models_full[name]))
+        assert np.max(np.abs(models_mom[name] - models_full[name])) <= 1e-12 * scale
+    assert np.max(np.abs(chi2_mom - chi2_full) / np.maximum(1.0, np.abs(chi2_full) / 1e4)) <= CHI2_ATOL
+    ref = oracle.compute_model(dict(zip(names, theta[0])))
+    assert_xi_close({n: models_mom[n][0] for n in ref}, ref, 'moment form')

@@ -13,6 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / 'libvega_b200.so'
 VG_MAX_BB_TERMS = 8
 F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP = (1 << i for i in range(8))
 STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE = 1, 2, 4
+OPT_MOMENTS = 0
 
 i32, u32, f64 = C.c_int32, C.c_uint32, C.c_double
 
@@ -77,6 +78,8 @@ _SIGNATURES = {
                                  _PTR, i32, C.POINTER(_PTR)]),
     'vg_plan_destroy': (C.c_int, [_PTR]),
     'vg_plan_set_chunk': (C.c_int, [_PTR, C.c_int64]),
+    'vg_plan_set_option': (C.c_int, [_PTR, i32, i32]),
+    'vg_corr_n_moment': (C.c_int, [_PTR, i32]),
     'vg_plan_set_fvoigt': (C.c_int, [_PTR, i32, _PTR, _PTR]),
     'vg_plan_set_uvshot_table': (C.c_int, [_PTR, i32, _PTR, _PTR]),
     'vg_plan_set_priors': (C.c_int, [_PTR, i32, _PTR, _PTR, _PTR]),

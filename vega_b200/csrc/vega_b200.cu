@@ -11,6 +11,7 @@
 #include "../../include/vega_b200.h"
 #include "vg_common.cuh"
 #include "vg_gemm.cuh"
+#include "vg_moments.cuh"
 #include "vg_pk.cuh"
 #include "vg_post.cuh"
 #include "vg_xi.cuh"
@@ -98,6 +99,15 @@ struct Corr {
   // evaluations grouped by pk_ell kernel class: 0..9 fast (MODE*5 + KIND), 10..12 generic (10 + MODE)
   std::vector<int> mode_ids[13];
   DevBuf d_mode_ids[13];
+  // the same classes without the evaluations served by the moment form (vg_moments.cuh)
+  std::vector<int> full_mode_ids[13];
+  DevBuf d_full_mode_ids[13];
+  std::vector<int> mom_ids;      // evaluations in moment form
+  int n_full = 0;                // evaluations that keep the per-point pass
+  DevBuf d_mom_ids, d_mom_ktab;  // ktab [n_mom][9][n_ell][2*n_out_pad]
+  // per evaluation: slot in the multipole buffer / encoded slot in the knot tables, for the
+  // all-evaluations layout (ident) and the split layout (full-pass evaluations compacted)
+  DevBuf d_slot_ident, d_slot_split, d_tabslot_ident, d_tabslot_split;
   std::vector<DevBuf> coords;
   std::vector<double> opz_eff2;
   DevBuf d_coord_ptrs, d_opz_eff2;
@@ -136,6 +146,7 @@ struct vg_plan {
   std::vector<DevBuf> grids;
   DevBuf d_grid_ptrs;
   bool finalized = false;
+  bool use_moments = true;
   int static_bad = 0;
   int std_ells = 0;
   // global covariance
@@ -184,7 +195,10 @@ struct ProfScope {
   }
   ~ProfScope() { if (e1) cudaEventRecord(e1, st); }
 };
-enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_NTAGS = 8 };
+int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, long long ldb,
+              double* C, long long ldc, int M, int N, int K, int batch, long long strideA,
+              long long strideB, long long strideC, cudaStream_t st);
+enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_MOMENT = 7, PROF_NTAGS = 8 };
 }  // namespace
 
 extern "C" {
@@ -242,6 +256,13 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk) {
   VG_REQUIRE(plan && chunk > 0, "bad chunk");
   plan->chunk_max = chunk;
   return VG_OK;
+}
+
+int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
+  VG_REQUIRE(plan, "null plan");
+  if (option == VG_OPT_MOMENTS) { plan->use_moments = value != 0; return VG_OK; }
+  vg_set_error("vg_plan_set_option: unknown option %d", option);
+  return VG_ERR_ARG;
 }
 
 int vg_plan_set_fvoigt(vg_plan* plan, int32_t n, const double* x, const double* f) {
@@ -443,6 +464,11 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
     VG_REQUIRE(!c.evals.empty(), "correlation without evaluations");
     VG_TRY(upload(c.d_evals, c.evals.data(), c.evals.size()));
     for (auto& ids : c.mode_ids) ids.clear();
+    for (auto& ids : c.full_mode_ids) ids.clear();
+    c.mom_ids.clear();
+    c.n_full = 0;
+    std::vector<int> slot_ident(c.evals.size()), slot_split(c.evals.size(), 0), tabslot_split(c.evals.size(), 0);
+    for (size_t e = 0; e < c.evals.size(); ++e) slot_ident[e] = (int)e;
     for (size_t e = 0; e < c.evals.size(); ++e) {
       const vg_eval_desc& d = c.evals[e];
       const uint32_t m = d.dyn_mask;
@@ -455,10 +481,26 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
         else if (d.hcd_on[0] != d.hcd_on[1]) kind = d.fast_metals ? 4 : 3;
       }
       const bool fast = mode != vg::PK_MODE_GENERIC && kind >= 0 && plan->n_ell == vg::PK_MAX_ELL;
-      c.mode_ids[fast ? mode * 5 + kind : 10 + mode].push_back((int)e);
+      const int cls = fast ? mode * 5 + kind : 10 + mode;
+      c.mode_ids[cls].push_back((int)e);
+      if (vg::moment_eligible(d)) {
+        tabslot_split[e] = -((int)c.mom_ids.size() + 1);
+        c.mom_ids.push_back((int)e);
+      } else {
+        slot_split[e] = tabslot_split[e] = c.n_full++;
+        c.full_mode_ids[cls].push_back((int)e);
+      }
     }
-    for (int m = 0; m < 13; ++m)
+    for (int m = 0; m < 13; ++m) {
       if (!c.mode_ids[m].empty()) VG_TRY(upload(c.d_mode_ids[m], c.mode_ids[m].data(), c.mode_ids[m].size()));
+      if (!c.full_mode_ids[m].empty())
+        VG_TRY(upload(c.d_full_mode_ids[m], c.full_mode_ids[m].data(), c.full_mode_ids[m].size()));
+    }
+    VG_TRY(upload(c.d_slot_ident, slot_ident.data(), slot_ident.size()));
+    VG_TRY(upload(c.d_tabslot_ident, slot_ident.data(), slot_ident.size()));
+    VG_TRY(upload(c.d_slot_split, slot_split.data(), slot_split.size()));
+    VG_TRY(upload(c.d_tabslot_split, tabslot_split.data(), tabslot_split.size()));
+    if (!c.mom_ids.empty()) VG_TRY(upload(c.d_mom_ids, c.mom_ids.data(), c.mom_ids.size()));
     std::vector<const double*> cptrs;
     for (auto& b : c.coords) cptrs.push_back(b.as<double>());
     VG_TRY(upload(c.d_coord_ptrs, cptrs.data(), cptrs.size()));
@@ -481,6 +523,23 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
         VG_LAUNCHED();
         built[d.hcd_grid] = 1;
       }
+    }
+    // moment form: static knot tables K[j][m] = (Hankel + spline operator)(pk_lin * moment m)
+    if (!c.mom_ids.empty()) {
+      const Hankel& h = *plan->hankels[c.hankel_id];
+      const int rowT = 2 * h.n_out_pad;
+      const int rows = (int)c.mom_ids.size() * vg::MOM_MAX;
+      DevBuf mom;
+      VG_TRY(mom.alloc((size_t)rows * plan->n_ell * plan->nk_pad * 8));
+      VG_TRY(c.d_mom_ktab.alloc((size_t)rows * plan->n_ell * rowT * 8));
+      dim3 mgrid(vg_cdiv(plan->nk, 128), (unsigned)c.mom_ids.size());
+      vg::moment_grid_kernel<<<mgrid, 128, 0, st>>>(g, c.d_evals.as<vg_eval_desc>(), c.d_mom_ids.as<int>(),
+                                                  mom.as<double>());
+      VG_LAUNCHED();
+      VG_TRY(gemm_auto(plan, mom.as<double>(), (long long)plan->n_ell * plan->nk_pad, h.op.as<double>(),
+                       plan->nk_pad, c.d_mom_ktab.as<double>(), (long long)plan->n_ell * rowT, rows, rowT,
+                       plan->nk_pad, plan->n_ell, plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
+      VG_CUDA_CHECK(cudaStreamSynchronize(st));   // `mom` is released at the end of this scope
     }
     // metal matrices, concatenated along K: mcat[i][c*ld_model + j] = M_c[i][j]
     if (c.metal_dense && c.n_metal > 0) {
@@ -532,7 +591,7 @@ int64_t vg_plan_device_bytes(const vg_plan* plan) {
   for (auto& h : plan->hankels) n += h->xk.bytes + h->op.bytes;
   for (auto& cp : plan->corrs) {
     const Corr& c = *cp;
-    n += c.d_mcat.bytes + c.d_dmat.bytes + c.d_dmat_masked.bytes + c.d_invcov.bytes;
+    n += c.d_mcat.bytes + c.d_dmat.bytes + c.d_dmat_masked.bytes + c.d_invcov.bytes + c.d_mom_ktab.bytes;
     for (auto& b : c.coords) n += b.bytes;
   }
   n += plan->d_global_invcov.bytes;
@@ -664,7 +723,17 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   const Hankel& h = *plan->hankels[c.hankel_id];
   const int E = (int)c.evals.size();
   vg::PkGridDev g = plan->grid_dev();
-  {  // K1 + K2a
+  // the per-stage taps (upto <= 2) expose every evaluation's multipoles / knot tables, so
+  // they run all evaluations through the per-point pass
+  const bool split = plan->use_moments && upto > 2 && !c.mom_ids.empty();
+  const int Ef = split ? c.n_full : E;
+  const int Em = split ? (int)c.mom_ids.size() : 0;
+  const int rowT = 2 * h.n_out_pad;
+  const long long row_len = (long long)plan->n_ell * rowT;
+  double* tables_full = plan->w_tables.as<double>();
+  double* tables_mom = tables_full + Bc * Ef * row_len;
+  const int* out_slot = split ? c.d_slot_split.as<int>() : c.d_slot_ident.as<int>();
+  if (Ef > 0) {  // K1 + K2a
     ProfScope prof(plan, PROF_PK, st);
     const vg_eval_desc* ev = c.d_evals.as<vg_eval_desc>();
     double* out = plan->w_pkell.as<double>();
@@ -676,13 +745,14 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     dim3 block(vg::PK_KLANES, MG, EG);
     const bool fast_ok = NB == 2 && plan->nmu % (MG * vg::PK_FAST_U) == 0;
     for (int m = 0; m < 13; ++m) {
-      if (c.mode_ids[m].empty()) continue;
-      dim3 grid(vg_cdiv(Bc, NB * EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)c.mode_ids[m].size());
-      const int* ids = c.d_mode_ids[m].as<int>();
+      const std::vector<int>& class_ids = split ? c.full_mode_ids[m] : c.mode_ids[m];
+      if (class_ids.empty()) continue;
+      dim3 grid(vg_cdiv(Bc, NB * EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)class_ids.size());
+      const int* ids = split ? c.d_full_mode_ids[m].as<int>() : c.d_mode_ids[m].as<int>();
 #define VG_PK_FAST(MODEV, KINDV) \
-      vg::pk_ell_fast_kernel<2, MODEV, KINDV><<<grid, block, 0, st>>>(g, ev, E, ids, pf, plan->npf, (int)Bc, out)
+      vg::pk_ell_fast_kernel<2, MODEV, KINDV><<<grid, block, 0, st>>>(g, ev, E, ids, out_slot, Ef, pf, plan->npf, (int)Bc, out)
 #define VG_PK_GEN(NBV, MODEV) \
-      vg::pk_ell_kernel<NBV, MODEV><<<grid, block, 0, st>>>(g, ev, E, ids, pf, plan->npf, (int)Bc, out, status_dev)
+      vg::pk_ell_kernel<NBV, MODEV><<<grid, block, 0, st>>>(g, ev, E, ids, out_slot, Ef, pf, plan->npf, (int)Bc, out, status_dev)
       if (m < 10 && fast_ok) {
         switch (m) {
           case 0: VG_PK_FAST(0, 0); break; case 1: VG_PK_FAST(0, 1); break; case 2: VG_PK_FAST(0, 2); break;
@@ -709,13 +779,19 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   }
   if (upto <= 1) return VG_OK;
   // K2b: Hankel + spline operator, one GEMM batched over the multipoles
-  const int rowT = 2 * h.n_out_pad;
-  {
-  ProfScope prof(plan, PROF_HANKEL, st);
-  VG_TRY(gemm_auto(plan, plan->w_pkell.as<double>(), (long long)plan->n_ell * plan->nk_pad,
-                   h.op.as<double>(), plan->nk_pad, plan->w_tables.as<double>(),
-                   (long long)plan->n_ell * rowT, (int)(Bc * E), rowT, plan->nk_pad, plan->n_ell,
-                   plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
+  if (Ef > 0) {
+    ProfScope prof(plan, PROF_HANKEL, st);
+    VG_TRY(gemm_auto(plan, plan->w_pkell.as<double>(), (long long)plan->n_ell * plan->nk_pad,
+                     h.op.as<double>(), plan->nk_pad, tables_full, row_len, (int)(Bc * Ef), rowT,
+                     plan->nk_pad, plan->n_ell, plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
+  }
+  if (Em > 0) {  // moment form: knot tables as a 3/9-term combination of static tables
+    ProfScope prof(plan, PROF_MOMENT, st);
+    dim3 grid(vg_cdiv(row_len, 256 * vg::MOM_XPT), (unsigned)Em, (unsigned)vg_cdiv(Bc, vg::MOM_NB));
+    vg::moment_tables_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), c.d_mom_ids.as<int>(), Em,
+                                                  plan->w_pfull.as<double>(), plan->npf, (int)Bc,
+                                                  c.d_mom_ktab.as<double>(), (int)row_len, tables_mom);
+    VG_LAUNCHED();
   }
   if (upto <= 2) return VG_OK;
   {  // K3
@@ -726,7 +802,9 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     a.h.xk = h.xk.as<double>();
     a.evals = c.d_evals.as<vg_eval_desc>(); a.n_eval = E;
     a.pfull = plan->w_pfull.as<double>(); a.npf = plan->npf; a.B = (int)Bc;
-    a.tables = plan->w_tables.as<double>();
+    a.tables = tables_full; a.n_full = Ef;
+    a.tables_mom = tables_mom; a.n_mom = Em;
+    a.tab_slot = split ? c.d_tabslot_split.as<int>() : c.d_tabslot_ident.as<int>();
     a.coords = c.d_coord_ptrs.as<const double*>();
     a.opz_eff2 = c.d_opz_eff2.as<double>();
     a.n_model = c.n_model;
@@ -951,6 +1029,11 @@ int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, doubl
     for (long long b = 0; b < Bc; ++b) status_host[b0 + b] |= plan->static_bad;
   }
   return VG_OK;
+}
+
+int vg_corr_n_moment(const vg_plan* plan, int32_t corr) {
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments) return 0;
+  return (int)plan->corrs[corr]->mom_ids.size();
 }
 
 int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }

@@ -1,0 +1,149 @@
+// Moment form of K1+K2a+K2b for evaluations whose only sampled P(k,mu) parameters are the
+// Kaiser / HCD amplitudes.
+//
+// With F = F_hcd(k_par) and S = the product of every other factor both fixed for the batch,
+// the reference's P(k,mu) (vega/power_spectrum.py:87-196 with :198-222 and :263-309) is
+//   P = pk_lin(k) S(mu,k) [(a0 + h0 F) + (a1 + h1 F) mu^2]_t0 [(a0 + h0 F) + (a1 + h1 F) mu^2]_t1
+// i.e. a polynomial in (F, mu^2) whose 9 coefficients c[a][j] (powers F^a mu^2j, a,j = 0..2)
+// depend only on the parameter vector.  The mu projection (vega/pktoxi.py:79-97), the
+// FFTLog (mcfit.P2xi / Pk2Mp) and the cubic spline are linear, so
+//   knots_l[b] = sum_{a,j} c[a][j](theta_b) * K_l[a][j],
+//   K_l[a][j]  = (Hankel+spline operator)_l  applied to  pk_lin(k) sum_mu w_l(mu) S F^a mu^2j
+// with K built once per plan by the same DGEMM kernel the per-vector path uses.  The hot
+// path of such an evaluation is then 3 or 9 FMAs per knot instead of a pass over the
+// 814 000-point grid and a Hankel GEMM row.  Evaluations with velocity dispersion,
+// sampled L0_hcd, sampled non-linear parameters, UV-dependent bias or the effective-bias
+// division of fast_metals keep the full per-point pass (vg_pk.cuh).
+#pragma once
+#include "../../include/vega_b200.h"
+#include "vg_common.cuh"
+#include "vg_pk.cuh"
+
+namespace vg {
+
+constexpr int MOM_MAX = 9;   // F^a mu^2j, index a*3 + j
+
+// Host-side eligibility test (mirrors the kernel-class selection in vg_plan_finalize)
+inline bool moment_eligible(const vg_eval_desc& d) {
+  if (d.dyn_mask != 0) return false;
+  const bool uv = (d.uvb || d.heii) && (d.uv_on[0] || d.uv_on[1]);
+  if (uv) return false;
+  const bool hcd = d.hcd_model && (d.hcd_on[0] || d.hcd_on[1]);
+  if (hcd && d.hcd_grid < 0) return false;           // L0_hcd sampled: F differs per vector
+  if (hcd && d.fast_metals) return false;            // Kaiser / effective bias is rational in F
+  return true;
+}
+inline int moment_count(const vg_eval_desc& d) {
+  return (d.hcd_model && (d.hcd_on[0] || d.hcd_on[1])) ? 9 : 3;
+}
+
+// Plan time: mom[j][m][l][nk_pad] = pk_lin(k) * sum_i wleg[l][i] S(mu_i,k) F(mu_i,k)^a mu_i^2j
+// for the moment evaluations ids[j]; m = a*3 + j2.  grid = (ceil(nk/128), n_ids), block 128.
+__global__ void __launch_bounds__(128)
+moment_grid_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, const int* __restrict__ ids,
+                   double* __restrict__ mom) {
+  const int ik = blockIdx.x * 128 + threadIdx.x;
+  if (ik >= g.nk) return;
+  const vg_eval_desc& d = evals[ids[blockIdx.y]];
+  const bool hcd = d.hcd_model && (d.hcd_on[0] || d.hcd_on[1]);
+  const int na = hcd ? 3 : 1;
+  const double* S = d.static_grid >= 0 ? g.grids[d.static_grid] + ik : nullptr;
+  const double* F = hcd ? g.grids[d.hcd_grid] + ik : nullptr;
+  double acc[MOM_MAX][PK_MAX_ELL];
+#pragma unroll
+  for (int m = 0; m < MOM_MAX; ++m)
+#pragma unroll
+    for (int l = 0; l < PK_MAX_ELL; ++l) acc[m][l] = 0.0;
+  for (int i = 0; i < g.nmu; ++i) {
+    const double mu = g.mu[i], mu2 = mu * mu;
+    const double s = S ? S[(long long)i * g.nk] : 1.0;
+    const double f = F ? F[(long long)i * g.nk] : 0.0;
+    double w[PK_MAX_ELL];
+#pragma unroll
+    for (int l = 0; l < PK_MAX_ELL; ++l) w[l] = l < g.n_ell ? g.wleg[l * g.nmu + i] : 0.0;
+    double fa = s;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      if (a < na) {
+        double v = fa;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+#pragma unroll
+          for (int l = 0; l < PK_MAX_ELL; ++l) acc[a * 3 + j][l] = fma(w[l], v, acc[a * 3 + j][l]);
+          v *= mu2;
+        }
+        fa *= f;
+      }
+    }
+  }
+  const double pk_lin = g.pk_lin[d.pk_lin_sel][ik];
+  for (int m = 0; m < MOM_MAX; ++m)
+    for (int l = 0; l < g.n_ell; ++l)
+      mom[(((long long)blockIdx.y * MOM_MAX + m) * g.n_ell + l) * g.nk_pad + ik] = acc[m][l] * pk_lin;
+}
+
+// Coefficients of F^a mu^2j in the product of the two tracers' Kaiser terms
+__device__ __forceinline__ void moment_coefs(const KaiserCoef& c, double* q) {
+  const double A0 = c.a0[0], H0 = c.h0[0], A1 = c.a1[0], H1 = c.h1[0];
+  const double B0 = c.a0[1], G0 = c.h0[1], B1 = c.a1[1], G1 = c.h1[1];
+  // mu^0: (A0 + H0 F)(B0 + G0 F)
+  q[0 * 3 + 0] = A0 * B0;
+  q[1 * 3 + 0] = A0 * G0 + H0 * B0;
+  q[2 * 3 + 0] = H0 * G0;
+  // mu^2: (A0 + H0 F)(B1 + G1 F) + (A1 + H1 F)(B0 + G0 F)
+  q[0 * 3 + 1] = A0 * B1 + A1 * B0;
+  q[1 * 3 + 1] = A0 * G1 + H0 * B1 + A1 * G0 + H1 * B0;
+  q[2 * 3 + 1] = H0 * G1 + H1 * G0;
+  // mu^4: (A1 + H1 F)(B1 + G1 F)
+  q[0 * 3 + 2] = A1 * B1;
+  q[1 * 3 + 2] = A1 * G1 + H1 * B1;
+  q[2 * 3 + 2] = H1 * G1;
+}
+
+// Hot path: tables[b][j][x] = sum_m c_m(theta_b, eval ids[j]) * ktab[j][m][x],  x over the
+// n_ell*2*n_out_pad knot values and second derivatives of the evaluation.
+// grid = (ceil(row_len / (256*MOM_XPT)), n_ids, ceil(B / MOM_NB)), block 256.
+constexpr int MOM_NB = 4, MOM_XPT = 2;
+__global__ void __launch_bounds__(256)
+moment_tables_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__ ids, int n_ids,
+                     const double* __restrict__ pfull, int npf, int B, const double* __restrict__ ktab,
+                     int row_len, double* __restrict__ tables) {
+  __shared__ double cq[MOM_NB][MOM_MAX];
+  __shared__ int s_nm;
+  const int j = blockIdx.y, b0 = blockIdx.z * MOM_NB;
+  if (threadIdx.x < MOM_NB) {
+    const vg_eval_desc& d = evals[ids[j]];
+    const double* p = pfull + (long long)min(b0 + (int)threadIdx.x, B - 1) * npf;
+    KaiserCoef kc = kaiser_setup(d, p, 1.0);   // k only enters through the UV terms (excluded)
+    if (d.same_tracer) { kc.a0[1] = kc.a0[0]; kc.a1[1] = kc.a1[0]; kc.h0[1] = kc.h0[0]; kc.h1[1] = kc.h1[0]; }
+    double q[MOM_MAX];
+    moment_coefs(kc, q);
+#pragma unroll
+    for (int m = 0; m < MOM_MAX; ++m) cq[threadIdx.x][m] = q[m];
+    if (threadIdx.x == 0) s_nm = (d.hcd_model && (d.hcd_on[0] || d.hcd_on[1])) ? 3 : 1;
+  }
+  __syncthreads();
+  const int na = s_nm;
+  const double* kt = ktab + (long long)j * MOM_MAX * row_len;
+#pragma unroll
+  for (int u = 0; u < MOM_XPT; ++u) {
+    const int x = (blockIdx.x * MOM_XPT + u) * 256 + threadIdx.x;
+    if (x >= row_len) break;
+    double acc[MOM_NB];
+#pragma unroll
+    for (int e = 0; e < MOM_NB; ++e) acc[e] = 0.0;
+    for (int a = 0; a < na; ++a)
+#pragma unroll
+      for (int jj = 0; jj < 3; ++jj) {
+        const int m = a * 3 + jj;
+        const double v = __ldg(kt + (long long)m * row_len + x);
+#pragma unroll
+        for (int e = 0; e < MOM_NB; ++e) acc[e] = fma(cq[e][m], v, acc[e]);
+      }
+#pragma unroll
+    for (int e = 0; e < MOM_NB; ++e)
+      if (b0 + e < B) tables[((long long)(b0 + e) * n_ids + j) * row_len + x] = acc[e];
+  }
+}
+
+}  // namespace vg

@@ -196,6 +196,16 @@ __device__ __forceinline__ double kaiser_eval(const vg_eval_desc& d, const Kaise
   return t0 * t1;
 }
 
+// 1/sqrt(a) for finite a >= 1 (the Lorentzian velocity dispersion 1/sqrt(1 + (k_par sigma)^2),
+// power_spectrum.py:613-636): single-precision MUFU seed (relative error e ~ 2^-22) and one
+// third-order correction y (1 + e/2 + 3 e^2/8), leaving O(e^3) ~ 2^-64 -- 5 FP64 operations
+// instead of the ~15 of the general-purpose rsqrt() with its special-case handling.
+__device__ __forceinline__ double rsqrt_ge1(double a) {
+  const double y = (double)rsqrtf((float)a);
+  const double e = fma(-a * y, y, 1.0);
+  return fma(y, e * fma(0.375, e, 0.5), y);
+}
+
 constexpr int PK_KLANES = 32, PK_GROUPS = 8;   // CTA = 32 k lanes x (MG mu groups x EG vector groups)
 constexpr int PK_UNROLL = 4;                   // mu rows whose grid loads are issued together
 
@@ -215,11 +225,13 @@ enum { PK_MODE_STATIC = 0, PK_MODE_VELO = 1, PK_MODE_GENERIC = 2 };
 // fetched from L2 once per NB*EG vectors.  MODE selects how the per-vector factors are
 // evaluated: none, velocity dispersion only (parameters hoisted into registers), or the
 // generic path that reads parameters per point.
-// out[b][eval][l][nk_pad]  (pad columns are never written and stay zero)
+// out[b][out_slot[eval]][l][nk_pad], n_slots slots per vector (pad columns are never written
+// and stay zero)
 template <int NB, int MODE>
 __global__ void __launch_bounds__(PK_KLANES * PK_GROUPS, 2)
 pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
-              const int* __restrict__ eval_ids, const double* __restrict__ pfull, int npf, int B,
+              const int* __restrict__ eval_ids, const int* __restrict__ out_slot, int n_slots,
+              const double* __restrict__ pfull, int npf, int B,
               double* __restrict__ out, int* __restrict__ status) {
   __shared__ vg_eval_desc d;
   __shared__ double red[PK_GROUPS][NB * PK_MAX_ELL][PK_KLANES + 1];
@@ -227,6 +239,7 @@ pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
   const int MG = blockDim.y, EG = blockDim.z;
   const int tid = (eg * MG + mg) * PK_KLANES + tx;
   const int eval = eval_ids[blockIdx.z];
+  const int slot = out_slot[eval];
   {
     const int* src = reinterpret_cast<const int*>(evals + eval);
     int* dst = reinterpret_cast<int*>(&d);
@@ -326,7 +339,7 @@ pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
             if (d.idx_velo[t] < 0) continue;
             const double x = kpar * sv[e][t];
             if (velo_kind == 1) P *= exp(-0.25 * x * x);
-            else P *= rsqrt(fma(x, x, 1.0));
+            else P *= rsqrt_ge1(fma(x, x, 1.0));
           }
         } else if (MODE == PK_MODE_GENERIC) {
           P *= pk_factors(dyn_mask, d, pp[e], k, mu, pk_fid_k, &bad[e]);
@@ -355,7 +368,7 @@ pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
         double sum = 0.0;
         for (int m = 0; m < MG; ++m) sum += red[m][o][tx];
         if (std_ells) sum *= (double)(4 * l + 1) / (double)g.nmu;   // dmu * (2 ell + 1), ell = 2l
-        out[(((long long)(b0 + e) * n_eval + eval) * g.n_ell + l) * g.nk_pad + ik] = sum * pk_lin;
+        out[(((long long)(b0 + e) * n_slots + slot) * g.n_ell + l) * g.nk_pad + ik] = sum * pk_lin;
       }
     }
   }
@@ -377,7 +390,8 @@ constexpr int PK_FAST_U = 5;
 template <int NB, int MODE, int KIND>
 __global__ void __launch_bounds__(PK_KLANES * PK_GROUPS, 2)
 pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
-                   const int* __restrict__ eval_ids, const double* __restrict__ pfull, int npf, int B,
+                   const int* __restrict__ eval_ids, const int* __restrict__ out_slot, int n_slots,
+                   const double* __restrict__ pfull, int npf, int B,
                    double* __restrict__ out) {
   __shared__ vg_eval_desc d;
   __shared__ double red[PK_GROUPS][NB * PK_MAX_ELL][PK_KLANES + 1];
@@ -385,6 +399,7 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
   const int MG = blockDim.y, EG = blockDim.z;
   const int tid = (eg * MG + mg) * PK_KLANES + tx;
   const int eval = eval_ids[blockIdx.z];
+  const int slot = out_slot[eval];
   {
     const int* src = reinterpret_cast<const int*>(evals + eval);
     int* dst = reinterpret_cast<int*>(&d);
@@ -457,8 +472,8 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
         double P = TWO ? t * fma(aP1[e], mu2, aP0[e]) : t * t;
         P *= s[u];
         if (MODE == PK_MODE_VELO) {
-          if (velo0) { const double x = sv0[e] * mu[u]; P *= velo_gauss ? exp(-0.25 * x * x) : rsqrt(fma(x, x, 1.0)); }
-          if (velo1) { const double x = sv1[e] * mu[u]; P *= velo_gauss ? exp(-0.25 * x * x) : rsqrt(fma(x, x, 1.0)); }
+          if (velo0) { const double x = sv0[e] * mu[u]; P *= velo_gauss ? exp(-0.25 * x * x) : rsqrt_ge1(fma(x, x, 1.0)); }
+          if (velo1) { const double x = sv1[e] * mu[u]; P *= velo_gauss ? exp(-0.25 * x * x) : rsqrt_ge1(fma(x, x, 1.0)); }
         }
 #pragma unroll
         for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = fma(w[l], P, acc[e][l]);
@@ -482,7 +497,7 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
         if (b0 + e >= B || l >= g.n_ell || ik_raw >= g.nk) continue;
         double sum = 0.0;
         for (int m = 0; m < MG; ++m) sum += red[m][o][tx];
-        out[(((long long)(b0 + e) * n_eval + eval) * g.n_ell + l) * g.nk_pad + ik] = sum * pk_lin;
+        out[(((long long)(b0 + e) * n_slots + slot) * g.n_ell + l) * g.nk_pad + ik] = sum * pk_lin;
       }
     }
   }

@@ -33,7 +33,12 @@ struct XiArgs {
   HankelDev h;
   const vg_eval_desc* evals; int n_eval;
   const double* pfull; int npf; int B;
-  const double* tables;    // [B][n_eval][n_ell][2*n_out_pad]
+  // knot tables [B][n][n_ell][2*n_out_pad] from the Hankel GEMM (n_full per vector) and from
+  // the moment form (n_mom per vector); tab_slot[eval] >= 0: index in the first, < 0:
+  // -(index + 1) in the second
+  const double* tables; int n_full;
+  const double* tables_mom; int n_mom;
+  const int* tab_slot;
   const double* const* coords;   // coordinate tables, each [5][n_model]
   const double* opz_eff2;  // per coordinate table: (1+z_eff)^2
   int n_model;
@@ -135,7 +140,9 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
   if (tid == 0) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n"
                  ::"r"(smem_u32(&bar)), "r"(row_bytes * (unsigned)a.h.n_ell) : "memory");
-    const double* src = a.tables + ((long long)b * a.n_eval + e) * a.h.n_ell * row;
+    const int slot = a.tab_slot[e];
+    const double* src = slot >= 0 ? a.tables + ((long long)b * a.n_full + slot) * a.h.n_ell * row
+                                  : a.tables_mom + ((long long)b * a.n_mom + (-slot - 1)) * a.h.n_ell * row;
     for (int l = 0; l < a.h.n_ell; ++l) {
       asm volatile(
           "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"

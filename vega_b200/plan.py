@@ -710,6 +710,14 @@ class DevicePlan:
         _lib.check(self.lib.vg_plan_finalize(self.handle, self._stream()))
         self.static_status = self.lib.vg_plan_static_status(self.handle)
 
+    def set_option(self, option, value):
+        """Run-time switches of the CUDA library (include/vega_b200.h: VG_OPT_*)."""
+        _lib.check(self.lib.vg_plan_set_option(self.handle, int(option), int(value)))
+
+    def n_moment(self, ci):
+        """Evaluations of correlation ci computed in moment form (csrc/vg_moments.cuh)."""
+        return self.lib.vg_corr_n_moment(self.handle, ci)
+
     def device_bytes(self):
         return self.lib.vg_plan_device_bytes(self.handle)
 

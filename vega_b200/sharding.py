@@ -1,0 +1,135 @@
+"""Sharding of a batch of parameter vectors over one process per GPU.
+
+The chi2 path has no exchange inside an evaluation: every parameter vector (PolyChord live
+point, iminuit stencil point, Monte Carlo mock) is independent, exactly as in the
+reference's rank-per-replica MPI scripts (bin/run_vega_mpi.py:24-52,
+bin/run_vega_mc_fits_mpi.py:81-159, which split mocks with ``range(rank, n, size)`` and
+never communicate).  Here every rank holds a replica of the device plan, takes a
+contiguous shard of the batch, and the only collective is ONE all-gather of the
+per-vector chi2 (8 bytes per vector) and status words -- NCCL over NVLink on the GPU box,
+gloo in the CPU tests of the host logic.
+
+The evaluator is the device engine (``VegaInterface.chi2_device`` path); the host-side
+partition / gather arithmetic is separated from it so that it can be exercised with
+world_size 2 on CPU (tests/test_sharding.py) with a stand-in evaluator.  There is no CPU
+evaluator in the product: `ShardedChi2` built from a VegaInterface needs CUDA.
+"""
+import numpy as np
+
+
+def shard_bounds(n, world, rank):
+    """Contiguous shard [lo, hi) of n items for `rank` of `world`; the first n % world
+    ranks hold one extra item (ragged batches are allowed, empty shards too)."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError(f'rank {rank} outside world of {world}')
+    base, extra = divmod(int(n), world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_sizes(n, world):
+    return [shard_bounds(n, world, r)[1] - shard_bounds(n, world, r)[0] for r in range(world)]
+
+
+class ShardedChi2:
+    """chi2 of a global batch theta[B, P], evaluated shard-per-rank and all-gathered.
+
+    evaluate(theta_local: torch.Tensor[b, P]) -> (chi2[b] float64, status[b] int32) tensors
+    on `device`.  `group` is a torch.distributed process group (None = default)."""
+
+    def __init__(self, evaluate, device, group=None):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.evaluate = evaluate
+        self.device = torch.device(device)
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self._gather_buf = None
+
+    @classmethod
+    def from_vega(cls, vega, names=(), group=None):
+        """Shard evaluator backed by the device engine of a VegaInterface replica."""
+        import torch
+        if not torch.cuda.is_available():
+            from ._lib import VegaDeviceError
+            raise VegaDeviceError('ShardedChi2 needs a CUDA device: the B200 path has no CPU evaluator.')
+        engine = vega._engine_for(tuple(names))
+        return cls(lambda t: engine.chi2_device(t), engine.device, group)
+
+    def _buffers(self, cap):
+        torch = self.torch
+        if self._gather_buf is None or self._gather_buf[0].shape[1] < cap:
+            self._gather_buf = (
+                torch.empty(self.world, cap, dtype=torch.float64, device=self.device),
+                torch.empty(self.world, cap, dtype=torch.int32, device=self.device),
+                torch.zeros(cap, dtype=torch.float64, device=self.device),
+                torch.zeros(cap, dtype=torch.int32, device=self.device))
+        return self._gather_buf
+
+    def local_shard(self, theta):
+        lo, hi = shard_bounds(theta.shape[0], self.world, self.rank)
+        return theta[lo:hi]
+
+    def chi2_local(self, theta_local):
+        """(chi2, status) device tensors of this rank's shard (already on the device)."""
+        torch = self.torch
+        if theta_local.shape[0] == 0:
+            return (torch.empty(0, dtype=torch.float64, device=self.device),
+                    torch.empty(0, dtype=torch.int32, device=self.device))
+        return self.evaluate(theta_local)
+
+    def gather(self, chi2_local, status_local, n_total):
+        """All-gather the per-shard results into global order.  Shards are padded to the
+        largest shard so one fixed-size collective serves ragged batches."""
+        torch, dist = self.torch, self.dist
+        if self.world == 1:
+            return chi2_local, status_local
+        sizes = shard_sizes(n_total, self.world)
+        cap = max(max(sizes), 1)
+        g_chi2, g_stat, s_chi2, s_stat = self._buffers(cap)
+        cap = g_chi2.shape[1]
+        n = chi2_local.shape[0]
+        s_chi2[:n].copy_(chi2_local)
+        s_stat[:n].copy_(status_local)
+        dist.all_gather_into_tensor(g_chi2.view(-1), s_chi2, group=self.group)
+        dist.all_gather_into_tensor(g_stat.view(-1), s_stat, group=self.group)
+        if all(s == cap for s in sizes):
+            return g_chi2.view(-1)[:n_total].clone(), g_stat.view(-1)[:n_total].clone()
+        chi2 = torch.cat([g_chi2[r, :s] for r, s in enumerate(sizes)])
+        stat = torch.cat([g_stat[r, :s] for r, s in enumerate(sizes)])
+        return chi2, stat
+
+    def chi2(self, theta):
+        """theta: the GLOBAL batch (host ndarray or tensor, identical on every rank, e.g. the
+        sampler's live points after a broadcast).  Returns host ndarray chi2[B] with the
+        reference's 1e100 sentinel for model-domain failures, identical on every rank."""
+        from ._lib import STATUS_ARINYO, STATUS_BOUNDS
+        torch = self.torch
+        if not torch.is_tensor(theta):
+            theta = torch.from_numpy(np.ascontiguousarray(np.atleast_2d(theta), dtype=np.float64))
+        n_total = theta.shape[0]
+        local = self.local_shard(theta).contiguous().to(self.device)
+        c, s = self.chi2_local(local)
+        c, s = self.gather(c, s, n_total)
+        c = c.cpu().numpy().copy()
+        s = s.cpu().numpy()
+        c[(s & (STATUS_ARINYO | STATUS_BOUNDS)) != 0] = 1e100
+        return c
+
+    def broadcast_theta(self, theta, src=0):
+        """Broadcast a batch from the rank that owns the sampler."""
+        torch, dist = self.torch, self.dist
+        if self.world == 1:
+            return theta
+        shape = torch.zeros(2, dtype=torch.int64, device=self.device)
+        if self.rank == src:
+            theta = torch.as_tensor(np.asarray(theta, dtype=np.float64))
+            shape[0], shape[1] = theta.shape
+        dist.broadcast(shape, src, group=self.group)
+        buf = torch.empty(int(shape[0]), int(shape[1]), dtype=torch.float64, device=self.device)
+        if self.rank == src:
+            buf.copy_(theta)
+        dist.broadcast(buf, src, group=self.group)
+        return buf
