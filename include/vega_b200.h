@@ -93,6 +93,14 @@ typedef struct vg_eval_desc {
   int32_t weight_bias;      /* 1: multiply by b1*b2 of the pair (vega/metals.py:316-334) */
   int32_t idx_weight_extra; /* bias_{M1}_{M2} (separate-metal-auto-biases), -1 none */
   double weight_const;      /* 2 for M1 != M2 in an auto-correlation (vega/metals.py:238-239) */
+  /* ---- fast_metals caches (vega/metals.py:144-207) ---- */
+  int32_t table_owner;      /* >=0: this evaluation has no P(k,mu) of its own and reads the knot
+                               tables of evaluation `table_owner` -- the metal x main-tracer cache
+                               hit of compute_xi_metal_cross_main (:171-207), whose key holds the
+                               betas but not the pair; only weight and metal matrix differ */
+  int32_t frozen;           /* 1: metal x metal term of compute_xi_metal_metal (:144-169): M_c xi_c
+                               is evaluated once, at the plan's base parameters, in
+                               vg_plan_finalize; the hot path adds b1*b2 (x extra) times it */
 } vg_eval_desc;
 
 /* One broadband term (vega/broadband_poly.py:23-198) */

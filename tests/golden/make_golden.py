@@ -35,15 +35,44 @@ PERTURBED = {
         {'bias_hcd': -0.07, 'beta_hcd': 0.5, 'L0_hcd': 12.},
     ],
 }
+PERTURBED['full_fast'] = PERTURBED['full']
 CONFIGS = {'full': 'tests/full_configs/main.ini', 'c1': 'tests/configs/main.ini'}
+
+
+def fast_metals_copy(main_ini, tmp_dir):
+    """Copy of a reference configuration with `fast_metals = True` under every [model]
+    (vega/metals.py:58: the metal caches of compute_xi_metal_metal / _cross_main)."""
+    import configparser
+    tmp_dir.mkdir(parents=True, exist_ok=True)
+    main = configparser.ConfigParser()
+    main.optionxform = lambda option: option
+    main.read(main_ini)
+    new_paths = []
+    for path in main['data sets']['ini files'].split():
+        cfg = configparser.ConfigParser()
+        cfg.optionxform = lambda option: option
+        from vega.utils import find_file
+        cfg.read(find_file(os.path.expandvars(path)))
+        cfg['model']['fast_metals'] = 'True'
+        new_path = tmp_dir / Path(path).name
+        with open(new_path, 'w') as f:
+            cfg.write(f)
+        new_paths.append(str(new_path))
+    main['data sets']['ini files'] = ' '.join(new_paths)
+    out = tmp_dir / 'main.ini'
+    with open(out, 'w') as f:
+        main.write(f)
+    return str(out)
 
 
 def main():
     out, meta = {}, {}
+    CONFIGS['full_fast'] = fast_metals_copy(CONFIGS['full'], Path('/tmp/vega_golden_fast'))
     for key, ini in CONFIGS.items():
         vega = VegaInterface(ini)
         cases = [{}] + PERTURBED[key]
-        meta[key] = {'ini': ini, 'cases': cases, 'corr': list(vega.corr_items)}
+        meta[key] = {'ini': CONFIGS['full'] + ' + fast_metals = True' if key == 'full_fast' else ini,
+                     'cases': cases, 'corr': list(vega.corr_items)}
         for i, pars in enumerate(cases):
             model = vega.compute_model(pars, run_init=True)
             for name, xi in model.items():

@@ -44,6 +44,7 @@ class EvalDesc(C.Structure):
         ('uv_shot', i32), ('idx_uvshot', i32 * 3),
         ('out_slot', i32), ('weight_bias', i32), ('idx_weight_extra', i32),
         ('weight_const', f64),
+        ('table_owner', i32), ('frozen', i32),
     ]
 
     def __init__(self):
@@ -59,6 +60,7 @@ class EvalDesc(C.Structure):
         self.static_grid = -1
         self.single_ell = -1
         self.weight_const = 1.0
+        self.table_owner = -1
 
 
 class BBTerm(C.Structure):

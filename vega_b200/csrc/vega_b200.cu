@@ -92,29 +92,40 @@ struct Hankel {
   DevBuf op;    // [n_ell][2*n_out_pad][nk_pad]
 };
 
+struct EvalLayout {
+  // evaluations grouped by pk_ell kernel class: 0..19 fast (VMODE*5 + KIND), 20..22 generic (20 + MODE)
+  std::vector<int> class_ids[23];
+  DevBuf d_class_ids[23];
+  std::vector<int> mom_ids;      // evaluations in moment form
+  std::vector<int> gather_ids;   // evaluations K3 runs for
+  int n_full = 0;                // evaluations that go through pk_ell + the Hankel GEMM
+  int n_metal = 0;               // metal column blocks of xmet / mcat
+  std::vector<int> metal_map;    // metal slot -> column block (-1: not in this layout)
+  DevBuf d_mom_ids, d_gather_ids, d_slot, d_tabslot, d_metal_map;
+};
+enum { LAY_MOM = 0, LAY_FULL = 1, LAY_ALL = 2 };
+
 struct Corr {
   int hankel_id = 0, n_model = 0, n_dist = 0, ld_model = 0, ld_dist = 0;
   std::vector<vg_eval_desc> evals;
   DevBuf d_evals;
-  // evaluations grouped by pk_ell kernel class: 0..9 fast (MODE*5 + KIND), 10..12 generic (10 + MODE)
-  std::vector<int> mode_ids[13];
-  DevBuf d_mode_ids[13];
-  // the same classes without the evaluations served by the moment form (vg_moments.cuh)
-  std::vector<int> full_mode_ids[13];
-  DevBuf d_full_mode_ids[13];
-  std::vector<int> mom_ids;      // evaluations in moment form
-  int n_full = 0;                // evaluations that keep the per-point pass
-  DevBuf d_mom_ids, d_mom_ktab;  // ktab [n_mom][9][n_ell][2*n_out_pad]
-  // per evaluation: slot in the multipole buffer / encoded slot in the knot tables, for the
-  // all-evaluations layout (ident) and the split layout (full-pass evaluations compacted)
-  DevBuf d_slot_ident, d_slot_split, d_tabslot_ident, d_tabslot_split;
+  // Three ways of laying the evaluations out over the kernels of the front end:
+  //   LAY_MOM  hot path, moment form on: per-point pass for the evaluations that need it,
+  //            moment form for the rest;   LAY_FULL  hot path, every evaluation per point;
+  //   LAY_ALL  per-stage taps and the finalize pass of the frozen terms: every evaluation
+  //            incl. the frozen ones, per point, identity slots.
+  // Evaluations with table_owner >= 0 never own tables; frozen ones leave the hot layouts.
+  EvalLayout lay[3];
+  DevBuf d_mom_ktab;             // LAY_MOM: [n_mom][9][n_ell][2*n_out_pad]
   std::vector<DevBuf> coords;
   std::vector<double> opz_eff2;
   DevBuf d_coord_ptrs, d_opz_eff2;
-  int n_metal = 0;
+  int n_metal = 0;               // metal slots declared by the evaluations (all layouts)
   bool metal_dense = false;
   std::vector<std::vector<double>> metal_host;
-  DevBuf d_mcat;                 // [n_model][n_metal*ld_model]
+  std::vector<int> frozen_ids;   // frozen evaluations, in order of d_frozen rows
+  DevBuf d_frozen_ids, d_frozen; // d_frozen [n_frozen][ld_model] = weight_const * M_c xi_c
+  DevBuf d_mcat;                 // hot metal matrices [n_model][n_metal_hot*ld_model]
   bool has_dmat = false;
   DevBuf d_dmat;                 // [n_dist][ld_model]
   DevBuf d_dmat_masked;          // [n_mask][ld_model]
@@ -198,7 +209,83 @@ struct ProfScope {
 int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, long long ldb,
               double* C, long long ldc, int M, int N, int K, int batch, long long strideA,
               long long strideB, long long strideC, cudaStream_t st);
+int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
 enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_MOMENT = 7, PROF_NTAGS = 8 };
+}  // namespace
+
+namespace {
+constexpr int PK_NCLS = 23;   // 0..19 fast kernels (VMODE*5 + KIND), 20..22 generic (20 + MODE)
+
+// pk_ell kernel class of one evaluation
+int pk_class(const vg_plan* plan, const vg_eval_desc& d) {
+  const uint32_t m = d.dyn_mask;
+  const int mode = m == 0 ? vg::PK_MODE_STATIC : (m == VG_F_VELO ? vg::PK_MODE_VELO : vg::PK_MODE_GENERIC);
+  const bool hcd = d.hcd_model && (d.hcd_on[0] || d.hcd_on[1]);
+  int kind = -1;
+  if (!hcd) kind = d.same_tracer ? 0 : 1;
+  else if (d.hcd_grid >= 0) {
+    if (d.same_tracer) kind = d.fast_metals ? -1 : 2;
+    else if (d.hcd_on[0] != d.hcd_on[1]) kind = d.fast_metals ? 4 : 3;
+  }
+  int vmode = vg::PK_V_NONE;
+  if (mode == vg::PK_MODE_VELO) {
+    const int n_velo = (d.idx_velo[0] >= 0) + (d.idx_velo[1] >= 0);
+    vmode = d.velo_kind == 1 ? vg::PK_V_GAUSS : (n_velo == 2 ? vg::PK_V_LOR2 : vg::PK_V_LOR1);
+  }
+  const bool fast = mode != vg::PK_MODE_GENERIC && kind >= 0 && plan->n_ell == vg::PK_MAX_ELL;
+  return fast ? vmode * 5 + kind : 20 + mode;
+}
+
+// The three evaluation layouts of a correlation (see Corr::lay)
+int build_layouts(vg_plan* plan, Corr& c) {
+  const int E = (int)c.evals.size();
+  for (int e = 0; e < E; ++e) {
+    const vg_eval_desc& d = c.evals[e];
+    if (d.table_owner >= 0) {
+      VG_REQUIRE(d.table_owner < E && c.evals[d.table_owner].table_owner < 0 && !c.evals[d.table_owner].frozen,
+                 "evaluation %d: bad table_owner %d", e, d.table_owner);
+      VG_REQUIRE(!d.frozen, "evaluation %d: frozen and table_owner are exclusive", e);
+    }
+    if (d.frozen) VG_REQUIRE(d.out_slot >= 2, "evaluation %d: only metal terms can be frozen", e);
+  }
+  c.frozen_ids.clear();
+  for (int e = 0; e < E; ++e)
+    if (c.evals[e].frozen) c.frozen_ids.push_back(e);
+  if (!c.frozen_ids.empty()) VG_TRY(upload(c.d_frozen_ids, c.frozen_ids.data(), c.frozen_ids.size()));
+  for (int li = 0; li < 3; ++li) {
+    EvalLayout& L = c.lay[li];
+    for (auto& ids : L.class_ids) ids.clear();
+    L.mom_ids.clear(); L.gather_ids.clear();
+    L.n_full = 0; L.n_metal = 0;
+    L.metal_map.assign(std::max(c.n_metal, 1), -1);
+    std::vector<int> slot(E, 0), tabslot(E, 0);
+    for (int e = 0; e < E; ++e) {
+      const vg_eval_desc& d = c.evals[e];
+      const bool hot = li == LAY_ALL || !d.frozen;
+      if (!hot) continue;
+      L.gather_ids.push_back(e);
+      if (d.out_slot >= 2) L.metal_map[d.out_slot - 2] = L.n_metal++;
+      if (d.table_owner >= 0) continue;
+      if (li == LAY_MOM && vg::moment_eligible(d)) {
+        tabslot[e] = -((int)L.mom_ids.size() + 1);
+        L.mom_ids.push_back(e);
+      } else {
+        slot[e] = tabslot[e] = L.n_full++;
+        L.class_ids[pk_class(plan, d)].push_back(e);
+      }
+    }
+    for (int e = 0; e < E; ++e)
+      if (c.evals[e].table_owner >= 0) tabslot[e] = tabslot[c.evals[e].table_owner];
+    for (int m = 0; m < PK_NCLS; ++m)
+      if (!L.class_ids[m].empty()) VG_TRY(upload(L.d_class_ids[m], L.class_ids[m].data(), L.class_ids[m].size()));
+    if (!L.mom_ids.empty()) VG_TRY(upload(L.d_mom_ids, L.mom_ids.data(), L.mom_ids.size()));
+    if (!L.gather_ids.empty()) VG_TRY(upload(L.d_gather_ids, L.gather_ids.data(), L.gather_ids.size()));
+    VG_TRY(upload(L.d_slot, slot.data(), slot.size()));
+    VG_TRY(upload(L.d_tabslot, tabslot.data(), tabslot.size()));
+    VG_TRY(upload(L.d_metal_map, L.metal_map.data(), L.metal_map.size()));
+  }
+  return VG_OK;
+}
 }  // namespace
 
 extern "C" {
@@ -463,44 +550,7 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
     Corr& c = *cp;
     VG_REQUIRE(!c.evals.empty(), "correlation without evaluations");
     VG_TRY(upload(c.d_evals, c.evals.data(), c.evals.size()));
-    for (auto& ids : c.mode_ids) ids.clear();
-    for (auto& ids : c.full_mode_ids) ids.clear();
-    c.mom_ids.clear();
-    c.n_full = 0;
-    std::vector<int> slot_ident(c.evals.size()), slot_split(c.evals.size(), 0), tabslot_split(c.evals.size(), 0);
-    for (size_t e = 0; e < c.evals.size(); ++e) slot_ident[e] = (int)e;
-    for (size_t e = 0; e < c.evals.size(); ++e) {
-      const vg_eval_desc& d = c.evals[e];
-      const uint32_t m = d.dyn_mask;
-      const int mode = m == 0 ? vg::PK_MODE_STATIC : (m == VG_F_VELO ? vg::PK_MODE_VELO : vg::PK_MODE_GENERIC);
-      const bool hcd = d.hcd_model && (d.hcd_on[0] || d.hcd_on[1]);
-      int kind = -1;
-      if (!hcd) kind = d.same_tracer ? 0 : 1;
-      else if (d.hcd_grid >= 0) {
-        if (d.same_tracer) kind = d.fast_metals ? -1 : 2;
-        else if (d.hcd_on[0] != d.hcd_on[1]) kind = d.fast_metals ? 4 : 3;
-      }
-      const bool fast = mode != vg::PK_MODE_GENERIC && kind >= 0 && plan->n_ell == vg::PK_MAX_ELL;
-      const int cls = fast ? mode * 5 + kind : 10 + mode;
-      c.mode_ids[cls].push_back((int)e);
-      if (vg::moment_eligible(d)) {
-        tabslot_split[e] = -((int)c.mom_ids.size() + 1);
-        c.mom_ids.push_back((int)e);
-      } else {
-        slot_split[e] = tabslot_split[e] = c.n_full++;
-        c.full_mode_ids[cls].push_back((int)e);
-      }
-    }
-    for (int m = 0; m < 13; ++m) {
-      if (!c.mode_ids[m].empty()) VG_TRY(upload(c.d_mode_ids[m], c.mode_ids[m].data(), c.mode_ids[m].size()));
-      if (!c.full_mode_ids[m].empty())
-        VG_TRY(upload(c.d_full_mode_ids[m], c.full_mode_ids[m].data(), c.full_mode_ids[m].size()));
-    }
-    VG_TRY(upload(c.d_slot_ident, slot_ident.data(), slot_ident.size()));
-    VG_TRY(upload(c.d_tabslot_ident, slot_ident.data(), slot_ident.size()));
-    VG_TRY(upload(c.d_slot_split, slot_split.data(), slot_split.size()));
-    VG_TRY(upload(c.d_tabslot_split, tabslot_split.data(), tabslot_split.size()));
-    if (!c.mom_ids.empty()) VG_TRY(upload(c.d_mom_ids, c.mom_ids.data(), c.mom_ids.size()));
+    VG_TRY(build_layouts(plan, c));
     std::vector<const double*> cptrs;
     for (auto& b : c.coords) cptrs.push_back(b.as<double>());
     VG_TRY(upload(c.d_coord_ptrs, cptrs.data(), cptrs.size()));
@@ -525,15 +575,16 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
       }
     }
     // moment form: static knot tables K[j][m] = (Hankel + spline operator)(pk_lin * moment m)
-    if (!c.mom_ids.empty()) {
+    EvalLayout& LM = c.lay[LAY_MOM];
+    if (!LM.mom_ids.empty()) {
       const Hankel& h = *plan->hankels[c.hankel_id];
       const int rowT = 2 * h.n_out_pad;
-      const int rows = (int)c.mom_ids.size() * vg::MOM_MAX;
+      const int rows = (int)LM.mom_ids.size() * vg::MOM_MAX;
       DevBuf mom;
       VG_TRY(mom.alloc((size_t)rows * plan->n_ell * plan->nk_pad * 8));
       VG_TRY(c.d_mom_ktab.alloc((size_t)rows * plan->n_ell * rowT * 8));
-      dim3 mgrid(vg_cdiv(plan->nk, 128), (unsigned)c.mom_ids.size());
-      vg::moment_grid_kernel<<<mgrid, 128, 0, st>>>(g, c.d_evals.as<vg_eval_desc>(), c.d_mom_ids.as<int>(),
+      dim3 mgrid(vg_cdiv(plan->nk, 128), (unsigned)LM.mom_ids.size());
+      vg::moment_grid_kernel<<<mgrid, 128, 0, st>>>(g, c.d_evals.as<vg_eval_desc>(), LM.d_mom_ids.as<int>(),
                                                   mom.as<double>());
       VG_LAUNCHED();
       VG_TRY(gemm_auto(plan, mom.as<double>(), (long long)plan->n_ell * plan->nk_pad, h.op.as<double>(),
@@ -541,12 +592,14 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
                        plan->nk_pad, plan->n_ell, plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
       VG_CUDA_CHECK(cudaStreamSynchronize(st));   // `mom` is released at the end of this scope
     }
-    // metal matrices, concatenated along K: mcat[i][c*ld_model + j] = M_c[i][j]
-    if (c.metal_dense && c.n_metal > 0) {
-      const size_t ldk = (size_t)c.n_metal * c.ld_model;
+    // metal matrices of the hot evaluations, concatenated along K: mcat[i][c*ld_model + j] = M_c[i][j]
+    if (c.metal_dense && LM.n_metal > 0) {
+      const size_t ldk = (size_t)LM.n_metal * c.ld_model;
       VG_TRY(c.d_mcat.alloc((size_t)c.n_model * ldk * 8));
       std::vector<double> eye;
       for (int s = 0; s < c.n_metal; ++s) {
+        const int col = LM.metal_map[s];
+        if (col < 0) continue;
         const double* src;
         if (s < (int)c.metal_host.size() && !c.metal_host[s].empty()) {
           src = c.metal_host[s].data();
@@ -557,12 +610,10 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
           }
           src = eye.data();
         }
-        VG_CUDA_CHECK(cudaMemcpy2D(c.d_mcat.as<double>() + (size_t)s * c.ld_model, ldk * 8, src,
+        VG_CUDA_CHECK(cudaMemcpy2D(c.d_mcat.as<double>() + (size_t)col * c.ld_model, ldk * 8, src,
                                    (size_t)c.n_model * 8, (size_t)c.n_model * 8, c.n_model,
                                    cudaMemcpyHostToDevice));
       }
-      c.metal_host.clear();
-      c.metal_host.shrink_to_fit();
     }
     // masked rows of the distortion matrix (chi2 needs only the bins kept by the cuts)
     if (c.has_dmat && c.n_mask > 0) {
@@ -575,6 +626,11 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
   }
   VG_CUDA_CHECK(cudaStreamSynchronize(st));
   VG_CUDA_CHECK(cudaMemcpy(&plan->static_bad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
+  for (auto& cp : plan->corrs) {
+    VG_TRY(freeze_metal_terms(plan, *cp, st));
+    cp->metal_host.clear();
+    cp->metal_host.shrink_to_fit();
+  }
   if (plan->has_global) {
     int tot = 0;
     for (auto& cp : plan->corrs) tot += cp->n_mask;
@@ -591,7 +647,7 @@ int64_t vg_plan_device_bytes(const vg_plan* plan) {
   for (auto& h : plan->hankels) n += h->xk.bytes + h->op.bytes;
   for (auto& cp : plan->corrs) {
     const Corr& c = *cp;
-    n += c.d_mcat.bytes + c.d_dmat.bytes + c.d_dmat_masked.bytes + c.d_invcov.bytes + c.d_mom_ktab.bytes;
+    n += c.d_mcat.bytes + c.d_dmat.bytes + c.d_dmat_masked.bytes + c.d_invcov.bytes + c.d_mom_ktab.bytes + c.d_frozen.bytes;
     for (auto& b : c.coords) n += b.bytes;
   }
   n += plan->d_global_invcov.bytes;
@@ -717,51 +773,88 @@ vg::BroadbandDev bb_dev(const Corr& c) {
   return bb;
 }
 
+// Dispatch of the templated fast pk_ell kernels: vmode 0..3 (PK_V_*), kind 0..4
+template <int VM, int KD>
+int launch_pk_fast_one(dim3 grid, dim3 block, size_t smem, cudaStream_t st, const vg::PkGridDev& g,
+                       const vg_eval_desc* ev, int E, const int* ids, const int* out_slot, int n_slots,
+                       const double* pf, int npf, int B, double* out) {
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::pk_ell_fast_kernel<2, VM, KD>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  vg::pk_ell_fast_kernel<2, VM, KD><<<grid, block, smem, st>>>(g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+  return VG_OK;
+}
+template <int VM>
+int launch_pk_fast_kind(int kind, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const vg::PkGridDev& g,
+                        const vg_eval_desc* ev, int E, const int* ids, const int* out_slot, int n_slots,
+                        const double* pf, int npf, int B, double* out) {
+  switch (kind) {
+    case 0: return launch_pk_fast_one<VM, 0>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    case 1: return launch_pk_fast_one<VM, 1>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    case 2: return launch_pk_fast_one<VM, 2>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    case 3: return launch_pk_fast_one<VM, 3>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    default: return launch_pk_fast_one<VM, 4>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+  }
+}
+int launch_pk_fast(int vmode, int kind, dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                   const vg::PkGridDev& g, const vg_eval_desc* ev, int E, const int* ids, const int* out_slot,
+                   int n_slots, const double* pf, int npf, int B, double* out) {
+  switch (vmode) {
+    case 0: return launch_pk_fast_kind<0>(kind, grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    case 1: return launch_pk_fast_kind<1>(kind, grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    case 2: return launch_pk_fast_kind<2>(kind, grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    default: return launch_pk_fast_kind<3>(kind, grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+  }
+}
+
 // Stages K1..K3 + metals + pre-distortion assembly of one correlation: leaves
 // x[Bc][ld_model] in plan->w_x.  `upto` stops early for the per-stage taps.
-int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaStream_t st, int upto = 99) {
+int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaStream_t st, int upto = 99,
+                   int layout = -1, int unit_bias = 0) {
   const Hankel& h = *plan->hankels[c.hankel_id];
   const int E = (int)c.evals.size();
   vg::PkGridDev g = plan->grid_dev();
   // the per-stage taps (upto <= 2) expose every evaluation's multipoles / knot tables, so
   // they run all evaluations through the per-point pass
-  const bool split = plan->use_moments && upto > 2 && !c.mom_ids.empty();
-  const int Ef = split ? c.n_full : E;
-  const int Em = split ? (int)c.mom_ids.size() : 0;
+  if (layout < 0) layout = upto <= 2 ? LAY_ALL : (plan->use_moments ? LAY_MOM : LAY_FULL);
+  const EvalLayout& L = c.lay[layout];
+  const int Ef = L.n_full;
+  const int Em = (int)L.mom_ids.size();
   const int rowT = 2 * h.n_out_pad;
   const long long row_len = (long long)plan->n_ell * rowT;
   double* tables_full = plan->w_tables.as<double>();
   double* tables_mom = tables_full + Bc * Ef * row_len;
-  const int* out_slot = split ? c.d_slot_split.as<int>() : c.d_slot_ident.as<int>();
+  const int* out_slot = L.d_slot.as<int>();
   if (Ef > 0) {  // K1 + K2a
     ProfScope prof(plan, PROF_PK, st);
     const vg_eval_desc* ev = c.d_evals.as<vg_eval_desc>();
     double* out = plan->w_pkell.as<double>();
     const double* pf = plan->w_pfull.as<double>();
+    // fast kernels: fixed CTA shape (2 mu groups x 4 vector groups x 2 vectors)
+    const bool fast_ok = Bc >= 8 && plan->nmu % (vg::PK_FAST_MG * vg::PK_FAST_U) == 0;
     const int NB = Bc >= 2 ? 2 : 1;
     const int groups = vg_cdiv(Bc, NB);
     const int EG = groups >= 4 ? 4 : (groups >= 2 ? 2 : 1);
     const int MG = vg::PK_GROUPS / EG;
-    dim3 block(vg::PK_KLANES, MG, EG);
-    const bool fast_ok = NB == 2 && plan->nmu % (MG * vg::PK_FAST_U) == 0;
-    for (int m = 0; m < 13; ++m) {
-      const std::vector<int>& class_ids = split ? c.full_mode_ids[m] : c.mode_ids[m];
+    const size_t fast_smem = vg::pk_fast_smem_bytes(plan->nmu);
+    for (int m = 0; m < PK_NCLS; ++m) {
+      const std::vector<int>& class_ids = L.class_ids[m];
       if (class_ids.empty()) continue;
-      dim3 grid(vg_cdiv(Bc, NB * EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)class_ids.size());
-      const int* ids = split ? c.d_full_mode_ids[m].as<int>() : c.d_mode_ids[m].as<int>();
-#define VG_PK_FAST(MODEV, KINDV) \
-      vg::pk_ell_fast_kernel<2, MODEV, KINDV><<<grid, block, 0, st>>>(g, ev, E, ids, out_slot, Ef, pf, plan->npf, (int)Bc, out)
-#define VG_PK_GEN(NBV, MODEV) \
-      vg::pk_ell_kernel<NBV, MODEV><<<grid, block, 0, st>>>(g, ev, E, ids, out_slot, Ef, pf, plan->npf, (int)Bc, out, status_dev)
-      if (m < 10 && fast_ok) {
-        switch (m) {
-          case 0: VG_PK_FAST(0, 0); break; case 1: VG_PK_FAST(0, 1); break; case 2: VG_PK_FAST(0, 2); break;
-          case 3: VG_PK_FAST(0, 3); break; case 4: VG_PK_FAST(0, 4); break; case 5: VG_PK_FAST(1, 0); break;
-          case 6: VG_PK_FAST(1, 1); break; case 7: VG_PK_FAST(1, 2); break; case 8: VG_PK_FAST(1, 3); break;
-          default: VG_PK_FAST(1, 4); break;
-        }
+      const int* ids = L.d_class_ids[m].as<int>();
+      if (m < 20 && fast_ok) {
+        dim3 block(vg::PK_KLANES, vg::PK_FAST_MG, vg::PK_FAST_EG);
+        dim3 grid(vg_cdiv(Bc, 2 * vg::PK_FAST_EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)class_ids.size());
+        VG_TRY(launch_pk_fast(m / 5, m % 5, grid, block, fast_smem, st, g, ev, E, ids, out_slot, Ef, pf,
+                              plan->npf, (int)Bc, out));
       } else {
-        const int mode = m < 10 ? m / 5 : m - 10;
+        dim3 block(vg::PK_KLANES, MG, EG);
+        dim3 grid(vg_cdiv(Bc, NB * EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)class_ids.size());
+        const int mode = m < 20 ? (m < 5 ? vg::PK_MODE_STATIC : vg::PK_MODE_VELO) : m - 20;
+#define VG_PK_GEN(NBV, MODEV) \
+        vg::pk_ell_kernel<NBV, MODEV><<<grid, block, 0, st>>>(g, ev, E, ids, out_slot, Ef, pf, plan->npf, (int)Bc, out, status_dev)
         if (NB == 2) {
           if (mode == 0) VG_PK_GEN(2, vg::PK_MODE_STATIC);
           else if (mode == 1) VG_PK_GEN(2, vg::PK_MODE_VELO);
@@ -771,9 +864,8 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
           else if (mode == 1) VG_PK_GEN(1, vg::PK_MODE_VELO);
           else VG_PK_GEN(1, vg::PK_MODE_GENERIC);
         }
-      }
-#undef VG_PK_FAST
 #undef VG_PK_GEN
+      }
       VG_LAUNCHED();
     }
   }
@@ -788,7 +880,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   if (Em > 0) {  // moment form: knot tables as a 3/9-term combination of static tables
     ProfScope prof(plan, PROF_MOMENT, st);
     dim3 grid(vg_cdiv(row_len, 256 * vg::MOM_XPT), (unsigned)Em, (unsigned)vg_cdiv(Bc, vg::MOM_NB));
-    vg::moment_tables_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), c.d_mom_ids.as<int>(), Em,
+    vg::moment_tables_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_mom_ids.as<int>(), Em,
                                                   plan->w_pfull.as<double>(), plan->npf, (int)Bc,
                                                   c.d_mom_ktab.as<double>(), (int)row_len, tables_mom);
     VG_LAUNCHED();
@@ -796,6 +888,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   if (upto <= 2) return VG_OK;
   {  // K3
     ProfScope prof(plan, PROF_XI, st);
+    const int n_gather = (int)L.gather_ids.size();
     vg::XiArgs a{};
     a.h.n_ell = h.n_ell; a.h.n_out = h.n_out; a.h.n_out_pad = h.n_out_pad; a.h.bounds_error = h.bounds_error;
     for (int l = 0; l < vg::PK_MAX_ELL; ++l) a.h.ells[l] = h.ells[l];
@@ -804,18 +897,21 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     a.pfull = plan->w_pfull.as<double>(); a.npf = plan->npf; a.B = (int)Bc;
     a.tables = tables_full; a.n_full = Ef;
     a.tables_mom = tables_mom; a.n_mom = Em;
-    a.tab_slot = split ? c.d_tabslot_split.as<int>() : c.d_tabslot_ident.as<int>();
+    a.tab_slot = L.d_tabslot.as<int>();
+    a.gather_ids = L.d_gather_ids.as<int>();
+    a.metal_map = L.d_metal_map.as<int>();
+    a.unit_bias = unit_bias;
     a.coords = c.d_coord_ptrs.as<const double*>();
     a.opz_eff2 = c.d_opz_eff2.as<double>();
     a.n_model = c.n_model;
     for (int i = 0; i < 12; ++i) { a.sx.n[i] = c.sx_n[i]; a.sx.tab[i] = c.d_sx[i].as<double>(); }
     a.uv_tau = plan->d_uv_tau.as<double>(); a.uv_a = plan->d_uv_a.as<double>(); a.uv_n = plan->uv_n;
     a.core = plan->w_core.as<double>(); a.xmet = plan->w_xmet.as<double>();
-    a.ld_model = c.ld_model; a.n_metal = std::max(c.n_metal, 1);
+    a.ld_model = c.ld_model; a.n_metal = std::max(L.n_metal, 1);
     a.status = status_dev;
     long long ctas_wanted = 4LL * NUM_SMS;
     int chunks = (int)std::max<long long>(1, std::min<long long>(vg_cdiv(c.ld_model, 256),
-                                                             (ctas_wanted + Bc * E - 1) / (Bc * E)));
+                                                             (ctas_wanted + Bc * n_gather - 1) / (Bc * n_gather)));
     a.bins_per_cta = vg_cdiv(c.ld_model, chunks);
     const size_t smem = (size_t)h.n_ell * rowT * 8;
     static size_t smem_set = 0;
@@ -823,22 +919,22 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
       VG_CUDA_CHECK(cudaFuncSetAttribute(vg::xi_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       smem_set = smem;
     }
-    dim3 grid(vg_cdiv(c.ld_model, a.bins_per_cta), E, (unsigned)Bc);
+    dim3 grid(vg_cdiv(c.ld_model, a.bins_per_cta), n_gather, (unsigned)Bc);
     vg::xi_gather_kernel<<<grid, 256, smem, st>>>(a);
     VG_LAUNCHED();
   }
   if (upto <= 3) return VG_OK;
   // metals: sum_c w_c M_c xi_c  (vega/metals.py:258-367)
   const double* met = nullptr;
-  if (c.n_metal > 0) {
+  if (L.n_metal > 0) {
     ProfScope prof(plan, c.metal_dense ? PROF_METAL : PROF_ELEM, st);
     if (c.metal_dense) {
-      const long long ldk = (long long)c.n_metal * c.ld_model;
+      const long long ldk = (long long)L.n_metal * c.ld_model;
       VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, c.d_mcat.as<double>(), ldk,
                        plan->w_met.as<double>(), c.ld_model, (int)Bc, c.n_model, (int)ldk, 1, 0, 0, 0, st));
     } else {
       const long long n = Bc * c.ld_model;
-      vg::metal_sum_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->w_xmet.as<double>(), c.n_metal, c.ld_model,
+      vg::metal_sum_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->w_xmet.as<double>(), L.n_metal, c.ld_model,
                                                          c.n_model, Bc, plan->w_met.as<double>());
       VG_LAUNCHED();
     }
@@ -853,6 +949,8 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   ca.pfull = plan->w_pfull.as<double>(); ca.npf = plan->npf;
   ca.n = c.n_model; ca.ld = c.ld_model; ca.B = Bc;
   ca.x = plan->w_x.as<double>();
+  ca.frozen = c.d_frozen.as<double>(); ca.n_frozen = (int)c.frozen_ids.size();
+  ca.frozen_ids = c.d_frozen_ids.as<int>(); ca.evals = c.d_evals.as<vg_eval_desc>();
   const long long n = Bc * c.ld_model;
   ProfScope prof(plan, PROF_ELEM, st);
   vg::combine_pre_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(ca);
@@ -863,6 +961,40 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
 }  // namespace
 
 namespace {
+
+// fast_metals metal x metal terms (vega/metals.py:144-169): M_c xi_c evaluated ONCE at the
+// plan's base parameters (the reference caches the first evaluation forever), stored without
+// the bias product, which the hot path applies per vector.
+int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st) {
+  if (c.frozen_ids.empty()) return VG_OK;
+  VG_TRY(ensure_workspace(plan, 1));
+  VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_pfull.p, plan->d_base.p, (size_t)plan->npf * 8,
+                                cudaMemcpyDeviceToDevice, st));
+  VG_CUDA_CHECK(cudaMemsetAsync(plan->w_status.p, 0, 4, st));
+  VG_TRY(run_corr_front(plan, c, 1, plan->w_status.as<int>(), st, 3, LAY_ALL, 1));
+  const EvalLayout& L = c.lay[LAY_ALL];
+  const int nf = (int)c.frozen_ids.size();
+  VG_TRY(c.d_frozen.alloc((size_t)nf * c.ld_model * 8));
+  DevBuf mat;
+  for (int f = 0; f < nf; ++f) {
+    const int slot = c.evals[c.frozen_ids[f]].out_slot - 2;
+    const double* xi = plan->w_xmet.as<double>() + (size_t)L.metal_map[slot] * c.ld_model;
+    double* dst = c.d_frozen.as<double>() + (size_t)f * c.ld_model;
+    if (c.metal_dense && slot < (int)c.metal_host.size() && !c.metal_host[slot].empty()) {
+      VG_TRY(upload_padded(mat, c.metal_host[slot].data(), c.n_model, c.n_model, c.ld_model));
+      VG_TRY(gemm_auto(plan, xi, c.ld_model, mat.as<double>(), c.ld_model, dst, c.ld_model, 1, c.n_model,
+                       c.ld_model, 1, 0, 0, 0, st));
+      VG_CUDA_CHECK(cudaStreamSynchronize(st));   // `mat` is re-used by the next term
+    } else {
+      VG_CUDA_CHECK(cudaMemcpyAsync(dst, xi, (size_t)c.ld_model * 8, cudaMemcpyDeviceToDevice, st));
+    }
+  }
+  int bad = 0;
+  VG_CUDA_CHECK(cudaMemcpyAsync(&bad, plan->w_status.p, 4, cudaMemcpyDeviceToHost, st));
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  plan->static_bad |= bad;
+  return VG_OK;
+}
 
 // Distortion matrix + post-distortion broadband of one correlation.
 //   data == false: model rows for ALL distorted bins -> out[Bc][ldo = ld_dist]
@@ -1033,7 +1165,7 @@ int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, doubl
 
 int vg_corr_n_moment(const vg_plan* plan, int32_t corr) {
   if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments) return 0;
-  return (int)plan->corrs[corr]->mom_ids.size();
+  return (int)plan->corrs[corr]->lay[LAY_MOM].mom_ids.size();
 }
 
 int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }
@@ -1069,7 +1201,7 @@ int64_t vg_stage_size(const vg_plan* plan, int32_t corr, int32_t stage) {
     case 0: return (int64_t)plan->nmu * plan->nk;
     case 1: return E * plan->n_ell * plan->nk_pad;
     case 2: return E * plan->n_ell * 2 * h.n_out_pad;
-    case 3: return (int64_t)(2 + std::max(c.n_metal, 1)) * c.ld_model;
+    case 3: return (int64_t)(2 + std::max(c.lay[LAY_MOM].n_metal, 1)) * c.ld_model;
     case 4: return c.ld_model;
     default: return -1;
   }
@@ -1095,7 +1227,7 @@ int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
     return VG_OK;
   }
   VG_TRY(run_corr_front(plan, c, B, status_dev, st, stage == 4 ? 99 : stage));
-  const int nm = std::max(c.n_metal, 1);
+  const int nm = std::max(c.lay[LAY_MOM].n_metal, 1);
   if (stage == 1) {
     VG_CUDA_CHECK(cudaMemcpyAsync(out_dev, plan->w_pkell.p, (size_t)B * per * 8, cudaMemcpyDeviceToDevice, st));
   } else if (stage == 2) {

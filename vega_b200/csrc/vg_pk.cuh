@@ -196,16 +196,6 @@ __device__ __forceinline__ double kaiser_eval(const vg_eval_desc& d, const Kaise
   return t0 * t1;
 }
 
-// 1/sqrt(a) for finite a >= 1 (the Lorentzian velocity dispersion 1/sqrt(1 + (k_par sigma)^2),
-// power_spectrum.py:613-636): single-precision MUFU seed (relative error e ~ 2^-22) and one
-// third-order correction y (1 + e/2 + 3 e^2/8), leaving O(e^3) ~ 2^-64 -- 5 FP64 operations
-// instead of the ~15 of the general-purpose rsqrt() with its special-case handling.
-__device__ __forceinline__ double rsqrt_ge1(double a) {
-  const double y = (double)rsqrtf((float)a);
-  const double e = fma(-a * y, y, 1.0);
-  return fma(y, e * fma(0.375, e, 0.5), y);
-}
-
 constexpr int PK_KLANES = 32, PK_GROUPS = 8;   // CTA = 32 k lanes x (MG mu groups x EG vector groups)
 constexpr int PK_UNROLL = 4;                   // mu rows whose grid loads are issued together
 
@@ -339,7 +329,7 @@ pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
             if (d.idx_velo[t] < 0) continue;
             const double x = kpar * sv[e][t];
             if (velo_kind == 1) P *= exp(-0.25 * x * x);
-            else P *= rsqrt_ge1(fma(x, x, 1.0));
+            else P *= rsqrt(fma(x, x, 1.0));
           }
         } else if (MODE == PK_MODE_GENERIC) {
           P *= pk_factors(dyn_mask, d, pp[e], k, mu, pk_fid_k, &bad[e]);
@@ -378,25 +368,52 @@ pk_ell_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
 }
 
 // ---- fast path of the fused kernel ------------------------------------------------------
-// Same mapping as pk_ell_kernel, but every option that the generic kernel tests per grid
-// point is a template parameter, the mu loop has an exact trip count (nmu % (MG*5) == 0) and
-// all table reads of a 5-row batch are issued before the arithmetic.  KIND:
+// Same thread mapping as pk_ell_kernel with a fixed CTA shape (32 k lanes x 2 mu groups x 4
+// vector groups, NB = 2 vectors per thread), but every option the generic kernel tests per
+// grid point is a template parameter and the inner loop is branch free:
+//  * mu and the four Legendre weights of every mu row sit in shared memory (warp-broadcast
+//    LDS with immediate offsets instead of per-row global loads and 64-bit address math);
+//  * the loop over mu rows has an exact trip count (nmu % 10 == 0) and the grid loads of 5
+//    rows are issued before their arithmetic;
+//  * velocity dispersion is ONE special-function evaluation per point and vector:
+//    Lorentzians of both tracers as rsqrt((1 + x0^2)(1 + x1^2)), Gaussians as exp(g mu^2).
+// KIND:
 //   0 no HCD, same tracer      t^2            1 no HCD, two tracers      tA * tB
 //   2 HCD grid, same tracer    tH^2           3 HCD grid on one tracer   tH * tP
 //   4 as 3 with the Kaiser term of the HCD tracer divided by its effective bias
 //     (fast_metals, power_spectrum.py:219-220 with the effective bias of :305-307)
-constexpr int PK_FAST_U = 5;
+// VMODE: 0 no per-vector factor, 1 Lorentzian on one tracer, 2 Lorentzian on both, 3 Gaussian
+constexpr int PK_FAST_U = 5, PK_FAST_MG = 2, PK_FAST_EG = 4;
+enum { PK_V_NONE = 0, PK_V_LOR1 = 1, PK_V_LOR2 = 2, PK_V_GAUSS = 3 };
 
-template <int NB, int MODE, int KIND>
+// 1/sqrt(a) for finite a >= 1: MUFU.RSQ64H seed on the high word (relative error e < 2^-19)
+// and one third-order correction y (1 + e/2 + 3 e^2/8), leaving O(e^3) < 2^-58; returned as
+// (y, q) with 1/sqrt(a) = y + y q so that the caller folds y into its own product.
+__device__ __forceinline__ void rsqrt_ge1_parts(double a, double& y, double& q) {
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  const double e = fma(-a * y, y, 1.0);
+  q = e * fma(0.375, e, 0.5);
+}
+
+inline size_t pk_fast_smem_bytes(int nmu) {
+  return (size_t)nmu * 5 * 8 + (size_t)PK_GROUPS * 2 * PK_MAX_ELL * (PK_KLANES + 1) * 8;
+}
+
+template <int NB, int VMODE, int KIND>
 __global__ void __launch_bounds__(PK_KLANES * PK_GROUPS, 2)
 pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
                    const int* __restrict__ eval_ids, const int* __restrict__ out_slot, int n_slots,
                    const double* __restrict__ pfull, int npf, int B,
                    double* __restrict__ out) {
+  constexpr int MG = PK_FAST_MG, EG = PK_FAST_EG, U = PK_FAST_U;
+  extern __shared__ __align__(16) double pk_sm[];
   __shared__ vg_eval_desc d;
-  __shared__ double red[PK_GROUPS][NB * PK_MAX_ELL][PK_KLANES + 1];
+  const int nmu = g.nmu;
+  double2* wt = reinterpret_cast<double2*>(pk_sm);          // [nmu][2]: (w0,w1), (w2,w3)
+  double* mus = pk_sm + 4 * nmu;                            // [nmu]
+  typedef double RedRow[NB * PK_MAX_ELL][PK_KLANES + 1];
+  RedRow* red = reinterpret_cast<RedRow*>(pk_sm + 5 * nmu); // [PK_GROUPS]
   const int tx = threadIdx.x, mg = threadIdx.y, eg = threadIdx.z;
-  const int MG = blockDim.y, EG = blockDim.z;
   const int tid = (eg * MG + mg) * PK_KLANES + tx;
   const int eval = eval_ids[blockIdx.z];
   const int slot = out_slot[eval];
@@ -404,6 +421,11 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
     const int* src = reinterpret_cast<const int*>(evals + eval);
     int* dst = reinterpret_cast<int*>(&d);
     for (int i = tid; i < (int)(sizeof(vg_eval_desc) / 4); i += PK_KLANES * PK_GROUPS) dst[i] = src[i];
+    for (int i = tid; i < nmu; i += PK_KLANES * PK_GROUPS) {
+      wt[2 * i] = make_double2(g.wleg[i], g.wleg[nmu + i]);
+      wt[2 * i + 1] = make_double2(g.wleg[2 * nmu + i], g.wleg[3 * nmu + i]);
+      mus[i] = g.mu[i];
+    }
   }
   __syncthreads();
   const int ik_raw = blockIdx.y * PK_KLANES + tx;
@@ -415,25 +437,28 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
   const int tH = (KIND >= 3 && !d.hcd_on[0]) ? 1 : 0;   // tracer carrying the HCD term
   const int tP = 1 - tH;
 
-  double aH0[NB], aH1[NB], hH0[NB], hH1[NB], aP0[NB], aP1[NB], sv0[NB], sv1[NB];
+  double aH0[NB], aH1[NB], hH0[NB], hH1[NB], aP0[NB], aP1[NB], c0[NB], c1[NB];
 #pragma unroll
   for (int e = 0; e < NB; ++e) {
     const double* p = pfull + (long long)min(b0 + e, B - 1) * npf;
     const KaiserCoef kc = kaiser_setup(d, p, k);
-    aH0[e] = kc.a0[tH]; aH1[e] = kc.a1[tH]; hH0[e] = kc.h0[tH]; hH1[e] = kc.h1[tH];
-    aP0[e] = kc.a0[tP]; aP1[e] = kc.a1[tP];
-    sv0[e] = (MODE == PK_MODE_VELO && d.idx_velo[0] >= 0) ? k * p[d.idx_velo[0]] : 0.0;
-    sv1[e] = (MODE == PK_MODE_VELO && d.idx_velo[1] >= 0) ? k * p[d.idx_velo[1]] : 0.0;
+    aH0[e] = tH ? kc.a0[1] : kc.a0[0]; aH1[e] = tH ? kc.a1[1] : kc.a1[0];
+    hH0[e] = tH ? kc.h0[1] : kc.h0[0]; hH1[e] = tH ? kc.h1[1] : kc.h1[0];
+    aP0[e] = tP ? kc.a0[1] : kc.a0[0]; aP1[e] = tP ? kc.a1[1] : kc.a1[0];
+    // (k sigma_t)^2 per tracer; a Gaussian pair collapses to one exponent -(x0^2 + x1^2)/4
+    const double s0 = (VMODE != PK_V_NONE && d.idx_velo[0] >= 0) ? k * p[d.idx_velo[0]] : 0.0;
+    const double s1 = (VMODE != PK_V_NONE && d.idx_velo[1] >= 0) ? k * p[d.idx_velo[1]] : 0.0;
+    if (VMODE == PK_V_GAUSS) { c0[e] = -0.25 * (s0 * s0 + s1 * s1); c1[e] = 0.0; }
+    else if (VMODE == PK_V_LOR1) { c0[e] = s0 * s0 + s1 * s1; c1[e] = 0.0; }   // one of them is 0
+    else { c0[e] = s0 * s0; c1[e] = s1 * s1; }
   }
-  const bool velo0 = MODE == PK_MODE_VELO && d.idx_velo[0] >= 0;
-  const bool velo1 = MODE == PK_MODE_VELO && d.idx_velo[1] >= 0;
-  const bool velo_gauss = d.velo_kind == 1;
-  const long long row = (long long)MG * g.nk;
-  const double* S = d.static_grid >= 0 ? g.grids[d.static_grid] + (long long)mg * g.nk + ik : nullptr;
-  const double* Fg = HCD ? g.grids[d.hcd_grid] + (long long)mg * g.nk + ik : nullptr;
-  const double* mup = g.mu + mg;
-  const double* wp = g.wleg + mg;
-  const int nmu = g.nmu;
+  const bool has_s = d.static_grid >= 0;
+  const double* __restrict__ S = has_s ? g.grids[d.static_grid] : g.k;
+  const double* __restrict__ Fg = HCD ? g.grids[d.hcd_grid] : g.k;
+  const unsigned rs = (unsigned)(MG * g.nk);      // elements between the rows of one thread
+  unsigned off = (unsigned)(mg * g.nk + ik);
+  const double2* wrow = wt + 2 * mg;
+  const double* mrow = mus + mg;
 
   double acc[NB][PK_MAX_ELL];
 #pragma unroll
@@ -441,24 +466,20 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
 #pragma unroll
     for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = 0.0;
 
-  const int n_batches = nmu / (MG * PK_FAST_U);
+  const int n_batches = nmu / (MG * U);
   for (int jb = 0; jb < n_batches; ++jb) {
-    double s[PK_FAST_U], f[PK_FAST_U], mu[PK_FAST_U];
+    double s[U], f[U];
 #pragma unroll
-    for (int u = 0; u < PK_FAST_U; ++u) {   // the L2-latency loads of the whole batch first
-      s[u] = S ? __ldg(S + u * row) : 1.0;
-      f[u] = HCD ? __ldg(Fg + u * row) : 0.0;
-      mu[u] = __ldg(mup + u * MG);
+    for (int u = 0; u < U; ++u) {   // the L2-latency loads of the whole batch first
+      s[u] = has_s ? __ldg(S + (off + u * rs)) : 1.0;
+      f[u] = HCD ? __ldg(Fg + (off + u * rs)) : 0.0;
     }
-    if (S) S += PK_FAST_U * row;
-    if (HCD) Fg += PK_FAST_U * row;
-    mup += PK_FAST_U * MG;
+    off += U * rs;
 #pragma unroll
-    for (int u = 0; u < PK_FAST_U; ++u) {
-      const double mu2 = mu[u] * mu[u];
-      double w[PK_MAX_ELL];                   // warp-uniform, L1-resident
-#pragma unroll
-      for (int l = 0; l < PK_MAX_ELL; ++l) w[l] = __ldg(wp + l * nmu + u * MG);
+    for (int u = 0; u < U; ++u) {
+      const double mu = mrow[u * MG];
+      const double2 wa = wrow[u * MG * 2], wb = wrow[u * MG * 2 + 1];
+      const double mu2 = mu * mu;
 #pragma unroll
       for (int e = 0; e < NB; ++e) {
         double t;
@@ -469,17 +490,25 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
         } else {
           t = fma(aH1[e], mu2, aH0[e]);
         }
-        double P = TWO ? t * fma(aP1[e], mu2, aP0[e]) : t * t;
-        P *= s[u];
-        if (MODE == PK_MODE_VELO) {
-          if (velo0) { const double x = sv0[e] * mu[u]; P *= velo_gauss ? exp(-0.25 * x * x) : rsqrt_ge1(fma(x, x, 1.0)); }
-          if (velo1) { const double x = sv1[e] * mu[u]; P *= velo_gauss ? exp(-0.25 * x * x) : rsqrt_ge1(fma(x, x, 1.0)); }
+        double P = (TWO ? t * fma(aP1[e], mu2, aP0[e]) : t * t) * s[u];
+        if (VMODE == PK_V_LOR1 || VMODE == PK_V_LOR2) {
+          double a = fma(c0[e], mu2, 1.0);
+          if (VMODE == PK_V_LOR2) a *= fma(c1[e], mu2, 1.0);
+          double y, q;
+          rsqrt_ge1_parts(a, y, q);
+          const double Py = P * y;
+          P = fma(Py, q, Py);
+        } else if (VMODE == PK_V_GAUSS) {
+          P *= exp(c0[e] * mu2);
         }
-#pragma unroll
-        for (int l = 0; l < PK_MAX_ELL; ++l) acc[e][l] = fma(w[l], P, acc[e][l]);
+        acc[e][0] = fma(wa.x, P, acc[e][0]);
+        acc[e][1] = fma(wa.y, P, acc[e][1]);
+        acc[e][2] = fma(wb.x, P, acc[e][2]);
+        acc[e][3] = fma(wb.y, P, acc[e][3]);
       }
     }
-    wp += PK_FAST_U * MG;
+    wrow += U * MG * 2;
+    mrow += U * MG;
   }
   for (int turn = 0; turn < EG; ++turn) {
     __syncthreads();

@@ -73,7 +73,19 @@ struct CombineArgs {
   const double* pfull; int npf;
   int n, ld; long long B;
   double* x;               // [B][ld]
+  // fast_metals metal x metal terms: sum_f b1*b2(*extra)(theta) * frozen[f][i]
+  const double* frozen; int n_frozen; const int* frozen_ids; const vg_eval_desc* evals;
 };
+
+// weight of a metal term from its bias parameters (vega/metals.py:289-313)
+__device__ __forceinline__ double metal_bias_weight(const vg_eval_desc& d, const double* p) {
+  double b1, be1, b2, be2;
+  tracer_bias_beta(d, p, 0, b1, be1);
+  tracer_bias_beta(d, p, 1, b2, be2);
+  double w = b1 * b2;
+  if (d.idx_weight_extra >= 0) w *= p[d.idx_weight_extra];
+  return w;
+}
 
 __global__ void combine_pre_kernel(CombineArgs a) {
   long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -85,6 +97,8 @@ __global__ void combine_pre_kernel(CombineArgs a) {
   const double amp = par(p, a.idx_bao_amp, 1.0);
   double v = amp * a.core[idx] + a.core[a.B * a.ld + idx];
   if (a.met) v += a.met[idx];
+  for (int f = 0; f < a.n_frozen; ++f)
+    v = fma(metal_bias_weight(a.evals[a.frozen_ids[f]], p), a.frozen[(long long)f * a.ld + i], v);
   if (a.inst) v += par(p, a.idx_inst_amp, a.inst_amp_default) * a.inst[i];
   if (a.bb.n_terms) {
     v *= bb_eval(a.bb, 0, p, i, a.n);

@@ -39,6 +39,10 @@ struct XiArgs {
   const double* tables; int n_full;
   const double* tables_mom; int n_mom;
   const int* tab_slot;
+  const int* gather_ids;   // evaluations gathered by this launch (grid.y entries)
+  const int* metal_map;    // metal slot (out_slot - 2) -> column block of xmet
+  int unit_bias;           // 1: leave b1*b2 / extra bias out of the weight (finalize pass of the
+                           //    frozen fast_metals terms)
   const double* const* coords;   // coordinate tables, each [5][n_model]
   const double* opz_eff2;  // per coordinate table: (1+z_eff)^2
   int n_model;
@@ -124,7 +128,7 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
   __shared__ __align__(8) unsigned long long bar;
   __shared__ vg_eval_desc d;
   const int tid = threadIdx.x;
-  const int e = blockIdx.y, b = blockIdx.z;
+  const int e = a.gather_ids[blockIdx.y], b = blockIdx.z;
   {
     const int* src = reinterpret_cast<const int*>(a.evals + e);
     int* dst = reinterpret_cast<int*>(&d);
@@ -164,16 +168,16 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
   const bool croom = d.zevol_kind[0] == 1 || d.zevol_kind[1] == 1;
   const int n_croom = (d.zevol_kind[0] == 1) + (d.zevol_kind[1] == 1);
   double weight = d.weight_const;
-  if (d.weight_bias) {
+  if (d.weight_bias && !a.unit_bias) {
     double b1, be1, b2, be2;
     tracer_bias_beta(d, p, 0, b1, be1);
     tracer_bias_beta(d, p, 1, b2, be2);
     weight *= b1 * b2;
   }
-  if (d.idx_weight_extra >= 0) weight *= p[d.idx_weight_extra];
+  if (d.idx_weight_extra >= 0 && !a.unit_bias) weight *= p[d.idx_weight_extra];
   double* out;
   if (d.out_slot < 2) out = a.core + ((long long)d.out_slot * a.B + b) * a.ld_model;
-  else out = a.xmet + (long long)b * a.n_metal * a.ld_model + (long long)(d.out_slot - 2) * a.ld_model;
+  else out = a.xmet + (long long)b * a.n_metal * a.ld_model + (long long)a.metal_map[d.out_slot - 2] * a.ld_model;
 
   {  // wait for the table (phase 0)
     unsigned done = 0;

@@ -488,26 +488,54 @@ class PlanBuilder:
             separate_auto = mcfg.getboolean('separate-metal-auto-biases', False)
             fast_bias = mcfg.getboolean('fast_metal_bias', True) or fast_metals or separate_auto
             single_beta = mcfg.getboolean('single-metal-beta', False)
-            if fast_metals:
-                raise NotImplementedError('fast_metals caching mode is not built yet; use the slow mode.')
             main = [item.tracer1['name'], item.tracer2['name']]
+            # fast_metals (vega/metals.py:144-207,278-336): growth_rate pinned to the fiducial value,
+            # metal x metal terms frozen at the first evaluation, metal x main terms cached on
+            # (beta1, beta2, every parameter) -- NOT on the pair.
+            pinned = {}
+            if fast_metals and 'growth_rate' in self.params and 'growth_rate' in vega.fiducial:
+                self.add_extra('growth_rate@fiducial', vega.fiducial['growth_rate'])
+                pinned['growth_rate'] = 'growth_rate@fiducial'
+            # identity of every parameter as the reference's cache key sees it: a sampled column
+            # keeps its name, a fixed one its value; single-metal-beta adds entries as the loop
+            # over the pairs advances (local_pars is mutated in place, vega/metals.py:285-293)
+            key_state = {n: (n if n in self.sampled_set else float(v)) for n, v in self.params.items()}
+            owners = {}
             for c, pair in enumerate(item.metal_correlations):
                 n1, n2 = pair
                 tr1, tr2 = item.tracer_catalog[n1], item.tracer_catalog[n2]
                 coords, mat = data.get_metal(pair)
-                name_map = {}
+                name_map = dict(pinned)
                 if single_beta:
                     for n in pair:
                         if n not in main:
                             name_map[f'beta_{n}'] = 'beta_metals'
-                info['coords'].append(self.coord_table(coords, metcfg))
+                            key_state[f'beta_{n}'] = key_state['beta_metals']
+                with_main = n1 in main or n2 in main
                 d = EvalDesc()
                 self.fill_pk(d, metcfg, tr1, tr2, item.name, False, 2, fast_bias, name_map=name_map,
                              data_binsizes=binsizes)
-                self.fill_xi(d, metcfg, tr1, tr2, False, f'{n1}x{n2}', True, name_map=name_map)
-                d.coord_set, d.out_slot = len(info['coords']) - 1, 2 + c
+                owner = None
+                if fast_metals and with_main:
+                    betas = tuple(key_state.get(name_map.get(f'beta_{n}', f'beta_{n}')) for n in pair)
+                    key = (betas, tuple(sorted(key_state.items(), key=lambda kv: kv[0])))
+                    owner = owners.get(key)
+                    if owner is None:
+                        owners[key] = (len(info['evals']), len(info['coords']), tr1, tr2, f'{n1}x{n2}',
+                                       dict(name_map))
+                if owner is not None:
+                    # cache hit: the xi of the first pair with this key (its tracers, its coordinates)
+                    # is re-used; only the bias product and the metal matrix are this pair's
+                    o_eval, o_coords, o_tr1, o_tr2, o_pair, o_map = owner
+                    self.fill_xi(d, metcfg, o_tr1, o_tr2, False, o_pair, True, name_map=o_map)
+                    d.coord_set, d.table_owner = o_coords, o_eval
+                else:
+                    info['coords'].append(self.coord_table(coords, metcfg))
+                    self.fill_xi(d, metcfg, tr1, tr2, False, f'{n1}x{n2}', True, name_map=name_map)
+                    d.coord_set = len(info['coords']) - 1
+                d.out_slot = 2 + c
                 d.weight_bias = int(fast_bias)
-                with_main = n1 in main or n2 in main
+                d.frozen = int(fast_metals and not with_main)
                 if fast_bias and not with_main and separate_auto and n1 != n2:
                     if self.col(f'bias_{n1}_{n2}') >= 0:
                         d.idx_weight_extra = self.col(f'bias_{n1}_{n2}')
