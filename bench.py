@@ -148,8 +148,10 @@ def gemm_flops(engine, B):
         item, data = info['item'], info['data']
         nm = item.model_coordinates.r_grid.size
         nmask = int(data.model_mask.sum())
-        n_eval = len(info['evals']) - engine.n_moment(ci)   # evaluations that reach the Hankel GEMM
-        n_metal = sum(m is not None for m in info['metal_mats'])
+        own = [d for d in info['evals'] if d.table_owner < 0 and not d.frozen]
+        n_eval = len(own) - engine.n_moment(ci)             # evaluations that reach the Hankel GEMM
+        # metal matrices applied per vector (fast_metals freezes the metal x metal ones)
+        n_metal = sum(m is not None and not d.frozen for m, d in zip(info['metal_mats'], info['evals'][2:]))
         out['hankel_gemm'] += 2.0 * n_ell * nk * nk * n_eval * B
         out['metal_gemm'] += 2.0 * nm * nm * n_metal * B
         if not data.distortion_is_identity:

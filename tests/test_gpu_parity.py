@@ -135,3 +135,20 @@ def test_moment_form_matches_per_point_pass():
     assert np.max(np.abs(chi2_mom - chi2_full) / np.maximum(1.0, np.abs(chi2_full) / 1e4)) <= CHI2_ATOL
     ref = oracle.compute_model(dict(zip(names, theta[0])))
     assert_xi_close({n: models_mom[n][0] for n in ref}, ref, 'moment form')
+
+
+def test_c2_fast_metals_matches_oracle():
+    """fast_metals on the dense C2 operands: frozen metal x metal vectors (M_c xi_c evaluated
+    once at the plan parameters through the same kernels), shared metal x main tables."""
+    vega, oracle, theta = make_c2(3, width=0.2, fast_metals=True)
+    names = list(vega.sample_params['limits'])
+    oracle.compute_model()          # the reference freezes its metal x metal cache at the first call
+    chi2 = vega.chi2_batch(theta)
+    models, status = vega.compute_model_batch(theta)
+    assert not status.any()
+    for b in range(theta.shape[0]):
+        pars = dict(zip(names, theta[b]))
+        ref = oracle.compute_model(pars)
+        assert_xi_close({n: models[n][b] for n in ref}, ref, f'vector {b}')
+        ref_chi2 = oracle.chi2(pars)
+        assert abs(chi2[b] - ref_chi2) <= CHI2_ATOL * max(1.0, abs(ref_chi2) / 1e4), (chi2[b], ref_chi2)

@@ -84,8 +84,35 @@ def test_resolve_scale_rules():
     assert resolve_scale(cfg, {}, False, 'x', False) == (2, 'aiso_full', 'epsilon_full')
 
 
+def test_fast_metals_descriptors():
+    """fast_metals = True (vega/metals.py:144-207): metal x metal terms are frozen, metal x main
+    terms with the same cache key (betas + every parameter, not the pair) read the first
+    pair's knot tables on the first pair's coordinates."""
+    vega, pb = builder('configs/full_configs/main.ini')
+    item = vega.corr_items['lyalya_lyalya']
+    item.config['model']['fast_metals'] = 'True'
+    info = pb.describe_corr('lyalya_lyalya')
+    main = [item.tracer1['name'], item.tracer2['name']]
+    evals = info['evals'][2:]
+    pairs = item.metal_correlations
+    with_main = [n1 in main or n2 in main for n1, n2 in pairs]
+    assert all(d.frozen == (0 if wm else 1) for d, wm in zip(evals, with_main))
+    owners = [d for d, wm in zip(evals, with_main) if wm and d.table_owner < 0]
+    aliases = [d for d, wm in zip(evals, with_main) if wm and d.table_owner >= 0]
+    # every metal beta of the test configuration is the same fixed value: one owner
+    assert len(owners) == 1 and len(aliases) == sum(with_main) - 1
+    owner_id = 2 + with_main.index(True)
+    assert all(d.table_owner == owner_id and d.coord_set == owners[0].coord_set for d in aliases)
+    # the aliases keep their own bias columns (the weight) and metal slot
+    assert len({d.out_slot for d in evals}) == len(evals)
+    assert len({tuple(d.idx_bias) + tuple(d.idx_bias_eta) for d in aliases + owners}) == len(aliases) + 1
+    # growth rate pinned to the fiducial value for the metal evaluations
+    assert owners[0].idx_growth_rate == pb.col('growth_rate@fiducial')
+    assert info['evals'][0].idx_growth_rate == pb.col('growth_rate')
+
+
 def test_unsupported_options_fail_loudly():
     vega, pb = builder('configs/full_configs/main.ini')
-    vega.corr_items['lyalya_lyalya'].config['model']['fast_metals'] = 'True'
+    vega.corr_items['lyalya_lyalya'].config['model']['no-metal-decomp'] = 'False'
     with pytest.raises(NotImplementedError):
         pb.describe_corr('lyalya_lyalya')

@@ -10,7 +10,8 @@ import pytest
 from helpers import make_oracle
 
 GOLD = Path(__file__).resolve().parent / 'golden'
-INI = {'full': 'configs/full_configs/main.ini', 'c1': 'configs/configs/main.ini'}
+INI = {'full': 'configs/full_configs/main.ini', 'c1': 'configs/configs/main.ini',
+       'full_fast': 'configs/full_configs/main.ini'}
 
 
 def load():
@@ -28,16 +29,18 @@ def check(key, compute_model, chi2, log_lik, gold, meta):
         assert abs(log_lik(pars) - float(gold[f'{key}/{i}/log_lik'])) <= 1e-6
 
 
-@pytest.mark.parametrize('key', ['c1', 'full'])
+@pytest.mark.parametrize('key', ['c1', 'full', 'full_fast'])
 def test_oracle_matches_reference_outputs(key):
     gold, meta = load()
-    vega, oracle = make_oracle(INI[key])
+    vega, oracle = make_oracle(INI[key], fast_metals=key == 'full_fast')
     check(key, oracle.compute_model, oracle.chi2, oracle.log_lik, gold, meta)
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('key', ['c1', 'full'])
+@pytest.mark.parametrize('key', ['c1', 'full', 'full_fast'])
 def test_cuda_path_matches_reference_outputs(key):
+    """'full_fast': the reference's fast_metals caches (vega/metals.py:144-207) -- metal x metal
+    terms frozen at the plan parameters, metal x main terms sharing one xi per cache key."""
     gold, meta = load()
-    vega, oracle = make_oracle(INI[key])
+    vega, oracle = make_oracle(INI[key], fast_metals=key == 'full_fast')
     check(key, vega.compute_model, vega.chi2, vega.log_lik, gold, meta)
