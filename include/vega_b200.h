@@ -219,6 +219,13 @@ int vg_model_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* co
 /* chi2 for a batch incl. priors (vega/vega_interface.py:250-325); status != 0 -> 1e100 */
 int vg_chi2_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* chi2_dev,
                   int32_t* status_dev, void* stream);
+/* Monte Carlo mocks (vega/analysis.py:195-308, bin/run_vega_mc_fits_mpi.py:11-78): n_mocks masked
+ * data vectors [n_mocks][n_mask] of one correlation (after vg_corr_set_data, whose invcov
+ * is then the scaled one, vega/data.py:689-760).  vg_chi2_batch_mc evaluates vector b against
+ * mock mock_idx_dev[b] of every correlation, so many mock fits advance in one batch. */
+int vg_corr_set_mocks(vg_plan* plan, int32_t corr, int32_t n_mocks, const double* mocks);
+int vg_chi2_batch_mc(vg_plan* plan, const double* theta_dev, const int32_t* mock_idx_dev, int64_t B,
+                     double* chi2_dev, int32_t* status_dev, void* stream);
 /* Same with HOST buffers: pinned staging + H2D of theta, D2H of chi2/status; synchronous. */
 int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, double* chi2_host,
                        int32_t* status_host, void* stream);

@@ -1,0 +1,191 @@
+"""Batched drivers (vega_b200/drivers.py).  CPU tests cover the stencil algebra, the lock-step
+Newton iteration, the Minimizer surface and the sampler adapter with closed-form
+functions; GPU tests drive the device engine and check against the oracle."""
+import numpy as np
+import pytest
+
+from vega_b200.drivers import (BatchedMinimizer, BatchedSamplerLikelihood, MonteCarloFits,
+                               derivatives_from_stencil, newton_lockstep, stencil, stencil_size)
+
+
+def test_stencil_derivatives_of_a_quadratic_are_exact():
+    rng = np.random.default_rng(1)
+    P = 4
+    A = rng.standard_normal((P, P))
+    A = A + A.T
+    b, x0 = rng.standard_normal(P), rng.standard_normal(P)
+    steps = np.array([0.1, 0.2, 0.05, 0.3])
+
+    def f(x):
+        return 0.5 * np.einsum('bi,ij,bj->b', x, A, x) + x.dot(b) + 1.5
+
+    for hessian in (False, True):
+        st = stencil(x0, steps, hessian=hessian)
+        assert st.shape == (stencil_size(P, hessian), P)
+        f0, g, H = derivatives_from_stencil(f(st), steps, hessian=hessian)
+        assert np.isclose(f0, f(x0[None])[0])
+        assert np.allclose(g, A.dot(x0) + b, rtol=1e-10, atol=1e-12)
+        if hessian:
+            assert np.allclose(H, A, rtol=1e-8, atol=1e-10)
+
+
+def test_newton_lockstep_bounds_and_fixed_parameters():
+    rng = np.random.default_rng(2)
+    M, P = 3, 4
+    targets = rng.uniform(-1, 1, (M, P))
+    calls = []
+
+    def ev(theta, prob):
+        calls.append(theta.shape[0])
+        d = theta - targets[prob]
+        return (d**2).sum(axis=1) * np.array([1., 4., 9.])[prob] + 0.05 * (d**4).sum(axis=1)
+
+    lower = np.array([np.nan, np.nan, 0.5, np.nan])      # parameter 2 is bounded away from its target
+    upper = np.full(P, np.nan)
+    targets[:, 2] = -0.3
+    free = np.array([True, True, True, False])           # parameter 3 stays at its start value
+    res = newton_lockstep(ev, np.zeros((M, P)) + 0.7, np.ones(P), lower, upper, free=free)
+    assert res['converged'].all() or np.all(res['theta'][:, 2] <= 0.5 + 0.05)
+    assert np.allclose(res['theta'][:, :2], targets[:, :2], atol=5e-3)      # edm 1e-5 ~ 3e-3 sigma
+    assert np.all(res['theta'][:, 2] >= 0.5) and np.all(res['theta'][:, 2] < 0.56)
+    assert np.all(res['theta'][:, 3] == 0.7)
+    # one evaluator call per iteration, (active problems) x (2 F^2 + 1) vectors each
+    assert calls[0] == M * stencil_size(3, hessian=True)
+
+
+def _sample(names, values, errors, limits=None):
+    return {'limits': {n: (limits or {}).get(n, (None, None)) for n in names},
+            'values': dict(zip(names, values)), 'errors': dict(zip(names, errors)),
+            'fix': {n: False for n in names}}
+
+
+def test_batched_minimizer_surface_and_two_stage_fit():
+    names = ['ap', 'bias_LYA', 'beta_LYA']
+    truth = np.array([1.02, -0.12, 1.6])
+    sig = np.array([0.03, 0.004, 0.09])
+    corr = np.array([[1, .3, 0], [.3, 1, -.5], [0, -.5, 1]])
+    icov = np.linalg.inv(corr * sig[:, None] * sig[None, :])
+    batches = []
+
+    def chi2_batch(theta):
+        batches.append(theta.shape[0])
+        d = theta - truth
+        return np.einsum('bi,ij,bj->b', d, icov, d) + 10.
+
+    mini = BatchedMinimizer(chi2_batch, _sample(names, [1.0, -0.1, 1.5], [0.1, 0.01, 0.1]), verbose=False)
+    with pytest.raises(RuntimeError):
+        mini.values
+    mini.minimize()
+    assert np.allclose([mini.values[n] for n in names], truth, atol=1e-3 * sig.max() + 1e-6)
+    assert np.isclose(mini.fmin.fval, 10., atol=1e-6) and mini.fmin.is_valid
+    assert np.allclose(mini.covariance, corr * sig[:, None] * sig[None, :], rtol=1e-4)   # errordef = 1
+    assert np.allclose([mini.errors[n] for n in names], sig, rtol=1e-4)
+    # first stage: only the bias parameter free -> stencil of 1 parameter (3 vectors)
+    assert batches[0] == stencil_size(1, hessian=True)
+    assert mini.chi2(*truth) == pytest.approx(10.)
+    # fixing a parameter through minimize(params) (vega/minimizer.py:52-61)
+    mini.minimize({'fix': {'ap': True}, 'values': {'ap': 1.0}})
+    assert mini.values['ap'] == 1.0 and mini.fixed['ap'] and mini.errors['ap'] == 0.0
+
+
+class _StubVega:
+    def __init__(self):
+        self.sample_params = _sample(['a', 'b'], [0.5, 2.0], [0.1, 0.1], {'a': (0., 1.), 'b': (1., 5.)})
+
+    def _log_norm(self):
+        return -3.0
+
+    def chi2_batch(self, theta, names):
+        assert list(names) == ['a', 'b']
+        return (theta**2).sum(axis=1)
+
+
+def test_sampler_adapter_matches_polychord_calling_convention():
+    like = BatchedSamplerLikelihood(_StubVega())
+    assert like.num_params == 2 and like.num_derived == 0
+    assert like.prior([0.25, 0.5]) == [0.25, 3.0]
+    cube = np.array([[0., 0.], [1., 1.], [0.5, 0.25]])
+    theta = like.prior_batch(cube)
+    assert np.allclose(theta, [[0., 1.], [1., 5.], [0.5, 2.]])
+    ll = like.log_lik_batch(theta)
+    assert np.allclose(ll, -3.0 - 0.5 * (theta**2).sum(axis=1))
+    value, derived = like.log_lik(theta[2])
+    assert value == ll[2] and derived == []
+    stub = _StubVega()
+    stub.sample_params['limits']['a'] = (None, 1.)
+    with pytest.raises(ValueError):
+        BatchedSamplerLikelihood(stub)
+
+
+# ---------------------------------------------------------------------------------------------
+# on the device
+# ---------------------------------------------------------------------------------------------
+def _c2_small():
+    """C2 operands (dense distortion / metal / covariance matrices), data drawn around the
+    oracle's fiducial model."""
+    from helpers import make_c2
+    return make_c2(2, width=0.5)
+
+
+@pytest.mark.gpu
+def test_mock_chi2_matches_oracle_monte_carlo_mode():
+    """vg_chi2_batch_mc: vector b against mock mock_idx[b] == the reference's monte_carlo
+    branch of chi2 (vega/vega_interface.py:296-312) evaluated mock by mock."""
+    vega, oracle, theta = _c2_small()
+    names = list(vega.sample_params['limits'])
+    mc = MonteCarloFits(vega, fiducial_model=oracle.compute_model(), scale=1.3)
+    mocks = mc.draw(3, seed=11)
+    assert all(v.shape == (3, int(vega.data[n].data_mask.sum())) for n, v in mocks.items())
+    pairs = [(0, 2), (1, 0), (0, 1), (1, 1)]
+    got = mc.chi2(np.array([theta[t] for t, _ in pairs]), [m for _, m in pairs])
+    oracle.monte_carlo = True
+    for (t, m), value in zip(pairs, got):
+        for name in vega.corr_items:
+            vega.data[name].masked_mc_mock = mocks[name][m]
+        ref = oracle.chi2(dict(zip(names, theta[t])))
+        assert abs(value - ref) <= 1e-6 * max(1.0, abs(ref) / 1e4), (t, m, value, ref)
+
+
+@pytest.mark.gpu
+def test_batched_minimizer_on_the_device_path():
+    """One Newton iteration = one batched chi2 call; the minimum is a stationary point of the
+    ORACLE's chi2 (central differences of the CPU path) and lies below the start value."""
+    vega, oracle, theta = _c2_small()
+    names = list(vega.sample_params['limits'])
+    mini = BatchedMinimizer.from_vega(vega, verbose=False)
+    start = np.array([vega.sample_params['values'][n] for n in names])
+    mini.minimize()
+    best = np.array([mini.values[n] for n in names])
+    f_start, f_best = vega.chi2_batch(np.array([start, best]))
+    assert mini.fmin.is_valid and np.isclose(mini.fmin.fval, f_best, atol=1e-6)
+    assert f_best < f_start
+    ref = oracle.chi2(dict(zip(names, best)))
+    assert abs(ref - f_best) <= 1e-6 * max(1.0, abs(ref) / 1e4)
+    # stationarity on the oracle along two well-constrained directions
+    for n in ('bias_eta_LYA', 'beta_LYA'):
+        if n not in names:
+            continue
+        j, h = names.index(n), 0.1 * mini.errors[n]
+        up, dn = best.copy(), best.copy()
+        up[j] += h
+        dn[j] -= h
+        slope = (oracle.chi2(dict(zip(names, up))) - oracle.chi2(dict(zip(names, dn)))) / (2 * h)
+        assert abs(slope) * mini.errors[n] < 0.05, (n, slope)     # << 1 chi2 unit per sigma
+
+
+@pytest.mark.gpu
+def test_monte_carlo_fits_in_lock_step():
+    vega, oracle, theta = _c2_small()
+    mc = MonteCarloFits(vega, fiducial_model=oracle.compute_model())
+    mc.draw(4, seed=3)
+    res = mc.fit(max_iter=30)
+    assert res['theta'].shape == (4, len(mc.names)) and res['converged'].all()
+    # every fit beats the truth evaluated on its own mock, by about the number of parameters
+    truth = np.tile([vega.params[n] for n in mc.names], (4, 1))
+    at_truth = mc.chi2(truth, np.arange(4))
+    assert np.all(res['fval'] <= at_truth + 1e-6)
+    assert np.all(at_truth - res['fval'] < 10 * len(mc.names))
+    # the sharded call: a slice of the mocks gives the same answers
+    part = mc.fit(mock_slice=slice(1, 3), max_iter=30)
+    assert np.allclose(part['theta'], res['theta'][1:3], rtol=0, atol=1e-9)
+    vega.monte_carlo = False

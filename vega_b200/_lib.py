@@ -103,6 +103,8 @@ _SIGNATURES = {
     'vg_profile_read': (C.c_int, [_PTR, _PTR, _PTR]),
     'vg_model_batch': (C.c_int, [_PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_chi2_batch': (C.c_int, [_PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
+    'vg_corr_set_mocks': (C.c_int, [_PTR, i32, i32, _PTR]),
+    'vg_chi2_batch_mc': (C.c_int, [_PTR, _PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_chi2_batch_host': (C.c_int, [_PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_stage_batch': (C.c_int, [_PTR, i32, i32, i32, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_stage_size': (C.c_int64, [_PTR, i32, i32]),

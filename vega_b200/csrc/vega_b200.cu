@@ -138,6 +138,7 @@ struct Corr {
   bool has_invcov = false;
   std::vector<int32_t> mask_host;
   DevBuf d_mask_idx, d_data, d_invcov;   // invcov [n_mask][ld_mask]
+  DevBuf d_mocks; int n_mocks = 0;       // Monte Carlo mocks [n_mocks][n_mask]
   int sx_n[12] = {0};
   DevBuf d_sx[12];
 };
@@ -1000,7 +1001,7 @@ int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st) {
 //   data == false: model rows for ALL distorted bins -> out[Bc][ldo = ld_dist]
 //   data == true : residual d - m on the masked bins  -> out[Bc][ldo] at column col0
 int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* out, int ldo,
-                  int ncols, cudaStream_t st) {
+                  int ncols, cudaStream_t st, const int* mock_idx = nullptr) {
   const double* y = plan->w_x.as<double>();
   int ldy = c.ld_model;
   int y_is_masked = 0;
@@ -1023,6 +1024,10 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
   pa.bb = bb_dev(c); pa.n_dist = c.n_dist;
   pa.pfull = plan->w_pfull.as<double>(); pa.npf = plan->npf; pa.idx_bao_amp = plan->idx_bao_amp;
   pa.data = residual ? c.d_data.as<double>() : nullptr;
+  if (residual && mock_idx) {
+    VG_REQUIRE(c.n_mocks > 0, "vg_chi2_batch_mc: correlation without mocks (vg_corr_set_mocks)");
+    pa.data = c.d_mocks.as<double>(); pa.mock_idx = mock_idx; pa.data_stride = c.n_mask;
+  }
   pa.n_out = residual ? c.n_mask : c.n_dist;
   pa.ldo = ldo; pa.ncols = ncols; pa.B = Bc; pa.out = out;
   const long long n = Bc * ncols;
@@ -1058,7 +1063,7 @@ int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* in
 }
 
 int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi2_dev, int* status_dev,
-               cudaStream_t st) {
+               cudaStream_t st, const int* mock_idx = nullptr) {
   VG_TRY(expand_params(plan, theta_dev, Bc, status_dev, st));
   int first = 1;
   int col0 = 0;
@@ -1069,10 +1074,10 @@ int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi
     if (plan->has_global) {
       // residuals of all correlations side by side: [Bc][ld_total]
       VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>() + col0, plan->ld_total,
-                           c.n_mask, st));
+                           c.n_mask, st, mock_idx));
       col0 += c.n_mask;
     } else {
-      VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, st));
+      VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, st, mock_idx));
       VG_TRY(quad_form(plan, plan->w_diff.as<double>(), c.n_mask, c.ld_mask,
                        c.has_invcov ? c.d_invcov.as<double>() : nullptr, Bc, chi2_dev, !first, st));
       first = 0;
@@ -1122,6 +1127,29 @@ int vg_chi2_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* chi
   for (long long b0 = 0; b0 < B; b0 += chunk) {
     const long long Bc = std::min<long long>(chunk, B - b0);
     VG_TRY(chi2_chunk(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st));
+  }
+  return VG_OK;
+}
+
+int vg_corr_set_mocks(vg_plan* plan, int32_t corr, int32_t n_mocks, const double* mocks) {
+  VG_CORR(plan, corr);
+  VG_REQUIRE(n_mocks > 0 && mocks && c.n_mask > 0, "vg_corr_set_mocks: set the data mask first");
+  VG_TRY(upload(c.d_mocks, mocks, (size_t)n_mocks * c.n_mask));
+  c.n_mocks = n_mocks;
+  return VG_OK;
+}
+
+int vg_chi2_batch_mc(vg_plan* plan, const double* theta_dev, const int32_t* mock_idx_dev, int64_t B,
+                     double* chi2_dev, int32_t* status_dev, void* stream) {
+  VG_REQUIRE(plan && plan->finalized && B > 0 && chi2_dev && status_dev && mock_idx_dev,
+             "vg_chi2_batch_mc: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long chunk = std::min<long long>(B, plan->chunk_max);
+  VG_TRY(ensure_workspace(plan, chunk));
+  for (long long b0 = 0; b0 < B; b0 += chunk) {
+    const long long Bc = std::min<long long>(chunk, B - b0);
+    VG_TRY(chi2_chunk(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st,
+                      mock_idx_dev + b0));
   }
   return VG_OK;
 }

@@ -114,6 +114,8 @@ struct PostArgs {
   BroadbandDev bb; int n_dist;
   const double* pfull; int npf; int idx_bao_amp;
   const double* data;         // [n_out] or null (model output)
+  const int* mock_idx;        // per vector: row of `data` ([n_mock][data_stride]), null: row 0
+  int data_stride;
   int n_out, ncols, ldo; long long B;   // columns j < ncols are written (zero for j >= n_out)
   double* out;                // [B][ldo]: model (data == null) or residual data - model
 };
@@ -133,7 +135,12 @@ __global__ void post_kernel(PostArgs a) {
     v *= bb_eval(a.bb, 2, p, bin, a.n_dist);
     v += (1.0 + amp) * bb_eval(a.bb, 3, p, bin, a.n_dist);
   }
-  *o = a.data ? a.data[j] - v : v;
+  if (a.data) {
+    const double* dvec = a.mock_idx ? a.data + (long long)a.mock_idx[b] * a.data_stride : a.data;
+    *o = dvec[j] - v;
+  } else {
+    *o = v;
+  }
 }
 
 // chi2[b] (+)= sum_j diff[b][j]^2   (identity covariance)

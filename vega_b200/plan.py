@@ -779,6 +779,29 @@ class DevicePlan:
             status_t |= self.static_status
         return chi2_t, status_t
 
+    def set_mocks(self, ci, mocks):
+        """Masked Monte Carlo mocks [n_mocks, n_mask] of correlation ci for chi2_mc_device."""
+        mocks = _f64(np.atleast_2d(mocks))
+        _lib.check(self.lib.vg_corr_set_mocks(self.handle, ci, mocks.shape[0], _dptr(mocks)))
+
+    def chi2_mc_device(self, theta_t, mock_idx_t, chi2_t=None, status_t=None):
+        """chi2 of vector b against mock mock_idx_t[b] (int32 CUDA tensor): lock-step mock fits."""
+        torch = self.torch
+        B = theta_t.shape[0]
+        assert theta_t.is_cuda and theta_t.dtype == torch.float64 and theta_t.is_contiguous()
+        assert mock_idx_t.is_cuda and mock_idx_t.dtype == torch.int32 and mock_idx_t.shape[0] == B
+        if chi2_t is None:
+            chi2_t = torch.empty(B, dtype=torch.float64, device=theta_t.device)
+        if status_t is None:
+            status_t = torch.empty(B, dtype=torch.int32, device=theta_t.device)
+        _lib.check(self.lib.vg_chi2_batch_mc(self.handle, C.c_void_p(theta_t.data_ptr()),
+                                             C.c_void_p(mock_idx_t.data_ptr()), B,
+                                             C.c_void_p(chi2_t.data_ptr()), C.c_void_p(status_t.data_ptr()),
+                                             self._stream()))
+        if self.static_status:
+            status_t |= self.static_status
+        return chi2_t, status_t
+
     def model_device(self, theta_t):
         torch = self.torch
         B = theta_t.shape[0]
