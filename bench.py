@@ -183,7 +183,7 @@ def fp64_peaks(lib, torch):
     return dgemm, tf.value
 
 
-def run_reference_arm(args, rank, world):
+def run_reference_arm(args, rank, world, out=sys.stdout):
     if rank != 0:
         return
     vega = build_state()
@@ -198,10 +198,20 @@ def run_reference_arm(args, rank, world):
             'e2e': {'value': base['value'], 'unit': 'evals/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'note': 'the reference is pure Python with no compiled sources; its path is timed through the '
                     'numpy oracle (oracle/vega_oracle.py), one forked replica per host core'}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=out, flush=True)
+
+
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner,
+    torchrun notices) are sent to stderr; the returned file writes to the real stdout."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), 'w')
+    os.dup2(2, 1)
+    return real
 
 
 def main():
+    real_stdout = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=10)
@@ -215,7 +225,7 @@ def main():
     local_rank = int(os.environ.get('LOCAL_RANK', 0))
 
     if args.impl == 'reference':
-        run_reference_arm(args, rank, world)
+        run_reference_arm(args, rank, world, real_stdout)
         return
 
     from vega_b200 import synthetic, _lib
@@ -336,7 +346,7 @@ def main():
             'kernels': kernels,
             'cpu_baseline': base,
         }
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=real_stdout, flush=True)
     if world > 1:
         dist.destroy_process_group()
 

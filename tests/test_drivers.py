@@ -187,5 +187,8 @@ def test_monte_carlo_fits_in_lock_step():
     assert np.all(at_truth - res['fval'] < 10 * len(mc.names))
     # the sharded call: a slice of the mocks gives the same answers
     part = mc.fit(mock_slice=slice(1, 3), max_iter=30)
-    assert np.allclose(part['theta'], res['theta'][1:3], rtol=0, atol=1e-9)
+    # (a different batch composition changes the split-K reduction order of the GEMMs at the
+    # 1e-13 level, which the Newton iterations carry along)
+    sigma = np.maximum(res['errors'][1:3], 1e-30)
+    assert np.all(np.abs(part['theta'] - res['theta'][1:3]) <= 1e-4 * sigma + 1e-12)
     vega.monte_carlo = False

@@ -568,7 +568,59 @@ class PlanBuilder:
             info['inst'] = (_f64(table), self.col('desi_inst_sys_amp'), 0.0003189935987295203)
 
         info['bb_terms'], info['bb_design'] = self.broadband_terms(item)
+        self.share_identical_tables(info['evals'])
         return info
+
+    # fields of vg_eval_desc that determine P(k,mu) -> knot tables (everything before the xi block)
+    _PK_FIELDS = [name for name, _ in EvalDesc._fields_][
+        :[name for name, _ in EvalDesc._fields_].index('coord_set')]
+
+    def pk_signature(self, d):
+        """Hashable identity of the knot tables of one evaluation: two evaluations with equal
+        signatures get bit-identical P(k,mu) for every parameter vector of a batch.  A parameter
+        column counts by name when it is sampled and by value when it is fixed."""
+        base = self.base_vector()
+
+        def ident(idx):
+            if idx < 0:
+                return None
+            name = (self.names + list(self.extra))[idx]
+            return ('col', idx) if name in self.sampled_set else ('val', float(base[idx]))
+
+        skip = set()
+        if d.fast_metals:
+            # Kaiser term without the biases (vega/power_spectrum.py:219-220): when beta is given
+            # directly and the tracer carries no HCD term, its bias never enters P(k,mu)
+            for t in range(2):
+                if d.idx_beta[t] >= 0 and not (d.hcd_model and d.hcd_on[t]):
+                    skip.add(('idx_bias', t))
+                    skip.add(('idx_bias_eta', t))
+        sig = []
+        for name in self._PK_FIELDS:
+            v = getattr(d, name)
+            if hasattr(v, '__len__'):
+                vals = list(v)
+                if name.startswith('idx_'):
+                    vals = [None if (name, t) in skip else ident(x) for t, x in enumerate(vals)]
+                sig.append((name, tuple(vals)))
+            else:
+                sig.append((name, ident(v) if name.startswith('idx_') else v))
+        return tuple(sig)
+
+    def share_identical_tables(self, evals):
+        """Evaluations of one correlation whose P(k,mu) inputs are identical (e.g. QSO x metal terms
+        whose metal betas are the same fixed number) read the knot tables of the first of them
+        (vg_eval_desc.table_owner): the multipoles and the Hankel transform are computed once,
+        every evaluation keeps its own coordinates, weight and metal matrix."""
+        first = {}
+        for e, d in enumerate(evals):
+            if d.table_owner >= 0 or d.frozen:
+                continue
+            sig = self.pk_signature(d)
+            if sig in first:
+                d.table_owner = first[sig]
+            else:
+                first[sig] = e
 
     # -- push everything into the library ------------------------------------------------------
     def build(self, chunk=None):

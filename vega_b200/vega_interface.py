@@ -321,6 +321,54 @@ class VegaInterface:
             log_norm += self._gaussian_lik_prior(prior[1])
         return log_norm
 
+    def minimize(self):
+        """Best fit over the [sample] parameters (vega/vega_interface.py:581-644) with the batched
+        stencil minimizer; fills bestfit_model, per-correlation chi2 statistics, chisq, p_value."""
+        import scipy.stats
+        from .drivers import BatchedMinimizer
+        if not self.sample_params['limits']:
+            print('No sampled parameters. Skipping minimization.')
+            return
+        if self.minimizer is None:
+            self.minimizer = BatchedMinimizer.from_vega(self)
+        self.minimizer.minimize()
+        self.bestfit_model = self.compute_model(self.minimizer.values, run_init=False)
+        self.total_data_size = 0
+        self.bestfit_corr_stats = {}
+        num_pars = len(self.sample_params['limits'])
+        for name in self.corr_items:
+            corr_data = self.data[name]
+            data_size = getattr(corr_data, 'effective_data_size', corr_data.data_size)
+            self.total_data_size += data_size
+            if self.monte_carlo and self._use_global_cov:
+                chisq = 0
+            elif self.monte_carlo:
+                diff = corr_data.masked_mc_mock - self.bestfit_model[name][corr_data.model_mask]
+                chisq = diff.T.dot(corr_data.scaled_inv_masked_cov.dot(diff))
+            else:
+                diff = corr_data.masked_data_vec - self.bestfit_model[name][corr_data.model_mask]
+                chisq = diff.T.dot(corr_data.inv_masked_cov.dot(diff))
+            reduced_chisq = chisq / (data_size - num_pars)
+            p_value = 1 - scipy.stats.chi2.cdf(chisq, data_size - num_pars)
+            print(f'{name} chi^2/(ndata-nparam): {chisq:.1f}/({data_size}-{num_pars}) '
+                  f'= {reduced_chisq:.3f}, PTE={p_value:.2f}')
+            self.bestfit_corr_stats[name] = {
+                'masked_size': data_size, 'chisq': chisq, 'reduced_chisq': reduced_chisq,
+                'p_value': p_value, 'bestfit_marg_coeff': None}
+        self.chisq = self.minimizer.fmin.fval
+        self.reduced_chisq = self.chisq / (self.total_data_size - num_pars)
+        self.p_value = 1 - scipy.stats.chi2.cdf(self.chisq, self.total_data_size - num_pars)
+        print(f'Total chi^2/(ndata-nparam): {self.chisq:.1f}/({self.total_data_size}-{num_pars}) '
+              f'= {self.reduced_chisq:.3f}, PTE={self.p_value:.2f}')
+        if not self.minimizer.fmin.is_valid:
+            print('Invalid fit!!! Check data, covariance, model and priors.')
+
+    @property
+    def bestfit(self):
+        """The minimizer after minimize() (the reference returns its iminuit object here,
+        vega/vega_interface.py:646-663)."""
+        return self.minimizer
+
     # -- batched API (new) -----------------------------------------------------------------------
     def chi2_batch(self, theta, names=None):
         """chi2 of B parameter vectors.  theta: ndarray [B, P] with columns `names`
