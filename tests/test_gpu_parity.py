@@ -152,3 +152,49 @@ def test_c2_fast_metals_matches_oracle():
         assert_xi_close({n: models[n][b] for n in ref}, ref, f'vector {b}')
         ref_chi2 = oracle.chi2(pars)
         assert abs(chi2[b] - ref_chi2) <= CHI2_ATOL * max(1.0, abs(ref_chi2) / 1e4), (chi2[b], ref_chi2)
+
+
+def test_c3_shaped_four_correlations_global_covariance_fast_metals():
+    """The ingredients of the DESI-shaped workload C3 on the reference's own 4-correlation
+    configuration: dense distortion / metal matrices, fast_metals, post-distortion broadband
+    polynomials, ONE global covariance over all masked bins (vega/vega_interface.py:295-304)."""
+    from helpers import set_fast_metals
+    from oracle.vega_oracle import Oracle
+    from helpers import static_tables
+    from vega_b200 import VegaInterface
+    vega = VegaInterface('configs/full_configs/main.ini')
+    set_fast_metals(vega)
+    synthetic.inject_dense_operands(vega)
+    synthetic.inject_global_covariance(vega)
+    oracle = Oracle(vega, tables=static_tables())
+    synthetic.draw_mock_data(vega, oracle.compute_model())
+    names = ['bias_eta_LYA', 'beta_LYA', 'ap', 'at', 'bias_hcd', 'beta_hcd', 'drp_QSO',
+             'sigma_velo_disp_lorentz_QSO', 'bao_amp', 'bias_eta_SiII(1260)',
+             'BB-lyalya_lyalya-0 add post r,mu (1,2)']
+    rng = np.random.default_rng(8)
+    base = np.array([vega.params[n] for n in names])
+    theta = base * (1 + 0.03 * rng.standard_normal((3, len(names))))
+    chi2 = vega.chi2_batch(theta, names)
+    log_lik = vega.log_lik_batch(theta, names)
+    for b in range(theta.shape[0]):
+        pars = dict(zip(names, theta[b]))
+        ref = oracle.chi2(pars)
+        assert abs(chi2[b] - ref) <= CHI2_ATOL * max(1.0, abs(ref) / 1e4), (chi2[b], ref)
+        assert abs(log_lik[b] - oracle.log_lik(pars)) <= CHI2_ATOL * max(1.0, abs(ref) / 1e4)
+
+
+def test_chunked_batches_agree_with_single_vectors():
+    """C4-shaped call: more vectors than one workspace chunk (ragged last chunk); every chi2
+    must equal the batch-of-one result of the same vector, sentinel rows included."""
+    vega, oracle = make_oracle('configs/configs/main.ini')
+    vega._batch_chunk = 64
+    names = list(vega.sample_params['limits'])
+    theta = synthetic.draw_theta(vega, 150, seed=20261105, width=2.0)
+    theta[17, names.index('ap')] = 1e6          # out of the FFTLog range -> 1e100
+    chi2 = vega.chi2_batch(theta)
+    assert chi2[17] == 1e100 and np.sum(chi2 == 1e100) == 1
+    for b in (0, 63, 64, 127, 128, 149):
+        one = vega.chi2(dict(zip(names, theta[b])))
+        assert abs(one - chi2[b]) <= 1e-9 * max(1.0, abs(one))
+    assert np.allclose(vega.log_lik_batch(theta[:3]), [vega.log_lik(dict(zip(names, t))) for t in theta[:3]],
+                       rtol=0, atol=1e-8)

@@ -112,3 +112,31 @@ def draw_theta(vega, n, seed=20261104, width=3.0, names=None):
         b = centre + width * err if hi is None else min(hi, centre + width * err)
         theta[:, j] = rng.uniform(a, b, size=n)
     return theta
+
+
+def inject_global_covariance(vega, coupling=0.05):
+    """Joint covariance over all correlations, in memory (what read_global_cov builds from a
+    file, vega/vega_interface.py:888-954): the per-correlation covariances on the diagonal
+    blocks plus a weak positive-definite coupling between the blocks, then the masked inverse
+    and log-determinant exactly as the reference computes them."""
+    from . import utils
+    names = list(vega.corr_items)
+    covs = [vega.data[n].cov_mat for n in names]
+    sizes = [c.shape[0] for c in covs]
+    total = sum(sizes)
+    cov = np.zeros((total, total))
+    sig = np.concatenate([np.sqrt(c.diagonal()) for c in covs])
+    off = np.cumsum([0] + sizes)
+    for i, c in enumerate(covs):
+        cov[off[i]:off[i + 1], off[i]:off[i + 1]] = c
+    # rank-one coupling u u^T with u ~ sigma: keeps the matrix SPD
+    u = np.sqrt(coupling) * sig * np.cos(np.arange(total) * 0.37)
+    cov += np.outer(u, u)
+    vega.global_cov = cov
+    vega._use_global_cov = True
+    vega.full_data_mask = np.concatenate([vega.data[n].data_mask for n in names])
+    vega.full_model_mask = np.concatenate([vega.data[n].model_mask for n in names])
+    vega.masked_global_invcov = utils.compute_masked_invcov(cov, vega.full_data_mask)
+    vega.masked_global_log_cov_det = utils.compute_log_cov_det(cov, vega.full_data_mask)
+    vega._engine = None
+    return vega
