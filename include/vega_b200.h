@@ -36,6 +36,7 @@ extern "C" {
 #define VG_F_FSEXP    (1u << 5)   /* fullshape exp           :560-586 */
 #define VG_F_VELO     (1u << 6)   /* velocity dispersion     :588-636 */
 #define VG_F_KDAMP    (1u << 7)   /* k^n damping  vega/utils.py:423-441 */
+#define VG_F_MOCKGK   (1u << 8)   /* mock-bin-size G(k)      :143-160 */
 
 /* One P(k,mu) -> xi evaluation: the (PowerSpectrum, CorrelationFunction) pair the
  * reference builds per component (peak / smooth, vega/model.py:60-66) and per metal
@@ -98,6 +99,11 @@ typedef struct vg_eval_desc {
                                tables of evaluation `table_owner` -- the metal x main-tracer cache
                                hit of compute_xi_metal_cross_main (:171-207), whose key holds the
                                betas but not the pair; only weight and metal matrix differ */
+  /* ---- mock-bin-size smoothing (vega/power_spectrum.py:143-160) ---- */
+  int32_t mock_los_mode;    /* 0 none, 1 growth: rp size * (1+f), 2 amplitude: * (1+los_smooth_amp),
+                               3 only-los: transverse size 0 */
+  int32_t idx_los_smooth_amp;
+  double mock_bin_size;
   int32_t frozen;           /* 1: metal x metal term of compute_xi_metal_metal (:144-169): M_c xi_c
                                is evaluated once, at the plan's base parameters, in
                                vg_plan_finalize; the hot path adds b1*b2 (x extra) times it */

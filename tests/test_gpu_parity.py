@@ -198,3 +198,21 @@ def test_chunked_batches_agree_with_single_vectors():
         assert abs(one - chi2[b]) <= 1e-9 * max(1.0, abs(one))
     assert np.allclose(vega.log_lik_batch(theta[:3]), [vega.log_lik(dict(zip(names, t))) for t in theta[:3]],
                        rtol=0, atol=1e-8)
+
+
+@pytest.mark.parametrize('los', [None, 'growth', 'only-los'])
+def test_mock_bin_size_smoothing(los):
+    """vega/power_spectrum.py:143-160: the extra G(k) of mocks generated on a coarse grid."""
+    from oracle.vega_oracle import Oracle
+    from helpers import static_tables
+    from vega_b200 import VegaInterface
+    vega = VegaInterface('configs/configs/main.ini')
+    for item in vega.corr_items.values():
+        item.config['model']['mock-bin-size'] = '2.19'
+        if los is not None:
+            item.config['model']['mock-los-smoothing'] = los
+    oracle = Oracle(vega, tables=static_tables())
+    assert_xi_close(vega.compute_model(), oracle.compute_model(), f'mock-bin-size {los}')
+    pars = {'ap': 1.02, 'beta_LYA': 1.5}
+    assert_xi_close(vega.compute_model(pars), oracle.compute_model(pars), f'mock-bin-size {los}')
+    assert abs(vega.chi2(pars) - oracle.chi2(pars)) <= CHI2_ATOL

@@ -11,7 +11,7 @@ from .utils import VegaDeviceError
 LIB_PATH = Path(__file__).resolve().parent / 'libvega_b200.so'
 
 VG_MAX_BB_TERMS = 8
-F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP = (1 << i for i in range(8))
+F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP, F_MOCKGK = (1 << i for i in range(9))
 STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE = 1, 2, 4
 OPT_MOMENTS = 0
 
@@ -44,7 +44,8 @@ class EvalDesc(C.Structure):
         ('uv_shot', i32), ('idx_uvshot', i32 * 3),
         ('out_slot', i32), ('weight_bias', i32), ('idx_weight_extra', i32),
         ('weight_const', f64),
-        ('table_owner', i32), ('frozen', i32),
+        ('table_owner', i32), ('mock_los_mode', i32), ('idx_los_smooth_amp', i32),
+        ('mock_bin_size', f64), ('frozen', i32),
     ]
 
     def __init__(self):

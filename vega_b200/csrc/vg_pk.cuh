@@ -116,6 +116,14 @@ __device__ double pk_factors(uint32_t mask, const vg_eval_desc& d, const double*
     if (d.gk_drp != 0.0) { double x = kpar * d.gk_drp / 2.0; f *= sin(x) / x; }
     if (d.gk_drt != 0.0) { double x = kperp * d.gk_drt / 2.0; f *= sin(x) / x; }
   }
+  if (mask & VG_F_MOCKGK) {          // power_spectrum.py:143-160
+    double drp = d.mock_bin_size, drt = d.mock_bin_size;
+    if (d.mock_los_mode == 1) drp *= 1.0 + p[d.idx_growth_rate];
+    else if (d.mock_los_mode == 2) drp *= 1.0 + p[d.idx_los_smooth_amp];
+    else if (d.mock_los_mode == 3) drt = 0.0;
+    if (drp != 0.0) { double x = kpar * drp / 2.0; f *= sin(x) / x; }
+    if (drt != 0.0) { double x = kperp * drt / 2.0; f *= sin(x) / x; }
+  }
   if (mask & VG_F_PEAKNL) {          // power_spectrum.py:382-417
     const double gr = par(p, d.idx_growth_rate, 0.0);
     double sp = par(p, d.idx_sigmaNL[0], 0.0), st = par(p, d.idx_sigmaNL[1], 0.0);

@@ -227,7 +227,21 @@ class PlanBuilder:
             d.gk_drt = self.params.get(f'per binsize {dataset_name}', bs[1])
             factor(_lib.F_GK, [], (d.gk_drp, d.gk_drt))
         if 'mock-bin-size' in cfg:
-            raise NotImplementedError('mock-bin-size smoothing is not built into the B200 path yet.')
+            d.mock_bin_size = cfg.getfloat('mock-bin-size')
+            los = cfg.get('mock-los-smoothing', None)
+            names = []
+            if los == 'growth':
+                d.mock_los_mode, names = 1, ['growth_rate']
+                if d.idx_growth_rate < 0:
+                    raise KeyError('growth_rate')
+            elif los == 'amplitude':
+                d.mock_los_mode, names = 2, ['los_smooth_amp']
+                d.idx_los_smooth_amp = c('los_smooth_amp', True)
+            elif los == 'only-los':
+                d.mock_los_mode = 3
+            elif los is not None:
+                raise ValueError(f'Unknown mock LOS smoothing option {los}.')
+            factor(_lib.F_MOCKGK, names, (d.mock_bin_size, d.mock_los_mode))
 
         if is_peak:
             d.idx_sigmaNL[0], d.idx_sigmaNL[1] = c('sigmaNL_par'), c('sigmaNL_per')
