@@ -311,7 +311,10 @@ def main():
         gemm_ms = sum(stage_ms[s] for s in flops)
         achieved = sum(flops.values()) / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
         n_eval = sum(engine.n_eval)
-        n_grid_eval = n_eval - sum(engine.n_moment(ci) for ci in range(len(engine.infos)))
+        n_moment = sum(engine.n_moment(ci) for ci in range(len(engine.infos)))
+        n_own = sum(sum(1 for d in info['evals'] if d.table_owner < 0 and not d.frozen)
+                    for info in engine.infos)
+        n_grid_eval = n_own - n_moment
         grid_bytes = 6512000.0 * n_grid_eval * B
         kernels = {s: {'ms_per_step': stage_ms[s], 'launch_groups_per_step': cnt_stage[i] / args.steps}
                    for i, s in enumerate(STAGES)}
@@ -327,7 +330,10 @@ def main():
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
             'data': 'synthetic',
             'config': {'workload': WORKLOAD, 'batch_per_gpu': B, 'n_theta': len(engine.sampled),
-                       'evaluations_per_chi2': n_eval, 'evaluations_in_moment_form': n_eval - n_grid_eval,
+                       'evaluations_per_chi2': n_eval,
+                       'evaluations_through_pk_ell': n_grid_eval,
+                       'evaluations_in_moment_form': n_moment,
+                       'evaluations_sharing_tables': n_eval - n_grid_eval - n_moment,
                        'l2': 'inputs larger than L2: ~1.6 GB of static operands + ~2 GB of workspace '
                              'streamed per step'},
             'clocks': clock_info,
@@ -337,11 +343,25 @@ def main():
             'gpu_launches': int(launches),
             'roofline': {'bound': 'tensor', 'kernel': 'dgemm_tn_kernel (DMMA FP64: Hankel, metal, distortion, C^-1)',
                          'achieved': achieved, 'peak': dgemm_peak, 'unit': 'TFLOP/s',
-                         'frac': achieved / dgemm_peak if dgemm_peak else None, 'traffic': None,
+                         'frac': achieved / dgemm_peak if dgemm_peak else None,
+                         # DRAM bytes of ONE launch of the largest GEMM (auto-correlation metal
+                         # matrices, M=1024 N=2500 K=37680, 12 splits) from the committed ncu --set full
+                         # capture: dram__bytes_read.sum 1.384 GB + dram__bytes_write.sum 0.231 GB
+                         # (profiles/r01_ncu_full_c2_raw.csv); algorithmic operand bytes 1.083 GB, the
+                         # rest is the split-K partial sums
+                         'traffic': 1.615e9 if B == 1024 else None,
+                         'traffic_source': 'profiles/r01_ncu_full_c2_raw.csv (dgemm_tn_kernel<0>, grid 8x20x12)',
                          'peak_source': 'cuBLAS FP64 8192^3 measured live in this run (MEASURED_PEAKS.json has no '
                                         'FP64 figure); algorithmic flops per SURVEY.md 8d',
                          'share_of_step': gemm_ms / ms_per_step},
-            'roofline_pk_ell': {'bound': 'fp64 alu', 'dfma_probe_tflops': dfma_peak,
+            # 15.5 FP64 instructions per grid point and vector in the Lorentzian kernels (SASS main
+            # loop: 155 per 10 point-vectors), counted as FMAs against the measured DFMA peak
+            'roofline_pk_ell': {'bound': 'fp64 alu', 'peak': dfma_peak, 'unit': 'TFLOP/s (FP64 instr x 2)',
+                                'achieved': (2 * 15.5 * 814000.0 * n_grid_eval * B / (stage_ms['pk_ell'] * 1e-3) / 1e12
+                                             if stage_ms['pk_ell'] > 0 else None),
+                                'frac': (2 * 15.5 * 814000.0 * n_grid_eval * B / (stage_ms['pk_ell'] * 1e-3) / 1e12
+                                         / dfma_peak if stage_ms['pk_ell'] > 0 and dfma_peak else None),
+                                'ncu_fp64_pipe_active': [0.726, 0.674],
                                 'share_of_step': stage_ms['pk_ell'] / ms_per_step},
             'kernels': kernels,
             'cpu_baseline': base,
