@@ -87,6 +87,7 @@ int upload_padded(DevBuf& buf, const double* host, long long rows, long long col
 
 struct Hankel {
   int n_ell = 0, n_out = 0, n_out_pad = 0, bounds_error = 1;
+  double x0[vg::PK_MAX_ELL] = {0, 0, 0, 0}, x1[vg::PK_MAX_ELL] = {0, 0, 0, 0};
   int ells[vg::PK_MAX_ELL] = {0, 0, 0, 0};
   DevBuf xk;    // [n_ell][n_out_pad]
   DevBuf op;    // [n_ell][2*n_out_pad][nk_pad]
@@ -385,7 +386,11 @@ int vg_plan_add_hankel(vg_plan* plan, int32_t n_ell, const int32_t* ells, int32_
   VG_REQUIRE(plan && n_ell == plan->n_ell && n_out > 3, "bad hankel operator");
   std::unique_ptr<Hankel> h(new Hankel);
   h->n_ell = n_ell; h->n_out = n_out; h->n_out_pad = pad16(n_out) ; h->bounds_error = bounds_error;
-  for (int l = 0; l < n_ell; ++l) h->ells[l] = ells[l];
+  for (int l = 0; l < n_ell; ++l) {
+    h->ells[l] = ells[l];
+    h->x0[l] = xk[(size_t)l * n_out];
+    h->x1[l] = xk[(size_t)l * n_out + n_out - 1];
+  }
   VG_TRY(h->xk.alloc((size_t)n_ell * h->n_out_pad * 8));
   VG_CUDA_CHECK(cudaMemcpy2D(h->xk.p, (size_t)h->n_out_pad * 8, xk, (size_t)n_out * 8,
                              (size_t)n_out * 8, n_ell, cudaMemcpyHostToDevice));
@@ -666,8 +671,9 @@ constexpr int NUM_SMS = 148;
 
 // split-K so that the CTA count fills whole waves of the 148 SMs (1 CTA/SM): the split count
 // with the best wave efficiency, keeping >= 16 K-tiles per split
-int pick_splits(long long tiles, int ktiles) {
+int pick_splits(long long tiles, int ktiles, int ctas_per_sm = 1) {
   int splits = 1;
+  const int NUM_SMS = ::NUM_SMS * ctas_per_sm;   // CTA slots of one wave
   if (tiles < 8 * NUM_SMS) {
     double best = 0.0;
     const int max_splits = (int)std::min<long long>(32, std::max(1, ktiles / 16));
@@ -691,9 +697,10 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
   g.A = A; g.B = B; g.M = M; g.N = N; g.K = K; g.lda = lda; g.ldb = ldb; g.ldc = ldc;
   g.batch = batch; g.strideA = strideA; g.strideB = strideB; g.strideC = strideC;
   g.alpha = 1.0; g.beta = 0.0;
-  const long long tiles = (long long)vg_cdiv(M, vg::GEMM_BM) * vg_cdiv(N, vg::GEMM_BN) * batch;
+  const int bm = vg::gemm_tile_m(M);
+  const long long tiles = (long long)vg_cdiv(M, bm) * vg_cdiv(N, vg::GEMM_BN) * batch;
   const int ktiles = K / vg::GEMM_BK;
-  const int splits = pick_splits(tiles, ktiles);
+  const int splits = pick_splits(tiles, ktiles, bm == vg::GEMM_BM ? 1 : 2);
   g.splits = std::max(1, splits);
   if (g.splits == 1) {
     g.C = C;
@@ -892,7 +899,11 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     const int n_gather = (int)L.gather_ids.size();
     vg::XiArgs a{};
     a.h.n_ell = h.n_ell; a.h.n_out = h.n_out; a.h.n_out_pad = h.n_out_pad; a.h.bounds_error = h.bounds_error;
-    for (int l = 0; l < vg::PK_MAX_ELL; ++l) a.h.ells[l] = h.ells[l];
+    for (int l = 0; l < vg::PK_MAX_ELL; ++l) {
+      a.h.ells[l] = h.ells[l];
+      a.h.x0[l] = h.x0[l]; a.h.x1[l] = h.x1[l];
+      a.h.inv_dx[l] = l < h.n_ell ? (double)(h.n_out - 1) / (h.x1[l] - h.x0[l]) : 0.0;
+    }
     a.h.xk = h.xk.as<double>();
     a.evals = c.d_evals.as<vg_eval_desc>(); a.n_eval = E;
     a.pfull = plan->w_pfull.as<double>(); a.npf = plan->npf; a.B = (int)Bc;
@@ -1050,7 +1061,8 @@ int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* in
   g.A = diff; g.B = invcov; g.M = (int)Bc; g.N = n; g.K = ld; g.lda = ld; g.ldb = ld;
   g.batch = 1; g.alpha = 1.0; g.beta = 0.0;
   const int n_tiles0 = vg_cdiv(n, vg::GEMM_BN);
-  g.splits = pick_splits((long long)vg_cdiv(Bc, vg::GEMM_BM) * n_tiles0, ld / vg::GEMM_BK);
+  const int bm = vg::gemm_tile_m((int)Bc);
+  g.splits = pick_splits((long long)vg_cdiv(Bc, bm) * n_tiles0, ld / vg::GEMM_BK, bm == vg::GEMM_BM ? 1 : 2);
   const int n_tiles = n_tiles0 * g.splits;
   VG_TRY(plan->w_partial.ensure((size_t)Bc * n_tiles * 8));
   g.C = plan->w_partial.as<double>(); g.ldc = n_tiles;

@@ -52,15 +52,22 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
-template <int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_tn_kernel(GemmArgs g) {
+// BM = 128: 2 x 4 warps, warp tile 64 x 32.  BM = 32 (batches of a few vectors: the scalar API,
+// gradient stencils): 1 x 8 warps, warp tile 32 x 16 -- a 128-row tile would spend its DMMA
+// cycles on rows that do not exist, and the launch is bound by streaming the operator anyway.
+template <int EPI, int BM>
+__global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kernel(GemmArgs g) {
+  constexpr int MI = BM == 128 ? 8 : 4;                     // 8-row fragments per warp
+  constexpr int WARPS_M = BM / (MI * 8), WARPS_N = 8 / WARPS_M;
+  constexpr int NJ = GEMM_BN / (WARPS_N * 8);               // 8-column fragments per warp
+  constexpr int A_CHUNKS = BM * 8 / GEMM_THREADS;           // 16-byte chunks of the A tile per thread
   extern __shared__ __align__(16) double smem[];
   double* As = smem;                                        // [STAGES][BM][LDS]
-  double* Bs = smem + GEMM_STAGES * GEMM_BM * GEMM_LDS;     // [STAGES][BN][LDS]
+  double* Bs = smem + GEMM_STAGES * BM * GEMM_LDS;          // [STAGES][BN][LDS]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int wm = warp >> 2, wn = warp & 3;                  // 2 x 4 warps
-  const int m0 = blockIdx.x * GEMM_BM, n0 = blockIdx.y * GEMM_BN;
+  const int wm = warp / WARPS_N, wn = warp % WARPS_N;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * GEMM_BN;
   const int bz = blockIdx.z / g.splits, sp = blockIdx.z % g.splits;
 
   const int ktiles_total = g.K / GEMM_BK;
@@ -75,26 +82,31 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_tn_kernel(GemmArgs g) {
   // global -> smem mapping: 128 rows x 8 chunks of 16 B per operand, 4 chunks per thread
   auto load_stage = [&](int stage, int kt) {
     const int k0 = (kt_begin + kt) * GEMM_BK;
-    double* as = As + stage * GEMM_BM * GEMM_LDS;
+    double* as = As + stage * BM * GEMM_LDS;
     double* bs = Bs + stage * GEMM_BN * GEMM_LDS;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      int c = tid + i * GEMM_THREADS;        // 0..1023
+    for (int i = 0; i < A_CHUNKS; ++i) {
+      int c = tid + i * GEMM_THREADS;
       int row = c >> 3, ch = c & 7;
       int gm = m0 + row;
       bool p = gm < g.M;
       cp_async16(as + row * GEMM_LDS + ch * 2, A + (long long)(p ? gm : 0) * g.lda + k0 + ch * 2, p);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      int c = tid + i * GEMM_THREADS;        // 0..1023
+      int row = c >> 3, ch = c & 7;
       int gn = n0 + row;
       bool q = gn < g.N;
       cp_async16(bs + row * GEMM_LDS + ch * 2, B + (long long)(q ? gn : 0) * g.ldb + k0 + ch * 2, q);
     }
   };
 
-  double acc[8][4][2];
+  double acc[MI][NJ][2];
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
+  for (int i = 0; i < MI; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+    for (int j = 0; j < NJ; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
 #pragma unroll
   for (int s = 0; s < GEMM_STAGES - 1; ++s) {
@@ -111,19 +123,19 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_tn_kernel(GemmArgs g) {
       if (nk < nkt) load_stage(nk % GEMM_STAGES, nk);
       cp_async_commit();
     }
-    const double* as = As + (kt % GEMM_STAGES) * GEMM_BM * GEMM_LDS + (wm * 64 + frow) * GEMM_LDS + fcol;
-    const double* bs = Bs + (kt % GEMM_STAGES) * GEMM_BN * GEMM_LDS + (wn * 32 + frow) * GEMM_LDS + fcol;
+    const double* as = As + (kt % GEMM_STAGES) * BM * GEMM_LDS + (wm * MI * 8 + frow) * GEMM_LDS + fcol;
+    const double* bs = Bs + (kt % GEMM_STAGES) * GEMM_BN * GEMM_LDS + (wn * NJ * 8 + frow) * GEMM_LDS + fcol;
 #pragma unroll
     for (int kk = 0; kk < GEMM_BK; kk += 4) {
-      double a[8], b[4];
+      double a[MI], b[NJ];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) a[i] = as[i * 8 * GEMM_LDS + kk];
+      for (int i = 0; i < MI; ++i) a[i] = as[i * 8 * GEMM_LDS + kk];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) b[j] = bs[j * 8 * GEMM_LDS + kk];
+      for (int j = 0; j < NJ; ++j) b[j] = bs[j * 8 * GEMM_LDS + kk];
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+      for (int i = 0; i < MI; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        for (int j = 0; j < NJ; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
     }
   }
   cp_async_wait<0>();
@@ -131,12 +143,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_tn_kernel(GemmArgs g) {
   if (EPI == GEMM_STORE) {
     double* C = g.C + (long long)bz * g.strideC + (long long)sp * g.split_stride;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      int m = m0 + wm * 64 + i * 8 + frow;
+    for (int i = 0; i < MI; ++i) {
+      int m = m0 + wm * MI * 8 + i * 8 + frow;
       if (m >= g.M) continue;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        int n = n0 + wn * 32 + j * 8 + fcol * 2;
+      for (int j = 0; j < NJ; ++j) {
+        int n = n0 + wn * NJ * 8 + j * 8 + fcol * 2;
         double* c = C + (long long)m * g.ldc + n;
         double v0 = g.alpha * acc[i][j][0], v1 = g.alpha * acc[i][j][1];
         if (n + 1 < g.N) {
@@ -151,16 +163,16 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_tn_kernel(GemmArgs g) {
   } else {
     // ROWDOT: deterministic reduction of acc[m,n]*D[m,n] over this CTA's 128 columns
     __syncthreads();
-    double* red = smem;   // [BM][4] partials per n-warp
+    double* red = smem;   // [BM][WARPS_N] partials per n-warp
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      int ml = wm * 64 + i * 8 + frow;
+    for (int i = 0; i < MI; ++i) {
+      int ml = wm * MI * 8 + i * 8 + frow;
       int m = m0 + ml;
       double s = 0.0;
       if (m < g.M) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          int n = n0 + wn * 32 + j * 8 + fcol * 2;
+        for (int j = 0; j < NJ; ++j) {
+          int n = n0 + wn * NJ * 8 + j * 8 + fcol * 2;
           const double* d = g.D + (long long)m * g.ldd + n;
           if (n < g.N) s += acc[i][j][0] * d[0];
           if (n + 1 < g.N) s += acc[i][j][1] * d[1];
@@ -168,13 +180,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_tn_kernel(GemmArgs g) {
       }
       s += __shfl_xor_sync(0xffffffffu, s, 1);
       s += __shfl_xor_sync(0xffffffffu, s, 2);
-      if (fcol == 0) red[ml * 4 + wn] = s;
+      if (fcol == 0) red[ml * WARPS_N + wn] = s;
     }
     __syncthreads();
-    if (tid < GEMM_BM) {
+    if (tid < BM) {
       int m = m0 + tid;
       if (m < g.M) {
-        double s = (red[tid * 4 + 0] + red[tid * 4 + 1]) + (red[tid * 4 + 2] + red[tid * 4 + 3]);
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < WARPS_N; w += 4)
+          s += (red[tid * WARPS_N + w] + red[tid * WARPS_N + w + 1]) +
+               (red[tid * WARPS_N + w + 2] + red[tid * WARPS_N + w + 3]);
         // linear in the K range: each split contributes its own partial column
         g.C[(long long)bz * g.strideC + (long long)m * g.ldc + blockIdx.y * g.splits + sp] = g.alpha * s;
       }
@@ -192,24 +208,42 @@ __global__ void reduce_splits_kernel(const double* __restrict__ W, double* __res
   C[i] = s;
 }
 
+constexpr int GEMM_BM_SMALL = 32;
+constexpr int GEMM_SMEM_SMALL = GEMM_STAGES * (GEMM_BM_SMALL + GEMM_BN) * GEMM_LDS * 8;
+// rows of A at or below which the 32-row tile is used
+constexpr int GEMM_SMALL_M = 96;
+inline int gemm_tile_m(int M) { return M <= GEMM_SMALL_M ? GEMM_BM_SMALL : GEMM_BM; }
+
 inline int launch_dgemm(const GemmArgs& g, int epilogue, cudaStream_t stream) {
   if (g.K % GEMM_BK != 0 || (g.lda & 1) || (g.ldb & 1) || g.M <= 0 || g.N <= 0) {
     vg_set_error("dgemm: bad shape M=%d N=%d K=%d lda=%lld ldb=%lld", g.M, g.N, g.K, g.lda, g.ldb);
     return VG_ERR_ARG;
   }
-  dim3 grid(vg_cdiv(g.M, GEMM_BM), vg_cdiv(g.N, GEMM_BN), g.batch * g.splits);
+  const int bm = gemm_tile_m(g.M);
+  dim3 grid(vg_cdiv(g.M, bm), vg_cdiv(g.N, GEMM_BN), g.batch * g.splits);
   static bool attr_set = false;
   if (!attr_set) {
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE>,
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE, GEMM_BM>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT>,
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE, GEMM_BM_SMALL>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_SMALL));
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM_SMALL>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_SMALL));
     attr_set = true;
   }
-  if (epilogue == GEMM_STORE)
-    dgemm_tn_kernel<GEMM_STORE><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
-  else
-    dgemm_tn_kernel<GEMM_ROWDOT><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
+  if (bm == GEMM_BM) {
+    if (epilogue == GEMM_STORE)
+      dgemm_tn_kernel<GEMM_STORE, GEMM_BM><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
+    else
+      dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
+  } else {
+    if (epilogue == GEMM_STORE)
+      dgemm_tn_kernel<GEMM_STORE, GEMM_BM_SMALL><<<grid, GEMM_THREADS, GEMM_SMEM_SMALL, stream>>>(g);
+    else
+      dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM_SMALL><<<grid, GEMM_THREADS, GEMM_SMEM_SMALL, stream>>>(g);
+  }
   VG_CUDA_CHECK(cudaGetLastError());
   return VG_OK;
 }

@@ -22,6 +22,9 @@ struct HankelDev {
   int n_ell, n_out, n_out_pad, bounds_error;
   int ells[PK_MAX_ELL];
   const double* xk;        // [n_ell][n_out_pad] knots (log r)
+  // per multipole: ends of the knot vector and (n_out-1)/(x1-x0), the first guess of the
+  // interval search (host-computed, so they sit in the constant bank, not in registers)
+  double x0[PK_MAX_ELL], x1[PK_MAX_ELL], inv_dx[PK_MAX_ELL];
 };
 
 struct StaticXiDev {       // [which = rel l=1, rel l=3, asy l=0, asy l=2][pk_lin_sel]
@@ -84,12 +87,23 @@ __device__ __forceinline__ int knot_interval(const double* xk, int n, double x, 
   while (j < n - 2 && x >= xk[j + 1]) ++j;
   return j;
 }
+// same with the first guess from a precomputed (n-1)/(x1-x0); the correction loops make the
+// result independent of the guess
+__device__ __forceinline__ int knot_interval_inv(const double* xk, int n, double x, double x0, double x1,
+                                                 double inv_dx, bool* outside) {
+  *outside = !(x >= x0 && x <= x1);
+  int j = (int)floor((x - x0) * inv_dx);
+  j = max(0, min(n - 2, j));
+  while (j > 0 && x < xk[j]) --j;
+  while (j < n - 2 && x >= xk[j + 1]) ++j;
+  return j;
+}
 
 __device__ __forceinline__ double spline_eval(const double* xk, const double* y, const double* m,
                                               int j, double x) {
   const double h = xk[j + 1] - xk[j];
   const double t = (x - xk[j]) / h, a = 1.0 - t;
-  return a * y[j] + t * y[j + 1] + ((a * a * a - a) * m[j] + (t * t * t - t) * m[j + 1]) * (h * h / 6.0);
+  return a * y[j] + t * y[j + 1] + ((a * a * a - a) * m[j] + (t * t * t - t) * m[j + 1]) * (h * h * (1.0 / 6.0));
 }
 
 // (ap, at) from the fit parametrisation: vega/scale_parameters.py:79-125
@@ -203,7 +217,7 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
         if (d.single_ell >= 0 && a.h.ells[l] != d.single_ell) continue;
         const double* xk = a.h.xk + l * a.h.n_out_pad;
         bool outside;
-        const int j = knot_interval(xk, a.h.n_out, x, &outside);
+        const int j = knot_interval_inv(xk, a.h.n_out, x, a.h.x0[l], a.h.x1[l], a.h.inv_dx[l], &outside);
         if (outside && a.h.bounds_error) bad |= VG_STATUS_BOUNDS;
         const double v = spline_eval(xk, sm_tab + l * row, sm_tab + l * row + a.h.n_out_pad, j, x);
         xi += d.single_ell >= 0 ? v : v * legendre_eval(a.h.ells[l], mu2);
