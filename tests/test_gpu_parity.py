@@ -216,3 +216,58 @@ def test_mock_bin_size_smoothing(los):
     pars = {'ap': 1.02, 'beta_LYA': 1.5}
     assert_xi_close(vega.compute_model(pars), oracle.compute_model(pars), f'mock-bin-size {los}')
     assert abs(vega.chi2(pars) - oracle.chi2(pars)) <= CHI2_ATOL
+
+
+def test_desi_shaped_model_grid_larger_than_the_data_grid(tmp_path):
+    """The distortion-matrix file carries its own grid (vega/data.py:441-473): the model and
+    the distorted model live on 55x55 bins out to 220 Mpc/h while the data stay on 50x50 bins
+    out to 200 -- the DESI layout (5625/11250 model bins for 2500/5000 data bins), reduced.
+    The masks must pick the same bins from both grids and chi2 only needs the masked rows."""
+    import configparser
+    from oracle.vega_oracle import Oracle
+    from helpers import static_tables
+    from vega_b200 import VegaInterface
+    n_p = n_t = 55
+    size = 4.0
+    rp = (np.arange(n_p) + 0.5) * size
+    rt = (np.arange(n_t) + 0.5) * size
+    rp_grid, rt_grid = [g.ravel() for g in np.meshgrid(rp, rt, indexing='ij')]
+    dmat = synthetic.distortion_matrix(n_p, n_t)
+    dmat_path = tmp_path / 'dmat_55.fits'
+    fitsio.write_tables(dmat_path, [
+        ('DMAT', {'RPMIN': 0., 'RPMAX': n_p * size, 'RTMAX': n_t * size, 'NP': n_p, 'NT': n_t,
+                  'COEFMOD': 1}, {'DM': dmat}),
+        ('ATTRI', {}, {'RP': rp_grid, 'RT': rt_grid, 'Z': np.full(rp_grid.size, 2.33)})])
+    corr = configparser.ConfigParser()
+    corr.optionxform = lambda o: o
+    corr.read(utils.find_file('configs/configs/lya_lyaxlya_lya.ini'))
+    corr['data']['distortion-file'] = str(dmat_path)
+    corr_path = tmp_path / 'lyaxlya.ini'
+    with open(corr_path, 'w') as f:
+        corr.write(f)
+    main = configparser.ConfigParser()
+    main.optionxform = lambda o: o
+    main.read(utils.find_file('configs/configs/main.ini'))
+    main['data sets']['ini files'] = str(corr_path)
+    main_path = tmp_path / 'main.ini'
+    with open(main_path, 'w') as f:
+        main.write(f)
+
+    vega = VegaInterface(str(main_path))
+    data = vega.data['lyaxlya']
+    assert data.model_coordinates.r_grid.size == n_p * n_t and data.full_data_size == 2500
+    assert int(data.model_mask.sum()) == int(data.data_mask.sum())
+    synthetic.inject_dense_operands(vega, with_distortion=False, with_metals=False)   # covariance only
+    oracle = Oracle(vega, tables=static_tables())
+    synthetic.draw_mock_data(vega, oracle.compute_model())
+    names = list(vega.sample_params['limits'])
+    theta = synthetic.draw_theta(vega, 3, width=0.3)
+    models, status = vega.compute_model_batch(theta)
+    chi2 = vega.chi2_batch(theta)
+    assert not status.any() and models['lyaxlya'].shape == (3, n_p * n_t)
+    for b in range(3):
+        pars = dict(zip(names, theta[b]))
+        ref = oracle.compute_model(pars)
+        assert_xi_close({n: models[n][b] for n in ref}, ref, f'vector {b}')
+        ref_chi2 = oracle.chi2(pars)
+        assert abs(chi2[b] - ref_chi2) <= CHI2_ATOL * max(1.0, abs(ref_chi2) / 1e4), (chi2[b], ref_chi2)

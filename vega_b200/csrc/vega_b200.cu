@@ -90,6 +90,7 @@ struct Hankel {
   double x0[vg::PK_MAX_ELL] = {0, 0, 0, 0}, x1[vg::PK_MAX_ELL] = {0, 0, 0, 0};
   int ells[vg::PK_MAX_ELL] = {0, 0, 0, 0};
   DevBuf xk;    // [n_ell][n_out_pad]
+  DevBuf inv_h; // [n_ell][n_out_pad] reciprocal knot spacings
   DevBuf op;    // [n_ell][2*n_out_pad][nk_pad]
 };
 
@@ -394,6 +395,13 @@ int vg_plan_add_hankel(vg_plan* plan, int32_t n_ell, const int32_t* ells, int32_
   VG_TRY(h->xk.alloc((size_t)n_ell * h->n_out_pad * 8));
   VG_CUDA_CHECK(cudaMemcpy2D(h->xk.p, (size_t)h->n_out_pad * 8, xk, (size_t)n_out * 8,
                              (size_t)n_out * 8, n_ell, cudaMemcpyHostToDevice));
+  {
+    std::vector<double> inv((size_t)n_ell * h->n_out_pad, 0.0);
+    for (int l = 0; l < n_ell; ++l)
+      for (int j = 0; j + 1 < n_out; ++j)
+        inv[(size_t)l * h->n_out_pad + j] = 1.0 / (xk[(size_t)l * n_out + j + 1] - xk[(size_t)l * n_out + j]);
+    VG_TRY(upload(h->inv_h, inv.data(), inv.size()));
+  }
   // op[l][2][n_out][nk] -> device [l][2*n_out_pad][nk_pad], second derivatives at row n_out_pad
   const size_t rows = 2 * (size_t)h->n_out_pad;
   VG_TRY(h->op.alloc((size_t)n_ell * rows * plan->nk_pad * 8));
@@ -905,6 +913,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
       a.h.inv_dx[l] = l < h.n_ell ? (double)(h.n_out - 1) / (h.x1[l] - h.x0[l]) : 0.0;
     }
     a.h.xk = h.xk.as<double>();
+    a.h.inv_h = h.inv_h.as<double>();
     a.evals = c.d_evals.as<vg_eval_desc>(); a.n_eval = E;
     a.pfull = plan->w_pfull.as<double>(); a.npf = plan->npf; a.B = (int)Bc;
     a.tables = tables_full; a.n_full = Ef;

@@ -22,6 +22,7 @@ struct HankelDev {
   int n_ell, n_out, n_out_pad, bounds_error;
   int ells[PK_MAX_ELL];
   const double* xk;        // [n_ell][n_out_pad] knots (log r)
+  const double* inv_h;     // [n_ell][n_out_pad] 1 / (xk[j+1] - xk[j]), host-computed
   // per multipole: ends of the knot vector and (n_out-1)/(x1-x0), the first guess of the
   // interval search (host-computed, so they sit in the constant bank, not in registers)
   double x0[PK_MAX_ELL], x1[PK_MAX_ELL], inv_dx[PK_MAX_ELL];
@@ -125,6 +126,14 @@ __device__ __forceinline__ void rescale_coords(double r, double mu, double ap, d
   mu2 = rp / r2;
 }
 
+// same with the reciprocal knot spacing supplied (one multiplication instead of a division)
+__device__ __forceinline__ double spline_eval_inv(const double* xk, const double* y, const double* m,
+                                                  int j, double x, double inv_h) {
+  const double h = xk[j + 1] - xk[j];
+  const double t = (x - xk[j]) * inv_h, a = 1.0 - t;
+  return a * y[j] + t * y[j + 1] + ((a * a * a - a) * m[j] + (t * t * t - t) * m[j + 1]) * (h * h * (1.0 / 6.0));
+}
+
 __device__ __forceinline__ double static_xi_eval(const StaticXiDev& sx, int which, double logr) {
   const int n = sx.n[which];
   const double* t = sx.tab[which];
@@ -219,7 +228,8 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
         bool outside;
         const int j = knot_interval_inv(xk, a.h.n_out, x, a.h.x0[l], a.h.x1[l], a.h.inv_dx[l], &outside);
         if (outside && a.h.bounds_error) bad |= VG_STATUS_BOUNDS;
-        const double v = spline_eval(xk, sm_tab + l * row, sm_tab + l * row + a.h.n_out_pad, j, x);
+        const double v = spline_eval_inv(xk, sm_tab + l * row, sm_tab + l * row + a.h.n_out_pad, j, x,
+                                         __ldg(a.h.inv_h + l * a.h.n_out_pad + j));
         xi += d.single_ell >= 0 ? v : v * legendre_eval(a.h.ells[l], mu2);
       }
     }
