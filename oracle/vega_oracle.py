@@ -807,12 +807,38 @@ class Oracle:
         lp = self.local_params(params)
         return sum((lp[p] - pr[0])**2 / pr[1]**2 for p, pr in self.s.priors.items())
 
-    def chi2(self, params=None, direct_pk=None):
+    def compute_marg_coeff(self, model):
+        """vega/vega_interface.py:546-579: template amplitudes = marg_diff2coeff_matrix . (d - m)."""
+        s = self.s
+        out = {}
+        for n in s.corr_items:
+            d = s.data[n]
+            vec = d.masked_mc_mock if self.monte_carlo else d.masked_data_vec
+            diff = vec - model[n][d.model_mask]
+            if d.marg_diff2coeff_matrix is not None:
+                out[n] = d.marg_diff2coeff_matrix.dot(diff)
+        return out
+
+    def chi2(self, params=None, direct_pk=None, return_marg_coeff=False):
         """vega/vega_interface.py:250-325."""
         try:
             model = self.compute_model(params, direct_pk)
         except OracleModelError:
-            return 1e100
+            return (1e100, None) if return_marg_coeff else 1e100
+        s = self.s
+        marg_in_fit = getattr(s, 'marginalize_in_fit', False)
+        marg_coeff = None
+        if return_marg_coeff or marg_in_fit:          # :282-292
+            marg_coeff = self.compute_marg_coeff(model)
+        if marg_in_fit:
+            for n in s.data:
+                if s.data[n].marg_templates is not None:
+                    model[n] = model[n] + s.data[n].marg_templates.dot(marg_coeff[n])
+        if return_marg_coeff:
+            return self._chi2_of_model(model, params), marg_coeff
+        return self._chi2_of_model(model, params)
+
+    def _chi2_of_model(self, model, params):
         s = self.s
         if getattr(s, '_use_global_cov', False):
             if self.monte_carlo:

@@ -39,46 +39,105 @@ PERTURBED['full_fast'] = PERTURBED['full']
 CONFIGS = {'full': 'tests/full_configs/main.ini', 'c1': 'tests/configs/main.ini'}
 
 
-def fast_metals_copy(main_ini, tmp_dir):
-    """Copy of a reference configuration with `fast_metals = True` under every [model]
-    (vega/metals.py:58: the metal caches of compute_xi_metal_metal / _cross_main)."""
+def modified_copy(main_ini, tmp_dir, model=None, control=None, data=None):
+    """Copy of a reference configuration with extra options under every correlation's
+    [model] / [data] section and under the main file's [control]."""
     import configparser
+    from vega.utils import find_file
     tmp_dir.mkdir(parents=True, exist_ok=True)
     main = configparser.ConfigParser()
     main.optionxform = lambda option: option
-    main.read(main_ini)
+    main.read(find_file(main_ini))
     new_paths = []
     for path in main['data sets']['ini files'].split():
         cfg = configparser.ConfigParser()
         cfg.optionxform = lambda option: option
-        from vega.utils import find_file
         cfg.read(find_file(os.path.expandvars(path)))
-        cfg['model']['fast_metals'] = 'True'
+        for key, value in (model or {}).items():
+            cfg['model'][key] = str(value)
+        for key, value in (data or {}).items():
+            cfg['data'][key] = str(value)
         new_path = tmp_dir / Path(path).name
         with open(new_path, 'w') as f:
             cfg.write(f)
         new_paths.append(str(new_path))
     main['data sets']['ini files'] = ' '.join(new_paths)
+    if control:
+        if 'control' not in main:
+            main['control'] = {}
+        for key, value in control.items():
+            main['control'][key] = str(value)
     out = tmp_dir / 'main.ini'
     with open(out, 'w') as f:
         main.write(f)
     return str(out)
 
 
+def fast_metals_copy(main_ini, tmp_dir):
+    """`fast_metals = True` under every [model] (vega/metals.py:58: the metal caches of
+    compute_xi_metal_metal / _cross_main)."""
+    return modified_copy(main_ini, tmp_dir, model={'fast_metals': True})
+
+
+# small-scale marginalisation (vega/data.py:96-128,762-828; vega/vega_interface.py:282-292,546-579)
+MARG_CUTS = {'marginalize-below-rtmax': 16., 'marginalize-below-rpmax': 16.}
+MARG_FIT = {'marginalize-all-rmin-cuts': True, 'marginalize-prior-sigma': 5.0}
+
+
+def write_dmat_file(path, n_p=55, n_t=55, size=4.0):
+    """Distortion-matrix file with its own (larger) grid, as tests/test_gpu_parity.py writes it."""
+    from vega_b200 import fitsio, synthetic
+    rp = (np.arange(n_p) + 0.5) * size
+    rt = (np.arange(n_t) + 0.5) * size
+    rp_grid, rt_grid = [g.ravel() for g in np.meshgrid(rp, rt, indexing='ij')]
+    fitsio.write_tables(path, [
+        ('DMAT', {'RPMIN': 0., 'RPMAX': n_p * size, 'RTMAX': n_t * size, 'NP': n_p, 'NT': n_t,
+                  'COEFMOD': 1}, {'DM': synthetic.distortion_matrix(n_p, n_t)}),
+        ('ATTRI', {}, {'RP': rp_grid, 'RT': rt_grid, 'Z': np.full(rp_grid.size, 2.33)})])
+    return str(path)
+
+
 def main():
     out, meta = {}, {}
     CONFIGS['full_fast'] = fast_metals_copy(CONFIGS['full'], Path('/tmp/vega_golden_fast'))
+    # (the reference needs a distortion matrix from a file here: with the identity stand-in,
+    # np.eye(...).dot(sparse templates) is not a sparse matrix and vega/data.py:817 fails)
+    dmat = write_dmat_file(Path('/tmp/vega_golden_dmat55.fits'))
+    CONFIGS['c1_marg'] = modified_copy(CONFIGS['c1'], Path('/tmp/vega_golden_marg'), model=MARG_CUTS,
+                                       data={'distortion-file': dmat})
+    CONFIGS['c1_marg_fit'] = modified_copy(CONFIGS['c1'], Path('/tmp/vega_golden_marg_fit'), model=MARG_FIT,
+                                           control={'marginalize-in-fit': True},
+                                           data={'distortion-file': dmat})
+    PERTURBED['c1_marg'] = PERTURBED['c1_marg_fit'] = PERTURBED['c1']
+    notes = {'full_fast': CONFIGS['full'] + ' + fast_metals = True',
+             'c1_marg': f"{CONFIGS['c1']} + [model] {MARG_CUTS} + distortion-file (55x55 bins)",
+             'c1_marg_fit': f"{CONFIGS['c1']} + [model] {MARG_FIT} + [control] marginalize-in-fit "
+                            "+ distortion-file (55x55 bins, synthetic.distortion_matrix)"}
+    only = sys.argv[1:]
+    if only:      # regenerate a subset, keep the rest of the stored outputs
+        old = np.load(REPO / 'tests' / 'golden' / 'reference_outputs.npz')
+        out.update({k: old[k] for k in old.files if k.split('/')[0] not in only})
+        meta.update({k: v for k, v in json.loads(
+            (REPO / 'tests' / 'golden' / 'reference_outputs.json').read_text()).items() if k not in only})
     for key, ini in CONFIGS.items():
+        if only and key not in only:
+            continue
         vega = VegaInterface(ini)
         cases = [{}] + PERTURBED[key]
-        meta[key] = {'ini': CONFIGS['full'] + ' + fast_metals = True' if key == 'full_fast' else ini,
-                     'cases': cases, 'corr': list(vega.corr_items)}
+        meta[key] = {'ini': notes.get(key, ini), 'cases': cases, 'corr': list(vega.corr_items)}
         for i, pars in enumerate(cases):
             model = vega.compute_model(pars, run_init=True)
             for name, xi in model.items():
                 out[f'{key}/{i}/xi/{name}'] = np.asarray(xi, dtype=float)
             out[f'{key}/{i}/chi2'] = np.array(vega.chi2(pars))
             out[f'{key}/{i}/log_lik'] = np.array(vega.log_lik(pars))
+            if key.startswith('c1_marg'):
+                chi2, coeff = vega.chi2(pars, return_marg_coeff=True)
+                for name, c in coeff.items():
+                    out[f'{key}/{i}/marg_coeff/{name}'] = np.asarray(c, dtype=float)
+                model = vega.compute_model(pars, run_init=False, marg_coeff=coeff)
+                for name, xi in model.items():
+                    out[f'{key}/{i}/xi_marg/{name}'] = np.asarray(xi, dtype=float)
             print(key, i, float(out[f'{key}/{i}/chi2']), float(out[f'{key}/{i}/log_lik']))
     np.savez_compressed(REPO / 'tests' / 'golden' / 'reference_outputs.npz', **out)
     (REPO / 'tests' / 'golden' / 'reference_outputs.json').write_text(json.dumps(meta, indent=1))

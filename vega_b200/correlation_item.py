@@ -3,9 +3,9 @@
 Follows the attribute surface of the reference's vega/correlation_item.py:8-140
 that the data reader, the plan builder and the oracle consume: tracer names and
 types, the parsed ini sections, coordinate grids, the metal-correlation list.
-Small-scale marginalisation templates (vega/correlation_item.py:169-275) are not
-built yet; asking for them raises.
+plus the small-scale marginalisation templates (vega/correlation_item.py:169-275).
 """
+import numpy as np
 
 
 class CorrelationItem:
@@ -47,8 +47,6 @@ class CorrelationItem:
                 self.marginalize_small_scales[name] = value
         if model_cfg.getboolean('marginalize-all-rmin-cuts', False):
             self.marginalize_small_scales['all-rmin'] = True
-        if self.marginalize_small_scales:
-            raise NotImplementedError('Small-scale marginalisation templates are not built yet.')
         self.marginalize_small_scales_prior_sigma = model_cfg.getfloat(
             'marginalize-prior-sigma', 10.0)
         self.marginalize_match_data_bins = model_cfg.getboolean(
@@ -97,3 +95,48 @@ class CorrelationItem:
             return True
         return any(t in self.tracer1['name'] or t in self.tracer2['name']
                    for t in blind_tracers)
+
+    # -- small-scale marginalisation (vega/correlation_item.py:175-275) ------------------------
+    def get_undist_xi_marg_templates(self):
+        """Sparse [n_model, n_templates] matrix of indicator templates on the UNdistorted model
+        grid: one column per marginalised bin, or one per nearest distorted bin with
+        marginalize-match-data-bins.  The prior sigma is applied by the caller
+        (Data.get_dist_xi_marg_templates)."""
+        from scipy.sparse import csr_array
+        mc, cuts = self.model_coordinates, self.marginalize_small_scales
+        n = mc.rt_regular_grid.size
+        if 'all-rmin' in cuts:
+            # everything the small-scale part of the scale cuts removes, evaluated on the
+            # distorted grid and blown up to the finer model grid
+            dist = self.dist_model_coordinates
+            cb = mc.rp_nbins // dist.rp_nbins
+            keep_dist = dist.get_mask_scale_cuts(self.config['cuts'], small_scale_mask=True) \
+                .reshape(dist.rp_nbins, dist.rt_nbins)
+            keep = np.zeros((mc.rp_nbins, mc.rt_nbins), dtype=bool)
+            block = np.kron(keep_dist, np.ones((cb, cb), dtype=bool))
+            keep[:block.shape[0], :block.shape[1]] = block[:mc.rp_nbins, :mc.rt_nbins]
+            selected = ~keep.ravel()
+            print(f'Marginalizing distortion scales with {int(selected.sum())} points based on scale cuts.')
+        else:
+            selected = np.ones(n, dtype=bool)
+            if 'rtmax' in cuts:
+                selected &= mc.rt_regular_grid < cuts['rtmax']
+            if 'rtmin' in cuts:
+                selected &= mc.rt_regular_grid > cuts['rtmin']
+            if 'rpmax' in cuts:
+                selected &= np.abs(mc.rp_regular_grid) < cuts['rpmax']
+            if 'rpmin' in cuts:
+                selected &= np.abs(mc.rp_regular_grid) > cuts['rpmin']
+            if not selected.any():
+                raise ValueError('No common indices found for small-scale marginalization templates.')
+        bins = np.nonzero(selected)[0]
+        if self.marginalize_match_data_bins:
+            dist = self.dist_model_coordinates
+            d2 = (dist.rp_grid[None, :] - mc.rp_grid[bins][:, None])**2 \
+                + (dist.rt_grid[None, :] - mc.rt_grid[bins][:, None])**2
+            nearest = d2.argmin(axis=1)
+            columns = np.searchsorted(np.unique(nearest), nearest)
+            n_templates = np.unique(nearest).size
+        else:
+            columns, n_templates = np.arange(bins.size), bins.size
+        return csr_array((np.ones(bins.size), (bins, columns)), shape=(n, n_templates))

@@ -72,6 +72,8 @@ class Data:
         self.cov_marg_update = None
         self.marg_diff2coeff_matrix = None
         self.num_marg_modes = 0
+        if corr_item.marginalize_small_scales:
+            self._init_marginalization(marginalize_in_fit)
 
         self._cholesky = None
         self._scale = 1.
@@ -80,6 +82,73 @@ class Data:
         self.mc_mock = None
         self.masked_mc_mock = None
         self.effective_data_size = self.data_size - self.num_marg_modes
+
+    # -- small-scale marginalisation (vega/data.py:96-128,762-828) ------------------------------
+    def _init_marginalization(self, marginalize_in_fit):
+        """Templates for the marginalised bins pushed through the distortion matrix.  Default
+        mode: their prior covariance sigma^2 T T^T (SVD-compressed) is added to the masked
+        covariance, so the chi2 path is unchanged.  marginalize-in-fit: the covariance is left
+        alone and `marg_diff2coeff_matrix` = (T^T C^-1 T + S)^-1 T^T C^-1 gives the best-fit
+        template amplitudes from a residual (used by VegaInterface.chi2)."""
+        item = self.corr_item
+        self.marg_templates, self.cov_marg_update = self.get_dist_xi_marg_templates()
+        ntemps = self.marg_templates.shape[1]
+        self._inv_masked_cov = None
+        inv_cov = self.inv_masked_cov            # of the covariance BEFORE the update
+        self._inv_masked_cov = None
+        if not marginalize_in_fit:
+            self._cov_mat = np.array(self._cov_mat, dtype=float)
+            self._cov_mat[np.ix_(self.data_mask, self.data_mask)] += self.cov_marg_update
+            self.cov_is_identity = False
+            self._log_cov_det = None
+            self.variance = self._cov_mat.diagonal()
+        else:
+            self.cov_marg_update = None
+        t_masked = self.marg_templates[self.model_mask, :]
+        G = t_masked.T @ inv_cov
+        A = np.asarray((t_masked.T @ G.T).T)
+        if not (item.fit_marg_scales and item.marginalize_match_data_bins):
+            A = A + np.diag(np.full(ntemps, item.marginalize_small_scales_prior_sigma**-2))
+        self.marg_diff2coeff_matrix = np.linalg.inv(A).dot(np.asarray(G))
+
+    def marg_projector(self):
+        """Q = I - T_masked D2C on the masked bins: with the template amplitudes fitted on the fly
+        (vega/vega_interface.py:282-292) the residual entering chi2 is Q (d - m), so the
+        quadratic form is (d - m)^T [Q^T C^-1 Q] (d - m) -- one modified matrix for the device."""
+        if self.marg_diff2coeff_matrix is None:
+            return None
+        t_masked = self.marg_templates[self.model_mask, :]
+        return np.eye(int(self.model_mask.sum())) - np.asarray(t_masked @ self.marg_diff2coeff_matrix)
+
+    def get_dist_xi_marg_templates(self, factor=1e-8, return_AAT=True):
+        """(templates [n_dist, n_templates] sparse, covariance update on the masked bins)."""
+        from scipy.sparse import csr_array
+        item = self.corr_item
+        if not item.marginalize_small_scales:
+            raise ValueError('Marginalization not configured')
+        templates = item.get_undist_xi_marg_templates()
+        if not self.distortion_is_identity:
+            templates = csr_array(self._distortion_mat @ templates)
+        if item.fit_marg_scales:
+            self.data_mask = self.data_mask | self.data_coordinates.get_mask_marginalization_scales(
+                item.config['cuts'], item.marginalize_small_scales)
+            self.model_mask = self.model_mask | self.dist_model_coordinates.get_mask_marginalization_scales(
+                item.config['cuts'], item.marginalize_small_scales)
+            if self.data_mask.sum() != self.model_mask.sum():
+                raise ValueError(
+                    'Data and model masks should be the same after marginalization scale cuts.')
+            self._masked_data_vec = None
+        if not return_AAT:
+            return templates
+        t = (templates * item.marginalize_small_scales_prior_sigma)[self.model_mask, :].toarray()
+        print(f'  There are {templates.shape[1]} templates. '
+              'SVD of template matrix to remove degenerate modes.')
+        u, sv, _ = np.linalg.svd(t, full_matrices=False)
+        keep = sv > factor * sv[0]
+        u, sv = u[:, keep], sv[keep]
+        print(f'  There are {keep.sum()} remaining modes for marginalization.')
+        self.num_marg_modes = int(keep.sum())
+        return templates, np.dot(u * sv**2, u.T)
 
     # -- properties with the reference's names ------------------------------------
     @property

@@ -754,6 +754,14 @@ class PlanBuilder:
                 plan.set_data(ci, data)
         if getattr(vega, '_use_global_cov', False):
             inv = _f64(vega.masked_global_invcov)
+            if getattr(vega, 'marginalize_in_fit', False):
+                from scipy.linalg import block_diag
+                blocks = []
+                for name in vega.corr_items:
+                    proj = vega.data[name].marg_projector()
+                    blocks.append(np.eye(int(vega.data[name].model_mask.sum())) if proj is None else proj)
+                proj = block_diag(*blocks)
+                inv = _f64(proj.T @ inv @ proj)
             _lib.check(lib.vg_plan_set_global_invcov(handle, inv.shape[0], _dptr(inv)))
         plan.finalize()
         return plan
@@ -788,15 +796,19 @@ class DevicePlan:
 
     def set_data(self, ci, data, monte_carlo=False):
         """Masked data vector + inverse covariance of correlation ci
-        (vega/vega_interface.py:307-316; MC mode swaps in the mock and the scaled C^-1)."""
+        (vega/vega_interface.py:307-316; MC mode swaps in the mock and the scaled C^-1).
+        With marginalize-in-fit the template fit is folded into the matrix (Data.marg_projector)."""
         mask_idx = np.ascontiguousarray(np.nonzero(data.model_mask)[0], dtype=np.int32)
         vec = _f64(data.masked_mc_mock if monte_carlo else data.masked_data_vec)
         if vec.size != mask_idx.size:
             raise ValueError('Masked data and masked model have different sizes.')
-        if data.cov_is_identity and not monte_carlo:
+        proj = data.marg_projector() if getattr(self.builder.vega, 'marginalize_in_fit', False) else None
+        if data.cov_is_identity and not monte_carlo and proj is None:
             inv = None
         else:
             inv = _f64(data.scaled_inv_masked_cov if monte_carlo else data.inv_masked_cov)
+            if proj is not None:
+                inv = _f64(proj.T @ inv @ proj)
         _lib.check(self.lib.vg_corr_set_data(self.handle, ci, mask_idx.size, _dptr(mask_idx), _dptr(vec),
                                              _dptr(inv) if inv is not None else None))
 

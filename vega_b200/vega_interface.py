@@ -57,8 +57,6 @@ class VegaInterface:
         self.low_mem_mode = False
         self.marginalize_in_fit = control.getboolean('marginalize-in-fit', False) \
             if control else False
-        if self.marginalize_in_fit:
-            raise NotImplementedError('marginalize-in-fit is not built yet.')
 
         self.corr_items = {}
         for path in ini_files:
@@ -83,7 +81,7 @@ class VegaInterface:
                 self.fiducial[key] = self.params[key]
 
         self._has_data = all(item.has_data for item in self.corr_items.values())
-        self.data = {name: (Data(item) if self._has_data else None)
+        self.data = {name: (Data(item, self.marginalize_in_fit) if self._has_data else None)
                      for name, item in self.corr_items.items()}
 
         self._blind = False
@@ -113,7 +111,9 @@ class VegaInterface:
         if global_cov_file is not None:
             self.read_global_cov(global_cov_file, cov_scale)
 
-        self.corr_num_marg_modes = {name: 0 for name in self.corr_items}
+        self.corr_num_marg_modes = {name: (self.data[name].num_marg_modes if self._has_data else 0)
+                                    for name in self.corr_items}
+        self._random_marg_coeff = None
         self.run_sampler = control.getboolean('run_sampler', False) if control else False
         self.sampler = control.get('sampler', None) if control else None
         self.monte_carlo = False
@@ -276,8 +276,8 @@ class VegaInterface:
     def compute_model(self, params=None, run_init=True, direct_pk=None, marg_coeff=None):
         """Model xi of every correlation for one parameter dict
         (vega/vega_interface.py:208-248).  Returns {name: ndarray(n_dist)}."""
-        if direct_pk is not None or marg_coeff is not None:
-            raise NotImplementedError('direct_pk / marg_coeff are not part of the B200 path yet.')
+        if direct_pk is not None:
+            raise NotImplementedError('direct_pk is not part of the B200 path yet.')
         engine = self._engine_for(tuple(params) if params else ())
         models, status = engine.model_device(engine.theta_tensor(self._theta_row(engine, params)))
         status = int(status.cpu()[0])
@@ -285,26 +285,60 @@ class VegaInterface:
             raise utils.VegaArinyoError
         if status & _lib.STATUS_BOUNDS:
             raise utils.VegaBoundsError
-        return {name: xi[0].cpu().numpy() for name, xi in models.items()}
+        model_cf = {name: xi[0].cpu().numpy() for name, xi in models.items()}
+        if marg_coeff is not None:          # vega/vega_interface.py:243-246
+            for name in self.data:
+                if self.data[name].marg_templates is not None:
+                    model_cf[name] += self.data[name].marg_templates.dot(marg_coeff[name])
+        return model_cf
+
+    def compute_marg_coeff(self, model_cf):
+        """Best-fit amplitudes of the marginalisation templates for a model
+        (vega/vega_interface.py:546-579)."""
+        out = {}
+        for name in self.corr_items:
+            corr_data = self.data[name]
+            vec = corr_data.masked_mc_mock if self.monte_carlo else corr_data.masked_data_vec
+            diff = vec - model_cf[name][corr_data.model_mask]
+            if corr_data.marg_diff2coeff_matrix is not None:
+                out[name] = corr_data.marg_diff2coeff_matrix.dot(diff)
+        return out
 
     def chi2(self, params=None, direct_pk=None, return_marg_coeff=False):
         """chi2 incl. priors for one parameter dict (vega/vega_interface.py:250-325);
         model-domain failures give 1e100."""
         assert self._has_data
-        if direct_pk is not None or return_marg_coeff:
-            raise NotImplementedError('direct_pk / marginalisation are not part of the B200 path yet.')
+        if direct_pk is not None:
+            raise NotImplementedError('direct_pk is not part of the B200 path yet.')
         engine = self._engine_for(tuple(params) if params else ())
         chi2, status = engine.chi2_host(self._theta_row(engine, params))
         if status[0] & (_lib.STATUS_ARINYO | _lib.STATUS_BOUNDS):
+            if return_marg_coeff:           # vega/vega_interface.py:274-277
+                return 1e100, self._random_marg_coeff
             return 1e100
         chi2 = float(chi2[0])
         assert isinstance(chi2, float)
+        if return_marg_coeff:
+            # the chi2 above already holds the on-the-fly template fit (folded into C^-1 when
+            # marginalize-in-fit); the amplitudes themselves come from the model residual
+            marg_coeff = self.compute_marg_coeff(self.compute_model(params, run_init=False))
+            if self._random_marg_coeff is None:
+                self._random_marg_coeff = marg_coeff
+            return chi2, marg_coeff
         return chi2
 
     def log_lik(self, params=None, direct_pk=None, return_marg_coeff=False):
         """Log-likelihood for one parameter dict (vega/vega_interface.py:327-387)."""
         assert self._has_data
-        chi2 = self.chi2(params, direct_pk, return_marg_coeff)
+        if return_marg_coeff:               # vega/vega_interface.py:345-349,384-386
+            chi2, marg_coeff = self.chi2(params, direct_pk, True)
+            log_lik = float(self._log_norm() - 0.5 * chi2)
+            if marg_coeff is None:
+                return log_lik, None
+            corr_names = [corr for corr in sorted(self.corr_items.keys()) if corr in marg_coeff]
+            flat = np.hstack([marg_coeff[corr] for corr in corr_names]) if corr_names else np.array([])
+            return log_lik, flat
+        chi2 = self.chi2(params, direct_pk)
         return float(self._log_norm() - 0.5 * chi2)
 
     def _log_norm(self):
