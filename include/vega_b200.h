@@ -44,7 +44,8 @@ extern "C" {
  * vector (or -1 when the parameter is absent from the configuration). */
 typedef struct vg_eval_desc {
   /* ---- P(k,mu) ---- */
-  int32_t pk_lin_sel;       /* 0: pk_full - pk_smooth (peak), 1: pk_smooth, 2: pk_full */
+  int32_t pk_lin_sel;       /* 0: pk_full - pk_smooth (peak), 1: pk_smooth, 2: pk_full,
+                               3: the P(k) of vg_plan_set_direct_pk */
   int32_t is_peak;
   int32_t fast_metals;      /* Kaiser term without b1*b2 (vega/power_spectrum.py:219-220) */
   int32_t same_tracer;
@@ -104,6 +105,9 @@ typedef struct vg_eval_desc {
                                3 only-los: transverse size 0 */
   int32_t idx_los_smooth_amp;
   double mock_bin_size;
+  int32_t direct;           /* 1: the single `full` component of Model.compute_direct
+                               (vega/model.py:189-208): evaluated only in direct-P(k) mode, where it
+                               replaces peak, smooth and metals */
   int32_t frozen;           /* 1: metal x metal term of compute_xi_metal_metal (:144-169): M_c xi_c
                                is evaluated once, at the plan's base parameters, in
                                vg_plan_finalize; the hot path adds b1*b2 (x extra) times it */
@@ -206,7 +210,15 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
  * mu projection of vega/pktoxi.py:79-97, the FFTLog and the spline are linear); 0 sends every
  * evaluation through the per-point P(k,mu) pass. */
 #define VG_OPT_MOMENTS 0
+/* VG_OPT_DIRECT_PK (default 0): 1 makes vg_model_batch / vg_chi2_batch* evaluate
+ * Model.compute_direct (vega/model.py:189-208) -- one `full` component from the isotropic
+ * P(k) given to vg_plan_set_direct_pk, no peak/smooth split, no bao_amp, and (as in the
+ * reference with no-metal-decomp) no metal terms. */
+#define VG_OPT_DIRECT_PK 1
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
+/* Isotropic P(k) [nk] for the direct mode (e.g. from a Boltzmann code, the `direct_pk`
+ * argument of VegaInterface.compute_model / chi2 / log_lik); host pointer, copied. */
+int vg_plan_set_direct_pk(vg_plan* plan, const double* pk_host);
 /* Number of evaluations of a correlation served by the moment form (after finalize; 0 when
  * the option is off) -- the remaining ones go through pk_ell + the Hankel GEMM */
 int vg_corr_n_moment(const vg_plan* plan, int32_t corr);

@@ -109,7 +109,11 @@ def main():
                                            control={'marginalize-in-fit': True},
                                            data={'distortion-file': dmat})
     PERTURBED['c1_marg'] = PERTURBED['c1_marg_fit'] = PERTURBED['c1']
-    notes = {'full_fast': CONFIGS['full'] + ' + fast_metals = True',
+    # Model.compute_direct through the direct_pk argument (vega/model.py:189-208)
+    CONFIGS['full_direct'] = CONFIGS['full']
+    PERTURBED['full_direct'] = PERTURBED['full']
+    notes = {'full_direct': CONFIGS['full'] + ' with direct_pk = pk_full (1 + 0.05 sin(3 ln k))',
+             'full_fast': CONFIGS['full'] + ' + fast_metals = True',
              'c1_marg': f"{CONFIGS['c1']} + [model] {MARG_CUTS} + distortion-file (55x55 bins)",
              'c1_marg_fit': f"{CONFIGS['c1']} + [model] {MARG_FIT} + [control] marginalize-in-fit "
                             "+ distortion-file (55x55 bins, synthetic.distortion_matrix)"}
@@ -125,12 +129,16 @@ def main():
         vega = VegaInterface(ini)
         cases = [{}] + PERTURBED[key]
         meta[key] = {'ini': notes.get(key, ini), 'cases': cases, 'corr': list(vega.corr_items)}
+        direct = None
+        if key.endswith('_direct'):
+            k = vega.fiducial['k']
+            direct = vega.fiducial['pk_full'] * (1 + 0.05 * np.sin(3 * np.log(k)))
         for i, pars in enumerate(cases):
-            model = vega.compute_model(pars, run_init=True)
+            model = vega.compute_model(pars, run_init=True, direct_pk=direct)
             for name, xi in model.items():
                 out[f'{key}/{i}/xi/{name}'] = np.asarray(xi, dtype=float)
-            out[f'{key}/{i}/chi2'] = np.array(vega.chi2(pars))
-            out[f'{key}/{i}/log_lik'] = np.array(vega.log_lik(pars))
+            out[f'{key}/{i}/chi2'] = np.array(vega.chi2(pars, direct_pk=direct))
+            out[f'{key}/{i}/log_lik'] = np.array(vega.log_lik(pars, direct_pk=direct))
             if key.startswith('c1_marg'):
                 chi2, coeff = vega.chi2(pars, return_marg_coeff=True)
                 for name, c in coeff.items():

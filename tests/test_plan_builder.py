@@ -16,8 +16,13 @@ def builder(main, sampled=None):
 def test_full_config_descriptors():
     vega, pb = builder('configs/full_configs/main.ini')
     info = pb.describe_corr('lyalya_lyalya')
-    assert len(info['evals']) == 2 + 15
+    assert len(info['evals']) == 2 + 15 + 1
     peak, smooth = info['evals'][:2]
+    # last: the direct_pk evaluation (vega/model.py:189-208) = the smooth options on P(k) slot 3
+    direct = info['evals'][-1]
+    assert direct.direct == 1 and direct.pk_lin_sel == 3 and direct.out_slot == 1
+    assert direct.static_mask == smooth.static_mask and direct.scale_form == smooth.scale_form
+    assert sum(d.direct for d in info['evals']) == 1
     assert peak.is_peak == 1 and peak.pk_lin_sel == 0 and peak.out_slot == 0
     assert smooth.is_peak == 0 and smooth.pk_lin_sel == 1 and smooth.out_slot == 1
     # bias_eta_LYA and beta_LYA are sampled: Kaiser is per vector, every other factor static

@@ -105,7 +105,7 @@ struct EvalLayout {
   std::vector<int> metal_map;    // metal slot -> column block (-1: not in this layout)
   DevBuf d_mom_ids, d_gather_ids, d_slot, d_tabslot, d_metal_map;
 };
-enum { LAY_MOM = 0, LAY_FULL = 1, LAY_ALL = 2 };
+enum { LAY_MOM = 0, LAY_FULL = 1, LAY_ALL = 2, LAY_DIRECT = 3 };
 
 struct Corr {
   int hankel_id = 0, n_model = 0, n_dist = 0, ld_model = 0, ld_dist = 0;
@@ -115,9 +115,10 @@ struct Corr {
   //   LAY_MOM  hot path, moment form on: per-point pass for the evaluations that need it,
   //            moment form for the rest;   LAY_FULL  hot path, every evaluation per point;
   //   LAY_ALL  per-stage taps and the finalize pass of the frozen terms: every evaluation
-  //            incl. the frozen ones, per point, identity slots.
+  //            incl. the frozen ones, per point, identity slots;
+  //   LAY_DIRECT  Model.compute_direct: only the evaluations flagged `direct`, per point.
   // Evaluations with table_owner >= 0 never own tables; frozen ones leave the hot layouts.
-  EvalLayout lay[3];
+  EvalLayout lay[4];
   DevBuf d_mom_ktab;             // LAY_MOM: [n_mom][9][n_ell][2*n_out_pad]
   std::vector<DevBuf> coords;
   std::vector<double> opz_eff2;
@@ -150,7 +151,7 @@ struct Corr {
 struct vg_plan {
   int npf = 0, n_theta = 0, nk = 0, nk_pad = 0, nmu = 0, n_ell = 0, idx_bao_amp = -1;
   std::vector<double> base;
-  DevBuf d_base, d_theta_cols, d_k, d_pk[3], d_pk_fid, d_mu, d_wleg;
+  DevBuf d_base, d_theta_cols, d_k, d_pk[4], d_pk_fid, d_mu, d_wleg;
   DevBuf d_fv_x, d_fv_f; int fv_n = 0;
   DevBuf d_uv_tau, d_uv_a; int uv_n = 0;
   int n_prior = 0;
@@ -161,6 +162,7 @@ struct vg_plan {
   DevBuf d_grid_ptrs;
   bool finalized = false;
   bool use_moments = true;
+  bool direct_mode = false;      // VG_OPT_DIRECT_PK
   int static_bad = 0;
   int std_ells = 0;
   // global covariance
@@ -182,7 +184,7 @@ struct vg_plan {
     g.nk = nk; g.nk_pad = nk_pad; g.nmu = nmu; g.n_ell = n_ell;
     g.std_ells = std_ells;
     g.k = d_k.as<double>();
-    for (int i = 0; i < 3; ++i) g.pk_lin[i] = d_pk[i].as<double>();
+    for (int i = 0; i < 4; ++i) g.pk_lin[i] = d_pk[i].as<double>();
     g.pk_fid = d_pk_fid.as<double>();
     g.mu = d_mu.as<double>();
     g.wleg = d_wleg.as<double>();
@@ -250,12 +252,14 @@ int build_layouts(vg_plan* plan, Corr& c) {
       VG_REQUIRE(!d.frozen, "evaluation %d: frozen and table_owner are exclusive", e);
     }
     if (d.frozen) VG_REQUIRE(d.out_slot >= 2, "evaluation %d: only metal terms can be frozen", e);
+    if (d.direct) VG_REQUIRE(d.out_slot == 1 && d.table_owner < 0 && !d.frozen,
+                             "evaluation %d: a direct evaluation writes the smooth slot", e);
   }
   c.frozen_ids.clear();
   for (int e = 0; e < E; ++e)
-    if (c.evals[e].frozen) c.frozen_ids.push_back(e);
+    if (c.evals[e].frozen && !c.evals[e].direct) c.frozen_ids.push_back(e);
   if (!c.frozen_ids.empty()) VG_TRY(upload(c.d_frozen_ids, c.frozen_ids.data(), c.frozen_ids.size()));
-  for (int li = 0; li < 3; ++li) {
+  for (int li = 0; li < 4; ++li) {
     EvalLayout& L = c.lay[li];
     for (auto& ids : L.class_ids) ids.clear();
     L.mom_ids.clear(); L.gather_ids.clear();
@@ -264,7 +268,7 @@ int build_layouts(vg_plan* plan, Corr& c) {
     std::vector<int> slot(E, 0), tabslot(E, 0);
     for (int e = 0; e < E; ++e) {
       const vg_eval_desc& d = c.evals[e];
-      const bool hot = li == LAY_ALL || !d.frozen;
+      const bool hot = li == LAY_DIRECT ? d.direct != 0 : (!d.direct && (li == LAY_ALL || !d.frozen));
       if (!hot) continue;
       L.gather_ids.push_back(e);
       if (d.out_slot >= 2) L.metal_map[d.out_slot - 2] = L.n_metal++;
@@ -328,6 +332,7 @@ int vg_plan_create(int32_t n_params, const double* base, int32_t n_theta, const 
   VG_TRY(upload(p->d_pk[0], peak.data(), nk));
   VG_TRY(upload(p->d_pk[1], pk_smooth, nk));
   VG_TRY(upload(p->d_pk[2], pk_full, nk));
+  VG_TRY(upload(p->d_pk[3], pk_full, nk));       // direct P(k): the template until set
   VG_TRY(upload(p->d_pk_fid, pk_fid, nk));
   VG_TRY(upload(p->d_mu, mu, nmu));
   VG_TRY(upload(p->d_wleg, wleg, (size_t)n_ell * nmu));
@@ -351,8 +356,25 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk) {
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
   VG_REQUIRE(plan, "null plan");
   if (option == VG_OPT_MOMENTS) { plan->use_moments = value != 0; return VG_OK; }
+  if (option == VG_OPT_DIRECT_PK) {
+    if (value) {
+      bool any = false;
+      for (auto& cp : plan->corrs)
+        for (auto& d : cp->evals) any = any || d.direct;
+      VG_REQUIRE(any, "VG_OPT_DIRECT_PK: the plan holds no `direct` evaluation");
+    }
+    plan->direct_mode = value != 0;
+    return VG_OK;
+  }
   vg_set_error("vg_plan_set_option: unknown option %d", option);
   return VG_ERR_ARG;
+}
+
+int vg_plan_set_direct_pk(vg_plan* plan, const double* pk_host) {
+  VG_REQUIRE(plan && pk_host, "vg_plan_set_direct_pk: bad arguments");
+  VG_CUDA_CHECK(cudaDeviceSynchronize());
+  VG_CUDA_CHECK(cudaMemcpy(plan->d_pk[3].p, pk_host, (size_t)plan->nk * 8, cudaMemcpyHostToDevice));
+  return VG_OK;
 }
 
 int vg_plan_set_fvoigt(vg_plan* plan, int32_t n, const double* x, const double* f) {
@@ -835,7 +857,9 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   vg::PkGridDev g = plan->grid_dev();
   // the per-stage taps (upto <= 2) expose every evaluation's multipoles / knot tables, so
   // they run all evaluations through the per-point pass
-  if (layout < 0) layout = upto <= 2 ? LAY_ALL : (plan->use_moments ? LAY_MOM : LAY_FULL);
+  if (layout < 0)
+    layout = plan->direct_mode ? LAY_DIRECT : (upto <= 2 ? LAY_ALL : (plan->use_moments ? LAY_MOM : LAY_FULL));
+  const bool direct = layout == LAY_DIRECT;
   const EvalLayout& L = c.lay[layout];
   const int Ef = L.n_full;
   const int Em = (int)L.mom_ids.size();
@@ -970,7 +994,8 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   ca.pfull = plan->w_pfull.as<double>(); ca.npf = plan->npf;
   ca.n = c.n_model; ca.ld = c.ld_model; ca.B = Bc;
   ca.x = plan->w_x.as<double>();
-  ca.frozen = c.d_frozen.as<double>(); ca.n_frozen = (int)c.frozen_ids.size();
+  ca.direct = direct ? 1 : 0;
+  ca.frozen = c.d_frozen.as<double>(); ca.n_frozen = direct ? 0 : (int)c.frozen_ids.size();
   ca.frozen_ids = c.d_frozen_ids.as<int>(); ca.evals = c.d_evals.as<vg_eval_desc>();
   const long long n = Bc * c.ld_model;
   ProfScope prof(plan, PROF_ELEM, st);
@@ -1043,6 +1068,7 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
   pa.mask_idx = residual ? c.d_mask_idx.as<int>() : nullptr;
   pa.bb = bb_dev(c); pa.n_dist = c.n_dist;
   pa.pfull = plan->w_pfull.as<double>(); pa.npf = plan->npf; pa.idx_bao_amp = plan->idx_bao_amp;
+  pa.direct = plan->direct_mode ? 1 : 0;
   pa.data = residual ? c.d_data.as<double>() : nullptr;
   if (residual && mock_idx) {
     VG_REQUIRE(c.n_mocks > 0, "vg_chi2_batch_mc: correlation without mocks (vg_corr_set_mocks)");

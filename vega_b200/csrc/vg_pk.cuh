@@ -25,7 +25,7 @@ struct PkGridDev {
   int nk, nk_pad, nmu, n_ell;
   int std_ells;                // multipoles are exactly (0, 2, 4, 6): Legendre weights in registers
   const double* k;
-  const double* pk_lin[3];     // 0 full-smooth, 1 smooth, 2 full
+  const double* pk_lin[4];     // 0 full-smooth, 1 smooth, 2 full, 3 direct P(k)
   const double* pk_fid;
   const double* mu;
   const double* wleg;          // [n_ell][nmu]

@@ -75,6 +75,7 @@ struct CombineArgs {
   double* x;               // [B][ld]
   // fast_metals metal x metal terms: sum_f b1*b2(*extra)(theta) * frozen[f][i]
   const double* frozen; int n_frozen; const int* frozen_ids; const vg_eval_desc* evals;
+  int direct;              // 1: x = full component alone (Model.compute_direct), no bao_amp
 };
 
 // weight of a metal term from its bias parameters (vega/metals.py:289-313)
@@ -94,8 +95,8 @@ __global__ void combine_pre_kernel(CombineArgs a) {
   int i = (int)(idx % a.ld);
   if (i >= a.n) { a.x[idx] = 0.0; return; }
   const double* p = a.pfull + b * a.npf;
-  const double amp = par(p, a.idx_bao_amp, 1.0);
-  double v = amp * a.core[idx] + a.core[a.B * a.ld + idx];
+  const double amp = a.direct ? 0.0 : par(p, a.idx_bao_amp, 1.0);
+  double v = a.direct ? a.core[a.B * a.ld + idx] : amp * a.core[idx] + a.core[a.B * a.ld + idx];
   if (a.met) v += a.met[idx];
   for (int f = 0; f < a.n_frozen; ++f)
     v = fma(metal_bias_weight(a.evals[a.frozen_ids[f]], p), a.frozen[(long long)f * a.ld + i], v);
@@ -116,6 +117,7 @@ struct PostArgs {
   const double* data;         // [n_out] or null (model output)
   const int* mock_idx;        // per vector: row of `data` ([n_mock][data_stride]), null: row 0
   int data_stride;
+  int direct;                 // 1: additive broadband enters once (no peak component)
   int n_out, ncols, ldo; long long B;   // columns j < ncols are written (zero for j >= n_out)
   double* out;                // [B][ldo]: model (data == null) or residual data - model
 };
@@ -131,7 +133,7 @@ __global__ void post_kernel(PostArgs a) {
   const int bin = a.mask_idx ? a.mask_idx[j] : j;
   double v = a.y[b * a.ldy + (a.y_is_masked ? j : bin)];
   if (a.bb.n_terms) {
-    const double amp = par(p, a.idx_bao_amp, 1.0);
+    const double amp = a.direct ? 0.0 : par(p, a.idx_bao_amp, 1.0);
     v *= bb_eval(a.bb, 2, p, bin, a.n_dist);
     v += (1.0 + amp) * bb_eval(a.bb, 3, p, bin, a.n_dist);
   }

@@ -562,6 +562,15 @@ class PlanBuilder:
                 info['evals'].append(d)
                 info['metal_mats'].append(mat)
 
+        # Model.compute_direct (vega/model.py:189-208): the `full` component from an externally
+        # supplied isotropic P(k) -- the smooth component's options with pars['peak'] = False
+        d = EvalDesc()
+        self.fill_pk(d, mcfg, item.tracer1, item.tracer2, item.name, False, 3, False,
+                     data_binsizes=binsizes)
+        self.fill_xi(d, mcfg, item.tracer1, item.tracer2, False, pair_name, False)
+        d.coord_set, d.out_slot, d.direct = 0, 1, 1
+        info['evals'].append(d)
+
         # DESI instrumental systematics (vega/correlation_func.py:553-595)
         info['inst'] = None
         if mcfg.getboolean('desi-instrumental-systematics', False):
@@ -628,7 +637,7 @@ class PlanBuilder:
         every evaluation keeps its own coordinates, weight and metal matrix."""
         first = {}
         for e, d in enumerate(evals):
-            if d.table_owner >= 0 or d.frozen:
+            if d.table_owner >= 0 or d.frozen or d.direct:
                 continue
             sig = self.pk_signature(d)
             if sig in first:
@@ -779,7 +788,7 @@ class DevicePlan:
         self.sampled = list(builder.sampled)
         self.corr_names = [i['name'] for i in infos]
         self.n_dist = [i['item'].dist_model_coordinates.r_grid.size for i in infos]
-        self.n_eval = [len(i['evals']) for i in infos]
+        self.n_eval = [sum(1 for d in i['evals'] if not d.direct) for i in infos]
         self.infos = infos
         self.device = torch.device('cuda', torch.cuda.current_device())
 
@@ -815,6 +824,13 @@ class DevicePlan:
     def finalize(self):
         _lib.check(self.lib.vg_plan_finalize(self.handle, self._stream()))
         self.static_status = self.lib.vg_plan_static_status(self.handle)
+
+    def set_direct_pk(self, pk):
+        """Isotropic P(k) on the template's k grid for the direct mode (OPT_DIRECT_PK)."""
+        pk = _f64(pk)
+        if pk.size != self.builder.vega.fiducial['k'].size:
+            raise ValueError('direct_pk must be sampled on the k grid of the fiducial template.')
+        _lib.check(self.lib.vg_plan_set_direct_pk(self.handle, _dptr(pk)))
 
     def set_option(self, option, value):
         """Run-time switches of the CUDA library (include/vega_b200.h: VG_OPT_*)."""

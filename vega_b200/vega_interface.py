@@ -263,6 +263,24 @@ class VegaInterface:
             self._engine_mc = bool(self.monte_carlo)
         return self._engine
 
+    def _direct_mode(self, engine, direct_pk):
+        """Context in which the engine evaluates Model.compute_direct on `direct_pk`
+        (vega/model.py:189-208, the direct_pk argument of compute_model / chi2 / log_lik)."""
+        import contextlib
+
+        @contextlib.contextmanager
+        def mode():
+            if direct_pk is None:
+                yield
+                return
+            engine.set_direct_pk(direct_pk)
+            engine.set_option(_lib.OPT_DIRECT_PK, 1)
+            try:
+                yield
+            finally:
+                engine.set_option(_lib.OPT_DIRECT_PK, 0)
+        return mode()
+
     def _theta_row(self, engine, params=None):
         local = self._get_lcl_prms(params)
         return np.array([[local[n] for n in engine.sampled]], dtype=np.float64)
@@ -276,11 +294,10 @@ class VegaInterface:
     def compute_model(self, params=None, run_init=True, direct_pk=None, marg_coeff=None):
         """Model xi of every correlation for one parameter dict
         (vega/vega_interface.py:208-248).  Returns {name: ndarray(n_dist)}."""
-        if direct_pk is not None:
-            raise NotImplementedError('direct_pk is not part of the B200 path yet.')
         engine = self._engine_for(tuple(params) if params else ())
-        models, status = engine.model_device(engine.theta_tensor(self._theta_row(engine, params)))
-        status = int(status.cpu()[0])
+        with self._direct_mode(engine, direct_pk):
+            models, status = engine.model_device(engine.theta_tensor(self._theta_row(engine, params)))
+            status = int(status.cpu()[0])
         if status & _lib.STATUS_ARINYO:
             raise utils.VegaArinyoError
         if status & _lib.STATUS_BOUNDS:
@@ -308,10 +325,9 @@ class VegaInterface:
         """chi2 incl. priors for one parameter dict (vega/vega_interface.py:250-325);
         model-domain failures give 1e100."""
         assert self._has_data
-        if direct_pk is not None:
-            raise NotImplementedError('direct_pk is not part of the B200 path yet.')
         engine = self._engine_for(tuple(params) if params else ())
-        chi2, status = engine.chi2_host(self._theta_row(engine, params))
+        with self._direct_mode(engine, direct_pk):
+            chi2, status = engine.chi2_host(self._theta_row(engine, params))
         if status[0] & (_lib.STATUS_ARINYO | _lib.STATUS_BOUNDS):
             if return_marg_coeff:           # vega/vega_interface.py:274-277
                 return 1e100, self._random_marg_coeff
@@ -321,7 +337,8 @@ class VegaInterface:
         if return_marg_coeff:
             # the chi2 above already holds the on-the-fly template fit (folded into C^-1 when
             # marginalize-in-fit); the amplitudes themselves come from the model residual
-            marg_coeff = self.compute_marg_coeff(self.compute_model(params, run_init=False))
+            marg_coeff = self.compute_marg_coeff(
+                self.compute_model(params, run_init=False, direct_pk=direct_pk))
             if self._random_marg_coeff is None:
                 self._random_marg_coeff = marg_coeff
             return chi2, marg_coeff
@@ -404,12 +421,13 @@ class VegaInterface:
         return self.minimizer
 
     # -- batched API (new) -----------------------------------------------------------------------
-    def chi2_batch(self, theta, names=None):
+    def chi2_batch(self, theta, names=None, direct_pk=None):
         """chi2 of B parameter vectors.  theta: ndarray [B, P] with columns `names`
         (default: the [sample] set, see theta_names).  Host in, host out."""
         engine = self._engine_for(tuple(names) if names else ())
         theta = self._reorder(engine, theta, names)
-        chi2, status = engine.chi2_host(theta)
+        with self._direct_mode(engine, direct_pk):
+            chi2, status = engine.chi2_host(theta)
         chi2[(status & (_lib.STATUS_ARINYO | _lib.STATUS_BOUNDS)) != 0] = 1e100
         return chi2
 
