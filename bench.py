@@ -148,7 +148,7 @@ def gemm_flops(engine, B):
         item, data = info['item'], info['data']
         nm = item.model_coordinates.r_grid.size
         nmask = int(data.model_mask.sum())
-        own = [d for d in info['evals'] if d.table_owner < 0 and not d.frozen]
+        own = [d for d in info['evals'] if d.table_owner < 0 and not d.frozen and not d.direct]
         n_eval = len(own) - engine.n_moment(ci)             # evaluations that reach the Hankel GEMM
         # metal matrices applied per vector (fast_metals freezes the metal x metal ones)
         n_metal = sum(m is not None and not d.frozen for m, d in zip(info['metal_mats'], info['evals'][2:]))
@@ -312,7 +312,7 @@ def main():
         achieved = sum(flops.values()) / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
         n_eval = sum(engine.n_eval)
         n_moment = sum(engine.n_moment(ci) for ci in range(len(engine.infos)))
-        n_own = sum(sum(1 for d in info['evals'] if d.table_owner < 0 and not d.frozen)
+        n_own = sum(sum(1 for d in info['evals'] if d.table_owner < 0 and not d.frozen and not d.direct)
                     for info in engine.infos)
         n_grid_eval = n_own - n_moment
         grid_bytes = 6512000.0 * n_grid_eval * B

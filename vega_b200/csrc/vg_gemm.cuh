@@ -10,19 +10,23 @@
 //   - r^T C^-1 r              (vega/vega_interface.py:294-316)   [ROWDOT epilogue]
 //
 // Math is DMMA (mma.sync m8n8k4 f64: tcgen05 has no FP64 kind), fed from shared memory
-// filled by a 3-stage cp.async pipeline.  CTA tile 128x128x16, 8 warps as 2x4, warp tile
-// 64x32 = 8x4 DMMA fragments; smem rows padded to 20 doubles so the 64-bit fragment
-// loads of a half-warp hit 16 distinct bank pairs.
+// filled by a 3-stage cp.async pipeline.  CTA tile 128x128x32 (216 KB of shared memory, one
+// CTA per SM), 8 warps as 2x4, warp tile 64x32 = 8x4 DMMA fragments; smem rows padded to
+// BK+4 doubles so the 64-bit fragment loads of a half-warp hit 16 distinct bank pairs.
+// One CTA barrier per 32 k (256 DMMAs per warp): with 16 k per barrier ncu showed the
+// barrier + cp.async wait + LDS latency stalls at ~16 % of the DMMA pipe's cycles.
 #pragma once
 #include "vg_common.cuh"
 
 namespace vg {
 
-constexpr int GEMM_BM = 128, GEMM_BN = 128, GEMM_BK = 16;
-constexpr int GEMM_LDS = 20;          // padded smem row stride (doubles)
+constexpr int GEMM_BM = 128, GEMM_BN = 128;
+constexpr int GEMM_BK = 16;           // K granularity of the operands (zero padded to it)
+constexpr int GEMM_BK_BIG = 32;       // k per pipeline stage of the 128-row tile
 constexpr int GEMM_STAGES = 3;
 constexpr int GEMM_THREADS = 256;
-constexpr int GEMM_SMEM = GEMM_STAGES * (GEMM_BM + GEMM_BN) * GEMM_LDS * 8;
+constexpr int gemm_smem_bytes(int bm, int bk) { return GEMM_STAGES * (bm + GEMM_BN) * (bk + 4) * 8; }
+constexpr int GEMM_SMEM = gemm_smem_bytes(GEMM_BM, GEMM_BK_BIG);
 
 enum GemmEpilogue { GEMM_STORE = 0, GEMM_ROWDOT = 1 };
 
@@ -38,10 +42,17 @@ struct GemmArgs {
   const double* D; long long ldd;
 };
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, bool pred) {
-  unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+// shared-memory operands are addressed by their 32-bit shared-window offsets, computed once
+// per CTA: with generic pointers the compiler re-derived the window base (S2UR of
+// SR_CgaCtaId, a long-scoreboard read) inside the k loop -- 3 % of the stall samples
+__device__ __forceinline__ void cp_async16(unsigned smem_addr, const void* gmem, bool pred) {
   int bytes = pred ? 16 : 0;
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(bytes));
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(smem_addr), "l"(gmem), "r"(bytes));
+}
+__device__ __forceinline__ double lds_f64(unsigned smem_addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(v) : "r"(smem_addr));
+  return v;
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() {
@@ -55,12 +66,15 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 // BM = 128: 2 x 4 warps, warp tile 64 x 32.  BM = 32 (batches of a few vectors: the scalar API,
 // gradient stencils): 1 x 8 warps, warp tile 32 x 16 -- a 128-row tile would spend its DMMA
 // cycles on rows that do not exist, and the launch is bound by streaming the operator anyway.
-template <int EPI, int BM>
+template <int EPI, int BM, int BK>
 __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kernel(GemmArgs g) {
+  constexpr int GEMM_LDS = BK + 4;                          // padded smem row stride (doubles)
+  constexpr int CPR = BK / 2;                               // 16-byte chunks per tile row
   constexpr int MI = BM == 128 ? 8 : 4;                     // 8-row fragments per warp
   constexpr int WARPS_M = BM / (MI * 8), WARPS_N = 8 / WARPS_M;
   constexpr int NJ = GEMM_BN / (WARPS_N * 8);               // 8-column fragments per warp
-  constexpr int A_CHUNKS = BM * 8 / GEMM_THREADS;           // 16-byte chunks of the A tile per thread
+  constexpr int A_CHUNKS = BM * CPR / GEMM_THREADS;         // 16-byte chunks of the A tile per thread
+  constexpr int B_CHUNKS = GEMM_BN * CPR / GEMM_THREADS;
   extern __shared__ __align__(16) double smem[];
   double* As = smem;                                        // [STAGES][BM][LDS]
   double* Bs = smem + GEMM_STAGES * BM * GEMM_LDS;          // [STAGES][BN][LDS]
@@ -70,7 +84,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * GEMM_BN;
   const int bz = blockIdx.z / g.splits, sp = blockIdx.z % g.splits;
 
-  const int ktiles_total = g.K / GEMM_BK;
+  const int ktiles_total = (g.K + BK - 1) / BK;
   const int kt_per = (ktiles_total + g.splits - 1) / g.splits;
   const int kt_begin = sp * kt_per;
   const int kt_end = min(ktiles_total, kt_begin + kt_per);
@@ -79,28 +93,38 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
   const double* A = g.A + (long long)bz * g.strideA;
   const double* B = g.B + (long long)bz * g.strideB;
 
-  // global -> smem mapping: 128 rows x 8 chunks of 16 B per operand, 4 chunks per thread
-  auto load_stage = [&](int stage, int kt) {
-    const int k0 = (kt_begin + kt) * GEMM_BK;
-    double* as = As + stage * BM * GEMM_LDS;
-    double* bs = Bs + stage * GEMM_BN * GEMM_LDS;
+  // global -> smem mapping: a pass of the 256 threads covers RPP rows x CPR chunks of 16 B;
+  // each thread keeps ONE row pointer per operand (its chunk column is the same in every
+  // pass), the row-in-range bits are loop invariant, and chunks past K (a last 32-wide tile
+  // over a K that is a multiple of 16 only) are zero filled through the src-size operand.
+  constexpr int RPP = GEMM_THREADS / CPR;                   // tile rows per pass
+  const unsigned as_base = (unsigned)__cvta_generic_to_shared(As);
+  const unsigned bs_base = (unsigned)__cvta_generic_to_shared(Bs);
+  const int lrow = tid / CPR, lch = (tid % CPR) * 2;
+  const double* a_src = A + (long long)(m0 + lrow) * g.lda + lch;
+  const double* b_src = B + (long long)(n0 + lrow) * g.ldb + lch;
+  const long long a_pass = (long long)RPP * g.lda, b_pass = (long long)RPP * g.ldb;
+  unsigned a_rows = 0, b_rows = 0;
 #pragma unroll
-    for (int i = 0; i < A_CHUNKS; ++i) {
-      int c = tid + i * GEMM_THREADS;
-      int row = c >> 3, ch = c & 7;
-      int gm = m0 + row;
-      bool p = gm < g.M;
-      cp_async16(as + row * GEMM_LDS + ch * 2, A + (long long)(p ? gm : 0) * g.lda + k0 + ch * 2, p);
-    }
+  for (int i = 0; i < A_CHUNKS; ++i) a_rows |= (m0 + lrow + i * RPP < g.M ? 1u : 0u) << i;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      int c = tid + i * GEMM_THREADS;        // 0..1023
-      int row = c >> 3, ch = c & 7;
-      int gn = n0 + row;
-      bool q = gn < g.N;
-      cp_async16(bs + row * GEMM_LDS + ch * 2, B + (long long)(q ? gn : 0) * g.ldb + k0 + ch * 2, q);
+  for (int i = 0; i < B_CHUNKS; ++i) b_rows |= (n0 + lrow + i * RPP < g.N ? 1u : 0u) << i;
+  const unsigned a_dst = as_base + (lrow * GEMM_LDS + lch) * 8;
+  const unsigned b_dst = bs_base + (lrow * GEMM_LDS + lch) * 8;
+  // chunk q of a stage refill: q < A_CHUNKS from A, the rest from B
+  auto load_chunk = [&](int q, int stage, long long k0, bool live) {
+    if (q < A_CHUNKS) {
+      cp_async16(a_dst + stage * (BM * GEMM_LDS * 8) + q * (RPP * GEMM_LDS * 8),
+                 a_src + q * a_pass + k0, live && ((a_rows >> q) & 1u));
+    } else {
+      const int r = q - A_CHUNKS;
+      cp_async16(b_dst + stage * (GEMM_BN * GEMM_LDS * 8) + r * (RPP * GEMM_LDS * 8),
+                 b_src + r * b_pass + k0, live && ((b_rows >> r) & 1u));
     }
   };
+  constexpr int N_CHUNKS = A_CHUNKS + B_CHUNKS;
+  constexpr int N_STEPS = BK / 4;
+  constexpr int CHUNKS_PER_STEP = (N_CHUNKS + N_STEPS - 1) / N_STEPS;
 
   double acc[MI][NJ][2];
 #pragma unroll
@@ -110,33 +134,56 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
 
 #pragma unroll
   for (int s = 0; s < GEMM_STAGES - 1; ++s) {
-    if (s < nkt) load_stage(s, s);
+    const long long k0 = (long long)(kt_begin + s) * BK;
+    const bool live = s < nkt && k0 + lch < g.K;
+#pragma unroll
+    for (int q = 0; q < N_CHUNKS; ++q) load_chunk(q, s, k0, live);
     cp_async_commit();
   }
 
   const int frow = lane >> 2, fcol = lane & 3;
+  const unsigned as_frag = as_base + ((wm * MI * 8 + frow) * GEMM_LDS + fcol) * 8;
+  const unsigned bs_frag = bs_base + ((wn * NJ * 8 + frow) * GEMM_LDS + fcol) * 8;
+  int cur = 0, nxt = GEMM_STAGES - 1;      // stage consumed / stage refilled at this iteration
   for (int kt = 0; kt < nkt; ++kt) {
     cp_async_wait<GEMM_STAGES - 2>();
     __syncthreads();
-    {   // prefetch tile kt+STAGES-1 into the slot freed at iteration kt-1
-      int nk = kt + GEMM_STAGES - 1;
-      if (nk < nkt) load_stage(nk % GEMM_STAGES, nk);
-      cp_async_commit();
+    // tile kt+STAGES-1 goes into the slot freed at iteration kt-1; its cp.async are issued
+    // between the DMMA steps below (in the issue slots the 16-cycle DMMA cadence leaves
+    // free) instead of in a block after the barrier, where both warps of a scheduler would
+    // leave the DMMA pipe idle while they compute addresses
+    const long long k_next = (long long)(kt_begin + kt + GEMM_STAGES - 1) * BK;
+    const bool live = kt + GEMM_STAGES - 1 < nkt && k_next + lch < g.K;
+    const unsigned as = as_frag + cur * (BM * GEMM_LDS * 8);
+    const unsigned bs = bs_frag + cur * (GEMM_BN * GEMM_LDS * 8);
+    double a[2][MI], b[2][NJ];
+#pragma unroll
+    for (int i = 0; i < MI; ++i) a[0][i] = lds_f64(as + i * (8 * GEMM_LDS * 8));
+#pragma unroll
+    for (int j = 0; j < NJ; ++j) b[0][j] = lds_f64(bs + j * (8 * GEMM_LDS * 8));
+#pragma unroll
+    for (int st = 0; st < N_STEPS; ++st) {
+      const int c = st & 1;
+      if (st + 1 < N_STEPS) {
+#pragma unroll
+        for (int i = 0; i < MI; ++i) a[c ^ 1][i] = lds_f64(as + i * (8 * GEMM_LDS * 8) + (st + 1) * 32);
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) b[c ^ 1][j] = lds_f64(bs + j * (8 * GEMM_LDS * 8) + (st + 1) * 32);
+      }
+#pragma unroll
+      for (int i = 0; i < MI; ++i) {
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[c][i], b[c][j]);
+        // one refill chunk after every (MI / CHUNKS_PER_STEP)-th fragment row
+        if (CHUNKS_PER_STEP > 0 && (i + 1) % (MI / CHUNKS_PER_STEP) == 0) {
+          const int q = st * CHUNKS_PER_STEP + (i + 1) / (MI / CHUNKS_PER_STEP) - 1;
+          if (q < N_CHUNKS) load_chunk(q, nxt, k_next, live);
+        }
+      }
     }
-    const double* as = As + (kt % GEMM_STAGES) * BM * GEMM_LDS + (wm * MI * 8 + frow) * GEMM_LDS + fcol;
-    const double* bs = Bs + (kt % GEMM_STAGES) * GEMM_BN * GEMM_LDS + (wn * NJ * 8 + frow) * GEMM_LDS + fcol;
-#pragma unroll
-    for (int kk = 0; kk < GEMM_BK; kk += 4) {
-      double a[MI], b[NJ];
-#pragma unroll
-      for (int i = 0; i < MI; ++i) a[i] = as[i * 8 * GEMM_LDS + kk];
-#pragma unroll
-      for (int j = 0; j < NJ; ++j) b[j] = bs[j * 8 * GEMM_LDS + kk];
-#pragma unroll
-      for (int i = 0; i < MI; ++i)
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
-    }
+    cp_async_commit();
+    cur = cur + 1 == GEMM_STAGES ? 0 : cur + 1;
+    nxt = nxt + 1 == GEMM_STAGES ? 0 : nxt + 1;
   }
   cp_async_wait<0>();
 
@@ -209,7 +256,7 @@ __global__ void reduce_splits_kernel(const double* __restrict__ W, double* __res
 }
 
 constexpr int GEMM_BM_SMALL = 32;
-constexpr int GEMM_SMEM_SMALL = GEMM_STAGES * (GEMM_BM_SMALL + GEMM_BN) * GEMM_LDS * 8;
+constexpr int GEMM_SMEM_SMALL = gemm_smem_bytes(GEMM_BM_SMALL, GEMM_BK);
 // rows of A at or below which the 32-row tile is used
 constexpr int GEMM_SMALL_M = 96;
 inline int gemm_tile_m(int M) { return M <= GEMM_SMALL_M ? GEMM_BM_SMALL : GEMM_BM; }
@@ -223,26 +270,26 @@ inline int launch_dgemm(const GemmArgs& g, int epilogue, cudaStream_t stream) {
   dim3 grid(vg_cdiv(g.M, bm), vg_cdiv(g.N, GEMM_BN), g.batch * g.splits);
   static bool attr_set = false;
   if (!attr_set) {
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE, GEMM_BM>,
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE, GEMM_BM, GEMM_BK_BIG>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM>,
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM, GEMM_BK_BIG>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE, GEMM_BM_SMALL>,
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE, GEMM_BM_SMALL, GEMM_BK>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_SMALL));
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM_SMALL>,
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM_SMALL, GEMM_BK>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_SMALL));
     attr_set = true;
   }
   if (bm == GEMM_BM) {
     if (epilogue == GEMM_STORE)
-      dgemm_tn_kernel<GEMM_STORE, GEMM_BM><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
+      dgemm_tn_kernel<GEMM_STORE, GEMM_BM, GEMM_BK_BIG><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
     else
-      dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
+      dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM, GEMM_BK_BIG><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
   } else {
     if (epilogue == GEMM_STORE)
-      dgemm_tn_kernel<GEMM_STORE, GEMM_BM_SMALL><<<grid, GEMM_THREADS, GEMM_SMEM_SMALL, stream>>>(g);
+      dgemm_tn_kernel<GEMM_STORE, GEMM_BM_SMALL, GEMM_BK><<<grid, GEMM_THREADS, GEMM_SMEM_SMALL, stream>>>(g);
     else
-      dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM_SMALL><<<grid, GEMM_THREADS, GEMM_SMEM_SMALL, stream>>>(g);
+      dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM_SMALL, GEMM_BK><<<grid, GEMM_THREADS, GEMM_SMEM_SMALL, stream>>>(g);
   }
   VG_CUDA_CHECK(cudaGetLastError());
   return VG_OK;
