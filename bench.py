@@ -334,6 +334,8 @@ def main():
                        'evaluations_through_pk_ell': n_grid_eval,
                        'evaluations_in_moment_form': n_moment,
                        'evaluations_sharing_tables': n_eval - n_grid_eval - n_moment,
+                       'evaluations_with_static_xi_stage': sum(engine.n_static_xi(ci)
+                                                               for ci in range(len(engine.infos))),
                        'l2': 'inputs larger than L2: ~1.6 GB of static operands + ~2 GB of workspace '
                              'streamed per step'},
             'clocks': clock_info,

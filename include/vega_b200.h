@@ -111,6 +111,11 @@ typedef struct vg_eval_desc {
   int32_t frozen;           /* 1: metal x metal term of compute_xi_metal_metal (:144-169): M_c xi_c
                                is evaluated once, at the plan's base parameters, in
                                vg_plan_finalize; the hot path adds b1*b2 (x extra) times it */
+  int32_t static_xi;        /* 1: nothing the xi stage reads (AP scale, drp, bias-evolution exponents)
+                               is a sampled parameter and no additive xi term is on, so the
+                               coordinates and per-bin factors are the same for every vector: in
+                               moment form the gather is applied once to the static tables */
+  int32_t reserved_;
 } vg_eval_desc;
 
 /* One broadband term (vega/broadband_poly.py:23-198) */
@@ -222,6 +227,9 @@ int vg_plan_set_direct_pk(vg_plan* plan, const double* pk_host);
 /* Number of evaluations of a correlation served by the moment form (after finalize; 0 when
  * the option is off) -- the remaining ones go through pk_ell + the Hankel GEMM */
 int vg_corr_n_moment(const vg_plan* plan, int32_t corr);
+/* Evaluations of the correlation whose xi stage (vega/correlation_func.py:117-236) is in moment
+ * form too (vg_eval_desc::static_xi): read-out of static per-bin tables, no gather. */
+int vg_corr_n_static_xi(const vg_plan* plan, int32_t corr);
 /* Status bits raised while building the static grids (e.g. VG_STATUS_ARINYO): they apply
  * to every vector */
 int vg_plan_static_status(const vg_plan* plan);

@@ -40,6 +40,25 @@ def test_full_config_descriptors():
     assert all(d.weight_const == 2.0 for d in mixed)            # vega/metals.py:238-239
 
 
+def test_static_xi_flag_follows_the_sampled_set():
+    """vg_eval_desc.static_xi: set only when nothing the xi stage reads is sampled."""
+    vega, pb = builder('configs/full_configs/main.ini', sampled=['bias_eta_LYA', 'beta_LYA', 'ap', 'at'])
+    evals = pb.describe_corr('lyalya_lyalya')['evals']
+    assert evals[0].static_xi == 0                        # the peak is rescaled by the sampled (ap, at)
+    assert all(d.static_xi == 1 for d in evals[1:])       # smooth and metals: scale_form 0
+    vega, pb = builder('configs/full_configs/main.ini', sampled=['alpha_LYA'])
+    info = pb.describe_corr('lyalya_lyalya')
+    assert info['evals'][0].static_xi == 0 and info['evals'][1].static_xi == 0
+    for d, pair in zip(info['evals'][2:], info['item'].metal_correlations):
+        assert d.static_xi == int('LYA' not in pair)       # only the LYA x metal terms read alpha_LYA
+    vega, pb = builder('configs/full_configs/main.ini', sampled=['drp_QSO'])
+    assert all(d.static_xi == 0 for d in pb.describe_corr('lyalya_qso')['evals'])
+    assert all(d.static_xi == 1 for d in pb.describe_corr('lyalya_lyalya')['evals'])
+    # additive xi terms keep the gather
+    vega, pb = builder('configs/picca_bench/main_cross.ini', sampled=['bias_eta_LYA'])
+    assert pb.describe_corr('test_7')['evals'][0].static_xi == 0
+
+
 def test_sampled_parameter_makes_factor_dynamic():
     vega, pb = builder('configs/full_configs/main.ini',
                        sampled=['sigma_velo_disp_lorentz_QSO', 'L0_hcd', 'par_sigma_smooth'])

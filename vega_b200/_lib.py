@@ -45,7 +45,7 @@ class EvalDesc(C.Structure):
         ('out_slot', i32), ('weight_bias', i32), ('idx_weight_extra', i32),
         ('weight_const', f64),
         ('table_owner', i32), ('mock_los_mode', i32), ('idx_los_smooth_amp', i32),
-        ('mock_bin_size', f64), ('direct', i32), ('frozen', i32),
+        ('mock_bin_size', f64), ('direct', i32), ('frozen', i32), ('static_xi', i32), ('reserved_', i32),
     ]
 
     def __init__(self):
@@ -83,6 +83,7 @@ _SIGNATURES = {
     'vg_plan_set_chunk': (C.c_int, [_PTR, C.c_int64]),
     'vg_plan_set_option': (C.c_int, [_PTR, i32, i32]),
     'vg_corr_n_moment': (C.c_int, [_PTR, i32]),
+    'vg_corr_n_static_xi': (C.c_int, [_PTR, i32]),
     'vg_plan_set_direct_pk': (C.c_int, [_PTR, _PTR]),
     'vg_plan_set_fvoigt': (C.c_int, [_PTR, i32, _PTR, _PTR]),
     'vg_plan_set_uvshot_table': (C.c_int, [_PTR, i32, _PTR, _PTR]),

@@ -100,6 +100,9 @@ struct EvalLayout {
   DevBuf d_class_ids[23];
   std::vector<int> mom_ids;      // evaluations in moment form
   std::vector<int> gather_ids;   // evaluations K3 runs for
+  std::vector<int> mxi_ids;      // LAY_MOM: evaluations whose xi stage is in moment form (static_xi)
+  std::vector<int> mxi_owner;    //          evaluation whose moment tables each of them reads
+  DevBuf d_mxi_ids, d_mxi_owner;
   int n_full = 0;                // evaluations that go through pk_ell + the Hankel GEMM
   int n_metal = 0;               // metal column blocks of xmet / mcat
   std::vector<int> metal_map;    // metal slot -> column block (-1: not in this layout)
@@ -120,6 +123,8 @@ struct Corr {
   // Evaluations with table_owner >= 0 never own tables; frozen ones leave the hot layouts.
   EvalLayout lay[4];
   DevBuf d_mom_ktab;             // LAY_MOM: [n_mom][9][n_ell][2*n_out_pad]
+  DevBuf d_mxi_tab;              // LAY_MOM: [n_mxi][9][ld_model] xi stage applied to the moment tables
+  bool allow_mxi = true;         // cleared when the plan-time gather of the static tables fails
   std::vector<DevBuf> coords;
   std::vector<double> opz_eff2;
   DevBuf d_coord_ptrs, d_opz_eff2;
@@ -242,6 +247,67 @@ int pk_class(const vg_plan* plan, const vg_eval_desc& d) {
 }
 
 // The three evaluation layouts of a correlation (see Corr::lay)
+constexpr int NUM_SMS = 148;
+
+// K3 launch (hot path, per-stage taps, and the plan-time pass over the static moment tables)
+struct GatherJob {
+  const int* ids; int n_ids;            // evaluations gathered (device list)
+  const int* tab_slot; const int* metal_map; int n_metal;
+  const double* pfull; long long B;
+  const double* tables; int n_full;
+  const double* tables_mom; int n_mom; long long mom_stride_b, mom_stride_j;
+  int unit_bias;
+  double* core; double* xmet; double* flat_out;
+  int* status;
+};
+int launch_xi_gather(vg_plan* plan, Corr& c, const GatherJob& job, cudaStream_t st) {
+  const Hankel& h = *plan->hankels[c.hankel_id];
+  const int E = (int)c.evals.size();
+  const int rowT = 2 * h.n_out_pad;
+  const long long Bc = job.B;
+  const int n_gather = job.n_ids;
+  vg::XiArgs a{};
+  a.h.n_ell = h.n_ell; a.h.n_out = h.n_out; a.h.n_out_pad = h.n_out_pad; a.h.bounds_error = h.bounds_error;
+  for (int l = 0; l < vg::PK_MAX_ELL; ++l) {
+    a.h.ells[l] = h.ells[l];
+    a.h.x0[l] = h.x0[l]; a.h.x1[l] = h.x1[l];
+    a.h.inv_dx[l] = l < h.n_ell ? (double)(h.n_out - 1) / (h.x1[l] - h.x0[l]) : 0.0;
+  }
+  a.h.xk = h.xk.as<double>();
+  a.h.inv_h = h.inv_h.as<double>();
+  a.evals = c.d_evals.as<vg_eval_desc>(); a.n_eval = E;
+  a.pfull = job.pfull; a.npf = plan->npf; a.B = (int)Bc;
+  a.tables = job.tables; a.n_full = job.n_full;
+  a.tables_mom = job.tables_mom; a.n_mom = job.n_mom;
+  a.mom_stride_b = job.mom_stride_b; a.mom_stride_j = job.mom_stride_j;
+  a.tab_slot = job.tab_slot;
+  a.gather_ids = job.ids;
+  a.metal_map = job.metal_map;
+  a.unit_bias = job.unit_bias;
+  a.coords = c.d_coord_ptrs.as<const double*>();
+  a.opz_eff2 = c.d_opz_eff2.as<double>();
+  a.n_model = c.n_model;
+  for (int i = 0; i < 12; ++i) { a.sx.n[i] = c.sx_n[i]; a.sx.tab[i] = c.d_sx[i].as<double>(); }
+  a.uv_tau = plan->d_uv_tau.as<double>(); a.uv_a = plan->d_uv_a.as<double>(); a.uv_n = plan->uv_n;
+  a.core = job.core; a.xmet = job.xmet; a.flat_out = job.flat_out;
+  a.ld_model = c.ld_model; a.n_metal = std::max(job.n_metal, 1);
+  a.status = job.status;
+  long long ctas_wanted = 4LL * NUM_SMS;
+  int chunks = (int)std::max<long long>(1, std::min<long long>(vg_cdiv(c.ld_model, 256),
+                                                           (ctas_wanted + Bc * n_gather - 1) / (Bc * n_gather)));
+  a.bins_per_cta = vg_cdiv(c.ld_model, chunks);
+  const size_t smem = (size_t)h.n_ell * rowT * 8;
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::xi_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  dim3 grid(vg_cdiv(c.ld_model, a.bins_per_cta), n_gather, (unsigned)Bc);
+  vg::xi_gather_kernel<<<grid, 256, smem, st>>>(a);
+  VG_LAUNCHED();
+  return VG_OK;
+}
+
 int build_layouts(vg_plan* plan, Corr& c) {
   const int E = (int)c.evals.size();
   for (int e = 0; e < E; ++e) {
@@ -262,7 +328,7 @@ int build_layouts(vg_plan* plan, Corr& c) {
   for (int li = 0; li < 4; ++li) {
     EvalLayout& L = c.lay[li];
     for (auto& ids : L.class_ids) ids.clear();
-    L.mom_ids.clear(); L.gather_ids.clear();
+    L.mom_ids.clear(); L.gather_ids.clear(); L.mxi_ids.clear(); L.mxi_owner.clear();
     L.n_full = 0; L.n_metal = 0;
     L.metal_map.assign(std::max(c.n_metal, 1), -1);
     std::vector<int> slot(E, 0), tabslot(E, 0);
@@ -270,7 +336,13 @@ int build_layouts(vg_plan* plan, Corr& c) {
       const vg_eval_desc& d = c.evals[e];
       const bool hot = li == LAY_DIRECT ? d.direct != 0 : (!d.direct && (li == LAY_ALL || !d.frozen));
       if (!hot) continue;
-      L.gather_ids.push_back(e);
+      const int owner = d.table_owner >= 0 ? d.table_owner : e;
+      if (li == LAY_MOM && c.allow_mxi && d.static_xi && vg::moment_eligible(c.evals[owner])) {
+        L.mxi_ids.push_back(e);
+        L.mxi_owner.push_back(owner);
+      } else {
+        L.gather_ids.push_back(e);
+      }
       if (d.out_slot >= 2) L.metal_map[d.out_slot - 2] = L.n_metal++;
       if (d.table_owner >= 0) continue;
       if (li == LAY_MOM && vg::moment_eligible(d)) {
@@ -287,6 +359,10 @@ int build_layouts(vg_plan* plan, Corr& c) {
       if (!L.class_ids[m].empty()) VG_TRY(upload(L.d_class_ids[m], L.class_ids[m].data(), L.class_ids[m].size()));
     if (!L.mom_ids.empty()) VG_TRY(upload(L.d_mom_ids, L.mom_ids.data(), L.mom_ids.size()));
     if (!L.gather_ids.empty()) VG_TRY(upload(L.d_gather_ids, L.gather_ids.data(), L.gather_ids.size()));
+    if (!L.mxi_ids.empty()) {
+      VG_TRY(upload(L.d_mxi_ids, L.mxi_ids.data(), L.mxi_ids.size()));
+      VG_TRY(upload(L.d_mxi_owner, L.mxi_owner.data(), L.mxi_owner.size()));
+    }
     VG_TRY(upload(L.d_slot, slot.data(), slot.size()));
     VG_TRY(upload(L.d_tabslot, tabslot.data(), tabslot.size()));
     VG_TRY(upload(L.d_metal_map, L.metal_map.data(), L.metal_map.size()));
@@ -628,6 +704,41 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
                        plan->nk_pad, plan->n_ell, plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
       VG_CUDA_CHECK(cudaStreamSynchronize(st));   // `mom` is released at the end of this scope
     }
+    // xi stage in moment form: X[j][m] = gather of the static table K[owner(j)][m] on evaluation
+    // j's coordinates at the base parameters (nothing it reads is sampled), weight_const included
+    if (!LM.mxi_ids.empty()) {
+      const Hankel& h = *plan->hankels[c.hankel_id];
+      const long long row_len = (long long)plan->n_ell * 2 * h.n_out_pad;
+      const int n_mxi = (int)LM.mxi_ids.size();
+      VG_TRY(c.d_mxi_tab.alloc((size_t)n_mxi * vg::MOM_MAX * c.ld_model * 8));
+      std::vector<double> base9((size_t)vg::MOM_MAX * plan->npf);
+      for (int m = 0; m < vg::MOM_MAX; ++m) std::copy(plan->base.begin(), plan->base.end(), base9.begin() + (size_t)m * plan->npf);
+      DevBuf d_base9, d_stat;
+      VG_TRY(upload(d_base9, base9.data(), base9.size()));
+      VG_TRY(d_stat.alloc(vg::MOM_MAX * sizeof(int)));
+      VG_CUDA_CHECK(cudaMemsetAsync(d_stat.p, 0, vg::MOM_MAX * sizeof(int), st));
+      GatherJob job{};
+      job.ids = LM.d_mxi_ids.as<int>(); job.n_ids = n_mxi;
+      job.tab_slot = LM.d_tabslot.as<int>(); job.metal_map = LM.d_metal_map.as<int>(); job.n_metal = LM.n_metal;
+      job.pfull = d_base9.as<double>(); job.B = vg::MOM_MAX;
+      job.tables = nullptr; job.n_full = 0;
+      job.tables_mom = c.d_mom_ktab.as<double>(); job.n_mom = (int)LM.mom_ids.size();
+      job.mom_stride_b = row_len; job.mom_stride_j = (long long)vg::MOM_MAX * row_len;   // K is [j][m]
+      job.unit_bias = 1;
+      job.flat_out = c.d_mxi_tab.as<double>();
+      job.status = d_stat.as<int>();
+      VG_TRY(launch_xi_gather(plan, c, job, st));
+      int stat[vg::MOM_MAX];
+      VG_CUDA_CHECK(cudaMemcpyAsync(stat, d_stat.p, sizeof(stat), cudaMemcpyDeviceToHost, st));
+      VG_CUDA_CHECK(cudaStreamSynchronize(st));
+      int any = 0;
+      for (int m = 0; m < vg::MOM_MAX; ++m) any |= stat[m];
+      if (any) {   // out-of-bounds / non-finite bins must be reported per call: keep the gather
+        c.allow_mxi = false;
+        c.d_mxi_tab.release();
+        VG_TRY(build_layouts(plan, c));
+      }
+    }
     // metal matrices of the hot evaluations, concatenated along K: mcat[i][c*ld_model + j] = M_c[i][j]
     if (c.metal_dense && LM.n_metal > 0) {
       const size_t ldk = (size_t)LM.n_metal * c.ld_model;
@@ -697,7 +808,6 @@ int64_t vg_plan_device_bytes(const vg_plan* plan) {
 
 namespace {
 
-constexpr int NUM_SMS = 148;
 
 // split-K so that the CTA count fills whole waves of the 148 SMs (1 CTA/SM): the split count
 // with the best wave efficiency, keeping >= 16 K-tiles per split
@@ -926,46 +1036,28 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     VG_LAUNCHED();
   }
   if (upto <= 2) return VG_OK;
-  {  // K3
+  if (!L.gather_ids.empty()) {  // K3
     ProfScope prof(plan, PROF_XI, st);
-    const int n_gather = (int)L.gather_ids.size();
-    vg::XiArgs a{};
-    a.h.n_ell = h.n_ell; a.h.n_out = h.n_out; a.h.n_out_pad = h.n_out_pad; a.h.bounds_error = h.bounds_error;
-    for (int l = 0; l < vg::PK_MAX_ELL; ++l) {
-      a.h.ells[l] = h.ells[l];
-      a.h.x0[l] = h.x0[l]; a.h.x1[l] = h.x1[l];
-      a.h.inv_dx[l] = l < h.n_ell ? (double)(h.n_out - 1) / (h.x1[l] - h.x0[l]) : 0.0;
-    }
-    a.h.xk = h.xk.as<double>();
-    a.h.inv_h = h.inv_h.as<double>();
-    a.evals = c.d_evals.as<vg_eval_desc>(); a.n_eval = E;
-    a.pfull = plan->w_pfull.as<double>(); a.npf = plan->npf; a.B = (int)Bc;
-    a.tables = tables_full; a.n_full = Ef;
-    a.tables_mom = tables_mom; a.n_mom = Em;
-    a.tab_slot = L.d_tabslot.as<int>();
-    a.gather_ids = L.d_gather_ids.as<int>();
-    a.metal_map = L.d_metal_map.as<int>();
-    a.unit_bias = unit_bias;
-    a.coords = c.d_coord_ptrs.as<const double*>();
-    a.opz_eff2 = c.d_opz_eff2.as<double>();
-    a.n_model = c.n_model;
-    for (int i = 0; i < 12; ++i) { a.sx.n[i] = c.sx_n[i]; a.sx.tab[i] = c.d_sx[i].as<double>(); }
-    a.uv_tau = plan->d_uv_tau.as<double>(); a.uv_a = plan->d_uv_a.as<double>(); a.uv_n = plan->uv_n;
-    a.core = plan->w_core.as<double>(); a.xmet = plan->w_xmet.as<double>();
-    a.ld_model = c.ld_model; a.n_metal = std::max(L.n_metal, 1);
-    a.status = status_dev;
-    long long ctas_wanted = 4LL * NUM_SMS;
-    int chunks = (int)std::max<long long>(1, std::min<long long>(vg_cdiv(c.ld_model, 256),
-                                                             (ctas_wanted + Bc * n_gather - 1) / (Bc * n_gather)));
-    a.bins_per_cta = vg_cdiv(c.ld_model, chunks);
-    const size_t smem = (size_t)h.n_ell * rowT * 8;
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-      VG_CUDA_CHECK(cudaFuncSetAttribute(vg::xi_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      smem_set = smem;
-    }
-    dim3 grid(vg_cdiv(c.ld_model, a.bins_per_cta), n_gather, (unsigned)Bc);
-    vg::xi_gather_kernel<<<grid, 256, smem, st>>>(a);
+    GatherJob job{};
+    job.ids = L.d_gather_ids.as<int>(); job.n_ids = (int)L.gather_ids.size();
+    job.tab_slot = L.d_tabslot.as<int>(); job.metal_map = L.d_metal_map.as<int>(); job.n_metal = L.n_metal;
+    job.pfull = plan->w_pfull.as<double>(); job.B = Bc;
+    job.tables = tables_full; job.n_full = Ef;
+    job.tables_mom = tables_mom; job.n_mom = Em; job.mom_stride_b = Em * row_len; job.mom_stride_j = row_len;
+    job.unit_bias = unit_bias;
+    job.core = plan->w_core.as<double>(); job.xmet = plan->w_xmet.as<double>();
+    job.status = status_dev;
+    VG_TRY(launch_xi_gather(plan, c, job, st));
+  }
+  if (!L.mxi_ids.empty()) {  // xi stage in moment form
+    ProfScope prof(plan, PROF_XI, st);
+    const int n_mxi = (int)L.mxi_ids.size();
+    dim3 grid(vg_cdiv(c.ld_model, 256), (unsigned)n_mxi, (unsigned)vg_cdiv(Bc, vg::MXI_NB));
+    vg::moment_xi_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_mxi_ids.as<int>(),
+                                              L.d_mxi_owner.as<int>(), plan->w_pfull.as<double>(), plan->npf,
+                                              (int)Bc, c.d_mxi_tab.as<double>(), c.ld_model,
+                                              plan->w_core.as<double>(), plan->w_xmet.as<double>(),
+                                              L.d_metal_map.as<int>(), std::max(L.n_metal, 1));
     VG_LAUNCHED();
   }
   if (upto <= 3) return VG_OK;
@@ -1241,6 +1333,11 @@ int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, doubl
 int vg_corr_n_moment(const vg_plan* plan, int32_t corr) {
   if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments) return 0;
   return (int)plan->corrs[corr]->lay[LAY_MOM].mom_ids.size();
+}
+
+int vg_corr_n_static_xi(const vg_plan* plan, int32_t corr) {
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments) return 0;
+  return (int)plan->corrs[corr]->lay[LAY_MOM].mxi_ids.size();
 }
 
 int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }

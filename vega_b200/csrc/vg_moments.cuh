@@ -146,4 +146,72 @@ moment_tables_kernel(const vg_eval_desc* __restrict__ evals, const int* __restri
   }
 }
 
+// Moment form of the xi stage for evaluations whose coordinates and per-bin factors are the
+// same for every vector (vg_eval_desc::static_xi): the rescale / spline read-out / Legendre
+// sum / evolution factors (vega/correlation_func.py:117-236, vega/pktoxi.py:141-163) are
+// linear in the knot tables, so they are applied ONCE, in vg_plan_finalize, to the static
+// moment tables:  X[j][m][bin] = xi stage of evaluation ids[j] on K[owner(j)][m].  Hot path:
+//   out[b][slot(j)][bin] = w_j(theta_b) * sum_m c_m(theta_b; owner(j)) * X[j][m][bin]
+// -- 3 or 9 FMAs per bin instead of a knot-table row and a gather.  `owners[j]` is the
+// evaluation whose P(k,mu) the table belongs to (j itself unless it shares a table).
+// grid = (ceil(ld / 256), n_ids, ceil(B / MXI_NB)), block 256.
+constexpr int MXI_NB = 8;
+__global__ void __launch_bounds__(256)
+moment_xi_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__ ids,
+                 const int* __restrict__ owners, const double* __restrict__ pfull, int npf, int B,
+                 const double* __restrict__ X, int ld, double* __restrict__ core, double* __restrict__ xmet,
+                 const int* __restrict__ metal_map, int n_metal) {
+  __shared__ double cq[MXI_NB][MOM_MAX];
+  __shared__ int s_na, s_slot;
+  const int j = blockIdx.y, b0 = blockIdx.z * MXI_NB;
+  if (threadIdx.x < MXI_NB) {
+    const vg_eval_desc& d = evals[ids[j]];
+    const vg_eval_desc& o = evals[owners[j]];
+    const double* p = pfull + (long long)min(b0 + (int)threadIdx.x, B - 1) * npf;
+    KaiserCoef kc = kaiser_setup(o, p, 1.0);
+    if (o.same_tracer) { kc.a0[1] = kc.a0[0]; kc.a1[1] = kc.a1[0]; kc.h0[1] = kc.h0[0]; kc.h1[1] = kc.h1[0]; }
+    double q[MOM_MAX];
+    moment_coefs(kc, q);
+    double w = 1.0;                       // weight_const is part of X
+    if (d.weight_bias) {
+      double b1, be1, b2, be2;
+      tracer_bias_beta(d, p, 0, b1, be1);
+      tracer_bias_beta(d, p, 1, b2, be2);
+      w = b1 * b2;
+    }
+    if (d.idx_weight_extra >= 0) w *= p[d.idx_weight_extra];
+#pragma unroll
+    for (int m = 0; m < MOM_MAX; ++m) cq[threadIdx.x][m] = w * q[m];
+    if (threadIdx.x == 0) {
+      s_na = (o.hcd_model && (o.hcd_on[0] || o.hcd_on[1])) ? 3 : 1;
+      s_slot = d.out_slot;
+    }
+  }
+  __syncthreads();
+  const int x = blockIdx.x * 256 + threadIdx.x;
+  if (x >= ld) return;
+  const int na = s_na;
+  const double* xt = X + (long long)j * MOM_MAX * ld + x;
+  double acc[MXI_NB];
+#pragma unroll
+  for (int e = 0; e < MXI_NB; ++e) acc[e] = 0.0;
+  for (int a = 0; a < na; ++a)
+#pragma unroll
+    for (int jj = 0; jj < 3; ++jj) {
+      const int m = a * 3 + jj;
+      const double v = __ldg(xt + (long long)m * ld);
+#pragma unroll
+      for (int e = 0; e < MXI_NB; ++e) acc[e] = fma(cq[e][m], v, acc[e]);
+    }
+  const int slot = s_slot;
+#pragma unroll
+  for (int e = 0; e < MXI_NB; ++e) {
+    const int b = b0 + e;
+    if (b >= B) break;
+    double* out = slot < 2 ? core + ((long long)slot * B + b) * ld
+                           : xmet + ((long long)b * n_metal + metal_map[slot - 2]) * ld;
+    out[x] = acc[e];
+  }
+}
+
 }  // namespace vg

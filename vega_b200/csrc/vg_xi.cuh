@@ -42,6 +42,7 @@ struct XiArgs {
   // -(index + 1) in the second
   const double* tables; int n_full;
   const double* tables_mom; int n_mom;
+  long long mom_stride_b, mom_stride_j;   // element strides of tables_mom over vector / table
   const int* tab_slot;
   const int* gather_ids;   // evaluations gathered by this launch (grid.y entries)
   const int* metal_map;    // metal slot (out_slot - 2) -> column block of xmet
@@ -56,6 +57,7 @@ struct XiArgs {
   double* core;            // [2][B][ld_model]   slot 0 peak, 1 smooth
   double* xmet;            // [B][n_metal*ld_model]
   int ld_model, n_metal;
+  double* flat_out;        // non-null (plan time): out = flat_out[(blockIdx.y * B + b) * ld_model]
   int* status;
   int bins_per_cta;
 };
@@ -169,7 +171,7 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
                  ::"r"(smem_u32(&bar)), "r"(row_bytes * (unsigned)a.h.n_ell) : "memory");
     const int slot = a.tab_slot[e];
     const double* src = slot >= 0 ? a.tables + ((long long)b * a.n_full + slot) * a.h.n_ell * row
-                                  : a.tables_mom + ((long long)b * a.n_mom + (-slot - 1)) * a.h.n_ell * row;
+                                  : a.tables_mom + b * a.mom_stride_b + (-slot - 1) * a.mom_stride_j;
     for (int l = 0; l < a.h.n_ell; ++l) {
       asm volatile(
           "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
@@ -199,7 +201,8 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
   }
   if (d.idx_weight_extra >= 0 && !a.unit_bias) weight *= p[d.idx_weight_extra];
   double* out;
-  if (d.out_slot < 2) out = a.core + ((long long)d.out_slot * a.B + b) * a.ld_model;
+  if (a.flat_out) out = a.flat_out + ((long long)blockIdx.y * a.B + b) * a.ld_model;
+  else if (d.out_slot < 2) out = a.core + ((long long)d.out_slot * a.B + b) * a.ld_model;
   else out = a.xmet + (long long)b * a.n_metal * a.ld_model + (long long)a.metal_map[d.out_slot - 2] * a.ld_model;
 
   {  // wait for the table (phase 0)

@@ -384,6 +384,13 @@ class PlanBuilder:
             d.idx_uvshot[2] = c('uv_shotnoise_amp', True)
             self.need_uvshot = True
 
+        # static xi stage: no parameter read by the gather is sampled, no additive term
+        xi_names = [a, b] if form else []
+        xi_names += [drp_name] if drp_name is not None else []
+        xi_names += ['alpha_' + tr['name'] for tr in (tracer1, tracer2)] + ['croom_par0', 'croom_par1']
+        sampled = any(name_map.get(n, n) in self.sampled_set for n in xi_names)
+        d.static_xi = int(not sampled and not (d.radiation or d.rel or d.asy or d.uv_shot))
+
     def coord_table(self, coords, cfg):
         """[5][n] static per-bin table + (1+z_eff)^2 (vega/correlation_func.py:46-48,372-444)."""
         fid = self.vega.fiducial
@@ -839,6 +846,10 @@ class DevicePlan:
     def n_moment(self, ci):
         """Evaluations of correlation ci computed in moment form (csrc/vg_moments.cuh)."""
         return self.lib.vg_corr_n_moment(self.handle, ci)
+
+    def n_static_xi(self, ci):
+        """Evaluations of correlation ci whose xi stage is a read-out of static tables."""
+        return self.lib.vg_corr_n_static_xi(self.handle, ci)
 
     def device_bytes(self):
         return self.lib.vg_plan_device_bytes(self.handle)
