@@ -100,7 +100,10 @@ def test_dgemm_against_torch():
     from vega_b200 import _lib
     lib = _lib.load()
     torch.manual_seed(1)
-    for (M, N, K, splits) in [(1, 130, 32, 1), (37, 1590, 2512, 1), (300, 257, 4096, 5), (1024, 814, 816, 1)]:
+    # every tile height (8..64 in steps of 8, 3 x 32, 128), ragged edges, K % 32 == 16, split-K
+    shapes = [(1, 130, 32, 1), (37, 1590, 2512, 1), (300, 257, 4096, 5), (1024, 814, 816, 1)]
+    shapes += [(M, 200, 272, 1 + M % 3) for M in (5, 8, 9, 16, 17, 24, 25, 33, 41, 49, 57, 64, 65, 96, 97, 129, 130, 192, 193, 513)]
+    for (M, N, K, splits) in shapes:
         A = torch.randn(M, K, device='cuda', dtype=torch.float64)
         B = torch.randn(N, K, device='cuda', dtype=torch.float64)
         ldc = N + (N & 1)

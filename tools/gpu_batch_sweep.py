@@ -33,5 +33,20 @@ for B in [1, 8, 33, 64, 128, 256, 513, 1024, 2048, 4096]:
         vega.chi2_batch(theta)
     host_ms = (time.perf_counter() - t0) * 1e3 / n
     out[B] = {'device_ms': ms, 'host_api_ms': host_ms, 'evals_per_s': B / (ms * 1e-3)}
+    if B in (1, 33, 128, 513):       # per-stage events (they serialise the stages a little)
+        import ctypes as C
+        lib = engine.lib
+        lib.vg_profile_enable(engine.handle, 1)
+        lib.vg_launch_count(1)
+        for _ in range(n):
+            engine.chi2_device(tt)
+        torch.cuda.synchronize()
+        ms_stage, cnt_stage = (C.c_double * 8)(), (C.c_int64 * 8)()
+        lib.vg_profile_read(engine.handle, ms_stage, cnt_stage)
+        lib.vg_profile_enable(engine.handle, 0)
+        out[B]['stages_ms'] = {s_: round(ms_stage[i] / n, 4) for i, s_ in enumerate(bench.STAGES)}
+        out[B]['launches'] = lib.vg_launch_count(0) / n
     print(B, out[B], flush=True)
 print(json.dumps(out))
+Path('gpurun_out').mkdir(exist_ok=True)
+json.dump(out, open('gpurun_out/batch_sweep.json', 'w'), indent=1)

@@ -40,7 +40,8 @@ out = {}
 torch.manual_seed(0)
 for (M, N, K, splits) in [(1024, 2500, 37504, 1), (1024, 2500, 37504, 15), (1024, 2512, 2512, 1),
                           (23552, 1632, 816, 1), (8192, 8192, 8192, 1), (1184, 2500, 37504, 1),
-                          (33, 1590, 2512, 1), (1024, 5000, 20032, 4)]:
+                          (33, 1590, 2512, 1), (1024, 5000, 20032, 4),
+                          (1, 2500, 37504, 14), (35, 2500, 37504, 14), (64, 2500, 37504, 14), (35, 5000, 20032, 7)]:
     A = torch.randn(M, K, device='cuda', dtype=torch.float64)
     B = torch.randn(N, K, device='cuda', dtype=torch.float64)
     ldc = N + (N & 1)

@@ -378,8 +378,8 @@ int vg_version(void) { return 100; }
 int vg_sizeof_eval_desc(void) { return (int)sizeof(vg_eval_desc); }
 int vg_sizeof_bb_term(void) { return (int)sizeof(vg_bb_term); }
 int64_t vg_launch_count(int reset) {
-  long long v = g_launches;
-  if (reset) g_launches = 0;
+  long long v = g_launches + vg::gemm_launches();
+  if (reset) { g_launches = 0; vg::gemm_launches() = 0; }
   return v;
 }
 
@@ -845,7 +845,6 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
   if (g.splits == 1) {
     g.C = C;
     VG_TRY(vg::launch_dgemm(g, vg::GEMM_STORE, st));
-    ++g_launches;
     return VG_OK;
   }
   const long long n = (long long)M * ldc;
@@ -853,7 +852,6 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
   g.C = plan->w_split.as<double>();
   g.split_stride = n;
   VG_TRY(vg::launch_dgemm(g, vg::GEMM_STORE, st));
-  ++g_launches;
   vg::reduce_splits_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->w_split.as<double>(), C, n, g.splits, n);
   VG_LAUNCHED();
   return VG_OK;
@@ -1195,7 +1193,6 @@ int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* in
   g.C = plan->w_partial.as<double>(); g.ldc = n_tiles;
   g.D = diff; g.ldd = ld;
   VG_TRY(vg::launch_dgemm(g, vg::GEMM_ROWDOT, st));
-  ++g_launches;
   vg::chi2_partials_kernel<<<vg_cdiv(Bc, 256), 256, 0, st>>>(plan->w_partial.as<double>(), n_tiles, Bc, chi2, accumulate);
   VG_LAUNCHED();
   return VG_OK;

@@ -63,17 +63,19 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
-// BM = 128: 2 x 4 warps, warp tile 64 x 32.  BM = 32 (batches of a few vectors: the scalar API,
-// gradient stencils): 1 x 8 warps, warp tile 32 x 16 -- a 128-row tile would spend its DMMA
-// cycles on rows that do not exist, and the launch is bound by streaming the operator anyway.
+// BM = 128: 2 x 4 warps, warp tile 64 x 32.  BM = 8..64 in steps of 8 (batches of a few
+// vectors: the scalar API is 1 row, a gradient stencil 2P+1 ~ 35): 1 x 8 warps, warp tile
+// BM x 16 -- the tile is as tall as the batch (rounded up to the 8 rows of a DMMA fragment),
+// so no DMMA cycles go to rows that do not exist and the launch is bound by streaming the
+// operator from HBM.
 template <int EPI, int BM, int BK>
 __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kernel(GemmArgs g) {
   constexpr int GEMM_LDS = BK + 4;                          // padded smem row stride (doubles)
   constexpr int CPR = BK / 2;                               // 16-byte chunks per tile row
-  constexpr int MI = BM == 128 ? 8 : 4;                     // 8-row fragments per warp
+  constexpr int MI = BM == 128 ? 8 : BM / 8;                // 8-row fragments per warp
   constexpr int WARPS_M = BM / (MI * 8), WARPS_N = 8 / WARPS_M;
   constexpr int NJ = GEMM_BN / (WARPS_N * 8);               // 8-column fragments per warp
-  constexpr int A_CHUNKS = BM * CPR / GEMM_THREADS;         // 16-byte chunks of the A tile per thread
+  constexpr int A_CHUNKS = (BM * CPR + GEMM_THREADS - 1) / GEMM_THREADS;   // 16-byte chunks of the A tile per thread
   constexpr int B_CHUNKS = GEMM_BN * CPR / GEMM_THREADS;
   extern __shared__ __align__(16) double smem[];
   double* As = smem;                                        // [STAGES][BM][LDS]
@@ -114,8 +116,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
   // chunk q of a stage refill: q < A_CHUNKS from A, the rest from B
   auto load_chunk = [&](int q, int stage, long long k0, bool live) {
     if (q < A_CHUNKS) {
-      cp_async16(a_dst + stage * (BM * GEMM_LDS * 8) + q * (RPP * GEMM_LDS * 8),
-                 a_src + q * a_pass + k0, live && ((a_rows >> q) & 1u));
+      if (BM % RPP == 0 || lrow + q * RPP < BM)      // a short tile ends inside the last pass
+        cp_async16(a_dst + stage * (BM * GEMM_LDS * 8) + q * (RPP * GEMM_LDS * 8),
+                   a_src + q * a_pass + k0, live && ((a_rows >> q) & 1u));
     } else {
       const int r = q - A_CHUNKS;
       cp_async16(b_dst + stage * (GEMM_BN * GEMM_LDS * 8) + r * (RPP * GEMM_LDS * 8),
@@ -174,9 +177,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
       for (int i = 0; i < MI; ++i) {
 #pragma unroll
         for (int j = 0; j < NJ; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[c][i], b[c][j]);
-        // one refill chunk after every (MI / CHUNKS_PER_STEP)-th fragment row
-        if (CHUNKS_PER_STEP > 0 && (i + 1) % (MI / CHUNKS_PER_STEP) == 0) {
-          const int q = st * CHUNKS_PER_STEP + (i + 1) / (MI / CHUNKS_PER_STEP) - 1;
+        // the refill chunks of this step, spread over its fragment rows
+        constexpr int EVERY = MI >= CHUNKS_PER_STEP ? MI / CHUNKS_PER_STEP : 1;
+        if ((i + 1) % EVERY == 0 && (i + 1) / EVERY <= CHUNKS_PER_STEP) {
+          const int q = st * CHUNKS_PER_STEP + (i + 1) / EVERY - 1;
+          if (q < N_CHUNKS) load_chunk(q, nxt, k_next, live);
+        }
+      }
+      if (MI < CHUNKS_PER_STEP) {   // fewer fragment rows than chunks: the rest after the step
+#pragma unroll
+        for (int r = MI; r < CHUNKS_PER_STEP; ++r) {
+          const int q = st * CHUNKS_PER_STEP + r;
           if (q < N_CHUNKS) load_chunk(q, nxt, k_next, live);
         }
       }
@@ -255,43 +266,69 @@ __global__ void reduce_splits_kernel(const double* __restrict__ W, double* __res
   C[i] = s;
 }
 
-constexpr int GEMM_BM_SMALL = 32;
-constexpr int GEMM_SMEM_SMALL = gemm_smem_bytes(GEMM_BM_SMALL, GEMM_BK);
-// rows of A at or below which the 32-row tile is used
+// rows of A up to which a batch-height tile (8..64 rows) is used; 65..96 rows take three
+// 32-row tiles, anything taller the 128-row tile
 constexpr int GEMM_SMALL_M = 96;
-inline int gemm_tile_m(int M) { return M <= GEMM_SMALL_M ? GEMM_BM_SMALL : GEMM_BM; }
+inline int gemm_tile_m(int M) {
+  if (M <= 64) return 8 * ((M + 7) / 8);
+  return M <= GEMM_SMALL_M ? 32 : GEMM_BM;
+}
+
+template <int EPI, int BM, int BK>
+inline int launch_dgemm_tile(const GemmArgs& g, dim3 grid, cudaStream_t stream) {
+  constexpr int smem = gemm_smem_bytes(BM, BK);
+  static bool attr_set = false;
+  if (!attr_set) {
+    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<EPI, BM, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  dgemm_tn_kernel<EPI, BM, BK><<<grid, GEMM_THREADS, smem, stream>>>(g);
+  return VG_OK;
+}
+template <int EPI>
+inline int launch_dgemm_epi(const GemmArgs& g, int bm, dim3 grid, cudaStream_t stream) {
+  switch (bm) {
+    case 8: return launch_dgemm_tile<EPI, 8, GEMM_BK>(g, grid, stream);
+    case 16: return launch_dgemm_tile<EPI, 16, GEMM_BK>(g, grid, stream);
+    case 24: return launch_dgemm_tile<EPI, 24, GEMM_BK>(g, grid, stream);
+    case 32: return launch_dgemm_tile<EPI, 32, GEMM_BK>(g, grid, stream);
+    case 40: return launch_dgemm_tile<EPI, 40, GEMM_BK>(g, grid, stream);
+    case 48: return launch_dgemm_tile<EPI, 48, GEMM_BK>(g, grid, stream);
+    case 56: return launch_dgemm_tile<EPI, 56, GEMM_BK>(g, grid, stream);
+    case 64: return launch_dgemm_tile<EPI, 64, GEMM_BK>(g, grid, stream);
+    default: return launch_dgemm_tile<EPI, GEMM_BM, GEMM_BK_BIG>(g, grid, stream);
+  }
+}
+
+// kernels launched by launch_dgemm (bench bookkeeping)
+inline long long& gemm_launches() { static long long n = 0; return n; }
 
 inline int launch_dgemm(const GemmArgs& g, int epilogue, cudaStream_t stream) {
   if (g.K % GEMM_BK != 0 || (g.lda & 1) || (g.ldb & 1) || g.M <= 0 || g.N <= 0) {
     vg_set_error("dgemm: bad shape M=%d N=%d K=%d lda=%lld ldb=%lld", g.M, g.N, g.K, g.lda, g.ldb);
     return VG_ERR_ARG;
   }
+  // a batch a few rows taller than a multiple of 128 (the 2F^2+1 vectors of a Hessian stencil:
+  // 513 for F = 16) would spend a whole 128-row tile on them: those rows go to a second launch
+  // with a batch-height tile, which only streams the operator once more
+  const int rem = g.M % GEMM_BM;
+  if (g.M > GEMM_BM && rem > 0 && rem <= 64) {
+    GemmArgs head = g, tail = g;
+    head.M = g.M - rem;
+    tail.M = rem;
+    tail.A += (long long)head.M * g.lda;
+    tail.C += (long long)head.M * g.ldc;
+    if (g.D) tail.D += (long long)head.M * g.ldd;
+    const int rc = launch_dgemm(head, epilogue, stream);
+    return rc != VG_OK ? rc : launch_dgemm(tail, epilogue, stream);
+  }
   const int bm = gemm_tile_m(g.M);
   dim3 grid(vg_cdiv(g.M, bm), vg_cdiv(g.N, GEMM_BN), g.batch * g.splits);
-  static bool attr_set = false;
-  if (!attr_set) {
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE, GEMM_BM, GEMM_BK_BIG>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM, GEMM_BK_BIG>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM));
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_STORE, GEMM_BM_SMALL, GEMM_BK>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_SMALL));
-    VG_CUDA_CHECK(cudaFuncSetAttribute(dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM_SMALL, GEMM_BK>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_SMALL));
-    attr_set = true;
-  }
-  if (bm == GEMM_BM) {
-    if (epilogue == GEMM_STORE)
-      dgemm_tn_kernel<GEMM_STORE, GEMM_BM, GEMM_BK_BIG><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
-    else
-      dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM, GEMM_BK_BIG><<<grid, GEMM_THREADS, GEMM_SMEM, stream>>>(g);
-  } else {
-    if (epilogue == GEMM_STORE)
-      dgemm_tn_kernel<GEMM_STORE, GEMM_BM_SMALL, GEMM_BK><<<grid, GEMM_THREADS, GEMM_SMEM_SMALL, stream>>>(g);
-    else
-      dgemm_tn_kernel<GEMM_ROWDOT, GEMM_BM_SMALL, GEMM_BK><<<grid, GEMM_THREADS, GEMM_SMEM_SMALL, stream>>>(g);
-  }
+  const int rc = epilogue == GEMM_STORE ? launch_dgemm_epi<GEMM_STORE>(g, bm, grid, stream)
+                                       : launch_dgemm_epi<GEMM_ROWDOT>(g, bm, grid, stream);
+  if (rc != VG_OK) return rc;
   VG_CUDA_CHECK(cudaGetLastError());
+  ++gemm_launches();
   return VG_OK;
 }
 
