@@ -186,6 +186,11 @@ int vg_corr_set_static_xi(vg_plan* plan, int32_t corr, int32_t which, int32_t pk
 /* Metal matrix of metal slot c, [n_model][n_model] row-major (vega/metals.py:338-367).
  * Slots never set are identity (the reference's `test` flag, vega/data.py:683-684). */
 int vg_corr_set_metal_matrix(vg_plan* plan, int32_t corr, int32_t slot, const double* mat);
+/* rp-only metal matrix of a new_metals configuration (vega/metals.py:354-358, 679-752):
+ * mat[n_rp][n_rp], applied to every rt column of the metal xi (n_rp * n_rt = model bins).  A
+ * correlation uses either this form for all of its metal correlations or dense matrices. */
+int vg_corr_set_metal_matrix_rp(vg_plan* plan, int32_t corr, int32_t slot, const double* mat,
+                                int32_t n_rp, int32_t n_rt);
 /* Distortion matrix [n_dist][n_model] (vega/model.py:143-144); never set = identity. */
 int vg_corr_set_distortion(vg_plan* plan, int32_t corr, const double* dmat);
 /* DESI instrumental systematics: amp * table[n_model] added to the smooth component
@@ -274,6 +279,23 @@ int64_t vg_launch_count(int reset);
 /* FP64 FMA throughput probe (8 independent chains per thread): the measured ALU roofline
  * the fused P(k,mu) kernel is graded against.  out_dev: blocks*256 doubles of scratch. */
 int vg_probe_dfma(int blocks, int iters, double* out_dev, double* tflops, void* stream);
+
+/* new_metals metal matrices (vega/metals.py:502-752, init time): the weighted histograms over
+ * all N1 x N2 pixel pairs of two stacked-weight tables that the reference forms with
+ * np.histogram2d / np.histogram (:543-556, :566-584, :625-637, :716-728).  Host pointers.
+ * side = [5][n] doubles: comoving distance at the TRUE absorber redshift, at the ASSUMED
+ * (main-tracer) redshift, true redshift, assumed redshift, weight (scaling included).
+ *   vg_metal_pair_ratio_range  range_out[2] = min, max of d_assumed / d_true over all pairs
+ *   vg_metal_pair_histograms   H[nb][nb] by (assumed, true) rp bin; per_true[nb];
+ *                              per_assumed[3][nb] = sum w, sum w*rp_assumed, sum w*z_true_pair;
+ *                              ratio[nr] (nr = 0: skipped) = sum w / d_true^2 (|rp_true| < 20)
+ * Bins are [e_i, e_{i+1}), last one closed, as numpy's; signed_rp = a discrete tracer is in. */
+int vg_metal_pair_ratio_range(const double* side1, int32_t n1, const double* side2, int32_t n2,
+                              double* range_out);
+int vg_metal_pair_histograms(const double* side1, int32_t n1, const double* side2, int32_t n2,
+                             int32_t signed_rp, double zmin, double zmax, const double* rp_edges, int32_t nb,
+                             const double* ratio_edges, int32_t nr, double* H, double* per_true,
+                             double* per_assumed, double* ratio);
 
 /* Stand-alone FP64 tensor-core GEMM C[m,n] = alpha sum_k A[m,k] B[n,k] + beta C (tests) */
 int vg_dgemm_tn(const double* A, const double* B, double* C, int M, int N, int K,

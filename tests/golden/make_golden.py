@@ -109,10 +109,22 @@ def main():
                                            control={'marginalize-in-fit': True},
                                            data={'distortion-file': dmat})
     PERTURBED['c1_marg'] = PERTURBED['c1_marg_fit'] = PERTURBED['c1']
+    # new_metals (vega/metals.py:83-108,370-752): matrices from stacked weights, rp-only and
+    # full 2-D form, on the reference's own auto + cross options; picca.constants is the
+    # restatement in vega_b200/cosmo.py (tests/golden/shims/picca/constants.py)
+    sys.path.insert(0, str(REPO / 'tests'))
+    from helpers import make_new_metals_config
+    base = str(REPO / 'tests' / 'configs' / 'full_configs' / 'main.ini')
+    CONFIGS['new_metals_rp'] = make_new_metals_config('/tmp/vega_golden_nm_rp', True, base=base)
+    CONFIGS['new_metals_2d'] = make_new_metals_config('/tmp/vega_golden_nm_2d', False, base=base)
+    PERTURBED['new_metals_rp'] = PERTURBED['new_metals_2d'] = PERTURBED['full'][:2]
     # Model.compute_direct through the direct_pk argument (vega/model.py:189-208)
     CONFIGS['full_direct'] = CONFIGS['full']
     PERTURBED['full_direct'] = PERTURBED['full']
-    notes = {'full_direct': CONFIGS['full'] + ' with direct_pk = pk_full (1 + 0.05 sin(3 ln k))',
+    notes = {'new_metals_rp': 'helpers.make_new_metals_config(rp_only=True): full_configs auto + cross, '
+                              'new_metals = True, rp_only_metal_mats = True, seeded weight tables',
+             'new_metals_2d': 'same with rp_only_metal_mats = False',
+             'full_direct': CONFIGS['full'] + ' with direct_pk = pk_full (1 + 0.05 sin(3 ln k))',
              'full_fast': CONFIGS['full'] + ' + fast_metals = True',
              'c1_marg': f"{CONFIGS['c1']} + [model] {MARG_CUTS} + distortion-file (55x55 bins)",
              'c1_marg_fit': f"{CONFIGS['c1']} + [model] {MARG_FIT} + [control] marginalize-in-fit "
@@ -147,6 +159,24 @@ def main():
                 for name, xi in model.items():
                     out[f'{key}/{i}/xi_marg/{name}'] = np.asarray(xi, dtype=float)
             print(key, i, float(out[f'{key}/{i}/chi2']), float(out[f'{key}/{i}/log_lik']))
+        if key.startswith('new_metals'):
+            # the matrices themselves: rp-only in full, the 2-D ones through three probe vectors
+            # (a (Np Nt)^2 matrix is 50 MB), and the effective coordinate grids
+            meta[key]['pairs'] = {}
+            for name in vega.corr_items:
+                metals = vega.models[name].metals
+                pairs = list(vega.corr_items[name].metal_correlations)
+                meta[key]['pairs'][name] = [list(p) for p in pairs]
+                for c, pair in enumerate(pairs):
+                    mat = metals.rp_metal_dmats[pair]
+                    xi_c = metals.Xi_metal[pair]
+                    out[f'{key}/coords/{name}/{c}'] = np.stack([xi_c._r, xi_c._mu, xi_c._z])
+                    if key.endswith('_rp'):
+                        out[f'{key}/mat/{name}/{c}'] = np.asarray(mat, dtype=float)
+                    else:
+                        n = mat.shape[1]
+                        probes = np.stack([np.cos(0.013 * (j + 1) * np.arange(n)) for j in range(3)], axis=1)
+                        out[f'{key}/mat_probe/{name}/{c}'] = np.asarray(mat @ probes, dtype=float)
     np.savez_compressed(REPO / 'tests' / 'golden' / 'reference_outputs.npz', **out)
     (REPO / 'tests' / 'golden' / 'reference_outputs.json').write_text(json.dumps(meta, indent=1))
 

@@ -1,7 +1,3 @@
-"""Names only; new_metals / cosmo-dependent paths are out of scope."""
-ABSORBER_IGM = {}
-
-
-class Cosmo:
-    def __init__(self, *a, **k):
-        raise NotImplementedError('picca.Cosmo is not available in this image')
+"""picca.constants stand-in for the golden generator: the restated cosmology and rest
+wavelengths of vega_b200/cosmo.py (picca itself is not in the image; see that module)."""
+from vega_b200.cosmo import ABSORBER_IGM, SPEED_LIGHT, Cosmo  # noqa: F401

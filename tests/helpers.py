@@ -122,3 +122,101 @@ def make_marg_case(tmp_path, key):
                              control={'marginalize-in-fit': True}, data={'distortion-file': dmat})
     vega = VegaInterface(main)
     return vega, Oracle(vega, tables=static_tables())
+
+
+# ---------------------------------------------------------------------------------------------
+# new_metals (vega/metals.py:83-108, 370-752): configurations with stacked-weight tables
+# ---------------------------------------------------------------------------------------------
+NEW_METALS_ALPHA = {'LYA': 2.9, 'SiII(1190)': 1.0, 'SiII(1193)': 1.0, 'SiIII(1207)': 1.0,
+                    'SiII(1260)': 1.0, 'CIV(eff)': 1.0}
+
+
+def write_new_metals_inputs(tmp_dir, n_pix=520, n_qso=4000, seed=7):
+    """Stacked forest weights (LOGLAM, WEIGHT) and an object catalogue (Z), seeded."""
+    from vega_b200 import fitsio
+    tmp_dir = Path(tmp_dir)
+    tmp_dir.mkdir(parents=True, exist_ok=True)
+    rng = np.random.default_rng(seed)
+    loglam = np.log10(3600.) + 3e-4 * np.arange(n_pix)          # 3600 .. ~5160 A
+    weight = (1 + 0.3 * np.sin(np.linspace(0, 7, n_pix))) * np.exp(-0.5 * ((loglam - 3.63) / 0.05)**2) \
+        * (1 + 0.05 * rng.standard_normal(n_pix))
+    forest = tmp_dir / 'forest_weights.fits'
+    fitsio.write_tables(forest, [('STACK', {}, {'LOGLAM': loglam, 'WEIGHT': np.abs(weight)})])
+    catalogue = tmp_dir / 'objects.fits'
+    fitsio.write_tables(catalogue, [('CAT', {}, {'Z': 2.0 + 1.2 * rng.beta(2., 3., n_qso)})])
+    return str(forest), str(catalogue)
+
+
+def copy_data_with_cosmology(src, dst, omega_m=0.315):
+    """Copy of a correlation-function file whose header carries the fiducial cosmology
+    (vega/data.py:361-366 reads OMEGAM / OMEGAK / OMEGAR / WL)."""
+    from vega_b200 import fitsio
+    hdul = fitsio.open(utils.find_file(src))
+    tables = []
+    for i, hdu in enumerate(hdul[1:]):
+        header = {k: hdu.header[k] for k in ('RPMIN', 'RPMAX', 'RTMAX', 'NP', 'NT', 'BLINDING')
+                  if k in hdu.header}
+        if i == 0:
+            header.update({'OMEGAM': omega_m, 'OMEGAK': 0., 'OMEGAR': 7.9e-5, 'WL': -1.})
+        tables.append((hdu.header.get('EXTNAME', f'HDU{i + 1}'), header,
+                       {name: np.asarray(hdu.data[name]) for name in hdu.columns.names}))
+    fitsio.write_tables(dst, tables)
+    return str(dst)
+
+
+def make_new_metals_config(tmp_dir, rp_only, base='configs/full_configs/main.ini',
+                           corrs=('lyalya_lyalya', 'lyalya_qso'), rebin=2):
+    """The reference's own auto + cross configuration switched to new_metals: no metal file,
+    matrices from the weight tables.  Returns the main ini path."""
+    import configparser
+    tmp_dir = Path(tmp_dir)
+    forest, catalogue = write_new_metals_inputs(tmp_dir)
+
+    def read(path):
+        cfg = configparser.ConfigParser()
+        cfg.optionxform = lambda option: option
+        cfg.read(utils.find_file(path))
+        return cfg
+
+    main = read(base)
+    new_paths = []
+    for path in main['data sets']['ini files'].split():
+        if Path(path).stem not in corrs:
+            continue
+        cfg = read(path)
+        cfg['model']['new_metals'] = 'True'
+        cfg['model']['rp_only_metal_mats'] = str(bool(rp_only))
+        data_file = tmp_dir / (Path(path).stem + '_data.fits')
+        cfg['data']['filename'] = copy_data_with_cosmology(cfg['data']['filename'], data_file)
+        cfg['data']['weights-tracer1'] = forest
+        if cfg['data'].get('tracer2-type', 'continuous') == 'discrete':
+            cfg['data']['weights-tracer2'] = catalogue
+        cfg['metals'].pop('filename', None)
+        cfg['metal-matrix'] = {'rebin_factor': str(rebin), 'z_bins_objects': '300'}
+        for name, alpha in NEW_METALS_ALPHA.items():
+            cfg['metal-matrix'][f'alpha_{name}'] = str(alpha)
+        new_path = tmp_dir / Path(path).name
+        with open(new_path, 'w') as f:
+            cfg.write(f)
+        new_paths.append(str(new_path))
+    main['data sets']['ini files'] = ' '.join(new_paths)
+    main['output']['filename'] = str(tmp_dir / 'out')
+    out = tmp_dir / 'main.ini'
+    with open(out, 'w') as f:
+        main.write(f)
+    return str(out)
+
+
+def oracle_metal_builder(corr_item, data):
+    """The CPU oracle's new_metals matrices (oracle/metal_matrices.py) behind the Data hook."""
+    from oracle.metal_matrices import MetalMatrixOracle
+    from vega_b200 import fitsio
+    from vega_b200.coordinates import Coordinates
+    from vega_b200.cosmo import ABSORBER_IGM
+    from vega_b200.metal_matrices import RpOnlyMatrix
+    oracle = MetalMatrixOracle(corr_item, corr_item.cosmo, ABSORBER_IGM, fitsio.open)
+    rp_only = corr_item.config['model'].getboolean('rp_only_metal_mats', False)
+    for pair in corr_item.metal_correlations:
+        mat, rp, rt, z = oracle.rp_matrix(*pair) if rp_only else oracle.full_matrix(*pair)
+        data.metal_mats[pair] = RpOnlyMatrix(mat, corr_item.model_coordinates.rt_nbins) if rp_only else mat
+        data.metal_coordinates[pair] = Coordinates.init_from_grids(corr_item.model_coordinates, rp, rt, z)

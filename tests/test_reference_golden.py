@@ -96,6 +96,55 @@ def test_cuda_path_matches_reference_direct_pk():
         assert abs(value - ref) <= 1e-6 * max(1.0, abs(ref) / 1e4)
 
 
+def check_new_metals_matrices(key, vega, gold, meta, rtol):
+    """Metal matrices and effective coordinates of a new_metals plan against the reference's
+    (vega/metals.py:502-752): the rp-only matrices entry by entry, the 2-D ones through the
+    three probe vectors of make_golden.py."""
+    for name, pairs in meta[key]['pairs'].items():
+        data = vega.data[name]
+        for c, pair in enumerate(pairs):
+            coords, mat = data.get_metal(tuple(pair))
+            ref = gold[f'{key}/coords/{name}/{c}']
+            got = np.stack([coords.r_grid, coords.mu_grid, coords.z_grid])
+            assert np.max(np.abs(got - ref)) <= rtol * np.max(np.abs(ref)), (name, pair)
+            if key.endswith('_rp'):
+                ref = gold[f'{key}/mat/{name}/{c}']
+                assert np.max(np.abs(mat.rp_mat - ref)) <= rtol * np.max(np.abs(ref)), (name, pair)
+            else:
+                ref = gold[f'{key}/mat_probe/{name}/{c}']
+                n = mat.shape[1]
+                probes = np.stack([np.cos(0.013 * (j + 1) * np.arange(n)) for j in range(3)], axis=1)
+                assert np.max(np.abs(mat @ probes - ref)) <= rtol * np.max(np.abs(ref)), (name, pair)
+
+
+@pytest.mark.parametrize('key', ['new_metals_rp', 'new_metals_2d'])
+def test_oracle_matches_reference_new_metals(key, tmp_path):
+    """oracle/metal_matrices.py against the unmodified reference's compute_metal_rp_dmat /
+    compute_metal_dmat, and the model built on those matrices."""
+    from helpers import make_new_metals_config, oracle_metal_builder, static_tables
+    from oracle.vega_oracle import Oracle
+    from vega_b200 import VegaInterface
+    gold, meta = load()
+    vega = VegaInterface(make_new_metals_config(tmp_path, key.endswith('_rp')),
+                         metal_builder=oracle_metal_builder)
+    check_new_metals_matrices(key, vega, gold, meta, 1e-12)
+    oracle = Oracle(vega, tables=static_tables())
+    check(key, oracle.compute_model, oracle.chi2, oracle.log_lik, gold, meta)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('key', ['new_metals_rp', 'new_metals_2d'])
+def test_cuda_path_matches_reference_new_metals(key, tmp_path):
+    """Product path: pair histograms on the device (vg_metal_pair_histograms), the matrices
+    applied by the hot path."""
+    from helpers import make_new_metals_config
+    from vega_b200 import VegaInterface
+    gold, meta = load()
+    vega = VegaInterface(make_new_metals_config(tmp_path, key.endswith('_rp')))
+    check_new_metals_matrices(key, vega, gold, meta, 1e-11)
+    check(key, vega.compute_model, vega.chi2, vega.log_lik, gold, meta)
+
+
 @pytest.mark.parametrize('key', ['c1_marg', 'c1_marg_fit'])
 def test_oracle_matches_reference_marginalisation(key, tmp_path):
     from helpers import make_marg_case

@@ -94,6 +94,7 @@ _SIGNATURES = {
     'vg_corr_add_eval': (C.c_int, [_PTR, i32, C.POINTER(EvalDesc), C.POINTER(i32)]),
     'vg_corr_set_static_xi': (C.c_int, [_PTR, i32, i32, i32, i32, _PTR]),
     'vg_corr_set_metal_matrix': (C.c_int, [_PTR, i32, i32, _PTR]),
+    'vg_corr_set_metal_matrix_rp': (C.c_int, [_PTR, i32, i32, _PTR, i32, i32]),
     'vg_corr_set_distortion': (C.c_int, [_PTR, i32, _PTR]),
     'vg_corr_set_inst_sys': (C.c_int, [_PTR, i32, _PTR, i32, f64]),
     'vg_corr_set_broadband': (C.c_int, [_PTR, i32, i32, _PTR, i32, _PTR, i32, _PTR, _PTR, _PTR]),
@@ -112,6 +113,9 @@ _SIGNATURES = {
     'vg_stage_batch': (C.c_int, [_PTR, i32, i32, i32, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_stage_size': (C.c_int64, [_PTR, i32, i32]),
     'vg_probe_dfma': (C.c_int, [C.c_int, C.c_int, _PTR, C.POINTER(f64), _PTR]),
+    'vg_metal_pair_ratio_range': (C.c_int, [_PTR, i32, _PTR, i32, _PTR]),
+    'vg_metal_pair_histograms': (C.c_int, [_PTR, i32, _PTR, i32, i32, f64, f64, _PTR, i32, _PTR, i32,
+                                           _PTR, _PTR, _PTR, _PTR]),
     'vg_dgemm_tn': (C.c_int, [_PTR, _PTR, _PTR, C.c_int, C.c_int, C.c_int, C.c_longlong,
                               C.c_longlong, C.c_longlong, f64, f64, C.c_int, _PTR, _PTR]),
 }

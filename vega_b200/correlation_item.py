@@ -33,11 +33,11 @@ class CorrelationItem:
         self.test_flag = data_cfg.getboolean('test', False)
 
         self.new_metals = model_cfg.getboolean('new_metals', False)
-        if self.new_metals:
-            raise NotImplementedError(
-                'new_metals (metal matrices histogrammed from forest weights, '
-                'vega/metals.py:502-752) is init-time work outside the B200 hot path; '
-                'supply the metal matrices in a metal file instead.')
+        if self.new_metals:      # vega/correlation_item.py:44-49
+            self.tracer1['weights-path'] = data_cfg.get('weights-tracer1')
+            self.tracer2['weights-path'] = data_cfg.get('weights-tracer2', None)
+            if self.tracer2['weights-path'] is None:
+                self.tracer2['weights-path'] = self.tracer1['weights-path']
 
         self.marginalize_small_scales = {}
         for key, name in (('marginalize-below-rtmax', 'rtmax'), ('marginalize-above-rtmin', 'rtmin'),
@@ -84,11 +84,12 @@ class CorrelationItem:
             else dist_model_coordinates
 
     def init_cosmo(self, cosmo_params):
-        """The reference builds a picca Cosmo here (vega/correlation_item.py:139-151),
-        used only by new-bias-evolution and new_metals; both need picca, which is
-        outside this path, so only the parameters are kept."""
+        """vega/correlation_item.py:138-151; the cosmology object is vega_b200/cosmo.py's
+        restatement of picca's (used by new_metals)."""
+        from .cosmo import Cosmo
         self.cosmo_params = cosmo_params
-        self.cosmo = None
+        self.cosmo = Cosmo(Om=cosmo_params['Omega_m'], Ok=cosmo_params['Omega_k'],
+                           Or=cosmo_params['Omega_r'], wl=cosmo_params['wl'])
 
     def check_if_blind_corr(self, blind_tracers):
         if 'all' in blind_tracers:

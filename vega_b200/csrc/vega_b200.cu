@@ -11,6 +11,7 @@
 #include "../../include/vega_b200.h"
 #include "vg_common.cuh"
 #include "vg_gemm.cuh"
+#include "vg_metalmat.cuh"
 #include "vg_moments.cuh"
 #include "vg_pk.cuh"
 #include "vg_post.cuh"
@@ -131,6 +132,11 @@ struct Corr {
   int n_metal = 0;               // metal slots declared by the evaluations (all layouts)
   bool metal_dense = false;
   std::vector<std::vector<double>> metal_host;
+  // rp-only metal matrices (new_metals, vega/metals.py:354-358): [rp_np][rp_np] per slot
+  bool metal_rp = false;
+  int rp_np = 0, rp_nt = 0;
+  std::vector<std::vector<double>> metal_rp_host;
+  DevBuf d_mrp;                  // hot ones, [n_metal_hot][rp_np][rp_np] in column-block order
   std::vector<int> frozen_ids;   // frozen evaluations, in order of d_frozen rows
   DevBuf d_frozen_ids, d_frozen; // d_frozen [n_frozen][ld_model] = weight_const * M_c xi_c
   DevBuf d_mcat;                 // hot metal matrices [n_model][n_metal_hot*ld_model]
@@ -220,6 +226,8 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
               double* C, long long ldc, int M, int N, int K, int batch, long long strideA,
               long long strideB, long long strideC, cudaStream_t st);
 int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
+int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
+                    cudaStream_t st);
 enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_MOMENT = 7, PROF_NTAGS = 8 };
 }  // namespace
 
@@ -570,6 +578,20 @@ int vg_corr_set_metal_matrix(vg_plan* plan, int32_t corr, int32_t slot, const do
   return VG_OK;
 }
 
+int vg_corr_set_metal_matrix_rp(vg_plan* plan, int32_t corr, int32_t slot, const double* mat,
+                                int32_t n_rp, int32_t n_rt) {
+  VG_CORR(plan, corr);
+  VG_REQUIRE(slot >= 0 && slot < 4096, "bad metal slot");
+  VG_REQUIRE(n_rp > 0 && n_rt > 0 && n_rp * n_rt == c.n_model, "rp-only metal matrix: %d x %d bins != %d",
+             n_rp, n_rt, c.n_model);
+  VG_REQUIRE(n_rp <= 4 * vg::MRP_ROWS, "rp-only metal matrix: more than %d rp bins", 4 * vg::MRP_ROWS);
+  VG_REQUIRE(!c.metal_rp || (c.rp_np == n_rp && c.rp_nt == n_rt), "rp-only metal matrices of different shapes");
+  if ((int)c.metal_rp_host.size() <= slot) c.metal_rp_host.resize(slot + 1);
+  c.metal_rp_host[slot].assign(mat, mat + (size_t)n_rp * n_rp);
+  c.metal_rp = true; c.rp_np = n_rp; c.rp_nt = n_rt;
+  return VG_OK;
+}
+
 int vg_corr_set_distortion(vg_plan* plan, int32_t corr, const double* dmat) {
   VG_CORR(plan, corr);
   VG_TRY(upload_padded(c.d_dmat, dmat, c.n_dist, c.n_model, c.ld_model));
@@ -738,6 +760,21 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
         c.d_mxi_tab.release();
         VG_TRY(build_layouts(plan, c));
       }
+    }
+    VG_REQUIRE(!(c.metal_rp && c.metal_dense), "a correlation mixes dense and rp-only metal matrices");
+    if (c.metal_rp && LM.n_metal > 0) {   // rp-only matrices of the hot evaluations, column-block order
+      const size_t nn = (size_t)c.rp_np * c.rp_np;
+      std::vector<double> host((size_t)LM.n_metal * nn, 0.0);
+      for (int s = 0; s < c.n_metal; ++s) {
+        const int col = LM.metal_map[s];
+        if (col < 0) continue;
+        double* dst = host.data() + (size_t)col * nn;
+        if (s < (int)c.metal_rp_host.size() && !c.metal_rp_host[s].empty())
+          std::copy(c.metal_rp_host[s].begin(), c.metal_rp_host[s].end(), dst);
+        else
+          for (int i = 0; i < c.rp_np; ++i) dst[(size_t)i * c.rp_np + i] = 1.0;
+      }
+      VG_TRY(upload(c.d_mrp, host.data(), host.size()));
     }
     // metal matrices of the hot evaluations, concatenated along K: mcat[i][c*ld_model + j] = M_c[i][j]
     if (c.metal_dense && LM.n_metal > 0) {
@@ -956,6 +993,19 @@ int launch_pk_fast(int vmode, int kind, dim3 grid, dim3 block, size_t smem, cuda
   }
 }
 
+int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
+                    cudaStream_t st) {
+  const size_t smem = (size_t)c.n_model * 8;
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::metal_rp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  vg::metal_rp_kernel<<<(unsigned)B, 256, smem, st>>>(xmet, n_metal, c.ld_model, A, c.rp_np, c.rp_nt, met);
+  VG_LAUNCHED();
+  return VG_OK;
+}
+
 // Stages K1..K3 + metals + pre-distortion assembly of one correlation: leaves
 // x[Bc][ld_model] in plan->w_x.  `upto` stops early for the per-stage taps.
 int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaStream_t st, int upto = 99,
@@ -1062,8 +1112,11 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   // metals: sum_c w_c M_c xi_c  (vega/metals.py:258-367)
   const double* met = nullptr;
   if (L.n_metal > 0) {
-    ProfScope prof(plan, c.metal_dense ? PROF_METAL : PROF_ELEM, st);
-    if (c.metal_dense) {
+    ProfScope prof(plan, (c.metal_dense || c.metal_rp) ? PROF_METAL : PROF_ELEM, st);
+    if (c.metal_rp) {
+      VG_TRY(launch_metal_rp(c, plan->w_xmet.as<double>(), L.n_metal, c.d_mrp.as<double>(), Bc,
+                             plan->w_met.as<double>(), st));
+    } else if (c.metal_dense) {
       const long long ldk = (long long)L.n_metal * c.ld_model;
       VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, c.d_mcat.as<double>(), ldk,
                        plan->w_met.as<double>(), c.ld_model, (int)Bc, c.n_model, (int)ldk, 1, 0, 0, 0, st));
@@ -1116,7 +1169,11 @@ int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st) {
     const int slot = c.evals[c.frozen_ids[f]].out_slot - 2;
     const double* xi = plan->w_xmet.as<double>() + (size_t)L.metal_map[slot] * c.ld_model;
     double* dst = c.d_frozen.as<double>() + (size_t)f * c.ld_model;
-    if (c.metal_dense && slot < (int)c.metal_host.size() && !c.metal_host[slot].empty()) {
+    if (c.metal_rp && slot < (int)c.metal_rp_host.size() && !c.metal_rp_host[slot].empty()) {
+      VG_TRY(upload(mat, c.metal_rp_host[slot].data(), c.metal_rp_host[slot].size()));
+      VG_TRY(launch_metal_rp(c, xi, 1, mat.as<double>(), 1, dst, st));
+      VG_CUDA_CHECK(cudaStreamSynchronize(st));
+    } else if (c.metal_dense && slot < (int)c.metal_host.size() && !c.metal_host[slot].empty()) {
       VG_TRY(upload_padded(mat, c.metal_host[slot].data(), c.n_model, c.n_model, c.ld_model));
       VG_TRY(gemm_auto(plan, xi, c.ld_model, mat.as<double>(), c.ld_model, dst, c.ld_model, 1, c.n_model,
                        c.ld_model, 1, 0, 0, 0, st));
@@ -1330,6 +1387,83 @@ int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, doubl
 int vg_corr_n_moment(const vg_plan* plan, int32_t corr) {
   if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments) return 0;
   return (int)plan->corrs[corr]->lay[LAY_MOM].mom_ids.size();
+}
+
+// ---- new_metals pair histograms (init time; host pointers in, host pointers out) ----------
+namespace {
+int upload_pair_side(DevBuf& buf, const double* side, int n, vg::PairSide& out) {
+  VG_TRY(upload(buf, side, (size_t)5 * n));
+  const double* d = buf.as<double>();
+  out.r_true = d; out.r_assumed = d + n; out.z_true = d + 2 * (size_t)n; out.z_assumed = d + 3 * (size_t)n;
+  out.weight = d + 4 * (size_t)n; out.n = n;
+  return VG_OK;
+}
+}  // namespace
+
+int vg_metal_pair_ratio_range(const double* side1, int32_t n1, const double* side2, int32_t n2,
+                              double* range_out) {
+  VG_REQUIRE(side1 && side2 && n1 > 0 && n2 > 0 && range_out, "vg_metal_pair_ratio_range: bad arguments");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    vg_set_error("vg_metal_pair_ratio_range: no CUDA device (there is no CPU fallback)");
+    return VG_ERR_CUDA;
+  }
+  DevBuf b1, b2, mm;
+  vg::PairArgs a{};
+  VG_TRY(upload_pair_side(b1, side1, n1, a.s1));
+  VG_TRY(upload_pair_side(b2, side2, n2, a.s2));
+  dim3 grid(vg_cdiv(n2, vg::PAIR_TJ), vg_cdiv(n1, vg::PAIR_TI));
+  const size_t ctas = (size_t)grid.x * grid.y;
+  VG_TRY(mm.alloc(2 * ctas * 8));
+  a.minmax = mm.as<double>();
+  vg::pair_ratio_range_kernel<<<grid, vg::PAIR_TJ>>>(a);
+  VG_LAUNCHED();
+  std::vector<double> host(2 * ctas);
+  VG_CUDA_CHECK(cudaMemcpy(host.data(), mm.p, 2 * ctas * 8, cudaMemcpyDeviceToHost));
+  double lo = 1e300, hi = -1e300;
+  for (size_t c = 0; c < ctas; ++c) { lo = std::min(lo, host[2 * c]); hi = std::max(hi, host[2 * c + 1]); }
+  range_out[0] = lo; range_out[1] = hi;
+  return VG_OK;
+}
+
+int vg_metal_pair_histograms(const double* side1, int32_t n1, const double* side2, int32_t n2,
+                             int32_t signed_rp, double zmin, double zmax, const double* rp_edges, int32_t nb,
+                             const double* ratio_edges, int32_t nr, double* H, double* per_true,
+                             double* per_assumed, double* ratio) {
+  VG_REQUIRE(side1 && side2 && n1 > 0 && n2 > 0 && rp_edges && nb > 0 && H && per_true && per_assumed,
+             "vg_metal_pair_histograms: bad arguments");
+  VG_REQUIRE(nr == 0 || (ratio_edges && ratio), "vg_metal_pair_histograms: ratio histogram without edges");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    vg_set_error("vg_metal_pair_histograms: no CUDA device (there is no CPU fallback)");
+    return VG_ERR_CUDA;
+  }
+  const size_t n_out = (size_t)nb * nb + 4 * (size_t)nb + nr;
+  const size_t smem = n_out * 8;
+  VG_REQUIRE(smem <= 200 * 1024, "vg_metal_pair_histograms: %d rp bins do not fit shared memory", nb);
+  DevBuf b1, b2, be, bq, out;
+  vg::PairArgs a{};
+  VG_TRY(upload_pair_side(b1, side1, n1, a.s1));
+  VG_TRY(upload_pair_side(b2, side2, n2, a.s2));
+  VG_TRY(upload(be, rp_edges, (size_t)nb + 1));
+  if (nr > 0) VG_TRY(upload(bq, ratio_edges, (size_t)nr + 1));
+  VG_TRY(out.alloc(n_out * 8));   // zero filled
+  a.signed_rp = signed_rp; a.zmin = zmin; a.zmax = zmax;
+  a.rp_edges = be.as<double>(); a.nb = nb;
+  a.ratio_edges = nr > 0 ? bq.as<double>() : nullptr; a.nr = nr;
+  a.H = out.as<double>(); a.per_true = a.H + (size_t)nb * nb; a.per_assumed = a.per_true + nb;
+  a.ratio = a.per_assumed + 3 * (size_t)nb;
+  VG_CUDA_CHECK(cudaFuncSetAttribute(vg::pair_histogram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid(vg_cdiv(n2, vg::PAIR_TJ), vg_cdiv(n1, vg::PAIR_TI));
+  vg::pair_histogram_kernel<<<grid, vg::PAIR_TJ, smem>>>(a);
+  VG_LAUNCHED();
+  std::vector<double> host(n_out);
+  VG_CUDA_CHECK(cudaMemcpy(host.data(), out.p, n_out * 8, cudaMemcpyDeviceToHost));
+  std::copy(host.begin(), host.begin() + (size_t)nb * nb, H);
+  std::copy(host.begin() + (size_t)nb * nb, host.begin() + (size_t)nb * nb + nb, per_true);
+  std::copy(host.begin() + (size_t)nb * nb + nb, host.begin() + (size_t)nb * nb + 4 * (size_t)nb, per_assumed);
+  if (nr > 0) std::copy(host.begin() + (size_t)nb * nb + 4 * (size_t)nb, host.end(), ratio);
+  return VG_OK;
 }
 
 int vg_corr_n_static_xi(const vg_plan* plan, int32_t corr) {

@@ -88,6 +88,54 @@ __device__ __forceinline__ double metal_bias_weight(const vg_eval_desc& d, const
   return w;
 }
 
+// rp-only metal matrices (new_metals with rp_only_metal_mats, vega/metals.py:354-358):
+//   met[b][rp][rt] = sum_c sum_rp' A_c[rp][rp'] xmet[b][c][rp'][rt]
+// -- Np^2 numbers per metal correlation instead of (Np Nt)^2, and 2 Np^2 Nt flops per vector
+// instead of 2 (Np Nt)^2.  One CTA per vector: the (Np x Nt) block of each metal xi is staged
+// in shared memory, a thread owns one rt column and every 4th rp row (<= 32 rows), the
+// matrix row entries are warp-uniform loads served by L1.  grid = B, block 256,
+// dynamic shared memory Np*Nt doubles.
+constexpr int MRP_ROWS = 32;   // rp rows per thread (Np <= 128)
+__global__ void __launch_bounds__(256)
+metal_rp_kernel(const double* __restrict__ xmet, int n_metal, int ld, const double* __restrict__ A,
+                int np, int nt, double* __restrict__ met) {
+  extern __shared__ double xs[];                 // [np][nt]
+  const long long b = blockIdx.x;
+  const int tid = threadIdx.x, g = tid >> 6, lane_rt = tid & 63;
+  const int n = np * nt;
+  for (int rt0 = 0; rt0 < nt; rt0 += 64) {
+    const int rt = rt0 + lane_rt;
+    double acc[MRP_ROWS];
+#pragma unroll
+    for (int r = 0; r < MRP_ROWS; ++r) acc[r] = 0.0;
+    for (int c = 0; c < n_metal; ++c) {
+      __syncthreads();
+      const double* x = xmet + (b * n_metal + c) * ld;
+      for (int i = tid; i < n; i += 256) xs[i] = x[i];
+      __syncthreads();
+      if (rt < nt) {
+        const double* Ac = A + (long long)c * np * np;
+        for (int k = 0; k < np; ++k) {
+          const double xv = xs[k * nt + rt];
+#pragma unroll
+          for (int r = 0; r < MRP_ROWS; ++r) {
+            const int rp = g + 4 * r;
+            if (rp < np) acc[r] = fma(__ldg(Ac + (long long)rp * np + k), xv, acc[r]);
+          }
+        }
+      }
+    }
+    if (rt < nt) {
+#pragma unroll
+      for (int r = 0; r < MRP_ROWS; ++r) {
+        const int rp = g + 4 * r;
+        if (rp < np) met[b * ld + rp * nt + rt] = acc[r];
+      }
+    }
+  }
+  for (int i = n + tid; i < ld; i += 256) met[b * ld + i] = 0.0;   // pad columns stay finite
+}
+
 __global__ void combine_pre_kernel(CombineArgs a) {
   long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.B * a.ld) return;

@@ -22,7 +22,7 @@ BLINDING_STRATEGIES = ['desi_dr3']
 
 
 class Data:
-    def __init__(self, corr_item, marginalize_in_fit=False):
+    def __init__(self, corr_item, marginalize_in_fit=False, metal_builder=None):
         self.corr_item = corr_item
         self.tracer1 = corr_item.tracer1
         self.tracer2 = corr_item.tracer2
@@ -54,12 +54,22 @@ class Data:
             self.model_coordinates, self.dist_model_coordinates, self.data_coordinates)
 
         if 'metals' in cfg:
-            tracer_catalog, metal_correlations = self._init_metals(cfg['metals'])
+            if corr_item.new_metals:      # no metal file: vega/data.py:60-66
+                tracer_catalog, metal_correlations = self._metal_tracers_and_pairs(cfg['metals'])
+            else:
+                tracer_catalog, metal_correlations = self._init_metals(cfg['metals'])
             corr_item.init_metals(tracer_catalog, metal_correlations)
         if 'broadband' in cfg:
             corr_item.init_broadband(self.coeff_binning_model)
         if self.cosmo_params is not None:
             corr_item.init_cosmo(self.cosmo_params)
+        if 'metals' in cfg and corr_item.new_metals:
+            # metal matrices and coordinates from the stacked weights (the reference does this in
+            # Metals.__init__, vega/metals.py:94-108).  `metal_builder` is a hook for callers that
+            # bring their own matrices; the package's builder runs the pair histograms on the device
+            if metal_builder is None:
+                from .metal_matrices import build_new_metals as metal_builder
+            metal_builder(corr_item, self)
 
         # Identity stand-ins (vega/data.py:77-80): kept implicit
         self.distortion_is_identity = self._distortion_mat is None
@@ -338,7 +348,27 @@ class Data:
         if hdul[1].header.get('BLINDING', 'none') != 'none':
             prefix = 'DM_BLIND_'
         file_columns = hdul[2].columns.names
+        pairs = self._metal_pairs(in1, in2)
+        for tracers in pairs:
+            name = tracers[0] + '_' + tracers[1]
+            if 'RP_' + name not in file_columns:
+                name = tracers[1] + '_' + tracers[0]
+            self._read_metal_correlation(hdul, tracers, name, prefix)
+        return catalog, pairs
 
+    def _metal_tracers_and_pairs(self, metal_config):
+        """Tracer catalogue and metal-correlation list without a metal file
+        (vega/data.py:475-554, the new_metals branch)."""
+        assert ('in tracer1' in metal_config) or ('in tracer2' in metal_config), (
+            "The metals config must specify 'in tracer1' and/or 'in tracer2'")
+        in1 = metal_config.get('in tracer1').split() if 'in tracer1' in metal_config else None
+        in2 = metal_config.get('in tracer2').split() if 'in tracer2' in metal_config else None
+        catalog = {self.tracer1['name']: self.tracer1, self.tracer2['name']: self.tracer2}
+        for metal in (in1 or []) + (in2 or []):
+            catalog[metal] = {'name': metal, 'type': 'continuous'}
+        return catalog, self._metal_pairs(in1, in2)
+
+    def _metal_pairs(self, in1, in2):
         t1, t2 = self.tracer1['name'], self.tracer2['name']
         pairs = []
         if in2 is not None:
@@ -350,13 +380,7 @@ class Data:
                 start = i if self.tracer1 == self.tracer2 else 0
                 pairs += [(metal1, metal2) for metal2 in in2[start:]
                           if self._use_correlation(metal1, metal2)]
-
-        for tracers in pairs:
-            name = tracers[0] + '_' + tracers[1]
-            if 'RP_' + name not in file_columns:
-                name = tracers[1] + '_' + tracers[0]
-            self._read_metal_correlation(hdul, tracers, name, prefix)
-        return catalog, pairs
+        return pairs
 
     def _read_metal_correlation(self, hdul, tracers, name, prefix):
         header = hdul[1].header

@@ -741,8 +741,15 @@ class PlanBuilder:
                     tab = hankel.build_static_table(k, pk_sel[sel], ell, n_pow)
                     _lib.check(lib.vg_corr_set_static_xi(handle, ci, which, sel, tab.shape[1], _dptr(tab)))
             if any(m is not None for m in info['metal_mats']):
+                rp_form = all(m is None or hasattr(m, 'rp_mat') for m in info['metal_mats'])
                 for slot, mat in enumerate(info['metal_mats']):
-                    if mat is not None:
+                    if mat is not None and rp_form:     # rp-only new_metals matrices stay rp-only
+                        rp_mat = _f64(mat.rp_mat)
+                        _lib.check(lib.vg_corr_set_metal_matrix_rp(
+                            handle, ci, slot, _dptr(rp_mat), rp_mat.shape[0], mat.rt_nbins))
+                    elif mat is not None:
+                        if hasattr(mat, 'rp_mat'):      # mixed with dense ones: A (x) 1_rt
+                            mat = np.kron(mat.rp_mat, np.eye(mat.rt_nbins))
                         mat = _f64(mat)
                         assert mat.shape == (n_model, n_model), 'metal matrix shape'
                         _lib.check(lib.vg_corr_set_metal_matrix(handle, ci, slot, _dptr(mat)))

@@ -37,7 +37,7 @@ class VegaInterface:
     _use_global_cov = False
     global_cov = None
 
-    def __init__(self, main_path, device=None, batch_chunk=None):
+    def __init__(self, main_path, device=None, batch_chunk=None, metal_builder=None):
         main_path = utils.find_file(main_path)
         utils.add_search_dir(Path(main_path).resolve().parent)
         self.main_config = _read_ini(main_path)
@@ -81,7 +81,7 @@ class VegaInterface:
                 self.fiducial[key] = self.params[key]
 
         self._has_data = all(item.has_data for item in self.corr_items.values())
-        self.data = {name: (Data(item, self.marginalize_in_fit) if self._has_data else None)
+        self.data = {name: (Data(item, self.marginalize_in_fit, metal_builder) if self._has_data else None)
                      for name, item in self.corr_items.items()}
 
         self._blind = False
