@@ -94,6 +94,58 @@ def test_world_size_2_gather_matches_single_process():
     assert out[0]['evaluated'] == 4 and out[1]['evaluated'] == 3
 
 
+class _StubFitter:
+    """Closed-form stand-in for drivers.MonteCarloFits.fit: mock m has best fit (m, 2m)."""
+    names = ['a', 'b']
+
+    def __init__(self):
+        self.calls = []
+
+    def result_shape(self, key):
+        return (2,) if key in ('theta', 'errors') else ()
+
+    def fit(self, mock_slice=None, **kw):
+        ids = np.arange(1000)[mock_slice]
+        self.calls.append((ids[0], ids[-1] + 1))
+        theta = np.stack([ids * 1.0, ids * 2.0], axis=1)
+        return {'theta': theta, 'fval': ids + 0.5, 'errors': theta * 0.1,
+                'converged': (ids % 3 != 0)}
+
+
+def _mc_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from vega_b200.sharding import fit_mocks_sharded, gather_rows
+        results = {}
+        for n in (1, 2, 7):          # n = 1: rank 1 holds an empty shard
+            fitter = _StubFitter()
+            results[n] = (fit_mocks_sharded(fitter, n, 'cpu'), fitter.calls)
+        lo, hi = shard_bounds(5, world, rank)
+        results['rows'] = gather_rows(np.arange(5.)[lo:hi, None] * np.ones((1, 3)), 5, 'cpu')
+        out[rank] = results
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_mock_fits_are_sharded_and_gathered():
+    """C5 host logic: contiguous shards of the mocks, one padded gather per result array."""
+    world = 2
+    manager = mp.Manager()
+    out = manager.dict()
+    mp.spawn(_mc_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    for n in (1, 2, 7):
+        ids = np.arange(n)
+        for rank in range(world):
+            res, calls = out[rank][n]
+            assert np.array_equal(res['theta'], np.stack([ids * 1.0, ids * 2.0], axis=1))
+            assert np.array_equal(res['fval'], ids + 0.5)
+            assert np.array_equal(res['converged'], ids % 3 != 0)
+            lo, hi = shard_bounds(n, world, rank)
+            assert calls == ([(lo, hi)] if hi > lo else [])
+    assert np.array_equal(out[0]['rows'], np.arange(5.)[:, None] * np.ones((1, 3)))
+
+
 def test_sharded_engine_needs_cuda():
     """No CPU evaluator in the product: building the engine-backed shard evaluator without a
     device fails loudly."""

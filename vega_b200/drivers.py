@@ -416,6 +416,18 @@ class MonteCarloFits:
         chi2[status.cpu().numpy() != 0] = 1e100
         return chi2
 
+    def result_shape(self, key):
+        """Trailing shape of one row of fit()[key] (what an empty shard contributes to the
+        gather of sharding.fit_mocks_sharded)."""
+        return (len(self.names),) if key in ('theta', 'errors') else ()
+
+    def fit_sharded(self, **fit_kwargs):
+        """fit() of this rank's contiguous share of the mocks, best fits gathered on every rank
+        (one process per GPU; the C5 workload)."""
+        from .sharding import fit_mocks_sharded
+        n_mocks = next(iter(self.mocks.values())).shape[0]
+        return fit_mocks_sharded(self, n_mocks, self.engine.device, **fit_kwargs)
+
     def fit(self, mock_slice=None, params=None, max_iter=50, edm_tol=1e-5, verbose=False):
         """Best fit of every mock in mock_slice (default: all).  Returns the dict of
         newton_lockstep plus 'names' and 'errors'[M, P]."""

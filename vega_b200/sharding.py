@@ -133,3 +133,50 @@ class ShardedChi2:
             buf.copy_(theta)
         dist.broadcast(buf, src, group=self.group)
         return buf
+
+
+def gather_rows(local, n_total, device, group=None):
+    """All-gather of per-item result rows: rank r holds the rows of its contiguous shard
+    (shard_bounds(n_total, world, r)) as a float64 array [n_r, ...]; every rank gets the
+    [n_total, ...] array in item order.  One padded fixed-size collective."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    local = np.ascontiguousarray(local, dtype=np.float64)
+    if world == 1:
+        return local
+    sizes = shard_sizes(n_total, world)
+    tail = local.shape[1:]
+    width = int(np.prod(tail)) if tail else 1
+    cap = max(sizes)
+    send = torch.zeros(cap * width, dtype=torch.float64, device=device)
+    if local.size:
+        send[:local.size] = torch.from_numpy(local.reshape(-1)).to(device)
+    recv = torch.empty(world * cap * width, dtype=torch.float64, device=device)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    recv = recv.cpu().numpy().reshape(world, cap, width)
+    out = np.concatenate([recv[r, :sizes[r]] for r in range(world)], axis=0)
+    return out.reshape((n_total,) + tail)
+
+
+def fit_mocks_sharded(fitter, n_mocks, device, keys=('theta', 'fval', 'errors', 'converged'), group=None,
+                      **fit_kwargs):
+    """Monte Carlo mock fits sharded over the ranks (bin/run_vega_mc_fits_mpi.py:104-113 gives
+    rank r the mocks range(r, n, size) and writes one file per rank; here the shards are
+    contiguous and the best fits are all-gathered).  `fitter.fit(mock_slice=slice(lo, hi), ...)`
+    returns a dict of arrays with one row per mock of the slice (drivers.MonteCarloFits.fit)."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    lo, hi = shard_bounds(n_mocks, world, rank)
+    res = fitter.fit(mock_slice=slice(lo, hi), **fit_kwargs) if hi > lo else None
+    out = {}
+    for key in keys:
+        if res is not None:
+            local = np.asarray(res[key], dtype=np.float64)
+        else:          # an empty shard still takes part in the collective
+            local = np.zeros((0,) + tuple(fitter.result_shape(key)), dtype=np.float64)
+        out[key] = gather_rows(local, n_mocks, device, group)
+    if 'converged' in out:
+        out['converged'] = out['converged'] > 0.5
+    return out
