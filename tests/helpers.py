@@ -137,7 +137,8 @@ def write_new_metals_inputs(tmp_dir, n_pix=520, n_qso=4000, seed=7):
     tmp_dir = Path(tmp_dir)
     tmp_dir.mkdir(parents=True, exist_ok=True)
     rng = np.random.default_rng(seed)
-    loglam = np.log10(3600.) + 3e-4 * np.arange(n_pix)          # 3600 .. ~5160 A
+    step = 3e-4 if n_pix == 520 else 0.156 / n_pix             # 3600 .. ~5160 A whatever the sampling
+    loglam = np.log10(3600.) + step * np.arange(n_pix)
     weight = (1 + 0.3 * np.sin(np.linspace(0, 7, n_pix))) * np.exp(-0.5 * ((loglam - 3.63) / 0.05)**2) \
         * (1 + 0.05 * rng.standard_normal(n_pix))
     forest = tmp_dir / 'forest_weights.fits'
