@@ -172,8 +172,11 @@ int vg_plan_add_hankel(vg_plan* plan, int32_t n_ell, const int32_t* ells, int32_
 
 int vg_plan_add_corr(vg_plan* plan, int32_t hankel_id, int32_t n_model, int32_t n_dist,
                      int32_t* corr_id);
-/* Coordinate table of n_model bins: tab[5][n_model] = r, mu, log((1+z)/(1+z_eff)),
- * (1+z)^2, growth factor ratio squared (vega/correlation_func.py:46-48,76-80,372-403). */
+/* Coordinate table of n_model bins: tab[6][n_model] = r, mu, log((1+z_1)/(1+z_eff)),
+ * (1+z)^2, growth factor ratio squared, log((1+z_2)/(1+z_eff))
+ * (vega/correlation_func.py:46-48,76-80,372-403).  z_1 = z_2 = z of the bin unless
+ * new-bias-evolution gives the two tracers of a cross-correlation their own redshifts
+ * (vega/correlation_func.py:238-274). */
 int vg_corr_add_coords(vg_plan* plan, int32_t corr, const double* tab, double opz_eff2,
                        int32_t* coord_set);
 int vg_corr_add_eval(vg_plan* plan, int32_t corr, const vg_eval_desc* desc, int32_t* eval_id);

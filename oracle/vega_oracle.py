@@ -422,7 +422,7 @@ class XiModel:
     """One CorrelationFunction instance (vega/correlation_func.py:20-161)."""
 
     def __init__(self, cfg, fiducial, coords, scale_cfg, tracer1, tracer2, metal_corr=False,
-                 growth_fn=None, inst_table=None):
+                 growth_fn=None, inst_table=None, cosmo=None):
         self.cfg, self.scale_cfg = cfg, scale_cfg
         self.r, self.mu, self.z = coords.r_grid, coords.mu_grid, coords.z_grid
         self.t1, self.t2 = tracer1, tracer2
@@ -433,6 +433,16 @@ class XiModel:
         self.rescale_sys = cfg.getboolean('rescale-coords-systematics', False)
         self.rel_z = (1. + self.z) / (1 + self.z_eff)
         self.inst_table = inst_table
+        # vega/correlation_func.py:58,238-274: separate redshifts of the two tracers of a cross
+        self.rel_z_tracers = None
+        if cfg.getboolean('new-bias-evolution', False) and tracer1['type'] != tracer2['type']:
+            if cosmo is None:
+                print('Warning: No cosmology found in xcf files, using mean redshift evolution.')
+            else:
+                half = self.r * self.mu / (2 * cosmo.get_dist_hubble(self.z))
+                rel = {'discrete': (1. + self.z - half) / (1 + self.z_eff),
+                       'continuous': (1. + self.z + half) / (1 + self.z_eff)}
+                self.rel_z_tracers = (rel[tracer1['type']], rel[tracer2['type']])
 
         self.drp_name = None
         if tracer1['type'] == 'discrete' and tracer2['type'] != 'discrete':
@@ -461,16 +471,18 @@ class XiModel:
     def bias_evolution(self, pars):
         """vega/correlation_func.py:276-370."""
         out = 1.
-        for tr in (self.t1, self.t2):
+        for t, tr in enumerate((self.t1, self.t2)):
+            rel_z = self.rel_z if self.rel_z_tracers is None else self.rel_z_tracers[t]
             key = 'z evol {}'.format(tr['name'])
             kind = self.cfg.get(key, 'standard') if key in self.cfg \
                 else self.cfg.get('z evol', 'standard')
             if 'croom' in kind:
                 assert tr['name'] == 'QSO'
+                assert self.rel_z_tracers is None, 'Croom model is not supported with new bias evol'
                 p0, p1 = pars['croom_par0'], pars['croom_par1']
                 out = out * (p0 + p1 * (1. + self.z)**2) / (p0 + p1 * (1 + self.z_eff)**2)
             else:
-                out = out * self.rel_z**pars['alpha_{}'.format(tr['name'])]
+                out = out * rel_z**pars['alpha_{}'.format(tr['name'])]
         return out
 
     def compute(self, pk, pk_lin, transform, pars):
@@ -638,7 +650,8 @@ class CorrelationModel:
         self.transform = Transform(self.grid, mcfg)
         self.xi_core = XiModel(mcfg, fiducial, corr_item.model_coordinates, scale_cfg,
                                corr_item.tracer1, corr_item.tracer2, growth_fn=growth_squared,
-                               inst_table=tables.get('desi_inst'))
+                               inst_table=tables.get('desi_inst'),
+                               cosmo=getattr(corr_item, 'cosmo', None))
         self.bb = parse_broadband(cfg['broadband'], corr_item.name) \
             if 'broadband' in cfg else None
         self.inst_flag = mcfg.getboolean('desi-instrumental-systematics', False)
@@ -663,7 +676,7 @@ class CorrelationModel:
                 g = PkGrid(metcfg, fiducial, tr1, tr2, corr_item.name, fv)
                 self.metal[pair] = (g, Transform(g, mcfg), XiModel(
                     metcfg, fiducial, coords, scale_cfg, tr1, tr2, metal_corr=True,
-                    growth_fn=growth_squared), mat)
+                    growth_fn=growth_squared, cosmo=getattr(corr_item, 'cosmo', None)), mat)
 
     # -- metals: vega/metals.py:209-367 ------------------------------------------------
     def _metal_xi(self, pars, pk_lin, pair, fast, apply_matrix=True):

@@ -117,13 +117,18 @@ def main():
     base = str(REPO / 'tests' / 'configs' / 'full_configs' / 'main.ini')
     CONFIGS['new_metals_rp'] = make_new_metals_config('/tmp/vega_golden_nm_rp', True, base=base)
     CONFIGS['new_metals_2d'] = make_new_metals_config('/tmp/vega_golden_nm_2d', False, base=base)
+    # new-bias-evolution (vega/correlation_func.py:58,238-274) on the same configuration
+    CONFIGS['new_bias_evol'] = make_new_metals_config('/tmp/vega_golden_nbe', True, base=base,
+                                                      new_bias_evolution=True)
     PERTURBED['new_metals_rp'] = PERTURBED['new_metals_2d'] = PERTURBED['full'][:2]
+    PERTURBED['new_bias_evol'] = [PERTURBED['full'][0], PERTURBED['full'][2]]
     # Model.compute_direct through the direct_pk argument (vega/model.py:189-208)
     CONFIGS['full_direct'] = CONFIGS['full']
     PERTURBED['full_direct'] = PERTURBED['full']
     notes = {'new_metals_rp': 'helpers.make_new_metals_config(rp_only=True): full_configs auto + cross, '
                               'new_metals = True, rp_only_metal_mats = True, seeded weight tables',
              'new_metals_2d': 'same with rp_only_metal_mats = False',
+             'new_bias_evol': 'new_metals_rp + new-bias-evolution = True in [model] and [metals]',
              'full_direct': CONFIGS['full'] + ' with direct_pk = pk_full (1 + 0.05 sin(3 ln k))',
              'full_fast': CONFIGS['full'] + ' + fast_metals = True',
              'c1_marg': f"{CONFIGS['c1']} + [model] {MARG_CUTS} + distortion-file (55x55 bins)",
@@ -159,7 +164,7 @@ def main():
                 for name, xi in model.items():
                     out[f'{key}/{i}/xi_marg/{name}'] = np.asarray(xi, dtype=float)
             print(key, i, float(out[f'{key}/{i}/chi2']), float(out[f'{key}/{i}/log_lik']))
-        if key.startswith('new_metals'):
+        if key.startswith('new_metals') or key == 'new_bias_evol':
             # the matrices themselves: rp-only in full, the 2-D ones through three probe vectors
             # (a (Np Nt)^2 matrix is 50 MB), and the effective coordinate grids
             meta[key]['pairs'] = {}
@@ -171,7 +176,7 @@ def main():
                     mat = metals.rp_metal_dmats[pair]
                     xi_c = metals.Xi_metal[pair]
                     out[f'{key}/coords/{name}/{c}'] = np.stack([xi_c._r, xi_c._mu, xi_c._z])
-                    if key.endswith('_rp'):
+                    if not key.endswith('_2d'):
                         out[f'{key}/mat/{name}/{c}'] = np.asarray(mat, dtype=float)
                     else:
                         n = mat.shape[1]

@@ -166,7 +166,7 @@ def copy_data_with_cosmology(src, dst, omega_m=0.315):
 
 
 def make_new_metals_config(tmp_dir, rp_only, base='configs/full_configs/main.ini',
-                           corrs=('lyalya_lyalya', 'lyalya_qso'), rebin=2):
+                           corrs=('lyalya_lyalya', 'lyalya_qso'), rebin=2, new_bias_evolution=False):
     """The reference's own auto + cross configuration switched to new_metals: no metal file,
     matrices from the weight tables.  Returns the main ini path."""
     import configparser
@@ -187,6 +187,9 @@ def make_new_metals_config(tmp_dir, rp_only, base='configs/full_configs/main.ini
         cfg = read(path)
         cfg['model']['new_metals'] = 'True'
         cfg['model']['rp_only_metal_mats'] = str(bool(rp_only))
+        if new_bias_evolution:       # vega/correlation_func.py:58,238-274 (needs the cosmology header)
+            cfg['model']['new-bias-evolution'] = 'True'
+            cfg['metals']['new-bias-evolution'] = 'True'
         data_file = tmp_dir / (Path(path).stem + '_data.fits')
         cfg['data']['filename'] = copy_data_with_cosmology(cfg['data']['filename'], data_file)
         cfg['data']['weights-tracer1'] = forest

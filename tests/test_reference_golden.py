@@ -107,7 +107,7 @@ def check_new_metals_matrices(key, vega, gold, meta, rtol):
             ref = gold[f'{key}/coords/{name}/{c}']
             got = np.stack([coords.r_grid, coords.mu_grid, coords.z_grid])
             assert np.max(np.abs(got - ref)) <= rtol * np.max(np.abs(ref)), (name, pair)
-            if key.endswith('_rp'):
+            if not key.endswith('_2d'):
                 ref = gold[f'{key}/mat/{name}/{c}']
                 assert np.max(np.abs(mat.rp_mat - ref)) <= rtol * np.max(np.abs(ref)), (name, pair)
             else:
@@ -117,30 +117,35 @@ def check_new_metals_matrices(key, vega, gold, meta, rtol):
                 assert np.max(np.abs(mat @ probes - ref)) <= rtol * np.max(np.abs(ref)), (name, pair)
 
 
-@pytest.mark.parametrize('key', ['new_metals_rp', 'new_metals_2d'])
+def new_metals_config(key, tmp_path):
+    from helpers import make_new_metals_config
+    return make_new_metals_config(tmp_path, not key.endswith('_2d'),
+                                  new_bias_evolution=key == 'new_bias_evol')
+
+
+@pytest.mark.parametrize('key', ['new_metals_rp', 'new_metals_2d', 'new_bias_evol'])
 def test_oracle_matches_reference_new_metals(key, tmp_path):
     """oracle/metal_matrices.py against the unmodified reference's compute_metal_rp_dmat /
-    compute_metal_dmat, and the model built on those matrices."""
-    from helpers import make_new_metals_config, oracle_metal_builder, static_tables
+    compute_metal_dmat, and the model built on those matrices; 'new_bias_evol' adds
+    new-bias-evolution (vega/correlation_func.py:58,238-274) in [model] and [metals]."""
+    from helpers import oracle_metal_builder, static_tables
     from oracle.vega_oracle import Oracle
     from vega_b200 import VegaInterface
     gold, meta = load()
-    vega = VegaInterface(make_new_metals_config(tmp_path, key.endswith('_rp')),
-                         metal_builder=oracle_metal_builder)
+    vega = VegaInterface(new_metals_config(key, tmp_path), metal_builder=oracle_metal_builder)
     check_new_metals_matrices(key, vega, gold, meta, 1e-12)
     oracle = Oracle(vega, tables=static_tables())
     check(key, oracle.compute_model, oracle.chi2, oracle.log_lik, gold, meta)
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('key', ['new_metals_rp', 'new_metals_2d'])
+@pytest.mark.parametrize('key', ['new_metals_rp', 'new_metals_2d', 'new_bias_evol'])
 def test_cuda_path_matches_reference_new_metals(key, tmp_path):
     """Product path: pair histograms on the device (vg_metal_pair_histograms), the matrices
     applied by the hot path."""
-    from helpers import make_new_metals_config
     from vega_b200 import VegaInterface
     gold, meta = load()
-    vega = VegaInterface(make_new_metals_config(tmp_path, key.endswith('_rp')))
+    vega = VegaInterface(new_metals_config(key, tmp_path))
     check_new_metals_matrices(key, vega, gold, meta, 1e-11)
     check(key, vega.compute_model, vega.chi2, vega.log_lik, gold, meta)
 

@@ -543,7 +543,7 @@ int vg_corr_add_coords(vg_plan* plan, int32_t corr, const double* tab, double op
                        int32_t* coord_set) {
   VG_CORR(plan, corr);
   DevBuf buf;
-  VG_TRY(upload(buf, tab, (size_t)5 * c.n_model));
+  VG_TRY(upload(buf, tab, (size_t)6 * c.n_model));
   *coord_set = (int)c.coords.size();
   c.coords.push_back(std::move(buf));
   c.opz_eff2.push_back(opz_eff2);

@@ -48,7 +48,7 @@ struct XiArgs {
   const int* metal_map;    // metal slot (out_slot - 2) -> column block of xmet
   int unit_bias;           // 1: leave b1*b2 / extra bias out of the weight (finalize pass of the
                            //    frozen fast_metals terms)
-  const double* const* coords;   // coordinate tables, each [5][n_model]
+  const double* const* coords;   // coordinate tables, each [6][n_model]
   const double* opz_eff2;  // per coordinate table: (1+z_eff)^2
   int n_model;
   StaticXiDev sx;
@@ -187,9 +187,11 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
   const double* ct = a.coords[d.coord_set];
   const double opz_eff2 = a.opz_eff2[d.coord_set];
   const int n = a.n_model;
-  double zexp = 0.0;
-  if (d.zevol_kind[0] == 0) zexp += p[d.idx_alpha[0]];
-  if (d.zevol_kind[1] == 0) zexp += p[d.idx_alpha[1]];
+  // (1+z)^alpha evolution per tracer; rows 2 and 5 of the coordinate table hold
+  // log((1+z_t)/(1+z_eff)) of tracer 1 and 2 (equal unless new-bias-evolution separates the
+  // redshifts of the two tracers of a cross-correlation, vega/correlation_func.py:238-299)
+  const double zexp0 = d.zevol_kind[0] == 0 ? p[d.idx_alpha[0]] : 0.0;
+  const double zexp1 = d.zevol_kind[1] == 0 ? p[d.idx_alpha[1]] : 0.0;
   const bool croom = d.zevol_kind[0] == 1 || d.zevol_kind[1] == 1;
   const int n_croom = (d.zevol_kind[0] == 1) + (d.zevol_kind[1] == 1);
   double weight = d.weight_const;
@@ -237,7 +239,7 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
       }
     }
     // redshift evolution of the biases (:276-370) and growth (:372-403)
-    double evol = exp(zexp * ct[2 * n + i]);
+    double evol = exp(fma(zexp0, ct[2 * n + i], zexp1 * ct[5 * n + i]));
     if (croom) {
       const double p0 = p[d.idx_croom[0]], p1 = p[d.idx_croom[1]];
       const double c = (p0 + p1 * ct[3 * n + i]) / (p0 + p1 * opz_eff2);

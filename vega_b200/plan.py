@@ -329,8 +329,6 @@ class PlanBuilder:
             d.idx_scale[0], d.idx_scale[1] = c(a, True), c(b, True)
         d.single_ell = cfg.getint('single_multipole', -1)
         d.rescale_sys = int(cfg.getboolean('rescale-coords-systematics', False))
-        if cfg.getboolean('new-bias-evolution', False):
-            raise NotImplementedError('new-bias-evolution needs a picca cosmology (not built).')
 
         types = (tracer1['type'], tracer2['type'])
         drp_name = None
@@ -391,8 +389,9 @@ class PlanBuilder:
         sampled = any(name_map.get(n, n) in self.sampled_set for n in xi_names)
         d.static_xi = int(not sampled and not (d.radiation or d.rel or d.asy or d.uv_shot))
 
-    def coord_table(self, coords, cfg):
-        """[5][n] static per-bin table + (1+z_eff)^2 (vega/correlation_func.py:46-48,372-444)."""
+    def coord_table(self, coords, cfg, tracer1=None, tracer2=None, cosmo=None):
+        """[6][n] static per-bin table + (1+z_eff)^2 (vega/correlation_func.py:46-48,238-274,
+        372-444)."""
         fid = self.vega.fiducial
         n = coords.r_grid.size
         z = np.broadcast_to(np.asarray(coords.z_grid, dtype=float), (n,)).copy()
@@ -404,8 +403,21 @@ class PlanBuilder:
             growth = (utils.growth_function_old(z, om, ode) / utils.growth_function_old(z_fid, om, ode))**2
         else:
             growth = (utils.growth_function(z, om, ode) / utils.growth_function(z_fid, om, ode))**2
-        tab = np.stack([coords.r_grid, coords.mu_grid, np.log((1. + z) / (1 + z_eff)),
-                        (1. + z)**2, growth])
+        rel1 = rel2 = (1. + z) / (1 + z_eff)
+        types = (tracer1['type'], tracer2['type']) if tracer1 is not None else ('', '')
+        if cfg.getboolean('new-bias-evolution', False) and types[0] != types[1]:
+            if cosmo is None:
+                print('Warning: No cosmology found in xcf files, using mean redshift evolution.')
+            else:       # separate redshifts of the two tracers: rp ~ (z_F - z_Q) D_H(z)
+                for t in (tracer1, tracer2):
+                    key = 'z evol {}'.format(t['name'])
+                    kind = cfg.get(key, 'standard') if key in cfg else cfg.get('z evol', 'standard')
+                    assert 'croom' not in kind, 'Croom model is not supported with new bias evol'
+                half = coords.r_grid * coords.mu_grid / (2 * cosmo.get_dist_hubble(z))
+                rel_q, rel_f = (1. + z - half) / (1 + z_eff), (1. + z + half) / (1 + z_eff)
+                rel1 = rel_q if types[0] == 'discrete' else rel_f
+                rel2 = rel_q if types[1] == 'discrete' else rel_f
+        tab = np.stack([coords.r_grid, coords.mu_grid, np.log(rel1), (1. + z)**2, growth, np.log(rel2)])
         return _f64(tab), (1 + z_eff)**2
 
     # -- broadband --------------------------------------------------------------------------
@@ -484,7 +496,8 @@ class PlanBuilder:
         info['lowring'] = mcfg.getboolean('fht_lowring', True)
         pair_name = f"{item.tracer1['name']}x{item.tracer2['name']}"
 
-        info['coords'].append(self.coord_table(item.model_coordinates, mcfg))
+        cosmo = getattr(item, 'cosmo', None)
+        info['coords'].append(self.coord_table(item.model_coordinates, mcfg, item.tracer1, item.tracer2, cosmo))
         for comp, (is_peak, sel, slot) in {'peak': (True, 0, 0), 'smooth': (False, 1, 1)}.items():
             d = EvalDesc()
             self.fill_pk(d, mcfg, item.tracer1, item.tracer2, item.name, is_peak, sel, False,
@@ -551,7 +564,7 @@ class PlanBuilder:
                     self.fill_xi(d, metcfg, o_tr1, o_tr2, False, o_pair, True, name_map=o_map)
                     d.coord_set, d.table_owner = o_coords, o_eval
                 else:
-                    info['coords'].append(self.coord_table(coords, metcfg))
+                    info['coords'].append(self.coord_table(coords, metcfg, tr1, tr2, cosmo))
                     self.fill_xi(d, metcfg, tr1, tr2, False, f'{n1}x{n2}', True, name_map=name_map)
                     d.coord_set = len(info['coords']) - 1
                 d.out_slot = 2 + c
