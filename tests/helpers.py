@@ -59,14 +59,14 @@ MARG_CUTS = {'marginalize-below-rtmax': 16., 'marginalize-below-rpmax': 16.}
 MARG_FIT = {'marginalize-all-rmin-cuts': True, 'marginalize-prior-sigma': 5.0}
 
 
-def write_dmat_file(path, n_p=55, n_t=55, size=4.0):
+def write_dmat_file(path, n_p=55, n_t=55, size=4.0, rp_min=0.):
     """Distortion-matrix file with its own, larger grid (vega/data.py:441-473)."""
     from vega_b200 import fitsio, synthetic
-    rp = (np.arange(n_p) + 0.5) * size
+    rp = rp_min + (np.arange(n_p) + 0.5) * size
     rt = (np.arange(n_t) + 0.5) * size
     rp_grid, rt_grid = [g.ravel() for g in np.meshgrid(rp, rt, indexing='ij')]
     fitsio.write_tables(path, [
-        ('DMAT', {'RPMIN': 0., 'RPMAX': n_p * size, 'RTMAX': n_t * size, 'NP': n_p, 'NT': n_t,
+        ('DMAT', {'RPMIN': rp_min, 'RPMAX': rp_min + n_p * size, 'RTMAX': n_t * size, 'NP': n_p, 'NT': n_t,
                   'COEFMOD': 1}, {'DM': synthetic.distortion_matrix(n_p, n_t)}),
         ('ATTRI', {}, {'RP': rp_grid, 'RT': rt_grid, 'Z': np.full(rp_grid.size, 2.33)})])
     return str(path)
@@ -127,7 +127,7 @@ def make_marg_case(tmp_path, key):
 # ---------------------------------------------------------------------------------------------
 # new_metals (vega/metals.py:83-108, 370-752): configurations with stacked-weight tables
 # ---------------------------------------------------------------------------------------------
-NEW_METALS_ALPHA = {'LYA': 2.9, 'SiII(1190)': 1.0, 'SiII(1193)': 1.0, 'SiIII(1207)': 1.0,
+NEW_METALS_ALPHA = {'LYA': 2.9, 'LYB': 2.9, 'SiII(1190)': 1.0, 'SiII(1193)': 1.0, 'SiIII(1207)': 1.0,
                     'SiII(1260)': 1.0, 'CIV(eff)': 1.0}
 
 
@@ -166,7 +166,8 @@ def copy_data_with_cosmology(src, dst, omega_m=0.315):
 
 
 def make_new_metals_config(tmp_dir, rp_only, base='configs/full_configs/main.ini',
-                           corrs=('lyalya_lyalya', 'lyalya_qso'), rebin=2, new_bias_evolution=False):
+                           corrs=('lyalya_lyalya', 'lyalya_qso'), rebin=2, new_bias_evolution=False,
+                           model=None, dmat_bins=None):
     """The reference's own auto + cross configuration switched to new_metals: no metal file,
     matrices from the weight tables.  Returns the main ini path."""
     import configparser
@@ -195,6 +196,18 @@ def make_new_metals_config(tmp_dir, rp_only, base='configs/full_configs/main.ini
         cfg['data']['weights-tracer1'] = forest
         if cfg['data'].get('tracer2-type', 'continuous') == 'discrete':
             cfg['data']['weights-tracer2'] = catalogue
+        if cfg['data'].get('tracer1-type', 'continuous') == 'discrete':
+            cfg['data']['weights-tracer1'] = catalogue
+            cfg['data']['weights-tracer2'] = forest
+        for k, v in (model or {}).items():
+            cfg['model'][k] = str(v)
+        if dmat_bins is not None:    # distortion-matrix file with its own, larger model grid
+            cross = cfg['data'].get('tracer2-type', 'continuous') == 'discrete'
+            n_rp = 2 * dmat_bins if cross else dmat_bins
+            dm_path = tmp_dir / f'dmat_{n_rp}x{dmat_bins}.fits'
+            if not dm_path.exists():
+                write_dmat_file(dm_path, n_rp, dmat_bins, 4.0, -4.0 * dmat_bins if cross else 0.)
+            cfg['data']['distortion-file'] = str(dm_path)
         cfg['metals'].pop('filename', None)
         cfg['metal-matrix'] = {'rebin_factor': str(rebin), 'z_bins_objects': '300'}
         for name, alpha in NEW_METALS_ALPHA.items():
@@ -224,3 +237,13 @@ def oracle_metal_builder(corr_item, data):
         mat, rp, rt, z = oracle.rp_matrix(*pair) if rp_only else oracle.full_matrix(*pair)
         data.metal_mats[pair] = RpOnlyMatrix(mat, corr_item.model_coordinates.rt_nbins) if rp_only else mat
         data.metal_coordinates[pair] = Coordinates.init_from_grids(corr_item.model_coordinates, rp, rt, z)
+
+
+def make_c3_config(tmp_dir, dmat_bins=75):
+    """C3: the DESI-DR2-shaped workload -- the reference's four correlations
+    (lyaxlya, lyaxlyb, lyaxqso, lybxqso), data on 2500/5000 bins, distorted AND undistorted model
+    on the distortion matrix's own grid (75 x 75 = 5625 / 150 x 75 = 11250 bins out to 300 Mpc/h),
+    new_metals rp-only matrices on that grid, fast_metals, post-distortion broadband."""
+    return make_new_metals_config(
+        tmp_dir, True, corrs=('lyalya_lyalya', 'lyalya_lyalyb', 'lyalya_qso', 'lyalyb_qso'),
+        model={'fast_metals': True}, dmat_bins=dmat_bins)

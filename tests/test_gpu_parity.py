@@ -274,3 +274,37 @@ def test_desi_shaped_model_grid_larger_than_the_data_grid(tmp_path):
         assert_xi_close({n: models[n][b] for n in ref}, ref, f'vector {b}')
         ref_chi2 = oracle.chi2(pars)
         assert abs(chi2[b] - ref_chi2) <= CHI2_ATOL * max(1.0, abs(ref_chi2) / 1e4), (chi2[b], ref_chi2)
+
+
+def test_c3_full_size_desi_shaped(tmp_path):
+    """C3 at its full size: four correlations, data on 2500/5000 bins, model and
+    distorted model on the distortion matrices' own 5625/11250-bin grids (dense 253 MB / 1 GB
+    matrices), new_metals rp-only matrices built on the device on those grids, fast_metals
+    (frozen metal x metal terms, shared metal x main tables), post-distortion broadband, ONE
+    global covariance over the 9540 masked bins.  A gradient stencil of 2P+1 vectors -- the
+    batch an iminuit step consumes -- against the oracle on the same operands."""
+    from helpers import make_c3_config, static_tables
+    from oracle.vega_oracle import Oracle
+    from vega_b200 import VegaInterface
+    from vega_b200.drivers import stencil
+    vega = VegaInterface(make_c3_config(tmp_path))
+    sizes = {n: (d.model_coordinates.r_grid.size, d.full_data_size) for n, d in vega.data.items()}
+    assert sorted(sizes.values()) == [(5625, 2500), (5625, 2500), (11250, 5000), (11250, 5000)]
+    synthetic.inject_dense_operands(vega, with_distortion=False, with_metals=False)   # covariances
+    synthetic.inject_global_covariance(vega)
+    oracle = Oracle(vega, tables=static_tables(), fast_metals=True)
+    synthetic.draw_mock_data(vega, oracle.compute_model())
+    names = ['bias_eta_LYA', 'beta_LYA', 'ap', 'at', 'bias_hcd', 'beta_hcd', 'drp_QSO',
+             'sigma_velo_disp_lorentz_QSO', 'bao_amp', 'bias_eta_SiII(1260)',
+             'BB-lyalya_lyalya-0 add post r,mu (1,2)']
+    base = np.array([vega.params[n] for n in names])
+    theta = stencil(base, 0.02 * np.abs(base) + 1e-4, hessian=False)
+    assert theta.shape[0] == 2 * len(names) + 1
+    chi2 = vega.chi2_batch(theta, names)
+    engine = vega._engine_for(tuple(names))
+    assert sum(engine.n_static_xi(ci) for ci in range(4)) > 0
+    for b in (0, 3, 2 * len(names)):
+        ref = oracle.chi2(dict(zip(names, theta[b])))
+        assert abs(chi2[b] - ref) <= CHI2_ATOL * max(1.0, abs(ref) / 1e4), (b, chi2[b], ref)
+    model = vega.compute_model(dict(zip(names, theta[3])))
+    assert_xi_close(model, oracle.compute_model(dict(zip(names, theta[3]))), 'C3 stencil point')

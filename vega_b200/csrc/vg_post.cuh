@@ -95,7 +95,7 @@ __device__ __forceinline__ double metal_bias_weight(const vg_eval_desc& d, const
 // in shared memory, a thread owns one rt column and every 4th rp row (<= 32 rows), the
 // matrix row entries are warp-uniform loads served by L1.  grid = B, block 256,
 // dynamic shared memory Np*Nt doubles.
-constexpr int MRP_ROWS = 32;   // rp rows per thread (Np <= 128)
+constexpr int MRP_ROWS = 40;   // rp rows per thread (Np <= 160: DESI's 150 rp bins of a cross on the 300 Mpc/h grid)
 __global__ void __launch_bounds__(256)
 metal_rp_kernel(const double* __restrict__ xmet, int n_metal, int ld, const double* __restrict__ A,
                 int np, int nt, double* __restrict__ met) {
