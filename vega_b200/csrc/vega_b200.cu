@@ -584,7 +584,7 @@ int vg_corr_set_metal_matrix_rp(vg_plan* plan, int32_t corr, int32_t slot, const
   VG_REQUIRE(slot >= 0 && slot < 4096, "bad metal slot");
   VG_REQUIRE(n_rp > 0 && n_rt > 0 && n_rp * n_rt == c.n_model, "rp-only metal matrix: %d x %d bins != %d",
              n_rp, n_rt, c.n_model);
-  VG_REQUIRE(n_rp <= 4 * vg::MRP_ROWS, "rp-only metal matrix: more than %d rp bins", 4 * vg::MRP_ROWS);
+  VG_REQUIRE(n_rp <= vg::MRP_MAX_NP, "rp-only metal matrix: more than %d rp bins", vg::MRP_MAX_NP);
   VG_REQUIRE(!c.metal_rp || (c.rp_np == n_rp && c.rp_nt == n_rt), "rp-only metal matrices of different shapes");
   if ((int)c.metal_rp_host.size() <= slot) c.metal_rp_host.resize(slot + 1);
   c.metal_rp_host[slot].assign(mat, mat + (size_t)n_rp * n_rp);
@@ -995,13 +995,8 @@ int launch_pk_fast(int vmode, int kind, dim3 grid, dim3 block, size_t smem, cuda
 
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st) {
-  const size_t smem = (size_t)c.n_model * 8;
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
-    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::metal_rp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
-  }
-  vg::metal_rp_kernel<<<(unsigned)B, 256, smem, st>>>(xmet, n_metal, c.ld_model, A, c.rp_np, c.rp_nt, met);
+  dim3 grid(vg_cdiv(c.rp_nt, vg::MRP_TN), vg_cdiv(c.rp_np, vg::MRP_TM), (unsigned)B);
+  vg::metal_rp_kernel<<<grid, 256, 0, st>>>(xmet, n_metal, c.ld_model, A, c.rp_np, c.rp_nt, met);
   VG_LAUNCHED();
   return VG_OK;
 }

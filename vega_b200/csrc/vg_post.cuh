@@ -91,49 +91,56 @@ __device__ __forceinline__ double metal_bias_weight(const vg_eval_desc& d, const
 // rp-only metal matrices (new_metals with rp_only_metal_mats, vega/metals.py:354-358):
 //   met[b][rp][rt] = sum_c sum_rp' A_c[rp][rp'] xmet[b][c][rp'][rt]
 // -- Np^2 numbers per metal correlation instead of (Np Nt)^2, and 2 Np^2 Nt flops per vector
-// instead of 2 (Np Nt)^2.  One CTA per vector: the (Np x Nt) block of each metal xi is staged
-// in shared memory, a thread owns one rt column and every 4th rp row (<= 32 rows), the
-// matrix row entries are warp-uniform loads served by L1.  grid = B, block 256,
-// dynamic shared memory Np*Nt doubles.
-constexpr int MRP_ROWS = 40;   // rp rows per thread (Np <= 160: DESI's 150 rp bins of a cross on the 300 Mpc/h grid)
+// instead of 2 (Np Nt)^2.  A small batched GEMM (M = Np, N = Nt, K = n_metal*Np per vector):
+// CTA tile 40 rp x 32 rt, K in chunks of 32 staged in shared memory (A chunk [40][32+1],
+// X chunk [32][32]); a thread owns one rt column and 5 rp rows; the A entries are
+// warp-uniform (broadcast) shared loads.  grid = (rt tiles, rp chunks, B), block 256.
+constexpr int MRP_TM = 40, MRP_TN = 32, MRP_TK = 32, MRP_R = 5;
+constexpr int MRP_MAX_NP = 4096;
 __global__ void __launch_bounds__(256)
 metal_rp_kernel(const double* __restrict__ xmet, int n_metal, int ld, const double* __restrict__ A,
                 int np, int nt, double* __restrict__ met) {
-  extern __shared__ double xs[];                 // [np][nt]
-  const long long b = blockIdx.x;
-  const int tid = threadIdx.x, g = tid >> 6, lane_rt = tid & 63;
-  const int n = np * nt;
-  for (int rt0 = 0; rt0 < nt; rt0 += 64) {
-    const int rt = rt0 + lane_rt;
-    double acc[MRP_ROWS];
+  __shared__ double As[MRP_TM][MRP_TK + 1];
+  __shared__ double Xs[MRP_TK][MRP_TN];
+  const long long b = blockIdx.z;
+  const int rt0 = blockIdx.x * MRP_TN, rp0 = blockIdx.y * MRP_TM;
+  const int tid = threadIdx.x, lane = tid & 31, g = tid >> 5;      // g: 8 groups of 5 rows
+  double acc[MRP_R];
 #pragma unroll
-    for (int r = 0; r < MRP_ROWS; ++r) acc[r] = 0.0;
-    for (int c = 0; c < n_metal; ++c) {
+  for (int r = 0; r < MRP_R; ++r) acc[r] = 0.0;
+  for (int c = 0; c < n_metal; ++c) {
+    const double* Ac = A + (long long)c * np * np;
+    const double* x = xmet + (b * n_metal + c) * ld;
+    for (int k0 = 0; k0 < np; k0 += MRP_TK) {
       __syncthreads();
-      const double* x = xmet + (b * n_metal + c) * ld;
-      for (int i = tid; i < n; i += 256) xs[i] = x[i];
-      __syncthreads();
-      if (rt < nt) {
-        const double* Ac = A + (long long)c * np * np;
-        for (int k = 0; k < np; ++k) {
-          const double xv = xs[k * nt + rt];
-#pragma unroll
-          for (int r = 0; r < MRP_ROWS; ++r) {
-            const int rp = g + 4 * r;
-            if (rp < np) acc[r] = fma(__ldg(Ac + (long long)rp * np + k), xv, acc[r]);
-          }
-        }
+      for (int i = tid; i < MRP_TM * MRP_TK; i += 256) {
+        const int r = i / MRP_TK, k = i % MRP_TK;
+        As[r][k] = (rp0 + r < np && k0 + k < np) ? __ldg(Ac + (long long)(rp0 + r) * np + k0 + k) : 0.0;
       }
-    }
-    if (rt < nt) {
+      for (int i = tid; i < MRP_TK * MRP_TN; i += 256) {
+        const int k = i / MRP_TN, t = i % MRP_TN;
+        Xs[k][t] = (k0 + k < np && rt0 + t < nt) ? x[(k0 + k) * nt + rt0 + t] : 0.0;
+      }
+      __syncthreads();
+#pragma unroll 8
+      for (int k = 0; k < MRP_TK; ++k) {
+        const double xv = Xs[k][lane];
 #pragma unroll
-      for (int r = 0; r < MRP_ROWS; ++r) {
-        const int rp = g + 4 * r;
-        if (rp < np) met[b * ld + rp * nt + rt] = acc[r];
+        for (int r = 0; r < MRP_R; ++r) acc[r] = fma(As[g * MRP_R + r][k], xv, acc[r]);
       }
     }
   }
-  for (int i = n + tid; i < ld; i += 256) met[b * ld + i] = 0.0;   // pad columns stay finite
+  const int rt = rt0 + lane;
+  if (rt < nt) {
+#pragma unroll
+    for (int r = 0; r < MRP_R; ++r) {
+      const int rp = rp0 + g * MRP_R + r;
+      if (rp < np) met[b * ld + rp * nt + rt] = acc[r];
+    }
+  }
+  // pad columns stay finite (written by the first CTA of each vector)
+  if (blockIdx.x == 0 && blockIdx.y == 0)
+    for (int i = np * nt + tid; i < ld; i += 256) met[b * ld + i] = 0.0;
 }
 
 __global__ void combine_pre_kernel(CombineArgs a) {
