@@ -315,6 +315,18 @@ def main():
         n_own = sum(sum(1 for d in info['evals'] if d.table_owner < 0 and not d.frozen and not d.direct)
                     for info in engine.infos)
         n_grid_eval = n_own - n_moment
+        pk_instr = 0.0          # summed over the evaluations that go through the per-point pass
+        for ci, info in enumerate(engine.infos):
+            own = [d for d in info['evals'] if d.table_owner < 0 and not d.frozen and not d.direct]
+            if engine.n_moment(ci) >= len(own):
+                continue
+            twinned = {d.pk_twin for d in own if d.pk_twin >= 0}
+            part = 0.0
+            for e, d in enumerate(info['evals']):
+                if any(d is o for o in own):
+                    hcd = d.hcd_model and (d.hcd_on[0] or d.hcd_on[1])
+                    part += 12.0 if (d.pk_twin >= 0 or e in twinned) else (18.5 if hcd else 16.5)
+            pk_instr += part * (len(own) - engine.n_moment(ci)) / len(own)
         grid_bytes = 6512000.0 * n_grid_eval * B
         kernels = {s: {'ms_per_step': stage_ms[s], 'launch_groups_per_step': cnt_stage[i] / args.steps}
                    for i, s in enumerate(STAGES)}
@@ -356,14 +368,16 @@ def main():
                          'peak_source': 'cuBLAS FP64 8192^3 measured live in this run (MEASURED_PEAKS.json has no '
                                         'FP64 figure); algorithmic flops per SURVEY.md 8d',
                          'share_of_step': gemm_ms / ms_per_step},
-            # 15.5 FP64 instructions per grid point and vector in the Lorentzian kernels (SASS main
-            # loop: 155 per 10 point-vectors), counted as FMAs against the measured DFMA peak
+            # FP64 instructions per grid point, vector and evaluation from the SASS main loops of
+            # the fast kernels (cuobjdump): 16.5 (Kaiser x Lorentzian), 18.5 (+ HCD), 12 for each
+            # member of a peak/smooth pair evaluated together; counted as FMAs against the DFMA peak
             'roofline_pk_ell': {'bound': 'fp64 alu', 'peak': dfma_peak, 'unit': 'TFLOP/s (FP64 instr x 2)',
-                                'achieved': (2 * 15.5 * 814000.0 * n_grid_eval * B / (stage_ms['pk_ell'] * 1e-3) / 1e12
+                                'fp64_instr_per_point_vector': pk_instr,
+                                'achieved': (2 * pk_instr * 814000.0 * B / (stage_ms['pk_ell'] * 1e-3) / 1e12
                                              if stage_ms['pk_ell'] > 0 else None),
-                                'frac': (2 * 15.5 * 814000.0 * n_grid_eval * B / (stage_ms['pk_ell'] * 1e-3) / 1e12
+                                'frac': (2 * pk_instr * 814000.0 * B / (stage_ms['pk_ell'] * 1e-3) / 1e12
                                          / dfma_peak if stage_ms['pk_ell'] > 0 and dfma_peak else None),
-                                'ncu_fp64_pipe_active': [0.726, 0.674],
+                                'ncu_fp64_pipe_active': [0.727, 0.675],
                                 'share_of_step': stage_ms['pk_ell'] / ms_per_step},
             'kernels': kernels,
             'cpu_baseline': base,

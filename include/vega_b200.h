@@ -115,7 +115,10 @@ typedef struct vg_eval_desc {
                                is a sampled parameter and no additive xi term is on, so the
                                coordinates and per-bin factors are the same for every vector: in
                                moment form the gather is applied once to the static tables */
-  int32_t reserved_;
+  int32_t pk_twin;          /* >=0: evaluation `pk_twin` of the same correlation has the same P(k,mu)
+                               up to the linear P(k) and the static grid (peak / smooth of one
+                               correlation): the two go through the per-point pass together and
+                               share the Kaiser / HCD / velocity-dispersion arithmetic.  -1: none */
 } vg_eval_desc;
 
 /* One broadband term (vega/broadband_poly.py:23-198) */

@@ -45,7 +45,7 @@ class EvalDesc(C.Structure):
         ('out_slot', i32), ('weight_bias', i32), ('idx_weight_extra', i32),
         ('weight_const', f64),
         ('table_owner', i32), ('mock_los_mode', i32), ('idx_los_smooth_amp', i32),
-        ('mock_bin_size', f64), ('direct', i32), ('frozen', i32), ('static_xi', i32), ('reserved_', i32),
+        ('mock_bin_size', f64), ('direct', i32), ('frozen', i32), ('static_xi', i32), ('pk_twin', i32),
     ]
 
     def __init__(self):
@@ -62,6 +62,7 @@ class EvalDesc(C.Structure):
         self.single_ell = -1
         self.weight_const = 1.0
         self.table_owner = -1
+        self.pk_twin = -1
 
 
 class BBTerm(C.Structure):

@@ -99,6 +99,12 @@ struct EvalLayout {
   // evaluations grouped by pk_ell kernel class: 0..19 fast (VMODE*5 + KIND), 20..22 generic (20 + MODE)
   std::vector<int> class_ids[23];
   DevBuf d_class_ids[23];
+  // pairs of evaluations that go through the fast kernels together (vg_eval_desc::pk_twin):
+  // pair_ids[m][i] with twin pair_twins[m][i]; class_ids[m] then lists the pairs' members LAST
+  // (entries [0, n_single[m]) are launched one by one, B < 8 launches them all one by one)
+  std::vector<int> pair_ids[23], pair_twins[23];
+  DevBuf d_pair_ids[23], d_pair_twins[23];
+  int n_single[23] = {0};
   std::vector<int> mom_ids;      // evaluations in moment form
   std::vector<int> gather_ids;   // evaluations K3 runs for
   std::vector<int> mxi_ids;      // LAY_MOM: evaluations whose xi stage is in moment form (static_xi)
@@ -336,6 +342,7 @@ int build_layouts(vg_plan* plan, Corr& c) {
   for (int li = 0; li < 4; ++li) {
     EvalLayout& L = c.lay[li];
     for (auto& ids : L.class_ids) ids.clear();
+    for (int m = 0; m < 23; ++m) { L.pair_ids[m].clear(); L.pair_twins[m].clear(); L.n_single[m] = 0; }
     L.mom_ids.clear(); L.gather_ids.clear(); L.mxi_ids.clear(); L.mxi_owner.clear();
     L.n_full = 0; L.n_metal = 0;
     L.metal_map.assign(std::max(c.n_metal, 1), -1);
@@ -363,8 +370,32 @@ int build_layouts(vg_plan* plan, Corr& c) {
     }
     for (int e = 0; e < E; ++e)
       if (c.evals[e].table_owner >= 0) tabslot[e] = tabslot[c.evals[e].table_owner];
-    for (int m = 0; m < PK_NCLS; ++m)
+    // twins: both members per point in the same fast class of this layout
+    for (int m = 0; m < 20; ++m) {
+      std::vector<int>& ids = L.class_ids[m];
+      std::vector<int> single, paired;
+      std::vector<char> taken(E, 0);
+      for (int e : ids) {
+        const int t = c.evals[e].pk_twin;
+        if (t >= 0 && t < E && t != e && !taken[t] && !taken[e] &&
+            std::find(ids.begin(), ids.end(), t) != ids.end()) {
+          L.pair_ids[m].push_back(t); L.pair_twins[m].push_back(e);
+          taken[t] = taken[e] = 1;
+        }
+      }
+      for (int e : ids) (taken[e] ? paired : single).push_back(e);
+      L.n_single[m] = (int)single.size();
+      ids = single;
+      ids.insert(ids.end(), paired.begin(), paired.end());
+    }
+    for (int m = 20; m < PK_NCLS; ++m) L.n_single[m] = (int)L.class_ids[m].size();
+    for (int m = 0; m < PK_NCLS; ++m) {
       if (!L.class_ids[m].empty()) VG_TRY(upload(L.d_class_ids[m], L.class_ids[m].data(), L.class_ids[m].size()));
+      if (!L.pair_ids[m].empty()) {
+        VG_TRY(upload(L.d_pair_ids[m], L.pair_ids[m].data(), L.pair_ids[m].size()));
+        VG_TRY(upload(L.d_pair_twins[m], L.pair_twins[m].data(), L.pair_twins[m].size()));
+      }
+    }
     if (!L.mom_ids.empty()) VG_TRY(upload(L.d_mom_ids, L.mom_ids.data(), L.mom_ids.size()));
     if (!L.gather_ids.empty()) VG_TRY(upload(L.d_gather_ids, L.gather_ids.data(), L.gather_ids.size()));
     if (!L.mxi_ids.empty()) {
@@ -957,41 +988,53 @@ vg::BroadbandDev bb_dev(const Corr& c) {
 }
 
 // Dispatch of the templated fast pk_ell kernels: vmode 0..3 (PK_V_*), kind 0..4
-template <int VM, int KD>
+template <int VM, int KD, int TW>
 int launch_pk_fast_one(dim3 grid, dim3 block, size_t smem, cudaStream_t st, const vg::PkGridDev& g,
-                       const vg_eval_desc* ev, int E, const int* ids, const int* out_slot, int n_slots,
-                       const double* pf, int npf, int B, double* out) {
+                       const vg_eval_desc* ev, int E, const int* ids, const int* twins, const int* out_slot,
+                       int n_slots, const double* pf, int npf, int B, double* out) {
   static size_t smem_set = 0;
   if (smem > smem_set) {
-    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::pk_ell_fast_kernel<2, VM, KD>,
+    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::pk_ell_fast_kernel<2, VM, KD, TW>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     smem_set = smem;
   }
-  vg::pk_ell_fast_kernel<2, VM, KD><<<grid, block, smem, st>>>(g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+  vg::pk_ell_fast_kernel<2, VM, KD, TW><<<grid, block, smem, st>>>(g, ev, E, ids, twins, out_slot, n_slots, pf,
+                                                                 npf, B, out);
   return VG_OK;
 }
-template <int VM>
+#define VG_PK_ARGS grid, block, smem, st, g, ev, E, ids, twins, out_slot, n_slots, pf, npf, B, out
+template <int VM, int TW>
 int launch_pk_fast_kind(int kind, dim3 grid, dim3 block, size_t smem, cudaStream_t st, const vg::PkGridDev& g,
-                        const vg_eval_desc* ev, int E, const int* ids, const int* out_slot, int n_slots,
-                        const double* pf, int npf, int B, double* out) {
+                        const vg_eval_desc* ev, int E, const int* ids, const int* twins, const int* out_slot,
+                        int n_slots, const double* pf, int npf, int B, double* out) {
   switch (kind) {
-    case 0: return launch_pk_fast_one<VM, 0>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
-    case 1: return launch_pk_fast_one<VM, 1>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
-    case 2: return launch_pk_fast_one<VM, 2>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
-    case 3: return launch_pk_fast_one<VM, 3>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
-    default: return launch_pk_fast_one<VM, 4>(grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    case 0: return launch_pk_fast_one<VM, 0, TW>(VG_PK_ARGS);
+    case 1: return launch_pk_fast_one<VM, 1, TW>(VG_PK_ARGS);
+    case 2: return launch_pk_fast_one<VM, 2, TW>(VG_PK_ARGS);
+    case 3: return launch_pk_fast_one<VM, 3, TW>(VG_PK_ARGS);
+    default: return launch_pk_fast_one<VM, 4, TW>(VG_PK_ARGS);
   }
 }
+// twins == nullptr: one evaluation per grid.z entry; else pairs (ids[z], twins[z])
 int launch_pk_fast(int vmode, int kind, dim3 grid, dim3 block, size_t smem, cudaStream_t st,
-                   const vg::PkGridDev& g, const vg_eval_desc* ev, int E, const int* ids, const int* out_slot,
-                   int n_slots, const double* pf, int npf, int B, double* out) {
+                   const vg::PkGridDev& g, const vg_eval_desc* ev, int E, const int* ids, const int* twins,
+                   const int* out_slot, int n_slots, const double* pf, int npf, int B, double* out) {
+  if (twins) {
+    switch (vmode) {
+      case 0: return launch_pk_fast_kind<0, 1>(kind, VG_PK_ARGS);
+      case 1: return launch_pk_fast_kind<1, 1>(kind, VG_PK_ARGS);
+      case 2: return launch_pk_fast_kind<2, 1>(kind, VG_PK_ARGS);
+      default: return launch_pk_fast_kind<3, 1>(kind, VG_PK_ARGS);
+    }
+  }
   switch (vmode) {
-    case 0: return launch_pk_fast_kind<0>(kind, grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
-    case 1: return launch_pk_fast_kind<1>(kind, grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
-    case 2: return launch_pk_fast_kind<2>(kind, grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
-    default: return launch_pk_fast_kind<3>(kind, grid, block, smem, st, g, ev, E, ids, out_slot, n_slots, pf, npf, B, out);
+    case 0: return launch_pk_fast_kind<0, 0>(kind, VG_PK_ARGS);
+    case 1: return launch_pk_fast_kind<1, 0>(kind, VG_PK_ARGS);
+    case 2: return launch_pk_fast_kind<2, 0>(kind, VG_PK_ARGS);
+    default: return launch_pk_fast_kind<3, 0>(kind, VG_PK_ARGS);
   }
 }
+#undef VG_PK_ARGS
 
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st) {
@@ -1039,9 +1082,17 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
       const int* ids = L.d_class_ids[m].as<int>();
       if (m < 20 && fast_ok) {
         dim3 block(vg::PK_KLANES, vg::PK_FAST_MG, vg::PK_FAST_EG);
-        dim3 grid(vg_cdiv(Bc, 2 * vg::PK_FAST_EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)class_ids.size());
-        VG_TRY(launch_pk_fast(m / 5, m % 5, grid, block, fast_smem, st, g, ev, E, ids, out_slot, Ef, pf,
-                              plan->npf, (int)Bc, out));
+        if (L.n_single[m] > 0) {
+          dim3 grid(vg_cdiv(Bc, 2 * vg::PK_FAST_EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)L.n_single[m]);
+          VG_TRY(launch_pk_fast(m / 5, m % 5, grid, block, fast_smem, st, g, ev, E, ids, nullptr, out_slot, Ef,
+                                pf, plan->npf, (int)Bc, out));
+        }
+        if (!L.pair_ids[m].empty()) {      // one vector, two evaluations per thread
+          if (L.n_single[m] > 0) VG_LAUNCHED();
+          dim3 grid(vg_cdiv(Bc, vg::PK_FAST_EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)L.pair_ids[m].size());
+          VG_TRY(launch_pk_fast(m / 5, m % 5, grid, block, fast_smem, st, g, ev, E, L.d_pair_ids[m].as<int>(),
+                                L.d_pair_twins[m].as<int>(), out_slot, Ef, pf, plan->npf, (int)Bc, out));
+        }
       } else {
         dim3 block(vg::PK_KLANES, MG, EG);
         dim3 grid(vg_cdiv(Bc, NB * EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)class_ids.size());

@@ -407,12 +407,18 @@ inline size_t pk_fast_smem_bytes(int nmu) {
   return (size_t)nmu * 5 * 8 + (size_t)PK_GROUPS * 2 * PK_MAX_ELL * (PK_KLANES + 1) * 8;
 }
 
-template <int NB, int VMODE, int KIND>
+// TWIN = 1: the two accumulator sets of a thread belong to ONE vector and to TWO evaluations
+// (eval_ids[z] and twin_ids[z], vg_eval_desc::pk_twin) that differ only by the static grid and
+// the linear P(k): Kaiser / HCD / velocity dispersion are evaluated once per grid point for
+// both (23 instead of 2 x 18 FP64 instructions per point and vector with two Lorentzians).
+template <int NB, int VMODE, int KIND, int TWIN>
 __global__ void __launch_bounds__(PK_KLANES * PK_GROUPS, 2)
 pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_eval,
-                   const int* __restrict__ eval_ids, const int* __restrict__ out_slot, int n_slots,
+                   const int* __restrict__ eval_ids, const int* __restrict__ twin_ids,
+                   const int* __restrict__ out_slot, int n_slots,
                    const double* __restrict__ pfull, int npf, int B,
                    double* __restrict__ out) {
+  constexpr int NV = TWIN ? 1 : NB;      // vectors per thread
   constexpr int MG = PK_FAST_MG, EG = PK_FAST_EG, U = PK_FAST_U;
   extern __shared__ __align__(16) double pk_sm[];
   __shared__ vg_eval_desc d;
@@ -425,6 +431,7 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
   const int tid = (eg * MG + mg) * PK_KLANES + tx;
   const int eval = eval_ids[blockIdx.z];
   const int slot = out_slot[eval];
+  const int eval2 = TWIN ? twin_ids[blockIdx.z] : eval;
   {
     const int* src = reinterpret_cast<const int*>(evals + eval);
     int* dst = reinterpret_cast<int*>(&d);
@@ -439,15 +446,15 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
   const int ik_raw = blockIdx.y * PK_KLANES + tx;
   const int ik = min(ik_raw, g.nk - 1);
   const double k = g.k[ik];
-  const int b0 = (blockIdx.x * EG + eg) * NB;
+  const int b0 = (blockIdx.x * EG + eg) * NV;
   constexpr bool HCD = KIND >= 2;
   constexpr bool TWO = KIND == 1 || KIND >= 3;
   const int tH = (KIND >= 3 && !d.hcd_on[0]) ? 1 : 0;   // tracer carrying the HCD term
   const int tP = 1 - tH;
 
-  double aH0[NB], aH1[NB], hH0[NB], hH1[NB], aP0[NB], aP1[NB], c0[NB], c1[NB];
+  double aH0[NV], aH1[NV], hH0[NV], hH1[NV], aP0[NV], aP1[NV], c0[NV], c1[NV];
 #pragma unroll
-  for (int e = 0; e < NB; ++e) {
+  for (int e = 0; e < NV; ++e) {
     const double* p = pfull + (long long)min(b0 + e, B - 1) * npf;
     const KaiserCoef kc = kaiser_setup(d, p, k);
     aH0[e] = tH ? kc.a0[1] : kc.a0[0]; aH1[e] = tH ? kc.a1[1] : kc.a1[0];
@@ -462,6 +469,9 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
   }
   const bool has_s = d.static_grid >= 0;
   const double* __restrict__ S = has_s ? g.grids[d.static_grid] : g.k;
+  const int sg2 = TWIN ? evals[eval2].static_grid : -1;
+  const bool has_s2 = sg2 >= 0;
+  const double* __restrict__ S2 = has_s2 ? g.grids[sg2] : g.k;
   const double* __restrict__ Fg = HCD ? g.grids[d.hcd_grid] : g.k;
   const unsigned rs = (unsigned)(MG * g.nk);      // elements between the rows of one thread
   unsigned off = (unsigned)(mg * g.nk + ik);
@@ -476,11 +486,12 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
 
   const int n_batches = nmu / (MG * U);
   for (int jb = 0; jb < n_batches; ++jb) {
-    double s[U], f[U];
+    double s[U], f[U], s2[TWIN ? U : 1];
 #pragma unroll
     for (int u = 0; u < U; ++u) {   // the L2-latency loads of the whole batch first
       s[u] = has_s ? __ldg(S + (off + u * rs)) : 1.0;
       f[u] = HCD ? __ldg(Fg + (off + u * rs)) : 0.0;
+      if (TWIN) s2[u] = has_s2 ? __ldg(S2 + (off + u * rs)) : 1.0;
     }
     off += U * rs;
 #pragma unroll
@@ -489,7 +500,7 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
       const double2 wa = wrow[u * MG * 2], wb = wrow[u * MG * 2 + 1];
       const double mu2 = mu * mu;
 #pragma unroll
-      for (int e = 0; e < NB; ++e) {
+      for (int e = 0; e < NV; ++e) {
         double t;
         if (HCD) {
           const double tb = fma(hH0[e], f[u], aH0[e]);
@@ -498,7 +509,8 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
         } else {
           t = fma(aH1[e], mu2, aH0[e]);
         }
-        double P = (TWO ? t * fma(aP1[e], mu2, aP0[e]) : t * t) * s[u];
+        double P = TWO ? t * fma(aP1[e], mu2, aP0[e]) : t * t;
+        if (!TWIN) P *= s[u];
         if (VMODE == PK_V_LOR1 || VMODE == PK_V_LOR2) {
           double a = fma(c0[e], mu2, 1.0);
           if (VMODE == PK_V_LOR2) a *= fma(c1[e], mu2, 1.0);
@@ -509,10 +521,22 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
         } else if (VMODE == PK_V_GAUSS) {
           P *= exp(c0[e] * mu2);
         }
-        acc[e][0] = fma(wa.x, P, acc[e][0]);
-        acc[e][1] = fma(wa.y, P, acc[e][1]);
-        acc[e][2] = fma(wb.x, P, acc[e][2]);
-        acc[e][3] = fma(wb.y, P, acc[e][3]);
+        if (TWIN) {
+          const double P0 = P * s[u], P1 = P * s2[u];
+          acc[0][0] = fma(wa.x, P0, acc[0][0]);
+          acc[0][1] = fma(wa.y, P0, acc[0][1]);
+          acc[0][2] = fma(wb.x, P0, acc[0][2]);
+          acc[0][3] = fma(wb.y, P0, acc[0][3]);
+          acc[1][0] = fma(wa.x, P1, acc[1][0]);
+          acc[1][1] = fma(wa.y, P1, acc[1][1]);
+          acc[1][2] = fma(wb.x, P1, acc[1][2]);
+          acc[1][3] = fma(wb.y, P1, acc[1][3]);
+        } else {
+          acc[e][0] = fma(wa.x, P, acc[e][0]);
+          acc[e][1] = fma(wa.y, P, acc[e][1]);
+          acc[e][2] = fma(wb.x, P, acc[e][2]);
+          acc[e][3] = fma(wb.y, P, acc[e][3]);
+        }
       }
     }
     wrow += U * MG * 2;
@@ -529,12 +553,16 @@ pk_ell_fast_kernel(PkGridDev g, const vg_eval_desc* __restrict__ evals, int n_ev
     __syncthreads();
     if (eg == turn) {
       const double pk_lin = g.pk_lin[d.pk_lin_sel][ik];
+      const double pk_lin2 = TWIN ? g.pk_lin[evals[eval2].pk_lin_sel][ik] : pk_lin;
+      const int slot2 = TWIN ? out_slot[eval2] : slot;
       for (int o = mg; o < NB * PK_MAX_ELL; o += MG) {
         const int e = o / PK_MAX_ELL, l = o % PK_MAX_ELL;
-        if (b0 + e >= B || l >= g.n_ell || ik_raw >= g.nk) continue;
+        const int b = TWIN ? b0 : b0 + e;          // TWIN: e selects the evaluation, not the vector
+        if (b >= B || l >= g.n_ell || ik_raw >= g.nk) continue;
         double sum = 0.0;
         for (int m = 0; m < MG; ++m) sum += red[m][o][tx];
-        out[(((long long)(b0 + e) * n_slots + slot) * g.n_ell + l) * g.nk_pad + ik] = sum * pk_lin;
+        const int sl = (TWIN && e == 1) ? slot2 : slot;
+        out[(((long long)b * n_slots + sl) * g.n_ell + l) * g.nk_pad + ik] = sum * ((TWIN && e == 1) ? pk_lin2 : pk_lin);
       }
     }
   }

@@ -612,6 +612,7 @@ class PlanBuilder:
 
         info['bb_terms'], info['bb_design'] = self.broadband_terms(item)
         self.share_identical_tables(info['evals'])
+        self.pair_twins(info['evals'])
         return info
 
     # fields of vg_eval_desc that determine P(k,mu) -> knot tables (everything before the xi block)
@@ -649,6 +650,26 @@ class PlanBuilder:
             else:
                 sig.append((name, ident(v) if name.startswith('idx_') else v))
         return tuple(sig)
+
+    _TWIN_FREE = ('pk_lin_sel', 'is_peak', 'static_grid', 'static_mask')
+
+    def pair_twins(self, evals):
+        """Peak and smooth of one correlation differ only by the linear P(k) and by what is in
+        their static grids (vega/model.py:176-186): when every per-vector factor is the same, the
+        smooth evaluation points at the peak one (vg_eval_desc.pk_twin) and the device evaluates
+        the shared Kaiser / HCD / velocity-dispersion arithmetic once for both."""
+        def dynamic_part(d):
+            free = self._TWIN_FREE
+            if not (d.dyn_mask & _lib.F_PEAKNL):    # the peak's non-linear broadening is in its static grid
+                free = free + ('idx_sigmaNL',)
+            return tuple(kv for kv in self.pk_signature(d) if kv[0] not in free)
+        if len(evals) < 2:
+            return
+        peak, smooth = evals[0], evals[1]
+        if peak.table_owner >= 0 or smooth.table_owner >= 0 or peak.direct or smooth.direct:
+            return
+        if dynamic_part(peak) == dynamic_part(smooth):
+            smooth.pk_twin = 0
 
     def share_identical_tables(self, evals):
         """Evaluations of one correlation whose P(k,mu) inputs are identical (e.g. QSO x metal terms
