@@ -59,6 +59,19 @@ def test_static_xi_flag_follows_the_sampled_set():
     assert pb.describe_corr('test_7')['evals'][0].static_xi == 0
 
 
+def test_peak_and_smooth_are_paired_when_their_sampled_factors_agree():
+    """vg_eval_desc.pk_twin (vega/model.py:176-186: peak and smooth differ by the linear P(k) and
+    the peak's non-linear broadening)."""
+    vega, pb = builder('configs/full_configs/main.ini', sampled=['bias_eta_LYA', 'sigma_velo_disp_lorentz_QSO'])
+    for name in vega.corr_items:
+        evals = pb.describe_corr(name)['evals']
+        assert evals[0].pk_twin == -1 and evals[1].pk_twin == 0
+        assert all(d.pk_twin == -1 for d in evals[2:])
+    # a sampled sigmaNL makes the broadening a per-vector factor of the peak only
+    vega, pb = builder('configs/full_configs/main.ini', sampled=['sigmaNL_par'])
+    assert pb.describe_corr('lyalya_qso')['evals'][1].pk_twin == -1
+
+
 def test_sampled_parameter_makes_factor_dynamic():
     vega, pb = builder('configs/full_configs/main.ini',
                        sampled=['sigma_velo_disp_lorentz_QSO', 'L0_hcd', 'par_sigma_smooth'])
