@@ -308,3 +308,40 @@ def test_c3_full_size_desi_shaped(tmp_path):
         assert abs(chi2[b] - ref) <= CHI2_ATOL * max(1.0, abs(ref) / 1e4), (b, chi2[b], ref)
     model = vega.compute_model(dict(zip(names, theta[3])))
     assert_xi_close(model, oracle.compute_model(dict(zip(names, theta[3]))), 'C3 stencil point')
+
+
+def test_model_call_shapes_and_stage_components():
+    """VegaInterface.models[name]: Model.compute / compute_direct (vega/model.py:157-208) and the
+    per-stage components against the oracle's own stages (PowerSpectrum.compute,
+    PktoXi.compute_pk_ells, CorrelationFunction.compute)."""
+    from oracle.vega_oracle import pk_model
+    vega, oracle = make_oracle('configs/full_configs/main.ini')
+    fid = vega.fiducial
+    pars = dict(vega.params)
+    pars.update({'bias_eta_LYA': -0.21, 'beta_LYA': 1.5, 'ap': 0.98, 'sigma_velo_disp_lorentz_QSO': 5.0})
+    ref = oracle.compute_model({k: pars[k] for k in ('bias_eta_LYA', 'beta_LYA', 'ap', 'sigma_velo_disp_lorentz_QSO')})
+    for name in ('lyalya_lyalya', 'lyalya_qso'):
+        model = vega.models[name]
+        got = model.compute(pars, fid['pk_full'], fid['pk_smooth'])
+        assert_xi_close({name: got}, {name: ref[name]}, 'Model.compute')
+        with pytest.raises(ValueError):
+            model.compute(pars, fid['pk_full'] * 1.01, fid['pk_smooth'])
+        cm = oracle.models[name]
+        lp = oracle.local_params(pars)
+        for component, pk_lin, peak in (('peak', fid['pk_full'] - fid['pk_smooth'], True),
+                                        ('smooth', fid['pk_smooth'], False)):
+            lp['peak'] = peak
+            pk_ref = pk_model(cm.grid, pk_lin, lp)
+            pk_got = model.pk(pars, component)
+            assert np.max(np.abs(pk_got - pk_ref)) <= 1e-12 * np.max(np.abs(pk_ref)), (name, component)
+            ells_ref = cm.transform.multipoles(pk_ref)
+            ells_got = model.pk_ells(pars, component)
+            assert np.max(np.abs(ells_got - ells_ref)) <= 1e-11 * np.max(np.abs(ells_ref)), (name, component)
+            xi_ref = cm.xi_core.compute(pk_ref, pk_lin, cm.transform, lp)
+            xi_got = model.xi(pars, component)
+            assert np.max(np.abs(xi_got - xi_ref)) <= XI_RTOL * np.max(np.abs(xi_ref)), (name, component)
+    direct = fid['pk_full'] * (1 + 0.02 * np.cos(np.log(fid['k'])))
+    got = vega.models['lyalya_qso'].compute_direct(pars, direct)
+    want = oracle.compute_model({k: pars[k] for k in ('bias_eta_LYA', 'beta_LYA', 'ap', 'sigma_velo_disp_lorentz_QSO')},
+                                direct_pk=direct)['lyalya_qso']
+    assert np.max(np.abs(got - want)) <= XI_RTOL * np.max(np.abs(want))

@@ -1,0 +1,84 @@
+"""`Model` call shapes of the reference (vega/model.py:8-208) on top of the device engine.
+
+`VegaInterface.models[name]` exposes, per correlation, what the reference's scripts reach for:
+`compute(pars, pk_full, pk_smooth)`, `compute_direct(pars, pk_full)` and the per-stage
+components (`Pk_core.compute`, `PktoXi.compute_pk_ells`, `Xi_core` outputs) through the
+library's stage taps.  Everything is evaluated on the device for a batch of one; `pars` may be a
+complete parameter dictionary (as `_get_lcl_prms` builds) or only the entries to change.
+"""
+import numpy as np
+
+from . import utils
+
+
+class Model:
+    def __init__(self, vega, name):
+        self._vega = vega
+        self._name = name
+        self._index = list(vega.corr_items).index(name)
+        self._corr_item = vega.corr_items[name]
+
+    # -- helpers ------------------------------------------------------------------------------
+    def _changed(self, pars):
+        """Entries of `pars` that differ from the interface's [parameters] values."""
+        pars = pars or {}
+        base = self._vega.params
+        return {k: v for k, v in pars.items() if k in base and base[k] != v}
+
+    def _check_templates(self, pk_full, pk_smooth=None):
+        fid = self._vega.fiducial
+        ok = np.array_equal(np.asarray(pk_full), fid['pk_full'])
+        if pk_smooth is not None:
+            ok = ok and np.array_equal(np.asarray(pk_smooth), fid['pk_smooth'])
+        if not ok:
+            raise ValueError('Model.compute evaluates the peak/smooth decomposition of the fiducial template '
+                             'the plan was built on; pass another P(k) through compute_direct.')
+
+    # -- vega/model.py:157-208 ------------------------------------------------------------------
+    def compute(self, pars, pk_full, pk_smooth):
+        """bao_amp * peak + smooth (+ metals, systematics, broadband, distortion) of this
+        correlation (vega/model.py:157-187)."""
+        self._check_templates(pk_full, pk_smooth)
+        return self._vega.compute_model(self._changed(pars), run_init=False)[self._name]
+
+    def compute_direct(self, pars, pk_full):
+        """The model directly from a full P(k) (vega/model.py:189-208)."""
+        return self._vega.compute_model(self._changed(pars), run_init=False, direct_pk=pk_full)[self._name]
+
+    # -- per-stage components (the save-components dictionaries, vega/model.py:113-116) -----------
+    def _stage(self, pars, stage, component):
+        changed = self._changed(pars)
+        engine = self._vega._engine_for(tuple(changed))
+        theta = self._vega._theta_row(engine, changed)
+        eval_index = {'peak': 0, 'smooth': 1}[component] if isinstance(component, str) else int(component)
+        out, status = engine.stage(self._index, stage, theta, eval_index=eval_index)
+        from . import _lib
+        if status[0] & _lib.STATUS_ARINYO:
+            raise utils.VegaArinyoError
+        if status[0] & _lib.STATUS_BOUNDS:
+            raise utils.VegaBoundsError
+        return out[0], engine
+
+    def pk(self, pars=None, component='smooth'):
+        """P(k, mu) of one component on the (mu, k) grid -- PowerSpectrum.compute
+        (vega/power_spectrum.py:87-196) with that component's linear P(k)."""
+        out, engine = self._stage(pars, 0, component)
+        nk = self._vega.fiducial['k'].size
+        return out.reshape(-1, nk)
+
+    def pk_ells(self, pars=None, component='smooth'):
+        """Multipoles P_ell(k), [n_ell, nk] -- PktoXi.compute_pk_ells (vega/pktoxi.py:79-97)."""
+        out, engine = self._stage(pars, 1, component)
+        nk = self._vega.fiducial['k'].size
+        nk_pad = (nk + 15) // 16 * 16
+        n_ell = len(engine.infos[self._index]['ells'])
+        eval_index = {'peak': 0, 'smooth': 1}[component] if isinstance(component, str) else int(component)
+        return out.reshape(-1, n_ell, nk_pad)[eval_index][:, :nk]
+
+    def xi(self, pars=None, component='smooth'):
+        """xi of the peak or smooth component on the model grid, before metals / broadband /
+        distortion -- CorrelationFunction.compute (vega/correlation_func.py:117-161)."""
+        out, engine = self._stage(pars, 3, component)
+        n_model = self._corr_item.model_coordinates.rp_grid.size
+        ld = (n_model + 15) // 16 * 16
+        return out.reshape(-1, ld)[{'peak': 0, 'smooth': 1}[component]][:n_model]

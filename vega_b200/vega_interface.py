@@ -118,10 +118,12 @@ class VegaInterface:
         self.sampler = control.get('sampler', None) if control else None
         self.monte_carlo = False
         self.minimizer = None
+        # the reference's per-correlation Model objects (vega/vega_interface.py:136-139)
+        from .model import Model
+        self.models = {name: Model(self, name) for name in self.corr_items}
         self.analysis = None
         self.output = None
         self.plots = None
-        self.models = {}
 
         self._device = device
         self._batch_chunk = batch_chunk
