@@ -88,6 +88,46 @@ def test_batched_minimizer_surface_and_two_stage_fit():
     assert mini.values['ap'] == 1.0 and mini.fixed['ap'] and mini.errors['ap'] == 0.0
 
 
+def test_chi2_scan_fits_every_grid_point_in_one_batch():
+    """BatchedAnalysis.chi2_scan (vega/analysis.py:53-124) on a correlated quadratic: the profile
+    over the free parameter has a closed form."""
+    import configparser
+    from vega_b200.drivers import BatchedAnalysis
+    names = ['ap', 'at', 'bias']
+    truth = np.array([1.0, 1.0, -0.1])
+    sig = np.array([0.03, 0.04, 0.01])
+    corr = np.array([[1, .4, .2], [.4, 1, -.3], [.2, -.3, 1]])
+    icov = np.linalg.inv(corr * sig[:, None] * sig[None, :])
+    batches = []
+
+    def chi2_batch(theta):
+        batches.append(theta.shape[0])
+        d = theta - truth
+        return np.einsum('bi,ij,bj->b', d, icov, d) + 3.
+
+    cfg = configparser.ConfigParser()
+    cfg.optionxform = lambda o: o
+    cfg['chi2 scan'] = {'ap': '0.95 1.05 5', 'at': '0.9 1.1 3'}
+    scan = BatchedAnalysis(chi2_batch, _sample(names, [1.01, 0.99, -0.11], [0.05, 0.05, 0.02]), cfg, verbose=False)
+    results = scan.chi2_scan()
+    assert len(results) == 15 and scan.converged.all()
+    assert batches[0] == 15 * stencil_size(1, hessian=True)       # one free parameter per grid point
+    k = 0
+    for ap in np.linspace(0.95, 1.05, 5):            # the reference's loop order: first parameter outermost
+        for at in np.linspace(0.9, 1.1, 3):
+            r = results[k]
+            k += 1
+            assert r['ap'] == ap and r['at'] == at
+            d2 = np.array([ap, at]) - truth[:2]
+            bias = truth[2] - icov[2, :2].dot(d2) / icov[2, 2]            # profile over the free parameter
+            d = np.array([ap, at, bias]) - truth
+            # converged to the EDM tolerance (1e-5): << 1e-3 sigma on the parameter
+            assert abs(r['bias'] - bias) < 1e-3 * sig[2] and abs(r['fval'] - (d.dot(icov).dot(d) + 3.)) < 1e-4
+    cfg['chi2 scan'] = {'ap': '0.9 1 2', 'at': '0.9 1 2', 'bias': '-1 0 2'}
+    with pytest.raises(ValueError):
+        scan.chi2_scan()
+
+
 class _StubVega:
     def __init__(self):
         self.sample_params = _sample(['a', 'b'], [0.5, 2.0], [0.1, 0.1], {'a': (0., 1.), 'b': (1., 5.)})
@@ -192,3 +232,31 @@ def test_monte_carlo_fits_in_lock_step():
     sigma = np.maximum(res['errors'][1:3], 1e-30)
     assert np.all(np.abs(part['theta'] - res['theta'][1:3]) <= 1e-4 * sigma + 1e-12)
     vega.monte_carlo = False
+
+
+@pytest.mark.gpu
+def test_chi2_scan_on_the_device_path():
+    """vega.analysis.chi2_scan(): every grid point is a constrained best fit of the device chi2."""
+    from vega_b200 import VegaInterface
+    vega = VegaInterface('configs/configs/main.ini')
+    names = list(vega.sample_params['limits'])
+    assert 'ap' in names
+    vega.main_config['chi2 scan'] = {'ap': '0.97 1.03 3'}
+    results = vega.analysis.chi2_scan()
+    assert [r['ap'] for r in results] == list(np.linspace(0.97, 1.03, 3))
+    assert vega.analysis.converged.all()
+    start = np.array([vega.sample_params['values'][n] for n in names])
+    for r in results:
+        best = np.array([r[n] for n in names])
+        at_start = start.copy()
+        at_start[names.index('ap')] = r['ap']
+        f_best, f_start = vega.chi2_batch(np.array([best, at_start]), names)
+        assert abs(f_best - r['fval']) <= 1e-6 * max(1.0, abs(f_best)) and f_best <= f_start + 1e-9
+        # stationary in a free parameter
+        j = next(i for i, n in enumerate(names) if n != 'ap' and not vega.sample_params['fix'][n])
+        h = 1e-3 * abs(best[j]) + 1e-6
+        up, dn = best.copy(), best.copy()
+        up[j] += h
+        dn[j] -= h
+        f_up, f_dn = vega.chi2_batch(np.array([up, dn]), names)
+        assert f_up >= f_best - 1e-7 and f_dn >= f_best - 1e-7

@@ -454,3 +454,64 @@ class MonteCarloFits:
                 errs[m, res['free']] = np.nan
         res.update(names=self.names, errors=errs, mock_ids=ids)
         return res
+
+
+class BatchedAnalysis:
+    """`Analysis.chi2_scan` (vega/analysis.py:53-124) with every grid point fitted at once.
+
+    The reference minimises once per grid point of the one or two scanned parameters, those
+    parameters fixed at the grid value.  The fits are independent, so here they are the M
+    problems of one newton_lockstep call: each Newton iteration is one batched chi2 call of
+    (active grid points) x (2F^2 + 1) vectors.  Returns the reference's list of dictionaries
+    (best-fit values of every sampled parameter + 'fval'), in the reference's loop order."""
+
+    def __init__(self, chi2_batch, sample_params, main_config, max_iter=50, edm_tol=1e-5, verbose=True):
+        self._chi2_batch = chi2_batch
+        self._sample_params = sample_params
+        self.config = main_config
+        self._names = list(sample_params['limits'].keys())
+        self.max_iter, self.edm_tol, self.verbose = max_iter, edm_tol, verbose
+        self.grids = {}
+        self.scan_results = None
+
+    @classmethod
+    def from_vega(cls, vega, **kw):
+        names = list(vega.sample_params['limits'].keys())
+        return cls(lambda theta: vega.chi2_batch(theta, names), vega.sample_params, vega.main_config, **kw)
+
+    def chi2_scan(self):
+        if 'chi2 scan' not in self.config:
+            raise ValueError('Called chi2_scan, but no config specified in'
+                             ' main.ini. Add a "[chi2 scan]" section to main.')
+        self.grids = {}
+        for param, value in self.config.items('chi2 scan'):
+            start, end, num = value.split()[:3]
+            self.grids[param] = np.linspace(float(start), float(end), int(num))
+        if len(self.grids) > 2:
+            raise ValueError('chi2_scan only supports one/two parameter scans')
+        for param in self.grids:
+            if param not in self._names:
+                raise ValueError(f'chi2 scan parameter {param} is not in [sample].')
+        sp, names = self._sample_params, self._names
+        start = np.array([sp['values'][n] for n in names], dtype=np.float64)
+        errors = np.array([sp['errors'][n] for n in names], dtype=np.float64)
+        lower = np.array([np.nan if sp['limits'][n][0] is None else sp['limits'][n][0] for n in names])
+        upper = np.array([np.nan if sp['limits'][n][1] is None else sp['limits'][n][1] for n in names])
+        free = np.array([not sp['fix'][n] and n not in self.grids for n in names])
+        mesh = np.meshgrid(*self.grids.values(), indexing='ij')       # first parameter outermost
+        points = np.stack([m.ravel() for m in mesh], axis=1)
+        theta0 = np.tile(start, (points.shape[0], 1))
+        for j, param in enumerate(self.grids):
+            theta0[:, names.index(param)] = points[:, j]
+        res = newton_lockstep(lambda theta, prob: self._chi2_batch(theta), theta0, errors, lower, upper,
+                              free=free, max_iter=self.max_iter, edm_tol=self.edm_tol)
+        self.scan_results = []
+        for m in range(points.shape[0]):
+            result = {n: float(res['theta'][m, j]) for j, n in enumerate(names)}
+            result['fval'] = float(res['fval'][m])
+            self.scan_results.append(result)
+        self.converged = res['converged']
+        if self.verbose:
+            print('INFO: chi2 scan of {} points in {} batched chi2 evaluations, {} converged'.format(
+                points.shape[0], res['n_eval'], int(np.sum(res['converged']))))
+        return self.scan_results

@@ -121,7 +121,7 @@ class VegaInterface:
         # the reference's per-correlation Model objects (vega/vega_interface.py:136-139)
         from .model import Model
         self.models = {name: Model(self, name) for name in self.corr_items}
-        self.analysis = None
+        self._analysis = None
         self.output = None
         self.plots = None
 
@@ -373,6 +373,14 @@ class VegaInterface:
         for prior in self.priors.values():
             log_norm += self._gaussian_lik_prior(prior[1])
         return log_norm
+
+    @property
+    def analysis(self):
+        """vega/vega_interface.py:139-142: the Analysis object (here: the batched chi2 scan)."""
+        if self._analysis is None:
+            from .drivers import BatchedAnalysis
+            self._analysis = BatchedAnalysis.from_vega(self, verbose=False)
+        return self._analysis
 
     def minimize(self):
         """Best fit over the [sample] parameters (vega/vega_interface.py:581-644) with the batched
