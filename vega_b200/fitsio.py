@@ -130,6 +130,10 @@ def _read_header(buf, pos):
             if key == 'END':
                 finished = True
                 break
+            if key == 'HIERARCH' and '=' in card:
+                name, _, value = card[9:].partition('=')
+                header[name.strip()] = _parse_value(value)
+                continue
             if key in ('', 'COMMENT', 'HISTORY') or card[8:10] != '= ':
                 continue
             header[key] = _parse_value(card[10:])
@@ -210,7 +214,21 @@ def open(path, *args, **kwargs):  # noqa: A001 - mirrors astropy.io.fits.open
 # Writer (used to produce synthetic DESI/eBOSS-shaped inputs and fixtures)
 # ----------------------------------------------------------------------------
 def _card(key, value, comment=''):
-    if isinstance(value, bool):
+    key = str(key)
+    if key.lower().startswith('hierarch '):
+        key = key[9:]
+    if len(key) > 8 or not all(ch.isupper() or ch.isdigit() or ch in '-_' for ch in key):
+        # ESO HIERARCH convention for long / mixed-case keywords (what astropy writes for them)
+        if isinstance(value, (bool, np.bool_)):
+            val = 'T' if value else 'F'
+        elif isinstance(value, (int, np.integer)):
+            val = str(int(value))
+        elif isinstance(value, (float, np.floating)):
+            val = repr(float(value))
+        else:
+            val = "'" + str(value).replace("'", "''") + "'"
+        return f'HIERARCH {key} = {val}'[:80].ljust(80)
+    if isinstance(value, (bool, np.bool_)):
         val = 'T' if value else 'F'
         text = f'{key:<8}= {val:>20}'
     elif isinstance(value, (int, np.integer)):
@@ -247,7 +265,12 @@ def _table_bytes(columns, extname, extra_header):
         elif arr.dtype.kind in 'iu':
             code, dt = 'K', '>i8'
         elif arr.dtype.kind == 'b':
-            code, dt = 'K', '>i8'
+            code, dt = 'L', 'S1'
+        elif arr.dtype.kind in 'US':
+            width = max(1, max((len(str(x)) for x in arr.ravel()), default=1))
+            tforms.append(f'{width}A')
+            fields.append((name, f'S{width}'))
+            continue
         else:
             raise TypeError(f'Unsupported column dtype {arr.dtype}')
         tforms.append(f'{repeat}{code}' if repeat > 1 else code)
@@ -256,6 +279,10 @@ def _table_bytes(columns, extname, extra_header):
     table = np.zeros(nrows, dtype=dtype)
     for name in names:
         arr = np.asarray(columns[name])
+        if arr.dtype.kind == 'b':
+            arr = np.where(arr, b'T', b'F')
+        elif arr.dtype.kind == 'U':
+            arr = np.char.encode(arr, 'ascii')
         table[name] = arr.reshape(nrows, -1) if arr.ndim > 1 else arr
 
     cards = [

@@ -1,0 +1,127 @@
+"""Result files in the reference's FITS layout (vega/output.py:13-350): one `MODEL_<name>` table
+per correlation (model, masks, data, variance, coordinates; every parameter and the per-
+correlation fit statistics as header cards), `BESTFIT` (names, values, errors, covariance;
+FVAL / VALID / ACCURATE) and `SCAN` (one column per sampled parameter + fval, grid description
+in the header).  Written with the package's own FITS writer (astropy is not in the image).
+
+Not written: the HDF variant and the `write_pk` / `write_cf` component tables (the per-stage
+components are available from `VegaInterface.models[name].pk / pk_ells / xi`).
+"""
+import os
+from pathlib import Path
+
+import numpy as np
+
+from . import fitsio
+
+
+def _pad(array, size, value=np.nan):
+    array = np.asarray(array)
+    return np.pad(array, (0, size - len(array)), constant_values=value)
+
+
+class Output:
+    def __init__(self, config, data, corr_items, analysis=None):
+        self.data = data
+        self.analysis = analysis
+        self.corr_items = corr_items
+        self.type = config.get('type', 'fits')
+        self.overwrite = config.getboolean('overwrite', False) if hasattr(config, 'getboolean') \
+            else bool(config.get('overwrite', False))
+        self.outfile = os.path.expandvars(config['filename'])
+        self.output_cf = config.getboolean('write_cf', False) if hasattr(config, 'getboolean') else False
+        self.output_pk = config.getboolean('write_pk', False) if hasattr(config, 'getboolean') else False
+
+    # vega/output.py:37-123
+    def write_results(self, corr_funcs, params, minimizer=None, bestfit_corr_stats=None,
+                      scan_results=None, models=None):
+        if self.type != 'fits':
+            raise NotImplementedError('Only type = fits is written by this package.')
+        if self.output_pk or self.output_cf:
+            raise NotImplementedError('write_pk / write_cf tables are not written; use '
+                                      'VegaInterface.models[name].pk / pk_ells / xi.')
+        if self.data is None:
+            raise ValueError('Output object was initialized with an invalid data object.'
+                             ' Reinitialize with a valid vega.data object.')
+        tables = self._model_tables(corr_funcs, params, bestfit_corr_stats)
+        if minimizer is not None:
+            tables.append(self._bestfit_table(minimizer))
+        if scan_results is not None:
+            assert minimizer is not None
+            tables.append(self._scan_table(scan_results))
+        if self.outfile[-5:] != '.fits':
+            self.outfile += '.fits'
+        path = Path(self.outfile)
+        if path.exists() and not self.overwrite:
+            raise OSError(f"File {path} already exists. Set overwrite = True in [output] to replace it.")
+        fitsio.write_tables(path, tables)
+        return path
+
+    # vega/output.py:144-235
+    def _model_tables(self, corr_funcs, params, bestfit_corr_stats=None):
+        tables = []
+        for name, cf in corr_funcs.items():
+            data, item = self.data[name], self.corr_items[name]
+            n = len(cf)
+            if len(data.data_vec) > n:
+                raise ValueError('Data coordinate grid is larger than the model grid.')
+            columns = {
+                name + '_MODEL': _pad(cf, n),
+                name + '_MODEL_MASK': _pad(data.model_mask, n, False),
+                name + '_MASK': _pad(data.data_mask, n, False),
+                name + '_DATA': _pad(data.data_vec, n),
+                name + '_VAR': _pad(data.variance, n),
+                name + '_RP': _pad(item.dist_model_coordinates.rp_grid, n),
+                name + '_RT': _pad(item.dist_model_coordinates.rt_grid, n),
+            }
+            z = np.broadcast_to(np.asarray(item.model_coordinates.z_grid, dtype=float),
+                                item.model_coordinates.rp_grid.shape)
+            columns[name + '_Z'] = np.zeros(n) if n < z.size else _pad(z, n)
+            if data.nb is not None:
+                columns[name + '_NB'] = _pad(np.asarray(data.nb, dtype=np.int64), n, 0)
+            header = {}
+            for par, val in params.items():
+                header['hierarch ' + par] = val
+            if bestfit_corr_stats is not None:
+                for par, val in bestfit_corr_stats[name].items():
+                    if par == 'bestfit_marg_coeff':
+                        for i, v in enumerate(val if val is not None else []):
+                            header[f'hierarch marg_coeff_{i}'] = float(v)
+                    else:
+                        header['hierarch ' + par] = val
+            tables.append(('MODEL_' + name, header, columns))
+        return tables
+
+    # vega/output.py:237-289
+    def _bestfit_table(self, minimizer):
+        names = np.array(list(minimizer.values.keys()))
+        columns = {
+            'names': names,
+            'values': np.array([minimizer.values[n] for n in names], dtype=float),
+            'errors': np.array([minimizer.errors[n] for n in names], dtype=float),
+            'covariance': np.array(minimizer.covariance, dtype=float).reshape(len(names), len(names)),
+        }
+        valid = bool(minimizer.fmin.is_valid)
+        header = {'FVAL': float(minimizer.fmin.fval), 'VALID': valid,
+                  'ACCURATE': bool(getattr(minimizer.fmin, 'has_accurate_covar', valid))}
+        return ('BESTFIT', header, columns)
+
+    # vega/output.py:291-349
+    def _scan_table(self, scan_results):
+        names = list(scan_results[0].keys())
+        results = np.array([[res[par] for par in names] for res in scan_results], dtype=float)
+        columns = {'names': np.array(names)}
+        if len(names) != results.shape[0]:
+            # a FITS table needs equal-length columns: the name column is padded / cut to the
+            # number of grid points, the full list is also in the header
+            padded = (names + [''] * results.shape[0])[:results.shape[0]]
+            columns['names'] = np.array(padded)
+        for col, name in zip(results.T, names):
+            columns[name] = col
+        header = {f'hierarch name_{i}': n for i, n in enumerate(names)}
+        if self.analysis is not None and getattr(self.analysis, 'grids', None):
+            for par, grid in self.analysis.grids.items():
+                header[f'hierarch {par}_min'] = float(grid[0])
+                header[f'hierarch {par}_max'] = float(grid[-1])
+                header[f'hierarch {par}_num_bins'] = int(len(grid))
+        return ('SCAN', header, columns)

@@ -122,7 +122,7 @@ class VegaInterface:
         from .model import Model
         self.models = {name: Model(self, name) for name in self.corr_items}
         self._analysis = None
-        self.output = None
+        self._output = None
         self.plots = None
 
         self._device = device
@@ -373,6 +373,15 @@ class VegaInterface:
         for prior in self.priors.values():
             log_norm += self._gaussian_lik_prior(prior[1])
         return log_norm
+
+    @property
+    def output(self):
+        """vega/vega_interface.py:144-146: the Output object (FITS result files)."""
+        if self._output is None:
+            from .output import Output
+            self._output = Output(self.main_config['output'], self.data, self.corr_items, self._analysis)
+        self._output.analysis = self._analysis
+        return self._output
 
     @property
     def analysis(self):
