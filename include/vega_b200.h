@@ -231,6 +231,13 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
  * P(k) given to vg_plan_set_direct_pk, no peak/smooth split, no bao_amp, and (as in the
  * reference with no-metal-decomp) no metal terms. */
 #define VG_OPT_DIRECT_PK 1
+/* VG_OPT_FOLD_METALS (default 0): metal evaluations whose xi stage is in moment form
+ * (vg_eval_desc::static_xi) are a 3/9-term combination of static vectors X_m, so their matrix
+ * product M_c xi_c (vega/metals.py:350-358) is the same combination of Y_m = M_c X_m.  1 builds
+ * nothing new (the Y_m are made at finalize either way) but takes those terms out of the gather
+ * and out of the per-vector matrix product; same result to rounding (summation order).  Needs
+ * VG_OPT_MOMENTS.  The bench headline keeps it off: every matrix applied per vector. */
+#define VG_OPT_FOLD_METALS 2
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
 /* Isotropic P(k) [nk] for the direct mode (e.g. from a Boltzmann code, the `direct_pk`
  * argument of VegaInterface.compute_model / chi2 / log_lik); host pointer, copied. */
@@ -241,6 +248,8 @@ int vg_corr_n_moment(const vg_plan* plan, int32_t corr);
 /* Evaluations of the correlation whose xi stage (vega/correlation_func.py:117-236) is in moment
  * form too (vg_eval_desc::static_xi): read-out of static per-bin tables, no gather. */
 int vg_corr_n_static_xi(const vg_plan* plan, int32_t corr);
+/* Metal evaluations VG_OPT_FOLD_METALS = 1 serves from static vectors (after finalize). */
+int vg_corr_n_folded(const vg_plan* plan, int32_t corr);
 /* Status bits raised while building the static grids (e.g. VG_STATUS_ARINYO): they apply
  * to every vector */
 int vg_plan_static_status(const vg_plan* plan);

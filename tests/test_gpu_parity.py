@@ -140,6 +140,49 @@ def test_moment_form_matches_per_point_pass():
     assert_xi_close({n: models_mom[n][0] for n in ref}, ref, 'moment form')
 
 
+@pytest.mark.parametrize('case', ['c2_dense', 'c2_fast_metals', 'rp_only'])
+def test_folded_metals_match_the_matrix_product(case, tmp_path):
+    """VG_OPT_FOLD_METALS: metal terms whose xi stage is in moment form are served from static
+    vectors Y_m = M_c X_m instead of the per-vector matrix product (vega/metals.py:350-358).
+    Same model and chi2 as with the option off, and as the oracle."""
+    from vega_b200 import _lib
+    if case == 'rp_only':
+        from helpers import make_new_metals_config
+        from oracle.vega_oracle import Oracle
+        from helpers import static_tables
+        from vega_b200 import VegaInterface
+        vega = VegaInterface(make_new_metals_config(tmp_path, True))
+        oracle = Oracle(vega, tables=static_tables())
+        names = ['bias_eta_LYA', 'beta_LYA', 'ap', 'at', 'bias_eta_SiII(1260)', 'bias_eta_SiIII(1207)']
+        names = [n for n in names if n in vega.params]
+        rng = np.random.default_rng(11)
+        base = np.array([vega.params[n] for n in names])
+        theta = base * (1 + 0.02 * rng.standard_normal((9, len(names))))
+    else:
+        vega, oracle, theta = make_c2(9, width=0.5, fast_metals=case == 'c2_fast_metals')
+        names = list(vega.sample_params['limits'])
+        if case == 'c2_fast_metals':
+            oracle.compute_model()
+    engine = vega._engine_for(names)
+    n_folded = sum(engine.n_folded(ci) for ci in range(len(engine.infos)))
+    assert n_folded > 0
+    chi2_off = vega.chi2_batch(theta, names)
+    models_off, _ = vega.compute_model_batch(theta, names)
+    engine.set_option(_lib.OPT_FOLD_METALS, 1)
+    try:
+        chi2_on = vega.chi2_batch(theta, names)
+        models_on, status = vega.compute_model_batch(theta, names)
+    finally:
+        engine.set_option(_lib.OPT_FOLD_METALS, 0)
+    assert not status.any()
+    for name in models_off:
+        scale = np.max(np.abs(models_off[name]))
+        assert np.max(np.abs(models_on[name] - models_off[name])) <= 1e-12 * scale, name
+    assert np.max(np.abs(chi2_on - chi2_off) / np.maximum(1.0, np.abs(chi2_off) / 1e4)) <= CHI2_ATOL
+    ref = oracle.compute_model(dict(zip(names, theta[0])))
+    assert_xi_close({n: models_on[n][0] for n in ref}, ref, 'folded metals')
+
+
 def test_c2_fast_metals_matches_oracle():
     """fast_metals on the dense C2 operands: frozen metal x metal vectors (M_c xi_c evaluated
     once at the plan parameters through the same kernels), shared metal x main tables."""

@@ -13,7 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / 'libvega_b200.so'
 VG_MAX_BB_TERMS = 8
 F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP, F_MOCKGK = (1 << i for i in range(9))
 STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE = 1, 2, 4
-OPT_MOMENTS, OPT_DIRECT_PK = 0, 1
+OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS = 0, 1, 2
 
 i32, u32, f64 = C.c_int32, C.c_uint32, C.c_double
 
@@ -85,6 +85,7 @@ _SIGNATURES = {
     'vg_plan_set_option': (C.c_int, [_PTR, i32, i32]),
     'vg_corr_n_moment': (C.c_int, [_PTR, i32]),
     'vg_corr_n_static_xi': (C.c_int, [_PTR, i32]),
+    'vg_corr_n_folded': (C.c_int, [_PTR, i32]),
     'vg_plan_set_direct_pk': (C.c_int, [_PTR, _PTR]),
     'vg_plan_set_fvoigt': (C.c_int, [_PTR, i32, _PTR, _PTR]),
     'vg_plan_set_uvshot_table': (C.c_int, [_PTR, i32, _PTR, _PTR]),

@@ -110,12 +110,17 @@ struct EvalLayout {
   std::vector<int> mxi_ids;      // LAY_MOM: evaluations whose xi stage is in moment form (static_xi)
   std::vector<int> mxi_owner;    //          evaluation whose moment tables each of them reads
   DevBuf d_mxi_ids, d_mxi_owner;
+  // LAY_FOLD: row of each mxi evaluation in LAY_MOM's d_mxi_tab; metal evaluations folded into
+  // static vectors (fold_rows = their rows in d_mxi_tab)
+  std::vector<int> mxi_rows, fold_ids, fold_owner, fold_rows;
+  DevBuf d_mxi_rows, d_fold_ids, d_fold_owner;
   int n_full = 0;                // evaluations that go through pk_ell + the Hankel GEMM
   int n_metal = 0;               // metal column blocks of xmet / mcat
   std::vector<int> metal_map;    // metal slot -> column block (-1: not in this layout)
   DevBuf d_mom_ids, d_gather_ids, d_slot, d_tabslot, d_metal_map;
 };
-enum { LAY_MOM = 0, LAY_FULL = 1, LAY_ALL = 2, LAY_DIRECT = 3 };
+enum { LAY_MOM = 0, LAY_FULL = 1, LAY_ALL = 2, LAY_DIRECT = 3, LAY_FOLD = 4, LAY_COUNT = 5 };
+constexpr int FOLD_MAX = 64;   // folded metal terms per correlation (shared-memory coefficient table)
 
 struct Corr {
   int hankel_id = 0, n_model = 0, n_dist = 0, ld_model = 0, ld_dist = 0;
@@ -127,8 +132,10 @@ struct Corr {
   //   LAY_ALL  per-stage taps and the finalize pass of the frozen terms: every evaluation
   //            incl. the frozen ones, per point, identity slots;
   //   LAY_DIRECT  Model.compute_direct: only the evaluations flagged `direct`, per point.
+  //   LAY_FOLD  LAY_MOM with VG_OPT_FOLD_METALS: metal evaluations whose xi stage is in moment
+  //            form leave the gather and the matrix product (static vectors Y = M_c X instead).
   // Evaluations with table_owner >= 0 never own tables; frozen ones leave the hot layouts.
-  EvalLayout lay[4];
+  EvalLayout lay[LAY_COUNT];
   DevBuf d_mom_ktab;             // LAY_MOM: [n_mom][9][n_ell][2*n_out_pad]
   DevBuf d_mxi_tab;              // LAY_MOM: [n_mxi][9][ld_model] xi stage applied to the moment tables
   bool allow_mxi = true;         // cleared when the plan-time gather of the static tables fails
@@ -146,6 +153,8 @@ struct Corr {
   std::vector<int> frozen_ids;   // frozen evaluations, in order of d_frozen rows
   DevBuf d_frozen_ids, d_frozen; // d_frozen [n_frozen][ld_model] = weight_const * M_c xi_c
   DevBuf d_mcat;                 // hot metal matrices [n_model][n_metal_hot*ld_model]
+  DevBuf d_fold_tab;             // LAY_FOLD: [n_fold][9][ld_model] Y[f][m] = M_c X[row(f)][m]
+  DevBuf d_mcat_fold, d_mrp_fold;   // LAY_FOLD: matrices of the metal terms that stay in the product
   bool has_dmat = false;
   DevBuf d_dmat;                 // [n_dist][ld_model]
   DevBuf d_dmat_masked;          // [n_mask][ld_model]
@@ -180,6 +189,7 @@ struct vg_plan {
   bool finalized = false;
   bool use_moments = true;
   bool direct_mode = false;      // VG_OPT_DIRECT_PK
+  bool fold_metals = false;      // VG_OPT_FOLD_METALS
   int static_bad = 0;
   int std_ells = 0;
   // global covariance
@@ -187,7 +197,7 @@ struct vg_plan {
   DevBuf d_global_invcov;
   // workspace (sized for `chunk` vectors)
   long long chunk = 0, chunk_max = 1024;
-  DevBuf w_pfull, w_pkell, w_tables, w_core, w_xmet, w_met, w_x, w_y, w_diff, w_partial, w_split,
+  DevBuf w_pfull, w_pkell, w_tables, w_core, w_xmet, w_met, w_x, w_y, w_diff, w_partial, w_split, w_fold,
       w_chi2, w_status, w_theta;
   void* pinned = nullptr; size_t pinned_bytes = 0;
   // optional per-stage timing with CUDA events (bench.py roofline figures)
@@ -231,6 +241,7 @@ struct ProfScope {
 int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, long long ldb,
               double* C, long long ldc, int M, int N, int K, int batch, long long strideA,
               long long strideB, long long strideC, cudaStream_t st);
+int build_metal_operands(Corr& c, const EvalLayout& L, DevBuf& mcat, DevBuf& mrp);
 int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st);
@@ -339,11 +350,13 @@ int build_layouts(vg_plan* plan, Corr& c) {
   for (int e = 0; e < E; ++e)
     if (c.evals[e].frozen && !c.evals[e].direct) c.frozen_ids.push_back(e);
   if (!c.frozen_ids.empty()) VG_TRY(upload(c.d_frozen_ids, c.frozen_ids.data(), c.frozen_ids.size()));
-  for (int li = 0; li < 4; ++li) {
+  for (int li = 0; li < LAY_COUNT; ++li) {
     EvalLayout& L = c.lay[li];
+    const bool momlike = li == LAY_MOM || li == LAY_FOLD;
     for (auto& ids : L.class_ids) ids.clear();
     for (int m = 0; m < 23; ++m) { L.pair_ids[m].clear(); L.pair_twins[m].clear(); L.n_single[m] = 0; }
     L.mom_ids.clear(); L.gather_ids.clear(); L.mxi_ids.clear(); L.mxi_owner.clear();
+    L.mxi_rows.clear(); L.fold_ids.clear(); L.fold_owner.clear(); L.fold_rows.clear();
     L.n_full = 0; L.n_metal = 0;
     L.metal_map.assign(std::max(c.n_metal, 1), -1);
     std::vector<int> slot(E, 0), tabslot(E, 0);
@@ -352,15 +365,27 @@ int build_layouts(vg_plan* plan, Corr& c) {
       const bool hot = li == LAY_DIRECT ? d.direct != 0 : (!d.direct && (li == LAY_ALL || !d.frozen));
       if (!hot) continue;
       const int owner = d.table_owner >= 0 ? d.table_owner : e;
-      if (li == LAY_MOM && c.allow_mxi && d.static_xi && vg::moment_eligible(c.evals[owner])) {
-        L.mxi_ids.push_back(e);
-        L.mxi_owner.push_back(owner);
+      bool folded = false;
+      if (momlike && c.allow_mxi && d.static_xi && vg::moment_eligible(c.evals[owner])) {
+        int row = -1;
+        if (li == LAY_FOLD) {
+          const std::vector<int>& base_ids = c.lay[LAY_MOM].mxi_ids;
+          row = (int)(std::find(base_ids.begin(), base_ids.end(), e) - base_ids.begin());
+        }
+        if (li == LAY_FOLD && d.out_slot >= 2 && (int)L.fold_ids.size() < FOLD_MAX) {
+          folded = true;
+          L.fold_ids.push_back(e); L.fold_owner.push_back(owner); L.fold_rows.push_back(row);
+        } else {
+          L.mxi_ids.push_back(e);
+          L.mxi_owner.push_back(owner);
+          if (li == LAY_FOLD) L.mxi_rows.push_back(row);
+        }
       } else {
         L.gather_ids.push_back(e);
       }
-      if (d.out_slot >= 2) L.metal_map[d.out_slot - 2] = L.n_metal++;
+      if (d.out_slot >= 2 && !folded) L.metal_map[d.out_slot - 2] = L.n_metal++;
       if (d.table_owner >= 0) continue;
-      if (li == LAY_MOM && vg::moment_eligible(d)) {
+      if (momlike && vg::moment_eligible(d)) {
         tabslot[e] = -((int)L.mom_ids.size() + 1);
         L.mom_ids.push_back(e);
       } else {
@@ -401,6 +426,11 @@ int build_layouts(vg_plan* plan, Corr& c) {
     if (!L.mxi_ids.empty()) {
       VG_TRY(upload(L.d_mxi_ids, L.mxi_ids.data(), L.mxi_ids.size()));
       VG_TRY(upload(L.d_mxi_owner, L.mxi_owner.data(), L.mxi_owner.size()));
+      if (!L.mxi_rows.empty()) VG_TRY(upload(L.d_mxi_rows, L.mxi_rows.data(), L.mxi_rows.size()));
+    }
+    if (!L.fold_ids.empty()) {
+      VG_TRY(upload(L.d_fold_ids, L.fold_ids.data(), L.fold_ids.size()));
+      VG_TRY(upload(L.d_fold_owner, L.fold_owner.data(), L.fold_owner.size()));
     }
     VG_TRY(upload(L.d_slot, slot.data(), slot.size()));
     VG_TRY(upload(L.d_tabslot, tabslot.data(), tabslot.size()));
@@ -471,6 +501,7 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk) {
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
   VG_REQUIRE(plan, "null plan");
   if (option == VG_OPT_MOMENTS) { plan->use_moments = value != 0; return VG_OK; }
+  if (option == VG_OPT_FOLD_METALS) { plan->fold_metals = value != 0; return VG_OK; }
   if (option == VG_OPT_DIRECT_PK) {
     if (value) {
       bool any = false;
@@ -793,41 +824,32 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
       }
     }
     VG_REQUIRE(!(c.metal_rp && c.metal_dense), "a correlation mixes dense and rp-only metal matrices");
-    if (c.metal_rp && LM.n_metal > 0) {   // rp-only matrices of the hot evaluations, column-block order
-      const size_t nn = (size_t)c.rp_np * c.rp_np;
-      std::vector<double> host((size_t)LM.n_metal * nn, 0.0);
-      for (int s = 0; s < c.n_metal; ++s) {
-        const int col = LM.metal_map[s];
-        if (col < 0) continue;
-        double* dst = host.data() + (size_t)col * nn;
-        if (s < (int)c.metal_rp_host.size() && !c.metal_rp_host[s].empty())
-          std::copy(c.metal_rp_host[s].begin(), c.metal_rp_host[s].end(), dst);
-        else
-          for (int i = 0; i < c.rp_np; ++i) dst[(size_t)i * c.rp_np + i] = 1.0;
-      }
-      VG_TRY(upload(c.d_mrp, host.data(), host.size()));
-    }
-    // metal matrices of the hot evaluations, concatenated along K: mcat[i][c*ld_model + j] = M_c[i][j]
-    if (c.metal_dense && LM.n_metal > 0) {
-      const size_t ldk = (size_t)LM.n_metal * c.ld_model;
-      VG_TRY(c.d_mcat.alloc((size_t)c.n_model * ldk * 8));
-      std::vector<double> eye;
-      for (int s = 0; s < c.n_metal; ++s) {
-        const int col = LM.metal_map[s];
-        if (col < 0) continue;
-        const double* src;
-        if (s < (int)c.metal_host.size() && !c.metal_host[s].empty()) {
-          src = c.metal_host[s].data();
-        } else {
-          if (eye.empty()) {
-            eye.assign((size_t)c.n_model * c.n_model, 0.0);
-            for (int i = 0; i < c.n_model; ++i) eye[(size_t)i * c.n_model + i] = 1.0;
+    VG_TRY(build_metal_operands(c, LM, c.d_mcat, c.d_mrp));
+    // folded metal terms: Y[f][m] = M_c X[row(f)][m], and the matrices of the terms that stay
+    {
+      const EvalLayout& LF = c.lay[LAY_FOLD];
+      const int nf = (int)LF.fold_ids.size();
+      if (nf > 0) {
+        const size_t blk = (size_t)vg::MOM_MAX * c.ld_model;
+        VG_TRY(c.d_fold_tab.alloc((size_t)nf * blk * 8));
+        DevBuf mat;
+        for (int f = 0; f < nf; ++f) {
+          const int slot = c.evals[LF.fold_ids[f]].out_slot - 2;
+          const double* src = c.d_mxi_tab.as<double>() + (size_t)LF.fold_rows[f] * blk;
+          double* dst = c.d_fold_tab.as<double>() + (size_t)f * blk;
+          if (c.metal_rp && slot < (int)c.metal_rp_host.size() && !c.metal_rp_host[slot].empty()) {
+            VG_TRY(upload(mat, c.metal_rp_host[slot].data(), c.metal_rp_host[slot].size()));
+            VG_TRY(launch_metal_rp(c, src, 1, mat.as<double>(), vg::MOM_MAX, dst, st));
+          } else if (c.metal_dense && slot < (int)c.metal_host.size() && !c.metal_host[slot].empty()) {
+            VG_TRY(upload_padded(mat, c.metal_host[slot].data(), c.n_model, c.n_model, c.ld_model));
+            VG_TRY(gemm_auto(plan, src, c.ld_model, mat.as<double>(), c.ld_model, dst, c.ld_model,
+                             vg::MOM_MAX, c.n_model, c.ld_model, 1, 0, 0, 0, st));
+          } else {
+            VG_CUDA_CHECK(cudaMemcpyAsync(dst, src, blk * 8, cudaMemcpyDeviceToDevice, st));
           }
-          src = eye.data();
+          VG_CUDA_CHECK(cudaStreamSynchronize(st));   // `mat` is re-used by the next term
         }
-        VG_CUDA_CHECK(cudaMemcpy2D(c.d_mcat.as<double>() + (size_t)col * c.ld_model, ldk * 8, src,
-                                   (size_t)c.n_model * 8, (size_t)c.n_model * 8, c.n_model,
-                                   cudaMemcpyHostToDevice));
+        VG_TRY(build_metal_operands(c, LF, c.d_mcat_fold, c.d_mrp_fold));
       }
     }
     // masked rows of the distortion matrix (chi2 needs only the bins kept by the cuts)
@@ -862,7 +884,8 @@ int64_t vg_plan_device_bytes(const vg_plan* plan) {
   for (auto& h : plan->hankels) n += h->xk.bytes + h->op.bytes;
   for (auto& cp : plan->corrs) {
     const Corr& c = *cp;
-    n += c.d_mcat.bytes + c.d_dmat.bytes + c.d_dmat_masked.bytes + c.d_invcov.bytes + c.d_mom_ktab.bytes + c.d_frozen.bytes;
+    n += c.d_mcat.bytes + c.d_dmat.bytes + c.d_dmat_masked.bytes + c.d_invcov.bytes + c.d_mom_ktab.bytes + c.d_frozen.bytes +
+         c.d_mxi_tab.bytes + c.d_fold_tab.bytes + c.d_mcat_fold.bytes + c.d_mrp.bytes + c.d_mrp_fold.bytes;
     for (auto& b : c.coords) n += b.bytes;
   }
   n += plan->d_global_invcov.bytes;
@@ -948,6 +971,7 @@ int ensure_workspace(vg_plan* plan, long long Bc_) {
   VG_TRY(plan->w_core.alloc(core * 8));
   VG_TRY(plan->w_xmet.alloc(xmet * 8));
   VG_TRY(plan->w_met.alloc(met * 8));
+  VG_TRY(plan->w_fold.alloc(met * 8));
   VG_TRY(plan->w_x.alloc(met * 8));
   VG_TRY(plan->w_y.alloc(y * 8));
   VG_TRY(plan->w_diff.alloc(diff * 8));
@@ -1036,6 +1060,50 @@ int launch_pk_fast(int vmode, int kind, dim3 grid, dim3 block, size_t smem, cuda
 }
 #undef VG_PK_ARGS
 
+// Device operands of the metal product for one layout: rp-only blocks [n_metal][rp_np][rp_np] or
+// the dense matrices concatenated along K, mcat[i][col*ld_model + j] = M_c[i][j], both in the
+// layout's column-block order.
+int build_metal_operands(Corr& c, const EvalLayout& L, DevBuf& mcat, DevBuf& mrp) {
+  if (c.metal_rp && L.n_metal > 0) {   // rp-only matrices of the hot evaluations, column-block order
+    const size_t nn = (size_t)c.rp_np * c.rp_np;
+    std::vector<double> host((size_t)L.n_metal * nn, 0.0);
+    for (int s = 0; s < c.n_metal; ++s) {
+      const int col = L.metal_map[s];
+      if (col < 0) continue;
+      double* dst = host.data() + (size_t)col * nn;
+      if (s < (int)c.metal_rp_host.size() && !c.metal_rp_host[s].empty())
+        std::copy(c.metal_rp_host[s].begin(), c.metal_rp_host[s].end(), dst);
+      else
+        for (int i = 0; i < c.rp_np; ++i) dst[(size_t)i * c.rp_np + i] = 1.0;
+    }
+    VG_TRY(upload(mrp, host.data(), host.size()));
+  }
+  // metal matrices of the hot evaluations, concatenated along K: mcat[i][c*ld_model + j] = M_c[i][j]
+  if (c.metal_dense && L.n_metal > 0) {
+    const size_t ldk = (size_t)L.n_metal * c.ld_model;
+    VG_TRY(mcat.alloc((size_t)c.n_model * ldk * 8));
+    std::vector<double> eye;
+    for (int s = 0; s < c.n_metal; ++s) {
+      const int col = L.metal_map[s];
+      if (col < 0) continue;
+      const double* src;
+      if (s < (int)c.metal_host.size() && !c.metal_host[s].empty()) {
+        src = c.metal_host[s].data();
+      } else {
+        if (eye.empty()) {
+          eye.assign((size_t)c.n_model * c.n_model, 0.0);
+          for (int i = 0; i < c.n_model; ++i) eye[(size_t)i * c.n_model + i] = 1.0;
+        }
+        src = eye.data();
+      }
+      VG_CUDA_CHECK(cudaMemcpy2D(mcat.as<double>() + (size_t)col * c.ld_model, ldk * 8, src,
+                                 (size_t)c.n_model * 8, (size_t)c.n_model * 8, c.n_model,
+                                 cudaMemcpyHostToDevice));
+    }
+  }
+  return VG_OK;
+}
+
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st) {
   dim3 grid(vg_cdiv(c.rp_nt, vg::MRP_TN), vg_cdiv(c.rp_np, vg::MRP_TM), (unsigned)B);
@@ -1054,7 +1122,9 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   // the per-stage taps (upto <= 2) expose every evaluation's multipoles / knot tables, so
   // they run all evaluations through the per-point pass
   if (layout < 0)
-    layout = plan->direct_mode ? LAY_DIRECT : (upto <= 2 ? LAY_ALL : (plan->use_moments ? LAY_MOM : LAY_FULL));
+    layout = plan->direct_mode ? LAY_DIRECT : (upto <= 2 ? LAY_ALL
+                                                 : (plan->use_moments ? ((plan->fold_metals && upto > 3) ? LAY_FOLD : LAY_MOM)
+                                                                      : LAY_FULL));
   const bool direct = layout == LAY_DIRECT;
   const EvalLayout& L = c.lay[layout];
   const int Ef = L.n_full;
@@ -1149,7 +1219,8 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     dim3 grid(vg_cdiv(c.ld_model, 256), (unsigned)n_mxi, (unsigned)vg_cdiv(Bc, vg::MXI_NB));
     vg::moment_xi_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_mxi_ids.as<int>(),
                                               L.d_mxi_owner.as<int>(), plan->w_pfull.as<double>(), plan->npf,
-                                              (int)Bc, c.d_mxi_tab.as<double>(), c.ld_model,
+                                              (int)Bc, c.d_mxi_tab.as<double>(),
+                                              L.mxi_rows.empty() ? nullptr : L.d_mxi_rows.as<int>(), c.ld_model,
                                               plan->w_core.as<double>(), plan->w_xmet.as<double>(),
                                               L.d_metal_map.as<int>(), std::max(L.n_metal, 1));
     VG_LAUNCHED();
@@ -1157,14 +1228,29 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   if (upto <= 3) return VG_OK;
   // metals: sum_c w_c M_c xi_c  (vega/metals.py:258-367)
   const double* met = nullptr;
+  const double* met_fold = nullptr;
+  if (!L.fold_ids.empty()) {
+    ProfScope prof(plan, PROF_ELEM, st);
+    const int nf = (int)L.fold_ids.size();
+    const size_t smem = (size_t)nf * vg::MOM_MAX * vg::MXI_NB * 8 + (size_t)nf * sizeof(int);
+    dim3 grid(vg_cdiv(c.ld_model, 256), (unsigned)vg_cdiv(Bc, vg::MXI_NB));
+    vg::moment_fold_kernel<<<grid, 256, smem, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_fold_ids.as<int>(),
+                                                   L.d_fold_owner.as<int>(), nf, plan->w_pfull.as<double>(),
+                                                   plan->npf, (int)Bc, c.d_fold_tab.as<double>(), c.ld_model,
+                                                   plan->w_fold.as<double>());
+    VG_LAUNCHED();
+    met_fold = plan->w_fold.as<double>();
+  }
+  // a correlation with nothing folded keeps one set of matrices
+  const bool fold_layout = layout == LAY_FOLD && !L.fold_ids.empty();
   if (L.n_metal > 0) {
     ProfScope prof(plan, (c.metal_dense || c.metal_rp) ? PROF_METAL : PROF_ELEM, st);
     if (c.metal_rp) {
-      VG_TRY(launch_metal_rp(c, plan->w_xmet.as<double>(), L.n_metal, c.d_mrp.as<double>(), Bc,
-                             plan->w_met.as<double>(), st));
+      VG_TRY(launch_metal_rp(c, plan->w_xmet.as<double>(), L.n_metal,
+                             (fold_layout ? c.d_mrp_fold : c.d_mrp).as<double>(), Bc, plan->w_met.as<double>(), st));
     } else if (c.metal_dense) {
       const long long ldk = (long long)L.n_metal * c.ld_model;
-      VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, c.d_mcat.as<double>(), ldk,
+      VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, (fold_layout ? c.d_mcat_fold : c.d_mcat).as<double>(), ldk,
                        plan->w_met.as<double>(), c.ld_model, (int)Bc, c.n_model, (int)ldk, 1, 0, 0, 0, st));
     } else {
       const long long n = Bc * c.ld_model;
@@ -1175,7 +1261,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     met = plan->w_met.as<double>();
   }
   vg::CombineArgs ca{};
-  ca.core = plan->w_core.as<double>(); ca.met = met;
+  ca.core = plan->w_core.as<double>(); ca.met = met; ca.met_fold = met_fold;
   ca.inst = c.has_inst ? c.d_inst.as<double>() : nullptr;
   ca.idx_inst_amp = c.idx_inst_amp; ca.inst_amp_default = c.inst_amp_default;
   ca.idx_bao_amp = plan->idx_bao_amp;
@@ -1515,6 +1601,11 @@ int vg_metal_pair_histograms(const double* side1, int32_t n1, const double* side
 int vg_corr_n_static_xi(const vg_plan* plan, int32_t corr) {
   if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments) return 0;
   return (int)plan->corrs[corr]->lay[LAY_MOM].mxi_ids.size();
+}
+
+int vg_corr_n_folded(const vg_plan* plan, int32_t corr) {
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments) return 0;
+  return (int)plan->corrs[corr]->lay[LAY_FOLD].fold_ids.size();
 }
 
 int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }

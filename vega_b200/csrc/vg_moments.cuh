@@ -159,7 +159,8 @@ constexpr int MXI_NB = 8;
 __global__ void __launch_bounds__(256)
 moment_xi_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__ ids,
                  const int* __restrict__ owners, const double* __restrict__ pfull, int npf, int B,
-                 const double* __restrict__ X, int ld, double* __restrict__ core, double* __restrict__ xmet,
+                 const double* __restrict__ X, const int* __restrict__ rows, int ld,
+                 double* __restrict__ core, double* __restrict__ xmet,
                  const int* __restrict__ metal_map, int n_metal) {
   __shared__ double cq[MXI_NB][MOM_MAX];
   __shared__ int s_na, s_slot;
@@ -191,7 +192,7 @@ moment_xi_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__
   const int x = blockIdx.x * 256 + threadIdx.x;
   if (x >= ld) return;
   const int na = s_na;
-  const double* xt = X + (long long)j * MOM_MAX * ld + x;
+  const double* xt = X + (long long)(rows ? rows[j] : j) * MOM_MAX * ld + x;
   double acc[MXI_NB];
 #pragma unroll
   for (int e = 0; e < MXI_NB; ++e) acc[e] = 0.0;
@@ -211,6 +212,65 @@ moment_xi_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__
     double* out = slot < 2 ? core + ((long long)slot * B + b) * ld
                            : xmet + ((long long)b * n_metal + metal_map[slot - 2]) * ld;
     out[x] = acc[e];
+  }
+}
+
+// Folded metal terms (VG_OPT_FOLD_METALS): a metal evaluation whose xi stage is in moment
+// form is a 3/9-term combination of static vectors X[j][m], so its matrix product is the same
+// combination of Y[j][m] = M_c X[j][m], built once at finalize.  One pass sums them all:
+//   out[b][bin] = sum_j w_j(theta_b) sum_m c_m(theta_b; owner(j)) Y[j][m][bin]
+// grid = (ceil(ld / 256), ceil(B / MXI_NB)), block 256, dynamic smem n_ids*MXI_NB*MOM_MAX doubles
+// + n_ids ints.
+__global__ void __launch_bounds__(256)
+moment_fold_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__ ids,
+                   const int* __restrict__ owners, int n_ids, const double* __restrict__ pfull, int npf,
+                   int B, const double* __restrict__ Y, int ld, double* __restrict__ out) {
+  extern __shared__ double fold_smem[];
+  double* cq = fold_smem;                                   // [n_ids][MOM_MAX][MXI_NB]
+  int* s_na = reinterpret_cast<int*>(fold_smem + (size_t)n_ids * MOM_MAX * MXI_NB);
+  const int b0 = blockIdx.y * MXI_NB;
+  for (int t = threadIdx.x; t < n_ids * MXI_NB; t += 256) {
+    const int j = t / MXI_NB, e = t % MXI_NB;
+    const vg_eval_desc& d = evals[ids[j]];
+    const vg_eval_desc& o = evals[owners[j]];
+    const double* p = pfull + (long long)min(b0 + e, B - 1) * npf;
+    KaiserCoef kc = kaiser_setup(o, p, 1.0);
+    if (o.same_tracer) { kc.a0[1] = kc.a0[0]; kc.a1[1] = kc.a1[0]; kc.h0[1] = kc.h0[0]; kc.h1[1] = kc.h1[0]; }
+    double q[MOM_MAX];
+    moment_coefs(kc, q);
+    double w = 1.0;                       // weight_const is part of Y
+    if (d.weight_bias) {
+      double b1, be1, b2, be2;
+      tracer_bias_beta(d, p, 0, b1, be1);
+      tracer_bias_beta(d, p, 1, b2, be2);
+      w = b1 * b2;
+    }
+    if (d.idx_weight_extra >= 0) w *= p[d.idx_weight_extra];
+#pragma unroll
+    for (int m = 0; m < MOM_MAX; ++m) cq[((size_t)j * MOM_MAX + m) * MXI_NB + e] = w * q[m];
+    if (e == 0) s_na[j] = (o.hcd_model && (o.hcd_on[0] || o.hcd_on[1])) ? 3 : 1;
+  }
+  __syncthreads();
+  const int x = blockIdx.x * 256 + threadIdx.x;
+  if (x >= ld) return;
+  double acc[MXI_NB];
+#pragma unroll
+  for (int e = 0; e < MXI_NB; ++e) acc[e] = 0.0;
+  for (int j = 0; j < n_ids; ++j) {
+    const double* yt = Y + (long long)j * MOM_MAX * ld + x;
+    const int nm = 3 * s_na[j];
+    for (int m = 0; m < nm; ++m) {
+      const double v = __ldg(yt + (long long)m * ld);
+      const double* cj = cq + ((size_t)j * MOM_MAX + m) * MXI_NB;
+#pragma unroll
+      for (int e = 0; e < MXI_NB; ++e) acc[e] = fma(cj[e], v, acc[e]);
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < MXI_NB; ++e) {
+    const int b = b0 + e;
+    if (b >= B) break;
+    out[(long long)b * ld + x] = acc[e];
   }
 }
 

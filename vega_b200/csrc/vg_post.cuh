@@ -66,6 +66,7 @@ __global__ void metal_sum_kernel(const double* __restrict__ xmet, int n_metal, i
 struct CombineArgs {
   const double* core;      // [2][B][ld]
   const double* met;       // [B][ld] or null
+  const double* met_fold;  // [B][ld] or null: metal terms folded into static vectors
   const double* inst;      // [n] or null
   int idx_inst_amp; double inst_amp_default;
   int idx_bao_amp;
@@ -153,6 +154,7 @@ __global__ void combine_pre_kernel(CombineArgs a) {
   const double amp = a.direct ? 0.0 : par(p, a.idx_bao_amp, 1.0);
   double v = a.direct ? a.core[a.B * a.ld + idx] : amp * a.core[idx] + a.core[a.B * a.ld + idx];
   if (a.met) v += a.met[idx];
+  if (a.met_fold) v += a.met_fold[idx];
   for (int f = 0; f < a.n_frozen; ++f)
     v = fma(metal_bias_weight(a.evals[a.frozen_ids[f]], p), a.frozen[(long long)f * a.ld + i], v);
   if (a.inst) v += par(p, a.idx_inst_amp, a.inst_amp_default) * a.inst[i];

@@ -892,6 +892,10 @@ class DevicePlan:
         """Evaluations of correlation ci whose xi stage is a read-out of static tables."""
         return self.lib.vg_corr_n_static_xi(self.handle, ci)
 
+    def n_folded(self, ci):
+        """Metal evaluations of correlation ci that OPT_FOLD_METALS serves from static vectors."""
+        return self.lib.vg_corr_n_folded(self.handle, ci)
+
     def device_bytes(self):
         return self.lib.vg_plan_device_bytes(self.handle)
 
