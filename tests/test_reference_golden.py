@@ -173,3 +173,38 @@ def test_cuda_path_matches_reference_marginalisation(key, tmp_path):
     vega, oracle = make_marg_case(tmp_path, key)
     check(key, vega.compute_model, vega.chi2, vega.log_lik, gold, meta)
     check_marg(key, vega, gold, meta)
+
+
+@pytest.mark.gpu
+def test_cuda_path_matches_reference_sensitivity():
+    """VegaInterface.compute_sensitivity (vega/vega_interface.py:956-1071) against the unmodified
+    reference's output (tests/golden/make_sensitivity_golden.py): partial derivatives of the
+    distorted / undistorted peak and smooth components and the per-bin Fisher information.
+    The finite difference divides the 1e-10 model tolerance by a step of 0.2-1 % of the
+    parameter, hence 1e-6 * max|partial| here."""
+    from vega_b200 import VegaInterface
+    gold = np.load(GOLD / 'reference_sensitivity.npz')
+    nominal = {k: tuple(v) for k, v in json.loads(str(gold['nominal'])).items()}
+    vega = VegaInterface(INI['full'])
+    sens = vega.compute_sensitivity(nominal=nominal, frac=0.1, verbose=False)
+    assert list(sens['nominal']) == list(nominal)
+    n_checked = 0
+    for key in gold.files:
+        if key == 'nominal':
+            continue
+        kind, name, par = key.split('/')
+        ref = gold[key]
+        got = sens[kind][name][par if kind == 'partials' else tuple(par.split('|'))]
+        assert got.shape == ref.shape, key
+        assert np.array_equal(np.isnan(got), np.isnan(ref)), key
+        if kind == 'partials':
+            for d in range(2):
+                for c in range(2):
+                    scale = np.max(np.abs(ref[d, c]))
+                    assert np.max(np.abs(got[d, c] - ref[d, c])) <= 1e-6 * scale, (key, d, c)
+        else:
+            scale = np.nanmax(np.abs(ref), axis=1, keepdims=True)
+            ok = ~np.isnan(ref)
+            assert np.all((np.abs(got - ref) <= 1e-5 * scale + 0 * ref)[ok]), key
+        n_checked += 1
+    assert n_checked == 80

@@ -439,6 +439,84 @@ class VegaInterface:
         vega/vega_interface.py:646-663)."""
         return self.minimizer
 
+    def compute_sensitivity(self, nominal=None, frac=0.1, verbose=True):
+        """Model sensitivity to each floating parameter (vega/vega_interface.py:956-1071):
+        central differences at value +/- frac * error of the peak / smooth `core` components,
+        distorted ([0]) and undistorted ([1]), and the Fisher information per (rp, rt) bin of
+        every parameter pair.  Stored in `self.sensitivity` with the reference's keys
+        (`nominal`, `partials[corr][par]` [2, 2, Nm], `fisher[corr][(p1, p2)]` [2, Nm]).
+
+        One batch instead of the reference's 2P model evaluations: the 2P stencil points go
+        through the per-evaluation xi tap (undistorted components) and, paired with
+        bao_amp = 0 and 1, through vg_model_batch -- the model is bao_amp * peak + smooth with
+        every later stage linear (vega/model.py:186), so the distorted components of the
+        reference's save-components dictionaries are M(0) and M(1) - M(0)."""
+        if nominal is None:
+            if self.minimizer is None:
+                raise RuntimeError('No nominal parameter values provided or saved by minimize()')
+            values, errors, fixed = self.minimizer.values, self.minimizer.errors, self.minimizer.fixed
+            nominal = {n: (values[n], errors[n]) for n in values if not fixed[n]}
+        names = list(nominal)
+        P = len(names)
+        base = np.array([nominal[n][0] for n in names], dtype=np.float64)
+        delta = frac * np.array([nominal[n][1] for n in names], dtype=np.float64)
+        bao_amp = self.params['bao_amp']
+        if 'bao_amp' in names:
+            raise ValueError('compute_sensitivity weights the peak by the fixed bao_amp '
+                             '(vega/vega_interface.py:994): it cannot be one of the nominal parameters.')
+        if verbose:
+            for i, n in enumerate(names):
+                print(f'Calculating sensitivity for [{i}] {n} at {nominal[n][0]:.4f} ± {nominal[n][1]:.4f}')
+
+        # rows 2p (+delta) and 2p+1 (-delta)
+        pts = np.repeat(base[None, :], 2 * P, axis=0)
+        pts[2 * np.arange(P), np.arange(P)] += delta
+        pts[2 * np.arange(P) + 1, np.arange(P)] -= delta
+        cols = names + ['bao_amp']
+        engine = self._engine_for(tuple(cols))
+        theta = np.concatenate([np.column_stack([pts, np.full(2 * P, a)]) for a in (0.0, 1.0)])
+        theta = self._reorder(engine, theta, cols)
+        models, status = engine.model_device(engine.theta_tensor(theta))
+        status = status.cpu().numpy()
+        if np.any(status & _lib.STATUS_ARINYO):
+            raise utils.VegaArinyoError
+        if np.any(status & _lib.STATUS_BOUNDS):
+            raise utils.VegaBoundsError
+
+        self.sensitivity = dict(nominal=copy.deepcopy(nominal), partials={}, fisher={})
+        for ci, name in enumerate(self.corr_items):
+            n_model = self.corr_items[name].model_coordinates.rp_grid.size
+            ld = (n_model + 15) // 16 * 16
+            m = models[name].cpu().numpy()
+            smooth_d, peak_d = m[:2 * P], m[2 * P:] - m[:2 * P]
+            xi, _ = engine.stage(ci, 3, theta[:2 * P])
+            xi = xi.reshape(2 * P, -1, ld)[:, :2, :n_model]          # evaluations 0 / 1: peak / smooth
+            partials = self.sensitivity['partials'][name] = {}
+            for p, pname in enumerate(names):
+                out = np.zeros((2, 2, n_model))
+                out[0, 0] = bao_amp * (peak_d[2 * p] - peak_d[2 * p + 1])
+                out[0, 1] = smooth_d[2 * p] - smooth_d[2 * p + 1]
+                out[1, 0] = bao_amp * (xi[2 * p, 0] - xi[2 * p + 1, 0])
+                out[1, 1] = xi[2 * p, 1] - xi[2 * p + 1, 1]
+                partials[pname] = out / (2 * delta[p])
+
+        if verbose:
+            print('Computing Fisher information for each pair of parameters...')
+        import torch
+        for name in self.corr_items:
+            mask = self.data[name].data_mask
+            icov = torch.from_numpy(np.ascontiguousarray(self.data[name].inv_masked_cov)).to(engine.device)
+            fisher = self.sensitivity['fisher'][name] = {}
+            tot = np.stack([self.sensitivity['partials'][name][n].sum(axis=1) for n in names])   # [P, 2, Nm]
+            masked = torch.from_numpy(np.ascontiguousarray(tot[:, :, mask])).to(engine.device)  # [P, 2, Nmask]
+            weighted = torch.matmul(masked, icov.T).cpu().numpy()         # C^-1 . partial2
+            for i1, n1 in enumerate(names):
+                for i2 in range(i1, P):
+                    info = np.full((2, tot.shape[2]), np.nan)
+                    info[:, mask] = tot[i1][:, mask] * weighted[i2]
+                    fisher[(n1, names[i2])] = info
+        return self.sensitivity
+
     # -- batched API (new) -----------------------------------------------------------------------
     def chi2_batch(self, theta, names=None, direct_pk=None):
         """chi2 of B parameter vectors.  theta: ndarray [B, P] with columns `names`
