@@ -388,3 +388,29 @@ def test_model_call_shapes_and_stage_components():
     want = oracle.compute_model({k: pars[k] for k in ('bias_eta_LYA', 'beta_LYA', 'ap', 'sigma_velo_disp_lorentz_QSO')},
                                 direct_pk=direct)['lyalya_qso']
     assert np.max(np.abs(got - want)) <= XI_RTOL * np.max(np.abs(want))
+
+
+@pytest.mark.gpu
+def test_device_covariance_inverse_and_log_det():
+    """Init-time masked C^-1 and log|C| of a DESI-sized covariance on the device (one Cholesky
+    factor, vega_b200/utils.py) against the host LAPACK route the reference takes
+    (vega/utils.py:271-318), and the chi2-like quadratic form both give."""
+    from vega_b200 import utils
+    rng = np.random.default_rng(11)
+    n_all, n = 5200, 4600
+    idx = np.arange(n_all)
+    cov = 0.4 ** (np.abs(idx[:, None] - idx[None, :]) / 3.0) * np.outer(1 + 0.1 * rng.random(n_all),
+                                                                         1 + 0.1 * rng.random(n_all))
+    cov = 0.5 * (cov + cov.T) * 1e-8 + 1e-9 * np.eye(n_all)
+    mask = np.zeros(n_all, dtype=bool)
+    mask[rng.choice(n_all, n, replace=False)] = True
+    assert n >= utils.DEVICE_LINALG_MIN
+    got_inv = utils.compute_masked_invcov(cov, mask)
+    got_det = utils.compute_log_cov_det(cov, mask)
+    assert utils._factor_cache and next(iter(utils._factor_cache.values())) is not None
+    masked = cov[:, mask][mask, :]
+    ref_inv, ref_det = np.linalg.inv(masked), np.linalg.slogdet(masked)[1]
+    assert np.max(np.abs(got_inv - ref_inv)) <= 1e-10 * np.max(np.abs(ref_inv))
+    assert abs(got_det - ref_det) <= 1e-8
+    r = rng.standard_normal(n) * 1e-4
+    assert abs(r @ got_inv @ r - r @ ref_inv @ r) <= 1e-6

@@ -153,3 +153,18 @@ def test_unsupported_options_fail_loudly():
     vega.corr_items['lyalya_lyalya'].config['model']['no-metal-decomp'] = 'False'
     with pytest.raises(NotImplementedError):
         pb.describe_corr('lyalya_lyalya')
+
+
+def test_small_covariances_keep_the_reference_host_inverse():
+    """Below DEVICE_LINALG_MIN rows the masked inverse is numpy's LU inverse, bit-identical to
+    the reference's (vega/utils.py:271-299), whatever the machine."""
+    import numpy as np
+    from vega_b200 import utils
+    rng = np.random.default_rng(0)
+    a = rng.standard_normal((60, 60))
+    cov = a @ a.T + 60 * np.eye(60)
+    mask = rng.random(60) > 0.3
+    masked = cov[:, mask][mask, :]
+    assert np.array_equal(utils.compute_masked_invcov(cov, mask), np.linalg.inv(masked))
+    assert utils.compute_log_cov_det(cov, mask) == np.linalg.slogdet(masked)[1]
+    assert not utils._factor_cache

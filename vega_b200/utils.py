@@ -107,9 +107,39 @@ def growth_function_old(z, Omega_m, Omega_de):
     return _growth_interp_old(Omega_m, Omega_de)(z)
 
 
+DEVICE_LINALG_MIN = int(os.environ.get('VEGA_B200_DEVICE_LINALG_MIN', 4096))
+_factor_cache = {}
+
+
+def _device_cholesky(masked_cov):
+    """Cholesky factor of a large masked covariance on the GPU (cuSOLVER through torch; init
+    time).  One factorisation serves the positive-definiteness check, the inverse
+    and the log-determinant -- the reference factorises three times on the host
+    (vega/utils.py:271-318).  Returns None below DEVICE_LINALG_MIN rows (host LAPACK, bit-identical
+    to the reference), without a CUDA device, or when the matrix is not positive definite."""
+    n = masked_cov.shape[0]
+    if n < DEVICE_LINALG_MIN:
+        return None
+    import torch
+    if not torch.cuda.is_available():
+        return None
+    key = (n, float(masked_cov[0, 0]), float(masked_cov[-1, -1]), float(masked_cov[n // 2].sum()))
+    if key not in _factor_cache:
+        _factor_cache.clear()               # one matrix at a time: a 9540^2 factor is 728 MB
+        dev = torch.from_numpy(np.ascontiguousarray(masked_cov, dtype=np.float64)).cuda()
+        factor, info = torch.linalg.cholesky_ex(dev)
+        _factor_cache[key] = factor if int(info) == 0 else None
+    return _factor_cache[key]
+
+
 def compute_masked_invcov(cov_mat, data_mask):
     """inv(cov[mask][:, mask]) (vega/utils.py:271-299)."""
     masked_cov = cov_mat[:, data_mask][data_mask, :]
+    factor = _device_cholesky(masked_cov)
+    if factor is not None:
+        import torch
+        inv = torch.cholesky_inverse(factor)
+        return (0.5 * (inv + inv.T)).cpu().numpy()
     try:
         np.linalg.cholesky(masked_cov)
     except np.linalg.LinAlgError:
@@ -120,6 +150,10 @@ def compute_masked_invcov(cov_mat, data_mask):
 def compute_log_cov_det(cov_mat, data_mask):
     """log det of the masked covariance (vega/utils.py:302-318)."""
     masked_cov = cov_mat[:, data_mask][data_mask, :]
+    factor = _device_cholesky(masked_cov)
+    if factor is not None:
+        import torch
+        return float(2.0 * torch.log(torch.diagonal(factor)).sum().cpu())
     return np.linalg.slogdet(masked_cov)[1]
 
 
