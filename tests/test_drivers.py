@@ -259,3 +259,48 @@ def test_chi2_scan_on_the_device_path():
         dn[j] -= h
         f_up, f_dn = vega.chi2_batch(np.array([up, dn]), names)
         assert f_up >= f_best - 1e-7 and f_dn >= f_best - 1e-7
+
+
+@pytest.mark.gpu
+def test_mock_fits_with_a_global_covariance():
+    """Mocks of the joint data vector (Analysis.create_global_monte_carlo, vega/analysis.py:164-222)
+    drawn with the reference's random stream, their chi2 under the masked global C^-1
+    (vega/vega_interface.py:295-303) against the oracle mock by mock, and a lock-step fit."""
+    from helpers import set_fast_metals, static_tables
+    from oracle.vega_oracle import Oracle
+    from vega_b200 import VegaInterface, synthetic
+    vega = VegaInterface('configs/full_configs/main.ini')
+    set_fast_metals(vega)
+    synthetic.inject_global_covariance(vega)
+    oracle = Oracle(vega, tables=static_tables())
+    fiducial = oracle.compute_model()
+    mc = MonteCarloFits(vega, fiducial_model=fiducial, scale=1.2)
+    mocks = mc.draw(3, seed=5)
+    # the reference's draw, restated: one Cholesky factor, one randn(n) per mock from seed 5
+    names = list(vega.corr_items)
+    mask = np.concatenate([vega.data[n].data_mask for n in names])
+    chol = np.linalg.cholesky(1.2 * vega.global_cov[:, mask][mask, :])
+    np.random.seed(5)
+    fid = np.concatenate([fiducial[n] for n in names])[mask]
+    for m in range(3):
+        ref_mock = fid + chol.dot(np.random.randn(mask.sum()))
+        assert np.max(np.abs(mc.global_mocks[m] - ref_mock)) <= 1e-12 * np.max(np.abs(ref_mock))
+    assert np.array_equal(np.concatenate([mocks[n][2] for n in names]), mc.global_mocks[2])
+
+    pars = mc.names
+    base = np.array([vega.params[n] for n in pars])
+    theta = base * (1 + 0.01 * np.random.default_rng(2).standard_normal((2, len(pars))))
+    pairs = [(0, 1), (1, 2), (1, 0)]
+    got = mc.chi2(np.array([theta[t] for t, _ in pairs]), [m for _, m in pairs])
+    oracle.monte_carlo = True
+    for (t, m), value in zip(pairs, got):
+        vega.analysis.current_mc_mock = mc.global_mocks[m]
+        ref = oracle.chi2(dict(zip(pars, theta[t])))
+        assert abs(value - ref) <= 1e-6 * max(1.0, abs(ref) / 1e4), (t, m, value, ref)
+
+    res = mc.fit(max_iter=30)
+    truth = np.tile(base, (3, 1))
+    at_truth = mc.chi2(truth, np.arange(3))
+    assert np.all(res['fval'] <= at_truth + 1e-6)
+    assert np.all(at_truth - res['fval'] < 10 * len(pars))
+    vega.monte_carlo = False

@@ -1,8 +1,13 @@
 """C4 and C5 at their stated sizes, one process per GPU (run under torchrun or alone):
   C4  PolyChord-style batched log-likelihood: 1e5 parameter vectors sharded over the ranks,
       chi2 values all-gathered (sharding.ShardedChi2);
-  C5  Monte Carlo mock fits: 1000 mocks of the C2-shaped workload fitted in lock-step, the
-      mocks sharded over the ranks (drivers.MonteCarloFits.fit_sharded)."""
+  C5  Monte Carlo mock fits: 1000 mocks fitted in lock-step, the mocks sharded over the ranks
+      (drivers.MonteCarloFits.fit_sharded).
+Usage: gpu_c4_c5.py [n_vectors] [n_mocks] [c2|c3]
+  c2 (default)  the bench's C2-shaped workload (2 correlations, dense metal matrices)
+  c3            the DESI-DR2-shaped workload of SURVEY 8d (4 correlations, 5625/11250-bin model
+                grids, rp-only new_metals matrices, fast_metals, global covariance over 9540
+                masked bins; mocks drawn from the joint covariance)"""
 import json
 import os
 import sys
@@ -29,10 +34,34 @@ if world > 1:
 n_vectors = int(sys.argv[1]) if len(sys.argv) > 1 else 100000
 n_mocks = int(sys.argv[2]) if len(sys.argv) > 2 else 1000
 
-vega = bench.build_state()
+model = sys.argv[3] if len(sys.argv) > 3 else 'c2'
+t_init = time.perf_counter()
+if model == 'c3':
+    from helpers import make_c3_config
+    from vega_b200 import VegaInterface
+    vega = VegaInterface(make_c3_config(f'/tmp/c3_c4c5_{rank}'))
+    synthetic.inject_dense_operands(vega, with_distortion=False, with_metals=False)
+    synthetic.inject_global_covariance(vega)
+    names = ['bias_eta_LYA', 'beta_LYA', 'ap', 'at', 'bias_hcd', 'beta_hcd', 'drp_QSO',
+             'sigma_velo_disp_lorentz_QSO', 'bias_eta_SiII(1260)', 'bias_eta_SiIII(1207)',
+             'bias_eta_SiII(1193)', 'bias_eta_SiII(1190)', 'bias_eta_CIV(eff)', 'bias_QSO']
+    names = [n for n in names if n in vega.params]
+    # the [sample] set of the fits: restrict / extend the configuration's to `names`
+    sp = vega.sample_params
+    from vega_b200 import utils as vutils
+    for n in names:
+        if n not in sp['limits']:
+            sp['values'][n] = vega.params[n]
+            sp['errors'][n] = 0.02 * abs(vega.params[n]) + 1e-4
+            sp['limits'][n] = (None, None)
+            sp['fix'][n] = False
+    for key in ('values', 'errors', 'limits', 'fix'):
+        sp[key] = {n: sp[key][n] for n in names}
+else:
+    vega = bench.build_state()
 fiducial = vega.compute_model()
 synthetic.draw_mock_data(vega, fiducial)
-out = {'world': world}
+out = {'world': world, 'model': model, 'init_s': time.perf_counter() - t_init}
 
 # ---- C4 ----
 theta = synthetic.draw_theta(vega, n_vectors)
@@ -74,6 +103,6 @@ if rank == 0:
     print('C5', {k: out['c5'][k] for k in ('mocks', 'parameters', 'wall_s', 'fits_per_s', 'converged', 'mean_fval')},
           flush=True)
     Path('gpurun_out').mkdir(exist_ok=True)
-    json.dump(out, open(f'gpurun_out/c4_c5_n{world}.json', 'w'), indent=1)
+    json.dump(out, open(f'gpurun_out/c4_c5_{model}_n{world}.json', 'w'), indent=1)
 if world > 1:
     dist.destroy_process_group()

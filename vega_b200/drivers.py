@@ -26,6 +26,8 @@ import time
 
 import numpy as np
 
+from . import utils
+
 
 # ---------------------------------------------------------------------------------------------
 # stencils
@@ -379,8 +381,6 @@ class MonteCarloFits:
         self.sample_params = vega.mc_config['sample'] if getattr(vega, 'mc_config', None) \
             else vega.sample_params
         self.names = list(self.sample_params['limits'].keys())
-        if vega._use_global_cov:
-            raise NotImplementedError('Mock fits with a global covariance are not built yet.')
         self.fiducial_model = fiducial_model if fiducial_model is not None else vega.compute_model()
         self.scale = scale
         self.mocks = None
@@ -392,19 +392,66 @@ class MonteCarloFits:
         vega = self.vega
         mocks = {name: [] for name in vega.corr_items}
         np.random.seed(seed)
-        for m in range(n_mocks):
-            for name in vega.corr_items:
-                item_scale = self.scale if self.scale is not None else \
-                    getattr(vega.corr_items[name], 'cov_rescale', None)
-                vega.data[name].create_monte_carlo(self.fiducial_model[name], item_scale, None)
-                mocks[name].append(vega.data[name].masked_mc_mock.copy())
-        self.mocks = {name: np.array(v) for name, v in mocks.items()}
+        if vega._use_global_cov:
+            self.mocks = self._draw_global(n_mocks)
+        else:
+            for m in range(n_mocks):
+                for name in vega.corr_items:
+                    item_scale = self.scale if self.scale is not None else \
+                        getattr(vega.corr_items[name], 'cov_rescale', None)
+                    vega.data[name].create_monte_carlo(self.fiducial_model[name], item_scale, None)
+                    mocks[name].append(vega.data[name].masked_mc_mock.copy())
+            self.mocks = {name: np.array(v) for name, v in mocks.items()}
         vega.monte_carlo = True
         engine = vega._engine_for(tuple(self.names))   # swaps in the scaled inverse covariance (MC mode)
         for ci, name in enumerate(vega.corr_items):
             engine.set_mocks(ci, self.mocks[name])
         self.engine = engine
         return self.mocks
+
+    def _draw_global(self, n_mocks):
+        """Mocks of the joint data vector under a global covariance
+        (Analysis.create_global_monte_carlo, vega/analysis.py:164-222): one Cholesky factor of
+        scale * cov[mask][:, mask], mock = masked fiducial + L . randn(n) from the running
+        stream, one draw per mock.  The chi2 keeps the UNSCALED masked global inverse
+        (vega/vega_interface.py:295-303), as the reference does.  Returned split per correlation
+        in the order the residuals are concatenated."""
+        vega = self.vega
+        names = list(vega.corr_items)
+        full_mask = np.concatenate([vega.data[n].data_mask for n in names])
+        masked_cov = vega.global_cov[:, full_mask][full_mask, :]
+        scale = 1 if self.scale is None else self.scale
+        chol = None
+        if masked_cov.shape[0] >= utils.DEVICE_LINALG_MIN and self.torch.cuda.is_available():
+            # DESI-sized joint covariance (9540 rows): factor on the device (init time)
+            dev = self.torch.from_numpy(np.ascontiguousarray(scale * masked_cov)).cuda()
+            factor, info = self.torch.linalg.cholesky_ex(dev)
+            chol = factor.cpu().numpy() if int(info) == 0 else None
+        if chol is None:
+            chol = np.linalg.cholesky(scale * masked_cov)
+        fid = []
+        for n in names:
+            data, model = vega.data[n], np.asarray(self.fiducial_model[n])
+            to_data = data.dist_model_coordinates.get_mask_to_other(data.data_coordinates)
+            if data.data_mask.size == model.size:
+                fid.append(model)
+            elif to_data.size == model.size:
+                fid.append(model[to_data])
+            else:
+                raise ValueError('Input fiducial has unknown size. It must match the data or the model.')
+        fid = np.concatenate(fid)[full_mask]
+        z = np.stack([np.random.randn(fid.size) for _ in range(n_mocks)])
+        joint = fid[None, :] + z @ chol.T
+        self.global_mocks = joint
+        edges = np.cumsum([0] + [int(vega.data[n].data_mask.sum()) for n in names])
+        mocks = {n: np.ascontiguousarray(joint[:, edges[i]:edges[i + 1]]) for i, n in enumerate(names)}
+        vega.analysis.current_mc_mock = joint[-1].copy()       # vega/analysis.py:217-220
+        for n in names:      # what the scalar MC-mode chi2 reads (the last mock drawn, as in the reference)
+            data = vega.data[n]
+            data.masked_mc_mock = mocks[n][-1].copy()
+            if data.scaled_inv_masked_cov is None:
+                data.scaled_inv_masked_cov = data.inv_masked_cov
+        return mocks
 
     def chi2(self, theta, mock_idx):
         """chi2 of theta[b] against mock mock_idx[b]; host arrays in and out."""
