@@ -1106,8 +1106,15 @@ int build_metal_operands(Corr& c, const EvalLayout& L, DevBuf& mcat, DevBuf& mrp
 
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st) {
-  dim3 grid(vg_cdiv(c.rp_nt, vg::MRP_TN), vg_cdiv(c.rp_np, vg::MRP_TM), (unsigned)B);
-  vg::metal_rp_kernel<<<grid, 256, 0, st>>>(xmet, n_metal, c.ld_model, A, c.rp_np, c.rp_nt, met);
+  // batches go to the DMMA tile; a vector or two (plan-time folds, the scalar API) keep the FMA
+  // kernel, whose 40 x 32 tiles spread one vector over more CTAs
+  if (B >= 8) {
+    dim3 grid(vg_cdiv(c.rp_nt, vg::MRD_TN), vg_cdiv(c.rp_np, vg::MRD_TM), (unsigned)B);
+    vg::metal_rp_dmma_kernel<<<grid, vg::MRD_THREADS, 0, st>>>(xmet, n_metal, c.ld_model, A, c.rp_np, c.rp_nt, met);
+  } else {
+    dim3 grid(vg_cdiv(c.rp_nt, vg::MRP_TN), vg_cdiv(c.rp_np, vg::MRP_TM), (unsigned)B);
+    vg::metal_rp_kernel<<<grid, 256, 0, st>>>(xmet, n_metal, c.ld_model, A, c.rp_np, c.rp_nt, met);
+  }
   VG_LAUNCHED();
   return VG_OK;
 }

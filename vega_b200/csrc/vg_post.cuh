@@ -11,6 +11,7 @@
 #pragma once
 #include "../../include/vega_b200.h"
 #include "vg_common.cuh"
+#include "vg_gemm.cuh"
 #include "vg_pk.cuh"
 
 namespace vg {
@@ -142,6 +143,75 @@ metal_rp_kernel(const double* __restrict__ xmet, int n_metal, int ld, const doub
   // pad columns stay finite (written by the first CTA of each vector)
   if (blockIdx.x == 0 && blockIdx.y == 0)
     for (int i = np * nt + tid; i < ld; i += 256) met[b * ld + i] = 0.0;
+}
+
+// The same contraction on the FP64 tensor pipe (DMMA m8n8k4, tcgen05 has no FP64 kind).  Per
+// vector it is a small GEMM  met[rp][rt] = [A_0 | A_1 | ...][rp][c rp'] . X[c rp'][rt]  with
+// M = Np (75 / 150), N = Nt (75), K = n_metal Np.  CTA tile 80 rp x 80 rt x 32 k, 5 warps, a warp
+// owns 16 rp rows x all 80 rt columns (2 x 10 DMMA fragments: one B fragment feeds two DMMAs);
+// shared rows padded to 36 / 84 doubles so the 64-bit fragment loads of a half-warp fall in 16
+// distinct bank pairs.  45 KB of shared memory per CTA: 5 CTAs per SM hide the refill (single
+// stage, two barriers per 32 k).  Summation order over k is the FMA kernel's (ascending), per
+// output element, so results are independent of the batch composition.
+constexpr int MRD_TM = 80, MRD_TN = 80, MRD_TK = 32, MRD_SA = MRD_TK + 4, MRD_SX = MRD_TN + 4;
+constexpr int MRD_THREADS = 160;
+__global__ void __launch_bounds__(MRD_THREADS)
+metal_rp_dmma_kernel(const double* __restrict__ xmet, int n_metal, int ld, const double* __restrict__ A,
+                     int np, int nt, double* __restrict__ met) {
+  __shared__ double As[MRD_TM * MRD_SA];
+  __shared__ double Xs[MRD_TK * MRD_SX];
+  const long long b = blockIdx.z;
+  const int rt0 = blockIdx.x * MRD_TN, rp0 = blockIdx.y * MRD_TM;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int gid = lane >> 2, tig = lane & 3;
+  double acc[2][MRD_TN / 8][2];
+#pragma unroll
+  for (int m = 0; m < 2; ++m)
+#pragma unroll
+    for (int n = 0; n < MRD_TN / 8; ++n) acc[m][n][0] = acc[m][n][1] = 0.0;
+  const double* a_lo = As + (warp * 16 + gid) * MRD_SA + tig;
+  const double* b_lo = Xs + tig * MRD_SX + gid;
+  for (int c = 0; c < n_metal; ++c) {
+    const double* Ac = A + (long long)c * np * np;
+    const double* x = xmet + (b * n_metal + c) * ld;
+    for (int k0 = 0; k0 < np; k0 += MRD_TK) {
+      __syncthreads();
+      for (int i = tid; i < MRD_TM * MRD_TK; i += MRD_THREADS) {
+        const int r = i / MRD_TK, k = i % MRD_TK;
+        As[r * MRD_SA + k] = (rp0 + r < np && k0 + k < np) ? __ldg(Ac + (long long)(rp0 + r) * np + k0 + k) : 0.0;
+      }
+      for (int i = tid; i < MRD_TK * MRD_TN; i += MRD_THREADS) {
+        const int k = i / MRD_TN, t = i % MRD_TN;
+        Xs[k * MRD_SX + t] = (k0 + k < np && rt0 + t < nt) ? x[(k0 + k) * nt + rt0 + t] : 0.0;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < MRD_TK; kk += 4) {
+        if (k0 + kk >= np) break;            // tail chunk of a matrix (75 = 32 + 32 + 11): CTA-uniform
+        const double a0 = a_lo[kk], a1 = a_lo[8 * MRD_SA + kk];
+#pragma unroll
+        for (int n = 0; n < MRD_TN / 8; ++n) {
+          const double bf = b_lo[kk * MRD_SX + n * 8];
+          dmma884(acc[0][n][0], acc[0][n][1], a0, bf);
+          dmma884(acc[1][n][0], acc[1][n][1], a1, bf);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+    const int rp = rp0 + warp * 16 + m * 8 + gid;
+    if (rp >= np) continue;
+#pragma unroll
+    for (int n = 0; n < MRD_TN / 8; ++n)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int rt = rt0 + n * 8 + tig * 2 + j;
+        if (rt < nt) met[b * ld + rp * nt + rt] = acc[m][n][j];
+      }
+  }
+  if (blockIdx.x == 0 && blockIdx.y == 0)
+    for (int i = np * nt + tid; i < ld; i += MRD_THREADS) met[b * ld + i] = 0.0;
 }
 
 __global__ void combine_pre_kernel(CombineArgs a) {
