@@ -147,15 +147,17 @@ metal_rp_kernel(const double* __restrict__ xmet, int n_metal, int ld, const doub
 
 // The same contraction on the FP64 tensor pipe (DMMA m8n8k4, tcgen05 has no FP64 kind).  Per
 // vector it is a small GEMM  met[rp][rt] = [A_0 | A_1 | ...][rp][c rp'] . X[c rp'][rt]  with
-// M = Np (75 / 150), N = Nt (75), K = n_metal Np.  CTA tile 80 rp x 80 rt x 32 k, 5 warps, a warp
-// owns 16 rp rows x all 80 rt columns (2 x 10 DMMA fragments: one B fragment feeds two DMMAs);
-// shared rows padded to 36 / 84 doubles so the 64-bit fragment loads of a half-warp fall in 16
-// distinct bank pairs.  45 KB of shared memory per CTA: 5 CTAs per SM hide the refill (single
-// stage, two barriers per 32 k).  Summation order over k is the FMA kernel's (ascending), per
+// M = Np (75 / 150), N = Nt (75), K = n_metal Np.  CTA tile 80 rp x 40 rt x 32 k, 5 warps, a warp
+// owns 16 rp rows x the 40 rt columns (2 x 5 DMMA fragments: one B fragment feeds two DMMAs);
+// shared rows padded to 36 / 44 doubles so the 64-bit fragment loads of a half-warp fall in 16
+// distinct bank pairs.  34 KB of shared memory and ~80 registers per CTA thread: 5-6 CTAs per SM
+// hide the refill (next chunk prefetched into registers during the DMMAs, two barriers per
+// 32 k), and the half-width tile keeps the
+// wave tail short (a 451-vector Hessian stencil is 902 / 1804 CTAs).  Summation order over k is the FMA kernel's (ascending), per
 // output element, so results are independent of the batch composition.
-constexpr int MRD_TM = 80, MRD_TN = 80, MRD_TK = 32, MRD_SA = MRD_TK + 4, MRD_SX = MRD_TN + 4;
+constexpr int MRD_TM = 80, MRD_TN = 40, MRD_TK = 32, MRD_SA = MRD_TK + 4, MRD_SX = MRD_TN + 4;
 constexpr int MRD_THREADS = 160;
-__global__ void __launch_bounds__(MRD_THREADS)
+__global__ void __launch_bounds__(MRD_THREADS, 3)
 metal_rp_dmma_kernel(const double* __restrict__ xmet, int n_metal, int ld, const double* __restrict__ A,
                      int np, int nt, double* __restrict__ met) {
   __shared__ double As[MRD_TM * MRD_SA];
@@ -171,30 +173,52 @@ metal_rp_dmma_kernel(const double* __restrict__ xmet, int n_metal, int ld, const
     for (int n = 0; n < MRD_TN / 8; ++n) acc[m][n][0] = acc[m][n][1] = 0.0;
   const double* a_lo = As + (warp * 16 + gid) * MRD_SA + tig;
   const double* b_lo = Xs + tig * MRD_SX + gid;
-  for (int c = 0; c < n_metal; ++c) {
+  // chunks q = (matrix c, 32 k) in order; the next chunk's operands are fetched into registers
+  // while the DMMAs of the current one run, and stored to shared memory after the barrier
+  constexpr int NA = MRD_TM * MRD_TK / MRD_THREADS, NX = MRD_TK * MRD_TN / MRD_THREADS;
+  static_assert(NA * MRD_THREADS == MRD_TM * MRD_TK && NX * MRD_THREADS == MRD_TK * MRD_TN, "fill mapping");
+  const int nkc = (np + MRD_TK - 1) / MRD_TK, n_chunks = n_metal * nkc;
+  double ra[NA], rx[NX];
+  auto fetch = [&](int q) {
+    const int c = q / nkc, k0 = (q - c * nkc) * MRD_TK;
     const double* Ac = A + (long long)c * np * np;
     const double* x = xmet + (b * n_metal + c) * ld;
-    for (int k0 = 0; k0 < np; k0 += MRD_TK) {
-      __syncthreads();
-      for (int i = tid; i < MRD_TM * MRD_TK; i += MRD_THREADS) {
-        const int r = i / MRD_TK, k = i % MRD_TK;
-        As[r * MRD_SA + k] = (rp0 + r < np && k0 + k < np) ? __ldg(Ac + (long long)(rp0 + r) * np + k0 + k) : 0.0;
-      }
-      for (int i = tid; i < MRD_TK * MRD_TN; i += MRD_THREADS) {
-        const int k = i / MRD_TN, t = i % MRD_TN;
-        Xs[k * MRD_SX + t] = (k0 + k < np && rt0 + t < nt) ? x[(k0 + k) * nt + rt0 + t] : 0.0;
-      }
-      __syncthreads();
 #pragma unroll
-      for (int kk = 0; kk < MRD_TK; kk += 4) {
-        if (k0 + kk >= np) break;            // tail chunk of a matrix (75 = 32 + 32 + 11): CTA-uniform
-        const double a0 = a_lo[kk], a1 = a_lo[8 * MRD_SA + kk];
+    for (int j = 0; j < NA; ++j) {
+      const int i = tid + j * MRD_THREADS, r = i / MRD_TK, k = i % MRD_TK;
+      ra[j] = (rp0 + r < np && k0 + k < np) ? __ldg(Ac + (long long)(rp0 + r) * np + k0 + k) : 0.0;
+    }
 #pragma unroll
-        for (int n = 0; n < MRD_TN / 8; ++n) {
-          const double bf = b_lo[kk * MRD_SX + n * 8];
-          dmma884(acc[0][n][0], acc[0][n][1], a0, bf);
-          dmma884(acc[1][n][0], acc[1][n][1], a1, bf);
-        }
+    for (int j = 0; j < NX; ++j) {
+      const int i = tid + j * MRD_THREADS, k = i / MRD_TN, t = i % MRD_TN;
+      rx[j] = (k0 + k < np && rt0 + t < nt) ? __ldg(x + (k0 + k) * nt + rt0 + t) : 0.0;
+    }
+  };
+  fetch(0);
+  for (int q = 0; q < n_chunks; ++q) {
+    const int k0 = (q % nkc) * MRD_TK;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < NA; ++j) {
+      const int i = tid + j * MRD_THREADS;
+      As[(i / MRD_TK) * MRD_SA + i % MRD_TK] = ra[j];
+    }
+#pragma unroll
+    for (int j = 0; j < NX; ++j) {
+      const int i = tid + j * MRD_THREADS;
+      Xs[(i / MRD_TN) * MRD_SX + i % MRD_TN] = rx[j];
+    }
+    __syncthreads();
+    if (q + 1 < n_chunks) fetch(q + 1);
+#pragma unroll
+    for (int kk = 0; kk < MRD_TK; kk += 4) {
+      if (k0 + kk >= np) break;            // tail chunk of a matrix (75 = 32 + 32 + 11): CTA-uniform
+      const double a0 = a_lo[kk], a1 = a_lo[8 * MRD_SA + kk];
+#pragma unroll
+      for (int n = 0; n < MRD_TN / 8; ++n) {
+        const double bf = b_lo[kk * MRD_SX + n * 8];
+        dmma884(acc[0][n][0], acc[0][n][1], a0, bf);
+        dmma884(acc[1][n][0], acc[1][n][1], a1, bf);
       }
     }
   }
