@@ -123,7 +123,9 @@ def _device_cholesky(masked_cov):
     import torch
     if not torch.cuda.is_available():
         return None
-    key = (n, float(masked_cov[0, 0]), float(masked_cov[-1, -1]), float(masked_cov[n // 2].sum()))
+    # identity of the matrix: full sum, trace and a strided partial sum (one pass at memory speed)
+    key = (n, float(masked_cov.sum()), float(np.trace(masked_cov)), float(masked_cov[::7, ::13].sum()),
+           float(masked_cov[n // 2] @ masked_cov[n // 3]))
     if key not in _factor_cache:
         _factor_cache.clear()               # one matrix at a time: a 9540^2 factor is 728 MB
         dev = torch.from_numpy(np.ascontiguousarray(masked_cov, dtype=np.float64)).cuda()
