@@ -328,6 +328,18 @@ def main():
     engine.set_option(vlib.OPT_FOLD_METALS, 0)
 
     if rank == 0:
+        # the reference's scalar call (what iminuit / PolyChord make): one parameter dict -> float,
+        # host in, host out, a batch of one through the same plan (reported, not the headline)
+        names = list(engine.sampled)
+        scalar_calls = 50
+        for i in range(3):
+            vega.chi2(dict(zip(names, theta[i])))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(scalar_calls):
+            scalar_value = vega.chi2(dict(zip(names, theta[i % B])))
+        scalar_ms = (time.perf_counter() - t0) * 1e3 / scalar_calls
+        assert abs(scalar_value - float(c_host[(scalar_calls - 1) % B])) <= 1e-6 * max(1.0, abs(scalar_value) / 1e4)
         flops = gemm_flops(engine, B)
         stage_ms = {s: ms_stage[i] / args.steps for i, s in enumerate(STAGES)}
         gemm_ms = sum(stage_ms[s] for s in flops)
@@ -407,6 +419,8 @@ def main():
                                    'folded_metal_terms': n_folded, 'ms_per_step': fold_ms,
                                    'value': world * B / (fold_ms * 1e-3), 'unit': 'evals/s',
                                    'max_abs_chi2_difference': fold_diff},
+            'scalar_api': {'call': 'VegaInterface.chi2(params) -> float, batch of one', 'ms_per_call': scalar_ms,
+                           'calls': scalar_calls},
             'cpu_baseline': base,
         }
         print(json.dumps(line), file=real_stdout, flush=True)

@@ -304,3 +304,65 @@ def test_mock_fits_with_a_global_covariance():
     assert np.all(res['fval'] <= at_truth + 1e-6)
     assert np.all(at_truth - res['fval'] < 10 * len(pars))
     vega.monte_carlo = False
+
+
+@pytest.mark.gpu
+def test_monte_carlo_surface_of_the_scripts(tmp_path):
+    """What bin/run_vega_mc_mpi.py:42-62 and vega/scripts/run_vega.py:24 call:
+    get_fiducial_for_monte_carlo (initial fit over [sample], [mc parameters] on top),
+    initialize_monte_carlo (one mock from mc_seed, minimizer on the [monte carlo] set, MC mode on)
+    and analysis.run_monte_carlo (vega/analysis.py:224-308) with its result attributes."""
+    import configparser
+    from helpers import static_tables
+    from oracle.vega_oracle import Oracle
+    from vega_b200 import VegaInterface, synthetic, utils
+    cfg = configparser.ConfigParser()
+    cfg.optionxform = lambda option: option
+    cfg.read(utils.find_file('configs/c2/main.ini'))
+    cfg['sample'] = {'bias_eta_LYA': 'True', 'beta_LYA': 'True'}
+    cfg['priors'] = {}
+    cfg['monte carlo'] = {'ap': 'True', 'at': 'True', 'bias_eta_LYA': 'True'}
+    cfg['mc parameters'] = {'ap': '1.01', 'at': '0.99'}
+    cfg['control']['mc_seed'] = '4'
+    path = tmp_path / 'main_mc.ini'
+    with open(path, 'w') as f:
+        cfg.write(f)
+    vega = VegaInterface(str(path))
+    synthetic.inject_dense_operands(vega)
+    synthetic.draw_mock_data(vega, vega.compute_model())
+    quiet = lambda *a, **k: None    # noqa: E731
+
+    mocks = vega.initialize_monte_carlo(print_func=quiet)
+    assert vega.monte_carlo and list(mocks) == list(vega.corr_items)
+    assert list(vega.minimizer._names) == ['ap', 'at', 'bias_eta_LYA']
+    # the mock is the reference's draw: seed once, one create_monte_carlo per correlation in order
+    np.random.seed(4)
+    for name in vega.corr_items:
+        data = vega.data[name]
+        noise = data._cholesky.dot(np.random.randn(int(data.data_mask.sum())))
+        fid = np.asarray(vega._mc_fits.fiducial_model[name])[data.data_mask]
+        assert np.max(np.abs(mocks[name][data.data_mask] - (fid + noise))) <= 1e-14 * np.max(np.abs(fid))
+        assert mocks[name].shape == (data.full_data_size,)
+        assert np.array_equal(data.masked_mc_mock, mocks[name][data.data_mask])
+    # scalar chi2 in Monte Carlo mode against the oracle's monte_carlo branch
+    oracle = Oracle(vega, tables=static_tables())
+    oracle.monte_carlo = True
+    pars = {'ap': 1.004, 'at': 0.997, 'bias_eta_LYA': -0.2005}
+    ref = oracle.chi2(pars)
+    assert abs(vega.chi2(pars) - ref) <= 1e-6 * max(1.0, abs(ref) / 1e4)
+
+    best = vega.analysis.run_monte_carlo(vega._mc_fits.fiducial_model, num_mocks=3, seed=7)
+    ana = vega.analysis
+    assert ana.has_monte_carlo and set(best) == {'ap', 'at', 'bias_eta_LYA'}
+    assert all(v.shape == (3, 2) for v in best.values())
+    assert len(ana.mc_chisq) == len(ana.mc_covariances) == len(ana.mc_valid_minima) == 3
+    assert ana.mc_failed_mask == [False] * 3 and all(ana.mc_valid_minima) and all(ana.mc_valid_hesse)
+    n_dof = sum(int(d.data_mask.sum()) for d in vega.data.values()) - 3
+    assert all(abs(c - n_dof) < 6 * np.sqrt(2 * n_dof) for c in ana.mc_chisq)
+    assert all(len(ana.mc_mocks[n]) == 3 and ana.mc_mocks[n][0].shape == (vega.data[n].full_data_size,)
+               for n in vega.corr_items)
+    # best fits scatter around the template values by about their errors
+    for name, truth in (('ap', 1.01), ('at', 0.99)):
+        pull = (best[name][:, 0] - truth) / best[name][:, 1]
+        assert np.all(np.abs(pull) < 5), (name, pull)
+    vega.monte_carlo = False

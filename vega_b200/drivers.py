@@ -385,21 +385,33 @@ class MonteCarloFits:
         self.scale = scale
         self.mocks = None
 
-    def draw(self, n_mocks, seed=0):
+    def _item_scale(self, name):
+        """Covariance scale of one correlation as create_monte_carlo_sim resolves it
+        (vega/analysis.py:146-156): None -> the item's cov_rescale, number, or dict by name."""
+        if self.scale is None:
+            return getattr(self.vega.corr_items[name], 'cov_rescale', None)
+        if isinstance(self.scale, dict):
+            return self.scale.get(name, 1.)
+        return self.scale
+
+    def draw(self, n_mocks, seed=0, forecast=False):
         """masked mocks {name: [n_mocks, n_mask]}, drawn as run_monte_carlo draws them
         (vega/analysis.py:245,261-263): np.random.seed(seed) once, then one
-        Data.create_monte_carlo per correlation per mock from the running stream."""
+        Data.create_monte_carlo per correlation per mock from the running stream
+        (forecast: the fiducial itself, no noise)."""
         vega = self.vega
         mocks = {name: [] for name in vega.corr_items}
-        np.random.seed(seed)
+        self.full_mocks = {name: [] for name in vega.corr_items}
+        if seed is not None:
+            np.random.seed(seed)
         if vega._use_global_cov:
-            self.mocks = self._draw_global(n_mocks)
+            self.mocks = self._draw_global(n_mocks, forecast)
         else:
             for m in range(n_mocks):
                 for name in vega.corr_items:
-                    item_scale = self.scale if self.scale is not None else \
-                        getattr(vega.corr_items[name], 'cov_rescale', None)
-                    vega.data[name].create_monte_carlo(self.fiducial_model[name], item_scale, None)
+                    full = vega.data[name].create_monte_carlo(self.fiducial_model[name], self._item_scale(name),
+                                                              None, forecast)
+                    self.full_mocks[name].append(np.array(full))
                     mocks[name].append(vega.data[name].masked_mc_mock.copy())
             self.mocks = {name: np.array(v) for name, v in mocks.items()}
         vega.monte_carlo = True
@@ -409,7 +421,7 @@ class MonteCarloFits:
         self.engine = engine
         return self.mocks
 
-    def _draw_global(self, n_mocks):
+    def _draw_global(self, n_mocks, forecast=False):
         """Mocks of the joint data vector under a global covariance
         (Analysis.create_global_monte_carlo, vega/analysis.py:164-222): one Cholesky factor of
         scale * cov[mask][:, mask], mock = masked fiducial + L . randn(n) from the running
@@ -421,6 +433,8 @@ class MonteCarloFits:
         full_mask = np.concatenate([vega.data[n].data_mask for n in names])
         masked_cov = vega.global_cov[:, full_mask][full_mask, :]
         scale = 1 if self.scale is None else self.scale
+        if isinstance(scale, dict):
+            raise ValueError('A global covariance takes one scale, not one per correlation.')
         chol = None
         if masked_cov.shape[0] >= utils.DEVICE_LINALG_MIN and self.torch.cuda.is_available():
             # DESI-sized joint covariance (9540 rows): factor on the device (init time)
@@ -440,8 +454,11 @@ class MonteCarloFits:
             else:
                 raise ValueError('Input fiducial has unknown size. It must match the data or the model.')
         fid = np.concatenate(fid)[full_mask]
-        z = np.stack([np.random.randn(fid.size) for _ in range(n_mocks)])
-        joint = fid[None, :] + z @ chol.T
+        if forecast:                        # vega/analysis.py:214-215: the masked fiducial itself
+            joint = np.tile(fid, (n_mocks, 1))
+        else:
+            z = np.stack([np.random.randn(fid.size) for _ in range(n_mocks)])
+            joint = fid[None, :] + z @ chol.T
         self.global_mocks = joint
         edges = np.cumsum([0] + [int(vega.data[n].data_mask.sum()) for n in names])
         mocks = {n: np.ascontiguousarray(joint[:, edges[i]:edges[i + 1]]) for i, n in enumerate(names)}
@@ -520,11 +537,61 @@ class BatchedAnalysis:
         self.max_iter, self.edm_tol, self.verbose = max_iter, edm_tol, verbose
         self.grids = {}
         self.scan_results = None
+        self._vega = None
+        self.has_monte_carlo = False
+        self.current_mc_mock = None
 
     @classmethod
     def from_vega(cls, vega, **kw):
         names = list(vega.sample_params['limits'].keys())
-        return cls(lambda theta: vega.chi2_batch(theta, names), vega.sample_params, vega.main_config, **kw)
+        self = cls(lambda theta: vega.chi2_batch(theta, names), vega.sample_params, vega.main_config, **kw)
+        self._vega = vega
+        return self
+
+    def run_monte_carlo(self, fiducial_model, num_mocks=1, seed=0, scale=None, forecast=False,
+                        run_mc_fits=True):
+        """`Analysis.run_monte_carlo` (vega/analysis.py:224-308; the loop of
+        bin/run_vega_mc_mpi.py:62 and bin/run_vega_mc_fits_mpi.py:11-78): `num_mocks` Gaussian mocks
+        around `fiducial_model` from np.random.seed(seed), each fitted over the [monte carlo]
+        sample set.  The reference draws and fits one mock at a time; here all mocks are drawn
+        from the same random stream in the same order, uploaded once and fitted in lock-step
+        (MonteCarloFits).  Fills the reference's result attributes: mc_bestfits[param] ->
+        [num_mocks, 2] (value, error), mc_covariances, mc_chisq, mc_valid_minima,
+        mc_valid_hesse, mc_mocks, mc_failed_mask."""
+        vega = self._vega
+        if vega is None:
+            raise RuntimeError('run_monte_carlo needs the interface: build with BatchedAnalysis.from_vega.')
+        assert vega.mc_config is not None, 'No Monte Carlo config provided'
+        mc = MonteCarloFits(vega, fiducial_model=fiducial_model, scale=scale)
+        mc.draw(num_mocks, seed=seed, forecast=forecast)
+        if vega._use_global_cov:
+            self.mc_mocks = {'global': [m for m in mc.global_mocks]}
+        else:
+            self.mc_mocks = {name: list(v) for name, v in mc.full_mocks.items()}
+        self.mc_bestfits, self.mc_covariances, self.mc_chisq = {}, [], []
+        self.mc_valid_minima, self.mc_valid_hesse, self.mc_failed_mask = [], [], []
+        self.mc_fits = None
+        if run_mc_fits:
+            res = mc.fit(max_iter=self.max_iter, edm_tol=self.edm_tol)
+            self.mc_fits = res
+            free = res['free']
+            for j, name in enumerate(mc.names):
+                self.mc_bestfits[name] = np.column_stack([res['theta'][:, j], res['errors'][:, j]])
+            for m in range(num_mocks):
+                cov = np.zeros((len(mc.names), len(mc.names)))
+                ok = True
+                try:
+                    cov[np.ix_(free, free)] = 2.0 * np.linalg.inv(res['hess'][m])
+                    ok = bool(np.all(np.linalg.eigvalsh(res['hess'][m]) > 0))
+                except np.linalg.LinAlgError:
+                    ok = False
+                self.mc_covariances.append(cov)
+                self.mc_chisq.append(float(res['fval'][m]))
+                self.mc_valid_minima.append(bool(res['converged'][m]))
+                self.mc_valid_hesse.append(ok)
+                self.mc_failed_mask.append(False)
+        self.has_monte_carlo = True
+        return self.mc_bestfits
 
     def chi2_scan(self):
         if 'chi2 scan' not in self.config:

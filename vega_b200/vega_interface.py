@@ -439,6 +439,53 @@ class VegaInterface:
         vega/vega_interface.py:646-663)."""
         return self.minimizer
 
+    # -- Monte Carlo set-up (vega/vega_interface.py:448-545) ---------------------------------------
+    def get_fiducial_for_monte_carlo(self, print_func=print):
+        """Fiducial model the mocks are drawn around (vega/vega_interface.py:448-504): the
+        [mc parameters] over the best fit of an initial fit when [sample] is not empty, from
+        measured files (`use_measured_fiducial`), or from the full P(k) (`use_full_pk_for_mc`)."""
+        control = self.main_config['control']
+        mc_params = dict(self.mc_config['params'])
+        if control.get('mc_start_from_fit', None) is not None:
+            raise NotImplementedError('mc_start_from_fit reads a previous result file through FitResults '
+                                      '(vega/postprocess), which is outside the B200 path.')
+        if self.sample_params['limits']:
+            print_func('Running initial fit')
+            self.minimize()
+            mc_params = {**self.minimizer.values, **mc_params}
+            print_func(f'Set template parameters to {mc_params}.')
+        if control.getboolean('use_measured_fiducial', False):
+            fiducial_model = {}
+            for name in self.corr_items:
+                with fitsio.open(utils.find_file(control.get(f'mc_fiducial_{name}'))) as hdul:
+                    fiducial_model[name] = np.array(hdul[1].data['DA'], dtype=float)
+            return fiducial_model
+        if control.getboolean('use_full_pk_for_mc', False):
+            return self.compute_model(mc_params, run_init=False, direct_pk=self.fiducial['pk_full'])
+        return self.compute_model(mc_params, run_init=False)
+
+    def initialize_monte_carlo(self, scale=None, print_func=print):
+        """One mock in every Data object (or one joint mock under a global covariance), the
+        minimizer reset to the [monte carlo] sample set, Monte Carlo mode on
+        (vega/vega_interface.py:506-545; bin/run_vega_mpi.py:64, vega/scripts/run_vega.py:24)."""
+        from .drivers import BatchedMinimizer, MonteCarloFits
+        assert self.mc_config is not None, 'No Monte Carlo config provided'
+        fiducial_model = self.get_fiducial_for_monte_carlo(print_func)
+        sample = self.mc_config['sample']
+        names = list(sample['limits'].keys())
+        self.minimizer = BatchedMinimizer(lambda theta: self.chi2_batch(theta, names), sample)
+        control = self.main_config['control']
+        forecast = control.getboolean('forecast', False)
+        seed = control.getint('mc_seed', 0)
+        if self._use_global_cov and scale is None and 'global_cov_rescale' in control:
+            scale = control.getfloat('global_cov_rescale')
+        mc = MonteCarloFits(self, fiducial_model=fiducial_model, scale=scale)
+        mc.draw(1, seed=seed, forecast=forecast)        # leaves monte_carlo = True
+        self._mc_fits = mc
+        if self._use_global_cov:
+            return mc.global_mocks[0]
+        return {name: mc.full_mocks[name][0] for name in self.corr_items}
+
     def compute_sensitivity(self, nominal=None, frac=0.1, verbose=True):
         """Model sensitivity to each floating parameter (vega/vega_interface.py:956-1071):
         central differences at value +/- frac * error of the peak / smooth `core` components,
