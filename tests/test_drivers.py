@@ -366,3 +366,13 @@ def test_monte_carlo_surface_of_the_scripts(tmp_path):
         pull = (best[name][:, 0] - truth) / best[name][:, 1]
         assert np.all(np.abs(pull) < 5), (name, pull)
     vega.monte_carlo = False
+    # mc_start_from_fit: template parameters from the BESTFIT table of a result file
+    # (vega/vega_interface.py:466-471), [mc parameters] on top
+    from vega_b200 import fitsio
+    fit_file = tmp_path / 'fit.fits'
+    fitsio.write_tables(fit_file, [('BESTFIT', {}, {'names': np.array(['bias_eta_LYA', 'beta_LYA']),
+                                                    'values': np.array([-0.199, 1.7])})])
+    vega.main_config['control']['mc_start_from_fit'] = str(fit_file)
+    got = vega.get_fiducial_for_monte_carlo(print_func=quiet)
+    want = vega.compute_model({'bias_eta_LYA': -0.199, 'beta_LYA': 1.7, 'ap': 1.01, 'at': 0.99}, run_init=False)
+    assert all(np.array_equal(got[n], want[n]) for n in want)

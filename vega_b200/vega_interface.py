@@ -446,10 +446,16 @@ class VegaInterface:
         measured files (`use_measured_fiducial`), or from the full P(k) (`use_full_pk_for_mc`)."""
         control = self.main_config['control']
         mc_params = dict(self.mc_config['params'])
-        if control.get('mc_start_from_fit', None) is not None:
-            raise NotImplementedError('mc_start_from_fit reads a previous result file through FitResults '
-                                      '(vega/postprocess), which is outside the B200 path.')
-        if self.sample_params['limits']:
+        mc_start_from_fit = control.get('mc_start_from_fit', None)
+        if mc_start_from_fit is not None:
+            # FitResults.params (vega/postprocess/fit_results.py:50-53): BESTFIT names -> values
+            print_func(f'Reading input fit {mc_start_from_fit}')
+            with fitsio.open(utils.find_file(mc_start_from_fit)) as hdul:
+                best = next(h for h in hdul[1:] if h.header.get('EXTNAME') == 'BESTFIT')
+                fit_params = {str(n).strip(): float(v) for n, v in zip(best.data['names'], best.data['values'])}
+            mc_params = {**fit_params, **mc_params}
+            print_func(f'Set template parameters to {mc_params}.')
+        elif self.sample_params['limits']:
             print_func('Running initial fit')
             self.minimize()
             mc_params = {**self.minimizer.values, **mc_params}
