@@ -379,13 +379,13 @@ def test_model_call_shapes_and_stage_components():
                                         ('smooth', fid['pk_smooth'], False)):
             lp['peak'] = peak
             pk_ref = pk_model(cm.grid, pk_lin, lp)
-            pk_got = model.pk(pars, component)
+            pk_got = model.pk_grid(pars, component)
             assert np.max(np.abs(pk_got - pk_ref)) <= 1e-12 * np.max(np.abs(pk_ref)), (name, component)
             ells_ref = cm.transform.multipoles(pk_ref)
             ells_got = model.pk_ells(pars, component)
             assert np.max(np.abs(ells_got - ells_ref)) <= 1e-11 * np.max(np.abs(ells_ref)), (name, component)
             xi_ref = cm.xi_core.compute(pk_ref, pk_lin, cm.transform, lp)
-            xi_got = model.xi(pars, component)
+            xi_got = model.xi_of(pars, component)
             assert np.max(np.abs(xi_got - xi_ref)) <= XI_RTOL * np.max(np.abs(xi_ref)), (name, component)
     direct = fid['pk_full'] * (1 + 0.02 * np.cos(np.log(fid['k'])))
     got = vega.models['lyalya_qso'].compute_direct(pars, direct)
@@ -418,3 +418,38 @@ def test_device_covariance_inverse_and_log_det():
     assert abs(got_det - ref_det) <= 1e-8
     r = rng.standard_normal(n) * 1e-4
     assert abs(r @ got_inv @ r - r @ ref_inv @ r) <= 1e-6
+
+
+@pytest.mark.gpu
+def test_component_tables_of_write_pk_and_write_cf(tmp_path):
+    """The save-components dictionaries (vega/model.py:113-116,151-153) and the PK_ / Xi_ tables
+    write_pk / write_cf add to the result file (vega/output.py:100-110,351-440), against the
+    oracle's per-stage outputs; peak and smooth recombine to the model."""
+    import configparser
+    from vega_b200 import VegaInterface, fitsio, utils
+    cfg = configparser.ConfigParser()
+    cfg.optionxform = lambda option: option
+    cfg.read(utils.find_file('configs/full_configs/main.ini'))
+    cfg['output'] = {'filename': str(tmp_path / 'components'), 'write_cf': 'True', 'write_pk': 'True'}
+    path = tmp_path / 'main.ini'
+    with open(path, 'w') as f:
+        cfg.write(f)
+    vega = VegaInterface(str(path))
+    pars = {'bias_eta_LYA': -0.21, 'beta_LYA': 1.55, 'ap': 1.01, 'bao_amp': 0.9}
+    model = vega.compute_model(pars)
+    out = vega.output.write_results(model, vega._get_lcl_prms(pars), models=vega.models)
+    hdul = fitsio.open(out)
+    by_name = {h.header.get('EXTNAME'): h for h in hdul[1:]}
+    for name in vega.corr_items:
+        m = vega.models[name]
+        pk, xi = by_name['PK_' + name], by_name['Xi_' + name]
+        assert np.array_equal(pk.data['peak_core'], m.pk['peak']['core'])
+        assert np.array_equal(xi.data['raw_smooth_core'], m.xi['smooth']['core'])
+        assert np.array_equal(xi.data['distorted_peak_core'], m.xi_distorted['peak']['core'])
+        # bao_amp * peak + smooth is the model (vega/model.py:186)
+        total = 0.9 * m.xi_distorted['peak']['core'] + m.xi_distorted['smooth']['core']
+        assert np.max(np.abs(total - model[name])) <= 1e-13 * np.max(np.abs(model[name]))
+        # the same arrays as the per-stage accessors (parity-tested against the oracle's stages above;
+        # the distorted pair is pinned against the unmodified reference by the sensitivity golden)
+        assert np.array_equal(m.xi['peak']['core'], m.xi_of(pars, 'peak'))
+        assert pk.data['smooth_core'].shape == m.pk['smooth']['core'].shape == (1000, vega.fiducial['k'].size)

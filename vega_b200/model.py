@@ -17,6 +17,10 @@ class Model:
         self._name = name
         self._index = list(vega.corr_items).index(name)
         self._corr_item = vega.corr_items[name]
+        # the save-components dictionaries (vega/model.py:41-45), filled by save_components()
+        self.pk = {'peak': {}, 'smooth': {}, 'full': {}}
+        self.xi = {'peak': {}, 'smooth': {}, 'full': {}}
+        self.xi_distorted = {'peak': {}, 'smooth': {}, 'full': {}}
 
     # -- helpers ------------------------------------------------------------------------------
     def _changed(self, pars):
@@ -59,7 +63,7 @@ class Model:
             raise utils.VegaBoundsError
         return out[0], engine
 
-    def pk(self, pars=None, component='smooth'):
+    def pk_grid(self, pars=None, component='smooth'):
         """P(k, mu) of one component on the (mu, k) grid -- PowerSpectrum.compute
         (vega/power_spectrum.py:87-196) with that component's linear P(k)."""
         out, engine = self._stage(pars, 0, component)
@@ -75,10 +79,37 @@ class Model:
         eval_index = {'peak': 0, 'smooth': 1}[component] if isinstance(component, str) else int(component)
         return out.reshape(-1, n_ell, nk_pad)[eval_index][:, :nk]
 
-    def xi(self, pars=None, component='smooth'):
+    def xi_of(self, pars=None, component='smooth'):
         """xi of the peak or smooth component on the model grid, before metals / broadband /
         distortion -- CorrelationFunction.compute (vega/correlation_func.py:117-161)."""
         out, engine = self._stage(pars, 3, component)
         n_model = self._corr_item.model_coordinates.rp_grid.size
         ld = (n_model + 15) // 16 * 16
         return out.reshape(-1, ld)[{'peak': 0, 'smooth': 1}[component]][:n_model]
+
+    def save_components(self, pars=None):
+        """Fill `pk`, `xi` and `xi_distorted` as the reference does with `save-components` on
+        (vega/model.py:113-116,151-153; write_pk / write_cf of vega/output.py:100-110).  With the
+        default `no-metal-decomp = True` the reference stores the `core` entry of the peak and
+        the smooth component only (the metal dictionaries are merged in the other branch,
+        :125-131): P(k, mu) and xi before metals, and the component after metals, broadband and
+        distortion.  The distorted components come from one batch of two vectors -- the model is
+        bao_amp * peak + smooth with every later stage linear (:186), so they are M(bao_amp = 0)
+        and M(1) - M(0)."""
+        changed = self._changed(pars)
+        changed.pop('bao_amp', None)
+        names = list(changed) + ['bao_amp']
+        theta = np.array([[changed[n] for n in names[:-1]] + [a] for a in (0.0, 1.0)], dtype=np.float64)
+        models, status = self._vega.compute_model_batch(theta, names)
+        from . import _lib
+        if np.any(status & _lib.STATUS_ARINYO):
+            raise utils.VegaArinyoError
+        if np.any(status & _lib.STATUS_BOUNDS):
+            raise utils.VegaBoundsError
+        m = models[self._name]
+        self.xi_distorted['smooth']['core'] = m[0].copy()
+        self.xi_distorted['peak']['core'] = m[1] - m[0]
+        for component in ('peak', 'smooth'):
+            self.pk[component]['core'] = self.pk_grid(changed, component).copy()
+            self.xi[component]['core'] = self.xi_of(changed, component).copy()
+        return self

@@ -4,8 +4,8 @@ correlation fit statistics as header cards), `BESTFIT` (names, values, errors, c
 FVAL / VALID / ACCURATE) and `SCAN` (one column per sampled parameter + fval, grid description
 in the header).  Written with the package's own FITS writer (astropy is not in the image).
 
-Not written: the HDF variant and the `write_pk` / `write_cf` component tables (the per-stage
-components are available from `VegaInterface.models[name].pk / pk_ells / xi`).
+`write_pk` / `write_cf` add the reference's `PK_<name>` / `Xi_<name>` component tables
+(vega/output.py:100-110,351-440) from `Model.save_components`.  Not written: the HDF variant.
 """
 import os
 from pathlib import Path
@@ -37,15 +37,24 @@ class Output:
                       scan_results=None, models=None):
         if self.type != 'fits':
             raise NotImplementedError('Only type = fits is written by this package.')
-        if self.output_pk or self.output_cf:
-            raise NotImplementedError('write_pk / write_cf tables are not written; use '
-                                      'VegaInterface.models[name].pk / pk_ells / xi.')
         if self.data is None:
             raise ValueError('Output object was initialized with an invalid data object.'
                              ' Reinitialize with a valid vega.data object.')
         tables = self._model_tables(corr_funcs, params, bestfit_corr_stats)
         if minimizer is not None:
             tables.append(self._bestfit_table(minimizer))
+        if self.output_pk or self.output_cf:        # vega/output.py:100-110
+            assert models is not None
+            for model in models.values():
+                model.save_components(params)
+            if self.output_pk:
+                tables += [('PK_' + key, {}, self._get_components(model.pk)) for key, model in models.items()]
+            if self.output_cf:
+                for key, model in models.items():
+                    columns = {**self._get_components(model.xi, 'raw_'),
+                               **self._get_components(model.xi_distorted, 'distorted_')}
+                    size = max(v.shape[0] for v in columns.values())     # model grid > distorted grid: NaN tail
+                    tables.append(('Xi_' + key, {}, {k: _pad(v, size) for k, v in columns.items()}))
         if scan_results is not None:
             assert minimizer is not None
             tables.append(self._scan_table(scan_results))
@@ -56,6 +65,20 @@ class Output:
             raise OSError(f"File {path} already exists. Set overwrite = True in [output] to replace it.")
         fitsio.write_tables(path, tables)
         return path
+
+    # vega/output.py:401-440
+    @staticmethod
+    def _get_components(model_components, name_prefix=''):
+        """Columns `<prefix><part>_core` (and `<prefix><part>_<m1>_<m2>` for saved metal terms) of
+        the peak / smooth parts that hold something."""
+        columns = {}
+        for part, data in model_components.items():
+            if not data:
+                continue
+            for key, item in data.items():
+                name = name_prefix + part + ('_core' if key == 'core' else f'_{key[0]}_{key[1]}')
+                columns[name] = np.asarray(item, dtype=float)
+        return columns
 
     # vega/output.py:144-235
     def _model_tables(self, corr_funcs, params, bestfit_corr_stats=None):
