@@ -349,8 +349,8 @@ def test_c3_full_size_desi_shaped(tmp_path):
     for b in (0, 3, 2 * len(names)):
         ref = oracle.chi2(dict(zip(names, theta[b])))
         assert abs(chi2[b] - ref) <= CHI2_ATOL * max(1.0, abs(ref) / 1e4), (b, chi2[b], ref)
-    # the same vectors in a batch large enough (>= 96) for the DMMA tile of the rp-only metal
-    # matrices (metal_rp_dmma_kernel; the stencil above goes through the FMA tile)
+    # the same vectors in a larger batch (different CTA scheduling, split-K choices and chunking):
+    # results do not depend on the batch composition
     big = vega.chi2_batch(np.tile(theta, (5, 1)), names)
     assert np.max(np.abs(big.reshape(5, -1) - chi2[None, :])) <= 1e-7
     model = vega.compute_model(dict(zip(names, theta[3])))

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -1106,10 +1107,14 @@ int build_metal_operands(Corr& c, const EvalLayout& L, DevBuf& mcat, DevBuf& mrp
 
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st) {
-  // large batches go to the DMMA tile; up to a gradient stencil (and the plan-time folds, the
-  // scalar API) the FMA kernel's 40 x 32 tiles spread the few vectors over more CTAs (measured:
-  // 31 vectors 0.31 ms FMA vs 0.58 ms DMMA, 451 vectors 2.27 ms vs 1.66 ms with 80-wide tiles)
-  if (B >= 96) {
+  // the DMMA tile at every batch size (measured on C3: one vector 0.30 -> 0.17 ms, 31 vectors
+  // 0.31 -> 0.18 ms, 451 vectors 2.27 -> 0.89 ms against the FMA tile, which stays reachable
+  // through VG_RP_DMMA_MIN for comparison)
+  static const long long dmma_min = [] {
+    const char* e = std::getenv("VG_RP_DMMA_MIN");
+    return e ? std::atoll(e) : 1LL;
+  }();
+  if (B >= dmma_min) {
     dim3 grid(vg_cdiv(c.rp_nt, vg::MRD_TN), vg_cdiv(c.rp_np, vg::MRD_TM), (unsigned)B);
     vg::metal_rp_dmma_kernel<<<grid, vg::MRD_THREADS, 0, st>>>(xmet, n_metal, c.ld_model, A, c.rp_np, c.rp_nt, met);
   } else {
