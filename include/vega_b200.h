@@ -25,6 +25,19 @@
 extern "C" {
 #endif
 
+/* Return codes of every entry point (text of the last failure: vg_last_error()) */
+#define VG_OK 0
+#define VG_ERR_CUDA 1    /* a CUDA call failed, or there is no CUDA device (no CPU fallback) */
+#define VG_ERR_ARG 2     /* bad argument */
+#define VG_ERR_STATE 3   /* call out of order (e.g. a new data mask after vg_plan_finalize) */
+
+/* Per-vector status bits written by the kernels into status[b]: the model-domain failures the
+ * reference raises as exceptions (vega/utils.py:444-453) and VegaInterface.chi2 turns into 1e100
+ * (vega/vega_interface.py:268-279). */
+#define VG_STATUS_BOUNDS 1      /* r outside the FFTLog range  -> VegaBoundsError */
+#define VG_STATUS_ARINYO 2      /* NaN/Inf in the Arinyo D_NL  -> VegaArinyoError */
+#define VG_STATUS_NONFINITE 4   /* a non-finite model bin */
+
 #define VG_MAX_BB_TERMS 8
 
 /* P(k,mu) factor bits (vega/power_spectrum.py:118-194) */
@@ -157,6 +170,11 @@ int vg_plan_create(int32_t n_params, const double* base, int32_t n_theta, const 
                    const double* pk_fid, int32_t nmu, const double* mu, int32_t n_ell,
                    const double* wleg, int32_t idx_bao_amp, vg_plan** out);
 int vg_plan_destroy(vg_plan* plan);
+/* Blinding at the parameter level (vega/vega_interface.py:405-419, vega/utils.py:375-393), per
+ * theta column j: theta[b][j] + offset[j] enters the model (offset = pi - exp(v^2) for a blinded
+ * parameter, 0 otherwise), and force_one[j] != 0 pins the column to 1 whatever the caller passed
+ * (the BLIND_FIXED_PARS).  Never called = identity. */
+int vg_plan_set_theta_transform(vg_plan* plan, const double* offset, const int32_t* force_one);
 /* Fvoigt profile table for model-hcd = fvoigt (vega/power_spectrum.py:360-380) */
 int vg_plan_set_fvoigt(vg_plan* plan, int32_t n, const double* x, const double* f);
 /* UVB shot-noise A(tau) table (vega/correlation_func.py:597-626) */

@@ -797,11 +797,19 @@ class Oracle:
         self.monte_carlo = False
 
     def local_params(self, params=None):
-        """vega/vega_interface.py:389-421 (blinding offsets are not staged here: the
-        blinding files live at NERSC, vega/utils.py:337-349)."""
+        """vega/vega_interface.py:389-421: merge, then -- on blinded data with offsets loaded
+        (setup._rnsps) -- theta += pi - exp(v^2) for the blinded names (vega/utils.py:375-393) and
+        the BLIND_FIXED_PARS (vega/utils.py:16-18) pinned to 1."""
         lp = copy.deepcopy(self.s.params)
         if params is not None:
             lp.update(params)
+        rnsps = getattr(self.s, '_rnsps', None)
+        if rnsps is not None:
+            for par, val in rnsps.items():
+                lp[par] += np.pi - np.exp(val**2)
+            for par in lp:
+                if par in ('ap_full', 'at_full', 'aiso_full', 'epsilon_full', 'phi_full'):
+                    lp[par] = 1.
         return lp
 
     def compute_model(self, params=None, direct_pk=None):

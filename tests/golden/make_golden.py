@@ -125,6 +125,25 @@ def main():
     # Model.compute_direct through the direct_pk argument (vega/model.py:189-208)
     CONFIGS['full_direct'] = CONFIGS['full']
     PERTURBED['full_direct'] = PERTURBED['full']
+    # option variants of the auto + cross configuration (tests/helpers.py: VARIANTS)
+    from helpers import VARIANTS, make_variant_config, variant_cases
+    for vkey, spec in VARIANTS.items():
+        CONFIGS[vkey] = make_variant_config(f'/tmp/vega_golden_{vkey}', vkey, base=base)
+        PERTURBED[vkey] = variant_cases(vkey, ('lyalya_lyalya', 'lyalya_qso'))
+    # blinded data + parameter-level blinding (vega/vega_interface.py:389-421,853-886).  The one
+    # thing replaced in the reference is WHERE get_blinding finds its offsets: its table of NERSC
+    # files ships as None (vega/utils.py:331-341), so the reader below takes them from the
+    # synthetic npz of helpers.make_blind_config with the reference's own per-parameter rule (:369)
+    from helpers import make_blind_config, BLIND_CASES
+    CONFIGS['blind'], blind_file = make_blind_config('/tmp/vega_golden_blind', base=base)
+    PERTURBED['blind'] = BLIND_CASES
+    import vega.utils as ref_utils
+
+    def get_blinding_from_file(blind_pars, blinding_strat):
+        assert blinding_strat is not None, 'Blinding failed, do not run!!!'
+        with np.load(blind_file) as file:
+            return {par: float(file[par]) for par in blind_pars}
+    ref_utils.get_blinding = get_blinding_from_file
     notes = {'new_metals_rp': 'helpers.make_new_metals_config(rp_only=True): full_configs auto + cross, '
                               'new_metals = True, rp_only_metal_mats = True, seeded weight tables',
              'new_metals_2d': 'same with rp_only_metal_mats = False',
@@ -134,6 +153,12 @@ def main():
              'c1_marg': f"{CONFIGS['c1']} + [model] {MARG_CUTS} + distortion-file (55x55 bins)",
              'c1_marg_fit': f"{CONFIGS['c1']} + [model] {MARG_FIT} + [control] marginalize-in-fit "
                             "+ distortion-file (55x55 bins, synthetic.distortion_matrix)"}
+    for vkey in VARIANTS:
+        notes[vkey] = f'helpers.make_variant_config({vkey!r}): full_configs auto + cross with ' \
+                      f'{ {k: v for k, v in VARIANTS[vkey].items() if k != "cases"} }'
+    notes['blind'] = ('helpers.make_blind_config: auto + cross on data copies with BLINDING = desi_dr3 and a '
+                      'DA_BLIND column, growth_rate sampled and blinded (offset file value 1.06), smooth '
+                      'component scaled by ap_full / at_full (pinned to 1 by the blinding)')
     only = sys.argv[1:]
     if only:      # regenerate a subset, keep the rest of the stored outputs
         old = np.load(REPO / 'tests' / 'golden' / 'reference_outputs.npz')
@@ -144,6 +169,8 @@ def main():
         if only and key not in only:
             continue
         vega = VegaInterface(ini)
+        if key == 'blind':
+            assert vega._blind and vega._rnsps == {'growth_rate': 1.06}, (vega._blind, vega._rnsps)
         cases = [{}] + PERTURBED[key]
         meta[key] = {'ini': notes.get(key, ini), 'cases': cases, 'corr': list(vega.corr_items)}
         direct = None

@@ -247,3 +247,256 @@ def make_c3_config(tmp_dir, dmat_bins=75):
     return make_new_metals_config(
         tmp_dir, True, corrs=('lyalya_lyalya', 'lyalya_lyalyb', 'lyalya_qso', 'lyalyb_qso'),
         model={'fast_metals': True}, dmat_bins=dmat_bins)
+
+
+# ---------------------------------------------------------------------------------------------
+# Option variants of the reference's auto + cross configuration.  tests/golden/make_golden.py runs
+# the UNMODIFIED reference on each of them (-> reference_outputs.npz); the oracle and the CUDA path
+# are compared with those outputs in tests/test_reference_golden.py.  Each one turns on model
+# options no other configuration of tests/ reaches.
+# ---------------------------------------------------------------------------------------------
+_AUTO, _CROSS = 'lyalya_lyalya', 'lyalya_qso'
+_METALS = ('SiII(1190)', 'SiII(1193)', 'SiIII(1207)', 'SiII(1260)', 'CIV(eff)')
+
+
+def _separate_auto_bias_params():
+    """bias_{M1}_{M2} for every metal x metal pair of the auto-correlation with M1 != M2
+    (vega/metals.py:297-308), distinct values."""
+    out, k = {}, 0
+    for i, m1 in enumerate(_METALS):
+        for m2 in _METALS[i + 1:]:
+            out[f'bias_{m1}_{m2}'] = 0.6 + 0.07 * k
+            k += 1
+    return out
+
+
+VARIANTS = {
+    # vega/power_spectrum.py:224-261 (HeII branch), :190-194 + vega/utils.py:423-441 (k^n damping),
+    # :281-288 (per-correlation HCD bias / beta)
+    'v_pk': dict(
+        sections={'model': {'HeII-reionization': True, 'pk-damping-scale': 0.9, 'pk-damping-power': 3},
+                  'metals': {'pk-damping-scale': 1.3}},
+        main={'parameters': {'lambda_HeII': 180., 'bias_gamma_e': 0.07, 'bias_hcd_LYAxLYA': -0.035,
+                             'beta_hcd_LYAxQSO': 0.55}},
+        cases=[{'bias_gamma_e': 0.11, 'lambda_HeII': 250., 'bias_prim': -0.5},
+               {'bias_hcd_LYAxLYA': -0.06, 'beta_hcd_LYAxQSO': 0.8, 'bias_hcd': -0.03, 'beta_LYA': 1.4}]),
+    # vega/correlation_func.py:597-686 (UV shot noise), :553-595 + vega/model.py:133-135 (DESI
+    # instrumental systematics, auto-correlation only)
+    'v_xi': dict(
+        sections={'model': {'UVB-shotnoise': True}},
+        per_corr={_AUTO: {'model': {'desi-instrumental-systematics': True}}},
+        main={'parameters': {'uv_shotnoise_amp': 0.4, 'desi_inst_sys_amp': 2.5e-4}},
+        cases=[{'uv_shotnoise_amp': 0.9, 'lambda_uv': 220., 'bias_gamma': 0.15},
+               {'desi_inst_sys_amp': 5e-4, 'ap': 0.97, 'at': 1.04, 'drp_QSO': -0.4}]),
+    # the same additive terms on the rescaled coordinates (vega/correlation_func.py:470-475,681-684)
+    'v_xi_rescaled': dict(
+        sections={'model': {'UVB-shotnoise': True, 'rescale-coords-systematics': True}},
+        main={'parameters': {'uv_shotnoise_amp': 0.4},
+              'cosmo-fit type': {'smooth-scaling': True, 'full-shape-alpha': True}},
+        extra_main_params={'ap_full': 1.02, 'at_full': 0.99},
+        cases=[{'ap_full': 0.96, 'at_full': 1.03, 'uv_shotnoise_amp': 0.7, 'qso_rad_strength': 0.9},
+               {'drp_QSO': 1.1, 'qso_rad_asymmetry': 0.3, 'qso_rad_lifetime': 40.}]),
+    # vega/broadband_poly.py:98-116: multiplicative terms before and after the distortion matrix,
+    # next to additive ones in both positions and coordinate systems
+    'v_bb': dict(
+        replace={'broadband': {'bb1': 'mul pre r,mu 0:1:1 0:2:2', 'bb2': 'mul post rp,rt 0:1:1 0:1:1',
+                               'bb3': 'add pre rp,rt 0:1:1 0:1:1', 'bb4': 'add post r,mu 0:2:1 0:6:2',
+                               'bb5': 'mul pre r,mu 1:2:1 0:0:1'}},
+        bb_values=True,
+        cases=[{'BB-{corr}-0 mul pre r,mu (1,2)': 0.04, 'BB-{corr}-1 mul post rp,rt (1,1)': -0.03,
+                'BB-{corr}-4 mul pre r,mu (2,0)': 0.02},
+               {'BB-{corr}-2 add pre rp,rt (0,1)': 2e-4, 'BB-{corr}-3 add post r,mu (1,2)': 3e-3,
+                'BB-{corr}-1 mul post rp,rt (0,0)': 0.05, 'bao_amp': 0.8}]),
+    # vega/scale_parameters.py:38-230: phi_alpha with a rescaled smooth component
+    'v_phi_alpha': dict(
+        main={'cosmo-fit type': {'cosmo fit func': 'phi_alpha', 'smooth-scaling': True}},
+        extra_main_params={'phi': 1.02, 'alpha': 0.99, 'phi_smooth': 0.97, 'alpha_smooth': 1.01},
+        cases=[{'phi': 0.95, 'alpha': 1.03}, {'phi_smooth': 1.04, 'alpha_smooth': 0.96, 'bao_amp': 1.1}]),
+    # phi_alpha in a split full-shape fit with one smooth alpha per correlation
+    'v_phi_full': dict(
+        main={'cosmo-fit type': {'cosmo fit func': 'phi_alpha', 'full-shape': True, 'two-alpha-smooth': True}},
+        extra_main_params={'phi_full': 1.03, 'alpha': 0.98, 'alpha_smooth_LYAxLYA': 1.02,
+                           'alpha_smooth_LYAxQSO': 0.97},
+        cases=[{'phi_full': 0.96, 'alpha': 1.02}, {'alpha_smooth_LYAxLYA': 0.95, 'alpha_smooth_LYAxQSO': 1.05}]),
+    # aiso_epsilon, full-shape with its own alpha pair, metals rescaled too (metal-scaling)
+    'v_aiso': dict(
+        main={'cosmo-fit type': {'cosmo fit func': 'aiso_epsilon', 'full-shape': True, 'full-shape-alpha': True,
+                                 'metal-scaling': True}},
+        extra_main_params={'aiso': 1.0, 'epsilon': 0.0, 'aiso_full': 1.01, 'epsilon_full': 0.012},
+        cases=[{'aiso_full': 0.97, 'epsilon_full': -0.02}, {'aiso_full': 1.04, 'epsilon_full': 0.03,
+                                                              'bias_eta_SiIII(1207)': -0.006}]),
+    # aiso_epsilon on the peak only (the BAO branch of get_ap_at)
+    'v_aiso_bao': dict(
+        main={'cosmo-fit type': {'cosmo fit func': 'aiso_epsilon'}},
+        extra_main_params={'aiso': 1.01, 'epsilon': 0.015},
+        cases=[{'aiso': 0.96, 'epsilon': -0.03}]),
+    # vega/metals.py:285-313: one beta for all metals, extra bias per metal x metal pair
+    'v_metal_flags': dict(
+        sections={'model': {'single-metal-beta': True, 'separate-metal-auto-biases': True}},
+        extra_main_params={'beta_metals': 0.42, **_separate_auto_bias_params()},
+        cases=[{'beta_metals': 0.7, 'bias_SiII(1190)_SiIII(1207)': 1.4},
+               {'bias_eta_SiII(1260)': -0.004, 'bias_SiII(1193)_CIV(eff)': 0.2, 'beta_LYA': 1.5}]),
+}
+
+
+def make_variant_config(tmp_dir, key, base='configs/full_configs/main.ini', corrs=(_AUTO, _CROSS)):
+    """Writes the configuration files of VARIANTS[key] under tmp_dir; returns the main ini path."""
+    import configparser
+    spec = VARIANTS[key]
+    tmp_dir = Path(tmp_dir)
+    tmp_dir.mkdir(parents=True, exist_ok=True)
+
+    def read(path):
+        cfg = configparser.ConfigParser()
+        cfg.optionxform = lambda option: option
+        cfg.read(utils.find_file(path))
+        return cfg
+
+    main = read(base)
+    new_paths = []
+    for path in main['data sets']['ini files'].split():
+        stem = Path(path).stem
+        if stem not in corrs:
+            continue
+        cfg = read(path)
+        for section, options in spec.get('replace', {}).items():
+            cfg[section] = {k: str(v) for k, v in options.items()}
+        layers = [spec.get('sections', {}), spec.get('per_corr', {}).get(stem, {})]
+        for layer in layers:
+            for section, options in layer.items():
+                for k, v in options.items():
+                    cfg[section][k] = str(v)
+        if spec.get('bb_values'):      # a value for every coefficient of the new broadband terms
+            for name, value in broadband_parameters(cfg['broadband'], cfg['data']['name']).items():
+                main['parameters'][name] = repr(value)
+        new_path = tmp_dir / Path(path).name
+        with open(new_path, 'w') as f:
+            cfg.write(f)
+        new_paths.append(str(new_path))
+    main['data sets']['ini files'] = ' '.join(new_paths)
+    for section, options in spec.get('main', {}).items():
+        for k, v in options.items():
+            main[section][k] = str(v)
+    for k, v in spec.get('extra_main_params', {}).items():
+        main['parameters'][k] = repr(v)
+    main['output']['filename'] = str(tmp_dir / 'out')
+    out = tmp_dir / 'main.ini'
+    with open(out, 'w') as f:
+        main.write(f)
+    return str(out)
+
+
+def broadband_parameters(bb_section, corr_name):
+    """Seeded values for every coefficient of a [broadband] section
+    (names: vega/broadband_poly.py:62,182)."""
+    rng = np.random.default_rng(11)
+    out = {}
+    for i, spec in enumerate(bb_section.values()):
+        w = spec.split()
+        lo1, hi1, s1 = (int(x) for x in w[3].split(':'))
+        lo2, hi2, s2 = (int(x) for x in w[4].split(':'))
+        scale = 0.02 if w[0] == 'mul' else 5e-4
+        for a in range(lo1, hi1 + 1, s1):
+            for b in range(lo2, hi2 + 1, s2):
+                out[f'BB-{corr_name}-{i} {w[0]} {w[1]} {w[2]} ({a},{b})'] = float(
+                    np.round(scale * rng.uniform(-1, 1), 6))
+    return out
+
+
+def variant_cases(key, corr_names):
+    """Perturbed parameter dictionaries of a variant ('{corr}' in a name = every correlation)."""
+    cases = []
+    for case in VARIANTS[key]['cases']:
+        out = {}
+        for name, value in case.items():
+            if '{corr}' in name:
+                for corr in corr_names:
+                    out[name.format(corr=corr)] = value
+            else:
+                out[name] = value
+        cases.append(out)
+    return cases
+
+
+# ---------------------------------------------------------------------------------------------
+# Blinded data (vega/data.py:305-340, vega/vega_interface.py:389-421,853-886, vega/utils.py:320-393)
+# ---------------------------------------------------------------------------------------------
+BLINDING_VALUES = {'growth_rate': 1.06}      # offset pi - exp(v^2) = +0.0657
+
+
+def copy_data_blinded(src, dst, strategy='desi_dr3'):
+    """Copy of a correlation file with a BLINDING card and a DA_BLIND column (DA shifted by a
+    smooth, deterministic amount so that reading the wrong column cannot go unnoticed)."""
+    from vega_b200 import fitsio
+    hdul = fitsio.open(utils.find_file(src))
+    tables = []
+    for i, hdu in enumerate(hdul[1:]):
+        header = {k: hdu.header[k] for k in ('RPMIN', 'RPMAX', 'RTMAX', 'NP', 'NT') if k in hdu.header}
+        cols = {name: np.asarray(hdu.data[name]) for name in hdu.columns.names}
+        if i == 0:
+            header['BLINDING'] = strategy
+            da = np.asarray(cols['DA'], dtype=float)
+            cols['DA_BLIND'] = da + 1e-5 * np.cos(0.01 * np.arange(da.size))
+        tables.append((hdu.header.get('EXTNAME', f'HDU{i + 1}'), header, cols))
+    fitsio.write_tables(dst, tables)
+    return str(dst)
+
+
+def make_blind_config(tmp_dir, base='configs/full_configs/main.ini', corrs=(_AUTO, _CROSS)):
+    """Auto + cross on blinded copies of the data files: growth_rate sampled (hence blinded),
+    smooth component rescaled by ap_full / at_full, which the blinding pins to 1.  Returns
+    (main ini path, blinding-offset file)."""
+    import configparser
+    tmp_dir = Path(tmp_dir)
+    tmp_dir.mkdir(parents=True, exist_ok=True)
+
+    def read(path):
+        cfg = configparser.ConfigParser()
+        cfg.optionxform = lambda option: option
+        cfg.read(utils.find_file(path))
+        return cfg
+
+    main = read(base)
+    new_paths = []
+    for path in main['data sets']['ini files'].split():
+        if Path(path).stem not in corrs:
+            continue
+        cfg = read(path)
+        cfg['data']['filename'] = copy_data_blinded(cfg['data']['filename'],
+                                                    tmp_dir / (Path(path).stem + '_blind.fits'))
+        new_path = tmp_dir / Path(path).name
+        with open(new_path, 'w') as f:
+            cfg.write(f)
+        new_paths.append(str(new_path))
+    main['data sets']['ini files'] = ' '.join(new_paths)
+    main['cosmo-fit type']['smooth-scaling'] = 'True'
+    main['cosmo-fit type']['full-shape-alpha'] = 'True'
+    main['parameters']['ap_full'] = '1.03'
+    main['parameters']['at_full'] = '0.98'
+    main['sample']['growth_rate'] = '0.5 1.5 0.96 0.1'
+    if 'control' not in main:
+        main['control'] = {}
+    main['control']['use_template_growth_rate'] = 'False'
+    main['output']['filename'] = str(tmp_dir / 'out')
+    out = tmp_dir / 'main.ini'
+    with open(out, 'w') as f:
+        main.write(f)
+    offsets = tmp_dir / 'blinding_offsets.npz'
+    np.savez(offsets, **BLINDING_VALUES)
+    return str(out), str(offsets)
+
+
+BLIND_CASES = [{'growth_rate': 1.05, 'beta_LYA': 1.5}, {'ap_full': 1.2, 'at_full': 0.8, 'ap': 1.01},
+               {'bias_eta_LYA': -0.19, 'growth_rate': 0.9}]
+
+
+def make_blind_vega(tmp_dir):
+    """The B200 interface on the blinded configuration, offsets from the synthetic file."""
+    main, offsets = make_blind_config(tmp_dir)
+    saved = dict(utils.BLINDING_FILES)
+    utils.BLINDING_FILES['desi_dr3'] = {'full-shape': offsets, 'bao': None}
+    try:
+        return VegaInterface(main)
+    finally:
+        utils.BLINDING_FILES.clear()
+        utils.BLINDING_FILES.update(saved)

@@ -150,6 +150,110 @@ def test_cuda_path_matches_reference_new_metals(key, tmp_path):
     check(key, vega.compute_model, vega.chi2, vega.log_lik, gold, meta)
 
 
+def variant_keys():
+    from helpers import VARIANTS
+    return list(VARIANTS)
+
+
+@pytest.mark.parametrize('key', variant_keys())
+def test_oracle_matches_reference_option_variants(key, tmp_path):
+    """Model options no other configuration reaches (tests/helpers.py: VARIANTS), each against the
+    unmodified reference: HeII, k^n damping, per-correlation HCD bias, UV shot noise, DESI
+    instrumental systematics, rescale-coords-systematics, multiplicative broadband (pre and post),
+    phi_alpha / aiso_epsilon with smooth-scaling / full-shape / two-alpha-smooth / metal-scaling,
+    single-metal-beta, separate-metal-auto-biases."""
+    from helpers import make_variant_config, static_tables
+    from oracle.vega_oracle import Oracle
+    from vega_b200 import VegaInterface
+    gold, meta = load()
+    vega = VegaInterface(make_variant_config(tmp_path, key))
+    oracle = Oracle(vega, tables=static_tables())
+    check(key, oracle.compute_model, oracle.chi2, oracle.log_lik, gold, meta)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('key', variant_keys())
+def test_cuda_path_matches_reference_option_variants(key, tmp_path):
+    """The same variants through the C ABI: scalar calls against the reference outputs, then the
+    perturbed cases as ONE batch (sampled columns = every perturbed parameter) against the same."""
+    from helpers import make_variant_config
+    from vega_b200 import VegaInterface
+    gold, meta = load()
+    vega = VegaInterface(make_variant_config(tmp_path, key))
+    check(key, vega.compute_model, vega.chi2, vega.log_lik, gold, meta)
+    cases = meta[key]['cases']
+    names = sorted({n for case in cases for n in case})
+    theta = np.array([[case.get(n, vega.params[n]) for n in names] for case in cases])
+    models, status = vega.compute_model_batch(theta, names)
+    assert not status.any()
+    chi2 = vega.chi2_batch(theta, names)
+    for i in range(len(cases)):
+        for name in meta[key]['corr']:
+            ref = gold[f'{key}/{i}/xi/{name}']
+            assert np.max(np.abs(models[name][i] - ref)) <= 1e-10 * np.max(np.abs(ref)), (key, i, name)
+        assert abs(chi2[i] - float(gold[f'{key}/{i}/chi2'])) <= 1e-6
+
+
+def test_oracle_matches_reference_blinding(tmp_path):
+    """Blinded data: DA_BLIND column, growth_rate + (pi - exp(v^2)), ap_full / at_full pinned to 1
+    (vega/data.py:305-340, vega/vega_interface.py:389-421, vega/utils.py:375-393)."""
+    from helpers import make_blind_vega, static_tables
+    from oracle.vega_oracle import Oracle
+    gold, meta = load()
+    vega = make_blind_vega(tmp_path)
+    assert vega._blind and vega._rnsps == {'growth_rate': 1.06}
+    local = vega._get_lcl_prms({'ap_full': 1.2})
+    assert local['ap_full'] == 1. and local['at_full'] == 1.
+    assert abs(local['growth_rate'] - (vega.params['growth_rate'] + np.pi - np.exp(1.06**2))) < 1e-15
+    oracle = Oracle(vega, tables=static_tables())
+    check('blind', oracle.compute_model, oracle.chi2, oracle.log_lik, gold, meta)
+
+
+def test_blinding_guards(tmp_path):
+    """vega/vega_interface.py:853-886 and vega/utils.py:320-349: a BLIND_FIXED parameter may not be
+    sampled, bias_QSO and beta_QSO may not both be sampled, and without an offsets file for the
+    strategy the blinded parameters cannot be sampled at all."""
+    import configparser
+    from helpers import make_blind_config
+    from vega_b200 import VegaInterface, utils
+    main, offsets = make_blind_config(tmp_path)
+    with pytest.raises(ValueError, match='Unknown blinding version'):
+        VegaInterface(main)                      # no file registered for desi_dr3 (as shipped upstream)
+    cfg = configparser.ConfigParser()
+    cfg.optionxform = lambda option: option
+    cfg.read(main)
+    cfg['sample']['ap_full'] = '0.5 1.5 1.0 0.1'
+    with open(main, 'w') as f:
+        cfg.write(f)
+    utils.BLINDING_FILES['desi_dr3'] = {'full-shape': offsets, 'bao': None}
+    try:
+        with pytest.raises(ValueError, match='must be fixed'):
+            VegaInterface(main)
+    finally:
+        del utils.BLINDING_FILES['desi_dr3']
+
+
+@pytest.mark.gpu
+def test_cuda_path_matches_reference_blinding(tmp_path):
+    """The blinding transform on the device (vg_plan_set_theta_transform): scalar calls, then a
+    batch whose columns include the blinded growth_rate and the pinned ap_full / at_full."""
+    from helpers import make_blind_vega
+    gold, meta = load()
+    vega = make_blind_vega(tmp_path)
+    check('blind', vega.compute_model, vega.chi2, vega.log_lik, gold, meta)
+    cases = meta['blind']['cases']
+    names = sorted({n for case in cases for n in case})
+    theta = np.array([[case.get(n, vega.params[n]) for n in names] for case in cases])
+    models, status = vega.compute_model_batch(theta, names)
+    assert not status.any()
+    chi2 = vega.chi2_batch(theta, names)
+    for i in range(len(cases)):
+        for name in meta['blind']['corr']:
+            ref = gold[f'blind/{i}/xi/{name}']
+            assert np.max(np.abs(models[name][i] - ref)) <= 1e-10 * np.max(np.abs(ref)), (i, name)
+        assert abs(chi2[i] - float(gold[f'blind/{i}/chi2'])) <= 1e-6
+
+
 @pytest.mark.parametrize('key', ['c1_marg', 'c1_marg_fit'])
 def test_oracle_matches_reference_marginalisation(key, tmp_path):
     from helpers import make_marg_case

@@ -87,6 +87,7 @@ _SIGNATURES = {
     'vg_corr_n_static_xi': (C.c_int, [_PTR, i32]),
     'vg_corr_n_folded': (C.c_int, [_PTR, i32]),
     'vg_plan_set_direct_pk': (C.c_int, [_PTR, _PTR]),
+    'vg_plan_set_theta_transform': (C.c_int, [_PTR, _PTR, _PTR]),
     'vg_plan_set_fvoigt': (C.c_int, [_PTR, i32, _PTR, _PTR]),
     'vg_plan_set_uvshot_table': (C.c_int, [_PTR, i32, _PTR, _PTR]),
     'vg_plan_set_priors': (C.c_int, [_PTR, i32, _PTR, _PTR, _PTR]),

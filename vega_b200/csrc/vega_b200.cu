@@ -178,6 +178,8 @@ struct Corr {
 struct vg_plan {
   int npf = 0, n_theta = 0, nk = 0, nk_pad = 0, nmu = 0, n_ell = 0, idx_bao_amp = -1;
   std::vector<double> base;
+  DevBuf d_theta_offset, d_theta_force;   // blinding transform of the theta columns (optional)
+  bool has_theta_transform = false;
   DevBuf d_base, d_theta_cols, d_k, d_pk[4], d_pk_fid, d_mu, d_wleg;
   DevBuf d_fv_x, d_fv_f; int fv_n = 0;
   DevBuf d_uv_tau, d_uv_a; int uv_n = 0;
@@ -521,6 +523,15 @@ int vg_plan_set_direct_pk(vg_plan* plan, const double* pk_host) {
   VG_REQUIRE(plan && pk_host, "vg_plan_set_direct_pk: bad arguments");
   VG_CUDA_CHECK(cudaDeviceSynchronize());
   VG_CUDA_CHECK(cudaMemcpy(plan->d_pk[3].p, pk_host, (size_t)plan->nk * 8, cudaMemcpyHostToDevice));
+  return VG_OK;
+}
+
+int vg_plan_set_theta_transform(vg_plan* plan, const double* offset, const int32_t* force_one) {
+  VG_REQUIRE(plan && offset && force_one, "vg_plan_set_theta_transform: bad arguments");
+  if (plan->n_theta == 0) return VG_OK;
+  VG_TRY(upload(plan->d_theta_offset, offset, plan->n_theta));
+  VG_TRY(upload(plan->d_theta_force, force_one, plan->n_theta));
+  plan->has_theta_transform = true;
   return VG_OK;
 }
 
@@ -995,6 +1006,8 @@ int expand_params(vg_plan* plan, const double* theta_dev, long long Bc, int* sta
     const long long m = Bc * plan->n_theta;
     vg::scatter_theta_kernel<<<vg_cdiv(m, 256), 256, 0, st>>>(theta_dev, plan->n_theta,
                                                            plan->d_theta_cols.as<int>(), Bc, plan->npf,
+                                                           plan->has_theta_transform ? plan->d_theta_offset.as<double>() : nullptr,
+                                                           plan->has_theta_transform ? plan->d_theta_force.as<int>() : nullptr,
                                                            plan->w_pfull.as<double>());
     VG_LAUNCHED();
   }

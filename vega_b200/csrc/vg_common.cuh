@@ -4,15 +4,8 @@
 #include <cstdint>
 #include <cstdio>
 
-#define VG_OK 0
-#define VG_ERR_CUDA 1
-#define VG_ERR_ARG 2
-#define VG_ERR_STATE 3
-
-// per-vector status bits written by the kernels (vega/utils.py:444-453 exceptions)
-#define VG_STATUS_BOUNDS 1   // r outside the FFTLog range  -> VegaBoundsError
-#define VG_STATUS_ARINYO 2   // NaN/Inf in the Arinyo D_NL  -> VegaArinyoError
-#define VG_STATUS_NONFINITE 4
+// VG_OK / VG_ERR_* / VG_STATUS_*: public, in include/vega_b200.h
+#include "../../include/vega_b200.h"
 
 #define VG_CUDA_CHECK(expr)                                                        \
   do {                                                                             \

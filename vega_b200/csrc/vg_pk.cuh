@@ -618,14 +618,21 @@ __global__ void expand_theta_kernel(const double* __restrict__ base, int npf,
   if (idx >= B * npf) return;
   pfull[idx] = base[idx % npf];
 }
+// offset / force_one (nullable, per theta column): the blinding transform of
+// vega/vega_interface.py:405-419 -- theta += pi - exp(v^2) for the blinded parameters
+// (vega/utils.py:375-393) and the BLIND_FIXED_PARS pinned to 1 whatever the caller passed
 __global__ void scatter_theta_kernel(const double* __restrict__ theta, int n_theta,
                                      const int* __restrict__ cols, long long B, int npf,
+                                     const double* __restrict__ offset, const int* __restrict__ force_one,
                                      double* __restrict__ pfull) {
   long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= B * n_theta) return;
   long long b = idx / n_theta;
   int j = (int)(idx % n_theta);
-  pfull[b * npf + cols[j]] = theta[idx];
+  double v = theta[idx];
+  if (offset) v += offset[j];
+  if (force_one && force_one[j]) v = 1.0;
+  pfull[b * npf + cols[j]] = v;
 }
 
 }  // namespace vg

@@ -406,46 +406,51 @@ class Data:
         return self.metal_coordinates[corr_hash[::-1]], self.metal_mats[corr_hash[::-1]]
 
     # -- Monte Carlo mocks -------------------------------------------------------------
-    def create_monte_carlo(self, fiducial_model, scale=None, seed=None, forecast=False):
-        """Gaussian mock around a fiducial model (vega/data.py:689-760)."""
-        if scale is None:
-            scale = 1
-        recompute = not np.isclose(scale, self._scale)
-        if recompute:
+    def _set_mc_scale(self, scale):
+        """Scaled inverse covariance / log-determinant of the Monte Carlo mode; returns True when
+        the scale changed (the Cholesky factor is then stale)."""
+        changed = not np.isclose(scale, self._scale)
+        if changed:
             self._scale = scale
-            self.scaled_inv_masked_cov = self.inv_masked_cov / self._scale
-            self.scaled_log_cov_det = np.log(self._scale) + self.log_cov_det
+            self.scaled_inv_masked_cov = self.inv_masked_cov / scale
+            self.scaled_log_cov_det = self.log_cov_det + np.log(scale)
         if self.scaled_inv_masked_cov is None:
             self.scaled_inv_masked_cov = self.inv_masked_cov
         if self.scaled_log_cov_det is None:
             self.scaled_log_cov_det = self.log_cov_det
+        return changed
 
-        if (self._cholesky is None or recompute) and not forecast:
+    def _fiducial_on_data_grid(self, fiducial_model):
+        """A fiducial given on the distorted model grid is cut to the data bins."""
+        if fiducial_model.size == self.full_data_size:
+            return fiducial_model
+        if fiducial_model.size != self.dist_model_coordinates.rp_grid.size:
+            raise ValueError("Could not match fiducial model to data or model size.")
+        return fiducial_model[self.dist_model_coordinates.get_mask_to_other(self.data_coordinates)]
+
+    def create_monte_carlo(self, fiducial_model, scale=None, seed=None, forecast=False):
+        """One Gaussian mock around a fiducial model, mock = fiducial + L z with L the Cholesky
+        factor of scale * covariance (of the masked block when `cholesky_masked_cov`) and z from
+        numpy's global stream -- same draw order as vega/data.py:689-760, so a seed reproduces the
+        reference's mock.  `forecast`: the fiducial itself.  Sets mc_mock / masked_mc_mock and
+        bumps mc_version (the device re-uploads the data when it changes)."""
+        stale = self._set_mc_scale(1 if scale is None else scale)
+        if not forecast and (stale or self._cholesky is None):
+            cov = self.cov_mat
             if self.cholesky_masked_cov:
-                masked_cov = self.cov_mat[:, self.data_mask][self.data_mask, :]
-                self._cholesky = np.linalg.cholesky(self._scale * masked_cov)
-            else:
-                self._cholesky = np.linalg.cholesky(self._scale * self.cov_mat)
-
+                cov = cov[:, self.data_mask][self.data_mask, :]
+            self._cholesky = np.linalg.cholesky(self._scale * cov)
         if seed is not None:
             np.random.seed(seed)
-        masked_fiducial = fiducial_model
-        if fiducial_model.size != self.full_data_size:
-            if fiducial_model.size != self.dist_model_coordinates.rp_grid.size:
-                raise ValueError("Could not match fiducial model to data or model size.")
-            mask = self.dist_model_coordinates.get_mask_to_other(self.data_coordinates)
-            masked_fiducial = fiducial_model[mask]
-
+        fiducial = self._fiducial_on_data_grid(fiducial_model)
         if forecast:
-            self.mc_mock = masked_fiducial
-        else:
+            self.mc_mock = fiducial
+        elif self.cholesky_masked_cov:
+            noise = self._cholesky.dot(np.random.randn(int(self.data_mask.sum())))
             self.mc_mock = np.full(self.full_data_size, np.nan)
-            if self.cholesky_masked_cov:
-                ran_vec = np.random.randn(self.data_mask.sum())
-                self.mc_mock[self.data_mask] = \
-                    masked_fiducial[self.data_mask] + self._cholesky.dot(ran_vec)
-            else:
-                ran_vec = np.random.randn(self.full_data_size)
-                self.mc_mock = masked_fiducial + self._cholesky.dot(ran_vec)
+            self.mc_mock[self.data_mask] = fiducial[self.data_mask] + noise
+        else:
+            self.mc_mock = fiducial + self._cholesky.dot(np.random.randn(self.full_data_size))
         self.masked_mc_mock = self.mc_mock[self.data_mask]
+        self.mc_version = getattr(self, 'mc_version', 0) + 1
         return self.mc_mock

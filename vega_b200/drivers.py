@@ -466,6 +466,7 @@ class MonteCarloFits:
         for n in names:      # what the scalar MC-mode chi2 reads (the last mock drawn, as in the reference)
             data = vega.data[n]
             data.masked_mc_mock = mocks[n][-1].copy()
+            data.mc_version = getattr(data, 'mc_version', 0) + 1
             if data.scaled_inv_masked_cov is None:
                 data.scaled_inv_masked_cov = data.inv_masked_cov
         return mocks

@@ -86,10 +86,15 @@ def resolve_scale(scale_cfg, params, is_peak, corr_name, metal_corr):
 class PlanBuilder:
     """Translates a VegaInterface into a vg_plan."""
 
-    def __init__(self, vega, sampled=None, fast_metals=None):
+    def __init__(self, vega, sampled=None, fast_metals=None, extra_params=None):
         self.vega = vega
         self.lib = _lib.load()
-        self.params = dict(vega.params)
+        # the plan's constants are the BLINDED local parameters (vega/vega_interface.py:389-421:
+        # offsets on the blinded names, BLIND_FIXED_PARS pinned to 1); sampled columns receive the
+        # same transform on the device (vg_plan_set_theta_transform)
+        self.unblinded = {**vega.params, **(extra_params or {})}
+        self.params = dict(vega._get_lcl_prms(extra_params)) if hasattr(vega, '_get_lcl_prms') \
+            else dict(self.unblinded)
         self.names = list(self.params.keys())
         self.extra = {}
         self.sampled = list(vega.sample_params['limits'].keys()) if sampled is None else list(sampled)
@@ -718,6 +723,10 @@ class PlanBuilder:
             _dptr(_f64(fid['pk_full'])), _dptr(_f64(fid['pk_smooth'])), _dptr(pk_fid), nmu,
             _dptr(_f64(mu)), len(ells), _dptr(wleg), self.col('bao_amp'), C.byref(handle)))
         plan = DevicePlan(handle, self, infos)
+        transform = vega._theta_transform(self.sampled) if hasattr(vega, '_theta_transform') else None
+        if transform is not None and self.sampled:
+            _lib.check(lib.vg_plan_set_theta_transform(handle, _dptr(transform[0]), _dptr(transform[1])))
+            self.keep.append(transform)
         if chunk is not None:
             _lib.check(lib.vg_plan_set_chunk(handle, int(chunk)))
 

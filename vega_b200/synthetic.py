@@ -75,7 +75,7 @@ def inject_dense_operands(vega, seed=20261104, with_distortion=True, with_metals
             data._log_cov_det = None
             data._cholesky = None
             data.variance = data._cov_mat.diagonal()
-    vega._engine = None
+    vega._engine, vega._engines = None, {}
     return vega
 
 
@@ -94,7 +94,7 @@ def draw_mock_data(vega, model, seed=20261104):
         vec[data.data_mask] = fid[data.data_mask] + chol.dot(rng.standard_normal(int(data.data_mask.sum())))
         data._data_vec = vec
         data._masked_data_vec = None
-    vega._engine = None
+    vega._engine, vega._engines = None, {}
     return vega
 
 
@@ -138,5 +138,5 @@ def inject_global_covariance(vega, coupling=0.05):
     vega.full_model_mask = np.concatenate([vega.data[n].model_mask for n in names])
     vega.masked_global_invcov = utils.compute_masked_invcov(cov, vega.full_data_mask)
     vega.masked_global_log_cov_det = utils.compute_log_cov_det(cov, vega.full_data_mask)
-    vega._engine = None
+    vega._engine, vega._engines = None, {}
     return vega

@@ -23,6 +23,13 @@ _EXTRA_SEARCH_DIRS = []
 
 BLIND_FIXED_PARS = ['ap_full', 'at_full', 'aiso_full', 'epsilon_full', 'phi_full']
 DEFAULT_GROWTH_RATE = 0.970386
+# blinded parameters and the tracers they are blinded for (vega/utils.py:21-25)
+VEGA_BLINDED_PARS = {'phi_smooth': ['all'], 'growth_rate': ['all']}
+# blinding strategy -> {'bao' | 'full-shape': npz file of offsets}.  The reference's table
+# (vega/utils.py:331-341) points into a NERSC project directory and ships every entry as None;
+# a site fills it in (tests register a synthetic file).
+BLINDING_FILES = {'desi_y1': {'full-shape': None, 'bao': None},
+                  'desi_y3': {'full-shape': None, 'bao': None}}
 
 
 class VegaModelError(Exception):
@@ -41,6 +48,51 @@ class VegaArinyoError(VegaModelError):
 class VegaDeviceError(RuntimeError):
     """The CUDA library is missing or a kernel launch failed.  There is no CPU
     fallback: the product path fails loudly."""
+
+
+def get_blinding(blind_pars, blinding_strat):
+    """Offsets v of the blinded parameters from the strategy's file (vega/utils.py:320-372)."""
+    assert blinding_strat is not None, 'Blinding failed, do not run!!!'
+    print(f'Blinding parameters: {blind_pars}')
+    if ('ap' in blind_pars) or ('at' in blind_pars) or ('alpha' in blind_pars):
+        blinding_type = 'bao'
+    elif ('growth_rate' in blind_pars) or ('phi_smooth' in blind_pars):
+        blinding_type = 'full-shape'
+    else:
+        raise ValueError(f'No blinding implemented for parameters {blind_pars}')
+    if blinding_strat not in BLINDING_FILES:
+        raise ValueError(f'Unknown blinding version: {blinding_strat}.')
+    blinding_file = BLINDING_FILES[blinding_strat][blinding_type]
+    if blinding_file is None:
+        return None
+    blinding_file = Path(blinding_file)
+    if not blinding_file.exists():
+        raise ValueError(
+            f'Blinding file not found: {blinding_file}. Full-shape analyses must be run at NERSC.')
+    blinding = {}
+    with np.load(blinding_file) as file:
+        for par in blind_pars:
+            if par not in VEGA_BLINDED_PARS:
+                raise ValueError(f'Blinding for parameter {par} not implemented.')
+            if par == 'alpha':
+                dap, dat = float(file['ap']), float(file['at'])
+                blinding[par] = np.sqrt(np.log(
+                    np.pi - np.sqrt((1 + np.pi - np.exp(dap**2)) * (1 + np.pi - np.exp(dat**2))) + 1))
+            else:
+                blinding[par] = float(file[par])
+    return blinding
+
+
+def blinding_offset(value):
+    """The shift a blinded parameter receives: theta += pi - exp(v^2) (vega/utils.py:375-393)."""
+    return np.pi - np.exp(value**2)
+
+
+def apply_blinding(params, blinding):
+    """In-place, like the reference (vega/utils.py:375-393)."""
+    for par, val in blinding.items():
+        params[par] += blinding_offset(val)
+    return params
 
 
 def add_search_dir(path):

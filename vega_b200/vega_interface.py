@@ -86,9 +86,8 @@ class VegaInterface:
 
         self._blind = False
         self._rnsps = None
-        if self._has_data and any(d.blind for d in self.data.values()):
-            raise NotImplementedError(
-                'Blinded data sets need the NERSC blinding files (vega/utils.py:337-349).')
+        if self._has_data:
+            self._init_blinding()
 
         self.mc_config = None
         if 'monte carlo' in self.main_config:
@@ -128,8 +127,7 @@ class VegaInterface:
         self._device = device
         self._batch_chunk = batch_chunk
         self._engine = None
-        self._engine_params = None
-        self._engine_mc = False
+        self._engines = {}
         self._fast_metals = False
 
     # -- init-time readers (vega/vega_interface.py:665-851) ---------------------------
@@ -236,34 +234,119 @@ class VegaInterface:
     def _gaussian_lik_prior(sigma):
         return -0.5 * np.log(2 * np.pi) - np.log(sigma)
 
+    def _init_blinding(self):
+        """Blinding at the parameter level (vega/vega_interface.py:853-886)."""
+        blinding_strat = None
+        for data_obj in self.data.values():
+            if data_obj.blind:
+                self._blind = True
+                if blinding_strat is None:
+                    blinding_strat = data_obj.blinding_strat
+                elif blinding_strat != data_obj.blinding_strat:
+                    raise ValueError('Different blinding strategies found in the data sets.')
+        if not self._blind:
+            return
+        blind_pars = []
+        for par in self.sample_params['limits'].keys():
+            if par in utils.BLIND_FIXED_PARS:
+                raise ValueError(f'Running on blind data, parameter {par} must be fixed.')
+            if par not in utils.VEGA_BLINDED_PARS:
+                continue
+            tracers = utils.VEGA_BLINDED_PARS[par]
+            if any(corr.check_if_blind_corr(tracers) for corr in self.corr_items.values()):
+                blind_pars += [par]
+        if len(blind_pars) > 0:
+            self._rnsps = utils.get_blinding(blind_pars, blinding_strat)
+        if ('bias_QSO' in self.sample_params['limits']) and ('beta_QSO' in self.sample_params['limits']):
+            raise ValueError('Running on blind data and sampling bias_QSO and beta_QSO.')
+
     def _get_lcl_prms(self, params=None):
+        """Local copy of the parameters with the blinding applied (vega/vega_interface.py:389-421).
+        The device applies the same transform to the theta columns (vg_plan_set_theta_transform);
+        this host version serves the plan's constants and callers that read the dictionary."""
         local_params = copy.deepcopy(self.params)
         if params is not None:
             local_params |= params
+        assert self._blind is not None, (
+            'Blinding flag is not set. Call _init_blinding() before computing the model.')
+        if self._rnsps is not None:
+            assert self._blind, ('Blinding offsets (_rnsps) are set but blinding flag is False. '
+                                 'This is an inconsistent state.')
+            local_params = utils.apply_blinding(local_params, self._rnsps)
+            for par in local_params:
+                if par in utils.BLIND_FIXED_PARS:
+                    local_params[par] = 1.
         return local_params
 
     # -- device engine -----------------------------------------------------------------------
-    def _engine_for(self, names=()):
-        """The device plan whose batch columns cover the [sample] set plus every name in
-        `names`.  Parameters outside those columns are constants folded into the plan's
-        static grids, so asking for a new one rebuilds the plan."""
+    def _engine_for(self, names=(), values=None):
+        """The device plan whose batch columns are the [sample] set plus every other name in
+        `names` (parameters outside the columns are constants folded into the plan's static
+        grids).  The plan of the [sample] set alone is kept for good; calls that bring extra
+        names -- a scalar chi2({'bao_amp': .9}), compute_sensitivity -- get a second plan with
+        exactly those extra columns, so they never widen (or slow down) the first one.  A name
+        absent from [parameters] is merged the way _get_lcl_prms merges it
+        (vega/vega_interface.py:402-404): it joins the parameter set with the value passed."""
         from .plan import PlanBuilder
-        wanted = list(self.sample_params['limits'].keys())
-        if self._engine is not None:
-            wanted = list(self._engine.sampled)
-        extra = [n for n in names if n not in wanted]
-        if self._engine is None or extra or self._engine_params != self.params:
-            for n in extra:
-                if n not in self.params:
+        base_names = list(self.sample_params['limits'].keys())
+        extra = [n for n in dict.fromkeys(names) if n not in base_names]
+        key = tuple(sorted(extra))
+        new_values = {}
+        for n in extra:
+            if n not in self.params:
+                if values is None or n not in values:
                     raise KeyError(f'Unknown parameter {n}: it is not listed under [parameters].')
-            self._engine = PlanBuilder(self, sampled=wanted + extra).build(chunk=self._batch_chunk)
-            self._engine_params = dict(self.params)
-            self._engine_mc = False
-        if self._has_data and self._engine_mc != bool(self.monte_carlo):
-            for ci, name in enumerate(self.corr_items):
-                self._engine.set_data(ci, self.data[name], monte_carlo=bool(self.monte_carlo))
-            self._engine_mc = bool(self.monte_carlo)
-        return self._engine
+                new_values[n] = float(values[n])
+        entry = self._engines.get(key)
+        if entry is not None and (entry['params'] != self.params or entry['new'] != new_values):
+            entry = None
+        if entry is None:
+            for old_key in [k for k in self._engines if k != () and k != key]:
+                del self._engines[old_key]          # one plan with extra columns at a time
+            builder = PlanBuilder(self, sampled=base_names + list(key), extra_params=new_values)
+            entry = {'engine': builder.build(chunk=self._batch_chunk), 'params': dict(self.params),
+                     'new': new_values, 'data_token': None}
+            self._engines[key] = entry
+        engine = entry['engine']
+        if self._has_data:
+            token = self._data_token()
+            if entry['data_token'] is None:
+                entry['data_token'] = (False,) + self._data_token(False)[1:]   # what build() uploaded
+            if not self._same_token(entry['data_token'], token):
+                # the reference reads data.masked_mc_mock / scaled_inv_masked_cov on EVERY chi2 call
+                # (vega/vega_interface.py:296-312): any re-draw or change of scale is uploaded
+                for ci, name in enumerate(self.corr_items):
+                    engine.set_data(ci, self.data[name], monte_carlo=bool(self.monte_carlo))
+                entry['data_token'] = token
+        self._engine = engine
+        return engine
+
+    def _data_token(self, monte_carlo=None):
+        """Identity of the arrays the chi2 reads (the Monte Carlo flag, and per correlation the
+        data vector / inverse covariance objects of that mode)."""
+        mc = bool(self.monte_carlo) if monte_carlo is None else monte_carlo
+        token = [mc]
+        for name in self.corr_items:
+            data = self.data[name]
+            if mc:
+                token += [data.masked_mc_mock, data.scaled_inv_masked_cov, getattr(data, 'mc_version', 0)]
+            else:
+                token += [data.masked_data_vec, data.inv_masked_cov, 0]
+        return tuple(token)
+
+    @staticmethod
+    def _same_token(a, b):
+        return len(a) == len(b) and all((x is y) or (not isinstance(x, np.ndarray) and x == y)
+                                        for x, y in zip(a, b))
+
+    def _theta_transform(self, sampled):
+        """Per-column blinding transform of the device (vg_plan_set_theta_transform)."""
+        if self._rnsps is None:
+            return None
+        offset = np.array([utils.blinding_offset(self._rnsps[n]) if n in self._rnsps else 0.
+                           for n in sampled], dtype=np.float64)
+        force = np.array([n in utils.BLIND_FIXED_PARS for n in sampled], dtype=np.int32)
+        return offset, force
 
     def _direct_mode(self, engine, direct_pk):
         """Context in which the engine evaluates Model.compute_direct on `direct_pk`
@@ -284,19 +367,23 @@ class VegaInterface:
         return mode()
 
     def _theta_row(self, engine, params=None):
-        local = self._get_lcl_prms(params)
-        return np.array([[local[n] for n in engine.sampled]], dtype=np.float64)
+        """The merge of vega/vega_interface.py:402-404 for the plan's columns; the blinding
+        transform of :405-419 happens on the device."""
+        own = self.params
+        if params:
+            return np.array([[params[n] if n in params else own[n] for n in engine.sampled]], dtype=np.float64)
+        return np.array([[own[n] for n in engine.sampled]], dtype=np.float64)
 
     @property
     def theta_names(self):
-        """Column names of the batched entry points."""
-        return list(self._engine_for().sampled)
+        """Default column names of the batched entry points: the [sample] set."""
+        return list(self.sample_params['limits'].keys())
 
     # -- the reference's scalar API (batch of one) ----------------------------------------------
     def compute_model(self, params=None, run_init=True, direct_pk=None, marg_coeff=None):
         """Model xi of every correlation for one parameter dict
         (vega/vega_interface.py:208-248).  Returns {name: ndarray(n_dist)}."""
-        engine = self._engine_for(tuple(params) if params else ())
+        engine = self._engine_for(tuple(params) if params else (), params)
         with self._direct_mode(engine, direct_pk):
             models, status = engine.model_device(engine.theta_tensor(self._theta_row(engine, params)))
             status = int(status.cpu()[0])
@@ -327,7 +414,7 @@ class VegaInterface:
         """chi2 incl. priors for one parameter dict (vega/vega_interface.py:250-325);
         model-domain failures give 1e100."""
         assert self._has_data
-        engine = self._engine_for(tuple(params) if params else ())
+        engine = self._engine_for(tuple(params) if params else (), params)
         with self._direct_mode(engine, direct_pk):
             chi2, status = engine.chi2_host(self._theta_row(engine, params))
         if status[0] & (_lib.STATUS_ARINYO | _lib.STATUS_BOUNDS):
@@ -592,13 +679,16 @@ class VegaInterface:
         return {name: xi.cpu().numpy() for name, xi in models.items()}, status.cpu().numpy()
 
     def _reorder(self, engine, theta, names):
+        """theta[B, len(names)] -> theta[B, len(engine.sampled)]; `names` defaults to the [sample]
+        set, columns of the plan that are not named keep their [parameters] value."""
         theta = np.atleast_2d(np.asarray(theta, dtype=np.float64))
-        if names is None or list(names) == engine.sampled:
-            if theta.shape[1] != len(engine.sampled):
-                raise ValueError(f'theta has {theta.shape[1]} columns, expected {len(engine.sampled)}: '
-                                 f'{engine.sampled}')
+        names = self.theta_names if names is None else list(names)
+        if theta.shape[1] != len(names):
+            raise ValueError(f'theta has {theta.shape[1]} columns, expected {len(names)}: {names}')
+        if names == engine.sampled:
             return theta
-        full = np.tile([self.params[n] for n in engine.sampled], (theta.shape[0], 1))
+        full = np.tile([engine.builder.params[n] if n not in self.params else self.params[n]
+                        for n in engine.sampled], (theta.shape[0], 1))
         for j, n in enumerate(names):
             full[:, engine.sampled.index(n)] = theta[:, j]
         return full
