@@ -54,7 +54,7 @@ class P2xi:
         if lowring:
             lnxy = self.delta / np.pi * np.angle(kernel(q + 1j * np.pi / self.delta))
         else:
-            lnxy = self.delta
+            lnxy = 0.0      # mcfit: lnxy = log(xy) with the default xy = 1 when lowring is off
         self.lnxy = lnxy
         self.y = np.exp(lnxy - self.delta) / self.x[::-1]
 

@@ -75,3 +75,35 @@ def test_static_tables_rel_asy():
             tab = hankel.build_static_table(k, pk, ell, n_pow)
             got = spline_from_operator(tab[0], tab[1], tab[2], np.log(r))
             assert np.max(np.abs(got - ref[ell // 2])) < 1e-11 * np.max(np.abs(ref[ell // 2]))
+
+
+@pytest.mark.parametrize('lowring', [True, False])
+def test_p2xi_analytic_gaussian_pair(lowring):
+    """P(k) = exp(-k^2 a^2 / 2)  <->  xi_0(r) = (2 pi)^-3/2 a^-3 exp(-r^2 / 2 a^2), with and
+    without the low-ringing shift.  With lowring off the output grid is y = 1 / (x e^Delta)
+    reversed, i.e. ln(xy) = 0 as in mcfit (xy = 1), not Delta."""
+    k, _ = template()
+    a = 30.
+    pk = np.exp(-0.5 * (k * a)**2)
+    for make in (lambda: oh.P2xi(k, l=0, lowring=lowring)(pk),
+                 lambda: (lambda r, H: (r, H @ pk))(*hankel.fftlog_mcfit_operator(k, 0, lowring=lowring))):
+        r, xi = make()
+        exact = (2 * np.pi)**-1.5 / a**3 * np.exp(-0.5 * (r / a)**2)
+        sel = (r > 1.) & (r < 150.)
+        assert np.max(np.abs(xi - exact)[sel]) < 2e-6 * exact.max()
+    if not lowring:
+        delta = np.log(k[-1] / k[0]) / (k.size - 1)
+        assert np.allclose(r, np.exp(-delta) / k[::-1], rtol=1e-14, atol=0)
+
+
+@pytest.mark.parametrize('ell', [2, 4])
+def test_p2xi_lowring_off_agrees_with_lowring_on(ell):
+    """Both grids sample the same continuous transform (interpolated onto common radii)."""
+    k, pk = template()
+    pk_ell = pk * np.exp(-(k * 3.)**2)
+    r_on, xi_on = oh.P2xi(k, l=ell, lowring=True)(pk_ell)
+    r_off, xi_off = oh.P2xi(k, l=ell, lowring=False)(pk_ell)
+    r = np.exp(np.linspace(np.log(5.), np.log(300.), 400))
+    on = interp1d(np.log(r_on), xi_on, kind='cubic')(np.log(r))
+    off = interp1d(np.log(r_off), xi_off, kind='cubic')(np.log(r))
+    assert np.max(np.abs(on - off)) < 2e-5 * np.max(np.abs(on))

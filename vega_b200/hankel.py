@@ -37,7 +37,7 @@ def fftlog_mcfit_operator(k, ell, q=1.5, lowring=True):
     if lowring:
         lnxy = delta / np.pi * np.angle(_mellin_sph_bessel(ell, q + 1j * np.pi / delta))
     else:
-        lnxy = delta
+        lnxy = 0.0          # mcfit: lnxy = log(xy), xy = 1, when the low-ringing shift is off
     r = np.exp(lnxy - delta) / k[::-1]
     m = np.arange(n_fft // 2 + 1)
     u = _mellin_sph_bessel(ell, q + 2j * np.pi * m / (n_fft * delta))
