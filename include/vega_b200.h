@@ -37,6 +37,7 @@ extern "C" {
 #define VG_STATUS_BOUNDS 1      /* r outside the FFTLog range  -> VegaBoundsError */
 #define VG_STATUS_ARINYO 2      /* NaN/Inf in the Arinyo D_NL  -> VegaArinyoError */
 #define VG_STATUS_NONFINITE 4   /* a non-finite model bin */
+#define VG_STATUS_DEVICE 8      /* internal: a kernel pipeline timed out -- the values are not valid */
 
 #define VG_MAX_BB_TERMS 8
 
@@ -256,6 +257,14 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
  * and out of the per-vector matrix product; same result to rounding (summation order).  Needs
  * VG_OPT_MOMENTS.  The bench headline keeps it off: every matrix applied per vector. */
 #define VG_OPT_FOLD_METALS 2
+/* VG_OPT_OZAKI (default -1 = automatic): the dense metal-matrix product (vega/metals.py:338-367 for
+ * a batch) in split-integer form: both operands are cut into S signed radix-128 digits per
+ * row-scaled entry, the S(S+1)/2 digit products run on the tcgen05 tensor cores (kind::i8, exact
+ * s32 accumulation in TMEM) and are recombined in FP64 (csrc/vg_ozaki.cuh).  -1: per correlation,
+ * the fewest digits whose worst-case truncation bound at the plan parameters is below 5e-11 max|xi|
+ * (vg_corr_ozaki_slices); 3..8: that many digits; 0: the FP64 DMMA kernel (the parity reference).
+ * Batches below 16 vectors always take the DMMA kernel. */
+#define VG_OPT_OZAKI 3
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
 /* Isotropic P(k) [nk] for the direct mode (e.g. from a Boltzmann code, the `direct_pk`
  * argument of VegaInterface.compute_model / chi2 / log_lik); host pointer, copied. */
@@ -268,6 +277,11 @@ int vg_corr_n_moment(const vg_plan* plan, int32_t corr);
 int vg_corr_n_static_xi(const vg_plan* plan, int32_t corr);
 /* Metal evaluations VG_OPT_FOLD_METALS = 1 serves from static vectors (after finalize). */
 int vg_corr_n_folded(const vg_plan* plan, int32_t corr);
+/* Digits the split-integer metal GEMM of a correlation runs with under the current VG_OPT_OZAKI
+ * (0: the correlation has no dense metal matrices or the option is off); bound_per_digits[9]
+ * (nullable) receives, for S = 3..8, the truncation bound relative to max|xi_smooth| at the plan
+ * parameters. */
+int vg_corr_ozaki_slices(const vg_plan* plan, int32_t corr, double* bound_per_digits);
 /* Status bits raised while building the static grids (e.g. VG_STATUS_ARINYO): they apply
  * to every vector */
 int vg_plan_static_status(const vg_plan* plan);
@@ -330,6 +344,11 @@ int vg_metal_pair_histograms(const double* side1, int32_t n1, const double* side
                              const double* ratio_edges, int32_t nr, double* H, double* per_true,
                              double* per_assumed, double* ratio);
 
+/* Stand-alone split-integer GEMM C[m,n] = sum_k A[m,k] B[n,k] on tcgen05 kind::i8 (tests): device
+ * pointers, row strides in doubles (K-contiguous operands), `slices` digits.  Synchronous.
+ * *error_out != 0: a pipeline wait timed out. */
+int vg_ozaki_gemm(const double* A, const double* B, double* C, int M, int N, int K, long long lda,
+                  long long ldb, long long ldc, int slices, int32_t* error_out, void* stream);
 /* Stand-alone FP64 tensor-core GEMM C[m,n] = alpha sum_k A[m,k] B[n,k] + beta C (tests) */
 int vg_dgemm_tn(const double* A, const double* B, double* C, int M, int N, int K,
                 long long lda, long long ldb, long long ldc, double alpha, double beta,

@@ -12,8 +12,8 @@ LIB_PATH = Path(__file__).resolve().parent / 'libvega_b200.so'
 
 VG_MAX_BB_TERMS = 8
 F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP, F_MOCKGK = (1 << i for i in range(9))
-STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE = 1, 2, 4
-OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS = 0, 1, 2
+STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE, STATUS_DEVICE = 1, 2, 4, 8
+OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS, OPT_OZAKI = 0, 1, 2, 3
 
 i32, u32, f64 = C.c_int32, C.c_uint32, C.c_double
 
@@ -85,6 +85,7 @@ _SIGNATURES = {
     'vg_plan_set_option': (C.c_int, [_PTR, i32, i32]),
     'vg_corr_n_moment': (C.c_int, [_PTR, i32]),
     'vg_corr_n_static_xi': (C.c_int, [_PTR, i32]),
+    'vg_corr_ozaki_slices': (C.c_int, [_PTR, i32, _PTR]),
     'vg_corr_n_folded': (C.c_int, [_PTR, i32]),
     'vg_plan_set_direct_pk': (C.c_int, [_PTR, _PTR]),
     'vg_plan_set_theta_transform': (C.c_int, [_PTR, _PTR, _PTR]),
@@ -119,6 +120,8 @@ _SIGNATURES = {
     'vg_metal_pair_ratio_range': (C.c_int, [_PTR, i32, _PTR, i32, _PTR]),
     'vg_metal_pair_histograms': (C.c_int, [_PTR, i32, _PTR, i32, i32, f64, f64, _PTR, i32, _PTR, i32,
                                            _PTR, _PTR, _PTR, _PTR]),
+    'vg_ozaki_gemm': (C.c_int, [_PTR, _PTR, _PTR, C.c_int, C.c_int, C.c_int, C.c_longlong, C.c_longlong,
+                                C.c_longlong, C.c_int, _PTR, _PTR]),
     'vg_dgemm_tn': (C.c_int, [_PTR, _PTR, _PTR, C.c_int, C.c_int, C.c_int, C.c_longlong,
                               C.c_longlong, C.c_longlong, f64, f64, C.c_int, _PTR, _PTR]),
 }

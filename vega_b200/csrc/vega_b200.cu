@@ -14,6 +14,7 @@
 #include "vg_gemm.cuh"
 #include "vg_metalmat.cuh"
 #include "vg_moments.cuh"
+#include "vg_ozaki.cuh"
 #include "vg_pk.cuh"
 #include "vg_post.cuh"
 #include "vg_xi.cuh"
@@ -96,6 +97,14 @@ struct Hankel {
   DevBuf op;    // [n_ell][2*n_out_pad][nk_pad]
 };
 
+// one operand of the split-integer GEMM (vg_ozaki.cuh): S digit planes [S][rows][Kp] + row exponents
+struct OzakiOperand {
+  DevBuf planes, exps;
+  long long rows = 0;       // rows the planes were built for (capacity for the workspace operand)
+  int Kp = 0, S = 0;
+  const double* src = nullptr;   // static operands: the matrix the digits were taken from
+};
+
 struct EvalLayout {
   // evaluations grouped by pk_ell kernel class: 0..19 fast (VMODE*5 + KIND), 20..22 generic (20 + MODE)
   std::vector<int> class_ids[23];
@@ -156,6 +165,9 @@ struct Corr {
   DevBuf d_mcat;                 // hot metal matrices [n_model][n_metal_hot*ld_model]
   DevBuf d_fold_tab;             // LAY_FOLD: [n_fold][9][ld_model] Y[f][m] = M_c X[row(f)][m]
   DevBuf d_mcat_fold, d_mrp_fold;   // LAY_FOLD: matrices of the metal terms that stay in the product
+  OzakiOperand oz_mcat, oz_mcat_fold;   // digit planes of d_mcat / d_mcat_fold (built on first use)
+  int oz_auto_slices = 0;        // digits that meet the truncation budget at the plan parameters (0: not dense)
+  double oz_bound[vg::OZ_MAX_S + 1] = {0};   // the bound per digit count, relative to max|xi| (diagnostics)
   bool has_dmat = false;
   DevBuf d_dmat;                 // [n_dist][ld_model]
   DevBuf d_dmat_masked;          // [n_mask][ld_model]
@@ -193,6 +205,10 @@ struct vg_plan {
   bool use_moments = true;
   bool direct_mode = false;      // VG_OPT_DIRECT_PK
   bool fold_metals = false;      // VG_OPT_FOLD_METALS
+  int ozaki_slices = -1;         // VG_OPT_OZAKI: digits of the split-integer metal GEMM (0: DMMA, -1: per
+                                 // correlation, the fewest digits that meet the truncation budget)
+  OzakiOperand oz_A;             // workspace: digit planes of the batch operand
+  DevBuf d_oz_error;             // set by a pipeline time-out inside ozaki_gemm_kernel
   int static_bad = 0;
   int std_ells = 0;
   // global covariance
@@ -246,6 +262,7 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
               long long strideB, long long strideC, cudaStream_t st);
 int build_metal_operands(Corr& c, const EvalLayout& L, DevBuf& mcat, DevBuf& mrp);
 int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
+int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st);
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st);
 enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_MOMENT = 7, PROF_NTAGS = 8 };
@@ -505,6 +522,12 @@ int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
   VG_REQUIRE(plan, "null plan");
   if (option == VG_OPT_MOMENTS) { plan->use_moments = value != 0; return VG_OK; }
   if (option == VG_OPT_FOLD_METALS) { plan->fold_metals = value != 0; return VG_OK; }
+  if (option == VG_OPT_OZAKI) {
+    VG_REQUIRE(value == 0 || value == -1 || (value >= 3 && value <= vg::OZ_MAX_S),
+               "VG_OPT_OZAKI: 0 (off), -1 (automatic) or 3..%d digits", vg::OZ_MAX_S);
+    plan->ozaki_slices = value;
+    return VG_OK;
+  }
   if (option == VG_OPT_DIRECT_PK) {
     if (value) {
       bool any = false;
@@ -877,6 +900,7 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
   VG_CUDA_CHECK(cudaMemcpy(&plan->static_bad, bad.p, sizeof(int), cudaMemcpyDeviceToHost));
   for (auto& cp : plan->corrs) {
     VG_TRY(freeze_metal_terms(plan, *cp, st));
+    VG_TRY(ozaki_budget(plan, *cp, st));
     cp->metal_host.clear();
     cp->metal_host.shrink_to_fit();
   }
@@ -957,6 +981,144 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
   VG_TRY(vg::launch_dgemm(g, vg::GEMM_STORE, st));
   vg::reduce_splits_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->w_split.as<double>(), C, n, g.splits, n);
   VG_LAUNCHED();
+  return VG_OK;
+}
+
+constexpr int OZAKI_MIN_BATCH = 16;      // below: the DMMA kernel's batch-sized tiles stream the operator once
+// ---- split-integer GEMM on tcgen05 (vg_ozaki.cuh) ------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+template <int S>
+int ozaki_slice_launch(const double* src, long long ld, int K, int Kp, long long rows, const int* exps,
+                       int8_t* planes, long long plane_stride, cudaStream_t st) {
+  const long long n = rows * (Kp / 16);
+  vg::ozaki_slice_kernel<S><<<vg_cdiv(n, 256), 256, 0, st>>>(src, ld, K, Kp, rows, exps, planes, plane_stride);
+  VG_LAUNCHED();
+  return VG_OK;
+}
+
+// digit planes + row exponents of src[rows][ld] (first K columns).  The buffers only grow (room for
+// `capacity` rows is taken at once), so a workspace operand re-sliced every call never reallocates.
+int ozaki_slice(OzakiOperand& op, const double* src, long long ld, long long rows, long long capacity, int K, int S,
+                cudaStream_t st) {
+  const int Kp = (K + 15) / 16 * 16;
+  capacity = std::max(capacity, rows);
+  const size_t need = (size_t)S * rows * Kp;
+  if (op.planes.bytes < need || op.exps.bytes < (size_t)rows * sizeof(int)) {
+    VG_CUDA_CHECK(cudaStreamSynchronize(st));
+    VG_TRY(op.planes.alloc(std::max<size_t>(op.planes.bytes, (size_t)S * (size_t)capacity * (size_t)Kp), false));
+    VG_TRY(op.exps.alloc(std::max(op.exps.bytes, (size_t)capacity * sizeof(int)), true));
+  }
+  op.S = S; op.Kp = Kp; op.rows = rows;
+  vg::ozaki_rowexp_kernel<<<(unsigned)rows, 256, 0, st>>>(src, ld, K, op.exps.as<int>());
+  VG_LAUNCHED();
+  int8_t* planes = op.planes.as<int8_t>();
+  const long long ps = op.rows * (long long)Kp;
+  switch (S) {
+    case 3: return ozaki_slice_launch<3>(src, ld, K, Kp, rows, op.exps.as<int>(), planes, ps, st);
+    case 4: return ozaki_slice_launch<4>(src, ld, K, Kp, rows, op.exps.as<int>(), planes, ps, st);
+    case 5: return ozaki_slice_launch<5>(src, ld, K, Kp, rows, op.exps.as<int>(), planes, ps, st);
+    case 6: return ozaki_slice_launch<6>(src, ld, K, Kp, rows, op.exps.as<int>(), planes, ps, st);
+    case 7: return ozaki_slice_launch<7>(src, ld, K, Kp, rows, op.exps.as<int>(), planes, ps, st);
+    default: return ozaki_slice_launch<8>(src, ld, K, Kp, rows, op.exps.as<int>(), planes, ps, st);
+  }
+}
+
+// 3-D tensor map over the digit planes: (k, row, digit), box (64, box_rows, S), 64-byte swizzle
+int ozaki_map(CUtensorMap* map, const OzakiOperand& op, int box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  VG_REQUIRE(fn, "cuTensorMapEncodeTiled is not available from this driver");
+  const cuuint64_t gdim[3] = {(cuuint64_t)op.Kp, (cuuint64_t)op.rows, (cuuint64_t)op.S};
+  const cuuint64_t gstride[2] = {(cuuint64_t)op.Kp, (cuuint64_t)op.rows * (cuuint64_t)op.Kp};
+  const cuuint32_t box[3] = {(cuuint32_t)vg::OZ_BK, (cuuint32_t)box_rows, (cuuint32_t)op.S};
+  const cuuint32_t estride[3] = {1, 1, 1};
+  const CUresult rc = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, op.planes.p, gdim, gstride, box, estride,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  VG_REQUIRE(rc == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d", (int)rc);
+  return VG_OK;
+}
+
+template <int S>
+int ozaki_gemm_launch(const CUtensorMap& ma, const CUtensorMap& mb, const vg::OzakiArgs& g, dim3 grid, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::ozaki_gemm_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       vg::OzakiSmem<S>::BYTES));
+    attr_set = true;
+  }
+  vg::ozaki_gemm_kernel<S><<<grid, vg::OZ_THREADS, vg::OzakiSmem<S>::BYTES, st>>>(ma, mb, g);
+  VG_LAUNCHED();
+  return VG_OK;
+}
+
+// C[M][ldc] = A B^T from the digit planes of A ([>= M rows]) and B ([N rows]); deterministic split-K
+int ozaki_gemm(const OzakiOperand& A, long long M, const OzakiOperand& B, int N, double* C, long long ldc,
+               DevBuf& split_ws, DevBuf& error_flag, cudaStream_t st) {
+  VG_REQUIRE(A.S == B.S && A.Kp == B.Kp && A.S >= 3, "ozaki_gemm: operands with different digit planes");
+  const int S = A.S;
+  if (!error_flag.p) VG_TRY(error_flag.alloc(sizeof(int)));
+  CUtensorMap ma, mb;
+  VG_TRY(ozaki_map(&ma, A, vg::OZ_BM));
+  VG_TRY(ozaki_map(&mb, B, vg::OZ_BN));
+  vg::OzakiArgs g{};
+  g.M = (int)M; g.N = N; g.S = S;
+  g.kb_total = vg_cdiv(A.Kp, vg::OZ_BK);
+  const long long tiles = (long long)vg_cdiv(M, vg::OZ_BM) * vg_cdiv(N, vg::OZ_BN);
+  // an s32 accumulator takes S products of |q q'| <= 2^12 per k: K blocks per split are bounded
+  const int kb_cap = (int)(((1LL << 31) - 1) / (4096LL * vg::OZ_BK * S));
+  int splits = vg_cdiv(g.kb_total, kb_cap);
+  {   // fill whole waves of the 148 SMs (one CTA each), >= 8 K blocks per split
+    double best = -1.0;
+    const int lo = splits, hi = std::max(lo, std::min(64, g.kb_total / 8));
+    for (int sp = lo; sp <= hi; ++sp) {
+      const int per = vg_cdiv(g.kb_total, sp);
+      if ((long long)per * (sp - 1) >= g.kb_total) continue;      // an empty last split
+      const long long ctas = tiles * sp;
+      const long long waves = (ctas + NUM_SMS - 1) / NUM_SMS;
+      const double eff = (double)ctas / (double)(waves * NUM_SMS) - 0.003 * (sp - 1);
+      if (eff > best + 1e-9) { best = eff; splits = sp; }
+    }
+  }
+  g.kb_per_split = vg_cdiv(g.kb_total, splits);
+  g.expA = A.exps.as<int>(); g.expB = B.exps.as<int>();
+  g.error_flag = error_flag.as<int>();
+  g.ldc = ldc;
+  const long long n = M * ldc;
+  if (splits > 1) {
+    VG_TRY(split_ws.ensure((size_t)splits * n * 8));
+    g.C = split_ws.as<double>(); g.split_stride = n;
+  } else {
+    g.C = C; g.split_stride = 0;
+  }
+  dim3 grid(vg_cdiv(N, vg::OZ_BN), vg_cdiv(M, vg::OZ_BM), splits);
+  int rc;
+  switch (S) {
+    case 3: rc = ozaki_gemm_launch<3>(ma, mb, g, grid, st); break;
+    case 4: rc = ozaki_gemm_launch<4>(ma, mb, g, grid, st); break;
+    case 5: rc = ozaki_gemm_launch<5>(ma, mb, g, grid, st); break;
+    case 6: rc = ozaki_gemm_launch<6>(ma, mb, g, grid, st); break;
+    case 7: rc = ozaki_gemm_launch<7>(ma, mb, g, grid, st); break;
+    default: rc = ozaki_gemm_launch<8>(ma, mb, g, grid, st); break;
+  }
+  VG_TRY(rc);
+  if (splits > 1) {
+    vg::reduce_splits_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(split_ws.as<double>(), C, n, splits, n);
+    VG_LAUNCHED();
+  }
   return VG_OK;
 }
 
@@ -1276,8 +1438,25 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
                              (fold_layout ? c.d_mrp_fold : c.d_mrp).as<double>(), Bc, plan->w_met.as<double>(), st));
     } else if (c.metal_dense) {
       const long long ldk = (long long)L.n_metal * c.ld_model;
-      VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, (fold_layout ? c.d_mcat_fold : c.d_mcat).as<double>(), ldk,
-                       plan->w_met.as<double>(), c.ld_model, (int)Bc, c.n_model, (int)ldk, 1, 0, 0, 0, st));
+      const DevBuf& mcat = fold_layout ? c.d_mcat_fold : c.d_mcat;
+      const int oz_S = plan->ozaki_slices < 0 ? c.oz_auto_slices : plan->ozaki_slices;
+      if (oz_S > 0 && Bc >= OZAKI_MIN_BATCH) {
+        // split-integer GEMM on tcgen05 (vg_ozaki.cuh): the operator's digit planes are built on
+        // first use, the batch operand's on every call
+        OzakiOperand& ob = fold_layout ? c.oz_mcat_fold : c.oz_mcat;
+        if (ob.S != oz_S || ob.src != mcat.as<double>()) {
+          VG_TRY(ozaki_slice(ob, mcat.as<double>(), ldk, c.n_model, c.n_model, (int)ldk, oz_S, st));
+          ob.src = mcat.as<double>();
+        }
+        VG_TRY(ozaki_slice(plan->oz_A, plan->w_xmet.as<double>(), ldk, Bc, plan->chunk, (int)ldk, oz_S, st));
+        VG_TRY(ozaki_gemm(plan->oz_A, Bc, ob, c.n_model, plan->w_met.as<double>(), c.ld_model, plan->w_split,
+                          plan->d_oz_error, st));
+        vg::flag_status_kernel<<<vg_cdiv(Bc, 256), 256, 0, st>>>(plan->d_oz_error.as<int>(), status_dev, Bc);
+        VG_LAUNCHED();
+      } else {
+        VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, mcat.as<double>(), ldk,
+                         plan->w_met.as<double>(), c.ld_model, (int)Bc, c.n_model, (int)ldk, 1, 0, 0, 0, st));
+      }
     } else {
       const long long n = Bc * c.ld_model;
       vg::metal_sum_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(plan->w_xmet.as<double>(), L.n_metal, c.ld_model,
@@ -1308,6 +1487,48 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
 }  // namespace
 
 namespace {
+
+// Digits of the split-integer metal GEMM for one correlation: the fewest S whose truncation bound,
+// evaluated with the row statistics of the operator and of the metal xi at the PLAN parameters,
+//   2^(-7S) [ max|a| max_j ||b_j||_1 + ||a||_1 max|b| + (S-1) max|a| max|b| max_j nnz(b_j) ]
+// (digits beyond S of A, of B, and the dropped digit products -- only where both are non-zero)
+// stays under OZAKI_BUDGET * max|xi_smooth|: half of the 1e-10 parity bar.  The bound is a worst
+// case (every dropped digit product at its largest magnitude and with the same sign); the errors
+// measured on the dense eBOSS-shaped workload are 1e-11 max|xi| at S = 6 and below 1e-12 at S = 7,
+// where this bound evaluates to 2e-9 and 2e-11.
+constexpr double OZAKI_BUDGET = 5e-11;
+int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st) {
+  const EvalLayout& L = c.lay[LAY_MOM];
+  c.oz_auto_slices = 0;
+  if (!c.metal_dense || L.n_metal == 0) return VG_OK;
+  VG_TRY(ensure_workspace(plan, 1));
+  VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_pfull.p, plan->d_base.p, (size_t)plan->npf * 8,
+                                cudaMemcpyDeviceToDevice, st));
+  VG_CUDA_CHECK(cudaMemsetAsync(plan->w_status.p, 0, 4, st));
+  VG_TRY(run_corr_front(plan, c, 1, plan->w_status.as<int>(), st, 3, LAY_MOM, 0));
+  const long long ldk = (long long)L.n_metal * c.ld_model;
+  DevBuf stats;
+  VG_TRY(stats.alloc(9 * sizeof(unsigned long long)));
+  unsigned long long* d = stats.as<unsigned long long>();
+  vg::ozaki_stats_kernel<<<1, 256, 0, st>>>(plan->w_xmet.as<double>(), ldk, (int)ldk, d);
+  VG_LAUNCHED();
+  vg::ozaki_stats_kernel<<<(unsigned)c.n_model, 256, 0, st>>>(c.d_mcat.as<double>(), ldk, (int)ldk, d + 3);
+  VG_LAUNCHED();
+  vg::ozaki_stats_kernel<<<1, 256, 0, st>>>(plan->w_core.as<double>() + c.ld_model, c.ld_model, c.n_model, d + 6);
+  VG_LAUNCHED();
+  double h[9];
+  VG_CUDA_CHECK(cudaMemcpyAsync(h, stats.p, sizeof(h), cudaMemcpyDeviceToHost, st));
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  const double amax = h[0], a1 = h[1], bmax = h[3], b1 = h[4], bnz = h[5], scale = h[6];
+  c.oz_auto_slices = vg::OZ_MAX_S;
+  for (int S = vg::OZ_MAX_S; S >= 3; --S) {
+    const double bound = std::ldexp(amax * b1 + a1 * bmax + (S - 1) * amax * bmax * bnz, -7 * S);
+    c.oz_bound[S] = scale > 0.0 ? bound / scale : 0.0;
+    if (scale > 0.0 && bound <= OZAKI_BUDGET * scale) c.oz_auto_slices = S;
+  }
+  if (!(scale > 0.0) || !(amax > 0.0)) c.oz_auto_slices = 0;    // nothing to size the digits against: DMMA
+  return VG_OK;
+}
 
 // fast_metals metal x metal terms (vega/metals.py:144-169): M_c xi_c evaluated ONCE at the
 // plan's base parameters (the reference caches the first evaluation forever), stored without
@@ -1636,6 +1857,14 @@ int vg_corr_n_folded(const vg_plan* plan, int32_t corr) {
 
 int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }
 
+int vg_corr_ozaki_slices(const vg_plan* plan, int32_t corr, double* bound_per_digits) {
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size()) return 0;
+  const Corr& c = *plan->corrs[corr];
+  if (bound_per_digits)
+    for (int S = 0; S <= vg::OZ_MAX_S; ++S) bound_per_digits[S] = c.oz_bound[S];
+  return plan->ozaki_slices < 0 ? c.oz_auto_slices : (c.oz_auto_slices > 0 ? plan->ozaki_slices : 0);
+}
+
 int vg_profile_enable(vg_plan* plan, int enable) {
   VG_REQUIRE(plan, "null plan");
   plan->profile = enable != 0;
@@ -1711,6 +1940,25 @@ int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
   } else {
     VG_CUDA_CHECK(cudaMemcpyAsync(out_dev, plan->w_x.p, (size_t)B * per * 8, cudaMemcpyDeviceToDevice, st));
   }
+  return VG_OK;
+}
+
+int vg_ozaki_gemm(const double* A, const double* B, double* C, int M, int N, int K, long long lda,
+                  long long ldb, long long ldc, int slices, int32_t* error_out, void* stream) {
+  if (!A || !B || !C || M <= 0 || N <= 0 || K <= 0 || slices < 3 || slices > vg::OZ_MAX_S) {
+    vg_set_error("vg_ozaki_gemm: bad arguments");
+    return VG_ERR_ARG;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  OzakiOperand oa, ob;
+  DevBuf ws, err;
+  VG_TRY(ozaki_slice(oa, A, lda, M, M, K, slices, st));
+  VG_TRY(ozaki_slice(ob, B, ldb, N, N, K, slices, st));
+  VG_TRY(ozaki_gemm(oa, M, ob, N, C, ldc, ws, err, st));
+  int flag = 0;
+  VG_CUDA_CHECK(cudaMemcpyAsync(&flag, err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));   // the operands above are released on return
+  if (error_out) *error_out = flag;
   return VG_OK;
 }
 

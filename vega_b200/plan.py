@@ -905,6 +905,12 @@ class DevicePlan:
         """Metal evaluations of correlation ci that OPT_FOLD_METALS serves from static vectors."""
         return self.lib.vg_corr_n_folded(self.handle, ci)
 
+    def ozaki_slices(self, ci):
+        """(digits, {S: bound / max|xi|}) of the split-integer metal GEMM of correlation ci."""
+        bounds = (C.c_double * 9)()
+        digits = self.lib.vg_corr_ozaki_slices(self.handle, ci, bounds)
+        return digits, {S: bounds[S] for S in range(3, 9)}
+
     def device_bytes(self):
         return self.lib.vg_plan_device_bytes(self.handle)
 
