@@ -133,6 +133,9 @@ typedef struct vg_eval_desc {
                                up to the linear P(k) and the static grid (peak / smooth of one
                                correlation): the two go through the per-point pass together and
                                share the Kaiser / HCD / velocity-dispersion arithmetic.  -1: none */
+  int32_t static_evol;      /* 1: the bias-evolution exponents (alpha_*, croom_*) of this evaluation are
+                               not sampled: (1+z)^alpha x growth per bin is a row built at finalize */
+  int32_t reserved0;        /* keeps the size a multiple of 8 */
 } vg_eval_desc;
 
 /* One broadband term (vega/broadband_poly.py:23-198) */

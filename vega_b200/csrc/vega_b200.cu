@@ -90,6 +90,7 @@ int upload_padded(DevBuf& buf, const double* host, long long rows, long long col
 
 struct Hankel {
   int n_ell = 0, n_out = 0, n_out_pad = 0, bounds_error = 1;
+  int uniform = 0;   // knots log-uniform to 1e-7 of a spacing: the fast gather kernel applies
   double x0[vg::PK_MAX_ELL] = {0, 0, 0, 0}, x1[vg::PK_MAX_ELL] = {0, 0, 0, 0};
   int ells[vg::PK_MAX_ELL] = {0, 0, 0, 0};
   DevBuf xk;    // [n_ell][n_out_pad]
@@ -116,7 +117,8 @@ struct EvalLayout {
   DevBuf d_pair_ids[23], d_pair_twins[23];
   int n_single[23] = {0};
   std::vector<int> mom_ids;      // evaluations in moment form
-  std::vector<int> gather_ids;   // evaluations K3 runs for
+  std::vector<int> gather_ids;   // evaluations K3 runs for: [0, n_gather_fast) through the fast kernel
+  int n_gather_fast = 0;
   std::vector<int> mxi_ids;      // LAY_MOM: evaluations whose xi stage is in moment form (static_xi)
   std::vector<int> mxi_owner;    //          evaluation whose moment tables each of them reads
   DevBuf d_mxi_ids, d_mxi_owner;
@@ -152,6 +154,7 @@ struct Corr {
   std::vector<DevBuf> coords;
   std::vector<double> opz_eff2;
   DevBuf d_coord_ptrs, d_opz_eff2;
+  DevBuf d_evolfac;              // [n_eval][ld_model] static bias-evolution x growth rows (vg_xi.cuh)
   int n_metal = 0;               // metal slots declared by the evaluations (all layouts)
   bool metal_dense = false;
   std::vector<std::vector<double>> metal_host;
@@ -304,7 +307,15 @@ struct GatherJob {
   int unit_bias;
   double* core; double* xmet; double* flat_out;
   int* status;
+  int fast;                             // the listed evaluations all qualify for xi_gather_fast_kernel
 };
+// VG_XI_FAST=0 in the environment sends every evaluation through the generic gather kernel
+// (comparison runs; the parity tests cover both)
+bool fast_gather_enabled() {
+  static const bool on = [] { const char* e = std::getenv("VG_XI_FAST"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 int launch_xi_gather(vg_plan* plan, Corr& c, const GatherJob& job, cudaStream_t st) {
   const Hankel& h = *plan->hankels[c.hankel_id];
   const int E = (int)c.evals.size();
@@ -313,6 +324,8 @@ int launch_xi_gather(vg_plan* plan, Corr& c, const GatherJob& job, cudaStream_t 
   const int n_gather = job.n_ids;
   vg::XiArgs a{};
   a.h.n_ell = h.n_ell; a.h.n_out = h.n_out; a.h.n_out_pad = h.n_out_pad; a.h.bounds_error = h.bounds_error;
+  a.h.uniform = h.uniform;
+  a.evolfac = c.d_evolfac.p ? c.d_evolfac.as<double>() : nullptr;
   for (int l = 0; l < vg::PK_MAX_ELL; ++l) {
     a.h.ells[l] = h.ells[l];
     a.h.x0[l] = h.x0[l]; a.h.x1[l] = h.x1[l];
@@ -345,10 +358,12 @@ int launch_xi_gather(vg_plan* plan, Corr& c, const GatherJob& job, cudaStream_t 
   static size_t smem_set = 0;
   if (smem > smem_set) {
     VG_CUDA_CHECK(cudaFuncSetAttribute(vg::xi_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::xi_gather_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     smem_set = smem;
   }
   dim3 grid(vg_cdiv(c.ld_model, a.bins_per_cta), n_gather, (unsigned)Bc);
-  vg::xi_gather_kernel<<<grid, 256, smem, st>>>(a);
+  if (job.fast) vg::xi_gather_fast_kernel<<<grid, 256, smem, st>>>(a);
+  else vg::xi_gather_kernel<<<grid, 256, smem, st>>>(a);
   VG_LAUNCHED();
   return VG_OK;
 }
@@ -415,6 +430,16 @@ int build_layouts(vg_plan* plan, Corr& c) {
     }
     for (int e = 0; e < E; ++e)
       if (c.evals[e].table_owner >= 0) tabslot[e] = tabslot[c.evals[e].table_owner];
+    {   // evaluations the fast gather kernel serves first (vg_xi.cuh: xi_gather_fast_kernel)
+      const Hankel& hk = *plan->hankels[c.hankel_id];
+      auto fast = [&](int e) {
+        const vg_eval_desc& d = c.evals[e];
+        return hk.uniform && hk.n_ell == 4 && plan->std_ells && d.single_ell < 0 && !d.rel && !d.asy &&
+               !d.uv_shot && d.zevol_kind[0] == 0 && d.zevol_kind[1] == 0;
+      };
+      std::stable_partition(L.gather_ids.begin(), L.gather_ids.end(), fast);
+      L.n_gather_fast = (int)std::count_if(L.gather_ids.begin(), L.gather_ids.end(), fast);
+    }
     // twins: both members per point in the same fast class of this layout
     for (int m = 0; m < 20; ++m) {
       std::vector<int>& ids = L.class_ids[m];
@@ -595,6 +620,15 @@ int vg_plan_add_hankel(vg_plan* plan, int32_t n_ell, const int32_t* ells, int32_
     h->x0[l] = xk[(size_t)l * n_out];
     h->x1[l] = xk[(size_t)l * n_out + n_out - 1];
   }
+  h->uniform = 1;
+  for (int l = 0; l < n_ell; ++l) {
+    const double* x = xk + (size_t)l * n_out;
+    const double mean = (x[n_out - 1] - x[0]) / (n_out - 1);
+    for (int j = 0; j + 1 < n_out; ++j) {
+      if (std::fabs((x[j + 1] - x[j]) / mean - 1.0) > 1e-7) h->uniform = 0;
+      if (std::fabs((x[j] - (x[0] + j * mean)) / mean) > 0.25) h->uniform = 0;
+    }
+  }
   VG_TRY(h->xk.alloc((size_t)n_ell * h->n_out_pad * 8));
   VG_CUDA_CHECK(cudaMemcpy2D(h->xk.p, (size_t)h->n_out_pad * 8, xk, (size_t)n_out * 8,
                              (size_t)n_out * 8, n_ell, cudaMemcpyHostToDevice));
@@ -639,8 +673,18 @@ int vg_plan_add_corr(vg_plan* plan, int32_t hankel_id, int32_t n_model, int32_t 
 int vg_corr_add_coords(vg_plan* plan, int32_t corr, const double* tab, double opz_eff2,
                        int32_t* coord_set) {
   VG_CORR(plan, corr);
+  // device table: the 6 rows of the caller + r mu and r sqrt(1 - mu^2) (the unscaled rp, rt of
+  // vega/correlation_func.py:226-230), so the gather does not take a square root per bin for them
+  const size_t n = (size_t)c.n_model;
+  std::vector<double> host(8 * n);
+  std::copy(tab, tab + 6 * n, host.begin());
+  for (size_t i = 0; i < n; ++i) {
+    const double r = tab[i], mu = tab[n + i];
+    host[6 * n + i] = r * mu;
+    host[7 * n + i] = r * std::sqrt(1.0 - mu * mu);
+  }
   DevBuf buf;
-  VG_TRY(upload(buf, tab, (size_t)6 * c.n_model));
+  VG_TRY(upload(buf, host.data(), host.size()));
   *coord_set = (int)c.coords.size();
   c.coords.push_back(std::move(buf));
   c.opz_eff2.push_back(opz_eff2);
@@ -786,6 +830,15 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
     for (auto& b : c.coords) cptrs.push_back(b.as<double>());
     VG_TRY(upload(c.d_coord_ptrs, cptrs.data(), cptrs.size()));
     VG_TRY(upload(c.d_opz_eff2, c.opz_eff2.data(), c.opz_eff2.size()));
+    {   // static bias-evolution x growth rows of the evaluations whose exponents are not sampled
+      const int E = (int)c.evals.size();
+      VG_TRY(c.d_evolfac.alloc((size_t)E * c.ld_model * 8));
+      dim3 egrid(vg_cdiv(c.ld_model, 256), (unsigned)E);
+      vg::evol_rows_kernel<<<egrid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), E, plan->d_base.as<double>(),
+                                                 c.d_coord_ptrs.as<const double*>(), c.d_opz_eff2.as<double>(),
+                                                 c.n_model, c.ld_model, c.d_evolfac.as<double>());
+      VG_LAUNCHED();
+    }
     vg::PkGridDev g = plan->grid_dev();
     dim3 grid(vg_cdiv(plan->nk, 128), plan->nmu);
     for (size_t e = 0; e < c.evals.size(); ++e) {
@@ -1399,7 +1452,15 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     job.unit_bias = unit_bias;
     job.core = plan->w_core.as<double>(); job.xmet = plan->w_xmet.as<double>();
     job.status = status_dev;
-    VG_TRY(launch_xi_gather(plan, c, job, st));
+    const int n_all = job.n_ids, n_fast = fast_gather_enabled() ? L.n_gather_fast : 0;
+    if (n_fast > 0) {
+      job.n_ids = n_fast; job.fast = 1;
+      VG_TRY(launch_xi_gather(plan, c, job, st));
+    }
+    if (n_all > n_fast) {
+      job.ids = L.d_gather_ids.as<int>() + n_fast; job.n_ids = n_all - n_fast; job.fast = 0;
+      VG_TRY(launch_xi_gather(plan, c, job, st));
+    }
   }
   if (!L.mxi_ids.empty()) {  // xi stage in moment form
     ProfScope prof(plan, PROF_XI, st);

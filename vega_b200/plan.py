@@ -393,6 +393,8 @@ class PlanBuilder:
         xi_names += ['alpha_' + tr['name'] for tr in (tracer1, tracer2)] + ['croom_par0', 'croom_par1']
         sampled = any(name_map.get(n, n) in self.sampled_set for n in xi_names)
         d.static_xi = int(not sampled and not (d.radiation or d.rel or d.asy or d.uv_shot))
+        evol_names = ['alpha_' + tr['name'] for tr in (tracer1, tracer2)] + ['croom_par0', 'croom_par1']
+        d.static_evol = int(not any(name_map.get(n, n) in self.sampled_set for n in evol_names))
 
     def coord_table(self, coords, cfg, tracer1=None, tracer2=None, cosmo=None):
         """[6][n] static per-bin table + (1+z_eff)^2 (vega/correlation_func.py:46-48,238-274,
