@@ -53,6 +53,66 @@ def test_newton_lockstep_bounds_and_fixed_parameters():
     assert calls[0] == M * stencil_size(3, hessian=True)
 
 
+def test_quasi_newton_matches_newton_with_fewer_evaluations():
+    """16 correlated parameters, 12 problems that share the curvature (mock fits): the gradient
+    stencil iteration + one finishing Hessian stencil reaches the same minima and Hessians as the
+    Hessian-stencil Newton iteration in a fraction of the evaluations; a shared start Hessian
+    (MonteCarloFits.fit(share_hessian=True)) cuts them further."""
+    from vega_b200.drivers import quasi_newton_lockstep
+    rng = np.random.default_rng(3)
+    M, P = 12, 16
+    sig = 10**rng.uniform(-3, 0, P)
+    c = rng.standard_normal((P, P))
+    c = c @ c.T
+    c = 0.6 * c / np.sqrt(np.outer(np.diag(c), np.diag(c))) + 0.4 * np.eye(P)
+    icov = np.linalg.inv(c * sig[:, None] * sig[None, :])
+    targets = rng.standard_normal((M, P)) * sig
+
+    def ev(theta, prob):
+        d = theta - targets[prob]
+        return np.einsum('bi,ij,bj->b', d, icov, d) + 0.02 * ((d / sig)**4).sum(axis=1)
+
+    start = np.zeros((M, P))
+    ref = newton_lockstep(ev, start, 2 * sig)
+    got = quasi_newton_lockstep(ev, start, 2 * sig)
+    shared = quasi_newton_lockstep(ev, start, 2 * sig, hess0=2 * icov)
+    for res in (got, shared):
+        assert res['converged'].all()
+        assert np.max(np.abs(res['theta'] - ref['theta']) / sig) < 5e-3      # EDM 1e-5 ~ 3e-3 sigma
+        assert np.allclose(res['fval'], ref['fval'], atol=1e-4)
+        assert np.allclose(res['hess'], ref['hess'], rtol=2e-2, atol=1e-6 * np.abs(ref['hess']).max())
+    assert got['n_eval'] < 0.8 * ref['n_eval'] and shared['n_eval'] < 0.5 * ref['n_eval']
+    # a bound every problem runs into: the parameter rests one stencil step inside it
+    lower = np.full(P, np.nan)
+    lower[3] = targets[:, 3].max() + 0.5 * sig[3]
+    start[:, 3] = lower[3] + sig[3]
+    ref = newton_lockstep(ev, start, 2 * sig, lower)
+    got = quasi_newton_lockstep(ev, start, 2 * sig, lower)
+    assert got['converged'].all() and np.all(got['theta'][:, 3] >= lower[3])
+    assert np.all(got['theta'][:, 3] < lower[3] + 0.05 * sig[3])
+    assert np.max(np.abs(got['theta'] - ref['theta']) / sig) < 1e-2
+    assert np.allclose(got['fval'], ref['fval'], atol=1e-2)
+
+
+def test_gradient_callable_for_iminuit():
+    """BatchedMinimizer.grad(*pars): one 2P + 1 batch per gradient, iminuit's calling convention."""
+    names = ['a', 'b', 'c']
+    batches = []
+
+    def chi2_batch(theta):
+        batches.append(theta.shape[0])
+        return (theta[:, 0] - 1)**2 + 3 * (theta[:, 1] + 2)**2 + theta[:, 0] * theta[:, 2] + np.exp(0.1 * theta[:, 2])
+
+    mini = BatchedMinimizer(chi2_batch, _sample(names, [0.3, 0.1, -0.2], [0.1, 0.1, 0.1]), verbose=False)
+    x = np.array([0.3, 0.1, -0.2])
+    g = mini.grad(*x)
+    assert batches == [7]
+    exact = np.array([2 * (x[0] - 1) + x[2], 6 * (x[1] + 2), x[0] + 0.1 * np.exp(0.1 * x[2])])
+    assert np.allclose(g, exact, rtol=1e-7)
+    f, g2 = mini.chi2_and_grad(x, steps=np.full(3, 1e-5))
+    assert f == pytest.approx(float(chi2_batch(x[None])[0])) and np.allclose(g2, exact, rtol=1e-8)
+
+
 def _sample(names, values, errors, limits=None):
     return {'limits': {n: (limits or {}).get(n, (None, None)) for n in names},
             'values': dict(zip(names, values)), 'errors': dict(zip(names, errors)),
@@ -72,7 +132,8 @@ def test_batched_minimizer_surface_and_two_stage_fit():
         d = theta - truth
         return np.einsum('bi,ij,bj->b', d, icov, d) + 10.
 
-    mini = BatchedMinimizer(chi2_batch, _sample(names, [1.0, -0.1, 1.5], [0.1, 0.01, 0.1]), verbose=False)
+    mini = BatchedMinimizer(chi2_batch, _sample(names, [1.0, -0.1, 1.5], [0.1, 0.01, 0.1]), verbose=False,
+                           method='newton')
     with pytest.raises(RuntimeError):
         mini.values
     mini.minimize()
@@ -108,7 +169,8 @@ def test_chi2_scan_fits_every_grid_point_in_one_batch():
     cfg = configparser.ConfigParser()
     cfg.optionxform = lambda o: o
     cfg['chi2 scan'] = {'ap': '0.95 1.05 5', 'at': '0.9 1.1 3'}
-    scan = BatchedAnalysis(chi2_batch, _sample(names, [1.01, 0.99, -0.11], [0.05, 0.05, 0.02]), cfg, verbose=False)
+    scan = BatchedAnalysis(chi2_batch, _sample(names, [1.01, 0.99, -0.11], [0.05, 0.05, 0.02]), cfg, verbose=False,
+                          method='newton')
     results = scan.chi2_scan()
     assert len(results) == 15 and scan.converged.all()
     assert batches[0] == 15 * stencil_size(1, hessian=True)       # one free parameter per grid point
@@ -227,10 +289,46 @@ def test_monte_carlo_fits_in_lock_step():
     assert np.all(at_truth - res['fval'] < 10 * len(mc.names))
     # the sharded call: a slice of the mocks gives the same answers
     part = mc.fit(mock_slice=slice(1, 3), max_iter=30)
-    # (a different batch composition changes the split-K reduction order of the GEMMs at the
-    # 1e-13 level, which the Newton iterations carry along)
+    # (the slice starts its BFGS iteration from the Hessian of ITS first mock: same minima to the
+    # EDM tolerance, 1e-5 ~ 3e-3 sigma)
     sigma = np.maximum(res['errors'][1:3], 1e-30)
-    assert np.all(np.abs(part['theta'] - res['theta'][1:3]) <= 1e-4 * sigma + 1e-12)
+    assert np.all(np.abs(part['theta'] - res['theta'][1:3]) <= 1e-2 * sigma + 1e-12)
+    # with the Hessian-stencil iteration the slice retraces the full run (a different batch
+    # composition only changes the split-K reduction order of the GEMMs at the 1e-13 level)
+    full_n = mc.fit(max_iter=30, method='newton')
+    part_n = mc.fit(mock_slice=slice(1, 3), max_iter=30, method='newton')
+    sigma = np.maximum(full_n['errors'][1:3], 1e-30)
+    assert np.all(np.abs(part_n['theta'] - full_n['theta'][1:3]) <= 1e-4 * sigma + 1e-12)
+    vega.monte_carlo = False
+
+
+@pytest.mark.gpu
+def test_lock_step_methods_and_sharded_draws_agree():
+    """quasi-Newton (gradient stencils, shared start Hessian, one finishing Hessian stencil) against
+    the Hessian-stencil Newton iteration on the device chi2, and a draw that keeps only a slice of
+    the mocks (every rank consumes the whole random stream) against the full draw."""
+    vega, oracle, theta = _c2_small()
+    fiducial = oracle.compute_model()
+    mc = MonteCarloFits(vega, fiducial_model=fiducial)
+    mc.draw(6, seed=9)
+    newton = mc.fit(max_iter=30, method='newton')
+    quasi = mc.fit(max_iter=40, method='quasi')
+    assert newton['converged'].all() and quasi['converged'].all()
+    sigma = np.maximum(newton['errors'], 1e-30)
+    assert np.max(np.abs(quasi['theta'] - newton['theta']) / sigma) < 2e-2
+    assert np.allclose(quasi['fval'], newton['fval'], atol=1e-3)
+    assert np.allclose(quasi['errors'], newton['errors'], rtol=2e-2)
+    assert quasi['n_eval'] < 0.6 * newton['n_eval']
+    full = {n: v.copy() for n, v in mc.mocks.items()}
+    part = MonteCarloFits(vega, fiducial_model=fiducial)
+    part.draw(6, seed=9, keep=slice(2, 5))
+    for n in full:
+        assert np.array_equal(part.mocks[n], full[n][2:5])
+    res = part.fit(mock_slice=slice(3, 5), max_iter=40)
+    assert list(res['mock_ids']) == [3, 4]
+    assert np.max(np.abs(res['theta'] - quasi['theta'][3:5]) / sigma[3:5]) < 2e-2
+    with pytest.raises(ValueError):
+        part.fit(mock_slice=slice(0, 2))
     vega.monte_carlo = False
 
 
@@ -365,10 +463,30 @@ def test_monte_carlo_surface_of_the_scripts(tmp_path):
     for name, truth in (('ap', 1.01), ('at', 0.99)):
         pull = (best[name][:, 0] - truth) / best[name][:, 1]
         assert np.all(np.abs(pull) < 5), (name, pull)
+    # the files the Monte Carlo scripts end with (bin/run_vega_mc_fits_mpi.py:155-159)
+    from vega_b200 import fitsio
+    vega.main_config['output']['filename'] = str(tmp_path / 'out')
+    vega._output = None
+    mc_file = vega.output.write_monte_carlo(cpu_id=0)
+    tables = {h.header.get('EXTNAME'): h.data for h in fitsio.open(mc_file)[1:]}
+    assert np.array_equal(tables['Bestfit']['values'][0], best['ap'][:, 0])
+    assert np.array_equal(tables['FitInfo']['chisq'], ana.mc_chisq)
+    # a re-draw is seen by the scalar API: the reference reads data.masked_mc_mock on every call
+    # (vega/vega_interface.py:296-312)
+    before = vega.chi2(pars)
+    for name in vega.corr_items:
+        vega.data[name].create_monte_carlo(vega._mc_fits.fiducial_model[name], seed=11 + len(name))
+    ref = oracle.chi2(pars)
+    after = vega.chi2(pars)
+    assert abs(after - ref) <= 1e-6 * max(1.0, abs(ref) / 1e4) and abs(after - before) > 1.0
+    for name in vega.corr_items:         # ... and so is a change of the covariance scale
+        vega.data[name].create_monte_carlo(vega._mc_fits.fiducial_model[name], scale=2.0, seed=5)
+    ref = oracle.chi2(pars)
+    assert abs(vega.chi2(pars) - ref) <= 1e-6 * max(1.0, abs(ref) / 1e4)
+    assert abs(vega.log_lik(pars) - oracle.log_lik(pars)) <= 1e-6 * max(1.0, abs(ref) / 1e4)
     vega.monte_carlo = False
     # mc_start_from_fit: template parameters from the BESTFIT table of a result file
     # (vega/vega_interface.py:466-471), [mc parameters] on top
-    from vega_b200 import fitsio
     fit_file = tmp_path / 'fit.fits'
     fitsio.write_tables(fit_file, [('BESTFIT', {}, {'names': np.array(['bias_eta_LYA', 'beta_LYA']),
                                                     'values': np.array([-0.199, 1.7])})])

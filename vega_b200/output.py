@@ -5,7 +5,9 @@ FVAL / VALID / ACCURATE) and `SCAN` (one column per sampled parameter + fval, gr
 in the header).  Written with the package's own FITS writer (astropy is not in the image).
 
 `write_pk` / `write_cf` add the reference's `PK_<name>` / `Xi_<name>` component tables
-(vega/output.py:100-110,351-440) from `Model.save_components`.  Not written: the HDF variant.
+(vega/output.py:100-110,351-440) from `Model.save_components`.  `write_monte_carlo` writes the
+`Bestfit` / `FitInfo` / `Mocks` tables of a Monte Carlo run (vega/output.py:442-520).  Not written:
+the HDF variant (h5py is not in the image).
 """
 import os
 from pathlib import Path
@@ -31,6 +33,7 @@ class Output:
         self.outfile = os.path.expandvars(config['filename'])
         self.output_cf = config.getboolean('write_cf', False) if hasattr(config, 'getboolean') else False
         self.output_pk = config.getboolean('write_pk', False) if hasattr(config, 'getboolean') else False
+        self.mc_output = config.get('mc_output', None)
 
     # vega/output.py:37-123
     def write_results(self, corr_funcs, params, minimizer=None, bestfit_corr_stats=None,
@@ -133,12 +136,11 @@ class Output:
     def _scan_table(self, scan_results):
         names = list(scan_results[0].keys())
         results = np.array([[res[par] for par in names] for res in scan_results], dtype=float)
-        columns = {'names': np.array(names)}
-        if len(names) != results.shape[0]:
-            # a FITS table needs equal-length columns: the name column is padded / cut to the
-            # number of grid points, the full list is also in the header
-            padded = (names + [''] * results.shape[0])[:results.shape[0]]
-            columns['names'] = np.array(padded)
+        # columns of different lengths: astropy's BinTableHDU.from_columns (vega/output.py:326) makes
+        # the table as long as the longest and fills the rest with blanks / zeros -- same here
+        rows = max(len(names), results.shape[0])
+        columns = {'names': np.array(names + [''] * (rows - len(names)))}
+        results = np.vstack([results, np.zeros((rows - results.shape[0], results.shape[1]))])
         for col, name in zip(results.T, names):
             columns[name] = col
         header = {f'hierarch name_{i}': n for i, n in enumerate(names)}
@@ -148,3 +150,40 @@ class Output:
                 header[f'hierarch {par}_max'] = float(grid[-1])
                 header[f'hierarch {par}_num_bins'] = int(len(grid))
         return ('SCAN', header, columns)
+
+    # vega/output.py:442-520
+    def write_monte_carlo(self, cpu_id=None):
+        """Best fits and mock data vectors of Analysis.run_monte_carlo as a FITS file:
+        `Bestfit` (one row per parameter: names, values[n_mocks], errors[n_mocks],
+        covariance[n_mocks * P]), `FitInfo` (one row per mock: chisq, valid_minima, valid_hesse,
+        failed_mask) and `Mocks` (one row per mock, one vector column per correlation, or `global`).
+        File: <output dir>/monte_carlo/monte_carlo[_<cpu_id>].fits, or under [output] mc_output."""
+        assert self.analysis is not None, 'Output.write_monte_carlo requires an Analysis object'
+        assert self.analysis.has_monte_carlo, (
+            'No Monte Carlo results found. Run Analysis.run_monte_carlo() first.')
+        tables = []
+        bestfits = self.analysis.mc_bestfits
+        if not bestfits:
+            print('No MC bestfit data to write.')
+        else:
+            names = np.array(list(bestfits.keys()))
+            values = np.array([bestfits[name][:, 0] for name in names])
+            errors = np.array([bestfits[name][:, 1] for name in names])
+            covariances = np.array(self.analysis.mc_covariances)
+            covariances = covariances.reshape(values.shape[1] * len(names), len(names)).T
+            tables.append(('Bestfit', {}, {'names': names, 'values': values, 'errors': errors,
+                                           'covariance': np.ascontiguousarray(covariances)}))
+            tables.append(('FitInfo', {}, {
+                'chisq': np.asarray(self.analysis.mc_chisq, dtype=float),
+                'valid_minima': np.asarray(self.analysis.mc_valid_minima, dtype=bool),
+                'valid_hesse': np.asarray(self.analysis.mc_valid_hesse, dtype=bool),
+                'failed_mask': np.asarray(self.analysis.mc_failed_mask, dtype=bool)}))
+        mocks = self.analysis.mc_mocks
+        tables.append(('Mocks', {}, {name: np.array(mocks[name], dtype=float) for name in mocks}))
+        dir_path = Path(self.outfile).parent / 'monte_carlo' if self.mc_output is None else Path(self.mc_output)
+        dir_path.mkdir(parents=True, exist_ok=True)
+        filepath = dir_path / ('monte_carlo.fits' if cpu_id is None else f'monte_carlo_{cpu_id}.fits')
+        if filepath.exists() and not self.overwrite:
+            raise OSError(f'File {filepath} already exists. Set overwrite = True in [output] to replace it.')
+        fitsio.write_tables(filepath, tables)
+        return filepath

@@ -505,13 +505,19 @@ class VegaInterface:
             else:
                 diff = corr_data.masked_data_vec - self.bestfit_model[name][corr_data.model_mask]
                 chisq = diff.T.dot(corr_data.inv_masked_cov.dot(diff))
+            # small-scale marginalisation: the template amplitudes at the best fit, added to the
+            # model that is written out (vega/vega_interface.py:612-618)
+            bestfit_marg_coeff = None
+            if not (self.monte_carlo and self._use_global_cov) and corr_data.marg_diff2coeff_matrix is not None:
+                bestfit_marg_coeff = corr_data.marg_diff2coeff_matrix.dot(diff)
+                self.bestfit_model[name] = self.bestfit_model[name] + corr_data.marg_templates.dot(bestfit_marg_coeff)
             reduced_chisq = chisq / (data_size - num_pars)
             p_value = 1 - scipy.stats.chi2.cdf(chisq, data_size - num_pars)
             print(f'{name} chi^2/(ndata-nparam): {chisq:.1f}/({data_size}-{num_pars}) '
                   f'= {reduced_chisq:.3f}, PTE={p_value:.2f}')
             self.bestfit_corr_stats[name] = {
                 'masked_size': data_size, 'chisq': chisq, 'reduced_chisq': reduced_chisq,
-                'p_value': p_value, 'bestfit_marg_coeff': None}
+                'p_value': p_value, 'bestfit_marg_coeff': bestfit_marg_coeff}
         self.chisq = self.minimizer.fmin.fval
         self.reduced_chisq = self.chisq / (self.total_data_size - num_pars)
         self.p_value = 1 - scipy.stats.chi2.cdf(self.chisq, self.total_data_size - num_pars)
