@@ -318,9 +318,12 @@ int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
                    void* stream);
 int64_t vg_stage_size(const vg_plan* plan, int32_t corr, int32_t stage);
 /* Per-stage device timing with CUDA events on the launch stream (bench.py roofline figures).
- * Tags: 0 P(k,mu)->multipoles, 1 Hankel GEMM, 2 xi gather, 3 metal GEMM, 4 distortion GEMM,
- * 5 C^-1 GEMM, 6 elementwise stages, 7 moment-form knot tables.  vg_profile_read synchronises the device, fills
- * ms_per_tag[8] / count_per_tag[8] with the totals since the last read and resets them. */
+ * Tags: 0 P(k,mu)->multipoles, 1 Hankel GEMM, 2 xi gather kernels, 3 dense metal GEMM (DMMA or the
+ * split-integer tcgen05 kernel, with its split-K reduction), 4 distortion GEMM, 5 C^-1 GEMM,
+ * 6 elementwise stages, 7 moment-form knot tables, 8 xi stage in moment form, 9 digit planes of the
+ * batch operand (split-integer GEMM), 10 rp-only metal matrices; 11..15 unused.
+ * vg_profile_read synchronises the device, fills ms_per_tag[16] / count_per_tag[16] with the
+ * totals since the last read and resets them. */
 int vg_profile_enable(vg_plan* plan, int enable);
 int vg_profile_read(vg_plan* plan, double* ms_per_tag, int64_t* count_per_tag);
 /* Number of kernels launched by the library since the last call (bench bookkeeping) */

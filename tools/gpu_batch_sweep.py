@@ -41,7 +41,7 @@ for B in [1, 8, 33, 64, 128, 256, 513, 1024, 2048, 4096]:
         for _ in range(n):
             engine.chi2_device(tt)
         torch.cuda.synchronize()
-        ms_stage, cnt_stage = (C.c_double * 8)(), (C.c_int64 * 8)()
+        ms_stage, cnt_stage = (C.c_double * 16)(), (C.c_int64 * 16)()
         lib.vg_profile_read(engine.handle, ms_stage, cnt_stage)
         lib.vg_profile_enable(engine.handle, 0)
         out[B]['stages_ms'] = {s_: round(ms_stage[i] / n, 4) for i, s_ in enumerate(bench.STAGES)}

@@ -45,8 +45,8 @@ for rep in range(3):
     torch.cuda.synchronize()
     print(f'device-resident: {e0.elapsed_time(e1):.1f} ms  {B / e0.elapsed_time(e1) * 1e3:.0f} evals/s')
 
-ms = (C.c_double * 8)()
-cnt = (C.c_int64 * 8)()
+ms = (C.c_double * 16)()
+cnt = (C.c_int64 * 16)()
 lib.vg_profile_enable(engine.handle, 1)
 engine.chi2_device(tt)
 lib.vg_profile_read(engine.handle, ms, cnt)

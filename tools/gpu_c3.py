@@ -63,7 +63,7 @@ for label, theta in (('single', base[None]), ('gradient_stencil', stencil(base, 
     for _ in range(5):
         engine.chi2_device(tt)
     torch.cuda.synchronize()
-    ms_stage, cnt_stage = (C.c_double * 8)(), (C.c_int64 * 8)()
+    ms_stage, cnt_stage = (C.c_double * 16)(), (C.c_int64 * 16)()
     lib.vg_profile_read(engine.handle, ms_stage, cnt_stage)
     lib.vg_profile_enable(engine.handle, 0)
     out[label]['stages_ms'] = {s_: round(ms_stage[i] / 5, 4) for i, s_ in enumerate(bench.STAGES)}

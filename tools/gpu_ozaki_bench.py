@@ -39,8 +39,8 @@ for slices in (ONLY or (0, -1, 6, 7, 8)):
         engine.chi2_device(tt, chi2, status)
     e1.record()
     torch.cuda.synchronize()
-    ms = (C.c_double * 8)()
-    cnt = (C.c_int64 * 8)()
+    ms = (C.c_double * 16)()
+    cnt = (C.c_int64 * 16)()
     lib.vg_profile_read(engine.handle, ms, cnt)
     lib.vg_profile_enable(engine.handle, 0)
     vals = chi2.cpu().numpy().copy()

@@ -248,7 +248,7 @@ namespace {
 struct ProfScope {
   vg_plan* plan; cudaStream_t st; cudaEvent_t e1 = nullptr;
   ProfScope(vg_plan* p, int tag, cudaStream_t s) : plan(p), st(s) {
-    if (!plan->profile) return;
+    if (!plan->profile || tag < 0) return;
     cudaEvent_t ev[2];
     for (auto& e : ev) {
       if (!plan->prof_pool.empty()) { e = plan->prof_pool.back(); plan->prof_pool.pop_back(); }
@@ -268,7 +268,8 @@ int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st);
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st);
-enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_MOMENT = 7, PROF_NTAGS = 8 };
+enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_MOMENT = 7,
+       PROF_MXI = 8, PROF_OZ_SLICE = 9, PROF_METAL_RP = 10, PROF_NTAGS = 16, PROF_NONE = -1 };
 }  // namespace
 
 namespace {
@@ -1157,7 +1158,7 @@ int ozaki_gemm(const OzakiOperand& A, long long M, const OzakiOperand& B, int N,
   } else {
     g.C = C; g.split_stride = 0;
   }
-  dim3 grid(vg_cdiv(N, vg::OZ_BN), vg_cdiv(M, vg::OZ_BM), splits);
+  dim3 grid(vg_cdiv(M, vg::OZ_BM), vg_cdiv(N, vg::OZ_BN), splits);
   int rc;
   switch (S) {
     case 3: rc = ozaki_gemm_launch<3>(ma, mb, g, grid, st); break;
@@ -1463,7 +1464,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     }
   }
   if (!L.mxi_ids.empty()) {  // xi stage in moment form
-    ProfScope prof(plan, PROF_XI, st);
+    ProfScope prof(plan, PROF_MXI, st);
     const int n_mxi = (int)L.mxi_ids.size();
     dim3 grid(vg_cdiv(c.ld_model, 256), (unsigned)n_mxi, (unsigned)vg_cdiv(Bc, vg::MXI_NB));
     vg::moment_xi_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_mxi_ids.as<int>(),
@@ -1492,16 +1493,18 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   }
   // a correlation with nothing folded keeps one set of matrices
   const bool fold_layout = layout == LAY_FOLD && !L.fold_ids.empty();
+  const int oz_S = !c.metal_dense ? 0 : (plan->ozaki_slices < 0 ? c.oz_auto_slices : plan->ozaki_slices);
   if (L.n_metal > 0) {
-    ProfScope prof(plan, (c.metal_dense || c.metal_rp) ? PROF_METAL : PROF_ELEM, st);
+    const bool use_ozaki = c.metal_dense && oz_S > 0 && Bc >= OZAKI_MIN_BATCH;
+    // (the split-integer branch times its two parts itself: PROF_NONE keeps this scope silent)
+    ProfScope prof(plan, use_ozaki ? PROF_NONE : (c.metal_rp ? PROF_METAL_RP : (c.metal_dense ? PROF_METAL : PROF_ELEM)), st);
     if (c.metal_rp) {
       VG_TRY(launch_metal_rp(c, plan->w_xmet.as<double>(), L.n_metal,
                              (fold_layout ? c.d_mrp_fold : c.d_mrp).as<double>(), Bc, plan->w_met.as<double>(), st));
     } else if (c.metal_dense) {
       const long long ldk = (long long)L.n_metal * c.ld_model;
       const DevBuf& mcat = fold_layout ? c.d_mcat_fold : c.d_mcat;
-      const int oz_S = plan->ozaki_slices < 0 ? c.oz_auto_slices : plan->ozaki_slices;
-      if (oz_S > 0 && Bc >= OZAKI_MIN_BATCH) {
+      if (use_ozaki) {
         // split-integer GEMM on tcgen05 (vg_ozaki.cuh): the operator's digit planes are built on
         // first use, the batch operand's on every call
         OzakiOperand& ob = fold_layout ? c.oz_mcat_fold : c.oz_mcat;
@@ -1509,9 +1512,15 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
           VG_TRY(ozaki_slice(ob, mcat.as<double>(), ldk, c.n_model, c.n_model, (int)ldk, oz_S, st));
           ob.src = mcat.as<double>();
         }
-        VG_TRY(ozaki_slice(plan->oz_A, plan->w_xmet.as<double>(), ldk, Bc, plan->chunk, (int)ldk, oz_S, st));
-        VG_TRY(ozaki_gemm(plan->oz_A, Bc, ob, c.n_model, plan->w_met.as<double>(), c.ld_model, plan->w_split,
-                          plan->d_oz_error, st));
+        {
+          ProfScope slice_prof(plan, PROF_OZ_SLICE, st);
+          VG_TRY(ozaki_slice(plan->oz_A, plan->w_xmet.as<double>(), ldk, Bc, plan->chunk, (int)ldk, oz_S, st));
+        }
+        {
+          ProfScope gemm_prof(plan, PROF_METAL, st);
+          VG_TRY(ozaki_gemm(plan->oz_A, Bc, ob, c.n_model, plan->w_met.as<double>(), c.ld_model, plan->w_split,
+                            plan->d_oz_error, st));
+        }
         vg::flag_status_kernel<<<vg_cdiv(Bc, 256), 256, 0, st>>>(plan->d_oz_error.as<int>(), status_dev, Bc);
         VG_LAUNCHED();
       } else {

@@ -254,7 +254,9 @@ ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   unsigned* tmem_slot = reinterpret_cast<unsigned*>(bars + 2 * L::STAGES + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tile_n = blockIdx.x, tile_m = blockIdx.y, split = blockIdx.z;
+  // m tiles vary fastest: a wave of CTAs covers every row block of a few column blocks, so the
+  // operator's digit planes (the larger operand) stream from HBM once
+  const int tile_m = blockIdx.x, tile_n = blockIdx.y, split = blockIdx.z;
   const int kb0 = split * g.kb_per_split;
   const int nkb = min(g.kb_total, kb0 + g.kb_per_split) - kb0;
 

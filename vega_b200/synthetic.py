@@ -93,8 +93,7 @@ def draw_mock_data(vega, model, seed=20261104):
         chol = np.linalg.cholesky(masked_cov)
         vec[data.data_mask] = fid[data.data_mask] + chol.dot(rng.standard_normal(int(data.data_mask.sum())))
         data._data_vec = vec
-        data._masked_data_vec = None
-    vega._engine, vega._engines = None, {}
+        data._masked_data_vec = None     # (the device re-uploads the data vector when it changes)
     return vega
 
 
