@@ -292,6 +292,15 @@ class Dist:
             self.dist.barrier()
         self.torch.cuda.synchronize()
 
+    def gather_floats(self, values):
+        """[[values of rank 0], [values of rank 1], ...] on every rank."""
+        t = self.torch.tensor(values, dtype=self.torch.float64, device='cuda')
+        if self.world == 1:
+            return [t.cpu().tolist()]
+        out = self.torch.empty(self.world * len(values), dtype=self.torch.float64, device='cuda')
+        self.dist.all_gather_into_tensor(out, t)
+        return out.view(self.world, -1).cpu().tolist()
+
     def max(self, value):
         t = self.torch.tensor([value], dtype=self.torch.float64, device='cuda')
         if self.world > 1:
@@ -475,12 +484,15 @@ def run_c5(vega, fiducial, torch, dd, world, n_mocks):
     t0 = time.perf_counter()
     res = mc.fit_sharded(max_iter=40, keys=('theta', 'fval', 'errors', 'converged', 'n_iter'))
     torch.cuda.synchronize()
-    dt = dd.max(time.perf_counter() - t0)
+    local_s = time.perf_counter() - t0
+    dt = dd.max(local_s)
+    per_rank = dd.gather_floats([local_s, float(getattr(mc, 'last_n_eval', 0))])
     vega.monte_carlo = False
     theta = res['theta']
     ndof = int(sum(int(d.data_mask.sum()) for d in vega.data.values())) - len(mc.names)
     return {'mocks': n_mocks, 'parameters': len(mc.names), 'scaling': 'strong', 'draw_s': t_draw, 'fit_wall_s': dt,
             'fits_per_s': n_mocks / dt, 'converged': int(np.sum(res['converged'])),
+            'per_rank_fit_s': [r[0] for r in per_rank], 'per_rank_chi2_evaluations': [int(r[1]) for r in per_rank],
             'mean_iterations': float(np.mean(res['n_iter'])), 'mean_fval': float(np.mean(res['fval'])),
             'degrees_of_freedom': ndof,
             'mean_pull_of_bestfit': {n: float(np.mean((theta[:, j] - vega.params[n]) / np.maximum(res['errors'][:, j], 1e-300)))

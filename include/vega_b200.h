@@ -317,6 +317,35 @@ int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
                    const double* theta_dev, int64_t B, double* out_dev, int32_t* status_dev,
                    void* stream);
 int64_t vg_stage_size(const vg_plan* plan, int32_t corr, int32_t stage);
+/* ---------------------------------------------------------------------------------
+ * Per-stage call shapes on CALLER-SUPPLIED arrays (the reference's PowerSpectrum.compute,
+ * PktoXi.compute / compute_pk_ells, CorrelationFunction.compute and Model.compute take their
+ * P(k) / P(k,mu) as arguments).  Synchronous; B <= the chunk size.
+ * ------------------------------------------------------------------------------- */
+/* New templates for Model.compute(pars, pk_full, pk_smooth) (vega/model.py:157-187): replaces the
+ * linear P(k) of the peak (pk_full - pk_smooth), smooth and full components and re-derives
+ * everything vg_plan_finalize derives from them.  Host pointers [nk]. */
+int vg_plan_set_templates(vg_plan* plan, const double* pk_full, const double* pk_smooth, void* stream);
+/* PowerSpectrum.compute(pk_lin, params, fast_metals) (vega/power_spectrum.py:87-196) of the
+ * PowerSpectrum object evaluation `eval` of the correlation stands for: out_dev[B][nmu][nk].
+ * pk_lin_host [nk] (NULL: the evaluation's own linear P(k)); fast_metals 0 / 1, -1 = as configured. */
+int vg_pk_batch(vg_plan* plan, int32_t corr, int32_t eval, const double* pk_lin_host, int32_t fast_metals,
+                const double* theta_dev, int64_t B, double* out_dev, int32_t* status_dev, void* stream);
+/* PktoXi.compute(r_grid, mu_grid, pk, single_ell) and compute_pk_ells(pk) (vega/pktoxi.py:79-163) for
+ * B caller-supplied P(k,mu) grids pk_grid_dev[B][nmu][nk] through transform `hankel_id`:
+ * xi_out_dev[B][n] on the coordinates r_host[n], mu_host[n] (n = 0: skipped), ells_out_dev
+ * [B][n_ell][nk_pad] (nullable).  Works on a plan that is not finalized (a stand-alone PktoXi). */
+int vg_pktoxi_batch(vg_plan* plan, int32_t hankel_id, const double* pk_grid_dev, int64_t B, const double* r_host,
+                    const double* mu_host, int32_t n, int32_t single_ell, double* xi_out_dev, double* ells_out_dev,
+                    int32_t* status_dev, void* stream);
+/* CorrelationFunction.compute(pk, pk_lin, PktoXi_obj, params) (vega/correlation_func.py:117-198) of
+ * the CorrelationFunction object evaluation `eval` stands for, on caller-supplied P(k,mu) grids:
+ * AP rescaling, spline read-out, bias evolution, growth and the additive terms; out_dev[B][n_model].
+ * pk_lin_sel: which template (0 peak, 1 smooth, 2 full) the relativistic / asymmetry tables are
+ * taken for (-1: the evaluation's own). */
+int vg_xi_from_grid_batch(vg_plan* plan, int32_t corr, int32_t eval, const double* pk_grid_dev, int32_t pk_lin_sel,
+                          const double* theta_dev, int64_t B, double* out_dev, int32_t* status_dev, void* stream);
+
 /* Per-stage device timing with CUDA events on the launch stream (bench.py roofline figures).
  * Tags: 0 P(k,mu)->multipoles, 1 Hankel GEMM, 2 xi gather kernels, 3 dense metal GEMM (DMMA or the
  * split-integer tcgen05 kernel, with its split-K reduction), 4 distortion GEMM, 5 C^-1 GEMM,

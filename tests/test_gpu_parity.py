@@ -357,6 +357,79 @@ def test_c3_full_size_desi_shaped(tmp_path):
     assert_xi_close(model, oracle.compute_model(dict(zip(names, theta[3]))), 'C3 stencil point')
 
 
+def stage_objects_match_the_oracle(vega, oracle, pars):
+    """The reference's per-stage call shapes on CALLER-SUPPLIED arrays:
+    PowerSpectrum.compute(pk_lin, params, fast_metals) (vega/power_spectrum.py:87),
+    PktoXi.compute_pk_ells(pk) / compute(r_grid, mu_grid, pk, single_ell) / init_from_Pk
+    (vega/pktoxi.py:61-163) and CorrelationFunction.compute(pk, pk_lin, PktoXi_obj, params)
+    (vega/correlation_func.py:117), each against the oracle's stage of the same name."""
+    from oracle.vega_oracle import pk_model
+    from vega_b200.pktoxi import PktoXi
+    fid = vega.fiducial
+    lp = oracle.local_params(pars)
+    pk_lin = fid['pk_smooth'] * (1 + 0.05 * np.cos(3 * np.log(fid['k'])))        # not one of the templates
+    for name in ('lyalya_lyalya', 'lyalya_qso'):
+        model, cm = vega.models[name], oracle.models[name]
+        for peak in (True, False):
+            lp['peak'] = peak
+            for fast in (False, True):
+                pk_ref = pk_model(cm.grid, pk_lin, lp, fast_metals=fast)
+                pk_got = model.Pk_core.compute(pk_lin, lp, fast_metals=fast)
+                assert pk_got.shape == pk_ref.shape
+                # (without b1 b2 the Kaiser term of a tracer is divided by its effective bias, which
+                # crosses zero at some k once the UV term is on: the grid points next to that pole carry
+                # the cancellation error of BOTH sides and are left out of the comparison)
+                regular = np.abs(pk_ref) <= 1e3 * np.median(np.abs(pk_ref[:, :400]))
+                assert regular.mean() > 0.99
+                assert np.max(np.abs(pk_got - pk_ref)[regular]) <= 1e-12 * np.max(np.abs(pk_ref[regular])), \
+                    (name, peak, fast)
+            pk_ref = pk_model(cm.grid, pk_lin, lp)
+            # the transform object: multipoles, xi on arbitrary coordinates, one multipole alone
+            pktoxi = model.PktoXi
+            ells = pktoxi.compute_pk_ells(pk_ref)
+            ells_ref = cm.transform.multipoles(pk_ref)
+            assert np.max(np.abs(ells - ells_ref)) <= 1e-12 * np.max(np.abs(ells_ref))
+            r = np.exp(np.linspace(np.log(3.), np.log(290.), 777))
+            r[5] = 0.
+            mu = np.linspace(-1, 1, 777)
+            xi = pktoxi.compute(r, mu, pk_ref)
+            xi_ref = cm.transform.xi(r, mu, pk_ref)
+            assert xi[5] == 0. and np.max(np.abs(xi - xi_ref)) <= XI_RTOL * np.max(np.abs(xi_ref))
+            xi2 = pktoxi.compute(r, mu, pk_ref, single_ell=2)
+            assert np.max(np.abs(xi2 - cm.transform.xi(r, mu, pk_ref, 2))) <= XI_RTOL * np.max(np.abs(xi_ref))
+            with pytest.raises(utils_errors().VegaBoundsError):
+                pktoxi.compute(np.array([1e-6, 10.]), np.array([0.5, 0.5]), pk_ref)
+            # CorrelationFunction.compute on the caller's P(k,mu)
+            xi_got = model.Xi_core.compute(pk_ref, fid['pk_smooth'], pktoxi, lp)
+            xi_want = cm.xi_core.compute(pk_ref, fid['pk_smooth'], cm.transform, lp)
+            assert np.max(np.abs(xi_got - xi_want)) <= XI_RTOL * np.max(np.abs(xi_want)), (name, peak)
+        # a metal correlation's objects
+        pair = next(iter(model.metals.Pk_metal))
+        g, tr, xim, mat = cm.metal[pair]
+        lp['peak'] = False
+        pk_ref = pk_model(g, fid['pk_full'], lp, fast_metals=True)
+        pk_got = model.metals.Pk_metal[pair].compute(fid['pk_full'], lp, fast_metals=True)
+        assert np.max(np.abs(pk_got - pk_ref)) <= 1e-12 * np.max(np.abs(pk_ref)), (name, pair)
+        xi_got = model.metals.Xi_metal[pair].compute(pk_ref, fid['pk_full'], model.metals.PktoXi[pair], lp)
+        xi_want = xim.compute(pk_ref, fid['pk_full'], tr, lp)
+        assert np.max(np.abs(xi_got - xi_want)) <= XI_RTOL * np.max(np.abs(xi_want)), (name, pair)
+    # a stand-alone transform object (bin/make_template-style use): PktoXi.init_from_Pk
+    model, cm = vega.models['lyalya_lyalya'], oracle.models['lyalya_lyalya']
+    alone = PktoXi.init_from_Pk(model.Pk_core, vega.corr_items['lyalya_lyalya'].config['model'])
+    lp['peak'] = False
+    pk_ref = pk_model(cm.grid, pk_lin, lp)
+    r, mu = np.linspace(5., 250., 300), np.full(300, 0.3)
+    assert np.max(np.abs(alone.compute(r, mu, pk_ref) - cm.transform.xi(r, mu, pk_ref))) <= \
+        XI_RTOL * np.max(np.abs(cm.transform.xi(r, mu, pk_ref)))
+    ells_ref = cm.transform.multipoles(pk_ref)
+    assert np.max(np.abs(alone.compute_pk_ells(pk_ref) - ells_ref)) <= 1e-12 * np.max(np.abs(ells_ref))
+
+
+def utils_errors():
+    from vega_b200 import utils
+    return utils
+
+
 def test_model_call_shapes_and_stage_components():
     """VegaInterface.models[name]: Model.compute / compute_direct (vega/model.py:157-208) and the
     per-stage components against the oracle's own stages (PowerSpectrum.compute,
@@ -371,8 +444,13 @@ def test_model_call_shapes_and_stage_components():
         model = vega.models[name]
         got = model.compute(pars, fid['pk_full'], fid['pk_smooth'])
         assert_xi_close({name: got}, {name: ref[name]}, 'Model.compute')
-        with pytest.raises(ValueError):
-            model.compute(pars, fid['pk_full'] * 1.01, fid['pk_smooth'])
+        # other templates than the fiducial file's (vega/model.py:157-187 takes them as arguments)
+        tilt = 1 + 0.03 * np.sin(2 * np.log(fid['k']))
+        got = model.compute(pars, fid['pk_full'] * tilt, fid['pk_smooth'] * tilt**0.5)
+        want = oracle.models[name].compute(oracle.local_params(pars), fid['pk_full'] * tilt, fid['pk_smooth'] * tilt**0.5)
+        assert_xi_close({name: got}, {name: want}, 'Model.compute, other templates')
+        again = vega.compute_model({k: pars[k] for k in ('bias_eta_LYA', 'beta_LYA', 'ap', 'sigma_velo_disp_lorentz_QSO')})
+        assert_xi_close({name: again[name]}, {name: ref[name]}, 'back on the fiducial templates')
         cm = oracle.models[name]
         lp = oracle.local_params(pars)
         for component, pk_lin, peak in (('peak', fid['pk_full'] - fid['pk_smooth'], True),
@@ -387,6 +465,7 @@ def test_model_call_shapes_and_stage_components():
             xi_ref = cm.xi_core.compute(pk_ref, pk_lin, cm.transform, lp)
             xi_got = model.xi_of(pars, component)
             assert np.max(np.abs(xi_got - xi_ref)) <= XI_RTOL * np.max(np.abs(xi_ref)), (name, component)
+    stage_objects_match_the_oracle(vega, oracle, pars)
     direct = fid['pk_full'] * (1 + 0.02 * np.cos(np.log(fid['k'])))
     got = vega.models['lyalya_qso'].compute_direct(pars, direct)
     want = oracle.compute_model({k: pars[k] for k in ('bias_eta_LYA', 'beta_LYA', 'ap', 'sigma_velo_disp_lorentz_QSO')},

@@ -115,6 +115,10 @@ _SIGNATURES = {
     'vg_corr_set_mocks': (C.c_int, [_PTR, i32, i32, _PTR]),
     'vg_chi2_batch_mc': (C.c_int, [_PTR, _PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_chi2_batch_host': (C.c_int, [_PTR, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
+    'vg_plan_set_templates': (C.c_int, [_PTR, _PTR, _PTR, _PTR]),
+    'vg_pk_batch': (C.c_int, [_PTR, i32, i32, _PTR, i32, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
+    'vg_pktoxi_batch': (C.c_int, [_PTR, i32, _PTR, C.c_int64, _PTR, _PTR, i32, i32, _PTR, _PTR, _PTR, _PTR]),
+    'vg_xi_from_grid_batch': (C.c_int, [_PTR, i32, i32, _PTR, i32, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_stage_batch': (C.c_int, [_PTR, i32, i32, i32, _PTR, C.c_int64, _PTR, _PTR, _PTR]),
     'vg_stage_size': (C.c_int64, [_PTR, i32, i32]),
     'vg_probe_dfma': (C.c_int, [C.c_int, C.c_int, _PTR, C.POINTER(f64), _PTR]),

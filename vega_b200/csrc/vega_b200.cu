@@ -60,6 +60,7 @@ struct DevBuf {
   DevBuf(DevBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
   ~DevBuf() { release(); }
   void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+  void swap(DevBuf& o) { std::swap(p, o.p); std::swap(bytes, o.bytes); }
   int alloc(size_t n, bool zero = true) {
     release();
     if (n == 0) n = 16;
@@ -822,9 +823,11 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
   DevBuf bad;
   VG_TRY(bad.alloc(sizeof(int)));
   std::vector<char> built(n_grids, 0);
+  plan->static_bad = 0;
   for (auto& cp : plan->corrs) {
     Corr& c = *cp;
     VG_REQUIRE(!c.evals.empty(), "correlation without evaluations");
+    c.allow_mxi = true;
     VG_TRY(upload(c.d_evals, c.evals.data(), c.evals.size()));
     VG_TRY(build_layouts(plan, c));
     std::vector<const double*> cptrs;
@@ -955,8 +958,7 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
   for (auto& cp : plan->corrs) {
     VG_TRY(freeze_metal_terms(plan, *cp, st));
     VG_TRY(ozaki_budget(plan, *cp, st));
-    cp->metal_host.clear();
-    cp->metal_host.shrink_to_fit();
+    // (the host copies of the metal matrices stay: vg_plan_set_templates runs finalize again)
   }
   if (plan->has_global) {
     int tot = 0;
@@ -2029,6 +2031,142 @@ int vg_ozaki_gemm(const double* A, const double* B, double* C, int M, int N, int
   VG_CUDA_CHECK(cudaMemcpyAsync(&flag, err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
   VG_CUDA_CHECK(cudaStreamSynchronize(st));   // the operands above are released on return
   if (error_out) *error_out = flag;
+  return VG_OK;
+}
+
+// ---- per-stage entry points on caller-supplied arrays ------------------------------------------
+int vg_plan_set_templates(vg_plan* plan, const double* pk_full, const double* pk_smooth, void* stream) {
+  VG_REQUIRE(plan && pk_full && pk_smooth, "vg_plan_set_templates: bad arguments");
+  VG_CUDA_CHECK(cudaDeviceSynchronize());
+  std::vector<double> peak(plan->nk);
+  for (int i = 0; i < plan->nk; ++i) peak[i] = pk_full[i] - pk_smooth[i];
+  VG_CUDA_CHECK(cudaMemcpy(plan->d_pk[0].p, peak.data(), (size_t)plan->nk * 8, cudaMemcpyHostToDevice));
+  VG_CUDA_CHECK(cudaMemcpy(plan->d_pk[1].p, pk_smooth, (size_t)plan->nk * 8, cudaMemcpyHostToDevice));
+  VG_CUDA_CHECK(cudaMemcpy(plan->d_pk[2].p, pk_full, (size_t)plan->nk * 8, cudaMemcpyHostToDevice));
+  // everything derived from the linear P(k): static moment tables, their xi stage, folded and
+  // frozen metal terms -- the same pass vg_plan_finalize runs
+  if (plan->finalized) return vg_plan_finalize(plan, stream);
+  return VG_OK;
+}
+
+int vg_pk_batch(vg_plan* plan, int32_t corr, int32_t eval, const double* pk_lin_host, int32_t fast_metals,
+                const double* theta_dev, int64_t B, double* out_dev, int32_t* status_dev, void* stream) {
+  VG_REQUIRE(plan && plan->finalized && B > 0 && out_dev && status_dev, "vg_pk_batch: bad arguments");
+  VG_CORR(plan, corr);
+  VG_REQUIRE(eval >= 0 && eval < (int)c.evals.size(), "vg_pk_batch: bad evaluation index");
+  VG_REQUIRE(B <= plan->chunk_max, "vg_pk_batch: B exceeds the chunk size");
+  cudaStream_t st = (cudaStream_t)stream;
+  vg_eval_desc d = c.evals[eval];
+  if (pk_lin_host) {
+    VG_TRY(vg_plan_set_direct_pk(plan, pk_lin_host));
+    d.pk_lin_sel = 3;
+  }
+  if (fast_metals >= 0) d.fast_metals = fast_metals;
+  DevBuf tmp;
+  VG_TRY(upload(tmp, &d, 1));
+  VG_TRY(ensure_workspace(plan, B));
+  VG_TRY(expand_params(plan, theta_dev, B, status_dev, st));
+  dim3 grid(vg_cdiv(plan->nk, 128), plan->nmu, (unsigned)B);
+  vg::pk_grid_kernel<<<grid, 128, 0, st>>>(plan->grid_dev(), tmp.as<vg_eval_desc>(), 0, plan->w_pfull.as<double>(),
+                                         plan->npf, out_dev, status_dev);
+  VG_LAUNCHED();
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));     // `tmp` is released on return
+  return VG_OK;
+}
+
+namespace {
+vg::HankelDev hankel_dev(const Hankel& h) {
+  vg::HankelDev d{};
+  d.n_ell = h.n_ell; d.n_out = h.n_out; d.n_out_pad = h.n_out_pad; d.bounds_error = h.bounds_error;
+  d.uniform = h.uniform;
+  for (int l = 0; l < vg::PK_MAX_ELL; ++l) {
+    d.ells[l] = h.ells[l]; d.x0[l] = h.x0[l]; d.x1[l] = h.x1[l];
+    d.inv_dx[l] = l < h.n_ell ? (double)(h.n_out - 1) / (h.x1[l] - h.x0[l]) : 0.0;
+  }
+  d.xk = h.xk.as<double>(); d.inv_h = h.inv_h.as<double>();
+  return d;
+}
+
+// multipoles + knot tables of B caller-supplied P(k,mu) grids: ells [B][n_ell][nk_pad], tables [B][n_ell][2 n_out_pad]
+int grid_to_tables(vg_plan* plan, const Hankel& h, const double* pk_grid_dev, long long B, DevBuf& ells, DevBuf& tables,
+                   cudaStream_t st) {
+  const int rowT = 2 * h.n_out_pad;
+  VG_TRY(ells.alloc((size_t)B * plan->n_ell * plan->nk_pad * 8));
+  VG_TRY(tables.alloc((size_t)B * plan->n_ell * rowT * 8));
+  dim3 grid(vg_cdiv(plan->nk_pad, 128), plan->n_ell, (unsigned)B);
+  vg::project_grid_kernel<<<grid, 128, 0, st>>>(pk_grid_dev, plan->nmu, plan->nk, plan->nk_pad, plan->n_ell,
+                                              plan->d_wleg.as<double>(), ells.as<double>());
+  VG_LAUNCHED();
+  VG_TRY(gemm_auto(plan, ells.as<double>(), (long long)plan->n_ell * plan->nk_pad, h.op.as<double>(), plan->nk_pad,
+                   tables.as<double>(), (long long)plan->n_ell * rowT, (int)B, rowT, plan->nk_pad, plan->n_ell,
+                   plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
+  return VG_OK;
+}
+}  // namespace
+
+int vg_pktoxi_batch(vg_plan* plan, int32_t hankel_id, const double* pk_grid_dev, int64_t B, const double* r_host,
+                    const double* mu_host, int32_t n, int32_t single_ell, double* xi_out_dev, double* ells_out_dev,
+                    int32_t* status_dev, void* stream) {
+  VG_REQUIRE(plan && pk_grid_dev && B > 0 && status_dev, "vg_pktoxi_batch: bad arguments");
+  VG_REQUIRE(hankel_id >= 0 && hankel_id < (int)plan->hankels.size(), "vg_pktoxi_batch: bad transform id");
+  VG_REQUIRE(n == 0 || (r_host && mu_host && xi_out_dev), "vg_pktoxi_batch: coordinates without an output");
+  cudaStream_t st = (cudaStream_t)stream;
+  const Hankel& h = *plan->hankels[hankel_id];
+  DevBuf ells, tables, dr, dm;
+  VG_CUDA_CHECK(cudaMemsetAsync(status_dev, 0, (size_t)B * 4, st));
+  VG_TRY(grid_to_tables(plan, h, pk_grid_dev, B, ells, tables, st));
+  if (ells_out_dev)
+    VG_CUDA_CHECK(cudaMemcpyAsync(ells_out_dev, ells.p, (size_t)B * plan->n_ell * plan->nk_pad * 8,
+                                  cudaMemcpyDeviceToDevice, st));
+  if (n > 0) {
+    VG_TRY(upload(dr, r_host, n));
+    VG_TRY(upload(dm, mu_host, n));
+    dim3 grid(vg_cdiv(n, 256), (unsigned)B);
+    vg::xi_plain_kernel<<<grid, 256, 0, st>>>(hankel_dev(h), tables.as<double>(), dr.as<double>(), dm.as<double>(), n,
+                                            single_ell, xi_out_dev, status_dev);
+    VG_LAUNCHED();
+  }
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));     // the temporaries are released on return
+  return VG_OK;
+}
+
+int vg_xi_from_grid_batch(vg_plan* plan, int32_t corr, int32_t eval, const double* pk_grid_dev, int32_t pk_lin_sel,
+                          const double* theta_dev, int64_t B, double* out_dev, int32_t* status_dev, void* stream) {
+  VG_REQUIRE(plan && plan->finalized && pk_grid_dev && B > 0 && out_dev && status_dev,
+             "vg_xi_from_grid_batch: bad arguments");
+  VG_CORR(plan, corr);
+  VG_REQUIRE(eval >= 0 && eval < (int)c.evals.size(), "vg_xi_from_grid_batch: bad evaluation index");
+  VG_REQUIRE(B <= plan->chunk_max, "vg_xi_from_grid_batch: B exceeds the chunk size");
+  cudaStream_t st = (cudaStream_t)stream;
+  const Hankel& h = *plan->hankels[c.hankel_id];
+  // a one-evaluation view of the correlation: the caller's tables in slot 0, weight 1
+  std::vector<vg_eval_desc> evs(c.evals);
+  if (pk_lin_sel >= 0 && pk_lin_sel < 3) evs[eval].pk_lin_sel = pk_lin_sel;   // rel / asy tables of that linear P(k)
+  DevBuf d_evs, d_id, d_slot, d_map, ells, tables, flat;
+  VG_TRY(upload(d_evs, evs.data(), evs.size()));
+  VG_TRY(upload(d_id, &eval, 1));
+  std::vector<int> zeros(std::max<size_t>(evs.size(), (size_t)std::max(c.n_metal, 1)), 0);
+  VG_TRY(upload(d_slot, zeros.data(), zeros.size()));
+  VG_TRY(upload(d_map, zeros.data(), zeros.size()));
+  VG_TRY(flat.alloc((size_t)B * c.ld_model * 8));
+  VG_TRY(ensure_workspace(plan, B));
+  VG_TRY(expand_params(plan, theta_dev, B, status_dev, st));
+  VG_TRY(grid_to_tables(plan, h, pk_grid_dev, B, ells, tables, st));
+  GatherJob job{};
+  job.ids = d_id.as<int>(); job.n_ids = 1;
+  job.tab_slot = d_slot.as<int>(); job.metal_map = d_map.as<int>(); job.n_metal = 1;
+  job.pfull = plan->w_pfull.as<double>(); job.B = B;
+  job.tables = tables.as<double>(); job.n_full = 1;
+  job.unit_bias = 2;
+  job.flat_out = flat.as<double>();
+  job.status = status_dev;
+  c.d_evals.swap(d_evs);                        // launch_xi_gather reads the descriptors of the correlation
+  int rc = launch_xi_gather(plan, c, job, st);
+  c.d_evals.swap(d_evs);
+  VG_TRY(rc);
+  VG_CUDA_CHECK(cudaMemcpy2DAsync(out_dev, (size_t)c.n_model * 8, flat.p, (size_t)c.ld_model * 8, (size_t)c.n_model * 8, B,
+                                  cudaMemcpyDeviceToDevice, st));
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));
   return VG_OK;
 }
 

@@ -49,7 +49,8 @@ struct XiArgs {
   const int* gather_ids;   // evaluations gathered by this launch (grid.y entries)
   const int* metal_map;    // metal slot (out_slot - 2) -> column block of xmet
   int unit_bias;           // 1: leave b1*b2 / extra bias out of the weight (finalize pass of the
-                           //    frozen fast_metals terms)
+                           //    frozen fast_metals terms); 2: weight 1 altogether (CorrelationFunction.compute
+                           //    on a caller's P(k,mu): vega/correlation_func.py:117-161 knows no weights)
   const double* const* coords;   // coordinate tables, each [6][n_model]
   const double* opz_eff2;  // per coordinate table: (1+z_eff)^2
   int n_model;
@@ -199,7 +200,7 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
   const double zexp1 = d.zevol_kind[1] == 0 ? p[d.idx_alpha[1]] : 0.0;
   const bool croom = d.zevol_kind[0] == 1 || d.zevol_kind[1] == 1;
   const int n_croom = (d.zevol_kind[0] == 1) + (d.zevol_kind[1] == 1);
-  double weight = d.weight_const;
+  double weight = a.unit_bias == 2 ? 1.0 : d.weight_const;
   if (d.weight_bias && !a.unit_bias) {
     double b1, be1, b2, be2;
     tracer_bias_beta(d, p, 0, b1, be1);
@@ -349,7 +350,7 @@ __global__ void __launch_bounds__(256) xi_gather_fast_kernel(XiArgs a) {
   const bool evol_static = d.static_evol != 0 && a.evolfac != nullptr;
   const double* evolrow = a.evolfac + (long long)e * a.ld_model;
   const double zexp0 = p[d.idx_alpha[0]], zexp1 = p[d.idx_alpha[1]];
-  double weight = d.weight_const;
+  double weight = a.unit_bias == 2 ? 1.0 : d.weight_const;
   if (d.weight_bias && !a.unit_bias) {
     double b1, be1, b2, be2;
     tracer_bias_beta(d, p, 0, b1, be1);
@@ -460,6 +461,54 @@ __global__ void evol_rows_kernel(const vg_eval_desc* __restrict__ evals, int n_e
     v *= ct[4 * n + i];
   }
   evolfac[(long long)e * ld + i] = v;
+}
+
+// ---- per-stage entry points with CALLER-SUPPLIED arrays (PktoXi / CorrelationFunction call shapes) ----
+// Multipoles of a P(k,mu) grid handed in by the caller (PktoXi.compute_pk_ells, vega/pktoxi.py:79-97):
+// out[b][l][k] = sum_i wleg[l][i] P[b][i][k], wleg = dmu (2l+1) L_l(mu_i).  grid (ceil(nk/128), n_ell, B).
+__global__ void __launch_bounds__(128)
+project_grid_kernel(const double* __restrict__ pk, int nmu, int nk, int nk_pad, int n_ell,
+                    const double* __restrict__ wleg, double* __restrict__ out) {
+  const int ik = blockIdx.x * 128 + threadIdx.x, l = blockIdx.y;
+  const long long b = blockIdx.z;
+  if (ik >= nk_pad) return;
+  double acc = 0.0;
+  if (ik < nk) {
+    const double* p = pk + b * (long long)nmu * nk + ik;
+    const double* w = wleg + (long long)l * nmu;
+    for (int i = 0; i < nmu; ++i) acc = fma(w[i], p[(long long)i * nk], acc);
+  }
+  out[(b * n_ell + l) * nk_pad + ik] = acc;
+}
+
+// xi(r, mu) on arbitrary coordinates from knot tables (PktoXi.compute, vega/pktoxi.py:99-163): spline
+// read-out in log r per multipole, times L_l(mu), summed -- or one multipole alone (single_ell >= 0).
+// r == 0 gives 0; r outside the transform's range flags VG_STATUS_BOUNDS.  grid (ceil(n/256), B).
+__global__ void __launch_bounds__(256)
+xi_plain_kernel(HankelDev h, const double* __restrict__ tables, const double* __restrict__ r,
+                const double* __restrict__ mu, int n, int single_ell, double* __restrict__ out,
+                int* __restrict__ status) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  const long long b = blockIdx.y;
+  if (i >= n) return;
+  const int row = 2 * h.n_out_pad;
+  const double* tab = tables + b * (long long)h.n_ell * row;
+  double xi = 0.0;
+  int bad = 0;
+  if (r[i] != 0.0) {
+    const double x = log(r[i]);
+    for (int l = 0; l < h.n_ell; ++l) {
+      if (single_ell >= 0 && h.ells[l] != single_ell) continue;
+      const double* xk = h.xk + l * h.n_out_pad;
+      bool outside;
+      const int j = knot_interval_inv(xk, h.n_out, x, h.x0[l], h.x1[l], h.inv_dx[l], &outside);
+      if (outside && h.bounds_error) bad |= VG_STATUS_BOUNDS;
+      const double v = spline_eval(xk, tab + l * row, tab + l * row + h.n_out_pad, j, x);
+      xi += single_ell >= 0 ? v : v * legendre_eval(h.ells[l], mu[i]);
+    }
+  }
+  out[b * n + i] = xi;
+  if (bad) atomicOr(status + b, bad);
 }
 
 }  // namespace vg

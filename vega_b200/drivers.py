@@ -754,6 +754,7 @@ class MonteCarloFits:
             res = newton_lockstep(evaluate, np.tile(start, (ids.size, 1)), errors, lower, upper, free=~fixed,
                                   max_iter=max_iter, edm_tol=edm_tol, verbose=verbose)
         res['n_eval'] += n_extra
+        self.last_n_eval = res['n_eval']
         errs = np.zeros((ids.size, len(self.names)))
         free_idx = res['free']
         try:

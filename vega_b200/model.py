@@ -11,12 +11,53 @@ import numpy as np
 from . import utils
 
 
+def _shared_pktoxi(vega, name, pk_obj):
+    from .pktoxi import PktoXi
+    engine = vega._engine_for()
+    ci = list(vega.corr_items).index(name)
+    cfg = vega.corr_items[name].config['model']
+    return PktoXi(pk_obj.k_grid, pk_obj.muk_grid, pk_obj.dmuk, cfg,
+                  _shared=(engine.handle, engine.infos[ci]['hankel_id'], engine))
+
+
+class _Metals:
+    """The per-pair objects of the reference's Metals (vega/metals.py:95-142): Pk_metal, PktoXi,
+    Xi_metal, keyed by the metal correlation."""
+
+    def __init__(self, vega, name):
+        from .correlation_func import CorrelationFunction
+        from .power_spectrum import PowerSpectrum
+        item, data = vega.corr_items[name], vega.data[name]
+        self.Pk_metal, self.Xi_metal, self._vega, self._name = {}, {}, vega, name
+        for slot, pair in enumerate(item.metal_correlations):
+            coords = data.get_metal(pair)[0] if data is not None else None
+            self.Pk_metal[pair] = PowerSpectrum(vega, name, metal_slot=slot)
+            self.Xi_metal[pair] = CorrelationFunction(vega, name, metal_slot=slot, coordinates=coords)
+        self._pktoxi = None
+
+    @property
+    def PktoXi(self):
+        if self._pktoxi is None:
+            any_pk = next(iter(self.Pk_metal.values()))
+            shared = _shared_pktoxi(self._vega, self._name, any_pk)
+            self._pktoxi = {pair: shared for pair in self.Pk_metal}
+        return self._pktoxi
+
+
 class Model:
     def __init__(self, vega, name):
         self._vega = vega
         self._name = name
         self._index = list(vega.corr_items).index(name)
         self._corr_item = vega.corr_items[name]
+        # the per-stage objects of the reference (vega/model.py:60-75), each with its call shape
+        from .correlation_func import CorrelationFunction
+        from .pktoxi import PktoXi
+        from .power_spectrum import PowerSpectrum
+        self.Pk_core = PowerSpectrum(vega, name)
+        self.Xi_core = CorrelationFunction(vega, name)
+        self._pktoxi = None
+        self.metals = _Metals(vega, name) if self._corr_item.has_metals else None
         # the save-components dictionaries (vega/model.py:41-45), filled by save_components()
         self.pk = {'peak': {}, 'smooth': {}, 'full': {}}
         self.xi = {'peak': {}, 'smooth': {}, 'full': {}}
@@ -29,21 +70,20 @@ class Model:
         base = self._vega.params
         return {k: v for k, v in pars.items() if k in base and base[k] != v}
 
-    def _check_templates(self, pk_full, pk_smooth=None):
-        fid = self._vega.fiducial
-        ok = np.array_equal(np.asarray(pk_full), fid['pk_full'])
-        if pk_smooth is not None:
-            ok = ok and np.array_equal(np.asarray(pk_smooth), fid['pk_smooth'])
-        if not ok:
-            raise ValueError('Model.compute evaluates the peak/smooth decomposition of the fiducial template '
-                             'the plan was built on; pass another P(k) through compute_direct.')
+    @property
+    def PktoXi(self):
+        """The transform object of this correlation (vega/model.py:63): shares the Hankel + spline
+        operator of the device plan."""
+        if self._pktoxi is None:
+            self._pktoxi = _shared_pktoxi(self._vega, self._name, self.Pk_core)
+        return self._pktoxi
 
     # -- vega/model.py:157-208 ------------------------------------------------------------------
     def compute(self, pars, pk_full, pk_smooth):
         """bao_amp * peak + smooth (+ metals, systematics, broadband, distortion) of this
         correlation (vega/model.py:157-187)."""
-        self._check_templates(pk_full, pk_smooth)
-        return self._vega.compute_model(self._changed(pars), run_init=False)[self._name]
+        with self._vega.templates(pk_full, pk_smooth):
+            return self._vega.compute_model(self._changed(pars), run_init=False)[self._name]
 
     def compute_direct(self, pars, pk_full):
         """The model directly from a full P(k) (vega/model.py:189-208)."""

@@ -767,6 +767,7 @@ class PlanBuilder:
                 _lib.check(lib.vg_plan_add_hankel(handle, len(ells), _dptr(ells_arr), xk.shape[1], _dptr(xk),
                                                   _dptr(op), 0 if info['legacy'] else 1, C.byref(hid)))
                 hankel_ids[hkey] = hid.value
+            info['hankel_id'] = hankel_ids[hkey]
             n_model = item.model_coordinates.r_grid.size
             n_dist = item.dist_model_coordinates.r_grid.size
             cid = C.c_int32()
@@ -882,6 +883,12 @@ class DevicePlan:
 
     def finalize(self):
         _lib.check(self.lib.vg_plan_finalize(self.handle, self._stream()))
+        self.static_status = self.lib.vg_plan_static_status(self.handle)
+
+    def set_templates(self, pk_full, pk_smooth):
+        """New peak / smooth templates (vg_plan_set_templates: runs the finalize pass again)."""
+        _lib.check(self.lib.vg_plan_set_templates(self.handle, _dptr(_f64(pk_full)), _dptr(_f64(pk_smooth)),
+                                                  self._stream()))
         self.static_status = self.lib.vg_plan_static_status(self.handle)
 
     def set_direct_pk(self, pk):

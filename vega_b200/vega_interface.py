@@ -128,6 +128,8 @@ class VegaInterface:
         self._batch_chunk = batch_chunk
         self._engine = None
         self._engines = {}
+        self._templates = None          # (pk_full, pk_smooth) when Model.compute was given other templates
+        self._templates_pinned = False
         self._fast_metals = False
 
     # -- init-time readers (vega/vega_interface.py:665-851) ---------------------------
@@ -288,6 +290,8 @@ class VegaInterface:
         absent from [parameters] is merged the way _get_lcl_prms merges it
         (vega/vega_interface.py:402-404): it joins the parameter set with the value passed."""
         from .plan import PlanBuilder
+        if self._templates is not None and not self._templates_pinned:
+            self.set_templates(self.fiducial['pk_full'], self.fiducial['pk_smooth'])
         base_names = list(self.sample_params['limits'].keys())
         extra = [n for n in dict.fromkeys(names) if n not in base_names]
         key = tuple(sorted(extra))
@@ -306,6 +310,8 @@ class VegaInterface:
             builder = PlanBuilder(self, sampled=base_names + list(key), extra_params=new_values)
             entry = {'engine': builder.build(chunk=self._batch_chunk), 'params': dict(self.params),
                      'new': new_values, 'data_token': None}
+            if self._templates is not None:
+                entry['engine'].set_templates(*self._templates)
             self._engines[key] = entry
         engine = entry['engine']
         if self._has_data:
@@ -347,6 +353,39 @@ class VegaInterface:
                            for n in sampled], dtype=np.float64)
         force = np.array([n in utils.BLIND_FIXED_PARS for n in sampled], dtype=np.int32)
         return offset, force
+
+    def set_templates(self, pk_full, pk_smooth):
+        """Templates other than the fiducial file's for Model.compute(pars, pk_full, pk_smooth)
+        (vega/model.py:157-187): the device re-derives what it derived from the linear P(k)
+        (vg_plan_set_templates).  A no-op when they are the ones in use."""
+        fid = self.fiducial
+        pk_full = np.ascontiguousarray(pk_full, dtype=np.float64)
+        pk_smooth = np.ascontiguousarray(pk_smooth, dtype=np.float64)
+        current = self._templates if self._templates is not None else (fid['pk_full'], fid['pk_smooth'])
+        if np.array_equal(pk_full, current[0]) and np.array_equal(pk_smooth, current[1]):
+            return
+        if pk_full.size != fid['k'].size or pk_smooth.size != pk_full.size:
+            raise ValueError('Templates must be sampled on the k grid of the fiducial file.')
+        is_fiducial = np.array_equal(pk_full, fid['pk_full']) and np.array_equal(pk_smooth, fid['pk_smooth'])
+        self._templates = None if is_fiducial else (pk_full.copy(), pk_smooth.copy())
+        for entry in self._engines.values():
+            entry['engine'].set_templates(pk_full, pk_smooth)
+
+    def templates(self, pk_full, pk_smooth):
+        """Context in which the engine evaluates on the given templates (Model.compute); the
+        interface's own compute_model / chi2 / log_lik always use the fiducial file's, as the
+        reference does (vega/vega_interface.py:236-240)."""
+        import contextlib
+
+        @contextlib.contextmanager
+        def scope():
+            self.set_templates(pk_full, pk_smooth)
+            self._templates_pinned = True
+            try:
+                yield
+            finally:
+                self._templates_pinned = False
+        return scope()
 
     def _direct_mode(self, engine, direct_pk):
         """Context in which the engine evaluates Model.compute_direct on `direct_pk`
