@@ -401,22 +401,28 @@ def run_c3(vega, names, torch, dd, rank, lib):
         tt = engine.theta_tensor(theta)
         chi2 = torch.empty(theta.shape[0], dtype=torch.float64, device='cuda')
         status = torch.empty(theta.shape[0], dtype=torch.int32, device='cuda')
-        for _ in range(3):
-            engine.chi2_device(tt, chi2, status)
-        torch.cuda.synchronize()
-        lib.vg_profile_enable(engine.handle, 1)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(10):
-            engine.chi2_device(tt, chi2, status)
-        e1.record()
-        torch.cuda.synchronize()
+        def timed(n=10):
+            for _ in range(4):
+                engine.chi2_device(tt, chi2, status)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                engine.chi2_device(tt, chi2, status)
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / n
+        replays0 = lib.vg_plan_graph_replays(engine.handle)
+        ms = timed()                                   # batches of <= 96 vectors replay a CUDA graph
+        graphed = lib.vg_plan_graph_replays(engine.handle) > replays0
+        lib.vg_profile_enable(engine.handle, 1)        # per-stage events: ordinary launches
+        ms_launches = timed()
         ms_stage, cnt_stage = (C.c_double * 16)(), (C.c_int64 * 16)()
         lib.vg_profile_read(engine.handle, ms_stage, cnt_stage)
         lib.vg_profile_enable(engine.handle, 0)
-        ms = e0.elapsed_time(e1) / 10
         out[label] = {'vectors': int(theta.shape[0]), 'ms_per_pass': ms, 'evals_per_s': theta.shape[0] / (ms * 1e-3),
-                      'stages_ms': {s: round(ms_stage[i] / 10, 4) for i, s in enumerate(STAGES) if ms_stage[i] > 0}}
+                      'cuda_graph': bool(graphed), 'ms_per_pass_ordinary_launches': ms_launches,
+                      'stages_ms': {s: round(ms_stage[i] / 14, 4) for i, s in enumerate(STAGES) if ms_stage[i] > 0}}
     t0 = time.perf_counter()
     vega.minimize()
     mini = vega.minimizer

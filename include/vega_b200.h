@@ -288,6 +288,9 @@ int vg_corr_ozaki_slices(const vg_plan* plan, int32_t corr, double* bound_per_di
 /* Status bits raised while building the static grids (e.g. VG_STATUS_ARINYO): they apply
  * to every vector */
 int vg_plan_static_status(const vg_plan* plan);
+/* chi2 passes of at most 96 vectors are replayed as CUDA graphs (after two ordinary calls per batch
+ * size; VG_GRAPHS=0 in the environment turns it off): number of replays so far */
+int64_t vg_plan_graph_replays(const vg_plan* plan);
 /* Bytes of device memory held by the plan (static state + current workspace) */
 int64_t vg_plan_device_bytes(const vg_plan* plan);
 

@@ -532,3 +532,39 @@ def test_component_tables_of_write_pk_and_write_cf(tmp_path):
         # the distorted pair is pinned against the unmodified reference by the sensitivity golden)
         assert np.array_equal(m.xi['peak']['core'], m.xi_of(pars, 'peak'))
         assert pk.data['smooth_core'].shape == m.pk['smooth']['core'].shape == (1000, vega.fiducial['k'].size)
+
+
+def test_small_batches_replay_a_cuda_graph():
+    """chi2 passes of <= 96 vectors: two ordinary calls per batch size, then a captured CUDA graph
+    on fixed staging buffers.  Replays with NEW parameter vectors must give what the ordinary path
+    gives (the 1024-vector path never takes a graph), also after a larger batch has re-allocated
+    work buffers, after an option changed, and in Monte Carlo mode."""
+    from vega_b200 import _lib
+    vega, oracle, theta = make_c2(1100, width=1.0)
+    engine = vega._engine_for()
+    lib = engine.lib
+    ref = vega.chi2_batch(theta)                      # chunks of 1024 + 76: the tail goes through chi2_chunk_small
+    for size in (1, 33, 76):
+        for rep in range(5):
+            rows = np.arange(rep * size, (rep + 1) * size)
+            got = vega.chi2_batch(theta[rows])
+            assert np.max(np.abs(got - ref[rows])) <= 1e-9 * np.max(np.abs(ref[rows])), (size, rep)
+    assert lib.vg_plan_graph_replays(engine.handle) >= 6
+    n0 = lib.vg_plan_graph_replays(engine.handle)
+    vega.chi2_batch(theta)                            # a large batch in between
+    got = vega.chi2_batch(theta[:33])
+    assert np.max(np.abs(got - ref[:33])) <= 1e-9 * np.max(np.abs(ref[:33]))
+    engine.set_option(_lib.OPT_FOLD_METALS, 1)        # an option drops the graphs
+    a = vega.chi2_batch(theta[:33])
+    engine.set_option(_lib.OPT_FOLD_METALS, 0)
+    for _ in range(4):
+        b = vega.chi2_batch(theta[:33])
+    assert np.max(np.abs(a - ref[:33])) <= 1e-9 * np.max(np.abs(ref[:33]))
+    assert np.max(np.abs(b - ref[:33])) <= 1e-9 * np.max(np.abs(ref[:33]))
+    assert lib.vg_plan_graph_replays(engine.handle) > n0
+    # the scalar API against the oracle after the graph is in place
+    names = vega.theta_names
+    for i in range(4):
+        value = vega.chi2(dict(zip(names, theta[i])))
+    want = oracle.chi2(dict(zip(names, theta[3])))
+    assert abs(value - want) <= 1e-6 * max(1.0, abs(want) / 1e4)

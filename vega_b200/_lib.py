@@ -107,6 +107,7 @@ _SIGNATURES = {
     'vg_plan_set_global_invcov': (C.c_int, [_PTR, i32, _PTR]),
     'vg_plan_finalize': (C.c_int, [_PTR, _PTR]),
     'vg_plan_device_bytes': (C.c_int64, [_PTR]),
+    'vg_plan_graph_replays': (C.c_int64, [_PTR]),
     'vg_plan_static_status': (C.c_int, [_PTR]),
     'vg_profile_enable': (C.c_int, [_PTR, C.c_int]),
     'vg_profile_read': (C.c_int, [_PTR, _PTR, _PTR]),

@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <string>
 #include <vector>
@@ -51,6 +52,10 @@ namespace {
 
 inline int pad16(long long n) { return (int)((n + 15) / 16 * 16); }
 
+// bumped by every device allocation: a captured CUDA graph holds raw pointers into the plan's
+// buffers, so it is only replayed while no buffer has been (re)allocated since its capture
+static long long g_alloc_generation = 0;
+
 struct DevBuf {
   void* p = nullptr;
   size_t bytes = 0;
@@ -64,6 +69,7 @@ struct DevBuf {
   int alloc(size_t n, bool zero = true) {
     release();
     if (n == 0) n = 16;
+    ++g_alloc_generation;
     VG_CUDA_CHECK(cudaMalloc(&p, n));
     bytes = n;
     if (zero) VG_CUDA_CHECK(cudaMemset(p, 0, n));
@@ -223,6 +229,18 @@ struct vg_plan {
   DevBuf w_pfull, w_pkell, w_tables, w_core, w_xmet, w_met, w_x, w_y, w_diff, w_partial, w_split, w_fold,
       w_chi2, w_status, w_theta;
   void* pinned = nullptr; size_t pinned_bytes = 0;
+  // CUDA graphs of the chi2 pass for small batches (B <= GRAPH_MAX_B): the ~50-100 launches of a
+  // pass are replayed as one graph on fixed staging buffers; keyed on (B, options); dropped
+  // whenever the plan's state changes
+  struct GraphEntry { cudaGraphExec_t exec = nullptr; int seen = 0; long long launches = 0, generation = -1; };
+  std::map<long long, GraphEntry> graphs;
+  cudaStream_t gstream = nullptr;
+  DevBuf w_mockidx;
+  long long graph_replays = 0;
+  void drop_graphs() {
+    for (auto& kv : graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    graphs.clear();
+  }
   // optional per-stage timing with CUDA events (bench.py roofline figures)
   bool profile = false;
   struct ProfRec { int tag; cudaEvent_t e0, e1; };
@@ -534,6 +552,8 @@ int vg_plan_create(int32_t n_params, const double* base, int32_t n_theta, const 
 
 int vg_plan_destroy(vg_plan* plan) {
   if (!plan) return VG_OK;
+  plan->drop_graphs();
+  if (plan->gstream) cudaStreamDestroy(plan->gstream);
   if (plan->pinned) cudaFreeHost(plan->pinned);
   delete plan;
   return VG_OK;
@@ -541,12 +561,14 @@ int vg_plan_destroy(vg_plan* plan) {
 
 int vg_plan_set_chunk(vg_plan* plan, int64_t chunk) {
   VG_REQUIRE(plan && chunk > 0, "bad chunk");
+  plan->drop_graphs();
   plan->chunk_max = chunk;
   return VG_OK;
 }
 
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
   VG_REQUIRE(plan, "null plan");
+  plan->drop_graphs();
   if (option == VG_OPT_MOMENTS) { plan->use_moments = value != 0; return VG_OK; }
   if (option == VG_OPT_FOLD_METALS) { plan->fold_metals = value != 0; return VG_OK; }
   if (option == VG_OPT_OZAKI) {
@@ -571,6 +593,7 @@ int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
 
 int vg_plan_set_direct_pk(vg_plan* plan, const double* pk_host) {
   VG_REQUIRE(plan && pk_host, "vg_plan_set_direct_pk: bad arguments");
+  plan->drop_graphs();
   VG_CUDA_CHECK(cudaDeviceSynchronize());
   VG_CUDA_CHECK(cudaMemcpy(plan->d_pk[3].p, pk_host, (size_t)plan->nk * 8, cudaMemcpyHostToDevice));
   return VG_OK;
@@ -769,6 +792,7 @@ int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t*
                      const double* data, const double* invcov) {
   VG_CORR(plan, corr);
   VG_REQUIRE(n_mask > 0, "empty data mask");
+  plan->drop_graphs();
   for (int j = 0; j < n_mask; ++j)
     VG_REQUIRE(mask_idx[j] >= 0 && mask_idx[j] < c.n_dist, "mask index out of range");
   const bool new_mask = c.mask_host.size() != (size_t)n_mask ||
@@ -794,6 +818,7 @@ int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t*
 
 int vg_plan_set_global_invcov(vg_plan* plan, int32_t n_total, const double* invcov) {
   VG_REQUIRE(plan && n_total > 0, "bad global covariance");
+  plan->drop_graphs();
   plan->n_total = n_total; plan->ld_total = pad16(n_total);
   VG_TRY(upload_padded(plan->d_global_invcov, invcov, n_total, n_total, plan->ld_total));
   plan->has_global = true;
@@ -802,6 +827,7 @@ int vg_plan_set_global_invcov(vg_plan* plan, int32_t n_total, const double* invc
 
 int vg_plan_finalize(vg_plan* plan, void* stream) {
   VG_REQUIRE(plan && !plan->corrs.empty(), "plan has no correlation");
+  plan->drop_graphs();
   cudaStream_t st = (cudaStream_t)stream;
   // number of static grids referenced
   int n_grids = 0;
@@ -1739,6 +1765,74 @@ int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi
   return VG_OK;
 }
 
+// chi2_chunk through a CUDA graph when the batch is small: the pass of a single vector or of a
+// gradient stencil is 50-100 launches of a few microseconds each, so launch latency, not the
+// device, sets its time.  The first two calls of a (B, options) key run normally (allocations and
+// function attributes settle), the third is captured on an internal stream, later ones replay.
+constexpr long long GRAPH_MAX_B = 96;
+bool graphs_enabled() {
+  static const bool on = [] { const char* e = std::getenv("VG_GRAPHS"); return !(e && e[0] == '0'); }();
+  return on;
+}
+int chi2_chunk_small(vg_plan* plan, const double* theta_dev, long long Bc, double* chi2_dev, int* status_dev,
+                     cudaStream_t st, const int* mock_idx = nullptr) {
+  if (Bc > GRAPH_MAX_B || plan->profile || !graphs_enabled())
+    return chi2_chunk(plan, theta_dev, Bc, chi2_dev, status_dev, st, mock_idx);
+  const long long key = Bc | ((long long)plan->use_moments << 20) | ((long long)plan->fold_metals << 21) |
+                        ((long long)plan->direct_mode << 22) | ((long long)(mock_idx != nullptr) << 23) |
+                        ((long long)(plan->ozaki_slices + 1) << 24);
+  vg_plan::GraphEntry& g = plan->graphs[key];
+  if (g.exec && g.generation != g_alloc_generation) {     // a buffer moved since the capture
+    cudaGraphExecDestroy(g.exec);
+    g.exec = nullptr;
+  }
+  if (!g.exec && g.seen < 2) {
+    ++g.seen;
+    return chi2_chunk(plan, theta_dev, Bc, chi2_dev, status_dev, st, mock_idx);
+  }
+  // fixed staging buffers: the graph is independent of the caller's pointers
+  double* th = plan->w_theta.as<double>();
+  double* c2 = plan->w_chi2.as<double>();
+  int* stt = plan->w_status.as<int>();
+  if (plan->n_theta > 0 && theta_dev != th)
+    VG_CUDA_CHECK(cudaMemcpyAsync(th, theta_dev, (size_t)Bc * plan->n_theta * 8, cudaMemcpyDeviceToDevice, st));
+  if (mock_idx) {
+    VG_TRY(plan->w_mockidx.ensure((size_t)GRAPH_MAX_B * sizeof(int)));
+    VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_mockidx.p, mock_idx, (size_t)Bc * sizeof(int), cudaMemcpyDeviceToDevice, st));
+  }
+  if (!g.exec) {
+    if (!plan->gstream) VG_CUDA_CHECK(cudaStreamCreateWithFlags(&plan->gstream, cudaStreamNonBlocking));
+    VG_CUDA_CHECK(cudaStreamSynchronize(st));
+    const long long before = g_launches + vg::gemm_launches();
+    VG_CUDA_CHECK(cudaStreamBeginCapture(plan->gstream, cudaStreamCaptureModeRelaxed));
+    const int rc = chi2_chunk(plan, th, Bc, c2, stt, plan->gstream, mock_idx ? plan->w_mockidx.as<int>() : nullptr);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t end = cudaStreamEndCapture(plan->gstream, &graph);
+    if (rc != VG_OK || end != cudaSuccess || !graph) {
+      if (graph) cudaGraphDestroy(graph);
+      cudaGetLastError();
+      g.seen = -1000000;                      // never try this key again
+      return chi2_chunk(plan, theta_dev, Bc, chi2_dev, status_dev, st, mock_idx);
+    }
+    g.launches = g_launches + vg::gemm_launches() - before;
+    g.generation = g_alloc_generation;
+    const cudaError_t inst = cudaGraphInstantiate(&g.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (inst != cudaSuccess) {
+      g.exec = nullptr; g.seen = -1000000;
+      cudaGetLastError();
+      return chi2_chunk(plan, theta_dev, Bc, chi2_dev, status_dev, st, mock_idx);
+    }
+  } else {
+    g_launches += g.launches;
+  }
+  VG_CUDA_CHECK(cudaGraphLaunch(g.exec, st));
+  ++plan->graph_replays;
+  if (chi2_dev != c2) VG_CUDA_CHECK(cudaMemcpyAsync(chi2_dev, c2, (size_t)Bc * 8, cudaMemcpyDeviceToDevice, st));
+  if (status_dev != stt) VG_CUDA_CHECK(cudaMemcpyAsync(status_dev, stt, (size_t)Bc * 4, cudaMemcpyDeviceToDevice, st));
+  return VG_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -1770,7 +1864,7 @@ int vg_chi2_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* chi
   VG_TRY(ensure_workspace(plan, chunk));
   for (long long b0 = 0; b0 < B; b0 += chunk) {
     const long long Bc = std::min<long long>(chunk, B - b0);
-    VG_TRY(chi2_chunk(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st));
+    VG_TRY(chi2_chunk_small(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st));
   }
   return VG_OK;
 }
@@ -1778,6 +1872,7 @@ int vg_chi2_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* chi
 int vg_corr_set_mocks(vg_plan* plan, int32_t corr, int32_t n_mocks, const double* mocks) {
   VG_CORR(plan, corr);
   VG_REQUIRE(n_mocks > 0 && mocks && c.n_mask > 0, "vg_corr_set_mocks: set the data mask first");
+  plan->drop_graphs();
   VG_TRY(upload(c.d_mocks, mocks, (size_t)n_mocks * c.n_mask));
   c.n_mocks = n_mocks;
   return VG_OK;
@@ -1792,7 +1887,7 @@ int vg_chi2_batch_mc(vg_plan* plan, const double* theta_dev, const int32_t* mock
   VG_TRY(ensure_workspace(plan, chunk));
   for (long long b0 = 0; b0 < B; b0 += chunk) {
     const long long Bc = std::min<long long>(chunk, B - b0);
-    VG_TRY(chi2_chunk(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st,
+    VG_TRY(chi2_chunk_small(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st,
                       mock_idx_dev + b0));
   }
   return VG_OK;
@@ -1823,7 +1918,7 @@ int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, doubl
       VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_theta.p, pin_theta, (size_t)Bc * plan->n_theta * 8,
                                     cudaMemcpyHostToDevice, st));
     }
-    VG_TRY(chi2_chunk(plan, plan->w_theta.as<double>(), Bc, plan->w_chi2.as<double>(),
+    VG_TRY(chi2_chunk_small(plan, plan->w_theta.as<double>(), Bc, plan->w_chi2.as<double>(),
                       plan->w_status.as<int>(), st));
     VG_CUDA_CHECK(cudaMemcpyAsync(pin_chi2, plan->w_chi2.p, (size_t)Bc * 8, cudaMemcpyDeviceToHost, st));
     VG_CUDA_CHECK(cudaMemcpyAsync(pin_status, plan->w_status.p, (size_t)Bc * 4, cudaMemcpyDeviceToHost, st));
@@ -1928,6 +2023,7 @@ int vg_corr_n_folded(const vg_plan* plan, int32_t corr) {
 }
 
 int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }
+int64_t vg_plan_graph_replays(const vg_plan* plan) { return plan ? plan->graph_replays : 0; }
 
 int vg_corr_ozaki_slices(const vg_plan* plan, int32_t corr, double* bound_per_digits) {
   if (!plan || corr < 0 || corr >= (int)plan->corrs.size()) return 0;
@@ -1939,6 +2035,7 @@ int vg_corr_ozaki_slices(const vg_plan* plan, int32_t corr, double* bound_per_di
 
 int vg_profile_enable(vg_plan* plan, int enable) {
   VG_REQUIRE(plan, "null plan");
+  plan->drop_graphs();
   plan->profile = enable != 0;
   return VG_OK;
 }
