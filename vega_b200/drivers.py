@@ -223,6 +223,23 @@ def newton_lockstep(eval_batch, theta0, steps, lower=None, upper=None, free=None
 # ---------------------------------------------------------------------------------------------
 # quasi-Newton on gradient stencils, Hessian stencil only to finish
 # ---------------------------------------------------------------------------------------------
+def _positive_definite(H, floor=1e-4):
+    """Nearest usable start Hessian(s) for a BFGS iteration: in the diagonally scaled space the
+    eigenvalues are lifted to at least `floor` times the largest (a finite-difference Hessian taken
+    away from the minimum can be indefinite along the bias / beta degeneracies, and BFGS keeps
+    whatever definiteness it starts from)."""
+    H = np.array(H, dtype=np.float64)
+    single = H.ndim == 2
+    H = H[None] if single else H
+    d = np.sqrt(np.abs(np.einsum('aii->ai', H))) + 1e-300
+    Hs = H / d[:, :, None] / d[:, None, :]
+    Hs = 0.5 * (Hs + np.swapaxes(Hs, 1, 2))
+    w, v = np.linalg.eigh(Hs)
+    w = np.maximum(w, floor * np.max(w, axis=1, keepdims=True))
+    out = np.einsum('aij,aj,akj->aik', v, w, v) * d[:, :, None] * d[:, None, :]
+    return out[0] if single else out
+
+
 def _lm_steps(g, H, lam, frozen):
     """Batched Levenberg-Marquardt steps in the diagonally scaled space: solves
     (Hs + lam I) p = -gs per problem; parameters flagged in `frozen` [A, F] (resting on a bound
@@ -279,12 +296,12 @@ def quasi_newton_lockstep(eval_batch, theta0, steps, lower=None, upper=None, fre
     g_best = np.zeros((M, F))
     H = np.tile(np.eye(F), (M, 1, 1))
     if hess0 is not None:
-        H[:] = np.asarray(hess0, dtype=np.float64)
+        H[:] = _positive_definite(np.asarray(hess0, dtype=np.float64))
         d0 = np.einsum('aii->ai', H)
         ls.scale = np.where(d0 > 0, np.sqrt(2. / np.where(d0 > 0, d0, 1.)), ls.scale)
     have_best = np.zeros(M, bool)
     have_H = np.full(M, hess0 is not None)
-    lam = np.full(M, 1e-3 if hess0 is None else 1e-6)
+    lam = np.full(M, 1e-3)
     done = np.zeros(M, bool)
     trial = x_best.copy()
     for it in range(max_iter):
@@ -739,13 +756,19 @@ class MonteCarloFits:
         kwargs = {}
         n_extra = 0
         if method == 'quasi' and share_hessian and ids.size > 1 and (~fixed).any():
+            # the Hessian every mock starts from: the Hessian stencil of the first mock AT THE START
+            # POINT (the right quadratic model for the first step of every mock: they share start,
+            # model and covariance; measured on the DESI-shaped model, the Hessian at a converged
+            # minimum is the worse model there -- the first Newton steps overshoot along the
+            # bias / beta / HCD degeneracies and are rejected).  A finite-difference Hessian away
+            # from the minimum can be indefinite along those directions: quasi_newton_lockstep
+            # lifts its eigenvalues (_positive_definite) before use.
             ls = _Lockstep(lambda theta, prob: self.chi2(theta, ids[prob]), start[None, :], errors, lower, upper,
                            ~fixed, 0.02)
             h = 0.02 * ls.scale[:1]
             f0, g, hess0 = ls.evaluate(np.array([0]), ls.clip(start[None, ~fixed], h), h, True)
             n_extra = ls.n_eval
-            d = np.diag(hess0[0])
-            if np.all(np.isfinite(hess0)) and np.all(d > 0):
+            if np.all(np.isfinite(hess0)):
                 kwargs['hess0'] = hess0[0]
         if method == 'quasi':
             res = quasi_newton_lockstep(evaluate, np.tile(start, (ids.size, 1)), errors, lower, upper, free=~fixed,
