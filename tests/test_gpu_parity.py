@@ -499,6 +499,36 @@ def test_device_covariance_inverse_and_log_det():
     assert abs(r @ got_inv @ r - r @ ref_inv @ r) <= 1e-6
 
 
+def test_device_marginalisation_matrices():
+    """Init-time small-scale marginalisation at DESI size on the device (vega/data.py:96-128,
+    762-828): SVD compression of the template covariance and the residual -> amplitudes matrix
+    (T^T C^-1 T + S)^-1 T^T C^-1, against the host LAPACK route the reference takes."""
+    from vega_b200 import utils
+    rng = np.random.default_rng(12)
+    n, nt = 4300, 60
+    assert n >= utils.DEVICE_LINALG_MIN
+    r = np.linspace(0, 1, n)
+    t = np.stack([np.exp(-0.5 * ((r - c) / 0.01)**2) for c in rng.random(nt - 4)] +
+                 [np.exp(-0.5 * ((r - 0.5) / 0.01)**2)] * 4, axis=1) * 5.0        # 4 degenerate templates
+    got, modes = utils.template_covariance(t)
+    u, sv, _ = np.linalg.svd(t, full_matrices=False)
+    keep = sv > 1e-8 * sv[0]
+    ref = np.dot(u[:, keep] * sv[keep]**2, u[:, keep].T)
+    assert modes == int(keep.sum()) and nt - 8 <= modes <= nt - 3      # the 4 equal templates are one mode
+    assert np.max(np.abs(got - ref)) <= 1e-10 * np.max(np.abs(ref))
+    idx = np.arange(n)
+    cov = 0.3 ** (np.abs(idx[:, None] - idx[None, :]) / 2.0) * 1e-8 + 1e-9 * np.eye(n)
+    inv_cov = np.linalg.inv(cov)
+    t_u = t[:, :40]
+    prior = np.full(40, 5.0**-2)
+    got = utils.diff_to_coeff_matrix(t_u, inv_cov, prior)
+    g = t_u.T @ inv_cov
+    ref = np.linalg.inv(g @ t_u + np.diag(prior)).dot(g)
+    assert np.max(np.abs(got - ref)) <= 1e-8 * np.max(np.abs(ref))
+    diff = rng.standard_normal(n) * 1e-4
+    assert np.max(np.abs(got @ diff - ref @ diff)) <= 1e-10 * np.max(np.abs(ref @ diff))
+
+
 @pytest.mark.gpu
 def test_component_tables_of_write_pk_and_write_cf(tmp_path):
     """The save-components dictionaries (vega/model.py:113-116,151-153) and the PK_ / Xi_ tables

@@ -10,6 +10,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/vega_b200.h"
 #include "vg_common.cuh"
 #include "vg_gemm.cuh"
@@ -264,10 +266,21 @@ struct vg_plan {
 
 namespace {
 // Brackets a stage with two events on the launch stream when profiling is on.
+// VG_NVTX=1 in the environment wraps every stage in an NVTX range named after its tag (timelines
+// of nsys / ncu --nvtx); off by default (a range costs a library call per stage)
+bool nvtx_enabled() {
+  static const bool on = [] { const char* e = std::getenv("VG_NVTX"); return e && e[0] == '1'; }();
+  return on;
+}
+const char* const PROF_NAMES[16] = {"vg:pk_ell", "vg:hankel_gemm", "vg:xi_gather", "vg:metal_gemm", "vg:dm_gemm",
+                                    "vg:chi2_gemm", "vg:elementwise", "vg:moment_tables", "vg:moment_xi",
+                                    "vg:ozaki_slice", "vg:metal_rp", "vg:11", "vg:12", "vg:13", "vg:14", "vg:15"};
 struct ProfScope {
-  vg_plan* plan; cudaStream_t st; cudaEvent_t e1 = nullptr;
+  vg_plan* plan; cudaStream_t st; cudaEvent_t e1 = nullptr; bool range = false;
   ProfScope(vg_plan* p, int tag, cudaStream_t s) : plan(p), st(s) {
-    if (!plan->profile || tag < 0) return;
+    if (tag < 0) return;
+    if (nvtx_enabled()) { nvtxRangePushA(PROF_NAMES[tag & 15]); range = true; }
+    if (!plan->profile) return;
     cudaEvent_t ev[2];
     for (auto& e : ev) {
       if (!plan->prof_pool.empty()) { e = plan->prof_pool.back(); plan->prof_pool.pop_back(); }
@@ -277,7 +290,10 @@ struct ProfScope {
     e1 = ev[1];
     plan->prof_recs.push_back({tag, ev[0], ev[1]});
   }
-  ~ProfScope() { if (e1) cudaEventRecord(e1, st); }
+  ~ProfScope() {
+    if (e1) cudaEventRecord(e1, st);
+    if (range) nvtxRangePop();
+  }
 };
 int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, long long ldb,
               double* C, long long ldc, int M, int N, int K, int batch, long long strideA,

@@ -14,7 +14,7 @@ Differences from the reference, all init-time representation choices:
 """
 import numpy as np
 
-from . import fitsio
+from . import fitsio, utils
 from .coordinates import Coordinates
 from .utils import find_file, compute_masked_invcov, compute_log_cov_det
 
@@ -115,11 +115,10 @@ class Data:
         else:
             self.cov_marg_update = None
         t_masked = self.marg_templates[self.model_mask, :]
-        G = t_masked.T @ inv_cov
-        A = np.asarray((t_masked.T @ G.T).T)
+        prior = None
         if not (item.fit_marg_scales and item.marginalize_match_data_bins):
-            A = A + np.diag(np.full(ntemps, item.marginalize_small_scales_prior_sigma**-2))
-        self.marg_diff2coeff_matrix = np.linalg.inv(A).dot(np.asarray(G))
+            prior = np.full(ntemps, item.marginalize_small_scales_prior_sigma**-2)
+        self.marg_diff2coeff_matrix = utils.diff_to_coeff_matrix(t_masked, inv_cov, prior)
 
     def marg_projector(self):
         """Q = I - T_masked D2C on the masked bins: with the template amplitudes fitted on the fly
@@ -153,12 +152,9 @@ class Data:
         t = (templates * item.marginalize_small_scales_prior_sigma)[self.model_mask, :].toarray()
         print(f'  There are {templates.shape[1]} templates. '
               'SVD of template matrix to remove degenerate modes.')
-        u, sv, _ = np.linalg.svd(t, full_matrices=False)
-        keep = sv > factor * sv[0]
-        u, sv = u[:, keep], sv[keep]
-        print(f'  There are {keep.sum()} remaining modes for marginalization.')
-        self.num_marg_modes = int(keep.sum())
-        return templates, np.dot(u * sv**2, u.T)
+        update, self.num_marg_modes = utils.template_covariance(t, factor)
+        print(f'  There are {self.num_marg_modes} remaining modes for marginalization.')
+        return templates, update
 
     # -- properties with the reference's names ------------------------------------
     @property

@@ -254,3 +254,50 @@ def uv_shotnoise_table(ntau=100, nrho=10000):
         y = rho * np.abs(1 - t / rho)
         amp[i] = -np.sum(drho * np.exp(-rho) / rho * (expn(1, x) - expn(1, y)))
     return tau, amp
+
+
+def _on_device(n_rows):
+    if n_rows < DEVICE_LINALG_MIN:
+        return False
+    import torch
+    return torch.cuda.is_available()
+
+
+def template_covariance(t, factor=1e-8):
+    """sum over the non-degenerate modes of the marginalisation templates t [n_mask, n_templates]:
+    SVD, modes with singular value <= factor * largest dropped, U diag(s^2) U^T
+    (vega/data.py:813-828).  Returns (covariance update [n_mask, n_mask], number of modes kept).
+    From DEVICE_LINALG_MIN rows on, SVD and product run on the GPU (cuSOLVER / cuBLAS through torch,
+    init time); below, numpy's LAPACK as the reference."""
+    if _on_device(t.shape[0]):
+        import torch
+        dev = torch.from_numpy(np.ascontiguousarray(t, dtype=np.float64)).cuda()
+        u, sv, _ = torch.linalg.svd(dev, full_matrices=False)
+        keep = sv > factor * sv[0]
+        u, sv = u[:, keep], sv[keep]
+        return torch.matmul(u * sv**2, u.T).cpu().numpy(), int(keep.sum())
+    u, sv, _ = np.linalg.svd(t, full_matrices=False)
+    keep = sv > factor * sv[0]
+    u, sv = u[:, keep], sv[keep]
+    return np.dot(u * sv**2, u.T), int(keep.sum())
+
+
+def diff_to_coeff_matrix(t_masked, inv_cov, prior_diag=None):
+    """(T^T C^-1 T + S)^-1 T^T C^-1: the matrix that turns a residual into the best-fit template
+    amplitudes (vega/data.py:113-128).  t_masked [n_mask, n_templates] (dense or scipy sparse),
+    inv_cov [n_mask, n_mask], prior_diag [n_templates] or None.  Device route as above."""
+    dense = np.asarray(t_masked.toarray() if hasattr(t_masked, 'toarray') else t_masked, dtype=np.float64)
+    if _on_device(dense.shape[0]):
+        import torch
+        t = torch.from_numpy(np.ascontiguousarray(dense)).cuda()
+        c = torch.from_numpy(np.ascontiguousarray(inv_cov, dtype=np.float64)).cuda()
+        g = torch.matmul(t.T, c)
+        a = torch.matmul(g, t)
+        if prior_diag is not None:
+            a = a + torch.diag(torch.from_numpy(np.asarray(prior_diag, dtype=np.float64)).cuda())
+        return torch.linalg.solve(a, g).cpu().numpy()
+    g = np.asarray(t_masked.T @ inv_cov)
+    a = np.asarray((t_masked.T @ g.T).T)
+    if prior_diag is not None:
+        a = a + np.diag(prior_diag)
+    return np.linalg.inv(a).dot(g)
