@@ -519,7 +519,7 @@ def test_device_marginalisation_matrices():
     idx = np.arange(n)
     cov = 0.3 ** (np.abs(idx[:, None] - idx[None, :]) / 2.0) * 1e-8 + 1e-9 * np.eye(n)
     inv_cov = np.linalg.inv(cov)
-    t_u = t[:, :40]
+    t_u = np.stack([np.exp(-0.5 * ((r - c) / 0.01)**2) for c in np.linspace(0.05, 0.95, 40)], axis=1) * 5.0
     prior = np.full(40, 5.0**-2)
     got = utils.diff_to_coeff_matrix(t_u, inv_cov, prior)
     g = t_u.T @ inv_cov
