@@ -135,7 +135,9 @@ typedef struct vg_eval_desc {
                                share the Kaiser / HCD / velocity-dispersion arithmetic.  -1: none */
   int32_t static_evol;      /* 1: the bias-evolution exponents (alpha_*, croom_*) of this evaluation are
                                not sampled: (1+z)^alpha x growth per bin is a row built at finalize */
-  int32_t reserved0;        /* keeps the size a multiple of 8 */
+  int32_t idx_weight_extra2; /* a second parameter multiplying the weight, -1 none: bao_amp on the metal
+                               terms of the PEAK component when no-metal-decomp = False
+                               (vega/model.py:119-131,186) */
 } vg_eval_desc;
 
 /* One broadband term (vega/broadband_poly.py:23-198) */

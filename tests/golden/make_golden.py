@@ -181,6 +181,9 @@ def main():
             model = vega.compute_model(pars, run_init=True, direct_pk=direct)
             for name, xi in model.items():
                 out[f'{key}/{i}/xi/{name}'] = np.asarray(xi, dtype=float)
+            if key in VARIANTS and VARIANTS[key].get('pk_only'):
+                print(key, i, {name: xi.shape for name, xi in model.items()})
+                continue
             out[f'{key}/{i}/chi2'] = np.array(vega.chi2(pars, direct_pk=direct))
             out[f'{key}/{i}/log_lik'] = np.array(vega.log_lik(pars, direct_pk=direct))
             if key.startswith('c1_marg'):

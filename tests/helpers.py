@@ -336,6 +336,16 @@ VARIANTS = {
         extra_main_params={'beta_metals': 0.42, **_separate_auto_bias_params()},
         cases=[{'beta_metals': 0.7, 'bias_SiII(1190)_SiIII(1207)': 1.4},
                {'bias_eta_SiII(1260)': -0.004, 'bias_SiII(1193)_CIV(eff)': 0.2, 'beta_LYA': 1.5}]),
+    # vega/model.py:119-131,178-186: the metal terms split into peak and smooth like the core
+    'v_metal_decomp': dict(
+        sections={'model': {'no-metal-decomp': False}},
+        cases=[{'bao_amp': 0.7, 'bias_eta_SiIII(1207)': -0.006, 'ap': 1.03, 'at': 0.97},
+               {'sigmaNL_par': 8., 'beta_SiII(1260)': 0.8, 'bias_eta_LYA': -0.19}]),
+    # vega/model.py:106-107: compute_model returns P_ell(k) (no chi2 exists for this output)
+    'v_model_pk': dict(
+        main={'control': {'model_pk': True}}, pk_only=True,
+        cases=[{'bao_amp': 0.8, 'bias_eta_LYA': -0.19, 'sigmaNL_per': 4.},
+               {'beta_LYA': 1.4, 'bias_hcd': -0.03, 'L0_hcd': 8.}]),
 }
 
 
@@ -375,6 +385,8 @@ def make_variant_config(tmp_dir, key, base='configs/full_configs/main.ini', corr
         new_paths.append(str(new_path))
     main['data sets']['ini files'] = ' '.join(new_paths)
     for section, options in spec.get('main', {}).items():
+        if section not in main:
+            main[section] = {}
         for k, v in options.items():
             main[section][k] = str(v)
     for k, v in spec.get('extra_main_params', {}).items():

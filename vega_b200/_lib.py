@@ -46,7 +46,7 @@ class EvalDesc(C.Structure):
         ('weight_const', f64),
         ('table_owner', i32), ('mock_los_mode', i32), ('idx_los_smooth_amp', i32),
         ('mock_bin_size', f64), ('direct', i32), ('frozen', i32), ('static_xi', i32), ('pk_twin', i32),
-        ('static_evol', i32), ('reserved0', i32),
+        ('static_evol', i32), ('idx_weight_extra2', i32),
     ]
 
     def __init__(self):

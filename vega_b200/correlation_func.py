@@ -42,11 +42,19 @@ class CorrelationFunction:
                                       'templates of the plan; pass one of them as pk_lin.')
         return -1
 
+    def _metal_eval(self, params):
+        """Evaluation of the plan this metal object stands for: one per pair, or -- with
+        no-metal-decomp = False (vega/model.py:119-131) -- the peak / smooth one of the pair."""
+        item = self._vega.corr_items[self._name]
+        if item.config['model'].getboolean('no-metal-decomp', True):
+            return 2 + self._metal_slot
+        return 2 + 2 * self._metal_slot + (0 if params.get('peak') else 1)
+
     def compute(self, pk, pk_lin, PktoXi_obj, params):
         import torch
         vega = self._vega
         if self._metal_slot is not None:
-            eval_index = 2 + self._metal_slot
+            eval_index = self._metal_eval(params)
         else:
             if 'peak' not in params:
                 raise KeyError("params['peak'] selects the component (vega/model.py:176,179).")

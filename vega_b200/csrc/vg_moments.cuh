@@ -181,6 +181,7 @@ moment_xi_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__
       w = b1 * b2;
     }
     if (d.idx_weight_extra >= 0) w *= p[d.idx_weight_extra];
+    if (d.idx_weight_extra2 >= 0) w *= p[d.idx_weight_extra2];
 #pragma unroll
     for (int m = 0; m < MOM_MAX; ++m) cq[threadIdx.x][m] = w * q[m];
     if (threadIdx.x == 0) {
@@ -246,6 +247,7 @@ moment_fold_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict
       w = b1 * b2;
     }
     if (d.idx_weight_extra >= 0) w *= p[d.idx_weight_extra];
+    if (d.idx_weight_extra2 >= 0) w *= p[d.idx_weight_extra2];
 #pragma unroll
     for (int m = 0; m < MOM_MAX; ++m) cq[((size_t)j * MOM_MAX + m) * MXI_NB + e] = w * q[m];
     if (e == 0) s_na[j] = (o.hcd_model && (o.hcd_on[0] || o.hcd_on[1])) ? 3 : 1;

@@ -87,6 +87,7 @@ __device__ __forceinline__ double metal_bias_weight(const vg_eval_desc& d, const
   tracer_bias_beta(d, p, 1, b2, be2);
   double w = b1 * b2;
   if (d.idx_weight_extra >= 0) w *= p[d.idx_weight_extra];
+  if (d.idx_weight_extra2 >= 0) w *= p[d.idx_weight_extra2];
   return w;
 }
 

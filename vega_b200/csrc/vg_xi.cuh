@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(256) xi_gather_kernel(XiArgs a) {
     weight *= b1 * b2;
   }
   if (d.idx_weight_extra >= 0 && !a.unit_bias) weight *= p[d.idx_weight_extra];
+  if (d.idx_weight_extra2 >= 0 && !a.unit_bias) weight *= p[d.idx_weight_extra2];
   double* out;
   if (a.flat_out) out = a.flat_out + ((long long)blockIdx.y * a.B + b) * a.ld_model;
   else if (d.out_slot < 2) out = a.core + ((long long)d.out_slot * a.B + b) * a.ld_model;
@@ -358,6 +359,7 @@ __global__ void __launch_bounds__(256) xi_gather_fast_kernel(XiArgs a) {
     weight *= b1 * b2;
   }
   if (d.idx_weight_extra >= 0 && !a.unit_bias) weight *= p[d.idx_weight_extra];
+  if (d.idx_weight_extra2 >= 0 && !a.unit_bias) weight *= p[d.idx_weight_extra2];
   const bool radiation = d.radiation && !d.is_peak;
   double rad0 = 0.0, rad1 = 0.0, rad2 = 0.0, rad3 = 0.0;
   if (radiation) {

@@ -489,10 +489,7 @@ class PlanBuilder:
         item, data = vega.corr_items[name], vega.data[name]
         cfg = item.config
         mcfg = cfg['model']
-        if item.model_pk:
-            raise NotImplementedError('model_pk (P(k) multipole output) is not part of the B200 path.')
-        if not mcfg.getboolean('no-metal-decomp', True):
-            raise NotImplementedError('no-metal-decomp = False is not built.')
+        no_decomp = mcfg.getboolean('no-metal-decomp', True)
         if mcfg.getboolean('fht_extrap', False):
             raise NotImplementedError('fht_extrap = True is not built.')
         binsizes = (item.data_coordinates.rp_binsize, item.data_coordinates.rt_binsize)
@@ -528,6 +525,15 @@ class PlanBuilder:
                 else self.fast_metals_override
             separate_auto = mcfg.getboolean('separate-metal-auto-biases', False)
             fast_bias = mcfg.getboolean('fast_metal_bias', True) or fast_metals or separate_auto
+            if fast_metals and not no_decomp:
+                # the reference's metal x metal cache is keyed on the pair alone (vega/metals.py:
+                # 144-170), so with two components it would hand the peak term back as the smooth one
+                raise NotImplementedError('fast_metals needs no-metal-decomp = True.')
+            # no-metal-decomp = False (vega/model.py:119-131,178-186): the metal terms go through
+            # the peak/smooth split like the core -- one evaluation per pair and component, the
+            # peak one weighted by bao_amp, both through the same metal matrix
+            components = [(False, 2, -1)] if no_decomp else \
+                [(True, 0, self.col('bao_amp')), (False, 1, -1)]
             single_beta = mcfg.getboolean('single-metal-beta', False)
             main = [item.tracer1['name'], item.tracer2['name']]
             # fast_metals (vega/metals.py:144-207,278-336): growth_rate pinned to the fiducial value,
@@ -553,41 +559,46 @@ class PlanBuilder:
                             name_map[f'beta_{n}'] = 'beta_metals'
                             key_state[f'beta_{n}'] = key_state['beta_metals']
                 with_main = n1 in main or n2 in main
-                d = EvalDesc()
-                self.fill_pk(d, metcfg, tr1, tr2, item.name, False, 2, fast_bias, name_map=name_map,
-                             data_binsizes=binsizes)
-                owner = None
-                if fast_metals and with_main:
-                    betas = tuple(key_state.get(name_map.get(f'beta_{n}', f'beta_{n}')) for n in pair)
-                    key = (betas, tuple(sorted(key_state.items(), key=lambda kv: kv[0])))
-                    owner = owners.get(key)
-                    if owner is None:
-                        owners[key] = (len(info['evals']), len(info['coords']), tr1, tr2, f'{n1}x{n2}',
-                                       dict(name_map))
-                if owner is not None:
-                    # cache hit: the xi of the first pair with this key (its tracers, its coordinates)
-                    # is re-used; only the bias product and the metal matrix are this pair's
-                    o_eval, o_coords, o_tr1, o_tr2, o_pair, o_map = owner
-                    self.fill_xi(d, metcfg, o_tr1, o_tr2, False, o_pair, True, name_map=o_map)
-                    d.coord_set, d.table_owner = o_coords, o_eval
-                else:
-                    info['coords'].append(self.coord_table(coords, metcfg, tr1, tr2, cosmo))
-                    self.fill_xi(d, metcfg, tr1, tr2, False, f'{n1}x{n2}', True, name_map=name_map)
-                    d.coord_set = len(info['coords']) - 1
-                d.out_slot = 2 + c
-                d.weight_bias = int(fast_bias)
-                d.frozen = int(fast_metals and not with_main)
-                if fast_bias and not with_main and separate_auto and n1 != n2:
-                    if self.col(f'bias_{n1}_{n2}') >= 0:
-                        d.idx_weight_extra = self.col(f'bias_{n1}_{n2}')
-                    elif self.col(f'bias_{n2}_{n1}') >= 0:
-                        d.idx_weight_extra = self.col(f'bias_{n2}_{n1}')
+                pair_coords = None
+                for comp_peak, comp_sel, comp_weight in components:
+                    d = EvalDesc()
+                    self.fill_pk(d, metcfg, tr1, tr2, item.name, comp_peak, comp_sel, fast_bias,
+                                 name_map=name_map, data_binsizes=binsizes)
+                    owner = None
+                    if fast_metals and with_main:
+                        betas = tuple(key_state.get(name_map.get(f'beta_{n}', f'beta_{n}')) for n in pair)
+                        key = (betas, tuple(sorted(key_state.items(), key=lambda kv: kv[0])))
+                        owner = owners.get(key)
+                        if owner is None:
+                            owners[key] = (len(info['evals']), len(info['coords']), tr1, tr2, f'{n1}x{n2}',
+                                           dict(name_map))
+                    if owner is not None:
+                        # cache hit: the xi of the first pair with this key (its tracers, its coordinates)
+                        # is re-used; only the bias product and the metal matrix are this pair's
+                        o_eval, o_coords, o_tr1, o_tr2, o_pair, o_map = owner
+                        self.fill_xi(d, metcfg, o_tr1, o_tr2, comp_peak, o_pair, True, name_map=o_map)
+                        d.coord_set, d.table_owner = o_coords, o_eval
                     else:
-                        raise ValueError(f'Separate metal auto biases is on, but no bias_{n1}_{n2}'
-                                         f' or bias_{n2}_{n1} parameter found for {pair}.')
-                d.weight_const = 2.0 if (main[0] == main[1] and n1 != n2) else 1.0
-                info['evals'].append(d)
-                info['metal_mats'].append(mat)
+                        if pair_coords is None:
+                            info['coords'].append(self.coord_table(coords, metcfg, tr1, tr2, cosmo))
+                            pair_coords = len(info['coords']) - 1
+                        self.fill_xi(d, metcfg, tr1, tr2, comp_peak, f'{n1}x{n2}', True, name_map=name_map)
+                        d.coord_set = pair_coords
+                    d.out_slot = 2 + len(info['metal_mats'])
+                    d.idx_weight_extra2 = comp_weight
+                    d.weight_bias = int(fast_bias)
+                    d.frozen = int(fast_metals and not with_main)
+                    if fast_bias and not with_main and separate_auto and n1 != n2:
+                        if self.col(f'bias_{n1}_{n2}') >= 0:
+                            d.idx_weight_extra = self.col(f'bias_{n1}_{n2}')
+                        elif self.col(f'bias_{n2}_{n1}') >= 0:
+                            d.idx_weight_extra = self.col(f'bias_{n2}_{n1}')
+                        else:
+                            raise ValueError(f'Separate metal auto biases is on, but no bias_{n1}_{n2}'
+                                             f' or bias_{n2}_{n1} parameter found for {pair}.')
+                    d.weight_const = 2.0 if (main[0] == main[1] and n1 != n2) else 1.0
+                    info['evals'].append(d)
+                    info['metal_mats'].append(mat)
 
         # Model.compute_direct (vega/model.py:189-208): the `full` component from an externally
         # supplied isotropic P(k) -- the smooth component's options with pars['peak'] = False

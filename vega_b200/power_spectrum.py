@@ -31,9 +31,17 @@ class PowerSpectrum:
         self.k_par_grid = self.k_grid * self.muk_grid
         self.k_trans_grid = self.k_grid * np.sqrt(1 - self.muk_grid**2)
 
+    def _metal_eval(self, params):
+        """Evaluation of the plan this metal object stands for: one per pair, or -- with
+        no-metal-decomp = False (vega/model.py:119-131) -- the peak / smooth one of the pair."""
+        item = self._vega.corr_items[self._name]
+        if item.config['model'].getboolean('no-metal-decomp', True):
+            return 2 + self._metal_slot
+        return 2 + 2 * self._metal_slot + (0 if params.get('peak') else 1)
+
     def _eval_index(self, params):
         if self._metal_slot is not None:
-            return 2 + self._metal_slot
+            return self._metal_eval(params)
         if 'peak' not in params:
             raise KeyError("params['peak'] selects the component (vega/model.py:176,179).")
         return 0 if params['peak'] else 1

@@ -397,6 +397,10 @@ class VegaInterface:
             if direct_pk is None:
                 yield
                 return
+            for item in self.corr_items.values():
+                if item.has_metals and not item.config['model'].getboolean('no-metal-decomp', True):
+                    # vega/model.py:119-121 would evaluate the metals on direct_pk as well
+                    raise NotImplementedError('direct_pk with no-metal-decomp = False is not built.')
             engine.set_direct_pk(direct_pk)
             engine.set_option(_lib.OPT_DIRECT_PK, 1)
             try:
@@ -421,7 +425,12 @@ class VegaInterface:
     # -- the reference's scalar API (batch of one) ----------------------------------------------
     def compute_model(self, params=None, run_init=True, direct_pk=None, marg_coeff=None):
         """Model xi of every correlation for one parameter dict
-        (vega/vega_interface.py:208-248).  Returns {name: ndarray(n_dist)}."""
+        (vega/vega_interface.py:208-248).  Returns {name: ndarray(n_dist)}; with `model_pk` in
+        [control], the P_ell(k) multipoles [n_ell, nk] instead (vega/model.py:106-107,186)."""
+        if self.model_pk:
+            bao_amp = self._get_lcl_prms(params)['bao_amp']
+            return {name: bao_amp * self.models[name].pk_ells(params, 'peak')
+                    + self.models[name].pk_ells(params, 'smooth') for name in self.corr_items}
         engine = self._engine_for(tuple(params) if params else (), params)
         with self._direct_mode(engine, direct_pk):
             models, status = engine.model_device(engine.theta_tensor(self._theta_row(engine, params)))
