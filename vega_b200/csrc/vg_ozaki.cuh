@@ -216,11 +216,12 @@ __device__ __forceinline__ unsigned long long oz_smem_desc(unsigned smem_addr) {
   d |= (unsigned long long)4u << 61;                            // layout type         [61,64)
   return d;
 }
-// instruction descriptor (cute::UMMA::InstrDescriptor): s32 accumulator, s8 x s8, both K-major
-__device__ __forceinline__ constexpr unsigned oz_instr_desc() {
+// instruction descriptor (cute::UMMA::InstrDescriptor): s32 accumulator, s8 x s8, both K-major;
+// n = 64 * (digit planes of the batch operand one instruction covers)
+__device__ __forceinline__ constexpr unsigned oz_instr_desc(int n = OZ_BN) {
   return (2u << 4)                      // c_format = S32
          | (1u << 7) | (1u << 10)       // a_format = b_format = INT8 (signed)
-         | ((unsigned)(OZ_BN >> 3) << 17)   // n_dim
+         | ((unsigned)(n >> 3) << 17)       // n_dim
          | ((unsigned)(OZ_BM >> 4) << 24);  // m_dim
 }
 
@@ -287,8 +288,13 @@ ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       oz_tma_load_3d(dst + L::A_STAGE, &map_b, full_bar(s), (kb0 + i) * OZ_BK, tile_n * OZ_BN, 0);
     }
   } else if (warp == 1 && lane == 0) {
-    // ===== MMA issuer: diagonal d accumulates sum_{t+u=d} A_t B_u^T in TMEM columns [d*64, d*64+64) =====
-    constexpr unsigned idesc = oz_instr_desc();
+    // ===== MMA issuer: diagonal d accumulates sum_{t+u=d} A_t B_u^T in TMEM columns [d*64, d*64+64).
+    // The planes B_u of a stage lie one after the other (64 rows of 64 bytes each), and plane u of
+    // the product with A_t lands in accumulator t+u, so ONE instruction of N = 64 m columns does
+    // A_t x [B_u .. B_u+m-1] into the m adjacent accumulators t+u .. t+u+m-1.  That reads the A
+    // tile from shared memory once per <= 256 columns instead of once per 64: 10 instructions per
+    // 32-byte K step for S = 7 instead of 28, ~110 B/clk of operand reads instead of 192 (the
+    // shared-memory port moves 128 B/clk, a 128 x 64 x 32 instruction takes 32 clk).
     for (int i = 0; i < nkb; ++i) {
       const int s = i % L::STAGES;
       const unsigned ph = (unsigned)(i / L::STAGES) & 1u;
@@ -298,13 +304,15 @@ ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
 #pragma unroll
       for (int ks = 0; ks < OZ_BK / 32; ++ks) {
 #pragma unroll
-        for (int d = 0; d < S; ++d) {
-#pragma unroll
-          for (int t = 0; t <= d; ++t) {
-            const unsigned long long ad = oz_smem_desc(a0 + t * (OZ_BM * OZ_BK) + ks * 32);
-            const unsigned long long bd = oz_smem_desc(b0 + (d - t) * (OZ_BN * OZ_BK) + ks * 32);
-            oz_mma_i8(tmem_base + d * OZ_BN, ad, bd, idesc, (i > 0 || ks > 0 || t > 0) ? 1u : 0u);
-          }
+        for (int t = 0; t < S; ++t) {
+          const int m = S - t;                              // planes u = 0 .. m-1 pair with A_t
+          const int m0 = m <= 4 ? m : (m + 1) / 2;          // first instruction, then the rest
+          const unsigned long long ad = oz_smem_desc(a0 + t * (OZ_BM * OZ_BK) + ks * 32);
+          const unsigned acc = (i > 0 || ks > 0 || t > 0) ? 1u : 0u;
+          oz_mma_i8(tmem_base + t * OZ_BN, ad, oz_smem_desc(b0 + ks * 32), oz_instr_desc(m0 * OZ_BN), acc);
+          if (m > m0)
+            oz_mma_i8(tmem_base + (t + m0) * OZ_BN, ad, oz_smem_desc(b0 + m0 * (OZ_BN * OZ_BK) + ks * 32),
+                      oz_instr_desc((m - m0) * OZ_BN), acc);
         }
       }
       oz_mma_commit(empty_bar(s));          // frees the stage when its MMAs have read it
