@@ -393,6 +393,20 @@ int vg_ozaki_gemm(const double* A, const double* B, double* C, int M, int N, int
 int vg_dgemm_tn(const double* A, const double* B, double* C, int M, int N, int K,
                 long long lda, long long ldb, long long ldc, double alpha, double beta,
                 int splits, double* workspace, void* stream);
+/* Split-K FP64 tensor-core GEMM C[m,n] = alpha sum_k A[m,k] B[n,k] that allocates NOTHING: no
+ * counterpart in the reference -- added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  It is vg_dgemm_tn with splits >= 2 and beta = 0, the split-K partials held in a file-scope
+ * device array of VG_STATIC_SCRATCH_DOUBLES doubles (16 MiB, resident on every GPU that loads the
+ * library until exit) instead of a caller workspace.  Device pointers, row strides in doubles,
+ * K % 16 == 0, lda and ldb even (as vg_dgemm_tn).  VG_ERR_ARG with a message when
+ * splits * M * (N rounded up to even) > VG_STATIC_SCRATCH_DOUBLES.  Asynchronous on `stream`; no
+ * cudaMalloc / cudaFree / allocating library call.  Every call on a device shares the one array
+ * (it keeps the last call's partials; each call overwrites all it reads, nothing needs clearing):
+ * two calls that overlap on the GPU -- different streams, different threads -- race. */
+#define VG_STATIC_SCRATCH_DOUBLES (1 << 21)
+int vg_dgemm_tn_static(const double* A, const double* B, double* C, int M, int N, int K, long long lda,
+                       long long ldb, long long ldc, double alpha, int splits, void* stream);
 #ifdef __cplusplus
 }
 #endif

@@ -14,6 +14,8 @@ VG_MAX_BB_TERMS = 8
 F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP, F_MOCKGK = (1 << i for i in range(9))
 STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE, STATUS_DEVICE = 1, 2, 4, 8
 OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS, OPT_OZAKI = 0, 1, 2, 3
+ERR_CUDA, ERR_ARG, ERR_STATE = 1, 2, 3
+STATIC_SCRATCH_DOUBLES = 1 << 21      # VG_STATIC_SCRATCH_DOUBLES of include/vega_b200.h
 
 i32, u32, f64 = C.c_int32, C.c_uint32, C.c_double
 
@@ -130,6 +132,8 @@ _SIGNATURES = {
                                 C.c_longlong, C.c_int, _PTR, _PTR]),
     'vg_dgemm_tn': (C.c_int, [_PTR, _PTR, _PTR, C.c_int, C.c_int, C.c_int, C.c_longlong,
                               C.c_longlong, C.c_longlong, f64, f64, C.c_int, _PTR, _PTR]),
+    'vg_dgemm_tn_static': (C.c_int, [_PTR, _PTR, _PTR, C.c_int, C.c_int, C.c_int, C.c_longlong,
+                                     C.c_longlong, C.c_longlong, f64, C.c_int, _PTR]),
 }
 
 _lib = None

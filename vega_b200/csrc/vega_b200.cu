@@ -8,6 +8,7 @@
 #include <map>
 #include <memory>
 #include <string>
+#include <mutex>
 #include <vector>
 
 #include <nvtx3/nvToolsExt.h>
@@ -2307,6 +2308,81 @@ int vg_dgemm_tn(const double* A, const double* B, double* C, int M, int N, int K
 }
 
 }  // extern "C"
+
+// ---- split-K DGEMM without any allocation (no counterpart in the reference; see the header) ----
+// The split-K partials live in this file-scope device array: every GPU that loads the library holds
+// VG_STATIC_SCRATCH_DOUBLES * 8 bytes (16 MiB) until exit.  All calls share it and it keeps the last
+// call's contents; the GEMM of a call writes every partial its reduction reads (empty K ranges store
+// zeros), so nothing needs clearing.  In host code the NAME below is a host-side stand-in, not a
+// device address: the device address comes from cudaGetSymbolAddress, once per device.
+static __device__ __align__(256) double vg_static_scratch[VG_STATIC_SCRATCH_DOUBLES];
+
+namespace {
+// C[m, n] = sum_s W[s * stride + m * ldw + n] for n < N only (fixed order => deterministic); the pad
+// columns of C and of the partials are neither read nor written
+__global__ void reduce_splits_cols_kernel(const double* __restrict__ W, double* __restrict__ C, int M, int N,
+                                          long long ldw, long long ldc, int splits, long long stride) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)M * N) return;
+  const long long m = i / N, n = i - m * N;
+  const double* w = W + m * ldw + n;
+  double s = w[0];
+  for (int k = 1; k < splits; ++k) s += w[(long long)k * stride];
+  C[m * ldc + n] = s;
+}
+
+constexpr int STATIC_SCRATCH_MAX_DEVICES = 64;
+std::mutex g_static_scratch_mutex;
+double* g_static_scratch_ptr[STATIC_SCRATCH_MAX_DEVICES] = {};
+
+// device address of vg_static_scratch on the CURRENT device, looked up once per device
+int static_scratch_address(double** out) {
+  int dev = -1;
+  VG_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= STATIC_SCRATCH_MAX_DEVICES) {
+    vg_set_error("vg_dgemm_tn_static: device ordinal %d outside [0, %d)", dev, STATIC_SCRATCH_MAX_DEVICES);
+    return VG_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (!g_static_scratch_ptr[dev]) {
+    double* ptr = nullptr;
+    VG_CUDA_CHECK(cudaGetSymbolAddress((void**)&ptr, vg_static_scratch));
+    g_static_scratch_ptr[dev] = ptr;
+  }
+  *out = g_static_scratch_ptr[dev];
+  return VG_OK;
+}
+}  // namespace
+
+extern "C" int vg_dgemm_tn_static(const double* A, const double* B, double* C, int M, int N, int K, long long lda,
+                                  long long ldb, long long ldc, double alpha, int splits, void* stream) {
+  if (!A || !B || !C || M <= 0 || N <= 0 || K <= 0 || splits < 2 || ldc < N) {
+    vg_set_error("vg_dgemm_tn_static: bad arguments (splits >= 2, ldc >= N, positive sizes, non-null pointers)");
+    return VG_ERR_ARG;
+  }
+  const long long ldw = N + (N & 1);                    // even row stride: the kernel stores pairs
+  const long long need = (long long)splits * M * ldw;
+  if (need > (long long)VG_STATIC_SCRATCH_DOUBLES) {
+    vg_set_error("vg_dgemm_tn_static: splits * M * (N rounded up to even) = %lld doubles exceeds the static "
+                 "scratch of %lld doubles (VG_STATIC_SCRATCH_DOUBLES); use vg_dgemm_tn with a caller workspace",
+                 need, (long long)VG_STATIC_SCRATCH_DOUBLES);
+    return VG_ERR_ARG;
+  }
+  double* scratch = nullptr;
+  VG_TRY(static_scratch_address(&scratch));
+  cudaStream_t st = (cudaStream_t)stream;
+  vg::GemmArgs g{};
+  g.A = A; g.B = B; g.M = M; g.N = N; g.K = K;
+  g.lda = lda; g.ldb = ldb; g.ldc = ldw;
+  g.batch = 1; g.splits = splits;
+  g.alpha = alpha; g.beta = 0.0;
+  g.C = scratch; g.split_stride = (long long)M * ldw;
+  VG_TRY(vg::launch_dgemm(g, vg::GEMM_STORE, st));
+  const long long n = (long long)M * N;
+  reduce_splits_cols_kernel<<<vg_cdiv(n, 256), 256, 0, st>>>(scratch, C, M, N, ldw, ldc, splits, g.split_stride);
+  VG_CUDA_CHECK(cudaGetLastError());
+  return VG_OK;
+}
 
 // ---- FP64 FMA peak probe (roofline denominator of the ALU-bound fused P(k,mu) kernel) ----
 namespace {
