@@ -150,9 +150,33 @@ def test_fast_metals_descriptors():
 
 def test_unsupported_options_fail_loudly():
     vega, pb = builder('configs/full_configs/main.ini')
-    vega.corr_items['lyalya_lyalya'].config['model']['no-metal-decomp'] = 'False'
+    model = vega.corr_items['lyalya_lyalya'].config['model']
+    model['fht_extrap'] = 'True'
     with pytest.raises(NotImplementedError):
         pb.describe_corr('lyalya_lyalya')
+    model['fht_extrap'] = 'False'
+    # the reference's metal x metal cache is keyed on the pair alone: with split metals it would
+    # return the peak term for the smooth one, so the combination is refused
+    model['no-metal-decomp'], model['fast_metals'] = 'False', 'True'
+    with pytest.raises(NotImplementedError):
+        pb.describe_corr('lyalya_lyalya')
+
+
+def test_split_metals_emit_a_peak_and_a_smooth_evaluation_per_pair():
+    """no-metal-decomp = False (vega/model.py:119-131,178-186)."""
+    vega, pb = builder('configs/full_configs/main.ini')
+    item = vega.corr_items['lyalya_lyalya']
+    item.config['model']['no-metal-decomp'] = 'False'
+    info = pb.describe_corr('lyalya_lyalya')
+    n_pairs = len(item.metal_correlations)
+    metals = [d for d in info['evals'] if d.out_slot >= 2]
+    assert len(metals) == 2 * n_pairs == len(info['metal_mats'])
+    for c in range(n_pairs):
+        peak, smooth = metals[2 * c], metals[2 * c + 1]
+        assert (peak.is_peak, peak.pk_lin_sel, peak.idx_weight_extra2) == (1, 0, pb.col('bao_amp'))
+        assert (smooth.is_peak, smooth.pk_lin_sel, smooth.idx_weight_extra2) == (0, 1, -1)
+        assert peak.coord_set == smooth.coord_set and peak.out_slot + 1 == smooth.out_slot
+        assert info['metal_mats'][2 * c] is info['metal_mats'][2 * c + 1]
 
 
 def test_small_covariances_keep_the_reference_host_inverse():
