@@ -216,6 +216,9 @@ def hbm_bytes(engine, B):
         if digits:
             n_metal = sum(1 for d in hot if d.out_slot >= 2)
             out['ozaki_slice'] += B * n_metal * nm * (2 * 8.0 + digits)   # two reads of xmet, S digit planes written
+        dm_digits, _ = engine.ozaki_dm_slices(ci)
+        if dm_digits:
+            out['ozaki_slice'] += B * nm * (2 * 8.0 + dm_digits)          # the same for the pre-distortion model
     return out
 
 
@@ -609,6 +612,7 @@ def main():
 
     # ---- comparison legs, not the headline ----
     digits = [engine.ozaki_slices(ci)[0] for ci in range(len(engine.infos))]
+    dm_digits = [engine.ozaki_dm_slices(ci)[0] for ci in range(len(engine.infos))]
     chi2_ref = chi2_t.clone()
     engine.set_option(_lib.OPT_OZAKI, 0)            # metal matrices on the FP64 DMMA kernel
     for _ in range(3):
@@ -710,7 +714,10 @@ def main():
             if stage_ms[s] > 0:
                 tf = flops[s] / (stage_ms[s] * 1e-3) / 1e12
                 kernels[s]['tflops'] = tf
-                roofline_kernels.append({'name': s, 'kernel': 'dgemm_tn_kernel (DMMA m8n8k4 FP64)', 'bound': 'tensor',
+                kname = 'dgemm_tn_kernel (DMMA m8n8k4 FP64)'
+                if s == 'dm_gemm' and any(dm_digits):
+                    kname = f'ozaki_gemm_kernel (tcgen05 kind::i8, digits {dm_digits}) + split-K reduction'
+                roofline_kernels.append({'name': s, 'kernel': kname, 'bound': 'tensor',
                                          'achieved': tf, 'peak': dgemm_peak, 'unit': 'TFLOP/s (algorithmic FP64)',
                                          'frac': frac(tf, dgemm_peak), 'ms_per_step': stage_ms[s],
                                          'share_of_step': stage_ms[s] / ms_per_step})
@@ -747,7 +754,7 @@ def main():
                        'evaluations_sharing_tables': n_eval - n_grid_eval - n_moment,
                        'evaluations_with_static_xi_stage': sum(engine.n_static_xi(ci)
                                                                for ci in range(len(engine.infos))),
-                       'metal_gemm_digits': digits,
+                       'metal_gemm_digits': digits, 'distortion_gemm_digits': dm_digits,
                        'l2': 'inputs larger than L2: ~2.9 GB of static operands + ~2 GB of workspace '
                              'streamed per step'},
             'clocks': clock_info,
@@ -766,8 +773,8 @@ def main():
                                    'nominal: 296 TFLOP/s FP64 per 8-GPU HGX B200'},
             'kernels': kernels,
             'init_s': init,
-            'with_dmma_metals': {'note': 'VG_OPT_OZAKI = 0: the dense metal matrices on the FP64 DMMA kernel (the parity '
-                                         'reference of the split-integer GEMM)', 'ms_per_step': dmma_ms,
+            'with_dmma_metals': {'note': 'VG_OPT_OZAKI = 0: the dense metal matrices and the distortion matrix on the FP64 '
+                                         'DMMA kernel (the parity reference of the split-integer GEMM)', 'ms_per_step': dmma_ms,
                                  'value': world * B / (dmma_ms * 1e-3), 'unit': 'evals/s',
                                  'max_rel_chi2_difference_to_headline': dmma_diff},
             'with_folded_metals': {'note': 'not the headline: VG_OPT_FOLD_METALS = 1, the metal terms with a '

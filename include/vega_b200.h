@@ -270,6 +270,10 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
  * (vg_corr_ozaki_slices); 3..8: that many digits; 0: the FP64 DMMA kernel (the parity reference).
  * Batches below 16 vectors always take the DMMA kernel. */
 #define VG_OPT_OZAKI 3
+/* VG_OPT_OZAKI_DM (default 1): the distortion-matrix product (vega/model.py:142-143) takes the same
+ * split-integer kernel, with the digits VG_OPT_OZAKI selects (automatic: its own bound against
+ * max|D xi| at the plan parameters, vg_corr_ozaki_dm_slices); 0 keeps it on the FP64 DMMA kernel. */
+#define VG_OPT_OZAKI_DM 4
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
 /* Isotropic P(k) [nk] for the direct mode (e.g. from a Boltzmann code, the `direct_pk`
  * argument of VegaInterface.compute_model / chi2 / log_lik); host pointer, copied. */
@@ -287,6 +291,8 @@ int vg_corr_n_folded(const vg_plan* plan, int32_t corr);
  * (nullable) receives, for S = 3..8, the truncation bound relative to max|xi_smooth| at the plan
  * parameters. */
 int vg_corr_ozaki_slices(const vg_plan* plan, int32_t corr, double* bound_per_digits);
+/* The same for the distortion-matrix product (bound relative to max|D xi|; 0: DMMA) */
+int vg_corr_ozaki_dm_slices(const vg_plan* plan, int32_t corr, double* bound_per_digits);
 /* Status bits raised while building the static grids (e.g. VG_STATUS_ARINYO): they apply
  * to every vector */
 int vg_plan_static_status(const vg_plan* plan);

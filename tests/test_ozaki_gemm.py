@@ -75,8 +75,9 @@ def test_zero_rows_and_nonfinite_rows():
 
 
 def test_metal_gemm_option_matches_dmma():
-    """VG_OPT_OZAKI on the dense C2 workload: chi2 and the model against the FP64 DMMA path
-    (option 0), for the automatic digit count (the default) and for fixed ones."""
+    """VG_OPT_OZAKI on the dense C2 workload (metal matrices AND the distortion matrix, VG_OPT_OZAKI_DM
+    = 1, the default): chi2 and the model against the FP64 DMMA path (option 0), for the automatic
+    digit count (the default) and for fixed ones; then the metal product alone (VG_OPT_OZAKI_DM = 0)."""
     from helpers import make_c2
     from vega_b200 import _lib
     vega, oracle, theta = make_c2(64, width=1.0)
@@ -91,17 +92,30 @@ def test_metal_gemm_option_matches_dmma():
             assert 3 <= digits <= 8
             if slices == -1:        # the automatic choice is the fewest digits under the budget
                 assert bounds[digits] <= 5e-11 and (digits == 3 or bounds[digits - 1] > 5e-11)
+            digits, bounds = engine.ozaki_dm_slices(ci)
+            assert 3 <= digits <= 8
+            if slices == -1:
+                assert bounds[digits] <= 5e-11 and (digits == 3 or bounds[digits - 1] > 5e-11)
         got = vega.chi2_batch(theta)
         model, status = vega.compute_model_batch(theta)
         assert not status.any()
         for name in ref_model:
             scale = np.max(np.abs(ref_model[name]))
-            tol = 5e-11 if slices == 6 else 1e-11
+            # fixed digit counts below the automatic ones (7 / 8 here) give up accuracy on purpose
+            tol = {6: 2e-10, 7: 2e-11}.get(slices, 1e-11)
             assert np.max(np.abs(model[name] - ref_model[name])) <= tol * scale, (slices, name)
         assert np.max(np.abs(got - ref)) <= 1e-6 * max(1.0, np.max(np.abs(ref)) / 1e4), slices
     engine.set_option(_lib.OPT_OZAKI, -1)
-    # the oracle itself, on the vectors whose chi2 is of the order of the degrees of freedom
-    got = vega.chi2_batch(theta[:4])
+    engine.set_option(_lib.OPT_OZAKI_DM, 0)
+    assert all(engine.ozaki_dm_slices(ci)[0] == 0 for ci in range(len(engine.infos)))
+    model, _ = vega.compute_model_batch(theta)
+    for name in ref_model:
+        assert np.max(np.abs(model[name] - ref_model[name])) <= 1e-11 * np.max(np.abs(ref_model[name])), name
+    assert np.max(np.abs(vega.chi2_batch(theta) - ref)) <= 1e-6 * max(1.0, np.max(np.abs(ref)) / 1e4)
+    engine.set_option(_lib.OPT_OZAKI_DM, 1)
+    # the oracle itself, on the vectors whose chi2 is of the order of the degrees of freedom (taken
+    # from the whole batch: fewer than 16 vectors would go to the DMMA kernel)
+    got = vega.chi2_batch(theta)[:4]
     for b in range(4):
         want = oracle.chi2(dict(zip(vega.theta_names, theta[b])))
         assert abs(got[b] - want) <= 1e-6 * max(1.0, abs(want) / 1e4)

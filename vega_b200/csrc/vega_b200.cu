@@ -182,6 +182,9 @@ struct Corr {
   int oz_auto_slices = 0;        // digits that meet the truncation budget at the plan parameters (0: not dense)
   double oz_bound[vg::OZ_MAX_S + 1] = {0};   // the bound per digit count, relative to max|xi| (diagnostics)
   bool has_dmat = false;
+  OzakiOperand oz_dmat, oz_dmat_masked;  // digit planes of d_dmat / d_dmat_masked (built on first use)
+  int oz_dm_slices = 0;          // digits of the distortion product that meet the budget (0: DMMA)
+  double oz_dm_bound[vg::OZ_MAX_S + 1] = {0};
   DevBuf d_dmat;                 // [n_dist][ld_model]
   DevBuf d_dmat_masked;          // [n_mask][ld_model]
   bool has_inst = false;
@@ -218,6 +221,7 @@ struct vg_plan {
   bool use_moments = true;
   bool direct_mode = false;      // VG_OPT_DIRECT_PK
   bool fold_metals = false;      // VG_OPT_FOLD_METALS
+  bool ozaki_dm = true;          // VG_OPT_OZAKI_DM: the distortion product on the split-integer kernel too
   int ozaki_slices = -1;         // VG_OPT_OZAKI: digits of the split-integer metal GEMM (0: DMMA, -1: per
                                  // correlation, the fewest digits that meet the truncation budget)
   OzakiOperand oz_A;             // workspace: digit planes of the batch operand
@@ -302,6 +306,7 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
 int build_metal_operands(Corr& c, const EvalLayout& L, DevBuf& mcat, DevBuf& mrp);
 int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st);
+int ozaki_budget_dm(vg_plan* plan, Corr& c, cudaStream_t st);
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st);
 enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_MOMENT = 7,
@@ -594,6 +599,7 @@ int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
     plan->ozaki_slices = value;
     return VG_OK;
   }
+  if (option == VG_OPT_OZAKI_DM) { plan->ozaki_dm = value != 0; return VG_OK; }
   if (option == VG_OPT_DIRECT_PK) {
     if (value) {
       bool any = false;
@@ -1001,6 +1007,7 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
   for (auto& cp : plan->corrs) {
     VG_TRY(freeze_metal_terms(plan, *cp, st));
     VG_TRY(ozaki_budget(plan, *cp, st));
+    VG_TRY(ozaki_budget_dm(plan, *cp, st));
     // (the host copies of the metal matrices stay: vg_plan_set_templates runs finalize again)
   }
   if (plan->has_global) {
@@ -1136,7 +1143,7 @@ int ozaki_slice(OzakiOperand& op, const double* src, long long ld, long long row
   }
 }
 
-// 3-D tensor map over the digit planes: (k, row, digit), box (64, box_rows, S), 64-byte swizzle
+// 3-D tensor map over the digit planes: (k, row, digit), box (OZ_BK, box_rows, S), OZ_BK-byte swizzle
 int ozaki_map(CUtensorMap* map, const OzakiOperand& op, int box_rows) {
   EncodeTiledFn fn = encode_tiled_fn();
   VG_REQUIRE(fn, "cuTensorMapEncodeTiled is not available from this driver");
@@ -1145,7 +1152,8 @@ int ozaki_map(CUtensorMap* map, const OzakiOperand& op, int box_rows) {
   const cuuint32_t box[3] = {(cuuint32_t)vg::OZ_BK, (cuuint32_t)box_rows, (cuuint32_t)op.S};
   const cuuint32_t estride[3] = {1, 1, 1};
   const CUresult rc = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, op.planes.p, gdim, gstride, box, estride,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, vg::OZ_BK == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   VG_REQUIRE(rc == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with %d", (int)rc);
   return VG_OK;
@@ -1180,9 +1188,9 @@ int ozaki_gemm(const OzakiOperand& A, long long M, const OzakiOperand& B, int N,
   // an s32 accumulator takes S products of |q q'| <= 2^12 per k: K blocks per split are bounded
   const int kb_cap = (int)(((1LL << 31) - 1) / (4096LL * vg::OZ_BK * S));
   int splits = vg_cdiv(g.kb_total, kb_cap);
-  {   // fill whole waves of the 148 SMs (one CTA each), >= 8 K blocks per split
+  {   // fill whole waves of the 148 SMs (one CTA each), >= 512 bytes of K per split
     double best = -1.0;
-    const int lo = splits, hi = std::max(lo, std::min(64, g.kb_total / 8));
+    const int lo = splits, hi = std::max(lo, std::min(64, g.kb_total / (512 / vg::OZ_BK)));
     for (int sp = lo; sp <= hi; ++sp) {
       const int per = vg_cdiv(g.kb_total, sp);
       if ((long long)per * (sp - 1) >= g.kb_total) continue;      // an empty last split
@@ -1645,6 +1653,44 @@ int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st) {
   return VG_OK;
 }
 
+// The same for the distortion matrix product y = D x (vega/model.py:142-143): x the model before
+// distortion at the plan parameters, the bound measured against max|y|.
+int ozaki_budget_dm(vg_plan* plan, Corr& c, cudaStream_t st) {
+  c.oz_dm_slices = 0;
+  for (double& b : c.oz_dm_bound) b = 0.0;
+  if (!c.has_dmat) return VG_OK;
+  VG_TRY(ensure_workspace(plan, 1));
+  VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_pfull.p, plan->d_base.p, (size_t)plan->npf * 8,
+                                cudaMemcpyDeviceToDevice, st));
+  VG_CUDA_CHECK(cudaMemsetAsync(plan->w_status.p, 0, 4, st));
+  VG_TRY(run_corr_front(plan, c, 1, plan->w_status.as<int>(), st));
+  VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_dmat.as<double>(), c.ld_model,
+                   plan->w_y.as<double>(), c.ld_dist, 1, c.n_dist, c.ld_model, 1, 0, 0, 0, st));
+  DevBuf stats;
+  VG_TRY(stats.alloc(9 * sizeof(unsigned long long)));
+  unsigned long long* d = stats.as<unsigned long long>();
+  vg::ozaki_stats_kernel<<<1, 256, 0, st>>>(plan->w_x.as<double>(), c.ld_model, c.n_model, d);
+  VG_LAUNCHED();
+  vg::ozaki_stats_kernel<<<(unsigned)c.n_dist, 256, 0, st>>>(c.d_dmat.as<double>(), c.ld_model, c.n_model, d + 3);
+  VG_LAUNCHED();
+  vg::ozaki_stats_kernel<<<1, 256, 0, st>>>(plan->w_y.as<double>(), c.ld_dist, c.n_dist, d + 6);
+  VG_LAUNCHED();
+  double h[9];
+  VG_CUDA_CHECK(cudaMemcpyAsync(h, stats.p, sizeof(h), cudaMemcpyDeviceToHost, st));
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  const double amax = h[0], a1 = h[1], bmax = h[3], b1 = h[4], bnz = h[5], scale = h[6];
+  if (!(scale > 0.0) || !(amax > 0.0) || !std::isfinite(scale)) return VG_OK;
+  c.oz_dm_slices = vg::OZ_MAX_S;
+  for (int S = vg::OZ_MAX_S; S >= 3; --S) {
+    const double bound = std::ldexp(amax * b1 + a1 * bmax + (S - 1) * amax * bmax * bnz, -7 * S);
+    c.oz_dm_bound[S] = bound / scale;
+    if (bound <= OZAKI_BUDGET * scale) c.oz_dm_slices = S;
+  }
+  // the largest digit count that still misses the budget: keep the FP64 kernel
+  if (c.oz_dm_bound[vg::OZ_MAX_S] > OZAKI_BUDGET) c.oz_dm_slices = 0;
+  return VG_OK;
+}
+
 // fast_metals metal x metal terms (vega/metals.py:144-169): M_c xi_c evaluated ONCE at the
 // plan's base parameters (the reference caches the first evaluation forever), stored without
 // the bias product, which the hot path applies per vector.
@@ -1687,20 +1733,39 @@ int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st) {
 //   data == false: model rows for ALL distorted bins -> out[Bc][ldo = ld_dist]
 //   data == true : residual d - m on the masked bins  -> out[Bc][ldo] at column col0
 int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* out, int ldo,
-                  int ncols, cudaStream_t st, const int* mock_idx = nullptr) {
+                  int ncols, cudaStream_t st, const int* mock_idx = nullptr, int* status_dev = nullptr) {
   const double* y = plan->w_x.as<double>();
   int ldy = c.ld_model;
   int y_is_masked = 0;
   if (c.has_dmat) {
-    ProfScope prof(plan, PROF_DM, st);
-    if (residual) {
-      VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_dmat_masked.as<double>(), c.ld_model,
-                       plan->w_y.as<double>(), c.ld_mask, (int)Bc, c.n_mask, c.ld_model, 1, 0, 0, 0, st));
-      ldy = c.ld_mask; y_is_masked = 1;
+    const DevBuf& dm = residual ? c.d_dmat_masked : c.d_dmat;
+    const int rows = residual ? c.n_mask : c.n_dist;
+    ldy = residual ? c.ld_mask : c.ld_dist;
+    y_is_masked = residual ? 1 : 0;
+    const int oz_S = plan->ozaki_slices < 0 ? c.oz_dm_slices : (c.oz_dm_slices > 0 ? plan->ozaki_slices : 0);
+    if (oz_S > 0 && plan->ozaki_dm && Bc >= OZAKI_MIN_BATCH) {
+      // split-integer GEMM on tcgen05, as for the dense metal matrices (run_corr_front)
+      OzakiOperand& ob = residual ? c.oz_dmat_masked : c.oz_dmat;
+      if (ob.S != oz_S || ob.src != dm.as<double>()) {
+        VG_TRY(ozaki_slice(ob, dm.as<double>(), c.ld_model, rows, rows, c.n_model, oz_S, st));
+        ob.src = dm.as<double>();
+      }
+      {
+        ProfScope slice_prof(plan, PROF_OZ_SLICE, st);
+        VG_TRY(ozaki_slice(plan->oz_A, plan->w_x.as<double>(), c.ld_model, Bc, plan->chunk, c.n_model, oz_S, st));
+      }
+      {
+        ProfScope gemm_prof(plan, PROF_DM, st);
+        VG_TRY(ozaki_gemm(plan->oz_A, Bc, ob, rows, plan->w_y.as<double>(), ldy, plan->w_split, plan->d_oz_error, st));
+      }
+      if (status_dev) {
+        vg::flag_status_kernel<<<vg_cdiv(Bc, 256), 256, 0, st>>>(plan->d_oz_error.as<int>(), status_dev, Bc);
+        VG_LAUNCHED();
+      }
     } else {
-      VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_dmat.as<double>(), c.ld_model,
-                       plan->w_y.as<double>(), c.ld_dist, (int)Bc, c.n_dist, c.ld_model, 1, 0, 0, 0, st));
-      ldy = c.ld_dist;
+      ProfScope prof(plan, PROF_DM, st);
+      VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, dm.as<double>(), c.ld_model,
+                       plan->w_y.as<double>(), ldy, (int)Bc, rows, c.ld_model, 1, 0, 0, 0, st));
     }
     y = plan->w_y.as<double>();
   }
@@ -1761,10 +1826,11 @@ int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi
     if (plan->has_global) {
       // residuals of all correlations side by side: [Bc][ld_total]
       VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>() + col0, plan->ld_total,
-                           c.n_mask, st, mock_idx));
+                           c.n_mask, st, mock_idx, status_dev));
       col0 += c.n_mask;
     } else {
-      VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, st, mock_idx));
+      VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, st, mock_idx,
+                           status_dev));
       VG_TRY(quad_form(plan, plan->w_diff.as<double>(), c.n_mask, c.ld_mask,
                        c.has_invcov ? c.d_invcov.as<double>() : nullptr, Bc, chi2_dev, !first, st));
       first = 0;
@@ -1797,7 +1863,7 @@ int chi2_chunk_small(vg_plan* plan, const double* theta_dev, long long Bc, doubl
     return chi2_chunk(plan, theta_dev, Bc, chi2_dev, status_dev, st, mock_idx);
   const long long key = Bc | ((long long)plan->use_moments << 20) | ((long long)plan->fold_metals << 21) |
                         ((long long)plan->direct_mode << 22) | ((long long)(mock_idx != nullptr) << 23) |
-                        ((long long)(plan->ozaki_slices + 1) << 24);
+                        ((long long)(plan->ozaki_slices + 1) << 24) | ((long long)plan->ozaki_dm << 30);
   vg_plan::GraphEntry& g = plan->graphs[key];
   if (g.exec && g.generation != g_alloc_generation) {     // a buffer moved since the capture
     cudaGraphExecDestroy(g.exec);
@@ -1867,7 +1933,8 @@ int vg_model_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* co
       Corr& c = *plan->corrs[ci];
       VG_TRY(run_corr_front(plan, c, Bc, status_dev + b0, st));
       // model rows straight into the caller's [B][n_dist] array
-      VG_TRY(run_corr_back(plan, c, Bc, false, xi_out_dev[ci] + b0 * c.n_dist, c.n_dist, c.n_dist, st));
+      VG_TRY(run_corr_back(plan, c, Bc, false, xi_out_dev[ci] + b0 * c.n_dist, c.n_dist, c.n_dist, st, nullptr,
+                           status_dev + b0));
     }
   }
   return VG_OK;
@@ -2039,6 +2106,14 @@ int vg_corr_n_folded(const vg_plan* plan, int32_t corr) {
   return (int)plan->corrs[corr]->lay[LAY_FOLD].fold_ids.size();
 }
 
+int vg_corr_ozaki_dm_slices(const vg_plan* plan, int32_t corr, double* bound_per_digits) {
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size()) return 0;
+  const Corr& c = *plan->corrs[corr];
+  if (bound_per_digits)
+    for (int S = 0; S <= vg::OZ_MAX_S; ++S) bound_per_digits[S] = c.oz_dm_bound[S];
+  if (!plan->ozaki_dm) return 0;
+  return plan->ozaki_slices < 0 ? c.oz_dm_slices : (c.oz_dm_slices > 0 ? plan->ozaki_slices : 0);
+}
 int vg_plan_static_status(const vg_plan* plan) { return plan ? plan->static_bad : 0; }
 int64_t vg_plan_graph_replays(const vg_plan* plan) { return plan ? plan->graph_replays : 0; }
 

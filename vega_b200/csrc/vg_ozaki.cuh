@@ -28,7 +28,11 @@
 
 namespace vg {
 
-constexpr int OZ_BM = 128, OZ_BN = 64, OZ_BK = 64;   // OZ_BK int8 elements = 64 bytes = swizzle span
+// OZ_BK int8 elements per pipeline stage = the swizzle span (32 or 64 bytes).  Measured on C2 with
+// S = 7: 64 bytes (2 stages of 86 KB) 4.16 ms for the two metal GEMMs, 32 bytes (5 stages of 43 KB,
+// SWIZZLE_32B) 5.26 ms -- the finer pipeline does not pay for the narrower rows
+constexpr int OZ_BM = 128, OZ_BN = 64, OZ_BK = 64;
+static_assert(OZ_BK == 32 || OZ_BK == 64, "the stage K extent is one 32- or 64-byte swizzle span");
 constexpr int OZ_MAX_S = 8;
 constexpr int OZ_THREADS = 256;
 constexpr int OZ_TMEM_COLS = 512;
@@ -204,16 +208,16 @@ __device__ __forceinline__ void oz_tmem_ld16(unsigned taddr, unsigned (&r)[16]) 
 }
 __device__ __forceinline__ void oz_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
 
-// shared-memory matrix descriptor of a K-major operand tile with the 64-byte swizzle: rows of 64
-// bytes, 8-row groups 512 bytes apart (SBO), descriptor version 1 (sm_100), layout type 4
-// (SWIZZLE_64B) -- field layout as in cute::UMMA::SmemDescriptor
+// shared-memory matrix descriptor of a K-major operand tile with the OZ_BK-byte swizzle: rows of
+// OZ_BK bytes, 8-row groups 8 * OZ_BK bytes apart (SBO), descriptor version 1 (sm_100), layout type
+// 4 (SWIZZLE_64B) or 6 (SWIZZLE_32B) -- field layout as in cute::UMMA::SmemDescriptor
 __device__ __forceinline__ unsigned long long oz_smem_desc(unsigned smem_addr) {
   unsigned long long d = 0;
   d |= (unsigned long long)((smem_addr >> 4) & 0x3fffu);        // start address  [0,14)
   d |= (unsigned long long)0u << 16;                            // leading byte offset [16,30): unused (one atom along K)
-  d |= (unsigned long long)((512u >> 4) & 0x3fffu) << 32;       // stride byte offset  [32,46)
+  d |= (unsigned long long)(((8u * OZ_BK) >> 4) & 0x3fffu) << 32;   // stride byte offset  [32,46)
   d |= (unsigned long long)1u << 46;                            // version             [46,48)
-  d |= (unsigned long long)4u << 61;                            // layout type         [61,64)
+  d |= (unsigned long long)(OZ_BK == 64 ? 4u : 6u) << 61;       // layout type         [61,64)
   return d;
 }
 // instruction descriptor (cute::UMMA::InstrDescriptor): s32 accumulator, s8 x s8, both K-major;
@@ -235,7 +239,9 @@ template <int S> struct OzakiSmem {
   static constexpr int A_STAGE = S * OZ_BM * OZ_BK;
   static constexpr int B_STAGE = S * OZ_BN * OZ_BK;
   static constexpr int STAGE = A_STAGE + B_STAGE;
-  static constexpr int STAGES = (220 * 1024 - 2048) / STAGE >= 3 ? 3 : 2;
+  static constexpr int FIT = (220 * 1024 - 2048) / STAGE;
+  static constexpr int STAGES = FIT > 8 ? 8 : FIT;
+  static_assert(STAGES >= 2, "two pipeline stages must fit");
   static constexpr int BYTES = STAGES * STAGE + 1024 /* alignment slack */ + 256 /* barriers */;
 };
 

@@ -931,6 +931,12 @@ class DevicePlan:
         digits = self.lib.vg_corr_ozaki_slices(self.handle, ci, bounds)
         return digits, {S: bounds[S] for S in range(3, 9)}
 
+    def ozaki_dm_slices(self, ci):
+        """(digits, {S: bound / max|D xi|}) of the distortion-matrix product of correlation ci."""
+        bounds = (C.c_double * 9)()
+        digits = self.lib.vg_corr_ozaki_dm_slices(self.handle, ci, bounds)
+        return digits, {S: bounds[S] for S in range(3, 9)}
+
     def device_bytes(self):
         return self.lib.vg_plan_device_bytes(self.handle)
 
