@@ -37,7 +37,7 @@ MAIN_INI = 'configs/c2/main.ini'
 WORKLOAD = 'C2 eBOSS-DR16-shaped LyaxLya(2500 bins,15 metal corr)+LyaxQSO(5000 bins,4 metal corr), dense DM/metal/cov'
 # tags of vg_profile_read (include/vega_b200.h)
 STAGES = ['pk_ell', 'hankel_gemm', 'xi_gather', 'metal_gemm', 'dm_gemm', 'chi2_gemm', 'elementwise',
-          'moment_tables', 'moment_xi', 'ozaki_slice', 'metal_rp']
+          'moment_tables', 'moment_xi', 'ozaki_slice', 'metal_rp', 'velo_tables']
 
 
 def build_state(seed=20261104):
@@ -161,12 +161,12 @@ class ClockSampler:
                 'samples': len(sm)}
 
 
-def gemm_flops(engine, B):
+def gemm_flops(engine, B, velo_tables=True):
     """Algorithmic FP64 flops of the contraction stages for B vectors:
     Hankel operator 2*n_ell*nk^2 per evaluation, metal matrices 2*Nm^2 each (dense) or 2*Np^2*Nt
     (rp-only new_metals form), distortion matrix 2*Nmask*Nm (masked rows), chi2 2*Nmask^2 (or one
     2*(sum Nmask)^2 under a global covariance)."""
-    out = {'hankel_gemm': 0.0, 'metal_gemm': 0.0, 'metal_rp': 0.0, 'dm_gemm': 0.0, 'chi2_gemm': 0.0}
+    out = {'hankel_gemm': 0.0, 'metal_gemm': 0.0, 'metal_rp': 0.0, 'dm_gemm': 0.0, 'chi2_gemm': 0.0, 'velo_tables': 0.0}
     nk, n_ell = 814, 4
     total_mask = 0
     for ci, info in enumerate(engine.infos):
@@ -175,7 +175,15 @@ def gemm_flops(engine, B):
         nmask = int(data.model_mask.sum())
         total_mask += nmask
         own = [d for d in info['evals'] if d.table_owner < 0 and not d.frozen and not d.direct]
-        n_eval = len(own) - engine.n_moment(ci)             # evaluations that reach the Hankel GEMM
+        n_vt, orders, _ = engine.velo_tables(ci) if velo_tables else (0, 0, 0.0)
+        n_eval = len(own) - engine.n_moment(ci) - n_vt      # evaluations that reach the Hankel GEMM
+        if n_vt:
+            # velocity-dispersion tables: one GEMM [B x orders*nm] x [orders*nm x 4*2*816] per evaluation,
+            # nm = 3 x (1 + tracers with an HCD term) moment coefficients (csrc/vg_moments.cuh)
+            vt = [d for d in own if d.dyn_mask == 64][:n_vt]
+            for d in vt:
+                n_hcd = (2 * bool(d.hcd_on[0]) if d.same_tracer else bool(d.hcd_on[0]) + bool(d.hcd_on[1])) if d.hcd_model else 0
+                out['velo_tables'] += 2.0 * orders * 3 * (1 + n_hcd) * n_ell * 2 * 816 * B
         out['hankel_gemm'] += 2.0 * n_ell * nk * nk * n_eval * B
         # metal matrices applied per vector (fast_metals freezes the metal x metal ones)
         for mat, d in zip(info['metal_mats'], [d for d in info['evals'] if d.out_slot >= 2 and not d.direct]):
@@ -368,13 +376,15 @@ def build_c3(rank):
     synthetic.inject_dense_operands(vega, with_distortion=False, with_metals=False)
     synthetic.inject_global_covariance(vega)
     t2 = time.perf_counter()
+    from vega_b200.parameters import get_default_values
+    defaults = get_default_values()
     names = [n for n in C3_NAMES if n in vega.params]
     sp = vega.sample_params
     for n in names:
-        if n not in sp['limits']:
+        if n not in sp['limits']:      # what `name = True` in [sample] gives (vega/vega_interface.py:737-816)
             sp['values'][n] = vega.params[n]
             sp['errors'][n] = 0.02 * abs(vega.params[n]) + 1e-4
-            sp['limits'][n] = (None, None)
+            sp['limits'][n] = defaults[n]['limits'] if n in defaults else (None, None)
             sp['fix'][n] = False
     for key in ('values', 'errors', 'limits', 'fix'):
         sp[key] = {n: sp[key][n] for n in names}
@@ -627,6 +637,16 @@ def main():
     fold_diff = float(((chi2_t - chi2_ref).abs() / chi2_ref.abs().clamp_min(1.0)).max().item())
     fold_ms = timed_device(torch, dd, step_device, args.steps)
     engine.set_option(_lib.OPT_FOLD_METALS, 0)
+    vt_info = [engine.velo_tables(ci) for ci in range(len(engine.infos))]
+    n_vt = sum(v[0] for v in vt_info)
+    pp_ms = pp_diff = None
+    if n_vt:
+        engine.set_option(_lib.OPT_VELO_TABLES, 0)  # the sampled velocity dispersion through the per-point pass
+        for _ in range(3):
+            step_device()
+        pp_diff = float(((chi2_t - chi2_ref).abs() / chi2_ref.abs().clamp_min(1.0)).max().item())
+        pp_ms = timed_device(torch, dd, step_device, args.steps)
+        engine.set_option(_lib.OPT_VELO_TABLES, 1)
 
     line = None
     if rank == 0:
@@ -649,11 +669,11 @@ def main():
         n_moment = sum(engine.n_moment(ci) for ci in range(len(engine.infos)))
         n_own = sum(sum(1 for d in info['evals'] if d.table_owner < 0 and not d.frozen and not d.direct)
                     for info in engine.infos)
-        n_grid_eval = n_own - n_moment
+        n_grid_eval = n_own - n_moment - n_vt
         pk_instr = 0.0          # summed over the evaluations that go through the per-point pass
         for ci, info in enumerate(engine.infos):
             own = [d for d in info['evals'] if d.table_owner < 0 and not d.frozen and not d.direct]
-            if engine.n_moment(ci) >= len(own):
+            if engine.n_moment(ci) + vt_info[ci][0] >= len(own):
                 continue
             twinned = {d.pk_twin for d in own if d.pk_twin >= 0}
             part = 0.0
@@ -661,7 +681,7 @@ def main():
                 if any(d is o for o in own):
                     hcd = d.hcd_model and (d.hcd_on[0] or d.hcd_on[1])
                     part += 12.0 if (d.pk_twin >= 0 or e in twinned) else (18.5 if hcd else 16.5)
-            pk_instr += part * (len(own) - engine.n_moment(ci)) / len(own)
+            pk_instr += part * (len(own) - engine.n_moment(ci) - vt_info[ci][0]) / len(own)
 
         def frac(a, b):
             return a / b if a is not None and b else None
@@ -710,11 +730,14 @@ def main():
                              'traffic_source': 'profiles/r01_ncu_full_c2_raw.csv (dgemm_tn_kernel<0>, grid 8x20x12)',
                              'share_of_step': gemm_ms / ms_per_step}
         roofline_kernels.append(dict(main_roofline, name='metal_gemm'))
-        for s in ('hankel_gemm', 'dm_gemm', 'chi2_gemm'):
+        for s in ('hankel_gemm', 'dm_gemm', 'chi2_gemm', 'velo_tables'):
             if stage_ms[s] > 0:
                 tf = flops[s] / (stage_ms[s] * 1e-3) / 1e12
                 kernels[s]['tflops'] = tf
                 kname = 'dgemm_tn_kernel (DMMA m8n8k4 FP64)'
+                if s == 'velo_tables':
+                    kname = ('vtab_weights_kernel + dgemm_tn_kernel (DMMA): knot tables of the evaluations with a sampled '
+                             f'velocity dispersion from their Chebyshev series, orders {[v[1] for v in vt_info if v[0]]}')
                 if s == 'dm_gemm' and any(dm_digits):
                     kname = f'ozaki_gemm_kernel (tcgen05 kind::i8, digits {dm_digits}) + split-K reduction'
                 roofline_kernels.append({'name': s, 'kernel': kname, 'bound': 'tensor',
@@ -751,7 +774,8 @@ def main():
                        'evaluations_per_chi2': n_eval,
                        'evaluations_through_pk_ell': n_grid_eval,
                        'evaluations_in_moment_form': n_moment,
-                       'evaluations_sharing_tables': n_eval - n_grid_eval - n_moment,
+                       'evaluations_on_velocity_tables': n_vt,
+                       'evaluations_sharing_tables': n_eval - n_grid_eval - n_moment - n_vt,
                        'evaluations_with_static_xi_stage': sum(engine.n_static_xi(ci)
                                                                for ci in range(len(engine.infos))),
                        'metal_gemm_digits': digits, 'distortion_gemm_digits': dm_digits,
@@ -782,6 +806,12 @@ def main():
                                    'folded_metal_terms': n_folded, 'ms_per_step': fold_ms,
                                    'value': world * B / (fold_ms * 1e-3), 'unit': 'evals/s',
                                    'max_rel_chi2_difference_to_headline': fold_diff},
+            'with_per_point_velocity': None if pp_ms is None else {
+                'note': 'VG_OPT_VELO_TABLES = 0: the evaluations with a sampled velocity dispersion through the per-point '
+                        'P(k,mu) pass and the Hankel GEMM (the parity reference of the velocity-dispersion tables)',
+                'tables': [{'evaluations': v[0], 'chebyshev_orders': v[1], 'error_at_finalize': v[2]} for v in vt_info],
+                'ms_per_step': pp_ms, 'value': world * B / (pp_ms * 1e-3), 'unit': 'evals/s',
+                'max_rel_chi2_difference_to_headline': pp_diff},
             'scalar_api': {'call': 'VegaInterface.chi2(params) -> float, batch of one', 'ms_per_call': scalar_ms,
                            'calls': scalar_calls},
             'cpu_baseline': base,

@@ -138,6 +138,10 @@ typedef struct vg_eval_desc {
   int32_t idx_weight_extra2; /* a second parameter multiplying the weight, -1 none: bao_amp on the metal
                                terms of the PEAK component when no-metal-decomp = False
                                (vega/model.py:119-131,186) */
+  int32_t uv_static;        /* 1: none of the UV / HeII parameters (lambda_uv, bias_gamma, bias_prim,
+                               lambda_heii, bias_gamma_e; vega/power_spectrum.py:224-261) is sampled: the
+                               scale-dependent bias term is a static function of k and the evaluation
+                               can take the moment form */
 } vg_eval_desc;
 
 /* One broadband term (vega/broadband_poly.py:23-198) */
@@ -181,6 +185,12 @@ int vg_plan_destroy(vg_plan* plan);
  * parameter, 0 otherwise), and force_one[j] != 0 pins the column to 1 whatever the caller passed
  * (the BLIND_FIXED_PARS).  Never called = identity. */
 int vg_plan_set_theta_transform(vg_plan* plan, const double* offset, const int32_t* force_one);
+/* The box the sampled parameters live in: lo[n_theta], hi[n_theta] per theta column, NaN where the
+ * [sample] section gives no limit (vega/vega_interface.py:737-790 `sample_params['limits']`: the
+ * limits iminuit and the samplers keep theta inside, vega/minimizer.py:60-66,
+ * vega/samplers/polychord.py:106-127).  Optional, before vg_plan_finalize: only the
+ * velocity-dispersion tables (VG_OPT_VELO_TABLES) read it. */
+int vg_plan_set_theta_limits(vg_plan* plan, const double* lo, const double* hi);
 /* Fvoigt profile table for model-hcd = fvoigt (vega/power_spectrum.py:360-380) */
 int vg_plan_set_fvoigt(vg_plan* plan, int32_t n, const double* x, const double* f);
 /* UVB shot-noise A(tau) table (vega/correlation_func.py:597-626) */
@@ -246,9 +256,10 @@ int vg_plan_finalize(vg_plan* plan, void* stream);
 int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
 /* Run-time options.  VG_OPT_MOMENTS (default 1): evaluations whose sampled P(k,mu)
  * parameters are only Kaiser / HCD amplitudes are computed in moment form -- their knot
- * tables are a 3/9-term combination of static tables built at finalize (exact algebra: the
- * mu projection of vega/pktoxi.py:79-97, the FFTLog and the spline are linear); 0 sends every
- * evaluation through the per-point P(k,mu) pass. */
+ * tables are a 3/9/14-term combination of static tables built at finalize (exact algebra: the
+ * mu projection of vega/pktoxi.py:79-97, the FFTLog and the spline are linear; 14 terms with the
+ * scale-dependent UV / HeII bias of vega/power_spectrum.py:224-261 at fixed UV parameters,
+ * vg_eval_desc::uv_static); 0 sends every evaluation through the per-point P(k,mu) pass. */
 #define VG_OPT_MOMENTS 0
 /* VG_OPT_DIRECT_PK (default 0): 1 makes vg_model_batch / vg_chi2_batch* evaluate
  * Model.compute_direct (vega/model.py:189-208) -- one `full` component from the isotropic
@@ -274,6 +285,17 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
  * split-integer kernel, with the digits VG_OPT_OZAKI selects (automatic: its own bound against
  * max|D xi| at the plan parameters, vg_corr_ozaki_dm_slices); 0 keeps it on the FP64 DMMA kernel. */
 #define VG_OPT_OZAKI_DM 4
+/* VG_OPT_VELO_TABLES (default 1): evaluations whose only sampled non-polynomial P(k,mu) factor is ONE
+ * velocity dispersion (vega/power_spectrum.py:588-636) with finite limits (vg_plan_set_theta_limits)
+ * take the moment form too: their static knot tables K(sigma_v) are a Chebyshev series in
+ * log(sigma_v^2 + eps^2) over [lo, hi], built at finalize from 64 per-point passes and CHECKED there
+ * against the per-point pass on 8 other values of sigma_v (order count = the smallest that meets
+ * 2e-12 max|xi| per output slot; none meeting it = no tables).  The hot path is then one FP64 GEMM
+ * per evaluation instead of the 814 000-point pass and its Hankel rows.  Used for calls whose vectors
+ * all lie inside [lo, hi] (checked per call: on the host for host theta, one small kernel and a
+ * 4-byte read-back for device theta); anything else, and 0, keeps the per-point pass (the parity
+ * reference of the tables). */
+#define VG_OPT_VELO_TABLES 5
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
 /* Isotropic P(k) [nk] for the direct mode (e.g. from a Boltzmann code, the `direct_pk`
  * argument of VegaInterface.compute_model / chi2 / log_lik); host pointer, copied. */
@@ -281,6 +303,13 @@ int vg_plan_set_direct_pk(vg_plan* plan, const double* pk_host);
 /* Number of evaluations of a correlation served by the moment form (after finalize; 0 when
  * the option is off) -- the remaining ones go through pk_ell + the Hankel GEMM */
 int vg_corr_n_moment(const vg_plan* plan, int32_t corr);
+/* Evaluations of the correlation served by velocity-dispersion tables (after finalize; 0 when off or
+ * when no order count met the tolerance); orders (nullable): Chebyshev orders kept, error
+ * (nullable): the largest |xi(tables) - xi(per point)| / max|xi| measured at finalize. */
+int vg_corr_velo_tables(const vg_plan* plan, int32_t corr, int32_t* orders, double* error);
+/* 1 when the last vg_model_batch / vg_chi2_batch* call ran on the velocity-dispersion tables (every
+ * vector inside the tabulated range), 0 when it took the per-point pass */
+int vg_plan_velo_tables_active(const vg_plan* plan);
 /* Evaluations of the correlation whose xi stage (vega/correlation_func.py:117-236) is in moment
  * form too (vg_eval_desc::static_xi): read-out of static per-bin tables, no gather. */
 int vg_corr_n_static_xi(const vg_plan* plan, int32_t corr);

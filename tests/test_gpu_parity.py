@@ -140,6 +140,35 @@ def test_moment_form_matches_per_point_pass():
     assert_xi_close({n: models_mom[n][0] for n in ref}, ref, 'moment form')
 
 
+def test_moment_form_with_the_uv_bias_term_matches_per_point_pass():
+    """The scale-dependent UV bias (vega/power_spectrum.py:224-261) at FIXED UV parameters is a static
+    function of k: five more moment terms (G, G F, G^2, G mu^2, G F mu^2).  Every evaluation of the
+    reference's 4-correlation configuration (UVB-fluctuations on) is then in moment form; same model
+    as the per-point pass and as the oracle."""
+    from vega_b200 import _lib
+    vega, oracle = make_oracle('configs/full_configs/main.ini')
+    names = ['bias_eta_LYA', 'beta_LYA', 'bias_hcd', 'beta_hcd', 'ap', 'at', 'bias_eta_SiII(1260)']
+    names = [n for n in names if n in vega.params]
+    base = np.array([vega.params[n] for n in names])
+    theta = base * (1 + 0.05 * np.random.default_rng(5).standard_normal((12, len(names))))
+    models_mom, _ = vega.compute_model_batch(theta, names)
+    engine = vega._engine_for(tuple(names))
+    n_mom = [engine.n_moment(ci) for ci in range(len(engine.infos))]
+    for ci, info in enumerate(engine.infos):
+        own = [d for d in info['evals'] if d.table_owner < 0 and not d.frozen and not d.direct]
+        assert any(d.uvb and (d.uv_on[0] or d.uv_on[1]) and d.uv_static for d in own)
+        assert n_mom[ci] == len(own), (info['item'].name, n_mom[ci], len(own))
+    engine.set_option(_lib.OPT_MOMENTS, 0)
+    models_pp, _ = vega.compute_model_batch(theta, names)
+    engine.set_option(_lib.OPT_MOMENTS, 1)
+    for name in models_pp:
+        scale = np.max(np.abs(models_pp[name]))
+        assert np.max(np.abs(models_mom[name] - models_pp[name])) <= 1e-12 * scale, name
+    for b in (0, 11):
+        ref = oracle.compute_model(dict(zip(names, theta[b])))
+        assert_xi_close({n: models_mom[n][b] for n in ref}, ref, f'uv moment form, row {b}')
+
+
 @pytest.mark.parametrize('case', ['c2_dense', 'c2_fast_metals', 'rp_only'])
 def test_folded_metals_match_the_matrix_product(case, tmp_path):
     """VG_OPT_FOLD_METALS: metal terms whose xi stage is in moment form are served from static

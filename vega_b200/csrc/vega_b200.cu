@@ -116,7 +116,8 @@ struct OzakiOperand {
   const double* src = nullptr;   // static operands: the matrix the digits were taken from
 };
 
-struct EvalLayout {
+// pk_ell launch lists of one layout
+struct PkLists {
   // evaluations grouped by pk_ell kernel class: 0..19 fast (VMODE*5 + KIND), 20..22 generic (20 + MODE)
   std::vector<int> class_ids[23];
   DevBuf d_class_ids[23];
@@ -126,7 +127,20 @@ struct EvalLayout {
   std::vector<int> pair_ids[23], pair_twins[23];
   DevBuf d_pair_ids[23], d_pair_twins[23];
   int n_single[23] = {0};
+};
+
+struct EvalLayout {
+  PkLists pk;                    // every evaluation that owns per-point tables
+  PkLists pk_hot;                // the same without the ones served by velocity-dispersion tables
   std::vector<int> mom_ids;      // evaluations in moment form
+  // velocity-dispersion tables (vg_moments.cuh): owners served by them when the tables are active;
+  // their per-point slots are numbered LAST (n_full_hot .. n_full-1), so with the tables active the
+  // per-point pass and the Hankel GEMM run on n_full_hot slots and these evaluations read rows
+  // n_mom .. n_mom + n_vt - 1 of the moment-table region (d_tabslot_vt)
+  std::vector<int> vt_ids, vt_nm;              // vt_nm[i] = terms of evaluation vt_ids[i] (vg::vt_terms)
+  std::vector<vg::VtTerms> vt_terms;
+  DevBuf d_vt_ids, d_vt_terms, d_tabslot_vt;
+  int n_full_hot = 0;
   std::vector<int> gather_ids;   // evaluations K3 runs for: [0, n_gather_fast) through the fast kernel
   int n_gather_fast = 0;
   std::vector<int> mxi_ids;      // LAY_MOM: evaluations whose xi stage is in moment form (static_xi)
@@ -160,6 +174,15 @@ struct Corr {
   EvalLayout lay[LAY_COUNT];
   DevBuf d_mom_ktab;             // LAY_MOM: [n_mom][9][n_ell][2*n_out_pad]
   DevBuf d_mxi_tab;              // LAY_MOM: [n_mxi][9][ld_model] xi stage applied to the moment tables
+  // velocity-dispersion tables (vg_moments.cuh): vt_flag[e] marks the owners served by them, all
+  // with the same sampled dispersion (full-vector column vt_col = theta column vt_tcol, limits in
+  // vt_map); vt_tab[i] = Chebyshev coefficients of evaluation LAY_MOM.vt_ids[i], K-major
+  // [row_len][VT_NODES * nm]; vt_n = Chebyshev orders kept (0: off), vt_err = error measured at finalize
+  std::vector<char> vt_flag;
+  int vt_col = -1, vt_tcol = -1, vt_n = 0;
+  vg::VtMap vt_map{};
+  double vt_err = 0.0;
+  std::vector<DevBuf> vt_tab;
   bool allow_mxi = true;         // cleared when the plan-time gather of the static tables fails
   std::vector<DevBuf> coords;
   std::vector<double> opz_eff2;
@@ -221,6 +244,11 @@ struct vg_plan {
   bool use_moments = true;
   bool direct_mode = false;      // VG_OPT_DIRECT_PK
   bool fold_metals = false;      // VG_OPT_FOLD_METALS
+  bool velo_tables = true;       // VG_OPT_VELO_TABLES
+  bool vt_now = false;           // this call's vectors lie inside the tabulated range: tables active
+  std::vector<double> theta_lo, theta_hi;   // [sample] limits per theta column (NaN: unbounded)
+  std::vector<int> theta_cols_host;
+  DevBuf d_vt_flag, w_vtw;       // range-check flag; weights [n_vt][chunk][ldw]
   bool ozaki_dm = true;          // VG_OPT_OZAKI_DM: the distortion product on the split-integer kernel too
   int ozaki_slices = -1;         // VG_OPT_OZAKI: digits of the split-integer metal GEMM (0: DMMA, -1: per
                                  // correlation, the fewest digits that meet the truncation budget)
@@ -279,7 +307,7 @@ bool nvtx_enabled() {
 }
 const char* const PROF_NAMES[16] = {"vg:pk_ell", "vg:hankel_gemm", "vg:xi_gather", "vg:metal_gemm", "vg:dm_gemm",
                                     "vg:chi2_gemm", "vg:elementwise", "vg:moment_tables", "vg:moment_xi",
-                                    "vg:ozaki_slice", "vg:metal_rp", "vg:11", "vg:12", "vg:13", "vg:14", "vg:15"};
+                                    "vg:ozaki_slice", "vg:metal_rp", "vg:velo_tables", "vg:12", "vg:13", "vg:14", "vg:15"};
 struct ProfScope {
   vg_plan* plan; cudaStream_t st; cudaEvent_t e1 = nullptr; bool range = false;
   ProfScope(vg_plan* p, int tag, cudaStream_t s) : plan(p), st(s) {
@@ -307,10 +335,12 @@ int build_metal_operands(Corr& c, const EvalLayout& L, DevBuf& mcat, DevBuf& mrp
 int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget_dm(vg_plan* plan, Corr& c, cudaStream_t st);
+void flag_velo_table_candidates(vg_plan* plan, Corr& c);
+int build_velo_tables(vg_plan* plan, Corr& c, cudaStream_t st);
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
                     cudaStream_t st);
 enum { PROF_PK = 0, PROF_HANKEL = 1, PROF_XI = 2, PROF_METAL = 3, PROF_DM = 4, PROF_CHI2 = 5, PROF_ELEM = 6, PROF_MOMENT = 7,
-       PROF_MXI = 8, PROF_OZ_SLICE = 9, PROF_METAL_RP = 10, PROF_NTAGS = 16, PROF_NONE = -1 };
+       PROF_MXI = 8, PROF_OZ_SLICE = 9, PROF_METAL_RP = 10, PROF_VTAB = 11, PROF_NTAGS = 16, PROF_NONE = -1 };
 }  // namespace
 
 namespace {
@@ -427,16 +457,21 @@ int build_layouts(vg_plan* plan, Corr& c) {
   for (int e = 0; e < E; ++e)
     if (c.evals[e].frozen && !c.evals[e].direct) c.frozen_ids.push_back(e);
   if (!c.frozen_ids.empty()) VG_TRY(upload(c.d_frozen_ids, c.frozen_ids.data(), c.frozen_ids.size()));
+  if ((int)c.vt_flag.size() != E) c.vt_flag.assign(E, 0);
   for (int li = 0; li < LAY_COUNT; ++li) {
     EvalLayout& L = c.lay[li];
     const bool momlike = li == LAY_MOM || li == LAY_FOLD;
-    for (auto& ids : L.class_ids) ids.clear();
-    for (int m = 0; m < 23; ++m) { L.pair_ids[m].clear(); L.pair_twins[m].clear(); L.n_single[m] = 0; }
+    for (PkLists* P : {&L.pk, &L.pk_hot}) {
+      for (auto& ids : P->class_ids) ids.clear();
+      for (int m = 0; m < 23; ++m) { P->pair_ids[m].clear(); P->pair_twins[m].clear(); P->n_single[m] = 0; }
+    }
     L.mom_ids.clear(); L.gather_ids.clear(); L.mxi_ids.clear(); L.mxi_owner.clear();
     L.mxi_rows.clear(); L.fold_ids.clear(); L.fold_owner.clear(); L.fold_rows.clear();
-    L.n_full = 0; L.n_metal = 0;
+    L.vt_ids.clear(); L.vt_nm.clear(); L.vt_terms.clear();
+    L.n_full = 0; L.n_full_hot = 0; L.n_metal = 0;
     L.metal_map.assign(std::max(c.n_metal, 1), -1);
     std::vector<int> slot(E, 0), tabslot(E, 0);
+    std::vector<int> full_ids;     // owners of per-point tables, in evaluation order
     for (int e = 0; e < E; ++e) {
       const vg_eval_desc& d = c.evals[e];
       const bool hot = li == LAY_DIRECT ? d.direct != 0 : (!d.direct && (li == LAY_ALL || !d.frozen));
@@ -466,12 +501,32 @@ int build_layouts(vg_plan* plan, Corr& c) {
         tabslot[e] = -((int)L.mom_ids.size() + 1);
         L.mom_ids.push_back(e);
       } else {
-        slot[e] = tabslot[e] = L.n_full++;
-        L.class_ids[pk_class(plan, d)].push_back(e);
+        full_ids.push_back(e);
       }
     }
+    // per-point slots: the evaluations served by velocity-dispersion tables last
+    for (int pass = 0; pass < 2; ++pass)
+      for (int e : full_ids) {
+        const bool vt = momlike && c.vt_flag[e];
+        if (vt != (pass == 1)) continue;
+        slot[e] = tabslot[e] = L.n_full++;
+        L.pk.class_ids[pk_class(plan, c.evals[e])].push_back(e);
+        if (!vt) {
+          L.n_full_hot = L.n_full;
+          L.pk_hot.class_ids[pk_class(plan, c.evals[e])].push_back(e);
+        } else {
+          L.vt_ids.push_back(e);
+          L.vt_terms.push_back(vg::vt_terms(c.evals[e]));
+          L.vt_nm.push_back(L.vt_terms.back().n);
+        }
+      }
+    std::vector<int> tabslot_vt = tabslot;
+    for (size_t i = 0; i < L.vt_ids.size(); ++i) tabslot_vt[L.vt_ids[i]] = -((int)(L.mom_ids.size() + i) + 1);
     for (int e = 0; e < E; ++e)
-      if (c.evals[e].table_owner >= 0) tabslot[e] = tabslot[c.evals[e].table_owner];
+      if (c.evals[e].table_owner >= 0) {
+        tabslot[e] = tabslot[c.evals[e].table_owner];
+        tabslot_vt[e] = tabslot_vt[c.evals[e].table_owner];
+      }
     {   // evaluations the fast gather kernel serves first (vg_xi.cuh: xi_gather_fast_kernel)
       const Hankel& hk = *plan->hankels[c.hankel_id];
       auto fast = [&](int e) {
@@ -483,31 +538,38 @@ int build_layouts(vg_plan* plan, Corr& c) {
       L.n_gather_fast = (int)std::count_if(L.gather_ids.begin(), L.gather_ids.end(), fast);
     }
     // twins: both members per point in the same fast class of this layout
-    for (int m = 0; m < 20; ++m) {
-      std::vector<int>& ids = L.class_ids[m];
-      std::vector<int> single, paired;
-      std::vector<char> taken(E, 0);
-      for (int e : ids) {
-        const int t = c.evals[e].pk_twin;
-        if (t >= 0 && t < E && t != e && !taken[t] && !taken[e] &&
-            std::find(ids.begin(), ids.end(), t) != ids.end()) {
-          L.pair_ids[m].push_back(t); L.pair_twins[m].push_back(e);
-          taken[t] = taken[e] = 1;
+    for (PkLists* P : {&L.pk, &L.pk_hot}) {
+      for (int m = 0; m < 20; ++m) {
+        std::vector<int>& ids = P->class_ids[m];
+        std::vector<int> single, paired;
+        std::vector<char> taken(E, 0);
+        for (int e : ids) {
+          const int t = c.evals[e].pk_twin;
+          if (t >= 0 && t < E && t != e && !taken[t] && !taken[e] &&
+              std::find(ids.begin(), ids.end(), t) != ids.end()) {
+            P->pair_ids[m].push_back(t); P->pair_twins[m].push_back(e);
+            taken[t] = taken[e] = 1;
+          }
+        }
+        for (int e : ids) (taken[e] ? paired : single).push_back(e);
+        P->n_single[m] = (int)single.size();
+        ids = single;
+        ids.insert(ids.end(), paired.begin(), paired.end());
+      }
+      for (int m = 20; m < PK_NCLS; ++m) P->n_single[m] = (int)P->class_ids[m].size();
+      for (int m = 0; m < PK_NCLS; ++m) {
+        if (!P->class_ids[m].empty()) VG_TRY(upload(P->d_class_ids[m], P->class_ids[m].data(), P->class_ids[m].size()));
+        if (!P->pair_ids[m].empty()) {
+          VG_TRY(upload(P->d_pair_ids[m], P->pair_ids[m].data(), P->pair_ids[m].size()));
+          VG_TRY(upload(P->d_pair_twins[m], P->pair_twins[m].data(), P->pair_twins[m].size()));
         }
       }
-      for (int e : ids) (taken[e] ? paired : single).push_back(e);
-      L.n_single[m] = (int)single.size();
-      ids = single;
-      ids.insert(ids.end(), paired.begin(), paired.end());
     }
-    for (int m = 20; m < PK_NCLS; ++m) L.n_single[m] = (int)L.class_ids[m].size();
-    for (int m = 0; m < PK_NCLS; ++m) {
-      if (!L.class_ids[m].empty()) VG_TRY(upload(L.d_class_ids[m], L.class_ids[m].data(), L.class_ids[m].size()));
-      if (!L.pair_ids[m].empty()) {
-        VG_TRY(upload(L.d_pair_ids[m], L.pair_ids[m].data(), L.pair_ids[m].size()));
-        VG_TRY(upload(L.d_pair_twins[m], L.pair_twins[m].data(), L.pair_twins[m].size()));
-      }
+    if (!L.vt_ids.empty()) {
+      VG_TRY(upload(L.d_vt_ids, L.vt_ids.data(), L.vt_ids.size()));
+      VG_TRY(upload(L.d_vt_terms, L.vt_terms.data(), L.vt_terms.size()));
     }
+    VG_TRY(upload(L.d_tabslot_vt, tabslot_vt.data(), tabslot_vt.size()));
     if (!L.mom_ids.empty()) VG_TRY(upload(L.d_mom_ids, L.mom_ids.data(), L.mom_ids.size()));
     if (!L.gather_ids.empty()) VG_TRY(upload(L.d_gather_ids, L.gather_ids.data(), L.gather_ids.size()));
     if (!L.mxi_ids.empty()) {
@@ -558,6 +620,7 @@ int vg_plan_create(int32_t n_params, const double* base, int32_t n_theta, const 
     VG_REQUIRE(theta_cols[j] >= 0 && theta_cols[j] < n_params, "theta column out of range");
   VG_TRY(upload(p->d_base, base, n_params));
   VG_TRY(upload(p->d_theta_cols, theta_cols, std::max(n_theta, 1)));
+  p->theta_cols_host.assign(theta_cols, theta_cols + n_theta);
   VG_TRY(upload(p->d_k, k, nk));
   std::vector<double> peak(nk);
   for (int i = 0; i < nk; ++i) peak[i] = pk_full[i] - pk_smooth[i];   // vega/model.py:177
@@ -600,6 +663,7 @@ int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
     return VG_OK;
   }
   if (option == VG_OPT_OZAKI_DM) { plan->ozaki_dm = value != 0; return VG_OK; }
+  if (option == VG_OPT_VELO_TABLES) { plan->velo_tables = value != 0; return VG_OK; }
   if (option == VG_OPT_DIRECT_PK) {
     if (value) {
       bool any = false;
@@ -628,6 +692,14 @@ int vg_plan_set_theta_transform(vg_plan* plan, const double* offset, const int32
   VG_TRY(upload(plan->d_theta_offset, offset, plan->n_theta));
   VG_TRY(upload(plan->d_theta_force, force_one, plan->n_theta));
   plan->has_theta_transform = true;
+  return VG_OK;
+}
+
+int vg_plan_set_theta_limits(vg_plan* plan, const double* lo, const double* hi) {
+  VG_REQUIRE(plan && lo && hi, "vg_plan_set_theta_limits: bad arguments");
+  VG_REQUIRE(!plan->finalized, "vg_plan_set_theta_limits: call before vg_plan_finalize");
+  plan->theta_lo.assign(lo, lo + plan->n_theta);
+  plan->theta_hi.assign(hi, hi + plan->n_theta);
   return VG_OK;
 }
 
@@ -851,6 +923,7 @@ int vg_plan_set_global_invcov(vg_plan* plan, int32_t n_total, const double* invc
 int vg_plan_finalize(vg_plan* plan, void* stream) {
   VG_REQUIRE(plan && !plan->corrs.empty(), "plan has no correlation");
   plan->drop_graphs();
+  plan->vt_now = false;
   cudaStream_t st = (cudaStream_t)stream;
   // number of static grids referenced
   int n_grids = 0;
@@ -878,6 +951,7 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
     VG_REQUIRE(!c.evals.empty(), "correlation without evaluations");
     c.allow_mxi = true;
     VG_TRY(upload(c.d_evals, c.evals.data(), c.evals.size()));
+    flag_velo_table_candidates(plan, c);
     VG_TRY(build_layouts(plan, c));
     std::vector<const double*> cptrs;
     for (auto& b : c.coords) cptrs.push_back(b.as<double>());
@@ -922,7 +996,7 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
       VG_TRY(c.d_mom_ktab.alloc((size_t)rows * plan->n_ell * rowT * 8));
       dim3 mgrid(vg_cdiv(plan->nk, 128), (unsigned)LM.mom_ids.size());
       vg::moment_grid_kernel<<<mgrid, 128, 0, st>>>(g, c.d_evals.as<vg_eval_desc>(), LM.d_mom_ids.as<int>(),
-                                                  mom.as<double>());
+                                                  plan->d_base.as<double>(), mom.as<double>());
       VG_LAUNCHED();
       VG_TRY(gemm_auto(plan, mom.as<double>(), (long long)plan->n_ell * plan->nk_pad, h.op.as<double>(),
                        plan->nk_pad, c.d_mom_ktab.as<double>(), (long long)plan->n_ell * rowT, rows, rowT,
@@ -964,6 +1038,8 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
         VG_TRY(build_layouts(plan, c));
       }
     }
+    // velocity-dispersion tables (vg_moments.cuh): built and checked against the per-point pass
+    if (!LM.vt_ids.empty()) VG_TRY(build_velo_tables(plan, c, st));
     VG_REQUIRE(!(c.metal_rp && c.metal_dense), "a correlation mixes dense and rp-only metal matrices");
     VG_TRY(build_metal_operands(c, LM, c.d_mcat, c.d_mrp));
     // folded metal terms: Y[f][m] = M_c X[row(f)][m], and the matrices of the terms that stay
@@ -1422,8 +1498,13 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
                                                                       : LAY_FULL));
   const bool direct = layout == LAY_DIRECT;
   const EvalLayout& L = c.lay[layout];
-  const int Ef = L.n_full;
+  // velocity-dispersion tables active: their evaluations leave the per-point pass and the Hankel
+  // GEMM (slots n_full_hot..) and get rows Em.. of the moment-table region
+  const bool vt = plan->vt_now && c.vt_n > 0 && (layout == LAY_MOM || layout == LAY_FOLD) && !L.vt_ids.empty();
+  const PkLists& PL = vt ? L.pk_hot : L.pk;
+  const int Ef = vt ? L.n_full_hot : L.n_full;
   const int Em = (int)L.mom_ids.size();
+  const int Ev = vt ? (int)L.vt_ids.size() : 0;
   const int rowT = 2 * h.n_out_pad;
   const long long row_len = (long long)plan->n_ell * rowT;
   double* tables_full = plan->w_tables.as<double>();
@@ -1442,21 +1523,21 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     const int MG = vg::PK_GROUPS / EG;
     const size_t fast_smem = vg::pk_fast_smem_bytes(plan->nmu);
     for (int m = 0; m < PK_NCLS; ++m) {
-      const std::vector<int>& class_ids = L.class_ids[m];
+      const std::vector<int>& class_ids = PL.class_ids[m];
       if (class_ids.empty()) continue;
-      const int* ids = L.d_class_ids[m].as<int>();
+      const int* ids = PL.d_class_ids[m].as<int>();
       if (m < 20 && fast_ok) {
         dim3 block(vg::PK_KLANES, vg::PK_FAST_MG, vg::PK_FAST_EG);
-        if (L.n_single[m] > 0) {
-          dim3 grid(vg_cdiv(Bc, 2 * vg::PK_FAST_EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)L.n_single[m]);
+        if (PL.n_single[m] > 0) {
+          dim3 grid(vg_cdiv(Bc, 2 * vg::PK_FAST_EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)PL.n_single[m]);
           VG_TRY(launch_pk_fast(m / 5, m % 5, grid, block, fast_smem, st, g, ev, E, ids, nullptr, out_slot, Ef,
                                 pf, plan->npf, (int)Bc, out));
         }
-        if (!L.pair_ids[m].empty()) {      // one vector, two evaluations per thread
-          if (L.n_single[m] > 0) VG_LAUNCHED();
-          dim3 grid(vg_cdiv(Bc, vg::PK_FAST_EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)L.pair_ids[m].size());
-          VG_TRY(launch_pk_fast(m / 5, m % 5, grid, block, fast_smem, st, g, ev, E, L.d_pair_ids[m].as<int>(),
-                                L.d_pair_twins[m].as<int>(), out_slot, Ef, pf, plan->npf, (int)Bc, out));
+        if (!PL.pair_ids[m].empty()) {      // one vector, two evaluations per thread
+          if (PL.n_single[m] > 0) VG_LAUNCHED();
+          dim3 grid(vg_cdiv(Bc, vg::PK_FAST_EG), vg_cdiv(plan->nk, vg::PK_KLANES), (unsigned)PL.pair_ids[m].size());
+          VG_TRY(launch_pk_fast(m / 5, m % 5, grid, block, fast_smem, st, g, ev, E, PL.d_pair_ids[m].as<int>(),
+                                PL.d_pair_twins[m].as<int>(), out_slot, Ef, pf, plan->npf, (int)Bc, out));
         }
       } else {
         dim3 block(vg::PK_KLANES, MG, EG);
@@ -1491,18 +1572,40 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     dim3 grid(vg_cdiv(row_len, 256 * vg::MOM_XPT), (unsigned)Em, (unsigned)vg_cdiv(Bc, vg::MOM_NB));
     vg::moment_tables_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_mom_ids.as<int>(), Em,
                                                   plan->w_pfull.as<double>(), plan->npf, (int)Bc,
-                                                  c.d_mom_ktab.as<double>(), (int)row_len, tables_mom);
+                                                  c.d_mom_ktab.as<double>(), (int)row_len, Em + Ev, tables_mom);
     VG_LAUNCHED();
+  }
+  if (Ev > 0) {  // velocity-dispersion tables: weights, then one GEMM per evaluation
+    ProfScope prof(plan, PROF_VTAB, st);
+    int ldw = 0;
+    for (int nm : L.vt_nm) ldw = std::max(ldw, pad16((long long)c.vt_n * nm));
+    VG_TRY(plan->w_vtw.ensure((size_t)Ev * (size_t)std::max(plan->chunk, Bc) * ldw * 8));
+    double* W = plan->w_vtw.as<double>();
+    dim3 wgrid(vg_cdiv(Bc, 128), (unsigned)Ev);
+    vg::vtab_weights_kernel<<<wgrid, 128, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_vt_ids.as<int>(),
+                                                  L.d_vt_terms.as<vg::VtTerms>(), plan->w_pfull.as<double>(), plan->npf,
+                                                  (int)Bc, c.vt_map, c.vt_n, ldw, W);
+    VG_LAUNCHED();
+    for (int i = 0; i < Ev; ++i) {
+      vg::GemmArgs ga{};
+      ga.A = W + (size_t)i * Bc * ldw; ga.lda = ldw;
+      ga.B = c.vt_tab[i].as<double>(); ga.ldb = (long long)vg::VT_NODES * L.vt_nm[i];
+      ga.C = tables_mom + (long long)(Em + i) * row_len; ga.ldc = (long long)(Em + Ev) * row_len;
+      ga.M = (int)Bc; ga.N = (int)row_len; ga.K = pad16((long long)c.vt_n * L.vt_nm[i]);
+      ga.batch = 1; ga.splits = 1; ga.alpha = 1.0; ga.beta = 0.0;
+      VG_TRY(vg::launch_dgemm(ga, vg::GEMM_STORE, st));
+    }
   }
   if (upto <= 2) return VG_OK;
   if (!L.gather_ids.empty()) {  // K3
     ProfScope prof(plan, PROF_XI, st);
     GatherJob job{};
     job.ids = L.d_gather_ids.as<int>(); job.n_ids = (int)L.gather_ids.size();
-    job.tab_slot = L.d_tabslot.as<int>(); job.metal_map = L.d_metal_map.as<int>(); job.n_metal = L.n_metal;
+    job.tab_slot = (vt ? L.d_tabslot_vt : L.d_tabslot).as<int>();
+    job.metal_map = L.d_metal_map.as<int>(); job.n_metal = L.n_metal;
     job.pfull = plan->w_pfull.as<double>(); job.B = Bc;
     job.tables = tables_full; job.n_full = Ef;
-    job.tables_mom = tables_mom; job.n_mom = Em; job.mom_stride_b = Em * row_len; job.mom_stride_j = row_len;
+    job.tables_mom = tables_mom; job.n_mom = Em + Ev; job.mom_stride_b = (Em + Ev) * row_len; job.mom_stride_j = row_len;
     job.unit_bias = unit_bias;
     job.core = plan->w_core.as<double>(); job.xmet = plan->w_xmet.as<double>();
     job.status = status_dev;
@@ -1536,6 +1639,11 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     ProfScope prof(plan, PROF_ELEM, st);
     const int nf = (int)L.fold_ids.size();
     const size_t smem = (size_t)nf * vg::MOM_MAX * vg::MXI_NB * 8 + (size_t)nf * sizeof(int);
+    static size_t fold_smem_set = 48 * 1024;
+    if (smem > fold_smem_set) {
+      VG_CUDA_CHECK(cudaFuncSetAttribute(vg::moment_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      fold_smem_set = smem;
+    }
     dim3 grid(vg_cdiv(c.ld_model, 256), (unsigned)vg_cdiv(Bc, vg::MXI_NB));
     vg::moment_fold_kernel<<<grid, 256, smem, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_fold_ids.as<int>(),
                                                    L.d_fold_owner.as<int>(), nf, plan->w_pfull.as<double>(),
@@ -1610,6 +1718,184 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
 }  // namespace
 
 namespace {
+
+// ---- velocity-dispersion tables (vg_moments.cuh) ------------------------------------------------
+constexpr long long VT_MIN_BATCH = 1;      // every batch size: a single vector reads ~15 MB of coefficients per evaluation
+                                           // instead of walking the 814 000-point grid (C3, one vector: pk_ell was 0.41 of 1.02 ms)
+
+// Marks the evaluations of a correlation that velocity-dispersion tables can serve: the moment form
+// applies to everything but ONE sampled velocity dispersion, which is a theta column with finite
+// [sample] limits 0 <= lo < hi (vg_plan_set_theta_limits); all of them read the same dispersion.
+void flag_velo_table_candidates(vg_plan* plan, Corr& c) {
+  const int E = (int)c.evals.size();
+  c.vt_flag.assign(E, 0);
+  c.vt_n = 0; c.vt_col = c.vt_tcol = -1; c.vt_err = 0.0;
+  c.vt_tab.clear();
+  if ((int)plan->theta_lo.size() != plan->n_theta || plan->n_theta == 0 || plan->has_theta_transform) return;
+  if (plan->n_ell != vg::PK_MAX_ELL) return;
+  for (int e = 0; e < E; ++e) {
+    const vg_eval_desc& d = c.evals[e];
+    if (d.table_owner >= 0 || d.frozen || d.direct || !vg::vt_eligible(d)) continue;
+    const int col = vg::vt_sigma_column(d);
+    if (c.vt_col >= 0 && col != c.vt_col) continue;
+    int tcol = -1;
+    for (int j = 0; j < plan->n_theta; ++j)
+      if (plan->theta_cols_host[j] == col) tcol = j;
+    if (tcol < 0) continue;
+    const double lo = plan->theta_lo[tcol], hi = plan->theta_hi[tcol];
+    if (!(std::isfinite(lo) && std::isfinite(hi) && lo >= 0.0 && hi > lo)) continue;
+    if (c.vt_col < 0) {
+      c.vt_col = col; c.vt_tcol = tcol;
+      c.vt_map.lo = lo; c.vt_map.hi = hi; c.vt_map.eps = vg::VT_EPS;
+      c.vt_map.tau_lo = vg::vt_tau(lo, vg::VT_EPS); c.vt_map.tau_hi = vg::vt_tau(hi, vg::VT_EPS);
+    }
+    c.vt_flag[e] = 1;
+  }
+  for (int e = 0; e < E; ++e) {   // twins go together or not at all
+    const int t = c.evals[e].pk_twin;
+    if (t >= 0 && t < E && c.vt_flag[e] != c.vt_flag[t]) c.vt_flag[e] = c.vt_flag[t] = 0;
+  }
+}
+
+// Chebyshev coefficient tables of the flagged evaluations, then the order count: the smallest of the
+// ladder whose xi-stage output matches the per-point pass on VT_NTEST values of sigma to VT_TOL
+// (relative to the largest bin of each output slot).  No order count passing clears the flags.
+int build_velo_tables(vg_plan* plan, Corr& c, cudaStream_t st) {
+  const EvalLayout& LM = c.lay[LAY_MOM];
+  const Hankel& h = *plan->hankels[c.hankel_id];
+  const int nv = (int)LM.vt_ids.size();
+  const int rowT = 2 * h.n_out_pad;
+  const long long row_len = (long long)plan->n_ell * rowT;
+  const int NQ = vg::VT_NODES;
+  {
+    std::vector<double> sig(NQ);
+    for (int q = 0; q < NQ; ++q) sig[q] = vg::vt_sigma_of(std::cos(M_PI * (q + 0.5) / NQ), c.vt_map);
+    DevBuf d_sig, mom, node;
+    VG_TRY(upload(d_sig, sig.data(), sig.size()));
+    VG_TRY(mom.alloc((size_t)NQ * vg::MOM_MAX * plan->n_ell * plan->nk_pad * 8));
+    VG_TRY(node.alloc((size_t)NQ * vg::MOM_MAX * row_len * 8));
+    c.vt_tab.clear();
+    c.vt_tab.resize(nv);
+    vg::PkGridDev g = plan->grid_dev();
+    for (int i = 0; i < nv; ++i) {
+      const int nm = LM.vt_nm[i];
+      dim3 ggrid(vg_cdiv(plan->nk, 128), (unsigned)NQ, 1);
+      vg::vtab_grid_kernel<<<ggrid, 128, 0, st>>>(g, c.d_evals.as<vg_eval_desc>(), LM.d_vt_ids.as<int>() + i,
+                                                 plan->d_base.as<double>(), d_sig.as<double>(), NQ, mom.as<double>());
+      VG_LAUNCHED();
+      VG_TRY(gemm_auto(plan, mom.as<double>(), (long long)plan->n_ell * plan->nk_pad, h.op.as<double>(),
+                       plan->nk_pad, node.as<double>(), row_len, NQ * vg::MOM_MAX, rowT, plan->nk_pad,
+                       plan->n_ell, plan->nk_pad, (long long)rowT * plan->nk_pad, rowT, st));
+      VG_TRY(c.vt_tab[i].alloc((size_t)row_len * NQ * nm * 8));
+      dim3 cgrid(vg_cdiv(row_len, 128), (unsigned)NQ);
+      vg::vtab_cheb_kernel<<<cgrid, 128, 0, st>>>(node.as<double>(), NQ, LM.vt_terms[i], (int)row_len, c.vt_tab[i].as<double>());
+      VG_LAUNCHED();
+    }
+    VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  }
+  // ---- check against the per-point pass ----
+  const int NT = vg::VT_NTEST;
+  static const double t_test[vg::VT_NTEST] = {-0.97, -0.71, -0.33, 0.05, 0.41, 0.68, 0.88, 0.985};
+  VG_TRY(ensure_workspace(plan, NT));
+  std::vector<double> pf((size_t)NT * plan->npf);
+  for (int i = 0; i < NT; ++i) {
+    std::copy(plan->base.begin(), plan->base.end(), pf.begin() + (size_t)i * plan->npf);
+    pf[(size_t)i * plan->npf + c.vt_col] = vg::vt_sigma_of(t_test[i], c.vt_map);
+  }
+  VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_pfull.p, pf.data(), pf.size() * 8, cudaMemcpyHostToDevice, st));
+  VG_CUDA_CHECK(cudaMemsetAsync(plan->w_status.p, 0, NT * 4, st));
+  const bool vt_now0 = plan->vt_now;
+  const size_t n_core = (size_t)2 * NT * c.ld_model, n_xmet = (size_t)NT * std::max(LM.n_metal, 1) * c.ld_model;
+  DevBuf ref_core, ref_xmet, d_cmp;
+  VG_TRY(ref_core.alloc(n_core * 8));
+  VG_TRY(ref_xmet.alloc(n_xmet * 8));
+  VG_TRY(d_cmp.alloc(2 * sizeof(unsigned long long)));
+  VG_CUDA_CHECK(cudaMemsetAsync(plan->w_core.p, 0, n_core * 8, st));
+  VG_CUDA_CHECK(cudaMemsetAsync(plan->w_xmet.p, 0, n_xmet * 8, st));
+  plan->vt_now = false;
+  int rc = run_corr_front(plan, c, NT, plan->w_status.as<int>(), st, 3, LAY_MOM);
+  if (rc == VG_OK) {
+    cudaMemcpyAsync(ref_core.p, plan->w_core.p, n_core * 8, cudaMemcpyDeviceToDevice, st);
+    cudaMemcpyAsync(ref_xmet.p, plan->w_xmet.p, n_xmet * 8, cudaMemcpyDeviceToDevice, st);
+  }
+  // (slot, first element, row stride, rows) of every output of the xi stage
+  struct Out { const double* ref; const double* got; long long stride; };
+  std::vector<Out> outs;
+  for (int sl = 0; sl < 2; ++sl)
+    outs.push_back({ref_core.as<double>() + (size_t)sl * NT * c.ld_model,
+                    plan->w_core.as<double>() + (size_t)sl * NT * c.ld_model, c.ld_model});
+  for (int m = 0; m < LM.n_metal; ++m)
+    outs.push_back({ref_xmet.as<double>() + (size_t)m * c.ld_model, plan->w_xmet.as<double>() + (size_t)m * c.ld_model,
+                    (long long)LM.n_metal * c.ld_model});
+  static const int ladder[] = {8, 12, 16, 24, 32, 40, 48, 56, 64};
+  int chosen = 0;
+  double chosen_err = 0.0;
+  for (int n : ladder) {
+    if (rc != VG_OK) break;
+    c.vt_n = n;
+    plan->vt_now = true;
+    rc = run_corr_front(plan, c, NT, plan->w_status.as<int>(), st, 3, LAY_MOM);
+    if (rc != VG_OK) break;
+    double err = 0.0;
+    for (const Out& o : outs) {
+      VG_CUDA_CHECK(cudaMemsetAsync(d_cmp.p, 0, 2 * sizeof(unsigned long long), st));
+      dim3 cg(vg_cdiv(c.n_model, 256), NT);
+      vg::vtab_compare_kernel<<<cg, 256, 0, st>>>(o.got, o.ref, c.n_model, o.stride, d_cmp.as<unsigned long long>());
+      VG_LAUNCHED();
+      double r[2];
+      VG_CUDA_CHECK(cudaMemcpyAsync(r, d_cmp.p, sizeof(r), cudaMemcpyDeviceToHost, st));
+      VG_CUDA_CHECK(cudaStreamSynchronize(st));
+      if (r[1] > 0.0) err = std::max(err, r[0] / r[1]);
+      else if (r[0] > 0.0) err = 1.0;
+    }
+    if (err <= vg::VT_TOL) { chosen = n; chosen_err = err; break; }
+  }
+  plan->vt_now = vt_now0;
+  VG_TRY(rc);
+  c.vt_n = chosen;
+  c.vt_err = chosen_err;
+  if (chosen == 0) {     // the tables do not reach the tolerance: these evaluations keep the per-point pass
+    std::fill(c.vt_flag.begin(), c.vt_flag.end(), 0);
+    c.vt_tab.clear();
+    VG_TRY(build_layouts(plan, c));
+  }
+  return VG_OK;
+}
+
+// Are this call's vectors inside the tabulated range of every correlation?  Sets plan->vt_now.
+// theta on the host is checked there; theta on the device costs one small kernel and a 4-byte
+// read-back per CALL (not per chunk).
+int decide_velo_tables(vg_plan* plan, const double* theta_dev, const double* theta_host, long long B, cudaStream_t st) {
+  plan->vt_now = false;
+  if (!plan->velo_tables || !plan->use_moments || plan->direct_mode || B < VT_MIN_BATCH) return VG_OK;
+  bool any = false;
+  for (auto& cp : plan->corrs) any = any || cp->vt_n > 0;
+  if (!any) return VG_OK;
+  if (theta_host) {
+    for (auto& cp : plan->corrs) {
+      if (cp->vt_n == 0) continue;
+      for (long long b = 0; b < B; ++b) {
+        const double v = theta_host[b * plan->n_theta + cp->vt_tcol];
+        if (!(v >= cp->vt_map.lo && v <= cp->vt_map.hi)) return VG_OK;
+      }
+    }
+    plan->vt_now = true;
+    return VG_OK;
+  }
+  if (!plan->d_vt_flag.p) VG_TRY(plan->d_vt_flag.alloc(sizeof(int)));
+  VG_CUDA_CHECK(cudaMemsetAsync(plan->d_vt_flag.p, 0, sizeof(int), st));
+  for (auto& cp : plan->corrs) {
+    if (cp->vt_n == 0) continue;
+    vg::vtab_range_kernel<<<vg_cdiv(B, 256), 256, 0, st>>>(theta_dev, plan->n_theta, cp->vt_tcol, B, cp->vt_map.lo,
+                                                        cp->vt_map.hi, plan->d_vt_flag.as<int>());
+    VG_LAUNCHED();
+  }
+  int flag = 1;
+  VG_CUDA_CHECK(cudaMemcpyAsync(&flag, plan->d_vt_flag.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  plan->vt_now = flag == 0;
+  return VG_OK;
+}
 
 // Digits of the split-integer metal GEMM for one correlation: the fewest S whose truncation bound,
 // evaluated with the row statistics of the operator and of the metal xi at the PLAN parameters,
@@ -1863,7 +2149,8 @@ int chi2_chunk_small(vg_plan* plan, const double* theta_dev, long long Bc, doubl
     return chi2_chunk(plan, theta_dev, Bc, chi2_dev, status_dev, st, mock_idx);
   const long long key = Bc | ((long long)plan->use_moments << 20) | ((long long)plan->fold_metals << 21) |
                         ((long long)plan->direct_mode << 22) | ((long long)(mock_idx != nullptr) << 23) |
-                        ((long long)(plan->ozaki_slices + 1) << 24) | ((long long)plan->ozaki_dm << 30);
+                        ((long long)(plan->ozaki_slices + 1) << 24) | ((long long)plan->ozaki_dm << 30) |
+                        ((long long)plan->vt_now << 31);
   vg_plan::GraphEntry& g = plan->graphs[key];
   if (g.exec && g.generation != g_alloc_generation) {     // a buffer moved since the capture
     cudaGraphExecDestroy(g.exec);
@@ -1926,6 +2213,7 @@ int vg_model_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* co
   cudaStream_t st = (cudaStream_t)stream;
   const long long chunk = std::min<long long>(B, plan->chunk_max);
   VG_TRY(ensure_workspace(plan, chunk));
+  VG_TRY(decide_velo_tables(plan, theta_dev, nullptr, B, st));
   for (long long b0 = 0; b0 < B; b0 += chunk) {
     const long long Bc = std::min<long long>(chunk, B - b0);
     VG_TRY(expand_params(plan, theta_dev + b0 * plan->n_theta, Bc, status_dev + b0, st));
@@ -1946,6 +2234,7 @@ int vg_chi2_batch(vg_plan* plan, const double* theta_dev, int64_t B, double* chi
   cudaStream_t st = (cudaStream_t)stream;
   const long long chunk = std::min<long long>(B, plan->chunk_max);
   VG_TRY(ensure_workspace(plan, chunk));
+  VG_TRY(decide_velo_tables(plan, theta_dev, nullptr, B, st));
   for (long long b0 = 0; b0 < B; b0 += chunk) {
     const long long Bc = std::min<long long>(chunk, B - b0);
     VG_TRY(chi2_chunk_small(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st));
@@ -1969,6 +2258,7 @@ int vg_chi2_batch_mc(vg_plan* plan, const double* theta_dev, const int32_t* mock
   cudaStream_t st = (cudaStream_t)stream;
   const long long chunk = std::min<long long>(B, plan->chunk_max);
   VG_TRY(ensure_workspace(plan, chunk));
+  VG_TRY(decide_velo_tables(plan, theta_dev, nullptr, B, st));
   for (long long b0 = 0; b0 < B; b0 += chunk) {
     const long long Bc = std::min<long long>(chunk, B - b0);
     VG_TRY(chi2_chunk_small(plan, theta_dev + b0 * plan->n_theta, Bc, chi2_dev + b0, status_dev + b0, st,
@@ -1995,6 +2285,7 @@ int vg_chi2_batch_host(vg_plan* plan, const double* theta_host, int64_t B, doubl
   double* pin_theta = reinterpret_cast<double*>(plan->pinned);
   double* pin_chi2 = pin_theta + (size_t)chunk * nt;
   int32_t* pin_status = reinterpret_cast<int32_t*>(pin_chi2 + chunk);
+  VG_TRY(decide_velo_tables(plan, nullptr, theta_host, B, st));
   for (long long b0 = 0; b0 < B; b0 += chunk) {
     const long long Bc = std::min<long long>(chunk, B - b0);
     if (plan->n_theta > 0) {
@@ -2096,6 +2387,19 @@ int vg_metal_pair_histograms(const double* side1, int32_t n1, const double* side
   return VG_OK;
 }
 
+int vg_corr_velo_tables(const vg_plan* plan, int32_t corr, int32_t* orders, double* error) {
+  if (orders) *orders = 0;
+  if (error) *error = 0.0;
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments || !plan->velo_tables) return 0;
+  const Corr& c = *plan->corrs[corr];
+  if (c.vt_n == 0) return 0;
+  if (orders) *orders = c.vt_n;
+  if (error) *error = c.vt_err;
+  return (int)c.lay[LAY_MOM].vt_ids.size();
+}
+
+int vg_plan_velo_tables_active(const vg_plan* plan) { return plan && plan->vt_now ? 1 : 0; }
+
 int vg_corr_n_static_xi(const vg_plan* plan, int32_t corr) {
   if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->use_moments) return 0;
   return (int)plan->corrs[corr]->lay[LAY_MOM].mxi_ids.size();
@@ -2182,6 +2486,7 @@ int vg_stage_batch(vg_plan* plan, int32_t corr, int32_t eval, int32_t stage,
     VG_LAUNCHED();
     return VG_OK;
   }
+  plan->vt_now = false;      // the taps expose the per-point pass
   VG_TRY(run_corr_front(plan, c, B, status_dev, st, stage == 4 ? 99 : stage));
   const int nm = std::max(c.lay[LAY_MOM].n_metal, 1);
   if (stage == 1) {

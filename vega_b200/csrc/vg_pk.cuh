@@ -33,12 +33,12 @@ struct PkGridDev {
   const double* const* grids;  // static grids, each [nmu][nk]
 };
 
-__device__ __forceinline__ double par(const double* p, int idx, double dflt) {
+__host__ __device__ __forceinline__ double par(const double* p, int idx, double dflt) {
   return idx >= 0 ? p[idx] : dflt;
 }
 
 // (bias, beta) of tracer t from any two of (bias, bias_eta, beta): vega/utils.py:45-81
-__device__ __forceinline__ void tracer_bias_beta(const vg_eval_desc& d, const double* p, int t,
+__host__ __device__ __forceinline__ void tracer_bias_beta(const vg_eval_desc& d, const double* p, int t,
                                                  double& bias, double& beta) {
   const double f = par(p, d.idx_growth_rate, DEFAULT_GROWTH_RATE);
   const double eta = par(p, d.idx_bias_eta[t], 0.0);
@@ -49,7 +49,7 @@ __device__ __forceinline__ void tracer_bias_beta(const vg_eval_desc& d, const do
 }
 
 // vega/power_spectrum.py:224-261: scale-dependent bias from UV / HeII fluctuations
-__device__ __forceinline__ void uv_bias_beta(const vg_eval_desc& d, const double* p, double k,
+__host__ __device__ __forceinline__ void uv_bias_beta(const vg_eval_desc& d, const double* p, double k,
                                              double& bias, double& beta) {
   double eff = bias;
   if (d.uvb) {
@@ -167,13 +167,16 @@ struct KaiserCoef {
   double L0;
 };
 
-__device__ __forceinline__ KaiserCoef kaiser_setup(const vg_eval_desc& d, const double* p, double k) {
+// with_uv = false leaves the scale-dependent UV term out (the moment form carries it as a static
+// function of k: vg_moments.cuh)
+__host__ __device__ __forceinline__ KaiserCoef kaiser_setup(const vg_eval_desc& d, const double* p, double k,
+                                                            bool with_uv = true) {
   KaiserCoef c;
 #pragma unroll
   for (int t = 0; t < 2; ++t) {
     double b, beta;
     tracer_bias_beta(d, p, t, b, beta);
-    if (d.uv_on[t] && (d.uvb || d.heii)) uv_bias_beta(d, p, k, b, beta);
+    if (with_uv && d.uv_on[t] && (d.uvb || d.heii)) uv_bias_beta(d, p, k, b, beta);
     c.a0[t] = b;
     c.a1[t] = b * beta;
     c.h0[t] = 0.0;

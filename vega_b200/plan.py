@@ -177,6 +177,10 @@ class PlanBuilder:
                 d.idx_lambda_uv, d.idx_bias_gamma = c('lambda_uv', True), c('bias_gamma', True)
             if d.heii:
                 d.idx_lambda_heii, d.idx_bias_gamma_e = c('lambda_HeII', True), c('bias_gamma_e', True)
+            # none of them sampled: the scale-dependent bias term is a static function of k (moment form)
+            uv_names = ['bias_prim'] + (['lambda_uv', 'bias_gamma'] if d.uvb else []) \
+                + (['lambda_HeII', 'bias_gamma_e'] if d.heii else [])
+            d.uv_static = int(not any(n in self.sampled_set for n in uv_names))
 
         # HCD (power_spectrum.py:53,116-120,263-309)
         hcd = cfg.get('model-hcd', None)
@@ -742,6 +746,13 @@ class PlanBuilder:
             self.keep.append(transform)
         if chunk is not None:
             _lib.check(lib.vg_plan_set_chunk(handle, int(chunk)))
+        if self.sampled:
+            # the box theta lives in ([sample] limits, vega/vega_interface.py:737-790): the velocity-
+            # dispersion tables of the device path are built over it (NaN = no limit = no tables)
+            limits = getattr(vega, 'sample_params', {}).get('limits', {})
+            lo = _f64([np.nan if limits.get(n, (None, None))[0] is None else limits[n][0] for n in self.sampled])
+            hi = _f64([np.nan if limits.get(n, (None, None))[1] is None else limits[n][1] for n in self.sampled])
+            _lib.check(lib.vg_plan_set_theta_limits(handle, _dptr(lo), _dptr(hi)))
 
         if self.need_fvoigt is not None:
             model = self.need_fvoigt
@@ -916,6 +927,17 @@ class DevicePlan:
     def n_moment(self, ci):
         """Evaluations of correlation ci computed in moment form (csrc/vg_moments.cuh)."""
         return self.lib.vg_corr_n_moment(self.handle, ci)
+
+    def velo_tables(self, ci):
+        """(evaluations, Chebyshev orders, error measured at finalize) of the velocity-dispersion
+        tables of correlation ci (csrc/vg_moments.cuh); (0, 0, 0.0) when they are off."""
+        orders, err = C.c_int32(0), C.c_double(0.0)
+        n = self.lib.vg_corr_velo_tables(self.handle, ci, C.byref(orders), C.byref(err))
+        return n, orders.value, err.value
+
+    def velo_tables_active(self):
+        """True when the last batch call ran on the velocity-dispersion tables."""
+        return bool(self.lib.vg_plan_velo_tables_active(self.handle))
 
     def n_static_xi(self, ci):
         """Evaluations of correlation ci whose xi stage is a read-out of static tables."""
