@@ -738,6 +738,9 @@ def main():
                 if s == 'velo_tables':
                     kname = ('vtab_weights_kernel + dgemm_tn_kernel (DMMA): knot tables of the evaluations with a sampled '
                              f'velocity dispersion from their Chebyshev series, orders {[v[1] for v in vt_info if v[0]]}')
+                if s == 'chi2_gemm':
+                    kname = ('dgemm_tn_kernel<ROWDOT> (DMMA), symmetric form: one triangle of C^-1 is read, the executed '
+                             'flops are (1 + 128/N) / 2 of the algorithmic 2 N^2 the figure counts')
                 if s == 'dm_gemm' and any(dm_digits):
                     kname = f'ozaki_gemm_kernel (tcgen05 kind::i8, digits {dm_digits}) + split-K reduction'
                 roofline_kernels.append({'name': s, 'kernel': kname, 'bound': 'tensor',

@@ -82,6 +82,17 @@ struct DevBuf {
   template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+// The quadratic form r^T B r only sees the symmetric part of B; the chi2 GEMM reads one triangle
+// (vg_gemm.cuh, GemmArgs::sym), so an inverse covariance that is symmetric to rounding only
+// (numpy's LU inverse, Q^T C^-1 Q of the marginalisation) is replaced by (B + B^T) / 2 once.
+int symmetrize(DevBuf& buf, int n, long long ld) {
+  dim3 grid((unsigned)((n + 255) / 256), (unsigned)n);
+  vg::symmetrize_kernel<<<grid, 256>>>(buf.as<double>(), n, ld);
+  VG_CUDA_CHECK(cudaGetLastError());
+  VG_CUDA_CHECK(cudaDeviceSynchronize());
+  return VG_OK;
+}
+
 template <class T> int upload(DevBuf& buf, const T* host, size_t n) {
   VG_TRY(buf.alloc(n * sizeof(T)));
   VG_CUDA_CHECK(cudaMemcpy(buf.p, host, n * sizeof(T), cudaMemcpyHostToDevice));
@@ -904,6 +915,7 @@ int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t*
   VG_TRY(upload(c.d_data, data, n_mask));
   if (invcov) {
     VG_TRY(upload_padded(c.d_invcov, invcov, n_mask, n_mask, c.ld_mask));
+    VG_TRY(symmetrize(c.d_invcov, n_mask, c.ld_mask));
     c.has_invcov = true;
   } else {
     c.has_invcov = false;
@@ -916,6 +928,7 @@ int vg_plan_set_global_invcov(vg_plan* plan, int32_t n_total, const double* invc
   plan->drop_graphs();
   plan->n_total = n_total; plan->ld_total = pad16(n_total);
   VG_TRY(upload_padded(plan->d_global_invcov, invcov, n_total, n_total, plan->ld_total));
+  VG_TRY(symmetrize(plan->d_global_invcov, n_total, plan->ld_total));
   plan->has_global = true;
   return VG_OK;
 }
@@ -2087,6 +2100,7 @@ int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* in
   vg::GemmArgs g{};
   g.A = diff; g.B = invcov; g.M = (int)Bc; g.N = n; g.K = ld; g.lda = ld; g.ldb = ld;
   g.batch = 1; g.alpha = 1.0; g.beta = 0.0;
+  g.sym = 1;      // invcov is symmetric (symmetrize() at upload): one triangle is read
   const int n_tiles0 = vg_cdiv(n, vg::GEMM_BN);
   const int bm = vg::gemm_tile_m((int)Bc);
   g.splits = pick_splits((long long)vg_cdiv(Bc, bm) * n_tiles0, ld / vg::GEMM_BK, bm == vg::GEMM_BM ? 1 : 2);

@@ -40,6 +40,11 @@ struct GemmArgs {
   double alpha, beta;
   // ROWDOT: out[m, blockIdx.y*splits + split] = sum_n acc[m,n] * D[m,n]   (C = out, ldc = n_tiles*splits)
   const double* D; long long ldd;
+  // ROWDOT with A = D and B a SYMMETRIC N x N matrix (the quadratic form r^T B r): sym = 1 makes the
+  // column tile [n0, n0 + 128) read only k >= n0 -- its diagonal block once, everything to the right
+  // of it twice -- so half of B is streamed and half of the DMMAs are issued; the splits of a tile
+  // divide that tile's own k range
+  int sym;
 };
 
 // shared-memory operands are addressed by their 32-bit shared-window offsets, computed once
@@ -87,10 +92,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
   const int bz = blockIdx.z / g.splits, sp = blockIdx.z % g.splits;
 
   const int ktiles_total = (g.K + BK - 1) / BK;
-  const int kt_per = (ktiles_total + g.splits - 1) / g.splits;
-  const int kt_begin = sp * kt_per;
+  const bool sym = EPI == GEMM_ROWDOT && g.sym != 0;
+  const int kt_lo = sym ? n0 / BK : 0;                       // (n0 is a multiple of 128, BK of 16 or 32)
+  const int kt_per = (ktiles_total - kt_lo + g.splits - 1) / g.splits;
+  const int kt_begin = kt_lo + sp * kt_per;
   const int kt_end = min(ktiles_total, kt_begin + kt_per);
   const int nkt = max(0, kt_end - kt_begin);
+  const int kt_diag_end = kt_lo + GEMM_BN / BK;              // sym: first k tile right of the diagonal block
 
   const double* A = g.A + (long long)bz * g.strideA;
   const double* B = g.B + (long long)bz * g.strideB;
@@ -149,6 +157,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
   const unsigned bs_frag = bs_base + ((wn * NJ * 8 + frow) * GEMM_LDS + fcol) * 8;
   int cur = 0, nxt = GEMM_STAGES - 1;      // stage consumed / stage refilled at this iteration
   for (int kt = 0; kt < nkt; ++kt) {
+    if (sym && kt > 0 && kt_begin + kt == kt_diag_end) {
+      // leaving the diagonal block: what follows counts twice, i.e. what came before counts half
+      // (the epilogue doubles the sum; both scalings are exact)
+#pragma unroll
+      for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < NJ; ++j) { acc[i][j][0] *= 0.5; acc[i][j][1] *= 0.5; }
+    }
     cp_async_wait<GEMM_STAGES - 2>();
     __syncthreads();
     // tile kt+STAGES-1 goes into the slot freed at iteration kt-1; its cp.async are issued
@@ -250,10 +266,20 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
           s += (red[tid * WARPS_N + w] + red[tid * WARPS_N + w + 1]) +
                (red[tid * WARPS_N + w + 2] + red[tid * WARPS_N + w + 3]);
         // linear in the K range: each split contributes its own partial column
+        if (sym && kt_end > kt_diag_end) s *= 2.0;
         g.C[(long long)bz * g.strideC + (long long)m * g.ldc + blockIdx.y * g.splits + sp] = g.alpha * s;
       }
     }
   }
+}
+
+// A <- (A + A^T) / 2 on the leading n x n block of A[n][ld], in place (each pair i < j belongs to one thread)
+__global__ void symmetrize_kernel(double* __restrict__ A, int n, long long ld) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+  if (j >= n || j <= i) return;
+  const double v = 0.5 * (A[(long long)i * ld + j] + A[(long long)j * ld + i]);
+  A[(long long)i * ld + j] = v;
+  A[(long long)j * ld + i] = v;
 }
 
 // sums `splits` partial slices: C[i] = sum_s W[s*stride + i] (fixed order => deterministic)
