@@ -1232,13 +1232,13 @@ int ozaki_slice(OzakiOperand& op, const double* src, long long ld, long long row
   }
 }
 
-// 3-D tensor map over the digit planes: (k, row, digit), box (OZ_BK, box_rows, S), OZ_BK-byte swizzle
-int ozaki_map(CUtensorMap* map, const OzakiOperand& op, int box_rows) {
+// 3-D tensor map over the digit planes: (k, row, digit), box (OZ_BK, box_rows, box_planes), OZ_BK-byte swizzle
+int ozaki_map(CUtensorMap* map, const OzakiOperand& op, int box_rows, int box_planes) {
   EncodeTiledFn fn = encode_tiled_fn();
   VG_REQUIRE(fn, "cuTensorMapEncodeTiled is not available from this driver");
   const cuuint64_t gdim[3] = {(cuuint64_t)op.Kp, (cuuint64_t)op.rows, (cuuint64_t)op.S};
   const cuuint64_t gstride[2] = {(cuuint64_t)op.Kp, (cuuint64_t)op.rows * (cuuint64_t)op.Kp};
-  const cuuint32_t box[3] = {(cuuint32_t)vg::OZ_BK, (cuuint32_t)box_rows, (cuuint32_t)op.S};
+  const cuuint32_t box[3] = {(cuuint32_t)vg::OZ_BK, (cuuint32_t)box_rows, (cuuint32_t)box_planes};
   const cuuint32_t estride[3] = {1, 1, 1};
   const CUresult rc = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, op.planes.p, gdim, gstride, box, estride,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, vg::OZ_BK == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B,
@@ -1248,17 +1248,46 @@ int ozaki_map(CUtensorMap* map, const OzakiOperand& op, int box_rows) {
   return VG_OK;
 }
 
-template <int S>
-int ozaki_gemm_launch(const CUtensorMap& ma, const CUtensorMap& mb, const vg::OzakiArgs& g, dim3 grid, cudaStream_t st) {
+// CTAs per cluster of the split-integer GEMM (1, 2 or 4; VG_OZ_CLUSTER in the environment): the CTAs
+// of a cluster share the batch operand's tile through multicast loads (vg_ozaki.cuh)
+int ozaki_cluster() {
+  static const int cl = [] {
+    const char* e = std::getenv("VG_OZ_CLUSTER");
+    const int v = e ? std::atoi(e) : 2;
+    return (v == 1 || v == 2 || v == 4) ? v : 2;
+  }();
+  return cl;
+}
+
+template <int S, int CL>
+int ozaki_gemm_launch_cl(const CUtensorMap& ma, const CUtensorMap& ma_rest, const CUtensorMap& mb, const vg::OzakiArgs& g,
+                         dim3 grid, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::ozaki_gemm_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    VG_CUDA_CHECK(cudaFuncSetAttribute(vg::ozaki_gemm_kernel<S, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        vg::OzakiSmem<S>::BYTES));
     attr_set = true;
   }
-  vg::ozaki_gemm_kernel<S><<<grid, vg::OZ_THREADS, vg::OzakiSmem<S>::BYTES, st>>>(ma, mb, g);
+  if (CL == 1) {
+    vg::ozaki_gemm_kernel<S, CL><<<grid, vg::OZ_THREADS, vg::OzakiSmem<S>::BYTES, st>>>(ma, ma_rest, mb, g);
+  } else {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = dim3(vg::OZ_THREADS); cfg.dynamicSmemBytes = vg::OzakiSmem<S>::BYTES; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = CL; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    VG_CUDA_CHECK(cudaLaunchKernelEx(&cfg, vg::ozaki_gemm_kernel<S, CL>, ma, ma_rest, mb, g));
+  }
   VG_LAUNCHED();
   return VG_OK;
+}
+template <int S>
+int ozaki_gemm_launch(int cl, const CUtensorMap& ma, const CUtensorMap& ma_rest, const CUtensorMap& mb,
+                      const vg::OzakiArgs& g, dim3 grid, cudaStream_t st) {
+  if (cl == 4) return ozaki_gemm_launch_cl<S, 4>(ma, ma_rest, mb, g, grid, st);
+  if (cl == 2) return ozaki_gemm_launch_cl<S, 2>(ma, ma_rest, mb, g, grid, st);
+  return ozaki_gemm_launch_cl<S, 1>(ma, ma_rest, mb, g, grid, st);
 }
 
 // C[M][ldc] = A B^T from the digit planes of A ([>= M rows]) and B ([N rows]); deterministic split-K
@@ -1267,13 +1296,18 @@ int ozaki_gemm(const OzakiOperand& A, long long M, const OzakiOperand& B, int N,
   VG_REQUIRE(A.S == B.S && A.Kp == B.Kp && A.S >= 3, "ozaki_gemm: operands with different digit planes");
   const int S = A.S;
   if (!error_flag.p) VG_TRY(error_flag.alloc(sizeof(int)));
-  CUtensorMap ma, mb;
-  VG_TRY(ozaki_map(&ma, A, vg::OZ_BM));
-  VG_TRY(ozaki_map(&mb, B, vg::OZ_BN));
+  const int tiles_n = vg_cdiv(N, vg::OZ_BN);
+  const int cl = std::min(ozaki_cluster(), tiles_n >= 4 ? 4 : (tiles_n >= 2 ? 2 : 1));
+  const int a_per = (S + cl - 1) / cl, a_rest = S % a_per;      // planes per CTA of a cluster; the last share
+  CUtensorMap ma, ma_rest, mb;
+  VG_TRY(ozaki_map(&ma, A, vg::OZ_BM, a_per));
+  VG_TRY(ozaki_map(&ma_rest, A, vg::OZ_BM, a_rest > 0 ? a_rest : a_per));
+  VG_TRY(ozaki_map(&mb, B, vg::OZ_BN, S));
   vg::OzakiArgs g{};
   g.M = (int)M; g.N = N; g.S = S;
   g.kb_total = vg_cdiv(A.Kp, vg::OZ_BK);
-  const long long tiles = (long long)vg_cdiv(M, vg::OZ_BM) * vg_cdiv(N, vg::OZ_BN);
+  const int grid_y = vg_cdiv(tiles_n, cl) * cl;
+  const long long tiles = (long long)vg_cdiv(M, vg::OZ_BM) * grid_y;
   // an s32 accumulator takes S products of |q q'| <= 2^12 per k: K blocks per split are bounded
   const int kb_cap = (int)(((1LL << 31) - 1) / (4096LL * vg::OZ_BK * S));
   int splits = vg_cdiv(g.kb_total, kb_cap);
@@ -1300,15 +1334,15 @@ int ozaki_gemm(const OzakiOperand& A, long long M, const OzakiOperand& B, int N,
   } else {
     g.C = C; g.split_stride = 0;
   }
-  dim3 grid(vg_cdiv(M, vg::OZ_BM), vg_cdiv(N, vg::OZ_BN), splits);
+  dim3 grid(vg_cdiv(M, vg::OZ_BM), grid_y, splits);
   int rc;
   switch (S) {
-    case 3: rc = ozaki_gemm_launch<3>(ma, mb, g, grid, st); break;
-    case 4: rc = ozaki_gemm_launch<4>(ma, mb, g, grid, st); break;
-    case 5: rc = ozaki_gemm_launch<5>(ma, mb, g, grid, st); break;
-    case 6: rc = ozaki_gemm_launch<6>(ma, mb, g, grid, st); break;
-    case 7: rc = ozaki_gemm_launch<7>(ma, mb, g, grid, st); break;
-    default: rc = ozaki_gemm_launch<8>(ma, mb, g, grid, st); break;
+    case 3: rc = ozaki_gemm_launch<3>(cl, ma, ma_rest, mb, g, grid, st); break;
+    case 4: rc = ozaki_gemm_launch<4>(cl, ma, ma_rest, mb, g, grid, st); break;
+    case 5: rc = ozaki_gemm_launch<5>(cl, ma, ma_rest, mb, g, grid, st); break;
+    case 6: rc = ozaki_gemm_launch<6>(cl, ma, ma_rest, mb, g, grid, st); break;
+    case 7: rc = ozaki_gemm_launch<7>(cl, ma, ma_rest, mb, g, grid, st); break;
+    default: rc = ozaki_gemm_launch<8>(cl, ma, ma_rest, mb, g, grid, st); break;
   }
   VG_TRY(rc);
   if (splits > 1) {

@@ -178,6 +178,24 @@ __device__ __forceinline__ void oz_tma_load_3d(unsigned dst, const CUtensorMap* 
       "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];\n"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
+// the same load delivered to the same shared-memory offset (and signalled on the barrier at the same
+// offset) of every CTA of the cluster whose bit is set in `mask`
+__device__ __forceinline__ void oz_tma_load_3d_mc(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1,
+                                                  int c2, unsigned short mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4, %5}], [%2], %6;\n"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "h"(mask) : "memory");
+}
+__device__ __forceinline__ unsigned oz_cluster_rank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void oz_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;\n" ::: "memory");
+}
 __device__ __forceinline__ void oz_tmem_alloc(unsigned slot_smem, unsigned cols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(slot_smem), "r"(cols));
   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n");
@@ -198,6 +216,11 @@ __device__ __forceinline__ void oz_mma_i8(unsigned tmem_d, unsigned long long ad
 // arrives on the mbarrier when every tcgen05.mma issued so far by this thread has completed
 __device__ __forceinline__ void oz_mma_commit(unsigned bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+// ... and on the barrier at the same offset in every CTA of the cluster in `mask`
+__device__ __forceinline__ void oz_mma_commit_mc(unsigned bar, unsigned short mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+               ::"r"(bar), "h"(mask) : "memory");
 }
 __device__ __forceinline__ void oz_tmem_ld16(unsigned taddr, unsigned (&r)[16]) {
   asm volatile(
@@ -245,9 +268,18 @@ template <int S> struct OzakiSmem {
   static constexpr int BYTES = STAGES * STAGE + 1024 /* alignment slack */ + 256 /* barriers */;
 };
 
-template <int S>
+// CL > 1: clusters of CL CTAs along the column tiles (grid.y, a multiple of CL) work on the SAME row
+// tile and K range, so they need the same A stage: each CTA fetches a share of its digit planes
+// (ceil(S / CL) of them, the last one the rest: map_a / map_a_rest differ by the planes per box) and
+// the load is multicast to every CTA of the cluster -- the batch operand's planes cross the L2 ->
+// shared-memory path once per CL column tiles instead of once per tile (the kernel was bound there:
+// 7 TB/s of L2 reads at 54-70 % tensor-pipe activity, profiles/r02_ncu_full_c2_raw.csv).  A stage is
+// free again when the MMAs of ALL CL CTAs have read it: every CTA's commit arrives on the empty
+// barrier of every CTA.
+template <int S, int CL>
 __global__ void __launch_bounds__(OZ_THREADS, 1)
-ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, OzakiArgs g) {
+ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_a_rest,
+                  const __grid_constant__ CUtensorMap map_b, OzakiArgs g) {
   using L = OzakiSmem<S>;
   extern __shared__ uint8_t oz_raw[];
   const unsigned raw = oz_smem_u32(oz_raw);
@@ -267,18 +299,27 @@ ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   const int kb0 = split * g.kb_per_split;
   const int nkb = min(g.kb_total, kb0 + g.kb_per_split) - kb0;
 
+  // this CTA's share of the A planes (CL > 1)
+  constexpr int A_PER = (S + CL - 1) / CL;
+  const int crank = CL > 1 ? (int)oz_cluster_rank() : 0;
+  const int a_p0 = crank * A_PER;
+  const int a_cnt = min(A_PER, S - a_p0);           // <= 0: nothing to fetch
+  constexpr unsigned short CL_MASK = (unsigned short)((1u << CL) - 1u);
+
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];\n" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];\n" ::"l"(&map_a_rest) : "memory");
     asm volatile("prefetch.tensormap [%0];\n" ::"l"(&map_b) : "memory");
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < L::STAGES; ++s) { oz_mbar_init(full_bar(s), 1); oz_mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < L::STAGES; ++s) { oz_mbar_init(full_bar(s), 1); oz_mbar_init(empty_bar(s), CL); }
     oz_mbar_init(tfull_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   if (warp == 2) oz_tmem_alloc(oz_smem_u32(tmem_slot), OZ_TMEM_COLS);
   oz_fence_before();
   __syncthreads();
+  if (CL > 1) oz_cluster_sync();      // every CTA's barriers exist before a peer signals them
   oz_fence_after();
   const unsigned tmem_base = *tmem_slot;
 
@@ -290,7 +331,12 @@ ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
       if (!oz_mbar_wait(empty_bar(s), ph ^ 1u, g.error_flag)) break;
       oz_mbar_expect_tx(full_bar(s), (unsigned)L::STAGE);
       const unsigned dst = base + s * L::STAGE;
-      oz_tma_load_3d(dst, &map_a, full_bar(s), (kb0 + i) * OZ_BK, tile_m * OZ_BM, 0);
+      if (CL == 1) {
+        oz_tma_load_3d(dst, &map_a, full_bar(s), (kb0 + i) * OZ_BK, tile_m * OZ_BM, 0);
+      } else if (a_cnt > 0) {
+        oz_tma_load_3d_mc(dst + a_p0 * (OZ_BM * OZ_BK), a_cnt == A_PER ? &map_a : &map_a_rest, full_bar(s),
+                          (kb0 + i) * OZ_BK, tile_m * OZ_BM, a_p0, CL_MASK);
+      }
       oz_tma_load_3d(dst + L::A_STAGE, &map_b, full_bar(s), (kb0 + i) * OZ_BK, tile_n * OZ_BN, 0);
     }
   } else if (warp == 1 && lane == 0) {
@@ -321,7 +367,9 @@ ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
                       oz_instr_desc((m - m0) * OZ_BN), acc);
         }
       }
-      oz_mma_commit(empty_bar(s));          // frees the stage when its MMAs have read it
+      // frees the stage when its MMAs have read it (CL > 1: in every CTA that multicasts into it)
+      if (CL == 1) oz_mma_commit(empty_bar(s));
+      else oz_mma_commit_mc(empty_bar(s), CL_MASK);
     }
     oz_mma_commit(tfull_bar);               // accumulators complete
   } else if (warp >= 4) {
@@ -361,6 +409,7 @@ ozaki_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   }
   oz_fence_before();
   __syncthreads();
+  if (CL > 1) oz_cluster_sync();      // no CTA leaves while a peer may still write to it or signal it
   if (warp == 2) oz_tmem_dealloc(tmem_base, OZ_TMEM_COLS);
 }
 
