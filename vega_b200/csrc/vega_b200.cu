@@ -1311,16 +1311,22 @@ int ozaki_gemm(const OzakiOperand& A, long long M, const OzakiOperand& B, int N,
   // an s32 accumulator takes S products of |q q'| <= 2^12 per k: K blocks per split are bounded
   const int kb_cap = (int)(((1LL << 31) - 1) / (4096LL * vg::OZ_BK * S));
   int splits = vg_cdiv(g.kb_total, kb_cap);
-  {   // fill whole waves of the 148 SMs (one CTA each), >= 512 bytes of K per split
-    double best = -1.0;
+  {   // Split count by a cost model in units of one K block of one CTA (~1.8 us): waves of the 148 SMs
+      // (one CTA each) x (the K blocks of a split + a CTA's fixed cost: TMEM allocation, pipeline fill,
+      // the epilogue over S accumulators) + the partial sums written and read back by the reduction.
+      // Long K (the metal matrices: 589 blocks) still takes the split that fills the last wave; short K
+      // (the distortion matrix: 40-79 blocks) no longer pays 7 short CTAs and a reduction for it
+    double best = 1e300;
     const int lo = splits, hi = std::max(lo, std::min(64, g.kb_total / (512 / vg::OZ_BK)));
+    const double cta_fixed = 2.5;
+    const double reduce_per_split = 2.0 * (double)M * (double)ldc * 8.0 / 6.0e12 / 1.8e-6;
     for (int sp = lo; sp <= hi; ++sp) {
       const int per = vg_cdiv(g.kb_total, sp);
       if ((long long)per * (sp - 1) >= g.kb_total) continue;      // an empty last split
       const long long ctas = tiles * sp;
       const long long waves = (ctas + NUM_SMS - 1) / NUM_SMS;
-      const double eff = (double)ctas / (double)(waves * NUM_SMS) - 0.003 * (sp - 1);
-      if (eff > best + 1e-9) { best = eff; splits = sp; }
+      const double cost = (double)waves * (cta_fixed + per) + (sp > 1 ? sp * reduce_per_split : 0.0);
+      if (cost < best - 1e-9) { best = cost; splits = sp; }
     }
   }
   g.kb_per_split = vg_cdiv(g.kb_total, splits);
