@@ -1199,7 +1199,7 @@ EncodeTiledFn encode_tiled_fn() {
 template <int S>
 int ozaki_slice_launch(const double* src, long long ld, int K, int Kp, long long rows, const int* exps,
                        int8_t* planes, long long plane_stride, cudaStream_t st) {
-  const long long n = rows * (Kp / 16);
+  const long long n = rows * (Kp / 4);
   vg::ozaki_slice_kernel<S><<<vg_cdiv(n, 256), 256, 0, st>>>(src, ld, K, Kp, rows, exps, planes, plane_stride);
   VG_LAUNCHED();
   return VG_OK;
