@@ -730,8 +730,8 @@ class MonteCarloFits:
 
         method 'quasi': gradient stencils on the way down and one Hessian stencil per mock to finish
         (quasi_newton_lockstep); with `share_hessian` the BFGS iteration of EVERY mock starts from
-        the Hessian of the first mock at the start point -- the mocks share the model and the
-        covariance, so their Hessians agree to the noise in the data.  'newton': a Hessian stencil
+        the mean Hessian of the first (up to 8) mocks at the start point -- the mocks share the model
+        and the covariance, so their Hessians agree to the noise in the data.  'newton': a Hessian stencil
         per mock per iteration."""
         if self.mocks is None:
             raise RuntimeError('draw() the mocks first.')
@@ -763,13 +763,19 @@ class MonteCarloFits:
             # bias / beta / HCD degeneracies and are rejected).  A finite-difference Hessian away
             # from the minimum can be indefinite along those directions: quasi_newton_lockstep
             # lifts its eigenvalues (_positive_definite) before use.
-            ls = _Lockstep(lambda theta, prob: self.chi2(theta, ids[prob]), start[None, :], errors, lower, upper,
-                           ~fixed, 0.02)
-            h = 0.02 * ls.scale[:1]
-            f0, g, hess0 = ls.evaluate(np.array([0]), ls.clip(start[None, ~fixed], h), h, True)
+            # ... taken as the MEAN over the first few mocks: one mock's finite-difference Hessian carries
+            # that mock's noise (second derivatives of the model times its residual), and a rank whose
+            # first mock is an outlier would hand a poor quadratic model to all of its fits (seen at
+            # N = 2: one rank needed 3.4x the evaluations of the other)
+            n_h = int(min(8, ids.size))
+            ls = _Lockstep(lambda theta, prob: self.chi2(theta, ids[prob]), np.tile(start, (n_h, 1)), errors, lower,
+                           upper, ~fixed, 0.02)
+            h = 0.02 * ls.scale
+            f0, g, hess0 = ls.evaluate(np.arange(n_h), ls.clip(np.tile(start[~fixed], (n_h, 1)), h), h, True)
             n_extra = ls.n_eval
-            if np.all(np.isfinite(hess0)):
-                kwargs['hess0'] = hess0[0]
+            ok = np.all(np.isfinite(hess0.reshape(n_h, -1)), axis=1)
+            if ok.any():
+                kwargs['hess0'] = hess0[ok].mean(axis=0)
         if method == 'quasi':
             res = quasi_newton_lockstep(evaluate, np.tile(start, (ids.size, 1)), errors, lower, upper, free=~fixed,
                                         max_iter=max_iter, edm_tol=edm_tol, verbose=verbose, **kwargs)
