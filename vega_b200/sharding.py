@@ -5,9 +5,9 @@ point, iminuit stencil point, Monte Carlo mock) is independent, exactly as in th
 reference's rank-per-replica MPI scripts (bin/run_vega_mpi.py:24-52,
 bin/run_vega_mc_fits_mpi.py:81-159, which split mocks with ``range(rank, n, size)`` and
 never communicate).  Here every rank holds a replica of the device plan, takes a
-contiguous shard of the batch, and the only collective is ONE all-gather of the
-per-vector chi2 (8 bytes per vector) and status words -- NCCL over NVLink on the GPU box,
-gloo in the CPU tests of the host logic.
+contiguous shard of the batch, and the only collective is ONE all-gather of 16 bytes per
+vector (chi2 and its status word side by side in one send buffer, which the chi2 kernels write
+into directly) -- NCCL over NVLink on the GPU box, gloo in the CPU tests of the host logic.
 
 The evaluator is the device engine (``VegaInterface.chi2_device`` path); the host-side
 partition / gather arithmetic is separated from it so that it can be exercised with
@@ -35,13 +35,16 @@ class ShardedChi2:
     """chi2 of a global batch theta[B, P], evaluated shard-per-rank and all-gathered.
 
     evaluate(theta_local: torch.Tensor[b, P]) -> (chi2[b] float64, status[b] int32) tensors
-    on `device`.  `group` is a torch.distributed process group (None = default)."""
+    on `device`; with `writes_into` it is called as evaluate(theta_local, chi2_out) and leaves the
+    chi2 values in chi2_out (a slice of the send buffer of the collective: no staging copy).
+    `group` is a torch.distributed process group (None = default)."""
 
-    def __init__(self, evaluate, device, group=None):
+    def __init__(self, evaluate, device, group=None, writes_into=False):
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
         self.evaluate = evaluate
+        self.writes_into = writes_into
         self.device = torch.device(device)
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -56,28 +59,29 @@ class ShardedChi2:
             from ._lib import VegaDeviceError
             raise VegaDeviceError('ShardedChi2 needs a CUDA device: the B200 path has no CPU evaluator.')
         engine = vega._engine_for(tuple(names))
-        return cls(lambda t: engine.chi2_device(t), engine.device, group)
+        return cls(lambda t, out=None: engine.chi2_device(t, out), engine.device, group, writes_into=True)
 
     def _buffers(self, cap):
+        """(gathered [world, 2, cap], send [2, cap]) float64: row 0 chi2, row 1 the status word (small
+        integers are exact in a double), so ONE collective moves both."""
         torch = self.torch
-        if self._gather_buf is None or self._gather_buf[0].shape[1] < cap:
-            self._gather_buf = (
-                torch.empty(self.world, cap, dtype=torch.float64, device=self.device),
-                torch.empty(self.world, cap, dtype=torch.int32, device=self.device),
-                torch.zeros(cap, dtype=torch.float64, device=self.device),
-                torch.zeros(cap, dtype=torch.int32, device=self.device))
+        if self._gather_buf is None or self._gather_buf[1].shape[1] < cap:
+            self._gather_buf = (torch.empty(self.world, 2, cap, dtype=torch.float64, device=self.device),
+                                torch.zeros(2, cap, dtype=torch.float64, device=self.device))
         return self._gather_buf
 
     def local_shard(self, theta):
         lo, hi = shard_bounds(theta.shape[0], self.world, self.rank)
         return theta[lo:hi]
 
-    def chi2_local(self, theta_local):
+    def chi2_local(self, theta_local, chi2_out=None):
         """(chi2, status) device tensors of this rank's shard (already on the device)."""
         torch = self.torch
         if theta_local.shape[0] == 0:
             return (torch.empty(0, dtype=torch.float64, device=self.device),
                     torch.empty(0, dtype=torch.int32, device=self.device))
+        if chi2_out is not None and self.writes_into:
+            return self.evaluate(theta_local, chi2_out)
         return self.evaluate(theta_local)
 
     def gather(self, chi2_local, status_local, n_total):
@@ -88,18 +92,23 @@ class ShardedChi2:
             return chi2_local, status_local
         sizes = shard_sizes(n_total, self.world)
         cap = max(max(sizes), 1)
-        g_chi2, g_stat, s_chi2, s_stat = self._buffers(cap)
-        cap = g_chi2.shape[1]
+        gathered, send = self._buffers(cap)
+        cap = send.shape[1]
         n = chi2_local.shape[0]
-        s_chi2[:n].copy_(chi2_local)
-        s_stat[:n].copy_(status_local)
-        dist.all_gather_into_tensor(g_chi2.view(-1), s_chi2, group=self.group)
-        dist.all_gather_into_tensor(g_stat.view(-1), s_stat, group=self.group)
-        if all(s == cap for s in sizes):
-            return g_chi2.view(-1)[:n_total].clone(), g_stat.view(-1)[:n_total].clone()
-        chi2 = torch.cat([g_chi2[r, :s] for r, s in enumerate(sizes)])
-        stat = torch.cat([g_stat[r, :s] for r, s in enumerate(sizes)])
+        if n and chi2_local.data_ptr() != send[0].data_ptr():     # (already there when evaluate wrote into it)
+            send[0, :n].copy_(chi2_local)
+        send[1, :n].copy_(status_local)
+        dist.all_gather_into_tensor(gathered.view(-1), send.view(-1), group=self.group)
+        chi2 = torch.cat([gathered[r, 0, :s] for r, s in enumerate(sizes)])
+        stat = torch.cat([gathered[r, 1, :s] for r, s in enumerate(sizes)]).to(torch.int32)
         return chi2, stat
+
+    def send_slot(self, n_local, n_total):
+        """The slice of the send buffer an evaluator can write this rank's n_local chi2 values into."""
+        if self.world == 1 or n_local == 0:
+            return None
+        cap = max(max(shard_sizes(n_total, self.world)), 1)
+        return self._buffers(cap)[1][0, :n_local]
 
     def chi2(self, theta):
         """theta: the GLOBAL batch (host ndarray or tensor, identical on every rank, e.g. the
@@ -111,7 +120,7 @@ class ShardedChi2:
             theta = torch.from_numpy(np.ascontiguousarray(np.atleast_2d(theta), dtype=np.float64))
         n_total = theta.shape[0]
         local = self.local_shard(theta).contiguous().to(self.device)
-        c, s = self.chi2_local(local)
+        c, s = self.chi2_local(local, self.send_slot(local.shape[0], n_total))
         c, s = self.gather(c, s, n_total)
         c = c.cpu().numpy().copy()
         s = s.cpu().numpy()
