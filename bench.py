@@ -622,14 +622,19 @@ def main():
 
     # ---- comparison legs, not the headline ----
     digits = [engine.ozaki_slices(ci)[0] for ci in range(len(engine.infos))]
+    fused = [engine.fused_metal_operator(ci) for ci in range(len(engine.infos))]
     dm_digits = [engine.ozaki_dm_slices(ci)[0] for ci in range(len(engine.infos))]
     chi2_ref = chi2_t.clone()
-    engine.set_option(_lib.OPT_OZAKI, 0)            # metal matrices on the FP64 DMMA kernel
+    engine.set_option(_lib.OPT_OZAKI, 0)            # metal matrices on the FP64 DMMA kernel ...
+    engine.set_option(_lib.OPT_FUSE_DM_METALS, 0)   # ... applied before the distortion matrix, as the reference does
     for _ in range(3):
         step_device()
     dmma_diff = float(((chi2_t - chi2_ref).abs() / chi2_ref.abs().clamp_min(1.0)).max().item())
     dmma_ms = timed_device(torch, dd, step_device, args.steps)
     engine.set_option(_lib.OPT_OZAKI, -1)
+    engine.set_option(_lib.OPT_FUSE_DM_METALS, 1)
+    if not dmma_diff <= 1e-10:      # the headline against its own FP64 two-step form, in every run
+        raise SystemExit(f'bench: the headline path differs from the FP64 DMMA two-step path by {dmma_diff:.3e} (relative chi2)')
     n_folded = sum(engine.n_folded(ci) for ci in range(len(engine.infos)))
     engine.set_option(_lib.OPT_FOLD_METALS, 1)      # metal terms with a static xi stage from M_c X_m vectors
     for _ in range(3):
@@ -701,7 +706,10 @@ def main():
                 nm = info['item'].model_coordinates.r_grid.size
                 n_metal = sum(1 for d in info['evals'] if d.out_slot >= 2 and not d.frozen and not d.direct)
                 k = n_metal * ((nm + 15) // 16 * 16)
-                ops += S * (S + 1) / 2 * 2.0 * (-(-B // 128) * 128) * (-(-nm // 64) * 64) * (-(-k // 64) * 64)
+                rows, S_fused = fused[ci]          # chi2 path: (D_masked M_c) has n_mask rows, its own digits
+                n_out = rows if rows else nm
+                S = S_fused if rows else S
+                ops += S * (S + 1) / 2 * 2.0 * (-(-B // 128) * 128) * (-(-n_out // 128) * 128) * (-(-k // 64) * 64)
             int8_peak = 2.0 * peaks['bf16_tflops']
             tops = ops / (metal_ms * 1e-3) / 1e12
             main_roofline = {
@@ -788,6 +796,7 @@ def main():
                        'evaluations_with_static_xi_stage': sum(engine.n_static_xi(ci)
                                                                for ci in range(len(engine.infos))),
                        'metal_gemm_digits': digits, 'distortion_gemm_digits': dm_digits,
+                       'fused_distortion_metal_operator': [{'rows': r, 'digits': s} for r, s in fused],
                        'l2': 'inputs larger than L2: ~2.9 GB of static operands + ~2 GB of workspace '
                              'streamed per step'},
             'clocks': clock_info,
@@ -806,8 +815,10 @@ def main():
                                    'nominal: 296 TFLOP/s FP64 per 8-GPU HGX B200'},
             'kernels': kernels,
             'init_s': init,
-            'with_dmma_metals': {'note': 'VG_OPT_OZAKI = 0: the dense metal matrices and the distortion matrix on the FP64 '
-                                         'DMMA kernel (the parity reference of the split-integer GEMM)', 'ms_per_step': dmma_ms,
+            'with_dmma_metals': {'note': 'VG_OPT_OZAKI = 0, VG_OPT_FUSE_DM_METALS = 0: the dense metal matrices, then the '
+                                         'distortion matrix, both on the FP64 DMMA kernel (the parity reference of the '
+                                         'split-integer GEMM and of the fused distortion x metal operator; the run fails '
+                                         'when the headline differs from it by more than 1e-10)', 'ms_per_step': dmma_ms,
                                  'value': world * B / (dmma_ms * 1e-3), 'unit': 'evals/s',
                                  'max_rel_chi2_difference_to_headline': dmma_diff},
             'with_folded_metals': {'note': 'not the headline: VG_OPT_FOLD_METALS = 1, the metal terms with a '

@@ -296,6 +296,13 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
  * 4-byte read-back for device theta); anything else, and 0, keeps the per-point pass (the parity
  * reference of the tables). */
 #define VG_OPT_VELO_TABLES 5
+/* VG_OPT_FUSE_DM_METALS (default 1): on the chi2 path the metal matrices are applied as the plan-time
+ * product (masked rows of the distortion matrix) x M_c -- D (M_c xi_c) = (D M_c) xi_c,
+ * vega/model.py:142-143 with vega/metals.py:350-358 -- so the per-vector product has n_mask output
+ * bins instead of n_model and the distortion product keeps the core terms only.  Needs dense metal
+ * matrices, a distortion matrix and no multiplicative pre-distortion broadband term; the model entry
+ * points (all distorted bins) keep the two products.  0: the two-step form (its parity reference). */
+#define VG_OPT_FUSE_DM_METALS 6
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
 /* Isotropic P(k) [nk] for the direct mode (e.g. from a Boltzmann code, the `direct_pk`
  * argument of VegaInterface.compute_model / chi2 / log_lik); host pointer, copied. */
@@ -322,6 +329,10 @@ int vg_corr_n_folded(const vg_plan* plan, int32_t corr);
 int vg_corr_ozaki_slices(const vg_plan* plan, int32_t corr, double* bound_per_digits);
 /* The same for the distortion-matrix product (bound relative to max|D xi|; 0: DMMA) */
 int vg_corr_ozaki_dm_slices(const vg_plan* plan, int32_t corr, double* bound_per_digits);
+/* The fused distortion x metal operator of a correlation (VG_OPT_FUSE_DM_METALS): returns its rows
+ * (n_mask; 0 when it was not built or the option is off), digits (nullable): digits of the split-integer
+ * GEMM on it (0: DMMA), bound_per_digits[9] (nullable): truncation bound relative to max|D xi|. */
+int vg_corr_fused_metal_operator(const vg_plan* plan, int32_t corr, int32_t* digits, double* bound_per_digits);
 /* Status bits raised while building the static grids (e.g. VG_STATUS_ARINYO): they apply
  * to every vector */
 int vg_plan_static_status(const vg_plan* plan);

@@ -13,7 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / 'libvega_b200.so'
 VG_MAX_BB_TERMS = 8
 F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP, F_MOCKGK = (1 << i for i in range(9))
 STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE, STATUS_DEVICE = 1, 2, 4, 8
-OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS, OPT_OZAKI, OPT_OZAKI_DM, OPT_VELO_TABLES = 0, 1, 2, 3, 4, 5
+OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS, OPT_OZAKI, OPT_OZAKI_DM, OPT_VELO_TABLES, OPT_FUSE_DM_METALS = 0, 1, 2, 3, 4, 5, 6
 ERR_CUDA, ERR_ARG, ERR_STATE = 1, 2, 3
 STATIC_SCRATCH_DOUBLES = 1 << 21      # VG_STATIC_SCRATCH_DOUBLES of include/vega_b200.h
 
@@ -91,6 +91,7 @@ _SIGNATURES = {
     'vg_corr_velo_tables': (C.c_int, [_PTR, i32, C.POINTER(i32), C.POINTER(f64)]),
     'vg_plan_set_theta_limits': (C.c_int, [_PTR, _PTR, _PTR]),
     'vg_plan_velo_tables_active': (C.c_int, [_PTR]),
+    'vg_corr_fused_metal_operator': (C.c_int, [_PTR, i32, C.POINTER(i32), _PTR]),
     'vg_corr_ozaki_slices': (C.c_int, [_PTR, i32, _PTR]),
     'vg_corr_ozaki_dm_slices': (C.c_int, [_PTR, i32, _PTR]),
     'vg_corr_n_folded': (C.c_int, [_PTR, i32]),

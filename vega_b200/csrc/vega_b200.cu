@@ -219,6 +219,13 @@ struct Corr {
   OzakiOperand oz_dmat, oz_dmat_masked;  // digit planes of d_dmat / d_dmat_masked (built on first use)
   int oz_dm_slices = 0;          // digits of the distortion product that meet the budget (0: DMMA)
   double oz_dm_bound[vg::OZ_MAX_S + 1] = {0};
+  // Fused operator of the chi2 path (VG_OPT_FUSE_DM_METALS): the masked rows of the distortion matrix
+  // times the metal matrices, d_dmcat[r][c*ld_model + j] = sum_i D[mask r][i] M_c[i][j], so that the
+  // metal product lands on the n_mask distorted bins directly (no pre-distortion multiplicative term)
+  DevBuf d_dmcat;
+  OzakiOperand oz_dmcat;
+  int oz_fused_slices = 0;       // digits that meet the budget against max|D xi| (0: DMMA)
+  double oz_fused_bound[vg::OZ_MAX_S + 1] = {0};
   DevBuf d_dmat;                 // [n_dist][ld_model]
   DevBuf d_dmat_masked;          // [n_mask][ld_model]
   bool has_inst = false;
@@ -255,6 +262,7 @@ struct vg_plan {
   bool use_moments = true;
   bool direct_mode = false;      // VG_OPT_DIRECT_PK
   bool fold_metals = false;      // VG_OPT_FOLD_METALS
+  bool fuse_dm_metals = true;    // VG_OPT_FUSE_DM_METALS
   bool velo_tables = true;       // VG_OPT_VELO_TABLES
   bool vt_now = false;           // this call's vectors lie inside the tabulated range: tables active
   std::vector<double> theta_lo, theta_hi;   // [sample] limits per theta column (NaN: unbounded)
@@ -273,7 +281,7 @@ struct vg_plan {
   // workspace (sized for `chunk` vectors)
   long long chunk = 0, chunk_max = 1024;
   DevBuf w_pfull, w_pkell, w_tables, w_core, w_xmet, w_met, w_x, w_y, w_diff, w_partial, w_split, w_fold,
-      w_chi2, w_status, w_theta;
+      w_chi2, w_status, w_theta, w_mety;
   void* pinned = nullptr; size_t pinned_bytes = 0;
   // CUDA graphs of the chi2 pass for small batches (B <= GRAPH_MAX_B): the ~50-100 launches of a
   // pass are replayed as one graph on fixed staging buffers; keyed on (B, options); dropped
@@ -346,6 +354,7 @@ int build_metal_operands(Corr& c, const EvalLayout& L, DevBuf& mcat, DevBuf& mrp
 int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget_dm(vg_plan* plan, Corr& c, cudaStream_t st);
+int build_fused_metal_operator(vg_plan* plan, Corr& c, cudaStream_t st);
 void flag_velo_table_candidates(vg_plan* plan, Corr& c);
 int build_velo_tables(vg_plan* plan, Corr& c, cudaStream_t st);
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
@@ -675,6 +684,7 @@ int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
   }
   if (option == VG_OPT_OZAKI_DM) { plan->ozaki_dm = value != 0; return VG_OK; }
   if (option == VG_OPT_VELO_TABLES) { plan->velo_tables = value != 0; return VG_OK; }
+  if (option == VG_OPT_FUSE_DM_METALS) { plan->fuse_dm_metals = value != 0; return VG_OK; }
   if (option == VG_OPT_DIRECT_PK) {
     if (value) {
       bool any = false;
@@ -1097,6 +1107,7 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
     VG_TRY(freeze_metal_terms(plan, *cp, st));
     VG_TRY(ozaki_budget(plan, *cp, st));
     VG_TRY(ozaki_budget_dm(plan, *cp, st));
+    VG_TRY(build_fused_metal_operator(plan, *cp, st));
     // (the host copies of the metal matrices stay: vg_plan_set_templates runs finalize again)
   }
   if (plan->has_global) {
@@ -1384,6 +1395,7 @@ int ensure_workspace(vg_plan* plan, long long Bc_) {
   VG_TRY(plan->w_fold.alloc(met * 8));
   VG_TRY(plan->w_x.alloc(met * 8));
   VG_TRY(plan->w_y.alloc(y * 8));
+  VG_TRY(plan->w_mety.alloc(y * 8));
   VG_TRY(plan->w_diff.alloc(diff * 8));
   VG_TRY(plan->w_partial.alloc((size_t)Bc * 256 * 8));
   VG_TRY(plan->w_chi2.alloc((size_t)Bc * 8));
@@ -1538,8 +1550,11 @@ int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, l
 
 // Stages K1..K3 + metals + pre-distortion assembly of one correlation: leaves
 // x[Bc][ld_model] in plan->w_x.  `upto` stops early for the per-stage taps.
+// `fused` (nullable): the caller wants the chi2 path's residual; when the correlation has the fused
+// distortion x metal operator the metal product is left in plan->w_mety [Bc][ld_mask] on the MASKED
+// DISTORTED bins (not added to x) and *fused is set -- run_corr_back adds it after the distortion.
 int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaStream_t st, int upto = 99,
-                   int layout = -1, int unit_bias = 0) {
+                   int layout = -1, int unit_bias = 0, bool* fused = nullptr) {
   const Hankel& h = *plan->hankels[c.hankel_id];
   const int E = (int)c.evals.size();
   vg::PkGridDev g = plan->grid_dev();
@@ -1707,7 +1722,15 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   }
   // a correlation with nothing folded keeps one set of matrices
   const bool fold_layout = layout == LAY_FOLD && !L.fold_ids.empty();
-  const int oz_S = !c.metal_dense ? 0 : (plan->ozaki_slices < 0 ? c.oz_auto_slices : plan->ozaki_slices);
+  int oz_S = !c.metal_dense ? 0 : (plan->ozaki_slices < 0 ? c.oz_auto_slices : plan->ozaki_slices);
+  // chi2 path with the fused operator: N = n_mask distorted bins instead of n_model model bins
+  const bool fuse = fused && plan->fuse_dm_metals && c.d_dmcat.p && !fold_layout && L.n_metal > 0 &&
+                    (layout == LAY_MOM || layout == LAY_FULL) && upto > 3 && !direct;
+  if (fused) *fused = fuse;
+  if (fuse) oz_S = plan->ozaki_slices < 0 ? c.oz_fused_slices : (c.oz_fused_slices > 0 ? plan->ozaki_slices : 0);
+  const int metal_rows = fuse ? c.n_mask : c.n_model;            // rows of the operator = columns of the product
+  const int metal_ldo = fuse ? c.ld_mask : c.ld_model;
+  double* metal_out = fuse ? plan->w_mety.as<double>() : plan->w_met.as<double>();
   if (L.n_metal > 0) {
     const bool use_ozaki = c.metal_dense && oz_S > 0 && Bc >= OZAKI_MIN_BATCH;
     // (the split-integer branch times its two parts itself: PROF_NONE keeps this scope silent)
@@ -1717,13 +1740,13 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
                              (fold_layout ? c.d_mrp_fold : c.d_mrp).as<double>(), Bc, plan->w_met.as<double>(), st));
     } else if (c.metal_dense) {
       const long long ldk = (long long)L.n_metal * c.ld_model;
-      const DevBuf& mcat = fold_layout ? c.d_mcat_fold : c.d_mcat;
+      const DevBuf& mcat = fuse ? c.d_dmcat : (fold_layout ? c.d_mcat_fold : c.d_mcat);
       if (use_ozaki) {
         // split-integer GEMM on tcgen05 (vg_ozaki.cuh): the operator's digit planes are built on
         // first use, the batch operand's on every call
-        OzakiOperand& ob = fold_layout ? c.oz_mcat_fold : c.oz_mcat;
+        OzakiOperand& ob = fuse ? c.oz_dmcat : (fold_layout ? c.oz_mcat_fold : c.oz_mcat);
         if (ob.S != oz_S || ob.src != mcat.as<double>()) {
-          VG_TRY(ozaki_slice(ob, mcat.as<double>(), ldk, c.n_model, c.n_model, (int)ldk, oz_S, st));
+          VG_TRY(ozaki_slice(ob, mcat.as<double>(), ldk, metal_rows, metal_rows, (int)ldk, oz_S, st));
           ob.src = mcat.as<double>();
         }
         {
@@ -1732,14 +1755,14 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
         }
         {
           ProfScope gemm_prof(plan, PROF_METAL, st);
-          VG_TRY(ozaki_gemm(plan->oz_A, Bc, ob, c.n_model, plan->w_met.as<double>(), c.ld_model, plan->w_split,
+          VG_TRY(ozaki_gemm(plan->oz_A, Bc, ob, metal_rows, metal_out, metal_ldo, plan->w_split,
                             plan->d_oz_error, st));
         }
         vg::flag_status_kernel<<<vg_cdiv(Bc, 256), 256, 0, st>>>(plan->d_oz_error.as<int>(), status_dev, Bc);
         VG_LAUNCHED();
       } else {
         VG_TRY(gemm_auto(plan, plan->w_xmet.as<double>(), ldk, mcat.as<double>(), ldk,
-                         plan->w_met.as<double>(), c.ld_model, (int)Bc, c.n_model, (int)ldk, 1, 0, 0, 0, st));
+                         metal_out, metal_ldo, (int)Bc, metal_rows, (int)ldk, 1, 0, 0, 0, st));
       }
     } else {
       const long long n = Bc * c.ld_model;
@@ -1747,7 +1770,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
                                                          c.n_model, Bc, plan->w_met.as<double>());
       VG_LAUNCHED();
     }
-    met = plan->w_met.as<double>();
+    met = fuse ? nullptr : plan->w_met.as<double>();
   }
   vg::CombineArgs ca{};
   ca.core = plan->w_core.as<double>(); ca.met = met; ca.met_fold = met_fold;
@@ -2030,6 +2053,76 @@ int ozaki_budget_dm(vg_plan* plan, Corr& c, cudaStream_t st) {
   return VG_OK;
 }
 
+// Fused operator of the chi2 path: (masked rows of the distortion matrix) x (metal matrices).
+// vega/model.py:142-143 applies D to xi_core + sum_c M_c xi_c; the chi2 only reads the n_mask bins
+// the cuts keep, and D (M_c xi_c) = (D M_c) xi_c, so with
+//   DM[r][c*ld + j] = sum_i D[mask r][i] M_c[i][j]          (one DGEMM per metal matrix, here)
+// the per-vector metal product has n_mask output columns instead of n_model (64 % of them with the
+// eBOSS cuts) and the distortion product is left with the core terms.  Exact algebra (rounding of
+// one more FP64 product at plan time); needs dense metal matrices, a distortion matrix and NO
+// multiplicative pre-distortion broadband term (it sits between the two products).  Digits of the
+// split-integer GEMM from the same worst-case bound as ozaki_budget, against max|D xi|.
+int build_fused_metal_operator(vg_plan* plan, Corr& c, cudaStream_t st) {
+  c.d_dmcat.release();
+  c.oz_dmcat.planes.release(); c.oz_dmcat.exps.release();
+  c.oz_dmcat.rows = 0; c.oz_dmcat.Kp = 0; c.oz_dmcat.S = 0; c.oz_dmcat.src = nullptr;
+  c.oz_fused_slices = 0;
+  for (double& b : c.oz_fused_bound) b = 0.0;
+  const EvalLayout& L = c.lay[LAY_MOM];
+  if (!c.has_dmat || !c.metal_dense || c.metal_rp || c.n_mask <= 0 || L.n_metal == 0 || !c.d_mcat.p) return VG_OK;
+  for (const vg_bb_term& t : c.bb_terms)
+    if (t.position == 0) return VG_OK;
+  const long long ldk = (long long)L.n_metal * c.ld_model;
+  VG_TRY(c.d_dmcat.alloc((size_t)c.n_mask * ldk * 8));
+  {
+    DevBuf mt, prod;   // M_c^T [n_model][ld_model]; D_masked M_c [n_mask][ld_model] (gemm_auto's split-K
+                       // reduction owns every column of its output rows: a compact block, copied afterwards)
+    VG_TRY(mt.alloc((size_t)c.ld_model * c.ld_model * 8));
+    VG_TRY(prod.alloc((size_t)c.n_mask * c.ld_model * 8));
+    for (int col = 0; col < L.n_metal; ++col) {
+      dim3 tgrid(vg_cdiv(c.n_model, 32), vg_cdiv(c.n_model, 32));
+      vg::transpose_kernel<<<tgrid, dim3(32, 8), 0, st>>>(c.d_mcat.as<double>() + (size_t)col * c.ld_model, ldk,
+                                                          c.n_model, mt.as<double>(), c.ld_model);
+      VG_LAUNCHED();
+      VG_TRY(gemm_auto(plan, c.d_dmat_masked.as<double>(), c.ld_model, mt.as<double>(), c.ld_model,
+                       prod.as<double>(), c.ld_model, c.n_mask, c.n_model, c.ld_model, 1, 0, 0, 0, st));
+      VG_CUDA_CHECK(cudaMemcpy2DAsync(c.d_dmcat.as<double>() + (size_t)col * c.ld_model, (size_t)ldk * 8,
+                                      prod.as<double>(), (size_t)c.ld_model * 8, (size_t)c.n_model * 8, c.n_mask,
+                                      cudaMemcpyDeviceToDevice, st));
+    }
+    VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  }
+  // digits: operator row statistics of DM, the metal xi and max|D x| at the plan parameters
+  VG_TRY(ensure_workspace(plan, 1));
+  VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_pfull.p, plan->d_base.p, (size_t)plan->npf * 8, cudaMemcpyDeviceToDevice, st));
+  VG_CUDA_CHECK(cudaMemsetAsync(plan->w_status.p, 0, 4, st));
+  VG_TRY(run_corr_front(plan, c, 1, plan->w_status.as<int>(), st, 99, LAY_MOM, 0));
+  VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_dmat_masked.as<double>(), c.ld_model,
+                   plan->w_y.as<double>(), c.ld_mask, 1, c.n_mask, c.ld_model, 1, 0, 0, 0, st));
+  DevBuf stats;
+  VG_TRY(stats.alloc(9 * sizeof(unsigned long long)));
+  unsigned long long* d = stats.as<unsigned long long>();
+  vg::ozaki_stats_kernel<<<1, 256, 0, st>>>(plan->w_xmet.as<double>(), ldk, (int)ldk, d);
+  VG_LAUNCHED();
+  vg::ozaki_stats_kernel<<<(unsigned)c.n_mask, 256, 0, st>>>(c.d_dmcat.as<double>(), ldk, (int)ldk, d + 3);
+  VG_LAUNCHED();
+  vg::ozaki_stats_kernel<<<1, 256, 0, st>>>(plan->w_y.as<double>(), c.ld_mask, c.n_mask, d + 6);
+  VG_LAUNCHED();
+  double h[9];
+  VG_CUDA_CHECK(cudaMemcpyAsync(h, stats.p, sizeof(h), cudaMemcpyDeviceToHost, st));
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  const double amax = h[0], a1 = h[1], bmax = h[3], b1 = h[4], bnz = h[5], scale = h[6];
+  if (!(scale > 0.0) || !(amax > 0.0) || !std::isfinite(scale)) return VG_OK;     // DMMA on the fused operator
+  c.oz_fused_slices = vg::OZ_MAX_S;
+  for (int S = vg::OZ_MAX_S; S >= 3; --S) {
+    const double bound = std::ldexp(amax * b1 + a1 * bmax + (S - 1) * amax * bmax * bnz, -7 * S);
+    c.oz_fused_bound[S] = bound / scale;
+    if (bound <= OZAKI_BUDGET * scale) c.oz_fused_slices = S;
+  }
+  if (c.oz_fused_bound[vg::OZ_MAX_S] > OZAKI_BUDGET) c.oz_fused_slices = 0;
+  return VG_OK;
+}
+
 // fast_metals metal x metal terms (vega/metals.py:144-169): M_c xi_c evaluated ONCE at the
 // plan's base parameters (the reference caches the first evaluation forever), stored without
 // the bias product, which the hot path applies per vector.
@@ -2071,8 +2164,11 @@ int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st) {
 // Distortion matrix + post-distortion broadband of one correlation.
 //   data == false: model rows for ALL distorted bins -> out[Bc][ldo = ld_dist]
 //   data == true : residual d - m on the masked bins  -> out[Bc][ldo] at column col0
+//   y_add (residual only): the metal product already on the masked distorted bins (fused operator,
+//   run_corr_front), [Bc][ld_mask], added to D x before the post-distortion broadband
 int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* out, int ldo,
-                  int ncols, cudaStream_t st, const int* mock_idx = nullptr, int* status_dev = nullptr) {
+                  int ncols, cudaStream_t st, const int* mock_idx = nullptr, int* status_dev = nullptr,
+                  const double* y_add = nullptr) {
   const double* y = plan->w_x.as<double>();
   int ldy = c.ld_model;
   int y_is_masked = 0;
@@ -2110,6 +2206,7 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
   }
   vg::PostArgs pa{};
   pa.y = y; pa.ldy = ldy; pa.y_is_masked = y_is_masked;
+  pa.y_add = y_add;
   pa.mask_idx = residual ? c.d_mask_idx.as<int>() : nullptr;
   pa.bb = bb_dev(c); pa.n_dist = c.n_dist;
   pa.pfull = plan->w_pfull.as<double>(); pa.npf = plan->npf; pa.idx_bao_amp = plan->idx_bao_amp;
@@ -2162,15 +2259,17 @@ int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi
   for (auto& cp : plan->corrs) {
     Corr& c = *cp;
     VG_REQUIRE(c.n_mask > 0, "vg_chi2_batch: correlation without data (vg_corr_set_data)");
-    VG_TRY(run_corr_front(plan, c, Bc, status_dev, st));
+    bool fused = false;
+    VG_TRY(run_corr_front(plan, c, Bc, status_dev, st, 99, -1, 0, &fused));
+    const double* y_add = fused ? plan->w_mety.as<double>() : nullptr;
     if (plan->has_global) {
       // residuals of all correlations side by side: [Bc][ld_total]
       VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>() + col0, plan->ld_total,
-                           c.n_mask, st, mock_idx, status_dev));
+                           c.n_mask, st, mock_idx, status_dev, y_add));
       col0 += c.n_mask;
     } else {
       VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, st, mock_idx,
-                           status_dev));
+                           status_dev, y_add));
       VG_TRY(quad_form(plan, plan->w_diff.as<double>(), c.n_mask, c.ld_mask,
                        c.has_invcov ? c.d_invcov.as<double>() : nullptr, Bc, chi2_dev, !first, st));
       first = 0;
@@ -2204,7 +2303,7 @@ int chi2_chunk_small(vg_plan* plan, const double* theta_dev, long long Bc, doubl
   const long long key = Bc | ((long long)plan->use_moments << 20) | ((long long)plan->fold_metals << 21) |
                         ((long long)plan->direct_mode << 22) | ((long long)(mock_idx != nullptr) << 23) |
                         ((long long)(plan->ozaki_slices + 1) << 24) | ((long long)plan->ozaki_dm << 30) |
-                        ((long long)plan->vt_now << 31);
+                        ((long long)plan->vt_now << 31) | ((long long)plan->fuse_dm_metals << 32);
   vg_plan::GraphEntry& g = plan->graphs[key];
   if (g.exec && g.generation != g_alloc_generation) {     // a buffer moved since the capture
     cudaGraphExecDestroy(g.exec);
@@ -2450,6 +2549,17 @@ int vg_corr_velo_tables(const vg_plan* plan, int32_t corr, int32_t* orders, doub
   if (orders) *orders = c.vt_n;
   if (error) *error = c.vt_err;
   return (int)c.lay[LAY_MOM].vt_ids.size();
+}
+
+int vg_corr_fused_metal_operator(const vg_plan* plan, int32_t corr, int32_t* digits, double* bound_per_digits) {
+  if (digits) *digits = 0;
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size() || !plan->fuse_dm_metals) return 0;
+  const Corr& c = *plan->corrs[corr];
+  if (!c.d_dmcat.p) return 0;
+  if (digits) *digits = plan->ozaki_slices < 0 ? c.oz_fused_slices : (c.oz_fused_slices > 0 ? plan->ozaki_slices : 0);
+  if (bound_per_digits)
+    for (int S = 0; S <= vg::OZ_MAX_S; ++S) bound_per_digits[S] = c.oz_fused_bound[S];
+  return c.n_mask;
 }
 
 int vg_plan_velo_tables_active(const vg_plan* plan) { return plan && plan->vt_now ? 1 : 0; }

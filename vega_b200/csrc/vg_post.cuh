@@ -262,6 +262,7 @@ __global__ void combine_pre_kernel(CombineArgs a) {
 
 struct PostArgs {
   const double* y; int ldy;   // distorted model rows; y[b][row]
+  const double* y_add;        // nullable, same layout: a term already on the distorted bins (fused metal operator)
   const int* mask_idx;        // [n_out] distorted-grid bin of output j (null: j)
   int y_is_masked;            // 1: y row j already is bin mask_idx[j]
   BroadbandDev bb; int n_dist;
@@ -284,6 +285,7 @@ __global__ void post_kernel(PostArgs a) {
   const double* p = a.pfull + b * a.npf;
   const int bin = a.mask_idx ? a.mask_idx[j] : j;
   double v = a.y[b * a.ldy + (a.y_is_masked ? j : bin)];
+  if (a.y_add) v += a.y_add[b * a.ldy + (a.y_is_masked ? j : bin)];
   if (a.bb.n_terms) {
     const double amp = a.direct ? 0.0 : par(p, a.idx_bao_amp, 1.0);
     v *= bb_eval(a.bb, 2, p, bin, a.n_dist);

@@ -935,6 +935,13 @@ class DevicePlan:
         n = self.lib.vg_corr_velo_tables(self.handle, ci, C.byref(orders), C.byref(err))
         return n, orders.value, err.value
 
+    def fused_metal_operator(self, ci):
+        """(rows, digits) of the fused distortion x metal operator of correlation ci on the chi2 path
+        (rows = masked bins; (0, 0) when it is not used)."""
+        digits = C.c_int32(0)
+        rows = self.lib.vg_corr_fused_metal_operator(self.handle, ci, C.byref(digits), None)
+        return rows, digits.value
+
     def velo_tables_active(self):
         """True when the last batch call ran on the velocity-dispersion tables."""
         return bool(self.lib.vg_plan_velo_tables_active(self.handle))
