@@ -192,3 +192,30 @@ def test_small_covariances_keep_the_reference_host_inverse():
     assert np.array_equal(utils.compute_masked_invcov(cov, mask), np.linalg.inv(masked))
     assert utils.compute_log_cov_det(cov, mask) == np.linalg.slogdet(masked)[1]
     assert not utils._factor_cache
+
+
+def test_uv_bias_term_is_static_unless_a_uv_parameter_is_sampled():
+    """vg_eval_desc::uv_static: the scale-dependent UV bias (vega/power_spectrum.py:224-261) is a static
+    function of k -- and the evaluation eligible for the moment form -- exactly when none of
+    bias_prim / lambda_uv / bias_gamma is a batch column."""
+    vega, pb = builder('configs/full_configs/main.ini')
+    peak = pb.describe_corr('lyalya_lyalya')['evals'][0]
+    assert peak.uvb == 1 and peak.uv_on[0] == 1 and peak.uv_static == 1
+    cross = pb.describe_corr('lyalya_qso')['evals'][0]
+    assert cross.uvb == 1 and list(cross.uv_on) == [1, 0] and cross.uv_static == 1
+    vega, pb = builder('configs/full_configs/main.ini', sampled=['bias_eta_LYA', 'beta_LYA', 'bias_gamma'])
+    assert pb.describe_corr('lyalya_lyalya')['evals'][0].uv_static == 0
+    # metal evaluations are built from the [metals] section: no UV term at all
+    metal = pb.describe_corr('lyalya_lyalya')['evals'][2]
+    assert metal.uvb == 0 and metal.uv_static == 0
+
+
+def test_theta_limits_follow_the_sample_section():
+    """The box handed to vg_plan_set_theta_limits is the [sample] limits (default_values.txt for
+    `name = True` entries): what the velocity-dispersion tables are built over."""
+    vega, pb = builder('configs/c2/main.ini')
+    limits = vega.sample_params['limits']
+    assert limits['sigma_velo_disp_lorentz_QSO'] == (0.0, 15.0)
+    assert 'sigma_velo_disp_lorentz_QSO' in pb.sampled
+    peak = pb.describe_corr('qsoxlya')['evals'][0]
+    assert peak.dyn_mask == _lib.F_VELO and max(peak.idx_velo) == pb.col('sigma_velo_disp_lorentz_QSO')
