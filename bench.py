@@ -730,10 +730,14 @@ def main():
                 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch (auto-correlation, M=1024
                 # N=2500 K=37680, S=7, 6 splits) from the committed ncu --set full capture; algorithmic bytes
                 # of that launch: 7 x (1024 + 2500) x 37680 digit bytes + 6 x 1024 x 2512 x 8 partial sums
-                'traffic': 1.610e9 if B == 1024 else None, 'algorithmic_bytes_of_that_launch': 1.053e9,
-                'traffic_source': 'profiles/r02_ncu_full_c2_raw.csv (ozaki_gemm_kernel<7>, grid 8x40x6, before the CTA-pair '
-                                  'multicast: 1.493 GB read + 0.117 GB written)',
-                'ncu_tensor_pipe_active': [0.538, 0.698], 'ncu_l1tex_throughput': [0.629, 0.599],
+                # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch (auto-correlation, fused operator:
+                # M = 1024, N = 1590, K = 37680, S = 8, 7 splits, CTA pairs) from the committed ncu --set full
+                # capture; algorithmic bytes of that launch: 8 x (1024 + 1590) x 37680 digit bytes + 7 x 1024 x
+                # 1600 x 8 of partial sums
+                'traffic': 1.283e9 if B == 1024 else None, 'algorithmic_bytes_of_that_launch': 0.880e9,
+                'traffic_source': 'profiles/r02_ncu_full_c2_final_raw.csv (ozaki_gemm_kernel<8, 2>, grid 8x26x7: 1.195 GB '
+                                  'read + 0.088 GB written)',
+                'ncu_tensor_pipe_active': [0.738, 0.726],
                 'share_of_step': metal_ms / ms_per_step}
         else:
             gemm_ms = sum(stage_ms[s] for s in ('hankel_gemm', 'metal_gemm', 'dm_gemm', 'chi2_gemm'))
