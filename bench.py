@@ -801,6 +801,7 @@ def main():
                                                                for ci in range(len(engine.infos))),
                        'metal_gemm_digits': digits, 'distortion_gemm_digits': dm_digits,
                        'fused_distortion_metal_operator': [{'rows': r, 'digits': s} for r, s in fused],
+                       'whitened_chi2': [engine.whitened(ci) for ci in range(len(engine.infos))],
                        'l2': 'inputs larger than L2: ~2.9 GB of static operands + ~2 GB of workspace '
                              'streamed per step'},
             'clocks': clock_info,

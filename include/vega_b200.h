@@ -248,6 +248,16 @@ int vg_corr_set_broadband(vg_plan* plan, int32_t corr, int32_t n_terms, const vg
  * to swap in a Monte Carlo mock (vega/vega_interface.py:296-312). */
 int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t* mask_idx,
                      const double* data, const double* invcov);
+/* A square root of the inverse covariance just given to vg_corr_set_data: w[n_mask][n_mask] with
+ * invcov = w^T w (e.g. the transposed lower Cholesky factor), or NULL to clear it.  Optional; with it
+ * (and VG_OPT_WHITEN) the chi2 (d - m)^T C^-1 (d - m) of vega/vega_interface.py:294-319 is evaluated as
+ * |w d - w m|^2 with w folded into the masked distortion rows, the fused metal operator, the data and the
+ * mocks, so no product with C^-1 is left on the hot path.  Used when the correlation has a distortion
+ * matrix, its own covariance (no global one) and no post-distortion broadband term; ignored otherwise.
+ * A later vg_corr_set_data with a new inverse covariance drops it until it is given again. */
+int vg_corr_set_whitening(vg_plan* plan, int32_t corr, int32_t n_mask, const double* w);
+/* 1 when the chi2 path of the correlation runs on the whitened operands (after the first chi2 call) */
+int vg_corr_whitened(const vg_plan* plan, int32_t corr);
 /* Global covariance over all correlations (vega/vega_interface.py:888-954) */
 int vg_plan_set_global_invcov(vg_plan* plan, int32_t n_total, const double* invcov);
 /* Uploads everything, builds the static factor grids on the device. Synchronous. */
@@ -303,6 +313,9 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
  * matrices, a distortion matrix and no multiplicative pre-distortion broadband term; the model entry
  * points (all distorted bins) keep the two products.  0: the two-step form (its parity reference). */
 #define VG_OPT_FUSE_DM_METALS 6
+/* VG_OPT_WHITEN (default 1): use the square root given to vg_corr_set_whitening (see there); 0 keeps the
+ * product with C^-1 (the parity reference). */
+#define VG_OPT_WHITEN 7
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
 /* Isotropic P(k) [nk] for the direct mode (e.g. from a Boltzmann code, the `direct_pk`
  * argument of VegaInterface.compute_model / chi2 / log_lik); host pointer, copied. */

@@ -169,6 +169,31 @@ def test_moment_form_with_the_uv_bias_term_matches_per_point_pass():
         assert_xi_close({n: models_mom[n][b] for n in ref}, ref, f'uv moment form, row {b}')
 
 
+def test_whitened_chi2_matches_the_product_with_the_inverse_covariance():
+    """VG_OPT_WHITEN: with C^-1 = W^T W (vg_corr_set_whitening) the chi2 of
+    vega/vega_interface.py:294-319 is |W d - W m|^2 with W folded into the masked distortion rows, the
+    fused metal operator, the data vector and the mocks.  Same values as the product with C^-1 (option
+    0), for large and small batches, and as the oracle."""
+    from vega_b200 import _lib
+    vega, oracle, theta = make_c2(48, width=1.0)
+    names = list(vega.sample_params['limits'])
+    engine = vega._engine_for()
+    got = vega.chi2_batch(theta)
+    assert all(engine.whitened(ci) for ci in range(len(engine.infos)))
+    small = vega.chi2_batch(theta[:3])
+    engine.set_option(_lib.OPT_WHITEN, 0)
+    ref = vega.chi2_batch(theta)
+    assert not any(engine.whitened(ci) for ci in range(len(engine.infos)))
+    ref_small = vega.chi2_batch(theta[:3])
+    engine.set_option(_lib.OPT_WHITEN, 1)
+    assert np.max(np.abs(got - ref) / np.abs(ref)) <= 1e-10
+    assert np.max(np.abs(small - ref_small) / np.abs(ref_small)) <= 1e-10
+    np.testing.assert_allclose(vega.chi2_batch(theta), got, rtol=1e-13)      # rebuilt after the option flip
+    for b in (0, 47):
+        want = oracle.chi2(dict(zip(names, theta[b])))
+        assert abs(got[b] - want) <= CHI2_ATOL * max(1.0, abs(want) / 1e4), (b, got[b], want)
+
+
 @pytest.mark.parametrize('case', ['c2_dense', 'c2_fast_metals', 'rp_only'])
 def test_folded_metals_match_the_matrix_product(case, tmp_path):
     """VG_OPT_FOLD_METALS: metal terms whose xi stage is in moment form are served from static

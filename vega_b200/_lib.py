@@ -13,7 +13,7 @@ LIB_PATH = Path(__file__).resolve().parent / 'libvega_b200.so'
 VG_MAX_BB_TERMS = 8
 F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP, F_MOCKGK = (1 << i for i in range(9))
 STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE, STATUS_DEVICE = 1, 2, 4, 8
-OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS, OPT_OZAKI, OPT_OZAKI_DM, OPT_VELO_TABLES, OPT_FUSE_DM_METALS = 0, 1, 2, 3, 4, 5, 6
+OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS, OPT_OZAKI, OPT_OZAKI_DM, OPT_VELO_TABLES, OPT_FUSE_DM_METALS, OPT_WHITEN = 0, 1, 2, 3, 4, 5, 6, 7
 ERR_CUDA, ERR_ARG, ERR_STATE = 1, 2, 3
 STATIC_SCRATCH_DOUBLES = 1 << 21      # VG_STATIC_SCRATCH_DOUBLES of include/vega_b200.h
 
@@ -111,6 +111,8 @@ _SIGNATURES = {
     'vg_corr_set_inst_sys': (C.c_int, [_PTR, i32, _PTR, i32, f64]),
     'vg_corr_set_broadband': (C.c_int, [_PTR, i32, i32, _PTR, i32, _PTR, i32, _PTR, _PTR, _PTR]),
     'vg_corr_set_data': (C.c_int, [_PTR, i32, i32, _PTR, _PTR, _PTR]),
+    'vg_corr_set_whitening': (C.c_int, [_PTR, i32, i32, _PTR]),
+    'vg_corr_whitened': (C.c_int, [_PTR, i32]),
     'vg_plan_set_global_invcov': (C.c_int, [_PTR, i32, _PTR]),
     'vg_plan_finalize': (C.c_int, [_PTR, _PTR]),
     'vg_plan_device_bytes': (C.c_int64, [_PTR]),

@@ -219,6 +219,16 @@ struct Corr {
   OzakiOperand oz_dmat, oz_dmat_masked;  // digit planes of d_dmat / d_dmat_masked (built on first use)
   int oz_dm_slices = 0;          // digits of the distortion product that meet the budget (0: DMMA)
   double oz_dm_bound[vg::OZ_MAX_S + 1] = {0};
+  // Whitened chi2 path (VG_OPT_WHITEN): with C^-1 = W^T W the chi2 is |W (d - y)|^2, and W folds into
+  // everything linear that produces y on the masked bins: d_wd = W x (masked rows of D), the fused
+  // operator is built on d_wd, d_wdata = W d, d_wmocks = mocks W^T.  The chi2 GEMM disappears.
+  bool has_white = false;        // a square root of the inverse covariance was given (vg_corr_set_whitening)
+  bool white_dirty = false;      // the whitened operands are out of date (rebuilt at the next chi2 call)
+  bool whitened = false;         // the residual path runs on the whitened operands
+  DevBuf d_white, d_wd, d_wdata, d_wmocks;
+  OzakiOperand oz_wd;
+  int oz_wd_slices = 0;
+  double oz_wd_bound[vg::OZ_MAX_S + 1] = {0};
   // Fused operator of the chi2 path (VG_OPT_FUSE_DM_METALS): the masked rows of the distortion matrix
   // times the metal matrices, d_dmcat[r][c*ld_model + j] = sum_i D[mask r][i] M_c[i][j], so that the
   // metal product lands on the n_mask distorted bins directly (no pre-distortion multiplicative term)
@@ -263,6 +273,7 @@ struct vg_plan {
   bool direct_mode = false;      // VG_OPT_DIRECT_PK
   bool fold_metals = false;      // VG_OPT_FOLD_METALS
   bool fuse_dm_metals = true;    // VG_OPT_FUSE_DM_METALS
+  bool whiten = true;            // VG_OPT_WHITEN
   bool velo_tables = true;       // VG_OPT_VELO_TABLES
   bool vt_now = false;           // this call's vectors lie inside the tabulated range: tables active
   std::vector<double> theta_lo, theta_hi;   // [sample] limits per theta column (NaN: unbounded)
@@ -355,6 +366,7 @@ int freeze_metal_terms(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget_dm(vg_plan* plan, Corr& c, cudaStream_t st);
 int build_fused_metal_operator(vg_plan* plan, Corr& c, cudaStream_t st);
+int rebuild_whitened(vg_plan* plan, Corr& c, cudaStream_t st);
 void flag_velo_table_candidates(vg_plan* plan, Corr& c);
 int build_velo_tables(vg_plan* plan, Corr& c, cudaStream_t st);
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
@@ -685,6 +697,11 @@ int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
   if (option == VG_OPT_OZAKI_DM) { plan->ozaki_dm = value != 0; return VG_OK; }
   if (option == VG_OPT_VELO_TABLES) { plan->velo_tables = value != 0; return VG_OK; }
   if (option == VG_OPT_FUSE_DM_METALS) { plan->fuse_dm_metals = value != 0; return VG_OK; }
+  if (option == VG_OPT_WHITEN) {
+    plan->whiten = value != 0;
+    for (auto& cp : plan->corrs) cp->white_dirty = true;
+    return VG_OK;
+  }
   if (option == VG_OPT_DIRECT_PK) {
     if (value) {
       bool any = false;
@@ -927,9 +944,23 @@ int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t*
     VG_TRY(upload_padded(c.d_invcov, invcov, n_mask, n_mask, c.ld_mask));
     VG_TRY(symmetrize(c.d_invcov, n_mask, c.ld_mask));
     c.has_invcov = true;
+    c.has_white = false;          // a square root of the OLD matrix: vg_corr_set_whitening gives the new one
   } else {
     c.has_invcov = false;
+    c.has_white = false;
   }
+  c.white_dirty = true;
+  return VG_OK;
+}
+
+int vg_corr_set_whitening(vg_plan* plan, int32_t corr, int32_t n_mask, const double* w) {
+  VG_CORR(plan, corr);
+  plan->drop_graphs();
+  c.white_dirty = true;
+  if (!w) { c.has_white = false; return VG_OK; }
+  VG_REQUIRE(n_mask == c.n_mask && c.has_invcov, "vg_corr_set_whitening: call after vg_corr_set_data with an inverse covariance of the same size");
+  VG_TRY(upload_padded(c.d_white, w, n_mask, n_mask, c.ld_mask));
+  c.has_white = true;
   return VG_OK;
 }
 
@@ -1107,7 +1138,8 @@ int vg_plan_finalize(vg_plan* plan, void* stream) {
     VG_TRY(freeze_metal_terms(plan, *cp, st));
     VG_TRY(ozaki_budget(plan, *cp, st));
     VG_TRY(ozaki_budget_dm(plan, *cp, st));
-    VG_TRY(build_fused_metal_operator(plan, *cp, st));
+    if (cp->n_mask > 0) VG_TRY(rebuild_whitened(plan, *cp, st));   // whitened operands + the fused operator
+    else cp->white_dirty = true;                                    // (data not set yet: at the first chi2 call)
     // (the host copies of the metal matrices stay: vg_plan_set_templates runs finalize again)
   }
   if (plan->has_global) {
@@ -2053,6 +2085,97 @@ int ozaki_budget_dm(vg_plan* plan, Corr& c, cudaStream_t st) {
   return VG_OK;
 }
 
+// rows [n][n_mask] (row stride n_mask) -> out[n][n_mask] = rows W^T, i.e. W applied to every row
+int whiten_rows(vg_plan* plan, Corr& c, const double* rows, int n, DevBuf& out, cudaStream_t st) {
+  DevBuf in_pad, out_pad;
+  VG_TRY(in_pad.alloc((size_t)n * c.ld_mask * 8));
+  VG_TRY(out_pad.alloc((size_t)n * c.ld_mask * 8));
+  VG_CUDA_CHECK(cudaMemcpy2DAsync(in_pad.p, (size_t)c.ld_mask * 8, rows, (size_t)c.n_mask * 8, (size_t)c.n_mask * 8, n,
+                                  cudaMemcpyDeviceToDevice, st));
+  VG_TRY(gemm_auto(plan, in_pad.as<double>(), c.ld_mask, c.d_white.as<double>(), c.ld_mask, out_pad.as<double>(),
+                   c.ld_mask, n, c.n_mask, c.ld_mask, 1, 0, 0, 0, st));
+  VG_TRY(out.alloc((size_t)n * c.n_mask * 8));
+  VG_CUDA_CHECK(cudaMemcpy2DAsync(out.p, (size_t)c.n_mask * 8, out_pad.p, (size_t)c.ld_mask * 8, (size_t)c.n_mask * 8, n,
+                                  cudaMemcpyDeviceToDevice, st));
+  VG_CUDA_CHECK(cudaStreamSynchronize(st));
+  return VG_OK;
+}
+
+// Whitened chi2 path (VG_OPT_WHITEN).  With C^-1 = W^T W (vg_corr_set_whitening: the Cholesky factor
+// the caller took of the matrix it gave to vg_corr_set_data),
+//   chi2 = (d - y)^T C^-1 (d - y) = |W d - W y|^2        (vega/vega_interface.py:294-319)
+// and y = D_mask x is linear, so W folds into the operators at plan time: d_wd = W D_mask, the fused
+// distortion x metal operator is built on d_wd, the data and the mocks are stored as W d.  The chi2
+// GEMM (2 n_mask^2 flops per vector) becomes a sum of squares.  Needs a per-correlation covariance
+// (under a global one W couples the correlations and W D would have sum(n_mask) rows per
+// correlation), a distortion matrix and no post-distortion broadband term (it sits between D and W).
+// Called with the correlation's state changed (finalize, new data / covariance / mocks / option);
+// rebuilds the fused operator too, which depends on the choice.
+int rebuild_whitened(vg_plan* plan, Corr& c, cudaStream_t st) {
+  c.white_dirty = false;
+  bool ok = plan->whiten && c.has_white && c.has_invcov && c.has_dmat && !plan->has_global && c.n_mask > 0 &&
+            c.d_dmat_masked.p != nullptr;
+  for (const vg_bb_term& t : c.bb_terms)
+    if (t.position >= 2) ok = false;
+  const bool was = c.whitened;
+  c.whitened = false;
+  c.oz_wd_slices = 0;
+  for (double& b : c.oz_wd_bound) b = 0.0;
+  if (ok) {
+    {   // d_wd = W D_mask: C[r][i] = sum_s W[r][s] D[s][i] -> the TN kernel wants D^T
+      DevBuf dt;
+      VG_TRY(dt.alloc((size_t)c.ld_model * c.ld_mask * 8));
+      dim3 tgrid(vg_cdiv(c.n_model, 32), vg_cdiv(c.n_mask, 32));
+      vg::transpose_kernel<<<tgrid, dim3(32, 8), 0, st>>>(c.d_dmat_masked.as<double>(), c.ld_model, c.n_mask, c.n_model,
+                                                          dt.as<double>(), c.ld_mask);
+      VG_LAUNCHED();
+      VG_TRY(c.d_wd.alloc((size_t)c.n_mask * c.ld_model * 8));
+      VG_TRY(gemm_auto(plan, c.d_white.as<double>(), c.ld_mask, dt.as<double>(), c.ld_mask, c.d_wd.as<double>(),
+                       c.ld_model, c.n_mask, c.n_model, c.ld_mask, 1, 0, 0, 0, st));
+      VG_CUDA_CHECK(cudaStreamSynchronize(st));
+    }
+    VG_TRY(whiten_rows(plan, c, c.d_data.as<double>(), 1, c.d_wdata, st));
+    if (c.n_mocks > 0) VG_TRY(whiten_rows(plan, c, c.d_mocks.as<double>(), c.n_mocks, c.d_wmocks, st));
+    c.whitened = true;
+    // digits of the split-integer GEMM on d_wd: the bound of ozaki_budget_dm against max|W D x|
+    VG_TRY(ensure_workspace(plan, 1));
+    VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_pfull.p, plan->d_base.p, (size_t)plan->npf * 8, cudaMemcpyDeviceToDevice, st));
+    VG_CUDA_CHECK(cudaMemsetAsync(plan->w_status.p, 0, 4, st));
+    const bool vt0 = plan->vt_now;
+    plan->vt_now = false;
+    VG_TRY(run_corr_front(plan, c, 1, plan->w_status.as<int>(), st));
+    plan->vt_now = vt0;
+    VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_wd.as<double>(), c.ld_model,
+                     plan->w_y.as<double>(), c.ld_mask, 1, c.n_mask, c.ld_model, 1, 0, 0, 0, st));
+    DevBuf stats;
+    VG_TRY(stats.alloc(9 * sizeof(unsigned long long)));
+    unsigned long long* d = stats.as<unsigned long long>();
+    vg::ozaki_stats_kernel<<<1, 256, 0, st>>>(plan->w_x.as<double>(), c.ld_model, c.n_model, d);
+    VG_LAUNCHED();
+    vg::ozaki_stats_kernel<<<(unsigned)c.n_mask, 256, 0, st>>>(c.d_wd.as<double>(), c.ld_model, c.n_model, d + 3);
+    VG_LAUNCHED();
+    vg::ozaki_stats_kernel<<<1, 256, 0, st>>>(plan->w_y.as<double>(), c.ld_mask, c.n_mask, d + 6);
+    VG_LAUNCHED();
+    double h[9];
+    VG_CUDA_CHECK(cudaMemcpyAsync(h, stats.p, sizeof(h), cudaMemcpyDeviceToHost, st));
+    VG_CUDA_CHECK(cudaStreamSynchronize(st));
+    const double amax = h[0], a1 = h[1], bmax = h[3], b1 = h[4], bnz = h[5], scale = h[6];
+    if (scale > 0.0 && amax > 0.0 && std::isfinite(scale)) {
+      c.oz_wd_slices = vg::OZ_MAX_S;
+      for (int S = vg::OZ_MAX_S; S >= 3; --S) {
+        const double bound = std::ldexp(amax * b1 + a1 * bmax + (S - 1) * amax * bmax * bnz, -7 * S);
+        c.oz_wd_bound[S] = bound / scale;
+        if (bound <= OZAKI_BUDGET * scale) c.oz_wd_slices = S;
+      }
+      if (c.oz_wd_bound[vg::OZ_MAX_S] > OZAKI_BUDGET) c.oz_wd_slices = 0;
+    }
+  } else {
+    c.d_wd.release(); c.d_wdata.release(); c.d_wmocks.release();
+  }
+  (void)was;
+  return build_fused_metal_operator(plan, c, st);
+}
+
 // Fused operator of the chi2 path: (masked rows of the distortion matrix) x (metal matrices).
 // vega/model.py:142-143 applies D to xi_core + sum_c M_c xi_c; the chi2 only reads the n_mask bins
 // the cuts keep, and D (M_c xi_c) = (D M_c) xi_c, so with
@@ -2073,6 +2196,7 @@ int build_fused_metal_operator(vg_plan* plan, Corr& c, cudaStream_t st) {
   for (const vg_bb_term& t : c.bb_terms)
     if (t.position == 0) return VG_OK;
   const long long ldk = (long long)L.n_metal * c.ld_model;
+  const double* dmasked = (c.whitened ? c.d_wd : c.d_dmat_masked).as<double>();   // W folded in (rebuild_whitened)
   VG_TRY(c.d_dmcat.alloc((size_t)c.n_mask * ldk * 8));
   {
     DevBuf mt, prod;   // M_c^T [n_model][ld_model]; D_masked M_c [n_mask][ld_model] (gemm_auto's split-K
@@ -2082,9 +2206,9 @@ int build_fused_metal_operator(vg_plan* plan, Corr& c, cudaStream_t st) {
     for (int col = 0; col < L.n_metal; ++col) {
       dim3 tgrid(vg_cdiv(c.n_model, 32), vg_cdiv(c.n_model, 32));
       vg::transpose_kernel<<<tgrid, dim3(32, 8), 0, st>>>(c.d_mcat.as<double>() + (size_t)col * c.ld_model, ldk,
-                                                          c.n_model, mt.as<double>(), c.ld_model);
+                                                          c.n_model, c.n_model, mt.as<double>(), c.ld_model);
       VG_LAUNCHED();
-      VG_TRY(gemm_auto(plan, c.d_dmat_masked.as<double>(), c.ld_model, mt.as<double>(), c.ld_model,
+      VG_TRY(gemm_auto(plan, dmasked, c.ld_model, mt.as<double>(), c.ld_model,
                        prod.as<double>(), c.ld_model, c.n_mask, c.n_model, c.ld_model, 1, 0, 0, 0, st));
       VG_CUDA_CHECK(cudaMemcpy2DAsync(c.d_dmcat.as<double>() + (size_t)col * c.ld_model, (size_t)ldk * 8,
                                       prod.as<double>(), (size_t)c.ld_model * 8, (size_t)c.n_model * 8, c.n_mask,
@@ -2097,7 +2221,7 @@ int build_fused_metal_operator(vg_plan* plan, Corr& c, cudaStream_t st) {
   VG_CUDA_CHECK(cudaMemcpyAsync(plan->w_pfull.p, plan->d_base.p, (size_t)plan->npf * 8, cudaMemcpyDeviceToDevice, st));
   VG_CUDA_CHECK(cudaMemsetAsync(plan->w_status.p, 0, 4, st));
   VG_TRY(run_corr_front(plan, c, 1, plan->w_status.as<int>(), st, 99, LAY_MOM, 0));
-  VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, c.d_dmat_masked.as<double>(), c.ld_model,
+  VG_TRY(gemm_auto(plan, plan->w_x.as<double>(), c.ld_model, dmasked, c.ld_model,
                    plan->w_y.as<double>(), c.ld_mask, 1, c.n_mask, c.ld_model, 1, 0, 0, 0, st));
   DevBuf stats;
   VG_TRY(stats.alloc(9 * sizeof(unsigned long long)));
@@ -2173,14 +2297,16 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
   int ldy = c.ld_model;
   int y_is_masked = 0;
   if (c.has_dmat) {
-    const DevBuf& dm = residual ? c.d_dmat_masked : c.d_dmat;
+    const bool white = residual && c.whitened;       // W folded into the masked rows (rebuild_whitened)
+    const DevBuf& dm = residual ? (white ? c.d_wd : c.d_dmat_masked) : c.d_dmat;
     const int rows = residual ? c.n_mask : c.n_dist;
     ldy = residual ? c.ld_mask : c.ld_dist;
     y_is_masked = residual ? 1 : 0;
-    const int oz_S = plan->ozaki_slices < 0 ? c.oz_dm_slices : (c.oz_dm_slices > 0 ? plan->ozaki_slices : 0);
+    const int auto_S = white ? c.oz_wd_slices : c.oz_dm_slices;
+    const int oz_S = plan->ozaki_slices < 0 ? auto_S : (auto_S > 0 ? plan->ozaki_slices : 0);
     if (oz_S > 0 && plan->ozaki_dm && Bc >= OZAKI_MIN_BATCH) {
       // split-integer GEMM on tcgen05, as for the dense metal matrices (run_corr_front)
-      OzakiOperand& ob = residual ? c.oz_dmat_masked : c.oz_dmat;
+      OzakiOperand& ob = residual ? (white ? c.oz_wd : c.oz_dmat_masked) : c.oz_dmat;
       if (ob.S != oz_S || ob.src != dm.as<double>()) {
         VG_TRY(ozaki_slice(ob, dm.as<double>(), c.ld_model, rows, rows, c.n_model, oz_S, st));
         ob.src = dm.as<double>();
@@ -2211,10 +2337,10 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
   pa.bb = bb_dev(c); pa.n_dist = c.n_dist;
   pa.pfull = plan->w_pfull.as<double>(); pa.npf = plan->npf; pa.idx_bao_amp = plan->idx_bao_amp;
   pa.direct = plan->direct_mode ? 1 : 0;
-  pa.data = residual ? c.d_data.as<double>() : nullptr;
+  pa.data = residual ? (c.whitened ? c.d_wdata : c.d_data).as<double>() : nullptr;
   if (residual && mock_idx) {
     VG_REQUIRE(c.n_mocks > 0, "vg_chi2_batch_mc: correlation without mocks (vg_corr_set_mocks)");
-    pa.data = c.d_mocks.as<double>(); pa.mock_idx = mock_idx; pa.data_stride = c.n_mask;
+    pa.data = (c.whitened ? c.d_wmocks : c.d_mocks).as<double>(); pa.mock_idx = mock_idx; pa.data_stride = c.n_mask;
   }
   pa.n_out = residual ? c.n_mask : c.n_dist;
   pa.ldo = ldo; pa.ncols = ncols; pa.B = Bc; pa.out = out;
@@ -2253,6 +2379,10 @@ int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* in
 
 int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi2_dev, int* status_dev,
                cudaStream_t st, const int* mock_idx = nullptr) {
+  // operands that follow the data / covariance / mocks / options (never inside a graph capture: a
+  // state change drops the graphs and their call counts, so the first call after it runs here)
+  for (auto& cp : plan->corrs)
+    if (cp->white_dirty && cp->n_mask > 0) VG_TRY(rebuild_whitened(plan, *cp, st));
   VG_TRY(expand_params(plan, theta_dev, Bc, status_dev, st));
   int first = 1;
   int col0 = 0;
@@ -2271,7 +2401,7 @@ int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi
       VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, st, mock_idx,
                            status_dev, y_add));
       VG_TRY(quad_form(plan, plan->w_diff.as<double>(), c.n_mask, c.ld_mask,
-                       c.has_invcov ? c.d_invcov.as<double>() : nullptr, Bc, chi2_dev, !first, st));
+                       (c.has_invcov && !c.whitened) ? c.d_invcov.as<double>() : nullptr, Bc, chi2_dev, !first, st));
       first = 0;
     }
   }
@@ -2303,7 +2433,8 @@ int chi2_chunk_small(vg_plan* plan, const double* theta_dev, long long Bc, doubl
   const long long key = Bc | ((long long)plan->use_moments << 20) | ((long long)plan->fold_metals << 21) |
                         ((long long)plan->direct_mode << 22) | ((long long)(mock_idx != nullptr) << 23) |
                         ((long long)(plan->ozaki_slices + 1) << 24) | ((long long)plan->ozaki_dm << 30) |
-                        ((long long)plan->vt_now << 31) | ((long long)plan->fuse_dm_metals << 32);
+                        ((long long)plan->vt_now << 31) | ((long long)plan->fuse_dm_metals << 32) |
+                        ((long long)plan->whiten << 33);
   vg_plan::GraphEntry& g = plan->graphs[key];
   if (g.exec && g.generation != g_alloc_generation) {     // a buffer moved since the capture
     cudaGraphExecDestroy(g.exec);
@@ -2401,6 +2532,7 @@ int vg_corr_set_mocks(vg_plan* plan, int32_t corr, int32_t n_mocks, const double
   plan->drop_graphs();
   VG_TRY(upload(c.d_mocks, mocks, (size_t)n_mocks * c.n_mask));
   c.n_mocks = n_mocks;
+  c.white_dirty = true;
   return VG_OK;
 }
 
@@ -2560,6 +2692,12 @@ int vg_corr_fused_metal_operator(const vg_plan* plan, int32_t corr, int32_t* dig
   if (bound_per_digits)
     for (int S = 0; S <= vg::OZ_MAX_S; ++S) bound_per_digits[S] = c.oz_fused_bound[S];
   return c.n_mask;
+}
+
+int vg_corr_whitened(const vg_plan* plan, int32_t corr) {
+  if (!plan || corr < 0 || corr >= (int)plan->corrs.size()) return 0;
+  const Corr& c = *plan->corrs[corr];
+  return (c.whitened && !c.white_dirty) ? 1 : 0;
 }
 
 int vg_plan_velo_tables_active(const vg_plan* plan) { return plan && plan->vt_now ? 1 : 0; }

@@ -273,22 +273,23 @@ __global__ void __launch_bounds__(GEMM_THREADS, BM == 128 ? 1 : 2) dgemm_tn_kern
   }
 }
 
-// dst[j][i] = src[i][j] on an n x n block (32 x 32 tiles through shared memory); block (32, 8)
-__global__ void transpose_kernel(const double* __restrict__ src, long long src_ld, int n, double* __restrict__ dst,
-                                 long long dst_ld) {
+// dst[j][i] = src[i][j] for i < rows, j < cols (32 x 32 tiles through shared memory); block (32, 8),
+// grid (ceil(cols / 32), ceil(rows / 32))
+__global__ void transpose_kernel(const double* __restrict__ src, long long src_ld, int rows, int cols,
+                                 double* __restrict__ dst, long long dst_ld) {
   __shared__ double tile[32][33];
   const int x = blockIdx.x * 32 + threadIdx.x;
 #pragma unroll
   for (int k = 0; k < 32; k += 8) {
     const int y = blockIdx.y * 32 + threadIdx.y + k;
-    if (x < n && y < n) tile[threadIdx.y + k][threadIdx.x] = src[(long long)y * src_ld + x];
+    if (x < cols && y < rows) tile[threadIdx.y + k][threadIdx.x] = src[(long long)y * src_ld + x];
   }
   __syncthreads();
   const int xo = blockIdx.y * 32 + threadIdx.x;
 #pragma unroll
   for (int k = 0; k < 32; k += 8) {
     const int yo = blockIdx.x * 32 + threadIdx.y + k;
-    if (xo < n && yo < n) dst[(long long)yo * dst_ld + xo] = tile[threadIdx.x][threadIdx.y + k];
+    if (xo < rows && yo < cols) dst[(long long)yo * dst_ld + xo] = tile[threadIdx.x][threadIdx.y + k];
   }
 }
 

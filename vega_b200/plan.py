@@ -902,6 +902,24 @@ class DevicePlan:
                 inv = _f64(proj.T @ inv @ proj)
         _lib.check(self.lib.vg_corr_set_data(self.handle, ci, mask_idx.size, _dptr(mask_idx), _dptr(vec),
                                              _dptr(inv) if inv is not None else None))
+        # a square root of the matrix just uploaded: the device folds it into its operators and drops
+        # the product with C^-1 (vg_corr_set_whitening; per-correlation covariances only -- and not the
+        # projected, singular matrix of marginalize-in-fit)
+        vega = self.builder.vega
+        if inv is not None and proj is None and not getattr(vega, '_use_global_cov', False):
+            w = self._whitening(inv)
+            if w is not None:
+                _lib.check(self.lib.vg_corr_set_whitening(self.handle, ci, mask_idx.size, _dptr(w)))
+
+    def _whitening(self, inv):
+        """Upper Cholesky factor w of inv (inv = w^T w) or None when inv is not positive definite."""
+        torch = self.torch
+        try:
+            low = torch.linalg.cholesky(torch.as_tensor(inv, dtype=torch.float64, device=self.device))
+        except Exception:
+            return None
+        w = low.T.contiguous().cpu().numpy()
+        return _f64(w) if np.all(np.isfinite(w)) else None
 
     def finalize(self):
         _lib.check(self.lib.vg_plan_finalize(self.handle, self._stream()))
@@ -941,6 +959,10 @@ class DevicePlan:
         digits = C.c_int32(0)
         rows = self.lib.vg_corr_fused_metal_operator(self.handle, ci, C.byref(digits), None)
         return rows, digits.value
+
+    def whitened(self, ci):
+        """True when the chi2 path of correlation ci runs on whitened operands (VG_OPT_WHITEN)."""
+        return bool(self.lib.vg_corr_whitened(self.handle, ci))
 
     def velo_tables_active(self):
         """True when the last batch call ran on the velocity-dispersion tables."""
