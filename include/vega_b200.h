@@ -248,6 +248,10 @@ int vg_corr_set_broadband(vg_plan* plan, int32_t corr, int32_t n_terms, const vg
  * to swap in a Monte Carlo mock (vega/vega_interface.py:296-312). */
 int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t* mask_idx,
                      const double* data, const double* invcov);
+/* A new data vector alone -- a Monte Carlo mock swapped in while mask and covariance stay
+ * (vega/vega_interface.py:296-312 reads data.masked_mc_mock on every call): data[n_mask], same mask as
+ * the last vg_corr_set_data.  Keeps the inverse covariance, its square root and everything built on them. */
+int vg_corr_set_data_vector(vg_plan* plan, int32_t corr, int32_t n_mask, const double* data);
 /* A square root of the inverse covariance just given to vg_corr_set_data: w[n_mask][n_mask] with
  * invcov = w^T w (e.g. the transposed lower Cholesky factor), or NULL to clear it.  Optional; with it
  * (and VG_OPT_WHITEN) the chi2 (d - m)^T C^-1 (d - m) of vega/vega_interface.py:294-319 is evaluated as

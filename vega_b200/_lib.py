@@ -112,6 +112,7 @@ _SIGNATURES = {
     'vg_corr_set_broadband': (C.c_int, [_PTR, i32, i32, _PTR, i32, _PTR, i32, _PTR, _PTR, _PTR]),
     'vg_corr_set_data': (C.c_int, [_PTR, i32, i32, _PTR, _PTR, _PTR]),
     'vg_corr_set_whitening': (C.c_int, [_PTR, i32, i32, _PTR]),
+    'vg_corr_set_data_vector': (C.c_int, [_PTR, i32, i32, _PTR]),
     'vg_corr_whitened': (C.c_int, [_PTR, i32]),
     'vg_plan_set_global_invcov': (C.c_int, [_PTR, i32, _PTR]),
     'vg_plan_finalize': (C.c_int, [_PTR, _PTR]),

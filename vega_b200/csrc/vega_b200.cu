@@ -224,6 +224,7 @@ struct Corr {
   // operator is built on d_wd, d_wdata = W d, d_wmocks = mocks W^T.  The chi2 GEMM disappears.
   bool has_white = false;        // a square root of the inverse covariance was given (vg_corr_set_whitening)
   bool white_dirty = false;      // the whitened operands are out of date (rebuilt at the next chi2 call)
+  bool wdata_dirty = false;      // only W d / the whitened mocks are out of date
   bool whitened = false;         // the residual path runs on the whitened operands
   DevBuf d_white, d_wd, d_wdata, d_wmocks;
   OzakiOperand oz_wd;
@@ -367,6 +368,7 @@ int ozaki_budget(vg_plan* plan, Corr& c, cudaStream_t st);
 int ozaki_budget_dm(vg_plan* plan, Corr& c, cudaStream_t st);
 int build_fused_metal_operator(vg_plan* plan, Corr& c, cudaStream_t st);
 int rebuild_whitened(vg_plan* plan, Corr& c, cudaStream_t st);
+int rewhiten_data(vg_plan* plan, Corr& c, cudaStream_t st);
 void flag_velo_table_candidates(vg_plan* plan, Corr& c);
 int build_velo_tables(vg_plan* plan, Corr& c, cudaStream_t st);
 int launch_metal_rp(Corr& c, const double* xmet, int n_metal, const double* A, long long B, double* met,
@@ -950,6 +952,16 @@ int vg_corr_set_data(vg_plan* plan, int32_t corr, int32_t n_mask, const int32_t*
     c.has_white = false;
   }
   c.white_dirty = true;
+  return VG_OK;
+}
+
+int vg_corr_set_data_vector(vg_plan* plan, int32_t corr, int32_t n_mask, const double* data) {
+  VG_CORR(plan, corr);
+  VG_REQUIRE(data && n_mask == c.n_mask && c.d_data.p, "vg_corr_set_data_vector: call vg_corr_set_data first (same mask)");
+  plan->drop_graphs();
+  VG_CUDA_CHECK(cudaDeviceSynchronize());
+  VG_CUDA_CHECK(cudaMemcpy(c.d_data.p, data, (size_t)n_mask * 8, cudaMemcpyHostToDevice));
+  c.wdata_dirty = true;
   return VG_OK;
 }
 
@@ -2111,8 +2123,17 @@ int whiten_rows(vg_plan* plan, Corr& c, const double* rows, int n, DevBuf& out, 
 // correlation), a distortion matrix and no post-distortion broadband term (it sits between D and W).
 // Called with the correlation's state changed (finalize, new data / covariance / mocks / option);
 // rebuilds the fused operator too, which depends on the choice.
+int rewhiten_data(vg_plan* plan, Corr& c, cudaStream_t st) {
+  c.wdata_dirty = false;
+  if (!c.whitened) return VG_OK;
+  VG_TRY(whiten_rows(plan, c, c.d_data.as<double>(), 1, c.d_wdata, st));
+  if (c.n_mocks > 0) VG_TRY(whiten_rows(plan, c, c.d_mocks.as<double>(), c.n_mocks, c.d_wmocks, st));
+  return VG_OK;
+}
+
 int rebuild_whitened(vg_plan* plan, Corr& c, cudaStream_t st) {
   c.white_dirty = false;
+  c.wdata_dirty = false;
   bool ok = plan->whiten && c.has_white && c.has_invcov && c.has_dmat && !plan->has_global && c.n_mask > 0 &&
             c.d_dmat_masked.p != nullptr;
   for (const vg_bb_term& t : c.bb_terms)
@@ -2381,8 +2402,10 @@ int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi
                cudaStream_t st, const int* mock_idx = nullptr) {
   // operands that follow the data / covariance / mocks / options (never inside a graph capture: a
   // state change drops the graphs and their call counts, so the first call after it runs here)
-  for (auto& cp : plan->corrs)
+  for (auto& cp : plan->corrs) {
     if (cp->white_dirty && cp->n_mask > 0) VG_TRY(rebuild_whitened(plan, *cp, st));
+    else if (cp->wdata_dirty) VG_TRY(rewhiten_data(plan, *cp, st));
+  }
   VG_TRY(expand_params(plan, theta_dev, Bc, status_dev, st));
   int first = 1;
   int col0 = 0;
@@ -2532,7 +2555,7 @@ int vg_corr_set_mocks(vg_plan* plan, int32_t corr, int32_t n_mocks, const double
   plan->drop_graphs();
   VG_TRY(upload(c.d_mocks, mocks, (size_t)n_mocks * c.n_mask));
   c.n_mocks = n_mocks;
-  c.white_dirty = true;
+  c.wdata_dirty = true;
   return VG_OK;
 }
 
@@ -2697,7 +2720,7 @@ int vg_corr_fused_metal_operator(const vg_plan* plan, int32_t corr, int32_t* dig
 int vg_corr_whitened(const vg_plan* plan, int32_t corr) {
   if (!plan || corr < 0 || corr >= (int)plan->corrs.size()) return 0;
   const Corr& c = *plan->corrs[corr];
-  return (c.whitened && !c.white_dirty) ? 1 : 0;
+  return (c.whitened && !c.white_dirty) ? 1 : 0;     // (a dirty data vector alone keeps the operators)
 }
 
 int vg_plan_velo_tables_active(const vg_plan* plan) { return plan && plan->vt_now ? 1 : 0; }
