@@ -127,12 +127,29 @@ class ClockSampler:
         self.gpu = gpu_index
         self.file = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
         self.proc = None
+        self.first = 0
+
+    def _lines(self):
+        try:
+            return len([r for r in Path(self.file.name).read_text().splitlines() if r.strip()])
+        except OSError:
+            return 0
+
+    def mark(self, wait_s=3.0):
+        """Samples from here on count (nvidia-smi takes a few hundred ms to deliver its first line: wait
+        for it, so that the load that follows is sampled from its start)."""
+        if self.proc is None:
+            return
+        t0 = time.perf_counter()
+        while self._lines() == 0 and time.perf_counter() - t0 < wait_s:
+            time.sleep(0.02)
+        self.first = self._lines()
 
     def start(self):
         try:
             self.proc = subprocess.Popen(
                 ['nvidia-smi', f'--id={self.gpu}', f'--query-gpu={self.QUERY}', '--format=csv,noheader,nounits',
-                 '-lms', '100'], stdout=self.file, stderr=subprocess.DEVNULL)
+                 '-lms', '50'], stdout=self.file, stderr=subprocess.DEVNULL)
         except OSError:
             self.proc = None
 
@@ -142,7 +159,7 @@ class ClockSampler:
         self.proc.terminate()
         self.proc.wait()
         self.file.flush()
-        rows = [r.split(', ') for r in Path(self.file.name).read_text().strip().splitlines() if r.strip()]
+        rows = [r.split(', ') for r in Path(self.file.name).read_text().strip().splitlines() if r.strip()][self.first:]
         os.unlink(self.file.name)
         sm, mx, reasons = [], [], set()
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
@@ -509,13 +526,17 @@ def run_c5(vega, fiducial, torch, dd, world, n_mocks):
     vega.monte_carlo = False
     theta = res['theta']
     ndof = int(sum(int(d.data_mask.sum()) for d in vega.data.values())) - len(mc.names)
+    ok = np.asarray(res['converged'], dtype=bool) & np.all(res['errors'] > 0, axis=1)   # pulls: converged fits only
+    if not ok.any():
+        ok[:] = True
     return {'mocks': n_mocks, 'parameters': len(mc.names), 'scaling': 'strong', 'draw_s': t_draw, 'fit_wall_s': dt,
             'fits_per_s': n_mocks / dt, 'converged': int(np.sum(res['converged'])),
             'per_rank_fit_s': [r[0] for r in per_rank], 'per_rank_chi2_evaluations': [int(r[1]) for r in per_rank],
             'mean_iterations': float(np.mean(res['n_iter'])), 'mean_fval': float(np.mean(res['fval'])),
             'degrees_of_freedom': ndof,
-            'mean_pull_of_bestfit': {n: float(np.mean((theta[:, j] - vega.params[n]) / np.maximum(res['errors'][:, j], 1e-300)))
+            'mean_pull_of_bestfit': {n: float(np.mean((theta[ok, j] - vega.params[n]) / np.maximum(res['errors'][ok, j], 1e-300)))
                                      for j, n in enumerate(mc.names)},
+            'mocks_in_the_mean_pull': int(ok.sum()),
             'method': 'quasi-Newton lock-step: gradient stencils (2P+1), start Hessian shared by the mocks, one '
                       'finishing Hessian stencil (P^2+P+1) per mock'}
 
@@ -589,6 +610,10 @@ def main():
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
+        clocks.mark()
+    dd.barrier()
+    for _ in range(3):            # (the wait for the sampler's first line left the GPU idle)
+        step_device()
     lib.vg_profile_enable(engine.handle, 1)
     lib.vg_launch_count(1)
     ms_per_step = timed_device(torch, dd, step_device, args.steps)
@@ -597,7 +622,15 @@ def main():
     cnt_stage = (C.c_int64 * 16)()
     lib.vg_profile_read(engine.handle, ms_stage, cnt_stage)
     lib.vg_profile_enable(engine.handle, 0)
+    # K steps of ~5 ms are shorter than the sampler's period: the SAME step keeps running (untimed) until
+    # the sampler has seen 0.6 s of this load, so the clocks line describes the load that was timed
+    t_load = time.perf_counter()
+    while time.perf_counter() - t_load < 0.6:
+        step_device()
+    torch.cuda.synchronize()
     clock_info = clocks.stop() if rank == 0 else None
+    if clock_info is not None:
+        clock_info['window'] = 'the timed steps plus 0.6 s of the same step, untimed (50 ms sampling period)'
 
     # ---- timed region 2: end to end through the public API with host buffers; at N > 1 the
     # per-rank chi2 values are gathered (device all-gather, read back) inside the timed region ----
