@@ -293,7 +293,7 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
  * s32 accumulation in TMEM) and are recombined in FP64 (csrc/vg_ozaki.cuh).  -1: per correlation,
  * the fewest digits whose worst-case truncation bound at the plan parameters is below 5e-11 max|xi|
  * (vg_corr_ozaki_slices); 3..8: that many digits; 0: the FP64 DMMA kernel (the parity reference).
- * Batches below 16 vectors always take the DMMA kernel. */
+ * Batches below VG_OPT_OZAKI_MIN_BATCH vectors take the DMMA kernel. */
 #define VG_OPT_OZAKI 3
 /* VG_OPT_OZAKI_DM (default 1): the distortion-matrix product (vega/model.py:142-143) takes the same
  * split-integer kernel, with the digits VG_OPT_OZAKI selects (automatic: its own bound against
@@ -320,6 +320,17 @@ int vg_plan_set_chunk(vg_plan* plan, int64_t chunk);
 /* VG_OPT_WHITEN (default 1): use the square root given to vg_corr_set_whitening (see there); 0 keeps the
  * product with C^-1 (the parity reference). */
 #define VG_OPT_WHITEN 7
+/* VG_OPT_OZAKI_MIN_BATCH (default 64, the measured crossover): chunks with fewer parameter vectors take the FP64 DMMA kernel for
+ * the products VG_OPT_OZAKI / VG_OPT_OZAKI_DM name (a thin batch streams the FP64 operator once; the
+ * split-integer kernel pays for all digit products of a 64-vector tile whatever the batch). */
+#define VG_OPT_OZAKI_MIN_BATCH 8
+/* VG_OPT_LANES (default 1): chunks below min(64, VG_OPT_OZAKI_MIN_BATCH) vectors -- a single vector, a
+ * gradient stencil: latency-bound kernels -- spread the correlations over up to four lanes (correlation
+ * i on lane i % 4; lanes 1..3 are streams of the plan with their own workspace, forked from and joined
+ * to the caller's stream, inside the CUDA graph of the pass too); the chi2 of the lanes are added at the
+ * end (same values: the per-correlation arithmetic does not change).  0 keeps every correlation on the
+ * caller's stream. */
+#define VG_OPT_LANES 9
 int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value);
 /* Isotropic P(k) [nk] for the direct mode (e.g. from a Boltzmann code, the `direct_pk`
  * argument of VegaInterface.compute_model / chi2 / log_lik); host pointer, copied. */

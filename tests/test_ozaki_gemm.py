@@ -118,7 +118,7 @@ def test_metal_gemm_option_matches_dmma():
     assert np.max(np.abs(vega.chi2_batch(theta) - ref)) <= 1e-6 * max(1.0, np.max(np.abs(ref)) / 1e4)
     engine.set_option(_lib.OPT_OZAKI_DM, 1)
     # the oracle itself, on the vectors whose chi2 is of the order of the degrees of freedom (taken
-    # from the whole batch: fewer than 16 vectors would go to the DMMA kernel)
+    # from the whole batch: fewer than 64 vectors would go to the DMMA kernel)
     got = vega.chi2_batch(theta)[:4]
     for b in range(4):
         want = oracle.chi2(dict(zip(vega.theta_names, theta[b])))

@@ -17,7 +17,7 @@ out = {}
 for B in [1, 8, 33, 64, 128, 256, 513, 1024, 2048, 4096]:
     theta = synthetic.draw_theta(vega, B)
     tt = engine.theta_tensor(theta)
-    for _ in range(3):
+    for _ in range(6):      # two ordinary passes, the graph capture, its first replays
         engine.chi2_device(tt)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -14,6 +14,7 @@ VG_MAX_BB_TERMS = 8
 F_ARINYO, F_MCDONALD, F_GK, F_PEAKNL, F_FSGAUSS, F_FSEXP, F_VELO, F_KDAMP, F_MOCKGK = (1 << i for i in range(9))
 STATUS_BOUNDS, STATUS_ARINYO, STATUS_NONFINITE, STATUS_DEVICE = 1, 2, 4, 8
 OPT_MOMENTS, OPT_DIRECT_PK, OPT_FOLD_METALS, OPT_OZAKI, OPT_OZAKI_DM, OPT_VELO_TABLES, OPT_FUSE_DM_METALS, OPT_WHITEN = 0, 1, 2, 3, 4, 5, 6, 7
+OPT_OZAKI_MIN_BATCH, OPT_LANES = 8, 9
 ERR_CUDA, ERR_ARG, ERR_STATE = 1, 2, 3
 STATIC_SCRATCH_DOUBLES = 1 << 21      # VG_STATIC_SCRATCH_DOUBLES of include/vega_b200.h
 

@@ -75,7 +75,13 @@ struct DevBuf {
     ++g_alloc_generation;
     VG_CUDA_CHECK(cudaMalloc(&p, n));
     bytes = n;
-    if (zero) VG_CUDA_CHECK(cudaMemset(p, 0, n));
+    if (zero) {
+      // the fill runs on the legacy default stream: waited for here, because the buffer may be used next
+      // on a non-blocking stream (the graph-capture stream, the lanes of a thin batch) that does not
+      // order itself after it
+      VG_CUDA_CHECK(cudaMemset(p, 0, n));
+      VG_CUDA_CHECK(cudaStreamSynchronize(cudaStreamLegacy));
+    }
     return VG_OK;
   }
   int ensure(size_t n) { return n <= bytes ? VG_OK : alloc(n); }
@@ -281,6 +287,8 @@ struct vg_plan {
   std::vector<int> theta_cols_host;
   DevBuf d_vt_flag, w_vtw;       // range-check flag; weights [n_vt][chunk][ldw]
   bool ozaki_dm = true;          // VG_OPT_OZAKI_DM: the distortion product on the split-integer kernel too
+  int ozaki_min_batch = 64;      // VG_OPT_OZAKI_MIN_BATCH: smaller chunks take the FP64 DMMA kernel (measured
+                                 // crossover on C2 and C3: profiles/r02_small_batches.json)
   int ozaki_slices = -1;         // VG_OPT_OZAKI: digits of the split-integer metal GEMM (0: DMMA, -1: per
                                  // correlation, the fewest digits that meet the truncation budget)
   OzakiOperand oz_A;             // workspace: digit planes of the batch operand
@@ -307,6 +315,19 @@ struct vg_plan {
     for (auto& kv : graphs) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
     graphs.clear();
   }
+  // Extra lanes for thin batches (chi2_chunk): the kernels of a single vector or of a gradient stencil
+  // are latency bound, so correlation ci runs on lane ci % (1 + EXTRA_LANES); lanes 1.. have their own
+  // stream and their own copy of the per-correlation workspace (swapped into the w_* members while
+  // their launches are issued)
+  static constexpr int EXTRA_LANES = 3;
+  struct Lane {
+    DevBuf w_pkell, w_tables, w_core, w_xmet, w_met, w_x, w_y, w_diff, w_partial, w_split, w_fold, w_mety, w_vtw;
+    DevBuf chi2;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+    long long chunk = 0;
+  } lanes[EXTRA_LANES];
+  bool two_lanes = true;         // VG_OPT_LANES (VG_LANES=0 in the environment turns the second lane off for good)
   // optional per-stage timing with CUDA events (bench.py roofline figures)
   bool profile = false;
   struct ProfRec { int tag; cudaEvent_t e0, e1; };
@@ -673,6 +694,11 @@ int vg_plan_destroy(vg_plan* plan) {
   if (!plan) return VG_OK;
   plan->drop_graphs();
   if (plan->gstream) cudaStreamDestroy(plan->gstream);
+  for (auto& l : plan->lanes) {
+    if (l.stream) cudaStreamDestroy(l.stream);
+    if (l.fork) cudaEventDestroy(l.fork);
+    if (l.join) cudaEventDestroy(l.join);
+  }
   if (plan->pinned) cudaFreeHost(plan->pinned);
   delete plan;
   return VG_OK;
@@ -697,6 +723,12 @@ int vg_plan_set_option(vg_plan* plan, int32_t option, int32_t value) {
     return VG_OK;
   }
   if (option == VG_OPT_OZAKI_DM) { plan->ozaki_dm = value != 0; return VG_OK; }
+  if (option == VG_OPT_LANES) { plan->two_lanes = value != 0; return VG_OK; }
+  if (option == VG_OPT_OZAKI_MIN_BATCH) {
+    VG_REQUIRE(value >= 1, "VG_OPT_OZAKI_MIN_BATCH: a batch size >= 1");
+    plan->ozaki_min_batch = value;
+    return VG_OK;
+  }
   if (option == VG_OPT_VELO_TABLES) { plan->velo_tables = value != 0; return VG_OK; }
   if (option == VG_OPT_FUSE_DM_METALS) { plan->fuse_dm_metals = value != 0; return VG_OK; }
   if (option == VG_OPT_WHITEN) {
@@ -1234,7 +1266,6 @@ int gemm_auto(vg_plan* plan, const double* A, long long lda, const double* B, lo
   return VG_OK;
 }
 
-constexpr int OZAKI_MIN_BATCH = 16;      // below: the DMMA kernel's batch-sized tiles stream the operator once
 // ---- split-integer GEMM on tcgen05 (vg_ozaki.cuh) ------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -1776,7 +1807,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   const int metal_ldo = fuse ? c.ld_mask : c.ld_model;
   double* metal_out = fuse ? plan->w_mety.as<double>() : plan->w_met.as<double>();
   if (L.n_metal > 0) {
-    const bool use_ozaki = c.metal_dense && oz_S > 0 && Bc >= OZAKI_MIN_BATCH;
+    const bool use_ozaki = c.metal_dense && oz_S > 0 && Bc >= plan->ozaki_min_batch;
     // (the split-integer branch times its two parts itself: PROF_NONE keeps this scope silent)
     ProfScope prof(plan, use_ozaki ? PROF_NONE : (c.metal_rp ? PROF_METAL_RP : (c.metal_dense ? PROF_METAL : PROF_ELEM)), st);
     if (c.metal_rp) {
@@ -2325,7 +2356,7 @@ int run_corr_back(vg_plan* plan, Corr& c, long long Bc, bool residual, double* o
     y_is_masked = residual ? 1 : 0;
     const int auto_S = white ? c.oz_wd_slices : c.oz_dm_slices;
     const int oz_S = plan->ozaki_slices < 0 ? auto_S : (auto_S > 0 ? plan->ozaki_slices : 0);
-    if (oz_S > 0 && plan->ozaki_dm && Bc >= OZAKI_MIN_BATCH) {
+    if (oz_S > 0 && plan->ozaki_dm && Bc >= plan->ozaki_min_batch) {
       // split-integer GEMM on tcgen05, as for the dense metal matrices (run_corr_front)
       OzakiOperand& ob = residual ? (white ? c.oz_wd : c.oz_dmat_masked) : c.oz_dmat;
       if (ob.S != oz_S || ob.src != dm.as<double>()) {
@@ -2398,6 +2429,60 @@ int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* in
   return VG_OK;
 }
 
+// ---- second lane of the chi2 pass (vg_plan::Lane) ----
+constexpr long long LANE_MAX_B = 63;
+bool lanes_enabled() {
+  static const bool on = [] { const char* e = std::getenv("VG_LANES"); return !(e && e[0] == '0'); }();
+  return on;
+}
+void swap_lane(vg_plan* plan, vg_plan::Lane& l) {
+  plan->w_pkell.swap(l.w_pkell); plan->w_tables.swap(l.w_tables); plan->w_core.swap(l.w_core);
+  plan->w_xmet.swap(l.w_xmet); plan->w_met.swap(l.w_met); plan->w_x.swap(l.w_x); plan->w_y.swap(l.w_y);
+  plan->w_partial.swap(l.w_partial); plan->w_split.swap(l.w_split); plan->w_fold.swap(l.w_fold);
+  plan->w_mety.swap(l.w_mety); plan->w_vtw.swap(l.w_vtw);
+  if (!plan->has_global) plan->w_diff.swap(l.w_diff);     // (a global covariance: one residual row for all)
+}
+struct LaneSwap {       // a lane's workspace stands in for the plan's while its launches are issued
+  vg_plan* plan; vg_plan::Lane* lane;
+  LaneSwap(vg_plan* p, vg_plan::Lane* l) : plan(p), lane(l) { if (lane) swap_lane(plan, *lane); }
+  ~LaneSwap() { if (lane) swap_lane(plan, *lane); }
+};
+int ensure_lane(vg_plan* plan, vg_plan::Lane& l, long long Bc_) {
+  if (!l.stream) {
+    VG_CUDA_CHECK(cudaStreamCreateWithFlags(&l.stream, cudaStreamNonBlocking));
+    VG_CUDA_CHECK(cudaEventCreateWithFlags(&l.fork, cudaEventDisableTiming));
+    VG_CUDA_CHECK(cudaEventCreateWithFlags(&l.join, cudaEventDisableTiming));
+  }
+  if (Bc_ <= l.chunk) return VG_OK;
+  const size_t Bc = (size_t)LANE_MAX_B;
+  size_t pkell = 0, tables = 0, core = 0, xmet = 0, met = 0, y = 0;
+  for (auto& cp : plan->corrs) {
+    const Corr& c = *cp;
+    const Hankel& h = *plan->hankels[c.hankel_id];
+    const size_t E = c.evals.size();
+    pkell = std::max(pkell, (size_t)Bc * E * plan->n_ell * plan->nk_pad);
+    tables = std::max(tables, (size_t)Bc * E * plan->n_ell * 2 * h.n_out_pad);
+    core = std::max(core, (size_t)2 * Bc * c.ld_model);
+    xmet = std::max(xmet, (size_t)Bc * std::max(c.n_metal, 1) * c.ld_model);
+    met = std::max(met, (size_t)Bc * c.ld_model);
+    y = std::max(y, (size_t)Bc * std::max(c.ld_dist, c.ld_mask));
+  }
+  VG_TRY(l.w_pkell.alloc(pkell * 8));
+  VG_TRY(l.w_tables.alloc(tables * 8));
+  VG_TRY(l.w_core.alloc(core * 8));
+  VG_TRY(l.w_xmet.alloc(xmet * 8));
+  VG_TRY(l.w_met.alloc(met * 8));
+  VG_TRY(l.w_fold.alloc(met * 8));
+  VG_TRY(l.w_x.alloc(met * 8));
+  VG_TRY(l.w_y.alloc(y * 8));
+  VG_TRY(l.w_mety.alloc(y * 8));
+  VG_TRY(l.w_diff.alloc(y * 8));
+  VG_TRY(l.w_partial.alloc((size_t)Bc * 256 * 8));
+  VG_TRY(l.chi2.alloc((size_t)Bc * 8));
+  l.chunk = LANE_MAX_B;
+  return VG_OK;
+}
+
 int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi2_dev, int* status_dev,
                cudaStream_t st, const int* mock_idx = nullptr) {
   // operands that follow the data / covariance / mocks / options (never inside a graph capture: a
@@ -2407,26 +2492,55 @@ int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi
     else if (cp->wdata_dirty) VG_TRY(rewhiten_data(plan, *cp, st));
   }
   VG_TRY(expand_params(plan, theta_dev, Bc, status_dev, st));
-  int first = 1;
+  // thin batches: the correlations spread over lanes (below the batch size of the split-integer
+  // GEMMs, whose digit planes of the batch are one plan-wide workspace)
+  const bool laned = plan->two_lanes && lanes_enabled() && !plan->profile && plan->corrs.size() > 1 &&
+                     Bc <= std::min<long long>(LANE_MAX_B, plan->ozaki_min_batch - 1);
+  const int n_lanes = laned ? (int)std::min<size_t>(1 + vg_plan::EXTRA_LANES, plan->corrs.size()) : 1;
+  for (int l = 1; l < n_lanes; ++l) {
+    vg_plan::Lane& lane = plan->lanes[l - 1];
+    VG_TRY(ensure_lane(plan, lane, Bc));
+    VG_CUDA_CHECK(cudaEventRecord(lane.fork, st));
+    VG_CUDA_CHECK(cudaStreamWaitEvent(lane.stream, lane.fork, 0));
+  }
+  int first[1 + vg_plan::EXTRA_LANES] = {1, 1, 1, 1};
   int col0 = 0;
-  for (auto& cp : plan->corrs) {
-    Corr& c = *cp;
-    VG_REQUIRE(c.n_mask > 0, "vg_chi2_batch: correlation without data (vg_corr_set_data)");
-    bool fused = false;
-    VG_TRY(run_corr_front(plan, c, Bc, status_dev, st, 99, -1, 0, &fused));
-    const double* y_add = fused ? plan->w_mety.as<double>() : nullptr;
-    if (plan->has_global) {
-      // residuals of all correlations side by side: [Bc][ld_total]
-      VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>() + col0, plan->ld_total,
-                           c.n_mask, st, mock_idx, status_dev, y_add));
-      col0 += c.n_mask;
-    } else {
-      VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, st, mock_idx,
-                           status_dev, y_add));
-      VG_TRY(quad_form(plan, plan->w_diff.as<double>(), c.n_mask, c.ld_mask,
-                       (c.has_invcov && !c.whitened) ? c.d_invcov.as<double>() : nullptr, Bc, chi2_dev, !first, st));
-      first = 0;
-    }
+  int rc = VG_OK;
+  for (size_t ci = 0; ci < plan->corrs.size() && rc == VG_OK; ++ci) {
+    Corr& c = *plan->corrs[ci];
+    const int alt = (int)(ci % n_lanes);
+    vg_plan::Lane* lane = alt ? &plan->lanes[alt - 1] : nullptr;
+    cudaStream_t s = alt ? lane->stream : st;
+    LaneSwap guard(plan, lane);
+    rc = [&]() -> int {
+      VG_REQUIRE(c.n_mask > 0, "vg_chi2_batch: correlation without data (vg_corr_set_data)");
+      bool fused = false;
+      VG_TRY(run_corr_front(plan, c, Bc, status_dev, s, 99, -1, 0, &fused));
+      const double* y_add = fused ? plan->w_mety.as<double>() : nullptr;
+      if (plan->has_global) {
+        // residuals of all correlations side by side: [Bc][ld_total]
+        VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>() + col0, plan->ld_total,
+                             c.n_mask, s, mock_idx, status_dev, y_add));
+        col0 += c.n_mask;
+      } else {
+        VG_TRY(run_corr_back(plan, c, Bc, true, plan->w_diff.as<double>(), c.ld_mask, c.ld_mask, s, mock_idx,
+                             status_dev, y_add));
+        VG_TRY(quad_form(plan, plan->w_diff.as<double>(), c.n_mask, c.ld_mask,
+                         (c.has_invcov && !c.whitened) ? c.d_invcov.as<double>() : nullptr, Bc,
+                         alt ? lane->chi2.as<double>() : chi2_dev, !first[alt], s));
+        first[alt] = 0;
+      }
+      return VG_OK;
+    }();
+  }
+  for (int l = 1; l < n_lanes; ++l) {   // (joined on the error path too: a capture must not end with a stream forked)
+    cudaEventRecord(plan->lanes[l - 1].join, plan->lanes[l - 1].stream);
+    cudaStreamWaitEvent(st, plan->lanes[l - 1].join, 0);
+  }
+  VG_TRY(rc);
+  for (int l = 1; l < n_lanes && !plan->has_global; ++l) {
+    vg::add_vector_kernel<<<vg_cdiv(Bc, 256), 256, 0, st>>>(plan->lanes[l - 1].chi2.as<double>(), Bc, chi2_dev);
+    VG_LAUNCHED();
   }
   if (plan->has_global)
     VG_TRY(quad_form(plan, plan->w_diff.as<double>(), plan->n_total, plan->ld_total,

@@ -325,6 +325,12 @@ __global__ void chi2_partials_kernel(const double* __restrict__ partial, int n_t
   chi2[b] = (accumulate ? chi2[b] : 0.0) + s;
 }
 
+// chi2[b] += part[b]   (the correlations that ran on the second lane of a thin batch)
+__global__ void add_vector_kernel(const double* __restrict__ part, long long B, double* __restrict__ chi2) {
+  long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) chi2[b] += part[b];
+}
+
 // chi2[b] += sum_priors (theta - mean)^2 / sigma^2   (vega/vega_interface.py:423-446)
 __global__ void prior_kernel(const double* __restrict__ pfull, int npf, const int* __restrict__ cols,
                              const double* __restrict__ mean, const double* __restrict__ sigma,
