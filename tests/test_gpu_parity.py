@@ -655,13 +655,13 @@ def test_small_batches_replay_a_cuda_graph():
 
 
 def test_second_lane_of_thin_batches_changes_nothing():
-    """VG_OPT_LANES: below 64 vectors the correlations are spread over up to four streams, each with its
-    own workspace.  Same chi2 as with every correlation on one stream -- two correlations with their
+    """VG_OPT_LANES: the correlations of a chunk are spread over up to four streams, each with its own
+    workspace (digit planes of the split-integer GEMMs included: the 100-vector case).  Same chi2 as with every correlation on one stream -- two correlations with their
     own covariances (C2), four under one global covariance, first calls (ordinary launches) and
     CUDA-graph replays alike."""
     from helpers import set_fast_metals
     from vega_b200 import _lib, VegaInterface
-    vega, oracle, theta = make_c2(40, width=1.0)
+    vega, oracle, theta = make_c2(104, width=1.0)
     cases = [(vega, None, theta)]
     vega4 = VegaInterface('configs/full_configs/main.ini')
     set_fast_metals(vega4)
@@ -670,10 +670,10 @@ def test_second_lane_of_thin_batches_changes_nothing():
     synthetic.draw_mock_data(vega4, vega4.compute_model())
     names4 = ['bias_eta_LYA', 'beta_LYA', 'ap', 'at', 'bias_hcd', 'drp_QSO', 'bao_amp', 'bias_eta_SiII(1260)']
     base = np.array([vega4.params[n] for n in names4])
-    cases.append((vega4, names4, base * (1 + 0.03 * np.random.default_rng(3).standard_normal((40, len(names4))))))
+    cases.append((vega4, names4, base * (1 + 0.03 * np.random.default_rng(3).standard_normal((104, len(names4))))))
     for v, names, th in cases:
         engine = v._engine_for(tuple(names)) if names else v._engine_for()
-        for size in (1, 7, 33):
+        for size in (1, 7, 33, 100):
             out = {}
             for lanes in (1, 0, 1):
                 engine.set_option(_lib.OPT_LANES, lanes)

@@ -322,6 +322,7 @@ struct vg_plan {
   static constexpr int EXTRA_LANES = 3;
   struct Lane {
     DevBuf w_pkell, w_tables, w_core, w_xmet, w_met, w_x, w_y, w_diff, w_partial, w_split, w_fold, w_mety, w_vtw;
+    OzakiOperand oz_A;
     DevBuf chi2;
     cudaStream_t stream = nullptr;
     cudaEvent_t fork = nullptr, join = nullptr;
@@ -2430,7 +2431,14 @@ int quad_form(vg_plan* plan, const double* diff, int n, int ld, const double* in
 }
 
 // ---- second lane of the chi2 pass (vg_plan::Lane) ----
-constexpr long long LANE_MAX_B = 63;
+long long lane_max_batch() {      // largest chunk that is spread over lanes (VG_LANE_MAX_B in the environment)
+  static const long long v = [] {
+    const char* e = std::getenv("VG_LANE_MAX_B");
+    const long long x = e ? std::atoll(e) : 1024;
+    return std::max(1LL, std::min(x, 4096LL));
+  }();
+  return v;
+}
 bool lanes_enabled() {
   static const bool on = [] { const char* e = std::getenv("VG_LANES"); return !(e && e[0] == '0'); }();
   return on;
@@ -2440,6 +2448,9 @@ void swap_lane(vg_plan* plan, vg_plan::Lane& l) {
   plan->w_xmet.swap(l.w_xmet); plan->w_met.swap(l.w_met); plan->w_x.swap(l.w_x); plan->w_y.swap(l.w_y);
   plan->w_partial.swap(l.w_partial); plan->w_split.swap(l.w_split); plan->w_fold.swap(l.w_fold);
   plan->w_mety.swap(l.w_mety); plan->w_vtw.swap(l.w_vtw);
+  plan->oz_A.planes.swap(l.oz_A.planes); plan->oz_A.exps.swap(l.oz_A.exps);
+  std::swap(plan->oz_A.rows, l.oz_A.rows); std::swap(plan->oz_A.Kp, l.oz_A.Kp);
+  std::swap(plan->oz_A.S, l.oz_A.S); std::swap(plan->oz_A.src, l.oz_A.src);
   if (!plan->has_global) plan->w_diff.swap(l.w_diff);     // (a global covariance: one residual row for all)
 }
 struct LaneSwap {       // a lane's workspace stands in for the plan's while its launches are issued
@@ -2454,7 +2465,9 @@ int ensure_lane(vg_plan* plan, vg_plan::Lane& l, long long Bc_) {
     VG_CUDA_CHECK(cudaEventCreateWithFlags(&l.join, cudaEventDisableTiming));
   }
   if (Bc_ <= l.chunk) return VG_OK;
-  const size_t Bc = (size_t)LANE_MAX_B;
+  long long cap = 64;                   // sized in a few steps: 64, 128, ... vectors
+  while (cap < Bc_) cap *= 2;
+  const size_t Bc = (size_t)cap;
   size_t pkell = 0, tables = 0, core = 0, xmet = 0, met = 0, y = 0;
   for (auto& cp : plan->corrs) {
     const Corr& c = *cp;
@@ -2479,7 +2492,7 @@ int ensure_lane(vg_plan* plan, vg_plan::Lane& l, long long Bc_) {
   VG_TRY(l.w_diff.alloc(y * 8));
   VG_TRY(l.w_partial.alloc((size_t)Bc * 256 * 8));
   VG_TRY(l.chi2.alloc((size_t)Bc * 8));
-  l.chunk = LANE_MAX_B;
+  l.chunk = cap;
   return VG_OK;
 }
 
@@ -2492,10 +2505,9 @@ int chi2_chunk(vg_plan* plan, const double* theta_dev, long long Bc, double* chi
     else if (cp->wdata_dirty) VG_TRY(rewhiten_data(plan, *cp, st));
   }
   VG_TRY(expand_params(plan, theta_dev, Bc, status_dev, st));
-  // thin batches: the correlations spread over lanes (below the batch size of the split-integer
-  // GEMMs, whose digit planes of the batch are one plan-wide workspace)
+  // thin batches: the correlations spread over lanes
   const bool laned = plan->two_lanes && lanes_enabled() && !plan->profile && plan->corrs.size() > 1 &&
-                     Bc <= std::min<long long>(LANE_MAX_B, plan->ozaki_min_batch - 1);
+                     Bc <= lane_max_batch();
   const int n_lanes = laned ? (int)std::min<size_t>(1 + vg_plan::EXTRA_LANES, plan->corrs.size()) : 1;
   for (int l = 1; l < n_lanes; ++l) {
     vg_plan::Lane& lane = plan->lanes[l - 1];
