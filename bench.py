@@ -777,9 +777,9 @@ def main():
                 # capture; algorithmic bytes of that launch: 8 x (1024 + 1590) x 37680 digit bytes + 7 x 1024 x
                 # 1600 x 8 of partial sums
                 'traffic': 1.283e9 if B == 1024 else None, 'algorithmic_bytes_of_that_launch': 0.880e9,
-                'traffic_source': 'profiles/r02_ncu_full_c2_final_raw.csv (ozaki_gemm_kernel<8, 2>, grid 8x26x7: 1.195 GB '
+                'traffic_source': 'profiles/r02_ncu_full_c2_lanes_raw.csv (ozaki_gemm_kernel<8, 2>, grid 8x26x7: 1.195 GB '
                                   'read + 0.088 GB written)',
-                'ncu_tensor_pipe_active': [0.738, 0.726],
+                'ncu_tensor_pipe_active': [0.726, 0.797],
                 'share_of_step': metal_ms / ms_per_step_staged}
         else:
             gemm_ms = sum(stage_ms[s] for s in ('hankel_gemm', 'metal_gemm', 'dm_gemm', 'chi2_gemm'))
