@@ -846,6 +846,7 @@ def main():
                        'fused_distortion_metal_operator': [{'rows': r, 'digits': s} for r, s in fused],
                        'whitened_chi2': [engine.whitened(ci) for ci in range(len(engine.infos))],
                        'lanes': 'correlation i on stream i % 4 (VG_OPT_LANES); one stream in the pass with stage events',
+                       'plan_device_bytes': int(engine.device_bytes()),
                        'l2': 'inputs larger than L2: ~2.9 GB of static operands + ~2 GB of workspace '
                              'streamed per step'},
             'clocks': clock_info,

@@ -368,7 +368,8 @@ int vg_plan_static_status(const vg_plan* plan);
 /* chi2 passes of at most 96 vectors are replayed as CUDA graphs (after two ordinary calls per batch
  * size; VG_GRAPHS=0 in the environment turns it off): number of replays so far */
 int64_t vg_plan_graph_replays(const vg_plan* plan);
-/* Bytes of device memory held by the plan (static state + current workspace) */
+/* Bytes of device memory held by the plan: static operands, the whitened / fused operators and the digit
+ * planes built so far, Monte Carlo mocks, the current workspace and its per-lane copies (VG_OPT_LANES) */
 int64_t vg_plan_device_bytes(const vg_plan* plan);
 
 /* ---------------------------------------------------------------------------------

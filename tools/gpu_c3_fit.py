@@ -36,4 +36,9 @@ for rep in range(4):
     out.append({'wall_s': time.perf_counter() - t0, 'chi2_evaluations': int(mini.n_eval), 'fval': float(mini.fmin.fval),
                 'graph_replays': int(engine.lib.vg_plan_graph_replays(engine.handle) - r0)})
     print(out[-1], flush=True)
+print('plan bytes after the fits', engine.device_bytes() / 1e9, 'GB')
+theta = synthetic.draw_theta(vega, 1024, width=1.0, names=names)
+engine.chi2_device(engine.theta_tensor(theta))
+torch.cuda.synchronize()
+print('plan bytes after a 1024-vector chunk', engine.device_bytes() / 1e9, 'GB')
 print(json.dumps(out))

@@ -1206,11 +1206,22 @@ int64_t vg_plan_device_bytes(const vg_plan* plan) {
     n += c.d_mcat.bytes + c.d_dmat.bytes + c.d_dmat_masked.bytes + c.d_invcov.bytes + c.d_mom_ktab.bytes + c.d_frozen.bytes +
          c.d_mxi_tab.bytes + c.d_fold_tab.bytes + c.d_mcat_fold.bytes + c.d_mrp.bytes + c.d_mrp_fold.bytes;
     for (auto& b : c.coords) n += b.bytes;
+    // whitened / fused operators, Monte Carlo mocks, and the digit planes built so far
+    n += c.d_white.bytes + c.d_wd.bytes + c.d_wdata.bytes + c.d_wmocks.bytes + c.d_dmcat.bytes + c.d_mocks.bytes +
+         c.d_evolfac.bytes;
+    for (const OzakiOperand* op : {&c.oz_mcat, &c.oz_mcat_fold, &c.oz_dmat, &c.oz_dmat_masked, &c.oz_wd, &c.oz_dmcat})
+      n += op->planes.bytes + op->exps.bytes;
+    for (auto& t : c.vt_tab) n += t.bytes;
   }
   n += plan->d_global_invcov.bytes;
   n += plan->w_pfull.bytes + plan->w_pkell.bytes + plan->w_tables.bytes + plan->w_core.bytes +
        plan->w_xmet.bytes + plan->w_met.bytes + plan->w_x.bytes + plan->w_y.bytes + plan->w_diff.bytes +
-       plan->w_partial.bytes + plan->w_split.bytes;
+       plan->w_partial.bytes + plan->w_split.bytes + plan->w_fold.bytes + plan->w_mety.bytes + plan->w_vtw.bytes +
+       plan->oz_A.planes.bytes + plan->oz_A.exps.bytes;
+  for (const auto& l : plan->lanes)     // the lanes' copies of the per-correlation workspace (VG_OPT_LANES)
+    n += l.w_pkell.bytes + l.w_tables.bytes + l.w_core.bytes + l.w_xmet.bytes + l.w_met.bytes + l.w_x.bytes +
+         l.w_y.bytes + l.w_diff.bytes + l.w_partial.bytes + l.w_split.bytes + l.w_fold.bytes + l.w_mety.bytes +
+         l.w_vtw.bytes + l.oz_A.planes.bytes + l.oz_A.exps.bytes + l.chi2.bytes;
   return (int64_t)n;
 }
 
