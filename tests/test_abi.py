@@ -52,3 +52,20 @@ def test_product_does_not_import_oracle():
     for path in (REPO / 'vega_b200').rglob('*.py'):
         text = path.read_text()
         assert 'import oracle' not in text and 'from oracle' not in text, path
+
+
+def test_option_and_status_constants_match_header():
+    """The binding's OPT_* / STATUS_* / error codes are the header's #defines (a binder reads the header)."""
+    text = (REPO / 'include' / 'vega_b200.h').read_text()
+    defines = {m.group(1): int(m.group(2), 0) for m in re.finditer(r'#define\s+(VG_[A-Z0-9_]+)\s+(-?(?:0x)?[0-9a-fA-F]+)\b', text)}
+    options = {k: v for k, v in defines.items() if k.startswith('VG_OPT_')}
+    assert len(options) >= 10 and sorted(options.values()) == list(range(len(options)))
+    for name, value in options.items():
+        assert getattr(_lib, name[3:]) == value, name
+    for name, value in defines.items():
+        if name.startswith('VG_STATUS_') and hasattr(_lib, name[3:]):
+            assert getattr(_lib, name[3:]) == value, name
+    # every option is accepted or rejected by value, never unknown: the dispatcher names each of them
+    source = (REPO / 'vega_b200' / 'csrc' / 'vega_b200.cu').read_text()
+    for name in options:
+        assert f'option == {name}' in source, name
