@@ -1736,7 +1736,7 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
     for (int nm : L.vt_nm) ldw = std::max(ldw, pad16((long long)c.vt_n * nm));
     VG_TRY(plan->w_vtw.ensure((size_t)Ev * (size_t)std::max(plan->chunk, Bc) * ldw * 8));
     double* W = plan->w_vtw.as<double>();
-    dim3 wgrid(vg_cdiv(Bc, 128), (unsigned)Ev);
+    dim3 wgrid((unsigned)Bc, (unsigned)Ev);
     vg::vtab_weights_kernel<<<wgrid, 128, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_vt_ids.as<int>(),
                                                   L.d_vt_terms.as<vg::VtTerms>(), plan->w_pfull.as<double>(), plan->npf,
                                                   (int)Bc, c.vt_map, c.vt_n, ldw, W);

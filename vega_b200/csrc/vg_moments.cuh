@@ -449,31 +449,50 @@ vtab_cheb_kernel(const double* __restrict__ node, int nq, VtTerms terms, int row
 }
 
 // Hot path: W[j][b][n*nm_j + i] = T_n(t(sigma_b)) * c_{terms_j[i]}(theta_b; evaluation ids[j]), zero
-// beyond n_keep*nm_j up to ldw.  terms: [n_ids] term lists.  grid = (ceil(B/128), n_ids), block 128.
+// beyond n_keep*nm_j up to ldw.  terms: [n_ids] term lists.  grid = (B, n_ids), block 128: one block per
+// row of W -- thread 0 evaluates the coefficients and t, every thread runs the Chebyshev recurrence up
+// to its own order (at most 64 steps) and the row is written coalesced.  (One thread per row wrote its
+// ~300 doubles one after the other, ldw doubles apart from its neighbour's: 47 us whatever the batch,
+// on the critical path of a single vector.)
 __global__ void __launch_bounds__(128)
 vtab_weights_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__ ids,
                     const VtTerms* __restrict__ terms, const double* __restrict__ pfull, int npf, int B,
                     VtMap map, int n_keep, int ldw, double* __restrict__ W) {
-  const int b = blockIdx.x * 128 + threadIdx.x, j = blockIdx.y;
+  const int b = blockIdx.x, j = blockIdx.y;
   if (b >= B) return;
-  const vg_eval_desc& d = evals[ids[j]];
   const VtTerms& tm = terms[j];
   const int nm = tm.n;
-  const double* p = pfull + (long long)b * npf;
-  double q[MOM_MAX];
-  moment_coefs_of(d, p, q);
-  const int col = d.idx_velo[0] >= 0 ? d.idx_velo[0] : d.idx_velo[1];
-  const double sg = fmin(fmax(fabs(p[col]), map.lo), map.hi);
-  double t = (2.0 * vt_tau(sg, map.eps) - map.tau_lo - map.tau_hi) / (map.tau_hi - map.tau_lo);
-  t = fmin(fmax(t, -1.0), 1.0);
-  double* w = W + ((long long)j * B + b) * ldw;
-  double t0 = 1.0, t1 = t;
-  for (int n = 0; n < n_keep; ++n) {
-    for (int i = 0; i < nm; ++i) w[n * nm + i] = t0 * q[tm.idx[i]];
-    const double t2 = 2.0 * t * t1 - t0;
-    t0 = t1; t1 = t2;
+  __shared__ double qs[MOM_MAX];
+  __shared__ double ts;
+  if (threadIdx.x == 0) {
+    const vg_eval_desc& d = evals[ids[j]];
+    const double* p = pfull + (long long)b * npf;
+    double q[MOM_MAX];
+    moment_coefs_of(d, p, q);
+#pragma unroll
+    for (int i = 0; i < MOM_MAX; ++i) qs[i] = q[i];
+    const int col = d.idx_velo[0] >= 0 ? d.idx_velo[0] : d.idx_velo[1];
+    const double sg = fmin(fmax(fabs(p[col]), map.lo), map.hi);
+    const double t = (2.0 * vt_tau(sg, map.eps) - map.tau_lo - map.tau_hi) / (map.tau_hi - map.tau_lo);
+    ts = fmin(fmax(t, -1.0), 1.0);
   }
-  for (int k = n_keep * nm; k < ldw; ++k) w[k] = 0.0;
+  __syncthreads();
+  const double t = ts;
+  double* w = W + ((long long)j * B + b) * ldw;
+  const int n_used = n_keep * nm;
+  for (int k = threadIdx.x; k < ldw; k += 128) {
+    double v = 0.0;
+    if (k < n_used) {
+      const int n = k / nm, i = k - n * nm;
+      double t0 = 1.0, t1 = t;
+      for (int m = 0; m < n; ++m) {
+        const double t2 = 2.0 * t * t1 - t0;
+        t0 = t1; t1 = t2;
+      }
+      v = t0 * qs[tm.idx[i]];
+    }
+    w[k] = v;
+  }
 }
 
 // flag[0] |= 1 when a vector's sigma (column col of theta) lies outside [lo, hi] or is not finite
