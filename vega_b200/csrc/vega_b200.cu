@@ -1724,10 +1724,12 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   }
   if (Em > 0) {  // moment form: knot tables as a 3/9-term combination of static tables
     ProfScope prof(plan, PROF_MOMENT, st);
-    dim3 grid(vg_cdiv(row_len, 256 * vg::MOM_XPT), (unsigned)Em, (unsigned)vg_cdiv(Bc, vg::MOM_NB));
+    const long long stretches = vg_cdiv(row_len, 256 * vg::MOM_XPT);
+    const int x_iters = vg::moment_x_iters(stretches, (long long)Em * vg_cdiv(Bc, vg::MOM_NB));
+    dim3 grid((unsigned)vg_cdiv(stretches, x_iters), (unsigned)Em, (unsigned)vg_cdiv(Bc, vg::MOM_NB));
     vg::moment_tables_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_mom_ids.as<int>(), Em,
                                                   plan->w_pfull.as<double>(), plan->npf, (int)Bc,
-                                                  c.d_mom_ktab.as<double>(), (int)row_len, Em + Ev, tables_mom);
+                                                  c.d_mom_ktab.as<double>(), (int)row_len, Em + Ev, tables_mom, x_iters);
     VG_LAUNCHED();
   }
   if (Ev > 0) {  // velocity-dispersion tables: weights, then one GEMM per evaluation
@@ -1777,13 +1779,15 @@ int run_corr_front(vg_plan* plan, Corr& c, long long Bc, int* status_dev, cudaSt
   if (!L.mxi_ids.empty()) {  // xi stage in moment form
     ProfScope prof(plan, PROF_MXI, st);
     const int n_mxi = (int)L.mxi_ids.size();
-    dim3 grid(vg_cdiv(c.ld_model, 256), (unsigned)n_mxi, (unsigned)vg_cdiv(Bc, vg::MXI_NB));
+    const long long stretches = vg_cdiv(c.ld_model, 256);
+    const int x_iters = vg::moment_x_iters(stretches, (long long)n_mxi * vg_cdiv(Bc, vg::MXI_NB));
+    dim3 grid((unsigned)vg_cdiv(stretches, x_iters), (unsigned)n_mxi, (unsigned)vg_cdiv(Bc, vg::MXI_NB));
     vg::moment_xi_kernel<<<grid, 256, 0, st>>>(c.d_evals.as<vg_eval_desc>(), L.d_mxi_ids.as<int>(),
                                               L.d_mxi_owner.as<int>(), plan->w_pfull.as<double>(), plan->npf,
                                               (int)Bc, c.d_mxi_tab.as<double>(),
                                               L.mxi_rows.empty() ? nullptr : L.d_mxi_rows.as<int>(), c.ld_model,
                                               plan->w_core.as<double>(), plan->w_xmet.as<double>(),
-                                              L.d_metal_map.as<int>(), std::max(L.n_metal, 1));
+                                              L.d_metal_map.as<int>(), std::max(L.n_metal, 1), x_iters);
     VG_LAUNCHED();
   }
   if (upto <= 3) return VG_OK;

@@ -160,12 +160,22 @@ __host__ __device__ __forceinline__ void moment_coefs_of(const vg_eval_desc& d, 
 // Hot path: tables[b][j][x] = sum_m c_m(theta_b, eval ids[j]) * ktab[j][m][x],  x over the
 // n_ell*2*n_out_pad knot values and second derivatives of the evaluation.
 // n_slots >= n_ids tables per vector (the velocity-dispersion tables follow the n_ids of this kernel).
-// grid = (ceil(row_len / (256*MOM_XPT)), n_ids, ceil(B / MOM_NB)), block 256.
+// grid = (ceil(row_len / (256*MOM_XPT*x_iters)), n_ids, ceil(B / MOM_NB)), block 256.  A block covers
+// x_iters stretches of 256*MOM_XPT values: the coefficients of its MOM_NB vectors (a serial chain of
+// parameter loads on MOM_NB threads while the others wait) are paid once per block, so large batches
+// take long blocks (moment_x_iters) and a thin batch keeps many short ones.
 constexpr int MOM_NB = 4, MOM_XPT = 2;
+// stretches per block: all of them once the grid still holds `enough` blocks, fewer for thin batches
+inline int moment_x_iters(long long stretches, long long blocks_per_stretch, long long enough = 1184) {
+  long long it = stretches * blocks_per_stretch / enough;
+  if (it < 1) it = 1;
+  if (it > stretches) it = stretches;
+  return (int)it;
+}
 __global__ void __launch_bounds__(256)
 moment_tables_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__ ids, int n_ids,
                      const double* __restrict__ pfull, int npf, int B, const double* __restrict__ ktab,
-                     int row_len, int n_slots, double* __restrict__ tables) {
+                     int row_len, int n_slots, double* __restrict__ tables, int x_iters) {
   __shared__ double cq[MOM_NB][MOM_MAX];
   __shared__ int s_nm;
   const int j = blockIdx.y, b0 = blockIdx.z * MOM_NB;
@@ -181,9 +191,10 @@ moment_tables_kernel(const vg_eval_desc* __restrict__ evals, const int* __restri
   __syncthreads();
   const int nm = s_nm;
   const double* kt = ktab + (long long)j * MOM_MAX * row_len;
+  for (int it = 0; it < x_iters; ++it)
 #pragma unroll
   for (int u = 0; u < MOM_XPT; ++u) {
-    const int x = (blockIdx.x * MOM_XPT + u) * 256 + threadIdx.x;
+    const int x = ((blockIdx.x * x_iters + it) * MOM_XPT + u) * 256 + threadIdx.x;
     if (x >= row_len) break;
     double acc[MOM_NB];
 #pragma unroll
@@ -222,14 +233,14 @@ __device__ __forceinline__ double moment_weight(const vg_eval_desc& d, const dou
 //   out[b][slot(j)][bin] = w_j(theta_b) * sum_m c_m(theta_b; owner(j)) * X[j][m][bin]
 // -- 3, 9 or 14 FMAs per bin instead of a knot-table row and a gather.  `owners[j]` is the
 // evaluation whose P(k,mu) the table belongs to (j itself unless it shares a table).
-// grid = (ceil(ld / 256), n_ids, ceil(B / MXI_NB)), block 256.
+// grid = (ceil(ld / (256*x_iters)), n_ids, ceil(B / MXI_NB)), block 256 (x_iters: as in moment_tables_kernel).
 constexpr int MXI_NB = 8;
 __global__ void __launch_bounds__(256)
 moment_xi_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__ ids,
                  const int* __restrict__ owners, const double* __restrict__ pfull, int npf, int B,
                  const double* __restrict__ X, const int* __restrict__ rows, int ld,
                  double* __restrict__ core, double* __restrict__ xmet,
-                 const int* __restrict__ metal_map, int n_metal) {
+                 const int* __restrict__ metal_map, int n_metal, int x_iters) {
   __shared__ double cq[MXI_NB][MOM_MAX];
   __shared__ int s_nm, s_slot;
   const int j = blockIdx.y, b0 = blockIdx.z * MXI_NB;
@@ -248,26 +259,28 @@ moment_xi_kernel(const vg_eval_desc* __restrict__ evals, const int* __restrict__
     }
   }
   __syncthreads();
-  const int x = blockIdx.x * 256 + threadIdx.x;
-  if (x >= ld) return;
   const int nm = s_nm;
-  const double* xt = X + (long long)(rows ? rows[j] : j) * MOM_MAX * ld + x;
-  double acc[MXI_NB];
-#pragma unroll
-  for (int e = 0; e < MXI_NB; ++e) acc[e] = 0.0;
-  for (int m = 0; m < nm; ++m) {
-    const double v = __ldg(xt + (long long)m * ld);
-#pragma unroll
-    for (int e = 0; e < MXI_NB; ++e) acc[e] = fma(cq[e][m], v, acc[e]);
-  }
   const int slot = s_slot;
+  for (int it = 0; it < x_iters; ++it) {
+    const int x = (blockIdx.x * x_iters + it) * 256 + threadIdx.x;
+    if (x >= ld) return;
+    const double* xt = X + (long long)(rows ? rows[j] : j) * MOM_MAX * ld + x;
+    double acc[MXI_NB];
 #pragma unroll
-  for (int e = 0; e < MXI_NB; ++e) {
-    const int b = b0 + e;
-    if (b >= B) break;
-    double* out = slot < 2 ? core + ((long long)slot * B + b) * ld
-                           : xmet + ((long long)b * n_metal + metal_map[slot - 2]) * ld;
-    out[x] = acc[e];
+    for (int e = 0; e < MXI_NB; ++e) acc[e] = 0.0;
+    for (int m = 0; m < nm; ++m) {
+      const double v = __ldg(xt + (long long)m * ld);
+#pragma unroll
+      for (int e = 0; e < MXI_NB; ++e) acc[e] = fma(cq[e][m], v, acc[e]);
+    }
+#pragma unroll
+    for (int e = 0; e < MXI_NB; ++e) {
+      const int b = b0 + e;
+      if (b >= B) break;
+      double* out = slot < 2 ? core + ((long long)slot * B + b) * ld
+                             : xmet + ((long long)b * n_metal + metal_map[slot - 2]) * ld;
+      out[x] = acc[e];
+    }
   }
 }
 
